@@ -1,0 +1,239 @@
+"""Benchmark of the Tacotron2 hot path (BASELINE.json metric: mel frames/sec, AR decode).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (BASELINE.json configs[1]): vanilla-ljspeech-stop autoregressive inference,
+batch 64 x 200 characters, 1000 mel frames per utterance (the random-init stop gate is biased so it
+never fires: the full 1000 frames are decoded, nothing is skipped), synthetic seeded inputs and weights.
+A "step" = one whole Tacotron2.forward: encoder -> memory projection -> 1000-frame persistent decoder
+kernel -> postnet -> residual/masking.  N > 1: one process per GPU, each with its own utterance shard
+(weak scaling, no data-path collective); timing = max over ranks of device time.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from tacotron2_b200 import synth  # noqa: E402
+
+B, L, T = 64, 200, 1000
+METRIC, UNIT = "mel_frames_per_sec_ar_decode", "frames/s"
+WORKLOAD = "C2: vanilla-ljspeech-stop AR inference, batch 64 x 200 chars x 1000 frames, fp32, stop gate evaluated (never fires)"
+# kernels launched by one Tacotron2.forward (AR): embed 1, encoder conv 3, BiLSTM input proj 1, BiLSTM 1,
+# att_encoder 1, persistent decoder 1, postnet conv 5, finalize 1  (memsets / memcpys not counted)
+LAUNCHES_PER_STEP = 14
+
+
+def algorithmic_bytes_per_frame_step(a=synth.VANILLA, b=B, l=L):
+    """bytes one decoder step must move for the whole batch, fp32, LSTM weights
+    not on-chip: memory + processed memory read once, attention-weight traffic, recurrent state, weights."""
+    ef, h, s = a.encoded_full_dim, a.att_rnn_dim, 4
+    act = b * l * (ef + a.att_dim) * s + 5 * b * l * s + b * (8 * h + ef + a.num_mels + a.prenet_dim) * s
+    lstm = 4 * h * (a.prenet_dim + ef + h) + 4 * h * (h + ef + a.controls_dim + h)
+    small = a.att_dim * h + (a.num_mels + 1) * (h + ef) + a.prenet_dim * (a.num_mels + a.prenet_dim) + 32 * 62 + a.att_dim * 33
+    return act + (lstm + small) * s
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 3 + i and r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def oracle_sample(frames, threads):
+    """Times the CPU oracle (port of the reference's torch-CPU path) on the same workload, bounded to
+    `frames` decoder frames (+ encoder + postnet on those frames).  Returns frames/s."""
+    from oracle import tacotron2_oracle as O  # the one place bench.py runs the oracle: the CPU baseline
+
+    torch.set_num_threads(threads)
+    sd = synth.synth_state_dict(synth.VANILLA, seed=0, gate_shift=5.0)
+    b = synth.synth_batch(synth.VANILLA, B, L, 8, seed=1234)
+    masks = synth.synth_masks(synth.VANILLA, B, L, frames, seed=7)
+    t0 = time.perf_counter()
+    with torch.no_grad():
+        out = O.tacotron2_forward(sd, synth.VANILLA, b["chars_idx"], b["chars_idx_len"], False, max_len_override=frames, masks=masks)
+    dt = time.perf_counter() - t0
+    assert out[0].shape[1] == frames
+    return B * frames / dt, dt
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    frames = 24  # bounded sample per step: ~2-4 s of host time
+    for _ in range(args.warmup):
+        oracle_sample(frames, threads)
+    t = []
+    for _ in range(args.steps):
+        v, dt = oracle_sample(frames, threads)
+        t.append(dt)
+    ms = 1e3 * sum(t) / len(t)
+    value = B * frames / (ms / 1e3)
+    sample = f"B={B} L={L}, first {frames} of {T} AR frames + encoder + postnet per step, torch CPU fp32"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    from tacotron2_b200.model import Tacotron2
+
+    assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    a = synth.VANILLA
+    model = Tacotron2(**a.kwargs()).to(dev).eval()
+    model.load_state_dict(synth.synth_state_dict(a, seed=0, gate_shift=5.0))
+    batch = synth.synth_batch(a, B, L, 8, seed=1234 + rank)
+    chars_h, lens_h = batch["chars_idx"].pin_memory(), batch["chars_idx_len"].pin_memory()
+    chars_d, lens_d = chars_h.to(dev), lens_h.to(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    out_h = torch.empty(B, T, a.num_mels).pin_memory()
+    len_h = torch.empty(B, dtype=torch.int64).pin_memory()
+
+    def step_resident():
+        with torch.no_grad():
+            return model(chars_d, lens_d, False, max_len_override=T)[1]
+
+    def step_e2e():
+        with torch.no_grad():
+            c, n = chars_h.to(dev, non_blocking=True), lens_h.to(dev, non_blocking=True)
+            mels, post, gates, al = model(c, n, False, max_len_override=T)
+            out_h[:, : post.shape[1]].copy_(post, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            return post
+
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    for _ in range(2):
+        step_e2e()
+
+    def timed(fn, k):
+        total, dec = 0.0, 0.0
+        for _ in range(k):
+            flush.zero_()  # flush L2 between timed iterations (untimed)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            model._prof = []
+            e0.record()
+            out = fn()
+            e1.record()
+            e1.synchronize()
+            assert out.shape[1] == T, "frames were skipped"
+            total += e0.elapsed_time(e1)
+            dec += sum(x.elapsed_time(y) for x, y in model._prof)
+        model._prof = None
+        return total, dec
+
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    t_res, t_dec = timed(step_resident, args.steps)
+    barrier()
+    t_e2e, _ = timed(step_e2e, args.steps)
+    barrier()
+    clocks = sampler.stop()
+    if world > 1:
+        tt = torch.tensor([t_res, t_e2e, t_dec], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t_res, t_e2e, t_dec = (float(x) for x in tt)
+    if rank != 0:
+        dist.destroy_process_group()
+        return
+    ms = t_res / args.steps
+    frames = world * B * T
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    dec_ms = t_dec / args.steps
+    bytes_launch = algorithmic_bytes_per_frame_step() * T
+    achieved = bytes_launch / (dec_ms * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": frames / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "l2": "flushed between timed iterations (256 MiB write)", "utterances_per_gpu": B,
+                   "us_per_decoder_step": 1e3 * dec_ms / T, "parallelism": f"replicas x{world}, no collective"},
+        "e2e": {"value": frames / (t_e2e / args.steps * 1e-3), "unit": UNIT,
+                "h2d_bytes_per_step": chars_h.numel() * 8 + lens_h.numel() * 8, "d2h_bytes_per_step": out_h.numel() * 4 + 4},
+        "gpu_launches": LAUNCHES_PER_STEP * args.steps,
+        "clocks": clocks,
+        "roofline": {"kernel": "decoder_persistent_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "peak_source": "measured" if peaks else "fallback",
+                     "algorithmic_bytes_per_launch": bytes_launch, "kernel_ms": dec_ms, "share_of_step": dec_ms / ms},
+    }
+    if not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        oracle_sample(4, threads)  # warm-up
+        v, dt = oracle_sample(150, threads)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": f"B={B} L={L}, first 150 of {T} AR frames + encoder + postnet, torch CPU fp32, {dt:.1f} s"}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

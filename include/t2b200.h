@@ -1,0 +1,105 @@
+/* libt2b200 -- C ABI of the B200-native Tacotron2 acoustic-model hot path.
+ *
+ * The reference (mattm458/tacotron2) is pure Python/PyTorch and has no FFI of its own; the
+ * boundary this library sits behind is the reference's nn.Module API.  Every entry point
+ * below names the reference function it replaces (paths relative to the reference root);
+ * tacotron2_b200/model.py mirrors those modules and binds these symbols with ctypes
+ * (INTEGRATION.md shows the stub).
+ *
+ * Conventions: all pointers are DEVICE pointers unless stated; tensors are dense, row-major,
+ * fp32 unless stated; `stream` is a cudaStream_t passed as void*; calls are asynchronous on
+ * that stream and never synchronise the host; no allocation or ownership transfer happens
+ * inside a call (outputs and a workspace of t2_workspace_bytes() are the caller's); the
+ * return value is 0 on success or a negative T2_ERR_* code, with t2_last_error() giving a
+ * thread-local message.  A context is not thread-safe.  There is no CPU fallback.
+ */
+#ifndef T2B200_H
+#define T2B200_H
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct t2_ctx t2_ctx;
+
+/* Constructor arguments of Tacotron2 (model/tacotron2.py:15-34). */
+typedef struct {
+  int num_chars, encoded_dim, encoder_kernel_size, num_mels, prenet_dim;
+  int att_rnn_dim, att_dim, rnn_hidden_dim, postnet_dim;
+  float dropout;
+  int num_speakers;     /* 0 = speaker tokens off */
+  int controls_dim;     /* 0 = controls off */
+  int description_dim;  /* 0 = description embeddings off (else 768 -> Linear -> 128) */
+} t2_model_config;
+
+const char* t2_last_error(void);
+int t2_abi_version(void);
+
+/* Context = one model replica on the current device. */
+int t2_ctx_create(const t2_model_config* cfg, t2_ctx** out);
+int t2_ctx_destroy(t2_ctx* ctx);
+/* Register the device pointer of one fp32 parameter / buffer under its reference state-dict
+ * key ("decoder.att_rnn.weight_ih", ...).  Zero-copy: the pointer must stay valid. */
+int t2_ctx_set_param(t2_ctx* ctx, const char* key, const float* ptr, long long numel);
+/* (Re)build the packed copies the kernels read (call after loading or updating weights). */
+int t2_ctx_commit(t2_ctx* ctx, void* stream);
+/* Upper bound of the workspace any call below needs for these sizes. */
+long long t2_workspace_bytes(const t2_ctx* ctx, int B, int L, int T);
+
+/* Encoder.forward (model/encoder.py:54-67).  chars_idx (B,L) int64, lens (B) int64 ->
+ * encoded (B,L,E).  keep: NULL (eval) or train-mode dropout keep-masks (3,B,L,E) uint8.
+ * train != 0 uses BatchNorm batch statistics (not available in this revision -> T2_ERR_UNSUPPORTED). */
+int t2_encoder_fwd(t2_ctx* ctx, const long long* chars_idx, const long long* lens, int B, int L, int train,
+                   const unsigned char* keep, float* encoded, void* ws, long long ws_bytes, void* stream);
+
+/* Conditioning + attention memory projection (model/tacotron2.py:201-212,229).
+ * encoded (B,L,E), speaker_id (B) int64 or NULL, description (B,Ddesc) or NULL ->
+ * memory (B,L,EF), processed_memory (B,L,A). */
+int t2_memory_fwd(t2_ctx* ctx, const float* encoded, const long long* speaker_id, const float* description, int B, int L,
+                  float* memory, float* processed_memory, void* ws, long long ws_bytes, void* stream);
+
+/* The autoregressive frame loop of Tacotron2.forward with teacher_forcing=False
+ * (model/tacotron2.py:262-325) as ONE persistent cooperative kernel: prenet, attention
+ * LSTMCell, location-sensitive attention, decoder LSTMCell, mel/gate projection, stop logic.
+ * mask (B,L) uint8 1 = padded; controls (B,C) or NULL; prenet_keep (max_len+1,2,B,P) uint8
+ * keep-masks for AlwaysDropout or NULL (in-kernel RNG from `seed`).
+ * Outputs: mels (B,max_len,M), gates (B,max_len), alignments (B,max_len,L) -- rows >= *n_frames
+ * are left untouched; lengths (B) int64; n_frames (1) int32 (device). B <= 64 per call. */
+int t2_decode_ar(t2_ctx* ctx, const float* memory, const float* processed_memory, const unsigned char* mask,
+                 const float* controls, int B, int L, int max_len, const unsigned char* prenet_keep,
+                 unsigned long long seed, float* mels, float* gates, float* alignments, long long* lengths,
+                 int* n_frames, void* ws, long long ws_bytes, void* stream);
+
+/* Teacher-forced frame loop (model/tacotron2.py:255-258,276-317): prenet over the shifted target
+ * in bulk, then the same persistent kernel without prenet/stop phases.  mel_target (B,T,M);
+ * train != 0 applies the p=0.1 hidden-state dropouts (att_keep/rnn_keep (T,B,H) or RNG). */
+int t2_decode_tf(t2_ctx* ctx, const float* memory, const float* processed_memory, const unsigned char* mask,
+                 const float* controls, const float* mel_target, int B, int L, int T, const unsigned char* prenet_keep,
+                 int train, const unsigned char* att_keep, const unsigned char* rnn_keep, unsigned long long seed,
+                 float* mels, float* gates, float* alignments, void* ws, long long ws_bytes, void* stream);
+
+/* Decoder.forward, one frame from explicit state (model/decoder.py:53-119).  All state tensors
+ * are (B,dim) row-major; w / w_cum (B,L); *_out may alias nothing.  w_cum_out = w_cum + w_out. */
+int t2_decoder_step(t2_ctx* ctx, const float* prev_mel_prenet, const float* att_h, const float* att_c, const float* att_ctx,
+                    const float* w, const float* w_cum, const float* rnn_h, const float* rnn_c, const float* memory,
+                    const float* processed_memory, const unsigned char* mask, const float* controls, int B, int L,
+                    float* mel_out, float* gate_out, float* att_h_out, float* att_c_out, float* att_ctx_out, float* w_out,
+                    float* w_cum_out, float* rnn_h_out, float* rnn_c_out, void* ws, long long ws_bytes, void* stream);
+
+/* prenet (model/tacotron2.py:85-92) on N rows: x (N,M) -> out (N,P); keep1/keep2 (N,P) uint8 or NULL (RNG). */
+int t2_prenet_fwd(t2_ctx* ctx, const float* x, const unsigned char* keep1, const unsigned char* keep2,
+                  unsigned long long seed, int N, float* out, void* ws, long long ws_bytes, void* stream);
+
+/* Postnet.forward (model/postnet.py:51-52) on channels-last input: mels (B,T,M) with row stride
+ * t_stride frames per batch item -> out (B,T,M) dense.  keep: NULL or (5,B,T,postnet_dim) uint8. */
+int t2_postnet_fwd(t2_ctx* ctx, const float* mels, int t_stride, int B, int T, int train, const unsigned char* keep,
+                   float* out, void* ws, long long ws_bytes, void* stream);
+
+/* Residual + output masking (model/tacotron2.py:333-345), in place: post <- masked(mels + post),
+ * mels <- masked(mels), gates <- masked_fill(-1000).  lengths (B) int64. */
+int t2_finalize(t2_ctx* ctx, float* mels, float* post, float* gates, const long long* lengths, int B, int T, int t_stride,
+                void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,74 @@
+"""ctypes binding of libt2b200.so (C ABI declared in include/t2b200.h).
+
+The library is built in-tree by ``__graft_entry__.build()`` (nvcc, sm_100a).  There is no
+fallback of any kind: if the shared object is missing or a call fails, this raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libt2b200.so")
+
+
+class T2ModelConfig(C.Structure):
+    _fields_ = [
+        ("num_chars", C.c_int), ("encoded_dim", C.c_int), ("encoder_kernel_size", C.c_int), ("num_mels", C.c_int),
+        ("prenet_dim", C.c_int), ("att_rnn_dim", C.c_int), ("att_dim", C.c_int), ("rnn_hidden_dim", C.c_int),
+        ("postnet_dim", C.c_int), ("dropout", C.c_float), ("num_speakers", C.c_int), ("controls_dim", C.c_int),
+        ("description_dim", C.c_int),
+    ]
+
+
+_P, _I, _LL, _ULL = C.c_void_p, C.c_int, C.c_longlong, C.c_ulonglong
+
+# name -> (restype, argtypes); kept in sync with include/t2b200.h (tests/test_abi.py checks the symbol list)
+SIGNATURES = {
+    "t2_last_error": (C.c_char_p, []),
+    "t2_abi_version": (_I, []),
+    "t2_ctx_create": (_I, [C.POINTER(T2ModelConfig), C.POINTER(_P)]),
+    "t2_ctx_destroy": (_I, [_P]),
+    "t2_ctx_set_param": (_I, [_P, C.c_char_p, _P, _LL]),
+    "t2_ctx_commit": (_I, [_P, _P]),
+    "t2_workspace_bytes": (_LL, [_P, _I, _I, _I]),
+    "t2_encoder_fwd": (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _P, _LL, _P]),
+    "t2_memory_fwd": (_I, [_P, _P, _P, _P, _I, _I, _P, _P, _P, _LL, _P]),
+    "t2_decode_ar": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _P, _ULL, _P, _P, _P, _P, _P, _P, _LL, _P]),
+    "t2_decode_tf": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _I, _P, _P, _ULL, _P, _P, _P, _P, _LL, _P]),
+    "t2_decoder_step": (_I, [_P] + [_P] * 12 + [_I, _I] + [_P] * 9 + [_P, _LL, _P]),
+    "t2_prenet_fwd": (_I, [_P, _P, _P, _P, _ULL, _I, _P, _P, _LL, _P]),
+    "t2_postnet_fwd": (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _P, _LL, _P]),
+    "t2_finalize": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _P]),
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Load the shared library (once).  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'`. "
+            "tacotron2_b200 has no CPU or PyTorch fallback."
+        )
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing
+        fn.restype, fn.argtypes = res, args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str = "libt2b200") -> None:
+    if rc != 0:
+        msg = load().t2_last_error().decode(errors="replace")
+        raise RuntimeError(f"{what} failed (code {rc}): {msg}")
+
+
+def ptr(t):
+    """Device pointer of a torch tensor (or None)."""
+    return None if t is None else C.c_void_p(t.data_ptr())

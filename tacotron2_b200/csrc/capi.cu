@@ -1,0 +1,636 @@
+// C ABI of libt2b200 (see include/t2b200.h): context, weight packing, op orchestration.
+#include "../../include/t2b200.h"
+#include "common.cuh"
+#include "decoder.cuh"
+#include "layers.cuh"
+
+#include <cstdarg>
+#include <map>
+#include <string>
+#include <vector>
+
+static thread_local char g_err[1024] = "";
+void t2_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+extern "C" const char* t2_last_error(void) { return g_err; }
+extern "C" int t2_abi_version(void) { return 1; }
+
+struct Param { const float* ptr; long long numel; };
+
+struct t2_ctx {
+  t2_model_config cfg;
+  int device, num_sms;
+  int EF, C, H, R, P, A, M, E, PD, KS;
+  DecDims dd;  // B, L filled per call
+  std::map<std::string, Param> params;
+  bool committed;
+  // packed device memory (one slab)
+  char* slab;
+  size_t slab_bytes;
+  DecWeights dw;
+  float *enc_Wr[3], *enc_scale[3], *enc_shift[3];
+  float *post_Wr[5], *post_scale[5], *post_shift[5];
+  float *lstm_Wr, *lstm_bias, *lstm_WhhT;  // BiLSTM: [1][E][2*4Hh], [2*4Hh], [2][Hh][4Hh]
+  float* attenc_Wr;                        // [1][EF][A]
+};
+
+namespace {
+
+__global__ void pack_lstm_kernel(const float* Wih, const float* Whh, float* Wp, int H, int Kin, int KP) {
+  // Wp[tile][k][rr], rr = gate*8 + unit_in_tile  <-  row = gate*H + tile*8 + unit_in_tile
+  const long long n = (long long)(H / 8) * KP * 32;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int rr = (int)(i % 32);
+    const int k = (int)((i / 32) % KP);
+    const int tile = (int)(i / (32ll * KP));
+    const int row = (rr / 8) * H + tile * 8 + (rr % 8);
+    float v = 0.f;
+    if (k < Kin) v = Wih[(size_t)row * Kin + k];
+    else if (k < Kin + H) v = Whh[(size_t)row * H + (k - Kin)];
+    Wp[i] = v;
+  }
+}
+
+__global__ void add_vec_kernel(const float* a, const float* b, float* o, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) o[i] = a[i] + b[i];
+}
+
+__global__ void pack_proj_kernel(const float* Wmel, const float* Wgate, const float* bmel, const float* bgate, float* Wproj,
+                                 float* bproj, int M, int Kmel, int Kgate, int KP) {
+  const int n = (M + 1) * KP;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int r = i / KP, k = i % KP;
+    float v = 0.f;
+    if (r < M) { if (k < Kmel) v = Wmel[(size_t)r * Kmel + k]; }
+    else if (k < Kgate) v = Wgate[k];
+    Wproj[i] = v;
+  }
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i <= M; i += gridDim.x * blockDim.x) bproj[i] = i < M ? bmel[i] : bgate[0];
+}
+
+// row-major (B,dim) -> k-major [dim][BP] rows at row offset, batch slots >= B zeroed
+__global__ void rm_to_km_kernel(const float* src, int ld, float* dst, int row0, int dim, int B) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < dim * DEC_BP; i += gridDim.x * blockDim.x) {
+    const int r = i / DEC_BP, b = i % DEC_BP;
+    dst[(size_t)(row0 + r) * DEC_BP + b] = (b < B && src) ? src[(size_t)b * ld + r] : 0.f;
+  }
+}
+__global__ void km_to_rm_kernel(const float* src, int row0, float* dst, int ld, int dim, int B) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < dim * B; i += gridDim.x * blockDim.x) {
+    const int b = i / dim, r = i % dim;
+    dst[(size_t)b * ld + r] = src[(size_t)(row0 + r) * DEC_BP + b];
+  }
+}
+__global__ void copy2d_kernel(const float* src, int lds, float* dst, int ldd, int rows, int cols) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rows * cols; i += gridDim.x * blockDim.x) {
+    const int r = i / cols, c = i % cols;
+    dst[(size_t)r * ldd + c] = src[(size_t)r * lds + c];
+  }
+}
+
+// prenet (model/tacotron2.py:85-92) on N independent rows, 8 rows per CTA pass.
+// mode 0: x (N,M) -> out (N,P), keep1/keep2 (N,P).
+// mode 1 (teacher forcing, model/tacotron2.py:255-257): row n = t*B + b, t in [0,T]; input is
+//   mel_target[b][t-1] (zeros for t = 0, the F.pad row); keep = prenet_keep (T+1,2,B,P);
+//   output is k-major [T+1][P][DEC_BP] for the persistent decoder kernel.
+struct PrenetArgs {
+  const float* x; const float* W1; const float* W2;
+  const unsigned char* k1; const unsigned char* k2;
+  unsigned long long seed; float p; int N, M, P, mode, B, T; float* out;
+};
+#define PN_ROWS 8
+__global__ void __launch_bounds__(256) prenet_rows_kernel(PrenetArgs a) {
+  extern __shared__ float sh[];  // xs[PN_ROWS][M] | hs[PN_ROWS][P]
+  float* xs = sh;
+  float* hs = sh + PN_ROWS * a.M;
+  const float scale = 1.0f / (1.0f - a.p);
+  const int M = a.M, P = a.P;
+  for (int n0 = blockIdx.x * PN_ROWS; n0 < a.N; n0 += gridDim.x * PN_ROWS) {
+    for (int i = threadIdx.x; i < PN_ROWS * M; i += blockDim.x) {
+      const int n = n0 + i / M, c = i % M;
+      float v = 0.f;
+      if (n < a.N) {
+        if (a.mode == 0) v = a.x[(size_t)n * M + c];
+        else { const int t = n / a.B, b = n % a.B; if (t > 0) v = a.x[((size_t)b * a.T + (t - 1)) * M + c]; }
+      }
+      xs[i] = v;
+    }
+    __syncthreads();
+    for (int layer = 0; layer < 2; ++layer) {
+      const float* W = layer ? a.W2 : a.W1;
+      const int K = layer ? P : M;
+      const float* in = layer ? hs : xs;
+      for (int o = threadIdx.x; o < P; o += blockDim.x) {
+        float acc[PN_ROWS];
+#pragma unroll
+        for (int r = 0; r < PN_ROWS; ++r) acc[r] = 0.f;
+        for (int k = 0; k < K; ++k) {
+          const float w = __ldg(W + (size_t)o * K + k);
+#pragma unroll
+          for (int r = 0; r < PN_ROWS; ++r) acc[r] = fmaf(w, in[r * K + k], acc[r]);
+        }
+#pragma unroll
+        for (int r = 0; r < PN_ROWS; ++r) {
+          const int n = n0 + r;
+          if (n >= a.N) continue;
+          size_t kidx; unsigned long long ridx;
+          if (a.mode == 0) { kidx = (size_t)n * P + o; ridx = ((unsigned long long)n * 2 + layer) * P + o; }
+          else {
+            const int t = n / a.B, b = n % a.B;
+            kidx = (((size_t)t * 2 + layer) * a.B + b) * P + o;
+            ridx = kidx;
+          }
+          const unsigned char* km = layer ? a.k2 : a.k1;
+          const bool keep = km ? (km[kidx] != 0) : rng_keep(a.seed, ridx, a.p);
+          const float v = (acc[r] > 0.f && keep) ? acc[r] * scale : 0.f;
+          if (layer == 0) hs[r * P + o] = v;  // safe: each thread writes only its own o, read after the barrier
+          else if (a.mode == 0) a.out[(size_t)n * P + o] = v;
+          else { const int t = n / a.B, b = n % a.B; a.out[((size_t)t * P + o) * DEC_BP + b] = v; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+const Param* find(const t2_ctx* c, const std::string& k) {
+  auto it = c->params.find(k);
+  return it == c->params.end() ? nullptr : &it->second;
+}
+
+inline int gsz(long long n) { return (int)std::min<long long>((n + 255) / 256, 148 * 8); }
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------ context
+extern "C" int t2_ctx_create(const t2_model_config* cfg, t2_ctx** out) {
+  T2_REQUIRE(cfg && out, T2_ERR_ARG, "t2_ctx_create: null argument");
+  int dev = 0, count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  T2_REQUIRE(e == cudaSuccess && count > 0, T2_ERR_CUDA, "t2_ctx_create: no CUDA device (%s); libt2b200 has no CPU fallback",
+             cudaGetErrorString(e));
+  T2_CHECK_CUDA(cudaGetDevice(&dev));
+  cudaDeviceProp prop;
+  T2_CHECK_CUDA(cudaGetDeviceProperties(&prop, dev));
+  T2_REQUIRE(prop.major >= 10, T2_ERR_UNSUPPORTED, "t2_ctx_create: device sm_%d%d; libt2b200 is built for sm_100a only", prop.major,
+             prop.minor);
+  t2_ctx* c = new t2_ctx();
+  c->cfg = *cfg;
+  c->device = dev;
+  c->num_sms = prop.multiProcessorCount;
+  c->E = cfg->encoded_dim;
+  c->EF = cfg->encoded_dim + (cfg->description_dim > 0 ? 128 : 0);
+  c->C = cfg->controls_dim;
+  c->H = cfg->att_rnn_dim;
+  c->R = cfg->rnn_hidden_dim;
+  c->P = cfg->prenet_dim;
+  c->A = cfg->att_dim;
+  c->M = cfg->num_mels;
+  c->PD = cfg->postnet_dim;
+  c->KS = cfg->encoder_kernel_size;
+  DecDims& d = c->dd;
+  d.B = d.L = 0;
+  d.EF = c->EF; d.H = c->H; d.R = c->R; d.P = c->P; d.A = c->A; d.M = c->M; d.C = c->C;
+  d.Katt = c->P + c->EF + c->H;
+  d.KattP = (int)round_up64(d.Katt, 64);
+  d.Kdec = c->H + c->EF + c->C + c->R;
+  d.KdecP = (int)round_up64(d.Kdec, 64);
+  d.Kproj = c->R + c->EF + c->C;
+  d.KprojP = (int)round_up64(d.Kproj, 4);
+  d.p_prenet = cfg->dropout;
+  c->committed = false;
+  c->slab = nullptr;
+  c->slab_bytes = 0;
+  *out = c;
+  return T2_OK;
+}
+
+extern "C" int t2_ctx_destroy(t2_ctx* c) {
+  if (!c) return T2_OK;
+  if (c->slab) cudaFree(c->slab);
+  delete c;
+  return T2_OK;
+}
+
+extern "C" int t2_ctx_set_param(t2_ctx* c, const char* key, const float* ptr, long long numel) {
+  T2_REQUIRE(c && key && ptr, T2_ERR_ARG, "t2_ctx_set_param: null argument");
+  c->params[key] = Param{ptr, numel};
+  c->committed = false;
+  return T2_OK;
+}
+
+#define NEED(var, key, n)                                                                                   \
+  const Param* var = find(c, key);                                                                          \
+  T2_REQUIRE(var && var->numel == (long long)(n), T2_ERR_STATE, "t2_ctx_commit: parameter %s missing or wrong size (want %lld)", \
+             std::string(key).c_str(), (long long)(n))
+
+static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
+  const bool sizing = ar.base == nullptr;
+  const DecDims& d = c->dd;
+  const int H = c->H, R = c->R, P = c->P, A = c->A, M = c->M, E = c->E, EF = c->EF, C = c->C, PD = c->PD, KS = c->KS;
+  const int Hh = E / 2;
+  float* Watt_p = ar.take<float>((size_t)(H / 8) * d.KattP * 32);
+  float* batt = ar.take<float>(4 * H);
+  float* Wdec_p = ar.take<float>((size_t)(R / 8) * d.KdecP * 32);
+  float* bdec = ar.take<float>(4 * R);
+  float* Wproj = ar.take<float>((size_t)(M + 1) * d.KprojP);
+  float* bproj = ar.take<float>(M + 1);
+  int chans[6] = {M, PD, PD, PD, PD, M};
+  for (int i = 0; i < 3; ++i) {
+    c->enc_Wr[i] = ar.take<float>((size_t)KS * E * E);
+    c->enc_scale[i] = ar.take<float>(E);
+    c->enc_shift[i] = ar.take<float>(E);
+  }
+  for (int i = 0; i < 5; ++i) {
+    c->post_Wr[i] = ar.take<float>((size_t)5 * chans[i] * chans[i + 1]);
+    c->post_scale[i] = ar.take<float>(chans[i + 1]);
+    c->post_shift[i] = ar.take<float>(chans[i + 1]);
+  }
+  c->lstm_Wr = ar.take<float>((size_t)E * 8 * Hh);
+  c->lstm_bias = ar.take<float>(8 * Hh);
+  c->lstm_WhhT = ar.take<float>((size_t)2 * Hh * 4 * Hh);
+  c->attenc_Wr = ar.take<float>((size_t)EF * A);
+  float* tmp = ar.take<float>((size_t)8 * Hh * E);  // staging for the concatenated BiLSTM W_ih
+  if (sizing) return T2_OK;
+  T2_REQUIRE(!ar.overflow, T2_ERR_STATE, "t2_ctx_commit: slab overflow");
+
+  NEED(att_ih, "decoder.att_rnn.weight_ih", (size_t)4 * H * (P + EF));
+  NEED(att_hh, "decoder.att_rnn.weight_hh", (size_t)4 * H * H);
+  NEED(att_bi, "decoder.att_rnn.bias_ih", 4 * H);
+  NEED(att_bh, "decoder.att_rnn.bias_hh", 4 * H);
+  NEED(dec_ih, "decoder.lstm.weight_ih", (size_t)4 * R * (H + EF + C));
+  NEED(dec_hh, "decoder.lstm.weight_hh", (size_t)4 * R * R);
+  NEED(dec_bi, "decoder.lstm.bias_ih", 4 * R);
+  NEED(dec_bh, "decoder.lstm.bias_hh", 4 * R);
+  NEED(wq, "decoder.attention.query_layer.weight", (size_t)A * H);
+  NEED(wv, "decoder.attention.v.weight", A);
+  NEED(lconv, "decoder.attention.location_conv.weight", 32 * 2 * 31);
+  NEED(ldense, "decoder.attention.location_dense.weight", (size_t)A * 32);
+  NEED(wmel, "decoder.mel_out.weight", (size_t)M * (R + EF + C));
+  NEED(bmel, "decoder.mel_out.bias", M);
+  NEED(wgate, "decoder.gate.weight", R + EF);
+  NEED(bgate, "decoder.gate.bias", 1);
+  NEED(w1, "prenet.0.weight", (size_t)P * M);
+  NEED(w2, "prenet.3.weight", (size_t)P * P);
+  NEED(wae, "att_encoder.weight", (size_t)A * EF);
+  T2_REQUIRE(H == R, T2_ERR_UNSUPPORTED, "att_rnn_dim != rnn_hidden_dim is not supported by the packed layout");
+
+  pack_lstm_kernel<<<gsz((long long)(H / 8) * d.KattP * 32), 256, 0, st>>>(att_ih->ptr, att_hh->ptr, Watt_p, H, P + EF, d.KattP);
+  pack_lstm_kernel<<<gsz((long long)(R / 8) * d.KdecP * 32), 256, 0, st>>>(dec_ih->ptr, dec_hh->ptr, Wdec_p, R, H + EF + C, d.KdecP);
+  add_vec_kernel<<<(4 * H + 255) / 256, 256, 0, st>>>(att_bi->ptr, att_bh->ptr, batt, 4 * H);
+  add_vec_kernel<<<(4 * R + 255) / 256, 256, 0, st>>>(dec_bi->ptr, dec_bh->ptr, bdec, 4 * R);
+  pack_proj_kernel<<<gsz((long long)(M + 1) * d.KprojP), 256, 0, st>>>(wmel->ptr, wgate->ptr, bmel->ptr, bgate->ptr, Wproj, bproj, M,
+                                                                      R + EF + C, R + EF, d.KprojP);
+  T2_CHECK_CUDA(cudaGetLastError());
+  c->dw = DecWeights{Watt_p, batt, Wdec_p, bdec, wq->ptr, wv->ptr, lconv->ptr, ldense->ptr, Wproj, bproj, w1->ptr, w2->ptr};
+
+  int rc;
+  for (int i = 0; i < 3; ++i) {
+    const std::string cv = "encoder.convolutions." + std::to_string(4 * i), bn = "encoder.convolutions." + std::to_string(4 * i + 1);
+    NEED(cw, cv + ".weight", (size_t)E * E * KS);
+    NEED(cb, cv + ".bias", E);
+    NEED(bw, bn + ".weight", E);
+    NEED(bb, bn + ".bias", E);
+    NEED(bm, bn + ".running_mean", E);
+    NEED(bv, bn + ".running_var", E);
+    if ((rc = repack_conv_launch(cw->ptr, c->enc_Wr[i], E, E, KS, st))) return rc;
+    if ((rc = bn_fold_launch(bw->ptr, bb->ptr, bm->ptr, bv->ptr, cb->ptr, c->enc_scale[i], c->enc_shift[i], E, st))) return rc;
+  }
+  for (int i = 0; i < 5; ++i) {
+    const std::string cv = "postnet.postnet." + std::to_string(4 * i), bn = "postnet.postnet." + std::to_string(4 * i + 1);
+    NEED(cw, cv + ".weight", (size_t)chans[i + 1] * chans[i] * 5);
+    NEED(bw, bn + ".weight", chans[i + 1]);
+    NEED(bb, bn + ".bias", chans[i + 1]);
+    NEED(bm, bn + ".running_mean", chans[i + 1]);
+    NEED(bv, bn + ".running_var", chans[i + 1]);
+    if ((rc = repack_conv_launch(cw->ptr, c->post_Wr[i], chans[i + 1], chans[i], 5, st))) return rc;
+    if ((rc = bn_fold_launch(bw->ptr, bb->ptr, bm->ptr, bv->ptr, nullptr, c->post_scale[i], c->post_shift[i], chans[i + 1], st))) return rc;
+  }
+  // BiLSTM: input projection for both directions as one k=1 "conv": Wr [E][8Hh]; recurrent W_hh^T per direction
+  for (int dir = 0; dir < 2; ++dir) {
+    const std::string sfx = dir ? "_reverse" : "";
+    NEED(wih, "encoder.lstm.weight_ih_l0" + sfx, (size_t)4 * Hh * E);
+    NEED(whh, "encoder.lstm.weight_hh_l0" + sfx, (size_t)4 * Hh * Hh);
+    NEED(bih, "encoder.lstm.bias_ih_l0" + sfx, 4 * Hh);
+    NEED(bhh, "encoder.lstm.bias_hh_l0" + sfx, 4 * Hh);
+    T2_CHECK_CUDA(cudaMemcpyAsync(tmp + (size_t)dir * 4 * Hh * E, wih->ptr, (size_t)4 * Hh * E * sizeof(float),
+                                  cudaMemcpyDeviceToDevice, st));
+    if ((rc = transpose_launch(whh->ptr, c->lstm_WhhT + (size_t)dir * Hh * 4 * Hh, 4 * Hh, Hh, st))) return rc;
+    add_vec_kernel<<<(4 * Hh + 255) / 256, 256, 0, st>>>(bih->ptr, bhh->ptr, c->lstm_bias + dir * 4 * Hh, 4 * Hh);
+  }
+  if ((rc = transpose_launch(tmp, c->lstm_Wr, 8 * Hh, E, st))) return rc;
+  if ((rc = transpose_launch(wae->ptr, c->attenc_Wr, A, EF, st))) return rc;
+  T2_CHECK_CUDA(cudaGetLastError());
+  c->committed = true;
+  return T2_OK;
+}
+
+extern "C" int t2_ctx_commit(t2_ctx* c, void* stream) {
+  T2_REQUIRE(c, T2_ERR_ARG, "t2_ctx_commit: null context");
+  if (!c->slab) {
+    Arena sizing(nullptr, 0);
+    commit_impl(c, sizing, nullptr);
+    c->slab_bytes = (size_t)sizing.off;
+    T2_CHECK_CUDA(cudaMalloc((void**)&c->slab, c->slab_bytes));
+  }
+  Arena ar(c->slab, (int64_t)c->slab_bytes);
+  return commit_impl(c, ar, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------ ops
+#define CHECK_CTX(name)                                                                        \
+  T2_REQUIRE(c, T2_ERR_ARG, name ": null context");                                            \
+  T2_REQUIRE(c->committed, T2_ERR_STATE, name ": weights not committed (call t2_ctx_commit)")
+#define RC(x) do { int _rc = (x); if (_rc) return _rc; } while (0)
+
+static int encoder_impl(t2_ctx* c, const long long* chars, const long long* lens, int B, int L, int train,
+                        const unsigned char* keep, float* encoded, Arena& ar, cudaStream_t st) {
+  const int E = c->E, Hh = E / 2;
+  float* x0 = ar.take<float>((size_t)B * L * E);
+  float* x1 = ar.take<float>((size_t)B * L * E);
+  float* xproj = ar.take<float>((size_t)B * L * 8 * Hh);
+  if (!ar.base) return T2_OK;
+  T2_REQUIRE(!ar.overflow, T2_ERR_WORKSPACE, "t2_encoder_fwd: workspace too small");
+  T2_REQUIRE(!train, T2_ERR_UNSUPPORTED, "t2_encoder_fwd: train-mode BatchNorm statistics are not implemented in this revision");
+  RC(embed_launch(chars, find(c, "encoder.embedding.weight")->ptr, x0, B * L, E, c->cfg.num_chars + 1, st));
+  float* cur = x0;
+  float* nxt = x1;
+  for (int i = 0; i < 3; ++i) {
+    ConvArgs a{};
+    a.in = cur; a.in_bstride = (long long)L * E; a.Wr = c->enc_Wr[i]; a.bias = nullptr;
+    a.bn_scale = c->enc_scale[i]; a.bn_shift = c->enc_shift[i];
+    a.keep = keep ? keep + (size_t)i * B * L * E : nullptr; a.keep_ld = E; a.drop_scale = 1.0f / (1.0f - c->cfg.dropout);
+    a.out = nxt; a.B = B; a.T = L; a.Cin = E; a.Cout = E; a.k = c->KS; a.act = ACT_RELU;
+    RC(conv1d_cl_launch(a, st));
+    std::swap(cur, nxt);
+  }
+  ConvArgs p{};
+  p.in = cur; p.in_bstride = (long long)L * E; p.Wr = c->lstm_Wr; p.bias = c->lstm_bias; p.out = xproj;
+  p.B = B; p.T = L; p.Cin = E; p.Cout = 8 * Hh; p.k = 1; p.act = ACT_NONE; p.drop_scale = 1.f;
+  RC(conv1d_cl_launch(p, st));
+  RC(bilstm_launch(xproj, c->lstm_WhhT, lens, encoded, B, L, Hh, st));
+  return T2_OK;
+}
+
+extern "C" int t2_encoder_fwd(t2_ctx* c, const long long* chars_idx, const long long* lens, int B, int L, int train,
+                              const unsigned char* keep, float* encoded, void* ws, long long ws_bytes, void* stream) {
+  CHECK_CTX("t2_encoder_fwd");
+  T2_REQUIRE(chars_idx && lens && encoded && ws && B > 0 && L > 0, T2_ERR_ARG, "t2_encoder_fwd: bad argument");
+  T2_REQUIRE(find(c, "encoder.embedding.weight"), T2_ERR_STATE, "t2_encoder_fwd: encoder.embedding.weight not set");
+  Arena ar(ws, ws_bytes);
+  return encoder_impl(c, chars_idx, lens, B, L, train, keep, encoded, ar, (cudaStream_t)stream);
+}
+
+static int memory_impl(t2_ctx* c, const float* encoded, const long long* spk, const float* desc, int B, int L, float* memory,
+                       float* pmem, Arena& ar, cudaStream_t st) {
+  const int E = c->E, EF = c->EF, D = EF - E;
+  float* dvec = ar.take<float>((size_t)B * 128);
+  if (!ar.base) return T2_OK;
+  T2_REQUIRE(!ar.overflow, T2_ERR_WORKSPACE, "t2_memory_fwd: workspace too small");
+  const float* spk_table = nullptr;
+  if (c->cfg.num_speakers > 0) {
+    T2_REQUIRE(spk, T2_ERR_ARG, "speaker_id tensor required when speaker tokens are active!");  // model/tacotron2.py:175-177
+    const Param* p = find(c, "speaker_embedding.weight");
+    T2_REQUIRE(p && p->numel == (long long)c->cfg.num_speakers * E, T2_ERR_STATE, "speaker_embedding.weight missing");
+    spk_table = p->ptr;
+  }
+  if (D > 0) {
+    T2_REQUIRE(desc, T2_ERR_ARG, "description tensor required when description tokens are active!");  // :179-181
+    const Param* w = find(c, "description_embeddings_linear.0.weight");
+    const Param* b = find(c, "description_embeddings_linear.0.bias");
+    T2_REQUIRE(w && b && w->numel == 128ll * c->cfg.description_dim, T2_ERR_STATE, "description_embeddings_linear missing");
+    RC(desc_linear_launch(desc, w->ptr, b->ptr, dvec, B, c->cfg.description_dim, 128, st));
+  }
+  if (spk_table || D > 0) RC(condition_launch(encoded, spk_table, spk, dvec, D, memory, B, L, E, st));
+  else T2_CHECK_CUDA(cudaMemcpyAsync(memory, encoded, (size_t)B * L * E * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  ConvArgs p{};
+  p.in = memory; p.in_bstride = (long long)L * EF; p.Wr = c->attenc_Wr; p.out = pmem;
+  p.B = B; p.T = L; p.Cin = EF; p.Cout = c->A; p.k = 1; p.act = ACT_NONE; p.drop_scale = 1.f;
+  RC(conv1d_cl_launch(p, st));
+  return T2_OK;
+}
+
+extern "C" int t2_memory_fwd(t2_ctx* c, const float* encoded, const long long* speaker_id, const float* description, int B, int L,
+                             float* memory, float* processed_memory, void* ws, long long ws_bytes, void* stream) {
+  CHECK_CTX("t2_memory_fwd");
+  T2_REQUIRE(encoded && memory && processed_memory && ws && B > 0 && L > 0, T2_ERR_ARG, "t2_memory_fwd: bad argument");
+  Arena ar(ws, ws_bytes);
+  return memory_impl(c, encoded, speaker_id, description, B, L, memory, processed_memory, ar, (cudaStream_t)stream);
+}
+
+// Decoder state carve-out; everything between zero_begin and zero_end is memset to 0 before a run.
+struct StatePlan { DecState s; char* zero_begin; size_t zero_bytes; };
+static StatePlan plan_state(const DecDims& d, int L, Arena& ar) {
+  StatePlan pl{};
+  int64_t off0 = ar.off;
+  DecState& s = pl.s;
+  for (int i = 0; i < 2; ++i) s.xpre[i] = ar.take<float>((size_t)d.P * DEC_BP);
+  for (int i = 0; i < 2; ++i) s.xatt[i] = ar.take<float>((size_t)(d.KattP - d.P) * DEC_BP);
+  for (int i = 0; i < 2; ++i) s.xdec[i] = ar.take<float>((size_t)d.KdecP * DEC_BP);
+  s.att_c = ar.take<float>((size_t)d.H * DEC_BP);
+  s.rnn_c = ar.take<float>((size_t)d.R * DEC_BP);
+  s.att_h_rm = ar.take<float>((size_t)DEC_BP * d.H);
+  s.projin = ar.take<float>((size_t)DEC_BP * d.KprojP);
+  s.q = ar.take<float>((size_t)DEC_BP * d.A);
+  s.w_prev = ar.take<float>((size_t)2 * DEC_BP * L);
+  s.w_cum = ar.take<float>((size_t)2 * DEC_BP * L);
+  s.mel_cur = ar.take<float>((size_t)DEC_BP * d.M);
+  s.p1 = ar.take<float>((size_t)DEC_BP * d.P);
+  s.done = ar.take<int>(DEC_BP);
+  s.lengths = ar.take<long long>(DEC_BP);
+  s.n_frames = ar.take<int>(4);
+  s.barrier = ar.take<unsigned>(4);
+  pl.zero_begin = ar.base ? ar.base + off0 : nullptr;
+  pl.zero_bytes = (size_t)(ar.off - off0);
+  return pl;
+}
+
+static int fill_controls(const DecDims& d, DecState& s, const float* controls, int B, cudaStream_t st) {
+  if (d.C == 0) return T2_OK;
+  T2_REQUIRE(controls, T2_ERR_ARG, "Controls are enabled, but no control vector was passed to the model!");  // model/tacotron2.py:183-185
+  for (int i = 0; i < 2; ++i) rm_to_km_kernel<<<gsz(d.C * DEC_BP), 256, 0, st>>>(controls, d.C, s.xdec[i], d.H + d.EF, d.C, B);
+  copy2d_kernel<<<gsz(B * d.C), 256, 0, st>>>(controls, d.C, s.projin + d.R + d.EF, d.KprojP, B, d.C);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+
+static int decode_impl(t2_ctx* c, bool tf, const float* memory, const float* pmem, const unsigned char* mask, const float* controls,
+                       const float* mel_target, int B, int L, int T, const unsigned char* prenet_keep, int train,
+                       const unsigned char* att_keep, const unsigned char* rnn_keep, unsigned long long seed, float* mels,
+                       float* gates, float* aligns, long long* lengths, int* n_frames, Arena& ar, cudaStream_t st) {
+  DecDims d = c->dd;
+  d.B = B; d.L = L;
+  StatePlan pl = plan_state(d, L, ar);
+  float* tfp = tf ? ar.take<float>((size_t)(T + 1) * d.P * DEC_BP) : nullptr;
+  if (!ar.base) return T2_OK;
+  T2_REQUIRE(!ar.overflow, T2_ERR_WORKSPACE, "t2_decode: workspace too small");
+  T2_CHECK_CUDA(cudaMemsetAsync(pl.zero_begin, 0, pl.zero_bytes, st));
+  DecState s = pl.s;
+  RC(fill_controls(d, s, controls, B, st));
+  DecIO io{};
+  io.memory = memory; io.pmem = pmem; io.mask = mask; io.prenet_keep = prenet_keep;
+  io.att_keep = att_keep; io.rnn_keep = rnn_keep; io.mels = mels; io.gates = gates; io.aligns = aligns;
+  io.projin_all = nullptr; io.Tmax = T; io.n_steps = T; io.t0 = 0; io.seed = seed;
+  io.hidden_dropout = train ? 1 : 0;
+  if (tf) {
+    T2_CHECK_CUDA(cudaMemsetAsync(tfp, 0, (size_t)(T + 1) * d.P * DEC_BP * sizeof(float), st));
+    PrenetArgs pa{mel_target, c->dw.W1, c->dw.W2, prenet_keep, prenet_keep, seed, d.p_prenet, (T + 1) * B, d.M, d.P, 1, B, T, tfp};
+    prenet_rows_kernel<<<std::min(((T + 1) * B + PN_ROWS - 1) / PN_ROWS, 148 * 4), 256, PN_ROWS * (d.M + d.P) * sizeof(float), st>>>(pa);
+    T2_CHECK_CUDA(cudaGetLastError());
+    io.tf_prenet = tfp; io.teacher_forcing = 1; io.stop_enabled = 0;
+  } else {
+    io.tf_prenet = nullptr; io.teacher_forcing = 0; io.stop_enabled = 1;
+    T2_CHECK_CUDA(cudaMemsetAsync(lengths, 0, (size_t)B * sizeof(long long), st));
+    s.lengths = lengths;
+    s.n_frames = n_frames;
+  }
+  return dec_launch(d, c->dw, s, io, c->num_sms, st);
+}
+
+extern "C" int t2_decode_ar(t2_ctx* c, const float* memory, const float* processed_memory, const unsigned char* mask,
+                            const float* controls, int B, int L, int max_len, const unsigned char* prenet_keep,
+                            unsigned long long seed, float* mels, float* gates, float* alignments, long long* lengths,
+                            int* n_frames, void* ws, long long ws_bytes, void* stream) {
+  CHECK_CTX("t2_decode_ar");
+  T2_REQUIRE(memory && processed_memory && mask && mels && gates && alignments && lengths && n_frames && ws, T2_ERR_ARG,
+             "t2_decode_ar: null argument");
+  T2_REQUIRE(B > 0 && L > 0 && max_len > 0, T2_ERR_ARG, "t2_decode_ar: bad sizes B=%d L=%d max_len=%d", B, L, max_len);
+  Arena ar(ws, ws_bytes);
+  return decode_impl(c, false, memory, processed_memory, mask, controls, nullptr, B, L, max_len, prenet_keep, 0, nullptr, nullptr,
+                     seed, mels, gates, alignments, lengths, n_frames, ar, (cudaStream_t)stream);
+}
+
+extern "C" int t2_decode_tf(t2_ctx* c, const float* memory, const float* processed_memory, const unsigned char* mask,
+                            const float* controls, const float* mel_target, int B, int L, int T, const unsigned char* prenet_keep,
+                            int train, const unsigned char* att_keep, const unsigned char* rnn_keep, unsigned long long seed,
+                            float* mels, float* gates, float* alignments, void* ws, long long ws_bytes, void* stream) {
+  CHECK_CTX("t2_decode_tf");
+  T2_REQUIRE(memory && processed_memory && mask && mel_target && mels && gates && alignments && ws, T2_ERR_ARG,
+             "Ground-truth Mel spectrogram is required for teacher forcing");  // model/tacotron2.py:168-170
+  T2_REQUIRE(B > 0 && L > 0 && T > 0, T2_ERR_ARG, "t2_decode_tf: bad sizes");
+  Arena ar(ws, ws_bytes);
+  return decode_impl(c, true, memory, processed_memory, mask, controls, mel_target, B, L, T, prenet_keep, train, att_keep, rnn_keep,
+                     seed, mels, gates, alignments, nullptr, nullptr, ar, (cudaStream_t)stream);
+}
+
+static int step_impl(t2_ctx* c, const float* prev, const float* att_h, const float* att_c, const float* ctx, const float* w,
+                     const float* w_cum, const float* rnn_h, const float* rnn_c, const float* memory, const float* pmem,
+                     const unsigned char* mask, const float* controls, int B, int L, float* mel_out, float* gate_out,
+                     float* att_h_out, float* att_c_out, float* ctx_out, float* w_out, float* w_cum_out, float* rnn_h_out,
+                     float* rnn_c_out, Arena& ar, cudaStream_t st) {
+  DecDims d = c->dd;
+  d.B = B; d.L = L;
+  StatePlan pl = plan_state(d, L, ar);
+  float* tfp = ar.take<float>((size_t)d.P * DEC_BP);
+  if (!ar.base) return T2_OK;
+  T2_REQUIRE(!ar.overflow, T2_ERR_WORKSPACE, "t2_decoder_step: workspace too small");
+  T2_CHECK_CUDA(cudaMemsetAsync(pl.zero_begin, 0, pl.zero_bytes, st));
+  DecState s = pl.s;
+  RC(fill_controls(d, s, controls, B, st));
+  // pack the caller's row-major state into the kernel's layout (parity 0 = "current")
+  rm_to_km_kernel<<<gsz(d.P * DEC_BP), 256, 0, st>>>(prev, d.P, tfp, 0, d.P, B);
+  rm_to_km_kernel<<<gsz(d.EF * DEC_BP), 256, 0, st>>>(ctx, d.EF, s.xatt[0], 0, d.EF, B);
+  rm_to_km_kernel<<<gsz(d.H * DEC_BP), 256, 0, st>>>(att_h, d.H, s.xatt[0], d.EF, d.H, B);
+  rm_to_km_kernel<<<gsz(d.H * DEC_BP), 256, 0, st>>>(att_c, d.H, s.att_c, 0, d.H, B);
+  rm_to_km_kernel<<<gsz(d.R * DEC_BP), 256, 0, st>>>(rnn_h, d.R, s.xdec[0], d.H + d.EF + d.C, d.R, B);
+  rm_to_km_kernel<<<gsz(d.R * DEC_BP), 256, 0, st>>>(rnn_c, d.R, s.rnn_c, 0, d.R, B);
+  copy2d_kernel<<<gsz(B * L), 256, 0, st>>>(w, L, s.w_prev, L, B, L);
+  copy2d_kernel<<<gsz(B * L), 256, 0, st>>>(w_cum, L, s.w_cum, L, B, L);
+  T2_CHECK_CUDA(cudaGetLastError());
+  DecIO io{};
+  io.memory = memory; io.pmem = pmem; io.mask = mask; io.tf_prenet = tfp; io.teacher_forcing = 1; io.stop_enabled = 0;
+  io.mels = mel_out; io.gates = gate_out; io.aligns = w_out; io.Tmax = 1; io.n_steps = 1; io.t0 = 0;
+  RC(dec_launch(d, c->dw, s, io, c->num_sms, st));
+  copy2d_kernel<<<gsz(B * d.H), 256, 0, st>>>(s.att_h_rm, d.H, att_h_out, d.H, B, d.H);
+  km_to_rm_kernel<<<gsz(B * d.H), 256, 0, st>>>(s.att_c, 0, att_c_out, d.H, d.H, B);
+  copy2d_kernel<<<gsz(B * d.EF), 256, 0, st>>>(s.projin + d.R, d.KprojP, ctx_out, d.EF, B, d.EF);
+  copy2d_kernel<<<gsz(B * L), 256, 0, st>>>(s.w_cum + (size_t)DEC_BP * L, L, w_cum_out, L, B, L);
+  copy2d_kernel<<<gsz(B * d.R), 256, 0, st>>>(s.projin, d.KprojP, rnn_h_out, d.R, B, d.R);
+  km_to_rm_kernel<<<gsz(B * d.R), 256, 0, st>>>(s.rnn_c, 0, rnn_c_out, d.R, d.R, B);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+
+extern "C" int t2_decoder_step(t2_ctx* c, const float* prev_mel_prenet, const float* att_h, const float* att_c, const float* att_ctx,
+                               const float* w, const float* w_cum, const float* rnn_h, const float* rnn_c, const float* memory,
+                               const float* processed_memory, const unsigned char* mask, const float* controls, int B, int L,
+                               float* mel_out, float* gate_out, float* att_h_out, float* att_c_out, float* att_ctx_out,
+                               float* w_out, float* w_cum_out, float* rnn_h_out, float* rnn_c_out, void* ws, long long ws_bytes,
+                               void* stream) {
+  CHECK_CTX("t2_decoder_step");
+  T2_REQUIRE(prev_mel_prenet && att_h && att_c && att_ctx && w && w_cum && rnn_h && rnn_c && memory && processed_memory && mask &&
+                 mel_out && gate_out && att_h_out && att_c_out && att_ctx_out && w_out && w_cum_out && rnn_h_out && rnn_c_out && ws,
+             T2_ERR_ARG, "t2_decoder_step: null argument");
+  Arena ar(ws, ws_bytes);
+  return step_impl(c, prev_mel_prenet, att_h, att_c, att_ctx, w, w_cum, rnn_h, rnn_c, memory, processed_memory, mask, controls, B, L,
+                   mel_out, gate_out, att_h_out, att_c_out, att_ctx_out, w_out, w_cum_out, rnn_h_out, rnn_c_out, ar,
+                   (cudaStream_t)stream);
+}
+
+extern "C" int t2_prenet_fwd(t2_ctx* c, const float* x, const unsigned char* keep1, const unsigned char* keep2,
+                             unsigned long long seed, int N, float* out, void* ws, long long ws_bytes, void* stream) {
+  CHECK_CTX("t2_prenet_fwd");
+  T2_REQUIRE(x && out && N > 0, T2_ERR_ARG, "t2_prenet_fwd: bad argument");
+  (void)ws; (void)ws_bytes;
+  PrenetArgs pa{x, c->dw.W1, c->dw.W2, keep1, keep2, seed, c->cfg.dropout, N, c->M, c->P, 0, 0, 0, out};
+  prenet_rows_kernel<<<std::min((N + PN_ROWS - 1) / PN_ROWS, 148 * 4), 256, PN_ROWS * (c->M + c->P) * sizeof(float),
+                       (cudaStream_t)stream>>>(pa);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+
+static int postnet_impl(t2_ctx* c, const float* mels, int t_stride, int B, int T, int train, const unsigned char* keep, float* out,
+                        Arena& ar, cudaStream_t st) {
+  const int M = c->M, PD = c->PD;
+  float* a0 = ar.take<float>((size_t)B * T * PD);
+  float* a1 = ar.take<float>((size_t)B * T * PD);
+  if (!ar.base) return T2_OK;
+  T2_REQUIRE(!ar.overflow, T2_ERR_WORKSPACE, "t2_postnet_fwd: workspace too small");
+  T2_REQUIRE(!train, T2_ERR_UNSUPPORTED, "t2_postnet_fwd: train-mode BatchNorm statistics are not implemented in this revision");
+  const int chans[6] = {M, PD, PD, PD, PD, M};
+  const float* in = mels;
+  long long in_bs = (long long)t_stride * M;
+  float* bufs[2] = {a0, a1};
+  for (int i = 0; i < 5; ++i) {
+    ConvArgs a{};
+    a.in = in; a.in_bstride = in_bs; a.Wr = c->post_Wr[i]; a.bn_scale = c->post_scale[i]; a.bn_shift = c->post_shift[i];
+    a.keep = keep ? keep + (size_t)i * B * T * PD : nullptr; a.keep_ld = PD; a.drop_scale = 1.0f / (1.0f - c->cfg.dropout);
+    a.out = (i == 4) ? out : bufs[i & 1];
+    a.B = B; a.T = T; a.Cin = chans[i]; a.Cout = chans[i + 1]; a.k = 5; a.act = (i < 4) ? ACT_TANH : ACT_NONE;
+    RC(conv1d_cl_launch(a, st));
+    in = a.out;
+    in_bs = (long long)T * chans[i + 1];
+  }
+  return T2_OK;
+}
+
+extern "C" int t2_postnet_fwd(t2_ctx* c, const float* mels, int t_stride, int B, int T, int train, const unsigned char* keep,
+                              float* out, void* ws, long long ws_bytes, void* stream) {
+  CHECK_CTX("t2_postnet_fwd");
+  T2_REQUIRE(mels && out && ws && B > 0 && T > 0 && t_stride >= T, T2_ERR_ARG, "t2_postnet_fwd: bad argument");
+  Arena ar(ws, ws_bytes);
+  return postnet_impl(c, mels, t_stride, B, T, train, keep, out, ar, (cudaStream_t)stream);
+}
+
+extern "C" int t2_finalize(t2_ctx* c, float* mels, float* post, float* gates, const long long* lengths, int B, int T, int t_stride,
+                           void* stream) {
+  T2_REQUIRE(c && mels && post && gates && lengths, T2_ERR_ARG, "t2_finalize: null argument");
+  return finalize_launch(mels, post, gates, lengths, B, T, t_stride, c->M, (cudaStream_t)stream);
+}
+
+extern "C" long long t2_workspace_bytes(const t2_ctx* cc, int B, int L, int T) {
+  t2_ctx* c = const_cast<t2_ctx*>(cc);
+  if (!c || B <= 0 || L <= 0 || T < 0) return -1;
+  long long best = 0;
+  { Arena a(nullptr, 0); encoder_impl(c, nullptr, nullptr, B, L, 0, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
+  { Arena a(nullptr, 0); memory_impl(c, nullptr, nullptr, nullptr, B, L, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
+  { Arena a(nullptr, 0); decode_impl(c, true, nullptr, nullptr, nullptr, nullptr, nullptr, B, L, std::max(T, 1), nullptr, 0, nullptr, nullptr, 0,
+                                    nullptr, nullptr, nullptr, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
+  { Arena a(nullptr, 0); postnet_impl(c, nullptr, std::max(T, 1), B, std::max(T, 1), 0, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
+  return best + 1024;
+}

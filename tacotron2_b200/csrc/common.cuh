@@ -1,0 +1,100 @@
+// Shared device/host helpers for libt2b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+
+#define T2_OK 0
+#define T2_ERR_ARG -1
+#define T2_ERR_CUDA -2
+#define T2_ERR_STATE -3
+#define T2_ERR_WORKSPACE -4
+#define T2_ERR_UNSUPPORTED -5
+#define T2_ERR_DEVICE_ABORT -6
+
+void t2_set_error(const char* fmt, ...);
+
+#define T2_CHECK_CUDA(expr)                                                                   \
+  do {                                                                                        \
+    cudaError_t _e = (expr);                                                                  \
+    if (_e != cudaSuccess) {                                                                  \
+      t2_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e));     \
+      return T2_ERR_CUDA;                                                                     \
+    }                                                                                         \
+  } while (0)
+
+#define T2_REQUIRE(cond, code, ...)  \
+  do {                               \
+    if (!(cond)) {                   \
+      t2_set_error(__VA_ARGS__);     \
+      return (code);                 \
+    }                                \
+  } while (0)
+
+static inline int64_t round_up64(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+// Bump allocator over the caller-provided workspace.
+struct Arena {
+  char* base;
+  int64_t size, off;
+  bool overflow;
+  Arena(void* p, int64_t n) : base((char*)p), size(n), off(0), overflow(false) {}
+  template <typename T>
+  T* take(int64_t count) {
+    int64_t bytes = round_up64(count * (int64_t)sizeof(T), 256);
+    if (base == nullptr) { off += bytes; return nullptr; }  // sizing pass
+    if (off + bytes > size) { overflow = true; return nullptr; }
+    T* r = (T*)(base + off);
+    off += bytes;
+    return r;
+  }
+};
+
+#ifdef __CUDACC__
+__device__ __forceinline__ float ld_cg(const float* p) { return __ldcg(p); }
+__device__ __forceinline__ float4 ld_cg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
+
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// Counter-based RNG for in-kernel dropout when no mask is injected (masks == NULL).
+// Not bit-compatible with torch's Philox stream (the reference draws from the global
+// RNG, model/modules.py:10-12); statistically equivalent Bernoulli(1-p) keep decisions.
+__device__ __forceinline__ uint32_t mix32(uint64_t seed, uint64_t idx) {
+  uint64_t z = seed + idx * 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z = z ^ (z >> 31);
+  return (uint32_t)(z >> 32);
+}
+__device__ __forceinline__ bool rng_keep(uint64_t seed, uint64_t idx, float p) {
+  return (mix32(seed, idx) >> 8) * (1.0f / 16777216.0f) >= p;
+}
+#endif

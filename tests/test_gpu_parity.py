@@ -1,0 +1,190 @@
+"""GPU parity tests: the CUDA path (through the C ABI, via the reference-shaped modules) against
+(a) the golden vectors produced by the unmodified reference and (b) the CPU oracle on seeded inputs.
+
+Tolerances are north_star's fp32 bars: max-abs mel <= 1e-3, per-frame attention max-abs <= 1e-4,
+identical stop-gate decisions (BASELINE.json).  Most checks pass far tighter bounds; the asserted
+value is the contractual one unless a tighter one is stated.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import tacotron2_oracle as O
+from tacotron2_b200 import synth
+from tacotron2_b200.model import Tacotron2
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(__file__), "golden")
+MEL_TOL, ATT_TOL = 1e-3, 1e-4
+
+
+def _dev():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return torch.device("cuda:0")
+
+
+def _model(args, sd, train=False):
+    m = Tacotron2(**args.kwargs()).to(_dev())
+    m.load_state_dict(sd)
+    return m.train(train)
+
+
+def _err(a, b):
+    a = a.detach().float().cpu().numpy() if isinstance(a, torch.Tensor) else a
+    b = b.detach().float().cpu().numpy() if isinstance(b, torch.Tensor) else b
+    assert a.shape == b.shape, (a.shape, b.shape)
+    return float(np.max(np.abs(a - b))) if a.size else 0.0
+
+
+def _cuda(batch):
+    return {k: v.to(_dev()) for k, v in batch.items()}
+
+
+@pytest.mark.parametrize("name,args", [("step_vanilla", synth.VANILLA), ("step_conditioned", synth.CONDITIONED)])
+def test_decoder_step_golden(name, args):
+    """Decoder.forward (model/decoder.py:53-119) from a non-trivial state, vs the reference's own output."""
+    g = dict(np.load(os.path.join(G, name + ".npz")))
+    m = _model(args, synth.synth_state_dict(args, seed=0))
+    t = lambda k: torch.from_numpy(g["in/" + k]).to(_dev())  # noqa: E731
+    w_cum = t("w_cum")
+    ctrl = t("controls") if args.controls else None
+    with torch.no_grad():
+        mel, gate, (ah, ac), ctx, w, wc, (rh, rc) = m.decoder(
+            t("prev"), (t("att_h"), t("att_c")), t("ctx"), t("w"), w_cum, (t("rnn_h"), t("rnn_c")), t("memory"), t("pm"),
+            t("mask"), extra_decoder_in=ctrl)
+    assert wc is w_cum  # in-place update of the caller's tensor (model/decoder.py:90)
+    for k, v, tol in (("mel", mel, 1e-5), ("gate", gate, 1e-5), ("att_h", ah, 1e-5), ("att_c", ac, 1e-5), ("ctx", ctx, 1e-5),
+                      ("w", w, 1e-6), ("w_cum", wc, 1e-5), ("rnn_h", rh, 1e-5), ("rnn_c", rc, 1e-5)):
+        assert _err(v, g[k]) <= tol, (k, _err(v, g[k]))
+
+
+@pytest.mark.parametrize("name,args", [("ar_vanilla", synth.VANILLA), ("ar_conditioned", synth.CONDITIONED)])
+def test_ar_golden(name, args):
+    """Tacotron2.forward(teacher_forcing=False) incl. stop logic and output masking vs the reference."""
+    g = dict(np.load(os.path.join(G, name + ".npz")))
+    B, L, max_len, shift, scale = g["meta"]
+    B, L, max_len = int(B), int(L), int(max_len)
+    sd = synth.synth_state_dict(args, seed=0, gate_shift=float(shift), gate_scale=float(scale))
+    b = _cuda(synth.synth_batch(args, B, L, 8, seed=1234))
+    masks = synth.synth_masks(args, B, L, max_len, seed=7)
+    m = _model(args, sd)
+    with torch.no_grad():
+        enc = m.encoder(b["chars_idx"], b["chars_idx_len"])
+        mels, post, gates, al = m(b["chars_idx"], b["chars_idx_len"], False, speaker_id=b.get("speaker_id"),
+                                  controls=b.get("controls"), max_len_override=max_len,
+                                  description_embeddings=b.get("description_embeddings"), dropout_masks=masks)
+    assert _err(enc, g["encoded"]) <= 2e-5
+    assert mels.shape == g["mels"].shape, "frame count (stop decision) differs"
+    assert np.array_equal(gates.cpu().numpy() == -1000.0, g["gates"] == -1000.0), "stop-gate decisions differ"
+    assert _err(al, g["alignments"]) <= ATT_TOL
+    assert _err(mels, g["mels"]) <= MEL_TOL
+    assert _err(post, g["mels_post"]) <= MEL_TOL
+    assert _err(al, g["alignments"]) <= 5e-6 and _err(mels, g["mels"]) <= 5e-5  # what fp32 FMA actually achieves
+
+
+def test_tf_eval_golden():
+    """Teacher-forced forward in eval mode (bulk prenet + persistent loop) vs the reference."""
+    args = synth.HIFI
+    g = dict(np.load(os.path.join(G, "tf_eval_hifi.npz")))
+    B, L, T, _ = (int(x) for x in g["meta"])
+    b = _cuda(synth.synth_batch(args, B, L, T, seed=1234))
+    masks = synth.synth_masks(args, B, L, T, seed=7)
+    m = _model(args, synth.synth_state_dict(args, seed=0))
+    with torch.no_grad():
+        mels, post, gates, al = m(b["chars_idx"], b["chars_idx_len"], True, b["mel_spectrogram"], b["mel_spectrogram_len"],
+                                  speaker_id=b["speaker_id"], dropout_masks=masks)
+    assert _err(al, g["alignments"]) <= ATT_TOL
+    assert _err(mels, g["mels"]) <= MEL_TOL and _err(post, g["mels_post"]) <= MEL_TOL
+    assert _err(gates, g["gates"]) <= MEL_TOL
+
+
+@pytest.mark.parametrize("B,L", [(1, 1), (2, 5), (7, 64), (64, 200)])
+def test_encoder_vs_oracle(B, L):
+    """Encoder.forward incl. ragged/unsorted lengths and the packed BiLSTM (model/encoder.py:54-67)."""
+    args = synth.VANILLA
+    sd = synth.synth_state_dict(args, seed=3)
+    b = synth.synth_batch(args, B, L, 4, seed=5)
+    m = _model(args, sd)
+    with torch.no_grad():
+        got = m.encoder(b["chars_idx"].to(_dev()), b["chars_idx_len"].to(_dev()))
+    want = O.encoder(sd, b["chars_idx"], b["chars_idx_len"])
+    assert _err(got, want) <= 2e-5
+
+
+@pytest.mark.parametrize("B,T", [(1, 1), (3, 7), (5, 130)])
+def test_postnet_vs_oracle(B, T):
+    args = synth.VANILLA
+    sd = synth.synth_state_dict(args, seed=3)
+    x = torch.randn(B, args.num_mels, T, generator=torch.Generator().manual_seed(1))
+    m = _model(args, sd)
+    with torch.no_grad():
+        got = m.postnet(x.to(_dev()))
+    want = O.postnet(sd, x)
+    assert _err(got, want) <= 5e-5
+
+
+def test_c2_shape_vs_oracle():
+    """BASELINE config C2 shapes (B=64, L=200) for the first 48 frames against the CPU oracle, plus the
+    size-independent properties on the full 1000-frame run (the oracle would need minutes there)."""
+    args, B, L, T = synth.VANILLA, 64, 200, 48
+    sd = synth.synth_state_dict(args, seed=0, gate_shift=5.0)  # never stops
+    b = synth.synth_batch(args, B, L, 8, seed=1234)
+    masks = synth.synth_masks(args, B, L, 1000, seed=7)
+    m = _model(args, sd)
+    bc = _cuda(b)
+    with torch.no_grad():
+        mels, post, gates, al = m(bc["chars_idx"], bc["chars_idx_len"], False, max_len_override=T, dropout_masks=masks)
+    want = O.tacotron2_forward(sd, args, b["chars_idx"], b["chars_idx_len"], False, max_len_override=T, masks=masks)
+    assert _err(al, want[3]) <= ATT_TOL and _err(mels, want[0]) <= MEL_TOL and _err(post, want[1]) <= MEL_TOL
+    assert _err(gates, want[2]) <= MEL_TOL
+    # full length: properties
+    with torch.no_grad():
+        mels2, post2, gates2, al2 = m(bc["chars_idx"], bc["chars_idx_len"], False, max_len_override=1000, dropout_masks=masks)
+        mels3, _, _, al3 = m(bc["chars_idx"], bc["chars_idx_len"], False, max_len_override=1000, dropout_masks=masks)
+    assert mels2.shape == (B, 1000, 80) and al2.shape == (B, 1000, L)
+    assert torch.equal(mels2, mels3) and torch.equal(al2, al3), "persistent kernel is not deterministic"
+    assert torch.equal(mels2[:, :T], mels), "prefix of the long run differs from the short run"
+    assert float((al2.sum(-1) - 1).abs().max()) <= 1e-5  # softmax rows sum to one
+    pad = torch.arange(L, device=_dev())[None, :] >= bc["chars_idx_len"][:, None]
+    assert float(al2.masked_select(pad[:, None, :].expand_as(al2)).abs().max()) == 0.0  # masked columns exactly 0
+    assert torch.isfinite(mels2).all() and torch.isfinite(post2).all()
+
+
+def test_step_api_matches_persistent_loop():
+    """One launch per frame (Decoder.forward + prenet) reproduces the whole-utterance persistent kernel."""
+    args, B, L, T = synth.VANILLA, 5, 23, 6
+    sd = synth.synth_state_dict(args, seed=0, gate_shift=5.0)
+    b = _cuda(synth.synth_batch(args, B, L, 8, seed=11))
+    masks = synth.synth_masks(args, B, L, T, seed=7)
+    m = _model(args, sd)
+    with torch.no_grad():
+        mels, _, gates, al = m(b["chars_idx"], b["chars_idx_len"], False, max_len_override=T, dropout_masks=masks)
+        enc = m.encoder(b["chars_idx"], b["chars_idx_len"])
+        memory, pmem = m._memory(enc, None, None)
+        mask = torch.arange(L, device=_dev())[None, :] >= b["chars_idx_len"][:, None]
+        ah, ctx, w, wc, rh = m.init_hidden(L, B, _dev())
+        prev = torch.zeros(B, args.prenet_dim, device=_dev())
+        pk = masks["prenet"].to(_dev()).float() * 2.0
+        for t in range(T):
+            mel, gate, ah, ctx, w, wc, rh = m.decoder(prev, ah, ctx, w, wc, rh, memory, pmem, mask)
+            assert _err(mel, mels[:, t]) <= 1e-5 and _err(w, al[:, t]) <= 1e-6, t
+            h1 = torch.relu(mel @ m.prenet[0].weight.T) * pk[t + 1, 0]
+            prev = torch.relu(h1 @ m.prenet[3].weight.T) * pk[t + 1, 1]
+
+
+def test_rng_dropout_statistics():
+    """Without injected masks the kernels draw their own AlwaysDropout decisions (p = 0.5)."""
+    args = synth.VANILLA
+    m = _model(args, synth.synth_state_dict(args, seed=0))
+    from tacotron2_b200 import _lib
+    lib = m._ready(_dev())
+    x = torch.rand(4096, args.num_mels, device=_dev()) + 0.5
+    out = torch.empty(4096, args.prenet_dim, device=_dev())
+    ws = m._workspace(lib, _dev(), 1, 1, 1)
+    _lib.check(lib.t2_prenet_fwd(m._ctx, _lib.ptr(x), None, None, 1234, 4096, _lib.ptr(out), _lib.ptr(ws), ws.numel(), m._stream()))
+    ref = torch.relu(torch.relu(x @ m.prenet[0].weight.T) @ m.prenet[3].weight.T)
+    frac_zero = float((out == 0).float().mean())
+    base_zero = float((ref == 0).float().mean())
+    assert 0.45 <= (frac_zero - base_zero) / max(1e-6, 1 - base_zero) <= 0.62
