@@ -224,6 +224,16 @@ def main():
                      "frac": achieved / peak, "traffic": None, "peak_source": "measured" if peaks else "fallback",
                      "algorithmic_bytes_per_launch": bytes_launch, "kernel_ms": dec_ms, "share_of_step": dec_ms / ms},
     }
+    try:  # per-phase breakdown of the last decode launch (CTA 0's SM-clock cycles -> us per frame)
+        import ctypes
+        from tacotron2_b200 import _lib
+        cyc = (ctypes.c_ulonglong * 16)()
+        _lib.check(_lib.load().t2_debug_phase_cycles(model._ctx, cyc))
+        mhz = clocks.get("sm_mhz") or 1965
+        names = ["att_lstm", "query", "attention", "dec_lstm", "proj", "prenet1", "prenet2"]
+        line["config"]["phase_us_per_frame"] = {n: round(cyc[i] / mhz / T, 2) for i, n in enumerate(names)}
+    except Exception as e:  # noqa: BLE001
+        line["config"]["phase_us_per_frame"] = str(e)
     if not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         oracle_sample(4, threads)  # warm-up

@@ -99,6 +99,10 @@ int t2_postnet_fwd(t2_ctx* ctx, const float* mels, int t_stride, int B, int T, i
 int t2_finalize(t2_ctx* ctx, float* mels, float* post, float* gates, const long long* lengths, int B, int T, int t_stride,
                 void* stream);
 
+/* Debug: SM-clock cycles CTA 0 spent in each phase of the last decode call (host pointer, 16 slots;
+ * synchronises the device).  Slots: 0 att-LSTM, 1 query, 2 attention, 3 dec-LSTM, 4 projection, 5 prenet1, 6 prenet2. */
+int t2_debug_phase_cycles(t2_ctx* ctx, unsigned long long* host_out16);
+
 #ifdef __cplusplus
 }
 #endif

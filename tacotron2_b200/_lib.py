@@ -39,6 +39,7 @@ SIGNATURES = {
     "t2_decoder_step": (_I, [_P] + [_P] * 12 + [_I, _I] + [_P] * 9 + [_P, _LL, _P]),
     "t2_prenet_fwd": (_I, [_P, _P, _P, _P, _ULL, _I, _P, _P, _LL, _P]),
     "t2_postnet_fwd": (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _P, _LL, _P]),
+    "t2_debug_phase_cycles": (_I, [_P, _P]),
     "t2_finalize": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _P]),
 }
 

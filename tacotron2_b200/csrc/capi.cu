@@ -36,6 +36,7 @@ struct t2_ctx {
   float *post_Wr[5], *post_scale[5], *post_shift[5];
   float *lstm_Wr, *lstm_bias, *lstm_WhhT;  // BiLSTM: [1][E][2*4Hh], [2*4Hh], [2][Hh][4Hh]
   float* attenc_Wr;                        // [1][EF][A]
+  unsigned long long* prof_buf;            // [16] device, decoder phase cycles
 };
 
 namespace {
@@ -206,6 +207,8 @@ extern "C" int t2_ctx_create(const t2_model_config* cfg, t2_ctx** out) {
   c->committed = false;
   c->slab = nullptr;
   c->slab_bytes = 0;
+  c->prof_buf = nullptr;
+  T2_CHECK_CUDA(cudaMalloc((void**)&c->prof_buf, 16 * sizeof(unsigned long long)));
   *out = c;
   return T2_OK;
 }
@@ -213,6 +216,7 @@ extern "C" int t2_ctx_create(const t2_model_config* cfg, t2_ctx** out) {
 extern "C" int t2_ctx_destroy(t2_ctx* c) {
   if (!c) return T2_OK;
   if (c->slab) cudaFree(c->slab);
+  if (c->prof_buf) cudaFree(c->prof_buf);
   delete c;
   return T2_OK;
 }
@@ -471,6 +475,8 @@ static int decode_impl(t2_ctx* c, bool tf, const float* memory, const float* pme
   T2_REQUIRE(!ar.overflow, T2_ERR_WORKSPACE, "t2_decode: workspace too small");
   T2_CHECK_CUDA(cudaMemsetAsync(pl.zero_begin, 0, pl.zero_bytes, st));
   DecState s = pl.s;
+  s.prof = c->prof_buf;
+  T2_CHECK_CUDA(cudaMemsetAsync(c->prof_buf, 0, 16 * sizeof(unsigned long long), st));
   RC(fill_controls(d, s, controls, B, st));
   DecIO io{};
   io.memory = memory; io.pmem = pmem; io.mask = mask; io.prenet_keep = prenet_keep;
@@ -621,6 +627,12 @@ extern "C" int t2_finalize(t2_ctx* c, float* mels, float* post, float* gates, co
                            void* stream) {
   T2_REQUIRE(c && mels && post && gates && lengths, T2_ERR_ARG, "t2_finalize: null argument");
   return finalize_launch(mels, post, gates, lengths, B, T, t_stride, c->M, (cudaStream_t)stream);
+}
+
+extern "C" int t2_debug_phase_cycles(t2_ctx* c, unsigned long long* host_out16) {
+  T2_REQUIRE(c && host_out16, T2_ERR_ARG, "t2_debug_phase_cycles: null argument");
+  T2_CHECK_CUDA(cudaMemcpy(host_out16, c->prof_buf, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  return T2_OK;
 }
 
 extern "C" long long t2_workspace_bytes(const t2_ctx* cc, int B, int L, int T) {

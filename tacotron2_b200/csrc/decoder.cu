@@ -384,6 +384,10 @@ decoder_persistent_kernel(DecDims d, DecWeights w, DecState s, DecIO io) {
   __syncthreads();
 
   GridBar bar{s.barrier, s.barrier + 1, gridDim.x, 0u};
+  long long prof_last = clock64();
+  auto prof_mark = [&](int slot) {
+    if (blockIdx.x == 0 && threadIdx.x == 0 && s.prof) { const long long now = clock64(); s.prof[slot] += (unsigned long long)(now - prof_last); prof_last = now; }
+  };
   const int B = d.B;
   const int n_att_tiles = d.H / 8, n_dec_tiles = d.R / 8;
   const int nsplit = max(1, min((int)gridDim.x / B, d.EF / 64));
@@ -410,16 +414,19 @@ decoder_persistent_kernel(DecDims d, DecWeights w, DecState s, DecIO io) {
       __syncthreads();
     }
     if (!(alive = bar.sync())) break;
+    prof_mark(0);
 
     // ---- P2: query projection (model/attention.py:52) ---------------------------------
     warp_gemm_rm(w.Wq, d.H, d.A, s.att_h_rm, d.H, B, d.H,
                  [&](int r, int b, float v) { s.q[(size_t)b * d.A + r] = v; });
     if (!(alive = bar.sync())) break;
+    prof_mark(1);
 
     // ---- P3: location-sensitive attention ---------------------------------------------
     for (int task = blockIdx.x; task < B * nsplit; task += gridDim.x)
       attention_task(d, s, io, sm, task / nsplit, task % nsplit, nsplit, cur, tg);
     if (!(alive = bar.sync())) break;
+    prof_mark(2);
 
     // ---- P4: decoder LSTMCell ----------------------------------------------------------
     for (int tile = blockIdx.x; tile < n_dec_tiles; tile += gridDim.x) {
@@ -437,6 +444,7 @@ decoder_persistent_kernel(DecDims d, DecWeights w, DecState s, DecIO io) {
       __syncthreads();
     }
     if (!(alive = bar.sync())) break;
+    prof_mark(3);
 
     // ---- P5: mel / gate projection + stop bookkeeping ----------------------------------
     warp_gemm_rm(w.Wproj, d.KprojP, d.M + 1, s.projin, d.KprojP, B, d.KprojP, [&](int r, int b, float v) {
@@ -461,6 +469,7 @@ decoder_persistent_kernel(DecDims d, DecWeights w, DecState s, DecIO io) {
     }
     frames = t + 1;
     if (!(alive = bar.sync())) break;
+    prof_mark(4);
     if (io.teacher_forcing) continue;
 
     if (io.stop_enabled) {  // model/tacotron2.py:321-322: break once every item has fired
@@ -479,12 +488,14 @@ decoder_persistent_kernel(DecDims d, DecWeights w, DecState s, DecIO io) {
       s.p1[(size_t)b * d.P + r] = (v > 0.f && keep) ? v * pscale : 0.f;
     });
     if (!(alive = bar.sync())) break;
+    prof_mark(5);
     warp_gemm_rm(w.W2, d.P, d.P, s.p1, d.P, B, d.P, [&](int r, int b, float v) {
       const bool keep = k2 ? (k2[(size_t)b * d.P + r] != 0)
                            : rng_keep(io.seed, ((unsigned long long)(tg + 1) * 2 + 1) * B * d.P + (size_t)b * d.P + r, d.p_prenet);
       s.xpre[nxt][(size_t)r * DEC_BP + b] = (v > 0.f && keep) ? v * pscale : 0.f;
     });
     if (!(alive = bar.sync())) break;
+    prof_mark(6);
   }
   if (blockIdx.x == 0 && tid == 0) *s.n_frames = alive ? frames : -1;
 }

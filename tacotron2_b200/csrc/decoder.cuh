@@ -52,6 +52,7 @@ struct DecState {
   long long* lengths;  // [BP]
   int* n_frames;     // [1]
   unsigned* barrier; // [2]  monotonic arrival counter, abort flag
+  unsigned long long* prof;  // [16] per-phase SM-clock cycles seen by CTA 0 (debug / DESIGN.md breakdown)
 };
 
 struct DecIO {
