@@ -103,6 +103,11 @@ int t2_finalize(t2_ctx* ctx, float* mels, float* post, float* gates, const long 
  * synchronises the device).  Slots: 0 att-LSTM, 1 query, 2 attention, 3 dec-LSTM, 4 projection, 5 prenet1, 6 prenet2. */
 int t2_debug_phase_cycles(t2_ctx* ctx, unsigned long long* host_out16);
 
+/* Debug: out (rows,64) = W (rows,K) * x (64,K)^T through the decoder's tcgen05 split-K path (TMA ring,
+ * cluster of 4, DSMEM reduce).  npass 3 = fp32-parity bf16 hi/lo split, 1 = plain bf16.  Synchronous. */
+int t2_debug_tcgemm(const float* W, const float* x, float* out, int rows, int K, int npass, void* ws, long long ws_bytes,
+                    void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -40,6 +40,7 @@ SIGNATURES = {
     "t2_prenet_fwd": (_I, [_P, _P, _P, _P, _ULL, _I, _P, _P, _LL, _P]),
     "t2_postnet_fwd": (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _P, _LL, _P]),
     "t2_debug_phase_cycles": (_I, [_P, _P]),
+    "t2_debug_tcgemm": (_I, [_P, _P, _P, _I, _I, _I, _P, _LL, _P]),
     "t2_finalize": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _P]),
 }
 
