@@ -29,6 +29,7 @@ typedef struct {
   int num_speakers;     /* 0 = speaker tokens off */
   int controls_dim;     /* 0 = controls off */
   int description_dim;  /* 0 = description embeddings off (else 768 -> Linear -> 128) */
+  int precision;        /* gate GEMMs: 0 = fp32-parity (three bf16 hi/lo passes, fp32 accumulate), 1 = bf16 */
 } t2_model_config;
 
 const char* t2_last_error(void);

@@ -17,7 +17,7 @@ class T2ModelConfig(C.Structure):
         ("num_chars", C.c_int), ("encoded_dim", C.c_int), ("encoder_kernel_size", C.c_int), ("num_mels", C.c_int),
         ("prenet_dim", C.c_int), ("att_rnn_dim", C.c_int), ("att_dim", C.c_int), ("rnn_hidden_dim", C.c_int),
         ("postnet_dim", C.c_int), ("dropout", C.c_float), ("num_speakers", C.c_int), ("controls_dim", C.c_int),
-        ("description_dim", C.c_int),
+        ("description_dim", C.c_int), ("precision", C.c_int),
     ]
 
 

@@ -2,6 +2,7 @@
 #include "../../include/t2b200.h"
 #include "common.cuh"
 #include "decoder.cuh"
+#include "decoder2.cuh"
 #include "layers.cuh"
 
 #include <cstdarg>
@@ -37,6 +38,12 @@ struct t2_ctx {
   float *lstm_Wr, *lstm_bias, *lstm_WhhT;  // BiLSTM: [1][E][2*4Hh], [2*4Hh], [2][Hh][4Hh]
   float* attenc_Wr;                        // [1][EF][A]
   unsigned long long* prof_buf;            // [16] device, decoder phase cycles
+  // tensor-core decoder (decoder2)
+  __nv_bfloat16 *Watt_b, *Wdec_b;          // [2 hi/lo][4H permuted][KattP] / [2][4R][KdecP]
+  float* loc_conv_t;                       // [2][31][32]
+  D2Weights d2w;
+  CUtensorMap map_w_att, map_w_dec;
+  int npass;
 };
 
 namespace {
@@ -103,6 +110,7 @@ struct PrenetArgs {
   const float* x; const float* W1; const float* W2;
   const unsigned char* k1; const unsigned char* k2;
   unsigned long long seed; float p; int N, M, P, mode, B, T; float* out;
+  __nv_bfloat16* out_b;  // mode 2: bf16 (hi,lo) [T+1][2][D2_BP][P] for the tensor-core decoder
 };
 #define PN_ROWS 8
 __global__ void __launch_bounds__(256) prenet_rows_kernel(PrenetArgs a) {
@@ -151,11 +159,58 @@ __global__ void __launch_bounds__(256) prenet_rows_kernel(PrenetArgs a) {
           const float v = (acc[r] > 0.f && keep) ? acc[r] * scale : 0.f;
           if (layer == 0) hs[r * P + o] = v;  // safe: each thread writes only its own o, read after the barrier
           else if (a.mode == 0) a.out[(size_t)n * P + o] = v;
-          else { const int t = n / a.B, b = n % a.B; a.out[((size_t)t * P + o) * DEC_BP + b] = v; }
+          else if (a.mode == 1) { const int t = n / a.B, b = n % a.B; a.out[((size_t)t * P + o) * DEC_BP + b] = v; }
+          else {
+            const int t = n / a.B, b = n % a.B;
+            __nv_bfloat16 hi, lo;
+            tc::split_bf16(v, hi, lo);
+            a.out_b[(((size_t)t * 2 + 0) * D2_BP + b) * P + o] = hi;
+            a.out_b[(((size_t)t * 2 + 1) * D2_BP + b) * P + o] = lo;
+          }
         }
       }
       __syncthreads();
     }
+  }
+}
+
+// bf16 (hi,lo) planes of [W_ih | W_hh] with rows permuted so that each 128-row tile holds 32 hidden units and
+// rows [32j, 32j+32) of a tile are gates (i,f,g,o) x 8 units: packed row p = tile*128 + j*32 + g*8 + ul.
+__global__ void pack_lstm_bf16_kernel(const float* Wih, const float* Whh, __nv_bfloat16* out, int H, int Kin, int KP) {
+  const long long n = 4ll * H * KP;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    // destination is tile-major: [tile][kb][128 rows][64 k] so every TMA box is one contiguous 16 KB chunk
+    const int kk = (int)(i % 64);
+    const int rr = (int)((i / 64) % 128);
+    const int nkb = KP / 64;
+    const int kb = (int)((i / (64 * 128)) % nkb);
+    const int tile = (int)(i / (64ll * 128 * nkb));
+    const int k = kb * 64 + kk;
+    const int j = (rr >> 5) & 3, g = (rr >> 3) & 3, ul = rr & 7;
+    const int row = g * H + tile * 32 + j * 8 + ul;
+    float v = 0.f;
+    if (k < Kin) v = Wih[(size_t)row * Kin + k];
+    else if (k < Kin + H) v = Whh[(size_t)row * H + (k - Kin)];
+    __nv_bfloat16 hi, lo;
+    tc::split_bf16(v, hi, lo);
+    out[i] = hi;
+    out[n + i] = lo;
+  }
+}
+__global__ void conv_t_kernel(const float* w /*[32][2][31]*/, float* out /*[2][31][32]*/) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 32 * 2 * 31) return;
+  const int f = i % 32, j = (i / 32) % 31, c = i / (32 * 31);
+  out[i] = w[(f * 2 + c) * 31 + j];
+}
+// fp32 row-major (B,dim) -> bf16 (hi,lo) columns [col0, col0+dim) of x[2][BP][ld]
+__global__ void rm_to_xsplit_kernel(const float* src, int lds, __nv_bfloat16* dst, long long plane, int ld, int col0, int dim, int B) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < dim * B; i += gridDim.x * blockDim.x) {
+    const int b = i / dim, c = i % dim;
+    __nv_bfloat16 hi, lo;
+    tc::split_bf16(src[(size_t)b * lds + c], hi, lo);
+    dst[(size_t)b * ld + col0 + c] = hi;
+    dst[plane + (size_t)b * ld + col0 + c] = lo;
   }
 }
 
@@ -204,6 +259,7 @@ extern "C" int t2_ctx_create(const t2_model_config* cfg, t2_ctx** out) {
   d.Kproj = c->R + c->EF + c->C;
   d.KprojP = (int)round_up64(d.Kproj, 4);
   d.p_prenet = cfg->dropout;
+  c->npass = cfg->precision == 1 ? 1 : 3;
   c->committed = false;
   c->slab = nullptr;
   c->slab_bytes = 0;
@@ -260,6 +316,9 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   c->lstm_WhhT = ar.take<float>((size_t)2 * Hh * 4 * Hh);
   c->attenc_Wr = ar.take<float>((size_t)EF * A);
   float* tmp = ar.take<float>((size_t)8 * Hh * E);  // staging for the concatenated BiLSTM W_ih
+  c->Watt_b = ar.take<__nv_bfloat16>((size_t)2 * 4 * H * d.KattP);
+  c->Wdec_b = ar.take<__nv_bfloat16>((size_t)2 * 4 * R * d.KdecP);
+  c->loc_conv_t = ar.take<float>(2 * 31 * 32);
   if (sizing) return T2_OK;
   T2_REQUIRE(!ar.overflow, T2_ERR_STATE, "t2_ctx_commit: slab overflow");
 
@@ -292,6 +351,23 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
                                                                       R + EF + C, R + EF, d.KprojP);
   T2_CHECK_CUDA(cudaGetLastError());
   c->dw = DecWeights{Watt_p, batt, Wdec_p, bdec, wq->ptr, wv->ptr, lconv->ptr, ldense->ptr, Wproj, bproj, w1->ptr, w2->ptr};
+  // tensor-core decoder operands
+  pack_lstm_bf16_kernel<<<gsz(4ll * H * d.KattP), 256, 0, st>>>(att_ih->ptr, att_hh->ptr, c->Watt_b, H, P + EF, d.KattP);
+  pack_lstm_bf16_kernel<<<gsz(4ll * R * d.KdecP), 256, 0, st>>>(dec_ih->ptr, dec_hh->ptr, c->Wdec_b, R, H + EF + C, d.KdecP);
+  conv_t_kernel<<<(32 * 2 * 31 + 255) / 256, 256, 0, st>>>(lconv->ptr, c->loc_conv_t);
+  T2_CHECK_CUDA(cudaGetLastError());
+  c->d2w = D2Weights{batt, bdec, wq->ptr, wv->ptr, c->loc_conv_t, ldense->ptr, Wproj, bproj, w1->ptr, w2->ptr};
+  {
+    const unsigned zb = c->npass == 3 ? 2u : 1u;
+    unsigned long long dims[3] = {64ull, 4ull * H * (d.KattP / 64), 2ull};
+    unsigned long long strides[2] = {128ull, 4ull * H * d.KattP * 2};
+    unsigned box[3] = {TG_BK, TG_M, zb};
+    int rc2;
+    if ((rc2 = tc_make_tmap_bf16(&c->map_w_att, c->Watt_b, 3, dims, strides, box))) return rc2;
+    unsigned long long dims2[3] = {64ull, 4ull * R * (d.KdecP / 64), 2ull};
+    unsigned long long strides2[2] = {128ull, 4ull * R * d.KdecP * 2};
+    if ((rc2 = tc_make_tmap_bf16(&c->map_w_dec, c->Wdec_b, 3, dims2, strides2, box))) return rc2;
+  }
 
   int rc;
   for (int i = 0; i < 3; ++i) {
@@ -485,7 +561,7 @@ static int decode_impl(t2_ctx* c, bool tf, const float* memory, const float* pme
   io.hidden_dropout = train ? 1 : 0;
   if (tf) {
     T2_CHECK_CUDA(cudaMemsetAsync(tfp, 0, (size_t)(T + 1) * d.P * DEC_BP * sizeof(float), st));
-    PrenetArgs pa{mel_target, c->dw.W1, c->dw.W2, prenet_keep, prenet_keep, seed, d.p_prenet, (T + 1) * B, d.M, d.P, 1, B, T, tfp};
+    PrenetArgs pa{mel_target, c->dw.W1, c->dw.W2, prenet_keep, prenet_keep, seed, d.p_prenet, (T + 1) * B, d.M, d.P, 1, B, T, tfp, nullptr};
     prenet_rows_kernel<<<std::min(((T + 1) * B + PN_ROWS - 1) / PN_ROWS, 148 * 4), 256, PN_ROWS * (d.M + d.P) * sizeof(float), st>>>(pa);
     T2_CHECK_CUDA(cudaGetLastError());
     io.tf_prenet = tfp; io.teacher_forcing = 1; io.stop_enabled = 0;
@@ -498,6 +574,162 @@ static int decode_impl(t2_ctx* c, bool tf, const float* memory, const float* pme
   return dec_launch(d, c->dw, s, io, c->num_sms, st);
 }
 
+// ------------------------------------------------------------------------------------------ tensor-core decoder (decoder2)
+static bool use_v2() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("T2B200_DECODER"); v = (e && e[0] == '1') ? 0 : 1; }
+  return v == 1;
+}
+
+struct State2Plan { D2State s; char* zero_begin; size_t zero_bytes; };
+static State2Plan plan_state2(const D2Dims& d, int L, Arena& ar) {
+  State2Plan pl{};
+  const int64_t off0 = ar.off;
+  D2State& s = pl.s;
+  s.xatt = ar.take<__nv_bfloat16>((size_t)4 * D2_BP * d.KattP);
+  s.xdec = ar.take<__nv_bfloat16>((size_t)4 * D2_BP * d.KdecP);
+  s.att_c = ar.take<float>((size_t)d.H * D2_BP);
+  s.rnn_c = ar.take<float>((size_t)d.R * D2_BP);
+  s.att_h_rm = ar.take<float>((size_t)D2_BP * d.H);
+  s.projin = ar.take<float>((size_t)D2_BP * d.KprojP);
+  s.q = ar.take<float>((size_t)D2_BP * d.A);
+  s.w_prev = ar.take<float>((size_t)2 * D2_BP * L);
+  s.w_cum = ar.take<float>((size_t)2 * D2_BP * L);
+  s.mel_cur = ar.take<float>((size_t)D2_BP * d.M);
+  s.p1 = ar.take<float>((size_t)D2_BP * d.P);
+  s.done = ar.take<int>(D2_BP);
+  s.lengths = ar.take<long long>(D2_BP);
+  s.n_frames = ar.take<int>(4);
+  s.barrier = ar.take<unsigned>(4);
+  pl.zero_begin = ar.base ? ar.base + off0 : nullptr;
+  pl.zero_bytes = (size_t)(ar.off - off0);
+  return pl;
+}
+
+static D2Dims dims2(const t2_ctx* c, int B, int L) {
+  D2Dims d{};
+  d.B = B; d.L = L; d.EF = c->EF; d.H = c->H; d.R = c->R; d.P = c->P; d.A = c->A; d.M = c->M; d.C = c->C;
+  d.KattP = c->dd.KattP; d.KdecP = c->dd.KdecP; d.KprojP = c->dd.KprojP;
+  d.npass = c->npass; d.p_prenet = c->cfg.dropout;
+  return d;
+}
+
+// activation tensor maps: x[4 = parity*2 + hl][BP][K] bf16, box {64, 64, 1|2}
+static int make_xmaps(const t2_ctx* c, const D2Dims& d, const D2State& s, const __nv_bfloat16* tfp, int T1, D2Maps* m) {
+  const unsigned zb = d.npass == 3 ? 2u : 1u;
+  unsigned box[3] = {TG_BK, TG_N, zb};
+  int rc;
+  {
+    unsigned long long dims[3] = {(unsigned long long)d.KattP, (unsigned long long)D2_BP, 4ull};
+    unsigned long long st[2] = {(unsigned long long)d.KattP * 2, (unsigned long long)D2_BP * d.KattP * 2};
+    if ((rc = tc_make_tmap_bf16(&m->x_att, s.xatt, 3, dims, st, box))) return rc;
+    unsigned long long dims_r[3] = {(unsigned long long)(d.KattP - d.P), (unsigned long long)D2_BP, 4ull};
+    if ((rc = tc_make_tmap_bf16(&m->x_att_rest, s.xatt + d.P, 3, dims_r, st, box))) return rc;
+  }
+  {
+    unsigned long long dims[3] = {(unsigned long long)d.KdecP, (unsigned long long)D2_BP, 4ull};
+    unsigned long long st[2] = {(unsigned long long)d.KdecP * 2, (unsigned long long)D2_BP * d.KdecP * 2};
+    if ((rc = tc_make_tmap_bf16(&m->x_dec, s.xdec, 3, dims, st, box))) return rc;
+  }
+  if (tfp) {
+    unsigned long long dims[3] = {(unsigned long long)d.P, (unsigned long long)D2_BP, (unsigned long long)T1 * 2};
+    unsigned long long st[2] = {(unsigned long long)d.P * 2, (unsigned long long)D2_BP * d.P * 2};
+    if ((rc = tc_make_tmap_bf16(&m->tf_pre, tfp, 3, dims, st, box))) return rc;
+  } else {
+    m->tf_pre = m->x_att;
+  }
+  m->w_att = c->map_w_att;
+  m->w_dec = c->map_w_dec;
+  return T2_OK;
+}
+
+static int fill_controls2(const D2Dims& d, D2State& s, const float* controls, int B, cudaStream_t st) {
+  if (d.C == 0) return T2_OK;
+  T2_REQUIRE(controls, T2_ERR_ARG, "Controls are enabled, but no control vector was passed to the model!");  // model/tacotron2.py:183-185
+  const long long pd = (long long)D2_BP * d.KdecP;
+  for (int par = 0; par < 2; ++par)
+    rm_to_xsplit_kernel<<<gsz(B * d.C), 256, 0, st>>>(controls, d.C, s.xdec + (size_t)par * 2 * pd, pd, d.KdecP, d.H + d.EF, d.C, B);
+  copy2d_kernel<<<gsz(B * d.C), 256, 0, st>>>(controls, d.C, s.projin + d.R + d.EF, d.KprojP, B, d.C);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+
+static int decode2_impl(t2_ctx* c, bool tf, const float* memory, const float* pmem, const unsigned char* mask, const float* controls,
+                        const float* mel_target, int B, int L, int T, const unsigned char* prenet_keep, int train,
+                        const unsigned char* att_keep, const unsigned char* rnn_keep, unsigned long long seed, float* mels,
+                        float* gates, float* aligns, long long* lengths, int* n_frames, Arena& ar, cudaStream_t st) {
+  D2Dims d = dims2(c, B, L);
+  State2Plan pl = plan_state2(d, L, ar);
+  __nv_bfloat16* tfp = tf ? ar.take<__nv_bfloat16>((size_t)(T + 1) * 2 * D2_BP * d.P) : nullptr;
+  if (!ar.base) return T2_OK;
+  T2_REQUIRE(!ar.overflow, T2_ERR_WORKSPACE, "t2_decode: workspace too small");
+  T2_CHECK_CUDA(cudaMemsetAsync(pl.zero_begin, 0, pl.zero_bytes, st));
+  D2State s = pl.s;
+  s.prof = c->prof_buf;
+  T2_CHECK_CUDA(cudaMemsetAsync(c->prof_buf, 0, 16 * sizeof(unsigned long long), st));
+  RC(fill_controls2(d, s, controls, B, st));
+  D2IO io{};
+  io.memory = memory; io.pmem = pmem; io.mask = mask; io.prenet_keep = prenet_keep;
+  io.att_keep = att_keep; io.rnn_keep = rnn_keep; io.mels = mels; io.gates = gates; io.aligns = aligns;
+  io.Tmax = T; io.n_steps = T; io.t0 = 0; io.seed = seed; io.hidden_dropout = train ? 1 : 0;
+  io.debug_barrier = getenv("T2B200_DEBUG_BARRIER") ? 1 : 0;
+  if (tf) {
+    T2_CHECK_CUDA(cudaMemsetAsync(tfp, 0, (size_t)(T + 1) * 2 * D2_BP * d.P * sizeof(__nv_bfloat16), st));
+    PrenetArgs pa{mel_target, c->dw.W1, c->dw.W2, prenet_keep, prenet_keep, seed, d.p_prenet, (T + 1) * B, d.M, d.P, 2, B, T, nullptr, tfp};
+    prenet_rows_kernel<<<std::min(((T + 1) * B + PN_ROWS - 1) / PN_ROWS, 148 * 4), 256, PN_ROWS * (d.M + d.P) * sizeof(float), st>>>(pa);
+    T2_CHECK_CUDA(cudaGetLastError());
+    io.teacher_forcing = 1; io.stop_enabled = 0;
+  } else {
+    io.teacher_forcing = 0; io.stop_enabled = 1;
+    T2_CHECK_CUDA(cudaMemsetAsync(lengths, 0, (size_t)B * sizeof(long long), st));
+    s.lengths = lengths;
+    s.n_frames = n_frames;
+  }
+  D2Maps maps;
+  RC(make_xmaps(c, d, s, tfp, T + 1, &maps));
+  return d2_launch(d, c->d2w, s, io, maps, st);
+}
+
+static int step2_impl(t2_ctx* c, const float* prev, const float* att_h, const float* att_c, const float* ctx, const float* w,
+                      const float* w_cum, const float* rnn_h, const float* rnn_c, const float* memory, const float* pmem,
+                      const unsigned char* mask, const float* controls, int B, int L, float* mel_out, float* gate_out,
+                      float* att_h_out, float* att_c_out, float* ctx_out, float* w_out, float* w_cum_out, float* rnn_h_out,
+                      float* rnn_c_out, Arena& ar, cudaStream_t st) {
+  D2Dims d = dims2(c, B, L);
+  State2Plan pl = plan_state2(d, L, ar);
+  __nv_bfloat16* tfp = ar.take<__nv_bfloat16>((size_t)2 * D2_BP * d.P);
+  if (!ar.base) return T2_OK;
+  T2_REQUIRE(!ar.overflow, T2_ERR_WORKSPACE, "t2_decoder_step: workspace too small");
+  T2_CHECK_CUDA(cudaMemsetAsync(pl.zero_begin, 0, pl.zero_bytes, st));
+  T2_CHECK_CUDA(cudaMemsetAsync(tfp, 0, (size_t)2 * D2_BP * d.P * sizeof(__nv_bfloat16), st));
+  D2State s = pl.s;
+  RC(fill_controls2(d, s, controls, B, st));
+  const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP, pp = (long long)D2_BP * d.P;
+  rm_to_xsplit_kernel<<<gsz(B * d.P), 256, 0, st>>>(prev, d.P, tfp, pp, d.P, 0, d.P, B);
+  rm_to_xsplit_kernel<<<gsz(B * d.EF), 256, 0, st>>>(ctx, d.EF, s.xatt, pa, d.KattP, d.P, d.EF, B);
+  rm_to_xsplit_kernel<<<gsz(B * d.H), 256, 0, st>>>(att_h, d.H, s.xatt, pa, d.KattP, d.P + d.EF, d.H, B);
+  rm_to_xsplit_kernel<<<gsz(B * d.R), 256, 0, st>>>(rnn_h, d.R, s.xdec, pd, d.KdecP, d.H + d.EF + d.C, d.R, B);
+  rm_to_km_kernel<<<gsz(d.H * D2_BP), 256, 0, st>>>(att_c, d.H, s.att_c, 0, d.H, B);
+  rm_to_km_kernel<<<gsz(d.R * D2_BP), 256, 0, st>>>(rnn_c, d.R, s.rnn_c, 0, d.R, B);
+  copy2d_kernel<<<gsz(B * L), 256, 0, st>>>(w, L, s.w_prev, L, B, L);
+  copy2d_kernel<<<gsz(B * L), 256, 0, st>>>(w_cum, L, s.w_cum, L, B, L);
+  T2_CHECK_CUDA(cudaGetLastError());
+  D2IO io{};
+  io.memory = memory; io.pmem = pmem; io.mask = mask; io.teacher_forcing = 1; io.stop_enabled = 0;
+  io.mels = mel_out; io.gates = gate_out; io.aligns = w_out; io.Tmax = 1; io.n_steps = 1; io.t0 = 0;
+  D2Maps maps;
+  RC(make_xmaps(c, d, s, tfp, 1, &maps));
+  RC(d2_launch(d, c->d2w, s, io, maps, st));
+  copy2d_kernel<<<gsz(B * d.H), 256, 0, st>>>(s.att_h_rm, d.H, att_h_out, d.H, B, d.H);
+  km_to_rm_kernel<<<gsz(B * d.H), 256, 0, st>>>(s.att_c, 0, att_c_out, d.H, d.H, B);
+  copy2d_kernel<<<gsz(B * d.EF), 256, 0, st>>>(s.projin + d.R, d.KprojP, ctx_out, d.EF, B, d.EF);
+  copy2d_kernel<<<gsz(B * L), 256, 0, st>>>(s.w_cum + (size_t)D2_BP * L, L, w_cum_out, L, B, L);
+  copy2d_kernel<<<gsz(B * d.R), 256, 0, st>>>(s.projin, d.KprojP, rnn_h_out, d.R, B, d.R);
+  km_to_rm_kernel<<<gsz(B * d.R), 256, 0, st>>>(s.rnn_c, 0, rnn_c_out, d.R, d.R, B);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+
 extern "C" int t2_decode_ar(t2_ctx* c, const float* memory, const float* processed_memory, const unsigned char* mask,
                             const float* controls, int B, int L, int max_len, const unsigned char* prenet_keep,
                             unsigned long long seed, float* mels, float* gates, float* alignments, long long* lengths,
@@ -507,8 +739,9 @@ extern "C" int t2_decode_ar(t2_ctx* c, const float* memory, const float* process
              "t2_decode_ar: null argument");
   T2_REQUIRE(B > 0 && L > 0 && max_len > 0, T2_ERR_ARG, "t2_decode_ar: bad sizes B=%d L=%d max_len=%d", B, L, max_len);
   Arena ar(ws, ws_bytes);
-  return decode_impl(c, false, memory, processed_memory, mask, controls, nullptr, B, L, max_len, prenet_keep, 0, nullptr, nullptr,
-                     seed, mels, gates, alignments, lengths, n_frames, ar, (cudaStream_t)stream);
+  return (use_v2() ? decode2_impl : decode_impl)(c, false, memory, processed_memory, mask, controls, nullptr, B, L, max_len, prenet_keep,
+                                                 0, nullptr, nullptr, seed, mels, gates, alignments, lengths, n_frames, ar,
+                                                 (cudaStream_t)stream);
 }
 
 extern "C" int t2_decode_tf(t2_ctx* c, const float* memory, const float* processed_memory, const unsigned char* mask,
@@ -520,8 +753,9 @@ extern "C" int t2_decode_tf(t2_ctx* c, const float* memory, const float* process
              "Ground-truth Mel spectrogram is required for teacher forcing");  // model/tacotron2.py:168-170
   T2_REQUIRE(B > 0 && L > 0 && T > 0, T2_ERR_ARG, "t2_decode_tf: bad sizes");
   Arena ar(ws, ws_bytes);
-  return decode_impl(c, true, memory, processed_memory, mask, controls, mel_target, B, L, T, prenet_keep, train, att_keep, rnn_keep,
-                     seed, mels, gates, alignments, nullptr, nullptr, ar, (cudaStream_t)stream);
+  return (use_v2() ? decode2_impl : decode_impl)(c, true, memory, processed_memory, mask, controls, mel_target, B, L, T, prenet_keep,
+                                                 train, att_keep, rnn_keep, seed, mels, gates, alignments, nullptr, nullptr, ar,
+                                                 (cudaStream_t)stream);
 }
 
 static int step_impl(t2_ctx* c, const float* prev, const float* att_h, const float* att_c, const float* ctx, const float* w,
@@ -573,9 +807,9 @@ extern "C" int t2_decoder_step(t2_ctx* c, const float* prev_mel_prenet, const fl
                  mel_out && gate_out && att_h_out && att_c_out && att_ctx_out && w_out && w_cum_out && rnn_h_out && rnn_c_out && ws,
              T2_ERR_ARG, "t2_decoder_step: null argument");
   Arena ar(ws, ws_bytes);
-  return step_impl(c, prev_mel_prenet, att_h, att_c, att_ctx, w, w_cum, rnn_h, rnn_c, memory, processed_memory, mask, controls, B, L,
-                   mel_out, gate_out, att_h_out, att_c_out, att_ctx_out, w_out, w_cum_out, rnn_h_out, rnn_c_out, ar,
-                   (cudaStream_t)stream);
+  return (use_v2() ? step2_impl : step_impl)(c, prev_mel_prenet, att_h, att_c, att_ctx, w, w_cum, rnn_h, rnn_c, memory, processed_memory,
+                                             mask, controls, B, L, mel_out, gate_out, att_h_out, att_c_out, att_ctx_out, w_out,
+                                             w_cum_out, rnn_h_out, rnn_c_out, ar, (cudaStream_t)stream);
 }
 
 extern "C" int t2_prenet_fwd(t2_ctx* c, const float* x, const unsigned char* keep1, const unsigned char* keep2,
@@ -583,7 +817,7 @@ extern "C" int t2_prenet_fwd(t2_ctx* c, const float* x, const unsigned char* kee
   CHECK_CTX("t2_prenet_fwd");
   T2_REQUIRE(x && out && N > 0, T2_ERR_ARG, "t2_prenet_fwd: bad argument");
   (void)ws; (void)ws_bytes;
-  PrenetArgs pa{x, c->dw.W1, c->dw.W2, keep1, keep2, seed, c->cfg.dropout, N, c->M, c->P, 0, 0, 0, out};
+  PrenetArgs pa{x, c->dw.W1, c->dw.W2, keep1, keep2, seed, c->cfg.dropout, N, c->M, c->P, 0, 0, 0, out, nullptr};
   prenet_rows_kernel<<<std::min((N + PN_ROWS - 1) / PN_ROWS, 148 * 4), 256, PN_ROWS * (c->M + c->P) * sizeof(float),
                        (cudaStream_t)stream>>>(pa);
   T2_CHECK_CUDA(cudaGetLastError());
@@ -643,6 +877,8 @@ extern "C" long long t2_workspace_bytes(const t2_ctx* cc, int B, int L, int T) {
   { Arena a(nullptr, 0); memory_impl(c, nullptr, nullptr, nullptr, B, L, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
   { Arena a(nullptr, 0); decode_impl(c, true, nullptr, nullptr, nullptr, nullptr, nullptr, B, L, std::max(T, 1), nullptr, 0, nullptr, nullptr, 0,
                                     nullptr, nullptr, nullptr, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
+  { Arena a(nullptr, 0); decode2_impl(c, true, nullptr, nullptr, nullptr, nullptr, nullptr, B, L, std::max(T, 1), nullptr, 0, nullptr, nullptr, 0,
+                                     nullptr, nullptr, nullptr, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
   { Arena a(nullptr, 0); postnet_impl(c, nullptr, std::max(T, 1), B, std::max(T, 1), 0, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
   return best + 1024;
 }

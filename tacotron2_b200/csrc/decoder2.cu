@@ -1,0 +1,569 @@
+// Persistent autoregressive decoder kernel, tensor-core revision.  One launch decodes the whole utterance
+// batch: 32 clusters x 4 CTAs (one CTA per SM), per frame
+//   P1 attention LSTMCell   gate GEMM on tcgen05 (TMA ring, split-K over the cluster, DSMEM reduce) + pointwise
+//   P2 query projection     (model/attention.py:52)
+//   P3 location-sensitive attention (model/attention.py:54-67, model/decoder.py:90)
+//   P4 decoder LSTMCell     same engine as P1 (model/decoder.py:94-101)
+//   P5 mel / gate projection + stop bookkeeping (model/decoder.py:103-109, model/tacotron2.py:311-322)
+//   P6/P7 prenet on the emitted frame (model/tacotron2.py:85-92,324-325)
+// separated by grid barriers.  Recurrent state never leaves the chip boundary it does not have to:
+// cell states live in shared memory, hidden states travel as bf16 (hi,lo) pairs for the next GEMM.
+#include "decoder2.cuh"
+
+namespace {
+
+struct GridBar {
+  unsigned* ctr;
+  unsigned* abort_flag;
+  unsigned nblocks;
+  unsigned epoch;
+  // `fail` = this CTA hit a pipeline timeout: it raises the abort flag before arriving so every CTA leaves together.
+  __device__ bool sync(bool fail) {
+    // generic-proxy global writes of this phase must be ordered before the TMA (async proxy) reads of the next one
+    asm volatile("fence.proxy.async;" ::: "memory");
+    __syncthreads();
+    __shared__ int ok_s;
+    if (threadIdx.x == 0) {
+      ++epoch;
+      if (fail) atomicExch(abort_flag, 1u);
+      __threadfence();
+      atomicAdd(ctr, 1u);
+      const unsigned target = epoch * nblocks;
+      long long spins = 0;
+      while (ld_acquire_u32(ctr) < target) {
+        if (++spins > (1ll << 24)) {
+          if (ld_acquire_u32(abort_flag) != 0u || spins > (1ll << 27)) { atomicExch(abort_flag, 1u); break; }
+        }
+      }
+      ok_s = (ld_acquire_u32(abort_flag) == 0u);
+      __threadfence();
+    }
+    __syncthreads();
+    asm volatile("fence.proxy.async;" ::: "memory");
+    return ok_s != 0;
+  }
+};
+
+// ------------------------------------------------------------------------------------------
+// Small dense phases on CUDA cores: out[b][r] = sum_k W[r][k] x[b][k].  The 128 CTAs form a 16 x 8 grid of
+// (row group, batch group of 8); W rows and x rows are staged in shared memory (row stride K+4 floats:
+// conflict-free float4 reads), 128 outputs per CTA, two K-halves per output.
+template <typename Epi>
+__device__ __forceinline__ void small_gemm(const float* __restrict__ W, int ldw, int rows, const float* x, int ldx, int B, int K,
+                                           float* scratch, Epi epi) {
+  const int tid = threadIdx.x;
+  const int rg = blockIdx.x >> 3, bg = blockIdx.x & 7;
+  const int rpc = (rows + 15) >> 4;           // rows per CTA (<= 16)
+  const int r0 = rg * rpc, b0 = bg * 8;
+  const int nr = max(0, min(rpc, rows - r0)), nb = max(0, min(8, B - b0));
+  if (blockIdx.x >= 128 || nr == 0 || nb == 0) return;
+  const int ld = K + 4, K4 = K >> 2;
+  float* Ws = scratch;                        // [rpc][ld]
+  float* xs = scratch + rpc * ld;             // [8][ld]
+  float* red = xs + 8 * ld;                   // [128]
+  for (int i = tid; i < nr * K4; i += D2_THREADS) {
+    const int r = i / K4, c = i % K4;
+    cp_async16(Ws + r * ld + c * 4, W + (size_t)(r0 + r) * ldw + c * 4);
+  }
+  for (int i = tid; i < nb * K4; i += D2_THREADS) {
+    const int b = i / K4, c = i % K4;
+    cp_async16(xs + b * ld + c * 4, x + (size_t)(b0 + b) * ldx + c * 4);
+  }
+  cp_async_commit();
+  cp_async_wait<0>();
+  __syncthreads();
+  const int o = tid & 127, kh = tid >> 7;
+  const int r = o >> 3, b = o & 7;
+  float acc = 0.f;
+  if (r < nr && b < nb) {
+    const float4* wp = reinterpret_cast<const float4*>(Ws + r * ld);
+    const float4* xp = reinterpret_cast<const float4*>(xs + b * ld);
+    const int kbeg = kh * (K4 >> 1), kend = kh ? K4 : (K4 >> 1);
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll 4
+    for (int k = kbeg; k < kend; ++k) {
+      const float4 wv = wp[k], xv = xp[k];
+      a0 = fmaf(wv.x, xv.x, a0); a1 = fmaf(wv.y, xv.y, a1); a2 = fmaf(wv.z, xv.z, a2); a3 = fmaf(wv.w, xv.w, a3);
+    }
+    acc = (a0 + a1) + (a2 + a3);
+  }
+  if (kh == 1) red[o] = acc;
+  __syncthreads();
+  if (kh == 0 && r < nr && b < nb) epi(r0 + r, b0 + b, acc + red[o]);
+  __syncthreads();
+}
+
+// ------------------------------------------------------------------------------------------
+// Shared-memory plan (bytes from the 1024-aligned base):
+//   [0, 3*48K)            TMA stage ring (also scratch for the CUDA-core phases, which never overlap it)
+//   part[128][68] f32     split-K partial accumulator (read by cluster peers)
+//   c_att[8][64], c_dec[8][64] f32   cell states of this CTA's 8 hidden units
+//   attention constants   conv_t[2*31*32] | dense[A*32] | v[A]
+//   barriers, tmem slot
+struct Smem {
+  uint8_t* stages;
+  float* part;
+  float* c_att;
+  float* c_dec;
+  float* conv_t;
+  float* dense;
+  float* v;
+  uint64_t* bars;
+  uint32_t* tmem_slot;
+};
+
+__device__ __forceinline__ Smem carve(uint8_t* base, const D2Dims& d) {
+  Smem s;
+  s.stages = base;
+  uint8_t* p = base + D2_STAGES * TG_STAGE_BYTES;
+  s.part = reinterpret_cast<float*>(p);  p += TG_M * TG_PART_LD * 4;
+  s.c_att = reinterpret_cast<float*>(p); p += 8 * D2_BP * 4;
+  s.c_dec = reinterpret_cast<float*>(p); p += 8 * D2_BP * 4;
+  s.conv_t = reinterpret_cast<float*>(p); p += 2 * D2_LOC_K * D2_LOC_F * 4;
+  s.dense = reinterpret_cast<float*>(p); p += d.A * D2_LOC_F * 4;
+  s.v = reinterpret_cast<float*>(p);     p += d.A * 4;
+  s.bars = reinterpret_cast<uint64_t*>(p); p += (2 * D2_STAGES + 2) * 8;
+  s.tmem_slot = reinterpret_cast<uint32_t*>(p);
+  return s;
+}
+
+// ------------------------------------------------------------------------------------------
+// LSTM phase tail: split-K reduce over the cluster + gate nonlinearities for this CTA's 8 units.
+// Tile rows are packed so that rows [32*rank, 32*rank+32) = gates (i,f,g,o) x 8 units of CTA `rank`.
+struct HOut {
+  __nv_bfloat16* x0; int ld0, col0;   // bf16 (hi,lo) destination: element (b, col0+u) of [2][BP][ld0]; lo plane at +plane0
+  long long plane0;
+  __nv_bfloat16* x1; int ld1, col1;
+  long long plane1;
+  float* rm; int rm_ld, rm_col;       // fp32 row-major destination [b][rm_ld]
+};
+
+__device__ __forceinline__ void store_split(__nv_bfloat16* base, long long plane, int ld, int b, int col, float h) {
+  __nv_bfloat16 hi, lo;
+  tc::split_bf16(h, hi, lo);
+  base[(size_t)b * ld + col] = hi;
+  base[plane + (size_t)b * ld + col] = lo;
+}
+
+__device__ __forceinline__ void lstm_tail(const float* part, uint32_t rank, int unit0, const float* __restrict__ bias, int H,
+                                          float* cst, int B, const HOut& ho, const unsigned char* keep, bool hidden_dropout,
+                                          unsigned long long seed, unsigned long long rng_base) {
+  const int ul = threadIdx.x >> 5, bp = threadIdx.x & 31;
+  const int u = unit0 + ul;
+  float2 pre[4];
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    pre[g] = tg::reduce4(part, 32 * (int)rank + g * 8 + ul, 2 * bp);
+    const float bv = __ldg(bias + g * H + u);
+    pre[g].x += bv; pre[g].y += bv;
+  }
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int b = 2 * bp + j;
+    if (b >= B) continue;
+    const float pi = j ? pre[0].y : pre[0].x, pf = j ? pre[1].y : pre[1].x;
+    const float pg = j ? pre[2].y : pre[2].x, po = j ? pre[3].y : pre[3].x;
+    const float c = sigmoidf_(pf) * cst[ul * D2_BP + b] + sigmoidf_(pi) * tanhf(pg);
+    float h = sigmoidf_(po) * tanhf(c);
+    cst[ul * D2_BP + b] = c;
+    if (hidden_dropout) {  // nn.Dropout(0.1), train only (model/decoder.py:75,101)
+      const bool k = keep ? (keep[(size_t)b * H + u] != 0) : rng_keep(seed, rng_base + (unsigned long long)b * H + u, 0.1f);
+      h = k ? h * (1.0f / 0.9f) : 0.f;
+    }
+    if (ho.x0) store_split(ho.x0, ho.plane0, ho.ld0, b, ho.col0 + u, h);
+    if (ho.x1) store_split(ho.x1, ho.plane1, ho.ld1, b, ho.col1 + u, h);
+    if (ho.rm) ho.rm[(size_t)b * ho.rm_ld + ho.rm_col + u] = h;
+  }
+}
+
+__device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  v = is_max ? warp_max(v) : warp_sum(v);
+  __syncthreads();
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float r = red[0];
+#pragma unroll
+  for (int i = 1; i < D2_THREADS / 32; ++i) r = is_max ? fmaxf(r, red[i]) : r + red[i];
+  return r;
+}
+
+// ------------------------------------------------------------------------------------------
+// Attention for batch element b, part `part` of `S` (the S CTAs of one b sit in the same cluster):
+// each part computes the energies of its L-slice, the slices are exchanged through DSMEM, every part
+// normalises the full row and reduces its slice of the context columns.
+// Scratch (floats, in the idle TMA ring): q[A] | wp[Lc+32] | wc[Lc+32] | fs[Lc][33] | epart[8][Lc] | e_slice[Lc] |
+//                                         e_full[L] | red[64] | cred[4*cols]
+__device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& io, const Smem& sm, float* scratch, bool active,
+                                int b, int part, int S, int cur, int t_out) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int L = d.L, A = d.A, EF = d.EF;
+  const int Lc = (L + S - 1) / S, l0 = part * Lc, l1 = min(L, l0 + Lc), nl = max(0, l1 - l0);
+  const int nxt = cur ^ 1;
+  float* q_s = scratch;
+  float* wp = q_s + A;
+  float* wc = wp + Lc + 32;
+  float* fs = wc + Lc + 32;
+  float* epart = fs + Lc * 33;
+  float* e_slice = epart + 8 * Lc;
+  float* e_full = e_slice + ((Lc + 3) & ~3);
+  float* red = e_full + ((L + 3) & ~3);
+  float* cred = scratch + (((red + 64) - scratch + 3) & ~3);
+  if (active) {
+    const float* wprev = s.w_prev + ((size_t)cur * D2_BP + b) * L;
+    const float* wcum = s.w_cum + ((size_t)cur * D2_BP + b) * L;
+    for (int i = tid; i < A; i += D2_THREADS) q_s[i] = ld_cg(s.q + (size_t)b * A + i);
+    for (int i = tid; i < nl + 30; i += D2_THREADS) {
+      const int l = l0 + i - 15;
+      const bool in = (l >= 0 && l < L);
+      wp[i] = in ? ld_cg(wprev + l) : 0.f;
+      wc[i] = in ? ld_cg(wcum + l) : 0.f;
+    }
+    __syncthreads();
+    // location conv: item = (position, group of 4 filters)  (model/attention.py:54)
+    for (int it = tid; it < nl * 8; it += D2_THREADS) {
+      const int fg = it / nl, li = it % nl;
+      float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int j = 0; j < D2_LOC_K; ++j) {
+        const float a0 = wp[li + j], a1 = wc[li + j];
+        const float4 w0 = *reinterpret_cast<const float4*>(sm.conv_t + (0 * D2_LOC_K + j) * D2_LOC_F + fg * 4);
+        const float4 w1 = *reinterpret_cast<const float4*>(sm.conv_t + (1 * D2_LOC_K + j) * D2_LOC_F + fg * 4);
+        f.x = fmaf(w0.x, a0, f.x); f.y = fmaf(w0.y, a0, f.y); f.z = fmaf(w0.z, a0, f.z); f.w = fmaf(w0.w, a0, f.w);
+        f.x = fmaf(w1.x, a1, f.x); f.y = fmaf(w1.y, a1, f.y); f.z = fmaf(w1.z, a1, f.z); f.w = fmaf(w1.w, a1, f.w);
+      }
+      float* dst = fs + li * 33 + fg * 4;
+      dst[0] = f.x; dst[1] = f.y; dst[2] = f.z; dst[3] = f.w;
+    }
+    __syncthreads();
+    // location dense + tanh energies: warp = group of A/8 attention dims, lane = position (model/attention.py:55-62)
+    const int ag = A >> 3, a0 = warp * ag;
+    const unsigned char* mk = io.mask + (size_t)b * L;
+    for (int lb = 0; lb < nl; lb += 32) {
+      const int li = lb + lane;
+      float e = 0.f;
+      if (li < nl && mk[l0 + li] == 0) {
+        const float* pm = io.pmem + ((size_t)b * L + l0 + li) * A + a0;
+        float4 p4[D2_MAX_A / 32];  // this warp's A/8 processed-memory values for position li, fetched up front
+#pragma unroll
+        for (int a = 0; a < D2_MAX_A / 32; ++a)
+          if (a * 4 < ag) p4[a] = __ldg(reinterpret_cast<const float4*>(pm) + a);
+        float f[D2_LOC_F];
+#pragma unroll
+        for (int i = 0; i < D2_LOC_F; ++i) f[i] = fs[li * 33 + i];
+#pragma unroll
+        for (int a4 = 0; a4 < D2_MAX_A / 32; ++a4) {
+          if (a4 * 4 >= ag) break;
+          const float pv[4] = {p4[a4].x, p4[a4].y, p4[a4].z, p4[a4].w};
+#pragma unroll
+          for (int aa = 0; aa < 4; ++aa) {
+            const int a = a0 + a4 * 4 + aa;
+            const float4* dr = reinterpret_cast<const float4*>(sm.dense + a * D2_LOC_F);
+            float l0a = 0.f, l1a = 0.f, l2a = 0.f, l3a = 0.f;
+#pragma unroll
+            for (int i = 0; i < D2_LOC_F / 4; i += 2) {
+              const float4 w4 = dr[i], w5 = dr[i + 1];
+              l0a = fmaf(w4.x, f[4 * i + 0], l0a); l1a = fmaf(w4.y, f[4 * i + 1], l1a);
+              l2a = fmaf(w4.z, f[4 * i + 2], l2a); l3a = fmaf(w4.w, f[4 * i + 3], l3a);
+              l0a = fmaf(w5.x, f[4 * i + 4], l0a); l1a = fmaf(w5.y, f[4 * i + 5], l1a);
+              l2a = fmaf(w5.z, f[4 * i + 6], l2a); l3a = fmaf(w5.w, f[4 * i + 7], l3a);
+            }
+            e = fmaf(sm.v[a], tanhf(q_s[a] + ((l0a + l1a) + (l2a + l3a)) + pv[aa]), e);
+          }
+        }
+      }
+      if (li < nl) epart[warp * Lc + li] = e;
+    }
+    __syncthreads();
+    for (int li = tid; li < nl; li += D2_THREADS) {
+      float e = -INFINITY;
+      if (mk[l0 + li] == 0) {
+        e = 0.f;
+#pragma unroll
+        for (int w8 = 0; w8 < 8; ++w8) e += epart[w8 * Lc + li];
+      }
+      e_slice[li] = e;  // masked_fill(-inf) (model/attention.py:63)
+    }
+  }
+  tc::cluster_sync();  // energy slices visible to the peers of this batch element
+  if (active) {
+    // gather the full energy row from the S parts (cluster ranks base..base+S-1)
+    const uint32_t my_rank = tc::cluster_ctarank();
+    const uint32_t base_rank = my_rank - (uint32_t)part;
+    const uint32_t ea = tc::smem_u32(e_slice);
+    for (int l = tid; l < L; l += D2_THREADS) {
+      const int pr = l / Lc, li = l - pr * Lc;
+      float v;
+      asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(tc::mapa(ea + 4u * (uint32_t)li, base_rank + (uint32_t)pr)) : "memory");
+      e_full[l] = v;
+    }
+    __syncthreads();
+    float mx = -INFINITY;
+    for (int l = tid; l < L; l += D2_THREADS) mx = fmaxf(mx, e_full[l]);
+    mx = block_reduce(mx, red, true);
+    float sum = 0.f;
+    for (int l = tid; l < L; l += D2_THREADS) {
+      const float p = expf(e_full[l] - mx);
+      e_full[l] = p;
+      sum += p;
+    }
+    sum = block_reduce(sum, red + 32, false);
+    const float inv = 1.0f / sum;
+    for (int l = tid; l < L; l += D2_THREADS) {
+      const float w = e_full[l] * inv;
+      e_full[l] = w;
+      if (l >= l0 && l < l1) {  // each part publishes its own slice
+        s.w_prev[((size_t)nxt * D2_BP + b) * L + l] = w;
+        s.w_cum[((size_t)nxt * D2_BP + b) * L + l] = wc[l - l0 + 15] + w;  // model/decoder.py:90
+        io.aligns[((size_t)b * io.Tmax + t_out) * L + l] = w;
+      }
+    }
+    __syncthreads();
+    // context columns of this part (model/attention.py:66-67)
+    const int cols_per = ((EF + S - 1) / S + 3) & ~3;
+    const int c0 = part * cols_per, c1 = min(EF, c0 + cols_per);
+    const int nq = max(0, (c1 - c0 + 3) >> 2);
+    const float* mem = io.memory + (size_t)b * L * EF;
+    const int lg = tid >> 6, cq0 = tid & 63;
+    const unsigned char* mk2 = io.mask + (size_t)b * L;
+    int Leff = 0;  // positions beyond the last unmasked one carry weight exactly 0 (softmax of -inf): skip them
+    for (int l = tid; l < L; l += D2_THREADS) if (mk2[l] == 0) Leff = max(Leff, l + 1);
+    Leff = (int)block_reduce((float)Leff, red, true);
+    for (int cq = cq0; cq < nq; cq += 64) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4* mp = reinterpret_cast<const float4*>(mem + c0) + cq;
+      const size_t rs = (size_t)EF / 4;  // row stride in float4
+      int l = lg;
+      for (; l + 28 < Leff; l += 32) {  // 8 independent 16-byte loads in flight per thread
+        float4 m[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) m[u] = __ldg(mp + (size_t)(l + 4 * u) * rs);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const float w = e_full[l + 4 * u];
+          acc.x = fmaf(w, m[u].x, acc.x); acc.y = fmaf(w, m[u].y, acc.y);
+          acc.z = fmaf(w, m[u].z, acc.z); acc.w = fmaf(w, m[u].w, acc.w);
+        }
+      }
+      for (; l < Leff; l += 4) {
+        const float4 m4 = __ldg(mp + (size_t)l * rs);
+        const float w = e_full[l];
+        acc.x = fmaf(w, m4.x, acc.x); acc.y = fmaf(w, m4.y, acc.y);
+        acc.z = fmaf(w, m4.z, acc.z); acc.w = fmaf(w, m4.w, acc.w);
+      }
+      *reinterpret_cast<float4*>(cred + (size_t)lg * cols_per + cq * 4) = acc;
+    }
+    __syncthreads();
+    const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
+    __nv_bfloat16* xa = s.xatt + (size_t)nxt * 2 * pa;   // next frame's attention-LSTM input
+    __nv_bfloat16* xd = s.xdec + (size_t)cur * 2 * pd;   // this frame's decoder-LSTM input
+    for (int c = tid; c < c1 - c0; c += D2_THREADS) {
+      const float v = cred[c] + cred[cols_per + c] + cred[2 * cols_per + c] + cred[3 * cols_per + c];
+      const int col = c0 + c;
+      store_split(xa, pa, d.KattP, b, d.P + col, v);
+      store_split(xd, pd, d.KdecP, b, d.H + col, v);
+      s.projin[(size_t)b * d.KprojP + d.R + col] = v;
+    }
+  }
+  tc::cluster_sync();  // peers are done reading this CTA's energy slice before the scratch is reused
+}
+
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(D2_THREADS, 1)
+decoder2_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weights w, D2State s, D2IO io) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* base = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const Smem sm = carve(base, d);
+  float* scratch = reinterpret_cast<float*>(sm.stages);
+  const int tid = threadIdx.x;
+  const uint32_t rank = tc::cluster_ctarank();
+  const int tile = blockIdx.x / D2_CLUSTER;       // 128-row gate tile = 32 hidden units
+  const int unit0 = tile * 32 + (int)rank * 8;    // this CTA's 8 hidden units (both LSTMs)
+  const int B = d.B;
+
+  if (tid == 0) {
+    tc::prefetch_tmap(&maps.w_att); tc::prefetch_tmap(&maps.w_dec); tc::prefetch_tmap(&maps.x_att);
+    tc::prefetch_tmap(&maps.x_att_rest); tc::prefetch_tmap(&maps.x_dec); tc::prefetch_tmap(&maps.tf_pre);
+  }
+  for (int i = tid; i < 2 * D2_LOC_K * D2_LOC_F; i += D2_THREADS) sm.conv_t[i] = w.loc_conv_t[i];
+  for (int i = tid; i < d.A * D2_LOC_F; i += D2_THREADS) sm.dense[i] = w.loc_dense[i];
+  for (int i = tid; i < d.A; i += D2_THREADS) sm.v[i] = w.v[i];
+  for (int i = tid; i < 8 * D2_BP; i += D2_THREADS) {
+    sm.c_att[i] = s.att_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP];
+    sm.c_dec[i] = s.rnn_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP];
+  }
+  tg::Pipe pipe;
+  tg::pipe_init(pipe, sm.bars, sm.stages, D2_STAGES, d.npass, sm.tmem_slot);
+  tc::cluster_sync();
+
+  GridBar bar{s.barrier, s.barrier + 1, gridDim.x, 0u};
+  long long prof_last = clock64();
+  auto prof_mark = [&](int slot) {
+    if (blockIdx.x == 0 && tid == 0 && s.prof) { const long long now = clock64(); s.prof[slot] += (unsigned long long)(now - prof_last); prof_last = now; }
+  };
+  // attention work split: S CTAs (same cluster) per batch element
+  const int S = (B * 4 <= (int)gridDim.x) ? 4 : ((B * 2 <= (int)gridDim.x) ? 2 : 1);
+  const int att_b = blockIdx.x / S, att_part = blockIdx.x % S;
+  const bool att_active = att_b < B;
+  const int nkb_att = d.KattP / TG_BK, nkb_dec = d.KdecP / TG_BK;
+  const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
+  const float pscale = 1.0f / (1.0f - d.p_prenet);
+  int frames = 0;
+  bool alive = true, fail = false;
+
+  for (int t = 0; t < io.n_steps && alive; ++t) {
+    const int cur = t & 1, nxt = cur ^ 1;
+    const int tg_ = io.t0 + t;
+
+    // ---- P1: attention LSTMCell (model/decoder.py:70-75) -------------------------------
+    {
+      tg::XSrc xs;
+      if (io.teacher_forcing) xs = tg::XSrc{&maps.tf_pre, tg_ * 2, &maps.x_att_rest, cur * 2, d.P / TG_BK};
+      else xs = tg::XSrc{&maps.x_att, cur * 2, &maps.x_att, cur * 2, nkb_att};
+      if (!tg::gemm(pipe, &maps.w_att, tile * TG_M, nkb_att, xs, (int)rank, nkb_att, D2_CLUSTER, 0)) fail = true;
+      prof_mark(8);
+      tg::accum_to_smem(pipe, 0, sm.part);
+      tc::cluster_sync();
+      HOut ho{s.xatt + (size_t)nxt * 2 * pa, d.KattP, d.P + d.EF, pa, s.xdec + (size_t)cur * 2 * pd, d.KdecP, 0, pd, s.att_h_rm, d.H, 0};
+      lstm_tail(sm.part, rank, unit0, w.batt, d.H, sm.c_att, B, ho, io.att_keep ? io.att_keep + (size_t)tg_ * B * d.H : nullptr,
+                io.hidden_dropout != 0, io.seed, (1ull << 40) + (unsigned long long)tg_ * B * d.H);
+    }
+    if (!(alive = bar.sync(fail))) break;
+    prof_mark(0);
+
+    // ---- P2: query projection (model/attention.py:52) ------------------------------------
+    small_gemm(w.Wq, d.H, d.A, s.att_h_rm, d.H, B, d.H, scratch, [&](int r, int b, float v) { s.q[(size_t)b * d.A + r] = v; });
+    if (!(alive = bar.sync(fail))) break;
+    prof_mark(1);
+
+    // ---- P3: location-sensitive attention -------------------------------------------------
+    attention_phase(d, s, io, sm, scratch, att_active, att_b, att_part, S, cur, tg_);
+    if (!(alive = bar.sync(fail))) break;
+    prof_mark(2);
+
+    // ---- P4: decoder LSTMCell (model/decoder.py:94-101) ----------------------------------
+    {
+      tg::XSrc xs{&maps.x_dec, cur * 2, &maps.x_dec, cur * 2, nkb_dec};
+      if (!tg::gemm(pipe, &maps.w_dec, tile * TG_M, nkb_dec, xs, (int)rank, nkb_dec, D2_CLUSTER, 64)) fail = true;
+      prof_mark(9);
+      tg::accum_to_smem(pipe, 64, sm.part);
+      tc::cluster_sync();
+      HOut ho{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, s.projin, d.KprojP, 0};
+      lstm_tail(sm.part, rank, unit0, w.bdec, d.R, sm.c_dec, B, ho, io.rnn_keep ? io.rnn_keep + (size_t)tg_ * B * d.R : nullptr,
+                io.hidden_dropout != 0, io.seed, (2ull << 40) + (unsigned long long)tg_ * B * d.R);
+    }
+    if (!(alive = bar.sync(fail))) break;
+    prof_mark(3);
+
+    // ---- P5: mel / gate projection + stop bookkeeping ------------------------------------
+    small_gemm(w.Wproj, d.KprojP, d.M + 1, s.projin, d.KprojP, B, d.KprojP, scratch, [&](int r, int b, float v) {
+      v += __ldg(w.bproj + r);
+      if (r < d.M) {
+        io.mels[((size_t)b * io.Tmax + tg_) * d.M + r] = v;
+        s.mel_cur[(size_t)b * d.M + r] = v;
+      } else {
+        io.gates[(size_t)b * io.Tmax + tg_] = v;
+        if (io.stop_enabled) {  // model/tacotron2.py:319-320
+          if (v < 0.0f) s.done[b] = 1;
+          if (v >= 0.0f) s.lengths[b] += 1;
+        }
+      }
+    });
+    frames = t + 1;
+    if (!(alive = bar.sync(fail))) break;
+    prof_mark(4);
+    if (io.teacher_forcing) continue;
+
+    if (io.stop_enabled) {  // model/tacotron2.py:321-322
+      int mine = 1;
+      for (int b = tid; b < B; b += D2_THREADS) mine &= (ld_acquire_u32((const unsigned*)s.done + b) != 0u);
+      if (__syncthreads_and(mine)) break;
+    }
+    if (t + 1 >= io.n_steps) break;  // the last frame's prenet output is never used
+
+    // ---- P6 / P7: prenet on the emitted frame (model/tacotron2.py:324-325) ---------------
+    const unsigned char* k1 = io.prenet_keep ? io.prenet_keep + ((size_t)(tg_ + 1) * 2 + 0) * B * d.P : nullptr;
+    const unsigned char* k2 = io.prenet_keep ? io.prenet_keep + ((size_t)(tg_ + 1) * 2 + 1) * B * d.P : nullptr;
+    small_gemm(w.W1, d.M, d.P, s.mel_cur, d.M, B, d.M, scratch, [&](int r, int b, float v) {
+      const bool keep = k1 ? (k1[(size_t)b * d.P + r] != 0)
+                           : rng_keep(io.seed, ((unsigned long long)(tg_ + 1) * 2 + 0) * B * d.P + (size_t)b * d.P + r, d.p_prenet);
+      s.p1[(size_t)b * d.P + r] = (v > 0.f && keep) ? v * pscale : 0.f;
+    });
+    if (!(alive = bar.sync(fail))) break;
+    prof_mark(5);
+    {
+      __nv_bfloat16* xa = s.xatt + (size_t)nxt * 2 * pa;
+      small_gemm(w.W2, d.P, d.P, s.p1, d.P, B, d.P, scratch, [&](int r, int b, float v) {
+        const bool keep = k2 ? (k2[(size_t)b * d.P + r] != 0)
+                             : rng_keep(io.seed, ((unsigned long long)(tg_ + 1) * 2 + 1) * B * d.P + (size_t)b * d.P + r, d.p_prenet);
+        store_split(xa, pa, d.KattP, b, r, (v > 0.f && keep) ? v * pscale : 0.f);
+      });
+    }
+    if (!(alive = bar.sync(fail))) break;
+    prof_mark(6);
+    if (io.debug_barrier) {  // measures the bare cost of one grid barrier (slot 7)
+      if (!(alive = bar.sync(fail))) break;
+      prof_mark(7);
+    }
+  }
+  if (blockIdx.x == 0 && tid == 0) *s.n_frames = alive ? frames : -1;
+  // write the cell states back (single-step API / resumable decoding)
+  for (int i = tid; i < 8 * D2_BP; i += D2_THREADS) {
+    s.att_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP] = sm.c_att[i];
+    s.rnn_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP] = sm.c_dec[i];
+  }
+  tc::tc_fence_before();
+  tc::cluster_sync();  // no CTA exits while a peer may still read its shared memory
+  if ((tid >> 5) == 1) tc::tmem_dealloc<TG_TMEM_COLS>(pipe.tmem);
+}
+
+size_t att_scratch_floats(const D2Dims& d, int S) {
+  const int Lc = (d.L + S - 1) / S;
+  const int cols = (((d.EF + S - 1) / S) + 3) & ~3;
+  return (size_t)d.A + 2 * (Lc + 32) + (size_t)Lc * 33 + 8 * (size_t)Lc + Lc + 4 + d.L + 4 + 64 + 4 * (size_t)cols;
+}
+
+}  // namespace
+
+size_t d2_smem_bytes(const D2Dims& d) {
+  return 1024 + (size_t)D2_STAGES * TG_STAGE_BYTES + TG_M * TG_PART_LD * 4 + 2 * 8 * D2_BP * 4 + 2 * D2_LOC_K * D2_LOC_F * 4 +
+         (size_t)d.A * D2_LOC_F * 4 + d.A * 4 + (2 * D2_STAGES + 2) * 8 + 64;
+}
+
+static int launch_cfg(const D2Dims& d, cudaLaunchConfig_t* cfg, cudaLaunchAttribute* at, size_t smem, cudaStream_t st) {
+  cfg->gridDim = dim3((unsigned)(d.H / 32) * D2_CLUSTER);
+  cfg->blockDim = dim3(D2_THREADS);
+  cfg->dynamicSmemBytes = smem;
+  cfg->stream = st;
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = D2_CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg->attrs = at;
+  cfg->numAttrs = 1;
+  return T2_OK;
+}
+
+int d2_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, const D2Maps& maps, cudaStream_t st) {
+  T2_REQUIRE(d.B >= 1 && d.B <= D2_BP, T2_ERR_ARG, "decoder: batch %d not in [1,%d] per launch", d.B, D2_BP);
+  T2_REQUIRE(d.H == d.R && d.H % 32 == 0 && d.P % TG_BK == 0 && d.EF % 4 == 0 && d.M % 4 == 0 && d.A % 32 == 0 && d.A <= D2_MAX_A,
+             T2_ERR_UNSUPPORTED, "decoder: unsupported dims H=%d R=%d EF=%d M=%d P=%d A=%d", d.H, d.R, d.EF, d.M, d.P, d.A);
+  const int grid = (d.H / 32) * D2_CLUSTER;
+  T2_REQUIRE(grid == 128, T2_ERR_UNSUPPORTED, "decoder: this revision is laid out for 128 CTAs (att_rnn_dim = 1024), got %d", grid);
+  const int S = (d.B * 4 <= grid) ? 4 : ((d.B * 2 <= grid) ? 2 : 1);
+  const size_t ring = (size_t)D2_STAGES * TG_STAGE_BYTES;
+  T2_REQUIRE(att_scratch_floats(d, S) * 4 <= ring, T2_ERR_UNSUPPORTED, "decoder: L=%d too long for the attention scratch", d.L);
+  T2_REQUIRE(((size_t)(((d.M + 1 + 15) / 16) + 8) * (d.KprojP + 4) + 128) * 4 <= ring, T2_ERR_UNSUPPORTED, "decoder: projection staging");
+  const size_t smem = d2_smem_bytes(d);
+  T2_REQUIRE(smem <= 227 * 1024, T2_ERR_UNSUPPORTED, "decoder: %zu B shared memory", smem);
+  T2_CHECK_CUDA(cudaFuncSetAttribute(decoder2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaLaunchConfig_t cfg{};
+  cudaLaunchAttribute at[1];
+  launch_cfg(d, &cfg, at, smem, st);
+  int nclusters = 0;
+  T2_CHECK_CUDA(cudaOccupancyMaxActiveClusters(&nclusters, decoder2_kernel, &cfg));
+  T2_REQUIRE(nclusters * D2_CLUSTER >= grid, T2_ERR_UNSUPPORTED,
+             "decoder: only %d clusters of %d can be co-resident, %d needed (persistent kernel needs the whole grid resident)",
+             nclusters, D2_CLUSTER, grid / D2_CLUSTER);
+  T2_CHECK_CUDA(cudaMemsetAsync(s.barrier, 0, 2 * sizeof(unsigned), st));
+  T2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, decoder2_kernel, maps, d, w, s, io));
+  return T2_OK;
+}

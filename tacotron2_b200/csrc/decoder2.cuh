@@ -1,0 +1,83 @@
+// Persistent autoregressive decoder, tensor-core revision: parameter blocks shared by host and device.
+// Replaces the Python frame loop of the reference (model/tacotron2.py:276-325), the per-frame
+// Decoder.forward (model/decoder.py:53-119), Attention.forward (model/attention.py:34-69) and the
+// prenet (model/tacotron2.py:85-92).
+#pragma once
+#include "tcgemm.cuh"
+
+#define D2_BP 64           // batch slots per launch (UMMA N)
+#define D2_THREADS 256
+#define D2_CLUSTER 4       // CTAs per cluster = split-K factor of the gate GEMMs
+#define D2_STAGES 3
+#define D2_LOC_F 32        // attention_location_n_filters  (model/decoder.py:35, hard-coded)
+#define D2_LOC_K 31        // attention_location_kernel_size (model/decoder.py:36, hard-coded)
+#define D2_MAX_A 128
+
+struct D2Dims {
+  int B, L, EF, H, R, P, A, M, C;
+  int KattP;   // P+EF+H padded to 64: columns [prenet | ctx | att_h | 0]
+  int KdecP;   // H+EF+C+R padded to 64: columns [att_h | ctx | controls | rnn_h | 0]
+  int KprojP;  // R+EF+C padded to 4:   columns [rnn_h | ctx | controls | 0]
+  int npass;   // 3 = fp32-parity (bf16 hi/lo split), 1 = bf16
+  float p_prenet;
+};
+
+struct D2Weights {
+  const float* batt;       // [4H] b_ih + b_hh, reference row order (i,f,g,o blocks)
+  const float* bdec;       // [4R]
+  const float* Wq;         // [A][H]
+  const float* v;          // [A]
+  const float* loc_conv_t; // [2][31][32]  location_conv.weight transposed to (channel, tap, filter)
+  const float* loc_dense;  // [A][32]
+  const float* Wproj;      // [M+1][KprojP]
+  const float* bproj;      // [M+1]
+  const float* W1;         // [P][M]
+  const float* W2;         // [P][P]
+};
+
+struct D2State {
+  __nv_bfloat16* xatt;   // [2 parity][2 hi/lo][BP][KattP]
+  __nv_bfloat16* xdec;   // [2][2][BP][KdecP]
+  float* att_c;          // [H][BP]  (loaded at kernel start, stored at kernel end)
+  float* rnn_c;          // [R][BP]
+  float* att_h_rm;       // [BP][H]
+  float* projin;         // [BP][KprojP]
+  float* q;              // [BP][A]
+  float* w_prev;         // [2][BP][L]
+  float* w_cum;          // [2][BP][L]
+  float* mel_cur;        // [BP][M]
+  float* p1;             // [BP][P]
+  int* done;             // [BP]
+  long long* lengths;    // [BP]
+  int* n_frames;         // [1]
+  unsigned* barrier;     // [2]
+  unsigned long long* prof;  // [16] or null
+};
+
+struct D2IO {
+  const float* memory;        // [B][L][EF]
+  const float* pmem;          // [B][L][A]
+  const unsigned char* mask;  // [B][L]
+  const unsigned char* prenet_keep;  // [T+1][2][B][P] or null
+  const unsigned char* att_keep;     // [T][B][H] or null
+  const unsigned char* rnn_keep;     // [T][B][R] or null
+  float* mels;   // [B][Tmax][M]
+  float* gates;  // [B][Tmax]
+  float* aligns; // [B][Tmax][L]
+  int Tmax, n_steps, t0;
+  int teacher_forcing, hidden_dropout, stop_enabled;
+  int debug_barrier;  // adds one empty grid barrier per frame and times it (profiling only)
+  unsigned long long seed;
+};
+
+struct D2Maps {  // TMA descriptors (bf16, 128-B swizzle, box 64 x rows x {1|2})
+  CUtensorMap w_att, w_dec;   // [K][4H permuted rows][2]
+  CUtensorMap x_att;          // [KattP][BP][4 = parity*2 + hl]
+  CUtensorMap x_att_rest;     // same buffer starting at column P (teacher forcing: prenet part comes from tf_pre)
+  CUtensorMap x_dec;          // [KdecP][BP][4]
+  CUtensorMap tf_pre;         // [P][BP][(T+1)*2]
+};
+
+int d2_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, const D2Maps& maps, cudaStream_t stream);
+int d2_max_clusters(int* out);
+size_t d2_smem_bytes(const D2Dims& d);

@@ -35,7 +35,7 @@ tg_debug_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant_
   tg::pipe_init(p, bars, stages, nstages, npass, tmem_slot);
   tc::cluster_sync();
   tg::XSrc xs{&xmap, 0, &xmap, 0, nkb};
-  const bool ok = tg::gemm(p, &wmap, tile * TG_M, xs, (int)rank, nkb, 4, 0);
+  const bool ok = tg::gemm(p, &wmap, tile * TG_M, 0, xs, (int)rank, nkb, 4, 0);
   if (!ok && threadIdx.x == 0) atomicExch(err, 1u);
   tg::accum_to_smem(p, 0, part);
   tc::cluster_sync();

@@ -55,7 +55,9 @@ __device__ __forceinline__ void pipe_init(Pipe& p, uint64_t* bars, uint8_t* stag
 
 // Runs the K-blocks kb = kb_begin, kb_begin+kb_stride, ... < kb_end of one 128-row tile into TMEM columns
 // [d_col, d_col+64).  All threads of the CTA must call it; returns false on a pipeline timeout.
-__device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row0, const XSrc& xs, int kb_begin, int kb_end,
+// w_nkb > 0: W is stored tile-major ([tile][kb][128][64], every TMA box one contiguous 16 KB chunk) with w_nkb K-blocks per
+// tile; w_nkb == 0: W is a plain row-major [rows][K] matrix.
+__device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row0, int w_nkb, const XSrc& xs, int kb_begin, int kb_end,
                                      int kb_stride, uint32_t d_col) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   bool ok = true;
@@ -69,13 +71,9 @@ __device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row
       const bool first = kb < xs.split;
       const CUtensorMap* xm = first ? xs.map0 : xs.map1;
       const int xk = (first ? kb : kb - xs.split) * TG_BK, xz = first ? xs.z0 : xs.z1;
-      if (p.npass == 3) {
-        tc::tma_load_3d(st, wmap, p.full + p.p_stage, kb * TG_BK, w_row0, 0);                 // [hi|lo] 32 KB
-        tc::tma_load_3d(st + 2 * TG_W_TILE, xm, p.full + p.p_stage, xk, 0, xz);                // [hi|lo] 16 KB
-      } else {
-        tc::tma_load_3d(st, wmap, p.full + p.p_stage, kb * TG_BK, w_row0, 0);                 // hi only (box z = 1)
-        tc::tma_load_3d(st + 2 * TG_W_TILE, xm, p.full + p.p_stage, xk, 0, xz);
-      }
+      const int wc0 = w_nkb ? 0 : kb * TG_BK, wc1 = w_nkb ? ((w_row0 / TG_M) * w_nkb + kb) * TG_M : w_row0;
+      tc::tma_load_3d(st, wmap, p.full + p.p_stage, wc0, wc1, 0);                 // [hi|lo] 32 KB (hi only when box z = 1)
+      tc::tma_load_3d(st + 2 * TG_W_TILE, xm, p.full + p.p_stage, xk, 0, xz);      // [hi|lo] 16 KB
       if (++p.p_stage == p.nstages) { p.p_stage = 0; p.p_phase ^= 1; }
     }
   } else if (warp == 1 && lane == 0) {

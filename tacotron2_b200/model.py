@@ -17,6 +17,7 @@ when absent the kernels draw their own (counter-based RNG seeded from torch's ge
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional
 
 import torch
@@ -179,7 +180,8 @@ class Tacotron2(nn.Module):
         self._cfg = _lib.T2ModelConfig(
             num_chars, encoded_dim, encoder_kernel_size, num_mels, prenet_dim, att_rnn_dim, att_dim, rnn_hidden_dim, postnet_dim,
             float(dropout), num_speakers if speaker_tokens else 0, self.controls_dim,
-            description_embeddings_dim if description_embeddings else 0)
+            description_embeddings_dim if description_embeddings else 0,
+            1 if os.environ.get("T2B200_PRECISION", "fp32").lower() == "bf16" else 0)
         self._ctx = None
         self._sig = None
         self._ws = None

@@ -34,7 +34,7 @@ def test_no_cpu_fallback(lib):
     if torch.cuda.is_available():
         pytest.skip("GPU present")
     import ctypes as C
-    cfg = _lib.T2ModelConfig(39, 512, 5, 80, 256, 1024, 128, 1024, 512, 0.5, 0, 0, 0)
+    cfg = _lib.T2ModelConfig(39, 512, 5, 80, 256, 1024, 128, 1024, 512, 0.5, 0, 0, 0, 0)
     h = C.c_void_p()
     rc = lib.t2_ctx_create(C.byref(cfg), C.byref(h))
     assert rc != 0 and b"no CPU fallback" in lib.t2_last_error()
