@@ -18,9 +18,11 @@ struct GridBar {
   unsigned nblocks;
   unsigned epoch;
   // `fail` = this CTA hit a pipeline timeout: it raises the abort flag before arriving so every CTA leaves together.
-  __device__ bool sync(bool fail) {
-    // generic-proxy global writes of this phase must be ordered before the TMA (async proxy) reads of the next one
-    asm volatile("fence.proxy.async;" ::: "memory");
+  // `wrote_x`: this phase stored GEMM operands with ordinary (generic-proxy) stores; they must be ordered before the
+  // TMA (async-proxy) reads of a later phase, hence the proxy fence on the writer side (the TMA producer thread
+  // issues the matching fence before its first load).
+  __device__ bool sync(bool fail, bool wrote_x) {
+    if (wrote_x) asm volatile("fence.proxy.async;" ::: "memory");
     __syncthreads();
     __shared__ int ok_s;
     if (threadIdx.x == 0) {
@@ -39,7 +41,6 @@ struct GridBar {
       __threadfence();
     }
     __syncthreads();
-    asm volatile("fence.proxy.async;" ::: "memory");
     return ok_s != 0;
   }
 };
@@ -47,27 +48,28 @@ struct GridBar {
 // ------------------------------------------------------------------------------------------
 // Small dense phases on CUDA cores: out[b][r] = sum_k W[r][k] x[b][k].  The 128 CTAs form a 16 x 8 grid of
 // (row group, batch group of 8); W rows and x rows are staged in shared memory (row stride K+4 floats:
-// conflict-free float4 reads), 128 outputs per CTA, two K-halves per output.
-template <typename Epi>
-__device__ __forceinline__ void small_gemm(const float* __restrict__ W, int ldw, int rows, const float* x, int ldx, int B, int K,
-                                           float* scratch, Epi epi) {
+// conflict-free float4 reads), 128 outputs per CTA, two K-halves per output.  Returns this thread's output (if any);
+// the caller applies the phase-specific epilogue and must __syncthreads() before reusing the scratch.
+struct SmallOut { int r, b; float v; bool valid; };
+__device__ __forceinline__ SmallOut small_gemm(const float* __restrict__ W, int ldw, int rows, const float* x, int ldx, int B, int K,
+                                               float* scratch) {
+  SmallOut out{0, 0, 0.f, false};
   const int tid = threadIdx.x;
   const int rg = blockIdx.x >> 3, bg = blockIdx.x & 7;
   const int rpc = (rows + 15) >> 4;           // rows per CTA (<= 16)
   const int r0 = rg * rpc, b0 = bg * 8;
   const int nr = max(0, min(rpc, rows - r0)), nb = max(0, min(8, B - b0));
-  if (blockIdx.x >= 128 || nr == 0 || nb == 0) return;
+  if (blockIdx.x >= 128 || nr == 0 || nb == 0) return out;
   const int ld = K + 4, K4 = K >> 2;
   float* Ws = scratch;                        // [rpc][ld]
   float* xs = scratch + rpc * ld;             // [8][ld]
   float* red = xs + 8 * ld;                   // [128]
-  for (int i = tid; i < nr * K4; i += D2_THREADS) {
-    const int r = i / K4, c = i % K4;
-    cp_async16(Ws + r * ld + c * 4, W + (size_t)(r0 + r) * ldw + c * 4);
-  }
-  for (int i = tid; i < nb * K4; i += D2_THREADS) {
-    const int b = i / K4, c = i % K4;
-    cp_async16(xs + b * ld + c * 4, x + (size_t)(b0 + b) * ldx + c * 4);
+#pragma unroll 1
+  for (int i = tid; i < (nr + nb) * K4; i += D2_THREADS) {
+    const int rr = i / K4, c = i - rr * K4;
+    const float* src = rr < nr ? W + (size_t)(r0 + rr) * ldw : x + (size_t)(b0 + rr - nr) * ldx;
+    float* dst = rr < nr ? Ws + rr * ld : xs + (rr - nr) * ld;
+    cp_async16(dst + c * 4, src + c * 4);
   }
   cp_async_commit();
   cp_async_wait<0>();
@@ -89,8 +91,8 @@ __device__ __forceinline__ void small_gemm(const float* __restrict__ W, int ldw,
   }
   if (kh == 1) red[o] = acc;
   __syncthreads();
-  if (kh == 0 && r < nr && b < nb) epi(r0 + r, b0 + b, acc + red[o]);
-  __syncthreads();
+  if (kh == 0 && r < nr && b < nb) { out.r = r0 + r; out.b = b0 + b; out.v = acc + red[o]; out.valid = true; }
+  return out;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -163,8 +165,8 @@ __device__ __forceinline__ void lstm_tail(const float* part, uint32_t rank, int 
     if (b >= B) continue;
     const float pi = j ? pre[0].y : pre[0].x, pf = j ? pre[1].y : pre[1].x;
     const float pg = j ? pre[2].y : pre[2].x, po = j ? pre[3].y : pre[3].x;
-    const float c = sigmoidf_(pf) * cst[ul * D2_BP + b] + sigmoidf_(pi) * tanhf(pg);
-    float h = sigmoidf_(po) * tanhf(c);
+    const float c = sigmoid_fast(pf) * cst[ul * D2_BP + b] + sigmoid_fast(pi) * tanh_fast(pg);
+    float h = sigmoid_fast(po) * tanh_fast(c);
     cst[ul * D2_BP + b] = c;
     if (hidden_dropout) {  // nn.Dropout(0.1), train only (model/decoder.py:75,101)
       const bool k = keep ? (keep[(size_t)b * H + u] != 0) : rng_keep(seed, rng_base + (unsigned long long)b * H + u, 0.1f);
@@ -212,7 +214,9 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
   if (active) {
     const float* wprev = s.w_prev + ((size_t)cur * D2_BP + b) * L;
     const float* wcum = s.w_cum + ((size_t)cur * D2_BP + b) * L;
+#pragma unroll 1
     for (int i = tid; i < A; i += D2_THREADS) q_s[i] = ld_cg(s.q + (size_t)b * A + i);
+#pragma unroll 1
     for (int i = tid; i < nl + 30; i += D2_THREADS) {
       const int l = l0 + i - 15;
       const bool in = (l >= 0 && l < L);
@@ -221,6 +225,7 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
     }
     __syncthreads();
     // location conv: item = (position, group of 4 filters)  (model/attention.py:54)
+#pragma unroll 1
     for (int it = tid; it < nl * 8; it += D2_THREADS) {
       const int fg = it / nl, li = it % nl;
       float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -239,22 +244,22 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
     // location dense + tanh energies: warp = group of A/8 attention dims, lane = position (model/attention.py:55-62)
     const int ag = A >> 3, a0 = warp * ag;
     const unsigned char* mk = io.mask + (size_t)b * L;
+#pragma unroll 1
     for (int lb = 0; lb < nl; lb += 32) {
       const int li = lb + lane;
       float e = 0.f;
       if (li < nl && mk[l0 + li] == 0) {
         const float* pm = io.pmem + ((size_t)b * L + l0 + li) * A + a0;
-        float4 p4[D2_MAX_A / 32];  // this warp's A/8 processed-memory values for position li, fetched up front
-#pragma unroll
-        for (int a = 0; a < D2_MAX_A / 32; ++a)
-          if (a * 4 < ag) p4[a] = __ldg(reinterpret_cast<const float4*>(pm) + a);
+        const int na4 = ag >> 2;
+        float4 pnext = __ldg(reinterpret_cast<const float4*>(pm));  // software-pipelined: fetch a4+1 while computing a4
         float f[D2_LOC_F];
 #pragma unroll
         for (int i = 0; i < D2_LOC_F; ++i) f[i] = fs[li * 33 + i];
-#pragma unroll
-        for (int a4 = 0; a4 < D2_MAX_A / 32; ++a4) {
-          if (a4 * 4 >= ag) break;
-          const float pv[4] = {p4[a4].x, p4[a4].y, p4[a4].z, p4[a4].w};
+#pragma unroll 1
+        for (int a4 = 0; a4 < na4; ++a4) {
+          const float4 pc = pnext;
+          if (a4 + 1 < na4) pnext = __ldg(reinterpret_cast<const float4*>(pm) + a4 + 1);
+          const float pv[4] = {pc.x, pc.y, pc.z, pc.w};
 #pragma unroll
           for (int aa = 0; aa < 4; ++aa) {
             const int a = a0 + a4 * 4 + aa;
@@ -268,13 +273,14 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
               l0a = fmaf(w5.x, f[4 * i + 4], l0a); l1a = fmaf(w5.y, f[4 * i + 5], l1a);
               l2a = fmaf(w5.z, f[4 * i + 6], l2a); l3a = fmaf(w5.w, f[4 * i + 7], l3a);
             }
-            e = fmaf(sm.v[a], tanhf(q_s[a] + ((l0a + l1a) + (l2a + l3a)) + pv[aa]), e);
+            e = fmaf(sm.v[a], tanh_fast(q_s[a] + ((l0a + l1a) + (l2a + l3a)) + pv[aa]), e);
           }
         }
       }
       if (li < nl) epart[warp * Lc + li] = e;
     }
     __syncthreads();
+#pragma unroll 1
     for (int li = tid; li < nl; li += D2_THREADS) {
       float e = -INFINITY;
       if (mk[l0 + li] == 0) {
@@ -291,6 +297,7 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
     const uint32_t my_rank = tc::cluster_ctarank();
     const uint32_t base_rank = my_rank - (uint32_t)part;
     const uint32_t ea = tc::smem_u32(e_slice);
+#pragma unroll 1
     for (int l = tid; l < L; l += D2_THREADS) {
       const int pr = l / Lc, li = l - pr * Lc;
       float v;
@@ -299,9 +306,11 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
     }
     __syncthreads();
     float mx = -INFINITY;
+#pragma unroll 1
     for (int l = tid; l < L; l += D2_THREADS) mx = fmaxf(mx, e_full[l]);
     mx = block_reduce(mx, red, true);
     float sum = 0.f;
+#pragma unroll 1
     for (int l = tid; l < L; l += D2_THREADS) {
       const float p = expf(e_full[l] - mx);
       e_full[l] = p;
@@ -309,6 +318,7 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
     }
     sum = block_reduce(sum, red + 32, false);
     const float inv = 1.0f / sum;
+#pragma unroll 1
     for (int l = tid; l < L; l += D2_THREADS) {
       const float w = e_full[l] * inv;
       e_full[l] = w;
@@ -327,8 +337,10 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
     const int lg = tid >> 6, cq0 = tid & 63;
     const unsigned char* mk2 = io.mask + (size_t)b * L;
     int Leff = 0;  // positions beyond the last unmasked one carry weight exactly 0 (softmax of -inf): skip them
+#pragma unroll 1
     for (int l = tid; l < L; l += D2_THREADS) if (mk2[l] == 0) Leff = max(Leff, l + 1);
     Leff = (int)block_reduce((float)Leff, red, true);
+#pragma unroll 1
     for (int cq = cq0; cq < nq; cq += 64) {
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
       const float4* mp = reinterpret_cast<const float4*>(mem + c0) + cq;
@@ -357,6 +369,7 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
     const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
     __nv_bfloat16* xa = s.xatt + (size_t)nxt * 2 * pa;   // next frame's attention-LSTM input
     __nv_bfloat16* xd = s.xdec + (size_t)cur * 2 * pd;   // this frame's decoder-LSTM input
+#pragma unroll 1
     for (int c = tid; c < c1 - c0; c += D2_THREADS) {
       const float v = cred[c] + cred[cols_per + c] + cred[2 * cols_per + c] + cred[3 * cols_per + c];
       const int col = c0 + c;
@@ -369,12 +382,15 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
 }
 
 // ------------------------------------------------------------------------------------------
+enum { PH_ATT_LSTM = 0, PH_QUERY, PH_ATTN, PH_DEC_LSTM, PH_PROJ, PH_PRE1, PH_PRE2, PH_COUNT };
+
 __global__ void __launch_bounds__(D2_THREADS, 1)
 decoder2_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weights w, D2State s, D2IO io) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* base = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // keep the pointer's shared-memory provenance (no integer round trip) so loads/stores compile to LDS/STS
+  uint8_t* base = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
   const Smem sm = carve(base, d);
-  float* scratch = reinterpret_cast<float*>(sm.stages);
+  float* scratch = reinterpret_cast<float*>(base);
   const int tid = threadIdx.x;
   const uint32_t rank = tc::cluster_ctarank();
   const int tile = blockIdx.x / D2_CLUSTER;       // 128-row gate tile = 32 hidden units
@@ -385,9 +401,13 @@ decoder2_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weights w, D2St
     tc::prefetch_tmap(&maps.w_att); tc::prefetch_tmap(&maps.w_dec); tc::prefetch_tmap(&maps.x_att);
     tc::prefetch_tmap(&maps.x_att_rest); tc::prefetch_tmap(&maps.x_dec); tc::prefetch_tmap(&maps.tf_pre);
   }
+#pragma unroll 1
   for (int i = tid; i < 2 * D2_LOC_K * D2_LOC_F; i += D2_THREADS) sm.conv_t[i] = w.loc_conv_t[i];
+#pragma unroll 1
   for (int i = tid; i < d.A * D2_LOC_F; i += D2_THREADS) sm.dense[i] = w.loc_dense[i];
+#pragma unroll 1
   for (int i = tid; i < d.A; i += D2_THREADS) sm.v[i] = w.v[i];
+#pragma unroll 1
   for (int i = tid; i < 8 * D2_BP; i += D2_THREADS) {
     sm.c_att[i] = s.att_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP];
     sm.c_dec[i] = s.rnn_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP];
@@ -408,106 +428,99 @@ decoder2_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weights w, D2St
   const int nkb_att = d.KattP / TG_BK, nkb_dec = d.KdecP / TG_BK;
   const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
   const float pscale = 1.0f / (1.0f - d.p_prenet);
+  const int nphase = io.teacher_forcing ? PH_PROJ + 1 : PH_COUNT;
   int frames = 0;
-  bool alive = true, fail = false;
+  bool alive = true, fail = false, stop = false;
 
-  for (int t = 0; t < io.n_steps && alive; ++t) {
+#pragma unroll 1
+  for (int t = 0; t < io.n_steps && alive && !stop; ++t) {
     const int cur = t & 1, nxt = cur ^ 1;
     const int tg_ = io.t0 + t;
-
-    // ---- P1: attention LSTMCell (model/decoder.py:70-75) -------------------------------
-    {
-      tg::XSrc xs;
-      if (io.teacher_forcing) xs = tg::XSrc{&maps.tf_pre, tg_ * 2, &maps.x_att_rest, cur * 2, d.P / TG_BK};
-      else xs = tg::XSrc{&maps.x_att, cur * 2, &maps.x_att, cur * 2, nkb_att};
-      if (!tg::gemm(pipe, &maps.w_att, tile * TG_M, nkb_att, xs, (int)rank, nkb_att, D2_CLUSTER, 0)) fail = true;
-      prof_mark(8);
-      tg::accum_to_smem(pipe, 0, sm.part);
-      tc::cluster_sync();
-      HOut ho{s.xatt + (size_t)nxt * 2 * pa, d.KattP, d.P + d.EF, pa, s.xdec + (size_t)cur * 2 * pd, d.KdecP, 0, pd, s.att_h_rm, d.H, 0};
-      lstm_tail(sm.part, rank, unit0, w.batt, d.H, sm.c_att, B, ho, io.att_keep ? io.att_keep + (size_t)tg_ * B * d.H : nullptr,
-                io.hidden_dropout != 0, io.seed, (1ull << 40) + (unsigned long long)tg_ * B * d.H);
-    }
-    if (!(alive = bar.sync(fail))) break;
-    prof_mark(0);
-
-    // ---- P2: query projection (model/attention.py:52) ------------------------------------
-    small_gemm(w.Wq, d.H, d.A, s.att_h_rm, d.H, B, d.H, scratch, [&](int r, int b, float v) { s.q[(size_t)b * d.A + r] = v; });
-    if (!(alive = bar.sync(fail))) break;
-    prof_mark(1);
-
-    // ---- P3: location-sensitive attention -------------------------------------------------
-    attention_phase(d, s, io, sm, scratch, att_active, att_b, att_part, S, cur, tg_);
-    if (!(alive = bar.sync(fail))) break;
-    prof_mark(2);
-
-    // ---- P4: decoder LSTMCell (model/decoder.py:94-101) ----------------------------------
-    {
-      tg::XSrc xs{&maps.x_dec, cur * 2, &maps.x_dec, cur * 2, nkb_dec};
-      if (!tg::gemm(pipe, &maps.w_dec, tile * TG_M, nkb_dec, xs, (int)rank, nkb_dec, D2_CLUSTER, 64)) fail = true;
-      prof_mark(9);
-      tg::accum_to_smem(pipe, 64, sm.part);
-      tc::cluster_sync();
-      HOut ho{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, s.projin, d.KprojP, 0};
-      lstm_tail(sm.part, rank, unit0, w.bdec, d.R, sm.c_dec, B, ho, io.rnn_keep ? io.rnn_keep + (size_t)tg_ * B * d.R : nullptr,
-                io.hidden_dropout != 0, io.seed, (2ull << 40) + (unsigned long long)tg_ * B * d.R);
-    }
-    if (!(alive = bar.sync(fail))) break;
-    prof_mark(3);
-
-    // ---- P5: mel / gate projection + stop bookkeeping ------------------------------------
-    small_gemm(w.Wproj, d.KprojP, d.M + 1, s.projin, d.KprojP, B, d.KprojP, scratch, [&](int r, int b, float v) {
-      v += __ldg(w.bproj + r);
-      if (r < d.M) {
-        io.mels[((size_t)b * io.Tmax + tg_) * d.M + r] = v;
-        s.mel_cur[(size_t)b * d.M + r] = v;
+#pragma unroll 1
+    for (int ph = 0; ph < nphase && alive && !stop; ++ph) {
+      bool wrote_x = false;  // this phase stored operands that a later phase reads through TMA
+      if (ph == PH_ATT_LSTM || ph == PH_DEC_LSTM) {
+        // ---- attention / decoder LSTMCell (model/decoder.py:70-75, 94-101): gate GEMM + split-K reduce + pointwise
+        const bool att = ph == PH_ATT_LSTM;
+        tg::XSrc xs;
+        if (att && io.teacher_forcing) xs = tg::XSrc{&maps.tf_pre, tg_ * 2, &maps.x_att_rest, cur * 2, d.P / TG_BK};
+        else if (att) xs = tg::XSrc{&maps.x_att, cur * 2, &maps.x_att, cur * 2, nkb_att};
+        else xs = tg::XSrc{&maps.x_dec, cur * 2, &maps.x_dec, cur * 2, nkb_dec};
+        const int nkb = att ? nkb_att : nkb_dec;
+        const uint32_t dcol = att ? 0u : 64u;
+        if (!tg::gemm(pipe, att ? &maps.w_att : &maps.w_dec, tile * TG_M, nkb, xs, (int)rank, nkb, D2_CLUSTER, dcol)) fail = true;
+        prof_mark(att ? 8 : 9);
+        tg::accum_to_smem(pipe, dcol, sm.part);
+        tc::cluster_sync();
+        HOut ho;
+        if (att) ho = HOut{s.xatt + (size_t)nxt * 2 * pa, d.KattP, d.P + d.EF, pa, s.xdec + (size_t)cur * 2 * pd, d.KdecP, 0, pd, s.att_h_rm, d.H, 0};
+        else ho = HOut{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, s.projin, d.KprojP, 0};
+        const unsigned char* keep = att ? io.att_keep : io.rnn_keep;
+        lstm_tail(sm.part, rank, unit0, att ? w.batt : w.bdec, d.H, att ? sm.c_att : sm.c_dec, B, ho,
+                  keep ? keep + (size_t)tg_ * B * d.H : nullptr, io.hidden_dropout != 0, io.seed,
+                  ((att ? 1ull : 2ull) << 40) + (unsigned long long)tg_ * B * d.H);
+        wrote_x = true;
+      } else if (ph == PH_ATTN) {
+        // ---- location-sensitive attention (model/attention.py:54-67, model/decoder.py:90)
+        attention_phase(d, s, io, sm, scratch, att_active, att_b, att_part, S, cur, tg_);
+        wrote_x = true;
       } else {
-        io.gates[(size_t)b * io.Tmax + tg_] = v;
-        if (io.stop_enabled) {  // model/tacotron2.py:319-320
-          if (v < 0.0f) s.done[b] = 1;
-          if (v >= 0.0f) s.lengths[b] += 1;
+        // ---- small dense phases: query (model/attention.py:52), mel/gate projection (model/decoder.py:103-109),
+        //      prenet layers on the emitted frame (model/tacotron2.py:85-92,324-325)
+        const float* Wm; const float* xin; int ldw, rows, ldx, K;
+        if (ph == PH_QUERY)     { Wm = w.Wq;    ldw = d.H;      rows = d.A;     xin = s.att_h_rm; ldx = d.H;      K = d.H; }
+        else if (ph == PH_PROJ) { Wm = w.Wproj; ldw = d.KprojP; rows = d.M + 1; xin = s.projin;   ldx = d.KprojP; K = d.KprojP; }
+        else if (ph == PH_PRE1) { Wm = w.W1;    ldw = d.M;      rows = d.P;     xin = s.mel_cur;  ldx = d.M;      K = d.M; }
+        else                    { Wm = w.W2;    ldw = d.P;      rows = d.P;     xin = s.p1;       ldx = d.P;      K = d.P; }
+        const SmallOut o = small_gemm(Wm, ldw, rows, xin, ldx, B, K, scratch);
+        if (o.valid) {
+          const int r = o.r, b = o.b;
+          float v = o.v;
+          if (ph == PH_QUERY) {
+            s.q[(size_t)b * d.A + r] = v;
+          } else if (ph == PH_PROJ) {
+            v += __ldg(w.bproj + r);
+            if (r < d.M) {
+              io.mels[((size_t)b * io.Tmax + tg_) * d.M + r] = v;
+              s.mel_cur[(size_t)b * d.M + r] = v;
+            } else {
+              io.gates[(size_t)b * io.Tmax + tg_] = v;
+              if (io.stop_enabled) {  // model/tacotron2.py:319-320
+                if (v < 0.0f) s.done[b] = 1;
+                if (v >= 0.0f) s.lengths[b] += 1;
+              }
+            }
+          } else {
+            const int layer = ph == PH_PRE1 ? 0 : 1;
+            const size_t kidx = (((size_t)(tg_ + 1) * 2 + layer) * B + b) * d.P + r;
+            const bool keep = io.prenet_keep ? (io.prenet_keep[kidx] != 0) : rng_keep(io.seed, kidx, d.p_prenet);
+            v = (v > 0.f && keep) ? v * pscale : 0.f;
+            if (layer == 0) s.p1[(size_t)b * d.P + r] = v;
+            else { store_split(s.xatt + (size_t)nxt * 2 * pa, pa, d.KattP, b, r, v); wrote_x = true; }
+          }
         }
+        if (ph == PH_PROJ) frames = t + 1;
       }
-    });
-    frames = t + 1;
-    if (!(alive = bar.sync(fail))) break;
-    prof_mark(4);
-    if (io.teacher_forcing) continue;
-
-    if (io.stop_enabled) {  // model/tacotron2.py:321-322
-      int mine = 1;
-      for (int b = tid; b < B; b += D2_THREADS) mine &= (ld_acquire_u32((const unsigned*)s.done + b) != 0u);
-      if (__syncthreads_and(mine)) break;
-    }
-    if (t + 1 >= io.n_steps) break;  // the last frame's prenet output is never used
-
-    // ---- P6 / P7: prenet on the emitted frame (model/tacotron2.py:324-325) ---------------
-    const unsigned char* k1 = io.prenet_keep ? io.prenet_keep + ((size_t)(tg_ + 1) * 2 + 0) * B * d.P : nullptr;
-    const unsigned char* k2 = io.prenet_keep ? io.prenet_keep + ((size_t)(tg_ + 1) * 2 + 1) * B * d.P : nullptr;
-    small_gemm(w.W1, d.M, d.P, s.mel_cur, d.M, B, d.M, scratch, [&](int r, int b, float v) {
-      const bool keep = k1 ? (k1[(size_t)b * d.P + r] != 0)
-                           : rng_keep(io.seed, ((unsigned long long)(tg_ + 1) * 2 + 0) * B * d.P + (size_t)b * d.P + r, d.p_prenet);
-      s.p1[(size_t)b * d.P + r] = (v > 0.f && keep) ? v * pscale : 0.f;
-    });
-    if (!(alive = bar.sync(fail))) break;
-    prof_mark(5);
-    {
-      __nv_bfloat16* xa = s.xatt + (size_t)nxt * 2 * pa;
-      small_gemm(w.W2, d.P, d.P, s.p1, d.P, B, d.P, scratch, [&](int r, int b, float v) {
-        const bool keep = k2 ? (k2[(size_t)b * d.P + r] != 0)
-                             : rng_keep(io.seed, ((unsigned long long)(tg_ + 1) * 2 + 1) * B * d.P + (size_t)b * d.P + r, d.p_prenet);
-        store_split(xa, pa, d.KattP, b, r, (v > 0.f && keep) ? v * pscale : 0.f);
-      });
-    }
-    if (!(alive = bar.sync(fail))) break;
-    prof_mark(6);
-    if (io.debug_barrier) {  // measures the bare cost of one grid barrier (slot 7)
-      if (!(alive = bar.sync(fail))) break;
-      prof_mark(7);
+      if (!(alive = bar.sync(fail, wrote_x))) break;
+      prof_mark(ph);
+      if (ph == PH_PROJ && !io.teacher_forcing) {
+        if (io.stop_enabled) {  // model/tacotron2.py:321-322: leave once every utterance has fired its stop gate
+          int mine = 1;
+#pragma unroll 1
+          for (int b = tid; b < B; b += D2_THREADS) mine &= (ld_acquire_u32((const unsigned*)s.done + b) != 0u);
+          if (__syncthreads_and(mine)) stop = true;
+        }
+        if (t + 1 >= io.n_steps) stop = true;  // the last frame's prenet output is never used
+      }
+      if (ph == PH_PRE2 && io.debug_barrier) {  // measures the bare cost of one grid barrier (slot 7)
+        if (!(alive = bar.sync(fail, false))) break;
+        prof_mark(7);
+      }
     }
   }
   if (blockIdx.x == 0 && tid == 0) *s.n_frames = alive ? frames : -1;
   // write the cell states back (single-step API / resumable decoding)
+#pragma unroll 1
   for (int i = tid; i < 8 * D2_BP; i += D2_THREADS) {
     s.att_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP] = sm.c_att[i];
     s.rnn_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP] = sm.c_dec[i];

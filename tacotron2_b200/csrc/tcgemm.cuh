@@ -64,6 +64,7 @@ __device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row
   const uint32_t stage_tx = (uint32_t)(p.npass == 3 ? TG_STAGE_BYTES : TG_W_TILE + TG_X_TILE);
   if (warp == 0 && lane == 0) {
     // ---------------- TMA producer
+    asm volatile("fence.proxy.async;" ::: "memory");  // operands written by generic stores in an earlier phase
     for (int kb = kb_begin; kb < kb_end; kb += kb_stride) {
       if (!tc::mbar_wait(p.empty + p.p_stage, p.p_phase ^ 1)) { ok = false; break; }
       uint8_t* st = p.stages + (size_t)p.p_stage * TG_STAGE_BYTES;
