@@ -41,6 +41,7 @@ struct t2_ctx {
   // tensor-core decoder (decoder2)
   __nv_bfloat16 *Watt_b, *Wdec_b;          // [2 hi/lo][4H permuted][KattP] / [2][4R][KdecP]
   float* loc_conv_t;                       // [2][31][32]
+  float* loc_dense_t;                      // [32][A]
   D2Weights d2w;
   CUtensorMap map_w_att, map_w_dec;
   int npass;
@@ -319,6 +320,7 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   c->Watt_b = ar.take<__nv_bfloat16>((size_t)2 * 4 * H * d.KattP);
   c->Wdec_b = ar.take<__nv_bfloat16>((size_t)2 * 4 * R * d.KdecP);
   c->loc_conv_t = ar.take<float>(2 * 31 * 32);
+  c->loc_dense_t = ar.take<float>((size_t)32 * A);
   if (sizing) return T2_OK;
   T2_REQUIRE(!ar.overflow, T2_ERR_STATE, "t2_ctx_commit: slab overflow");
 
@@ -356,7 +358,8 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   pack_lstm_bf16_kernel<<<gsz(4ll * R * d.KdecP), 256, 0, st>>>(dec_ih->ptr, dec_hh->ptr, c->Wdec_b, R, H + EF + C, d.KdecP);
   conv_t_kernel<<<(32 * 2 * 31 + 255) / 256, 256, 0, st>>>(lconv->ptr, c->loc_conv_t);
   T2_CHECK_CUDA(cudaGetLastError());
-  c->d2w = D2Weights{batt, bdec, wq->ptr, wv->ptr, c->loc_conv_t, ldense->ptr, Wproj, bproj, w1->ptr, w2->ptr};
+  { int rc3; if ((rc3 = transpose_launch(ldense->ptr, c->loc_dense_t, A, 32, st))) return rc3; }
+  c->d2w = D2Weights{batt, bdec, wq->ptr, wv->ptr, c->loc_conv_t, c->loc_dense_t, Wproj, bproj, w1->ptr, w2->ptr};
   {
     const unsigned zb = c->npass == 3 ? 2u : 1u;
     unsigned long long dims[3] = {64ull, 4ull * H * (d.KattP / 64), 2ull};

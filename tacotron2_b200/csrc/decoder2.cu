@@ -194,20 +194,20 @@ __device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) 
 // Attention for batch element b, part `part` of `S` (the S CTAs of one b sit in the same cluster):
 // each part computes the energies of its L-slice, the slices are exchanged through DSMEM, every part
 // normalises the full row and reduces its slice of the context columns.
-// Scratch (floats, in the idle TMA ring): q[A] | wp[Lc+32] | wc[Lc+32] | fs[Lc][33] | epart[8][Lc] | e_slice[Lc] |
+// Scratch (floats, in the idle TMA ring): q[A] | wp[Lc+32] | wc[Lc+32] | fs[Lc][36] | e_slice[Lc] |
 //                                         e_full[L] | red[64] | cred[4*cols]
+#define ATT_MARK(slot) do { if (blockIdx.x == 0 && threadIdx.x == 0 && s.prof) { const long long now_ = clock64(); s.prof[slot] += (unsigned long long)(now_ - *prof_last); *prof_last = now_; } } while (0)
 __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& io, const Smem& sm, float* scratch, bool active,
-                                int b, int part, int S, int cur, int t_out) {
+                                int b, int part, int S, int cur, int t_out, long long* prof_last) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int L = d.L, A = d.A, EF = d.EF;
   const int Lc = (L + S - 1) / S, l0 = part * Lc, l1 = min(L, l0 + Lc), nl = max(0, l1 - l0);
   const int nxt = cur ^ 1;
   float* q_s = scratch;
-  float* wp = q_s + A;
-  float* wc = wp + Lc + 32;
-  float* fs = wc + Lc + 32;
-  float* epart = fs + Lc * 33;
-  float* e_slice = epart + 8 * Lc;
+  float* wp = q_s + A;                            // previous / cumulative weights with a 15-tap halo
+  float* wc = wp + ((Lc + 35) & ~3);
+  float* fs = wc + ((Lc + 35) & ~3);            // [Lc][36] conv features (row stride 36: conflict-free float4 rows)
+  float* e_slice = fs + (size_t)Lc * 36;
   float* e_full = e_slice + ((Lc + 3) & ~3);
   float* red = e_full + ((L + 3) & ~3);
   float* cred = scratch + (((red + 64) - scratch + 3) & ~3);
@@ -224,74 +224,91 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
       wc[i] = in ? ld_cg(wcum + l) : 0.f;
     }
     __syncthreads();
-    // location conv: item = (position, group of 4 filters)  (model/attention.py:54)
+    // location conv (model/attention.py:54): warp task = (32 positions, 8 filters); lane = position
+    {
+      const int nchunk = (nl + 31) >> 5;
 #pragma unroll 1
-    for (int it = tid; it < nl * 8; it += D2_THREADS) {
-      const int fg = it / nl, li = it % nl;
-      float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int task = warp; task < nchunk * 4; task += D2_THREADS / 32) {
+        const int li = (task >> 2) * 32 + lane, fg = task & 3;
+        float acc[8];
 #pragma unroll
-      for (int j = 0; j < D2_LOC_K; ++j) {
-        const float a0 = wp[li + j], a1 = wc[li + j];
-        const float4 w0 = *reinterpret_cast<const float4*>(sm.conv_t + (0 * D2_LOC_K + j) * D2_LOC_F + fg * 4);
-        const float4 w1 = *reinterpret_cast<const float4*>(sm.conv_t + (1 * D2_LOC_K + j) * D2_LOC_F + fg * 4);
-        f.x = fmaf(w0.x, a0, f.x); f.y = fmaf(w0.y, a0, f.y); f.z = fmaf(w0.z, a0, f.z); f.w = fmaf(w0.w, a0, f.w);
-        f.x = fmaf(w1.x, a1, f.x); f.y = fmaf(w1.y, a1, f.y); f.z = fmaf(w1.z, a1, f.z); f.w = fmaf(w1.w, a1, f.w);
-      }
-      float* dst = fs + li * 33 + fg * 4;
-      dst[0] = f.x; dst[1] = f.y; dst[2] = f.z; dst[3] = f.w;
-    }
-    __syncthreads();
-    // location dense + tanh energies: warp = group of A/8 attention dims, lane = position (model/attention.py:55-62)
-    const int ag = A >> 3, a0 = warp * ag;
-    const unsigned char* mk = io.mask + (size_t)b * L;
+        for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+        const int lw = min(li, nl - 1);
 #pragma unroll 1
-    for (int lb = 0; lb < nl; lb += 32) {
-      const int li = lb + lane;
-      float e = 0.f;
-      if (li < nl && mk[l0 + li] == 0) {
-        const float* pm = io.pmem + ((size_t)b * L + l0 + li) * A + a0;
-        const int na4 = ag >> 2;
-        float4 pnext = __ldg(reinterpret_cast<const float4*>(pm));  // software-pipelined: fetch a4+1 while computing a4
-        float f[D2_LOC_F];
-#pragma unroll
-        for (int i = 0; i < D2_LOC_F; ++i) f[i] = fs[li * 33 + i];
-#pragma unroll 1
-        for (int a4 = 0; a4 < na4; ++a4) {
-          const float4 pc = pnext;
-          if (a4 + 1 < na4) pnext = __ldg(reinterpret_cast<const float4*>(pm) + a4 + 1);
-          const float pv[4] = {pc.x, pc.y, pc.z, pc.w};
-#pragma unroll
-          for (int aa = 0; aa < 4; ++aa) {
-            const int a = a0 + a4 * 4 + aa;
-            const float4* dr = reinterpret_cast<const float4*>(sm.dense + a * D2_LOC_F);
-            float l0a = 0.f, l1a = 0.f, l2a = 0.f, l3a = 0.f;
-#pragma unroll
-            for (int i = 0; i < D2_LOC_F / 4; i += 2) {
-              const float4 w4 = dr[i], w5 = dr[i + 1];
-              l0a = fmaf(w4.x, f[4 * i + 0], l0a); l1a = fmaf(w4.y, f[4 * i + 1], l1a);
-              l2a = fmaf(w4.z, f[4 * i + 2], l2a); l3a = fmaf(w4.w, f[4 * i + 3], l3a);
-              l0a = fmaf(w5.x, f[4 * i + 4], l0a); l1a = fmaf(w5.y, f[4 * i + 5], l1a);
-              l2a = fmaf(w5.z, f[4 * i + 6], l2a); l3a = fmaf(w5.w, f[4 * i + 7], l3a);
-            }
-            e = fmaf(sm.v[a], tanh_fast(q_s[a] + ((l0a + l1a) + (l2a + l3a)) + pv[aa]), e);
-          }
+        for (int j = 0; j < D2_LOC_K; ++j) {
+          const float a0 = wp[lw + j], a1 = wc[lw + j];
+          const float4* w0 = reinterpret_cast<const float4*>(sm.conv_t + (0 * D2_LOC_K + j) * D2_LOC_F + fg * 8);
+          const float4* w1 = reinterpret_cast<const float4*>(sm.conv_t + (1 * D2_LOC_K + j) * D2_LOC_F + fg * 8);
+          const float4 p0 = w0[0], p1 = w0[1], r0 = w1[0], r1 = w1[1];
+          acc[0] = fmaf(p0.x, a0, acc[0]); acc[1] = fmaf(p0.y, a0, acc[1]); acc[2] = fmaf(p0.z, a0, acc[2]); acc[3] = fmaf(p0.w, a0, acc[3]);
+          acc[4] = fmaf(p1.x, a0, acc[4]); acc[5] = fmaf(p1.y, a0, acc[5]); acc[6] = fmaf(p1.z, a0, acc[6]); acc[7] = fmaf(p1.w, a0, acc[7]);
+          acc[0] = fmaf(r0.x, a1, acc[0]); acc[1] = fmaf(r0.y, a1, acc[1]); acc[2] = fmaf(r0.z, a1, acc[2]); acc[3] = fmaf(r0.w, a1, acc[3]);
+          acc[4] = fmaf(r1.x, a1, acc[4]); acc[5] = fmaf(r1.y, a1, acc[5]); acc[6] = fmaf(r1.z, a1, acc[6]); acc[7] = fmaf(r1.w, a1, acc[7]);
+        }
+        if (li < nl) {
+          float4* dst = reinterpret_cast<float4*>(fs + (size_t)li * 36 + fg * 8);
+          dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+          dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
         }
       }
-      if (li < nl) epart[warp * Lc + li] = e;
     }
     __syncthreads();
+    ATT_MARK(10);
+    // location dense + tanh energies (model/attention.py:55-62): warp task = 4 positions; lane = 4 attention dims.
+    // acc[l][a] = sum_f fs[l][f] * Wd^T[f][a] on a 4x4 register tile, then e[l] = sum_a v[a] tanh(q[a] + acc + pm[l][a]).
+    {
+      const unsigned char* mk = io.mask + (size_t)b * L;
+      const int a4 = lane * 4;
+      const bool lane_on = a4 < A;
+      const int ac = lane_on ? a4 : 0;
+      const float4 q4 = *reinterpret_cast<const float4*>(q_s + ac);
+      const float4 v4 = *reinterpret_cast<const float4*>(sm.v + ac);
+      const int ntile = (nl + 3) >> 2;
 #pragma unroll 1
-    for (int li = tid; li < nl; li += D2_THREADS) {
-      float e = -INFINITY;
-      if (mk[l0 + li] == 0) {
-        e = 0.f;
+      for (int tl = warp; tl < ntile; tl += D2_THREADS / 32) {
+        const int lt = tl * 4;
+        float4 pm4[4];
 #pragma unroll
-        for (int w8 = 0; w8 < 8; ++w8) e += epart[w8 * Lc + li];
+        for (int l = 0; l < 4; ++l) {
+          const int lp = min(lt + l, nl - 1);
+          pm4[l] = __ldg(reinterpret_cast<const float4*>(io.pmem + ((size_t)b * L + l0 + lp) * A + ac));
+        }
+        float acc[4][4];
+#pragma unroll
+        for (int l = 0; l < 4; ++l)
+#pragma unroll
+          for (int a = 0; a < 4; ++a) acc[l][a] = 0.f;
+#pragma unroll 2
+        for (int f4 = 0; f4 < D2_LOC_F / 4; ++f4) {
+          float4 fv[4];
+#pragma unroll
+          for (int l = 0; l < 4; ++l) fv[l] = *reinterpret_cast<const float4*>(fs + (size_t)min(lt + l, nl - 1) * 36 + f4 * 4);
+#pragma unroll
+          for (int ff = 0; ff < 4; ++ff) {
+            const float4 wv = *reinterpret_cast<const float4*>(sm.dense + (f4 * 4 + ff) * A + ac);
+#pragma unroll
+            for (int l = 0; l < 4; ++l) {
+              const float fl = ff == 0 ? fv[l].x : (ff == 1 ? fv[l].y : (ff == 2 ? fv[l].z : fv[l].w));
+              acc[l][0] = fmaf(fl, wv.x, acc[l][0]); acc[l][1] = fmaf(fl, wv.y, acc[l][1]);
+              acc[l][2] = fmaf(fl, wv.z, acc[l][2]); acc[l][3] = fmaf(fl, wv.w, acc[l][3]);
+            }
+          }
+        }
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+          float e = v4.x * tanh_fast(q4.x + acc[l][0] + pm4[l].x);
+          e = fmaf(v4.y, tanh_fast(q4.y + acc[l][1] + pm4[l].y), e);
+          e = fmaf(v4.z, tanh_fast(q4.z + acc[l][2] + pm4[l].z), e);
+          e = fmaf(v4.w, tanh_fast(q4.w + acc[l][3] + pm4[l].w), e);
+          e = warp_sum(lane_on ? e : 0.f);
+          if (lane == 0 && lt + l < nl) e_slice[lt + l] = mk[l0 + lt + l] ? -INFINITY : e;  // masked_fill (model/attention.py:63)
+        }
       }
-      e_slice[li] = e;  // masked_fill(-inf) (model/attention.py:63)
     }
   }
+  ATT_MARK(11);
   tc::cluster_sync();  // energy slices visible to the peers of this batch element
+  ATT_MARK(12);
   if (active) {
     // gather the full energy row from the S parts (cluster ranks base..base+S-1)
     const uint32_t my_rank = tc::cluster_ctarank();
@@ -329,6 +346,7 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
       }
     }
     __syncthreads();
+    ATT_MARK(13);
     // context columns of this part (model/attention.py:66-67)
     const int cols_per = ((EF + S - 1) / S + 3) & ~3;
     const int c0 = part * cols_per, c1 = min(EF, c0 + cols_per);
@@ -378,6 +396,7 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
       s.projin[(size_t)b * d.KprojP + d.R + col] = v;
     }
   }
+  ATT_MARK(14);
   tc::cluster_sync();  // peers are done reading this CTA's energy slice before the scratch is reused
 }
 
@@ -462,7 +481,7 @@ decoder2_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weights w, D2St
         wrote_x = true;
       } else if (ph == PH_ATTN) {
         // ---- location-sensitive attention (model/attention.py:54-67, model/decoder.py:90)
-        attention_phase(d, s, io, sm, scratch, att_active, att_b, att_part, S, cur, tg_);
+        attention_phase(d, s, io, sm, scratch, att_active, att_b, att_part, S, cur, tg_, &prof_last);
         wrote_x = true;
       } else {
         // ---- small dense phases: query (model/attention.py:52), mel/gate projection (model/decoder.py:103-109),
@@ -533,7 +552,7 @@ decoder2_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weights w, D2St
 size_t att_scratch_floats(const D2Dims& d, int S) {
   const int Lc = (d.L + S - 1) / S;
   const int cols = (((d.EF + S - 1) / S) + 3) & ~3;
-  return (size_t)d.A + 2 * (Lc + 32) + (size_t)Lc * 33 + 8 * (size_t)Lc + Lc + 4 + d.L + 4 + 64 + 4 * (size_t)cols;
+  return (size_t)d.A + 2 * (size_t)((Lc + 35) & ~3) + (size_t)Lc * 36 + Lc + 4 + d.L + 4 + 64 + 8 + 4 * (size_t)cols;
 }
 
 }  // namespace

@@ -28,7 +28,7 @@ struct D2Weights {
   const float* Wq;         // [A][H]
   const float* v;          // [A]
   const float* loc_conv_t; // [2][31][32]  location_conv.weight transposed to (channel, tap, filter)
-  const float* loc_dense;  // [A][32]
+  const float* loc_dense;  // [32][A]  location_dense.weight transposed
   const float* Wproj;      // [M+1][KprojP]
   const float* bproj;      // [M+1]
   const float* W1;         // [P][M]
