@@ -3,6 +3,7 @@
 #include "common.cuh"
 #include "decoder.cuh"
 #include "decoder2.cuh"
+#include "convtc.cuh"
 #include "layers.cuh"
 
 #include <cstdarg>
@@ -45,6 +46,9 @@ struct t2_ctx {
   D2Weights d2w;
   CUtensorMap map_w_att, map_w_dec;
   int npass;
+  // tensor-core conv operands (bf16 hi/lo [2][Cout][k][Cin]) and their TMA descriptors
+  __nv_bfloat16 *enc_Wb[3], *post_Wb[5], *lstm_Wb, *attenc_Wb;
+  CUtensorMap enc_wmap[3], post_wmap[5], lstm_wmap, attenc_wmap;
 };
 
 namespace {
@@ -215,6 +219,19 @@ __global__ void rm_to_xsplit_kernel(const float* src, int lds, __nv_bfloat16* ds
   }
 }
 
+static int make_w_map(CUtensorMap* m, const __nv_bfloat16* w, int Cout, int Cin, int k, int NT, int npass) {
+  unsigned long long dims[4] = {(unsigned long long)Cin, (unsigned long long)k, (unsigned long long)Cout, 2ull};
+  unsigned long long st[3] = {(unsigned long long)Cin * 2, (unsigned long long)k * Cin * 2, (unsigned long long)Cout * k * Cin * 2};
+  unsigned box[4] = {64u, 1u, (unsigned)NT, npass == 3 ? 2u : 1u};
+  return tc_make_tmap_bf16(m, w, 4, dims, st, box);
+}
+static int make_in_map(CUtensorMap* m, const __nv_bfloat16* x, int B, int T, int Cin, int npass) {
+  unsigned long long dims[4] = {(unsigned long long)Cin, (unsigned long long)T, (unsigned long long)B, 2ull};
+  unsigned long long st[3] = {(unsigned long long)Cin * 2, (unsigned long long)T * Cin * 2, (unsigned long long)B * T * Cin * 2};
+  unsigned box[4] = {64u, 128u, 1u, npass == 3 ? 2u : 1u};
+  return tc_make_tmap_bf16(m, x, 4, dims, st, box);
+}
+
 const Param* find(const t2_ctx* c, const std::string& k) {
   auto it = c->params.find(k);
   return it == c->params.end() ? nullptr : &it->second;
@@ -321,6 +338,10 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   c->Wdec_b = ar.take<__nv_bfloat16>((size_t)2 * 4 * R * d.KdecP);
   c->loc_conv_t = ar.take<float>(2 * 31 * 32);
   c->loc_dense_t = ar.take<float>((size_t)32 * A);
+  for (int i = 0; i < 3; ++i) c->enc_Wb[i] = ar.take<__nv_bfloat16>((size_t)2 * E * KS * E);
+  for (int i = 0; i < 5; ++i) c->post_Wb[i] = ar.take<__nv_bfloat16>((size_t)2 * chans[i + 1] * 5 * chans[i]);
+  c->lstm_Wb = ar.take<__nv_bfloat16>((size_t)2 * 8 * Hh * E);
+  c->attenc_Wb = ar.take<__nv_bfloat16>((size_t)2 * A * EF);
   if (sizing) return T2_OK;
   T2_REQUIRE(!ar.overflow, T2_ERR_STATE, "t2_ctx_commit: slab overflow");
 
@@ -382,6 +403,8 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
     NEED(bm, bn + ".running_mean", E);
     NEED(bv, bn + ".running_var", E);
     if ((rc = repack_conv_launch(cw->ptr, c->enc_Wr[i], E, E, KS, st))) return rc;
+    if ((rc = pack_conv_w_launch(cw->ptr, c->enc_Wb[i], E, E, KS, st))) return rc;
+    if ((rc = make_w_map(&c->enc_wmap[i], c->enc_Wb[i], E, E, KS, 128, c->npass))) return rc;
     if ((rc = bn_fold_launch(bw->ptr, bb->ptr, bm->ptr, bv->ptr, cb->ptr, c->enc_scale[i], c->enc_shift[i], E, st))) return rc;
   }
   for (int i = 0; i < 5; ++i) {
@@ -392,6 +415,8 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
     NEED(bm, bn + ".running_mean", chans[i + 1]);
     NEED(bv, bn + ".running_var", chans[i + 1]);
     if ((rc = repack_conv_launch(cw->ptr, c->post_Wr[i], chans[i + 1], chans[i], 5, st))) return rc;
+    if ((rc = pack_conv_w_launch(cw->ptr, c->post_Wb[i], chans[i + 1], chans[i], 5, st))) return rc;
+    if ((rc = make_w_map(&c->post_wmap[i], c->post_Wb[i], chans[i + 1], chans[i], 5, chans[i + 1] % 128 == 0 ? 128 : chans[i + 1], c->npass))) return rc;
     if ((rc = bn_fold_launch(bw->ptr, bb->ptr, bm->ptr, bv->ptr, nullptr, c->post_scale[i], c->post_shift[i], chans[i + 1], st))) return rc;
   }
   // BiLSTM: input projection for both directions as one k=1 "conv": Wr [E][8Hh]; recurrent W_hh^T per direction
@@ -407,6 +432,10 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
     add_vec_kernel<<<(4 * Hh + 255) / 256, 256, 0, st>>>(bih->ptr, bhh->ptr, c->lstm_bias + dir * 4 * Hh, 4 * Hh);
   }
   if ((rc = transpose_launch(tmp, c->lstm_Wr, 8 * Hh, E, st))) return rc;
+  if ((rc = pack_conv_w_launch(tmp, c->lstm_Wb, 8 * Hh, E, 1, st))) return rc;   // tmp = [8Hh][E] = conv weight with k = 1
+  if ((rc = make_w_map(&c->lstm_wmap, c->lstm_Wb, 8 * Hh, E, 1, 128, c->npass))) return rc;
+  if ((rc = pack_conv_w_launch(wae->ptr, c->attenc_Wb, A, EF, 1, st))) return rc;
+  if ((rc = make_w_map(&c->attenc_wmap, c->attenc_Wb, A, EF, 1, A, c->npass))) return rc;
   if ((rc = transpose_launch(wae->ptr, c->attenc_Wr, A, EF, st))) return rc;
   T2_CHECK_CUDA(cudaGetLastError());
   c->committed = true;
@@ -431,31 +460,37 @@ extern "C" int t2_ctx_commit(t2_ctx* c, void* stream) {
   T2_REQUIRE(c->committed, T2_ERR_STATE, name ": weights not committed (call t2_ctx_commit)")
 #define RC(x) do { int _rc = (x); if (_rc) return _rc; } while (0)
 
+static int conv_tc(t2_ctx* c, const __nv_bfloat16* in, const CUtensorMap& wmap, int B, int T, int Cin, int Cout, int k, int NT, int act,
+                   const float* scale, const float* shift, const unsigned char* keep, int keep_ld, float* out_f32,
+                   __nv_bfloat16* out_b16, cudaStream_t st) {
+  ConvTcArgs a{};
+  RC(make_in_map(&a.in_map, in, B, T, Cin, c->npass));
+  a.w_map = wmap;
+  a.B = B; a.T = T; a.Cin = Cin; a.Cout = Cout; a.k = k; a.NT = NT; a.npass = c->npass; a.act = act;
+  a.scale = scale; a.shift = shift; a.keep = keep; a.keep_ld = keep_ld; a.drop_scale = 1.0f / (1.0f - c->cfg.dropout);
+  a.out_f32 = out_f32; a.out_b16 = out_b16; a.residual = nullptr; a.res_bstride = 0;
+  return convtc_launch(a, st);
+}
+
 static int encoder_impl(t2_ctx* c, const long long* chars, const long long* lens, int B, int L, int train,
                         const unsigned char* keep, float* encoded, Arena& ar, cudaStream_t st) {
   const int E = c->E, Hh = E / 2;
-  float* x0 = ar.take<float>((size_t)B * L * E);
-  float* x1 = ar.take<float>((size_t)B * L * E);
+  __nv_bfloat16* x0 = ar.take<__nv_bfloat16>((size_t)2 * B * L * E);
+  __nv_bfloat16* x1 = ar.take<__nv_bfloat16>((size_t)2 * B * L * E);
   float* xproj = ar.take<float>((size_t)B * L * 8 * Hh);
   if (!ar.base) return T2_OK;
   T2_REQUIRE(!ar.overflow, T2_ERR_WORKSPACE, "t2_encoder_fwd: workspace too small");
   T2_REQUIRE(!train, T2_ERR_UNSUPPORTED, "t2_encoder_fwd: train-mode BatchNorm statistics are not implemented in this revision");
-  RC(embed_launch(chars, find(c, "encoder.embedding.weight")->ptr, x0, B * L, E, c->cfg.num_chars + 1, st));
-  float* cur = x0;
-  float* nxt = x1;
-  for (int i = 0; i < 3; ++i) {
-    ConvArgs a{};
-    a.in = cur; a.in_bstride = (long long)L * E; a.Wr = c->enc_Wr[i]; a.bias = nullptr;
-    a.bn_scale = c->enc_scale[i]; a.bn_shift = c->enc_shift[i];
-    a.keep = keep ? keep + (size_t)i * B * L * E : nullptr; a.keep_ld = E; a.drop_scale = 1.0f / (1.0f - c->cfg.dropout);
-    a.out = nxt; a.B = B; a.T = L; a.Cin = E; a.Cout = E; a.k = c->KS; a.act = ACT_RELU;
-    RC(conv1d_cl_launch(a, st));
+  RC(embed_split_launch(chars, find(c, "encoder.embedding.weight")->ptr, x0, B * L, E, c->cfg.num_chars + 1, st));
+  __nv_bfloat16* cur = x0;
+  __nv_bfloat16* nxt = x1;
+  for (int i = 0; i < 3; ++i) {  // Conv1d k5 + BatchNorm (folded) + ReLU (+ Dropout)  model/encoder.py:31-46
+    RC(conv_tc(c, cur, c->enc_wmap[i], B, L, E, E, c->KS, 128, ACT_RELU, c->enc_scale[i], c->enc_shift[i],
+               keep ? keep + (size_t)i * B * L * E : nullptr, E, nullptr, nxt, st));
     std::swap(cur, nxt);
   }
-  ConvArgs p{};
-  p.in = cur; p.in_bstride = (long long)L * E; p.Wr = c->lstm_Wr; p.bias = c->lstm_bias; p.out = xproj;
-  p.B = B; p.T = L; p.Cin = E; p.Cout = 8 * Hh; p.k = 1; p.act = ACT_NONE; p.drop_scale = 1.f;
-  RC(conv1d_cl_launch(p, st));
+  // BiLSTM input projection for both directions (k = 1), then the packed recurrence  model/encoder.py:59-65
+  RC(conv_tc(c, cur, c->lstm_wmap, B, L, E, 8 * Hh, 1, 128, ACT_NONE, nullptr, c->lstm_bias, nullptr, 0, xproj, nullptr, st));
   RC(bilstm_launch(xproj, c->lstm_WhhT, lens, encoded, B, L, Hh, st));
   return T2_OK;
 }
@@ -473,6 +508,7 @@ static int memory_impl(t2_ctx* c, const float* encoded, const long long* spk, co
                        float* pmem, Arena& ar, cudaStream_t st) {
   const int E = c->E, EF = c->EF, D = EF - E;
   float* dvec = ar.take<float>((size_t)B * 128);
+  __nv_bfloat16* membf = ar.take<__nv_bfloat16>((size_t)2 * B * L * (c->EF));
   if (!ar.base) return T2_OK;
   T2_REQUIRE(!ar.overflow, T2_ERR_WORKSPACE, "t2_memory_fwd: workspace too small");
   const float* spk_table = nullptr;
@@ -491,10 +527,8 @@ static int memory_impl(t2_ctx* c, const float* encoded, const long long* spk, co
   }
   if (spk_table || D > 0) RC(condition_launch(encoded, spk_table, spk, dvec, D, memory, B, L, E, st));
   else T2_CHECK_CUDA(cudaMemcpyAsync(memory, encoded, (size_t)B * L * E * sizeof(float), cudaMemcpyDeviceToDevice, st));
-  ConvArgs p{};
-  p.in = memory; p.in_bstride = (long long)L * EF; p.Wr = c->attenc_Wr; p.out = pmem;
-  p.B = B; p.T = L; p.Cin = EF; p.Cout = c->A; p.k = 1; p.act = ACT_NONE; p.drop_scale = 1.f;
-  RC(conv1d_cl_launch(p, st));
+  RC(split_cl_launch(memory, (long long)L * EF, membf, B, L, EF, st));
+  RC(conv_tc(c, membf, c->attenc_wmap, B, L, EF, c->A, 1, c->A, ACT_NONE, nullptr, nullptr, nullptr, 0, pmem, nullptr, st));  // model/tacotron2.py:229
   return T2_OK;
 }
 
@@ -830,24 +864,21 @@ extern "C" int t2_prenet_fwd(t2_ctx* c, const float* x, const unsigned char* kee
 static int postnet_impl(t2_ctx* c, const float* mels, int t_stride, int B, int T, int train, const unsigned char* keep, float* out,
                         Arena& ar, cudaStream_t st) {
   const int M = c->M, PD = c->PD;
-  float* a0 = ar.take<float>((size_t)B * T * PD);
-  float* a1 = ar.take<float>((size_t)B * T * PD);
+  __nv_bfloat16* xin = ar.take<__nv_bfloat16>((size_t)2 * B * T * M);
+  __nv_bfloat16* a0 = ar.take<__nv_bfloat16>((size_t)2 * B * T * PD);
+  __nv_bfloat16* a1 = ar.take<__nv_bfloat16>((size_t)2 * B * T * PD);
   if (!ar.base) return T2_OK;
   T2_REQUIRE(!ar.overflow, T2_ERR_WORKSPACE, "t2_postnet_fwd: workspace too small");
   T2_REQUIRE(!train, T2_ERR_UNSUPPORTED, "t2_postnet_fwd: train-mode BatchNorm statistics are not implemented in this revision");
   const int chans[6] = {M, PD, PD, PD, PD, M};
-  const float* in = mels;
-  long long in_bs = (long long)t_stride * M;
-  float* bufs[2] = {a0, a1};
-  for (int i = 0; i < 5; ++i) {
-    ConvArgs a{};
-    a.in = in; a.in_bstride = in_bs; a.Wr = c->post_Wr[i]; a.bn_scale = c->post_scale[i]; a.bn_shift = c->post_shift[i];
-    a.keep = keep ? keep + (size_t)i * B * T * PD : nullptr; a.keep_ld = PD; a.drop_scale = 1.0f / (1.0f - c->cfg.dropout);
-    a.out = (i == 4) ? out : bufs[i & 1];
-    a.B = B; a.T = T; a.Cin = chans[i]; a.Cout = chans[i + 1]; a.k = 5; a.act = (i < 4) ? ACT_TANH : ACT_NONE;
-    RC(conv1d_cl_launch(a, st));
-    in = a.out;
-    in_bs = (long long)T * chans[i + 1];
+  RC(split_cl_launch(mels, (long long)t_stride * M, xin, B, T, M, st));
+  const __nv_bfloat16* in = xin;
+  __nv_bfloat16* bufs[2] = {a0, a1};
+  for (int i = 0; i < 5; ++i) {  // Conv1d k5 'same' + BatchNorm (folded) (+ Tanh) (+ Dropout)  model/postnet.py:8-47
+    const int Cout = chans[i + 1], NT = Cout % 128 == 0 ? 128 : Cout;
+    RC(conv_tc(c, in, c->post_wmap[i], B, T, chans[i], Cout, 5, NT, i < 4 ? ACT_TANH : ACT_NONE, c->post_scale[i], c->post_shift[i],
+               keep ? keep + (size_t)i * B * T * PD : nullptr, PD, i == 4 ? out : nullptr, i == 4 ? nullptr : bufs[i & 1], st));
+    in = bufs[i & 1];
   }
   return T2_OK;
 }

@@ -1,0 +1,33 @@
+// Channels-last conv1d (odd k, "same" padding) as an implicit GEMM on tcgen05:
+//   out[(b,t)][n] = sum_{j<k} sum_c in[b][t+j-pad][c] * W[n][c][j]
+// A = activations [128 positions x 64 channels] per (tap, channel block), fetched by TMA from a bf16 (hi,lo)
+// [2][B][T][C] tensor with out-of-bounds zero fill providing the padding; B = weights [N x 64] from a bf16 (hi,lo)
+// [2][Cout][k][Cin] pack; D = [128 x N] fp32 in TMEM.  fp32-parity mode issues three bf16 passes per K-step.
+// Used for Encoder convs (model/encoder.py:31-46), Postnet convs (model/postnet.py:8-47), and the 1x1 cases
+// att_encoder (model/tacotron2.py:229) and the BiLSTM input projection (model/encoder.py:49-52).
+#pragma once
+#include "tc.cuh"
+
+struct ConvTcArgs {
+  CUtensorMap in_map;   // dims {Cin, T, B, 2}, box {64, 128, 1, npass==3 ? 2 : 1}
+  CUtensorMap w_map;    // dims {Cin, k, Cout, 2}, box {64, 1, NT, ...}
+  int B, T, Cin, Cout, k, NT;   // NT = N tile (multiple of 16, <= 128)
+  int npass, act;
+  const float* scale;   // [Cout] folded BatchNorm scale or null
+  const float* shift;   // [Cout] folded shift / bias or null
+  const unsigned char* keep;  // dropout keep-mask [B][T][keep_ld] or null
+  int keep_ld;
+  float drop_scale;
+  float* out_f32;             // [B][T][Cout] or null
+  __nv_bfloat16* out_b16;     // [2][B][T][Cout] (hi plane, lo plane) or null
+  const float* residual;      // optional [B][res_tstride][Cout] added before the store (postnet residual), or null
+  long long res_bstride;
+};
+
+int convtc_launch(const ConvTcArgs& a, cudaStream_t st);
+// fp32 [B][T(stride)][C] -> bf16 (hi,lo) [2][B][T][C]
+int split_cl_launch(const float* src, long long src_bstride, __nv_bfloat16* dst, int B, int T, int C, cudaStream_t st);
+// conv weight [Cout][Cin][k] fp32 -> bf16 (hi,lo) [2][Cout][k][Cin]
+int pack_conv_w_launch(const float* W, __nv_bfloat16* dst, int Cout, int Cin, int k, cudaStream_t st);
+// embedding lookup straight to bf16 (hi,lo) [2][n_pos][E]
+int embed_split_launch(const long long* idx, const float* table, __nv_bfloat16* dst, int n_pos, int E, int n_rows, cudaStream_t st);
