@@ -36,7 +36,7 @@ struct t2_ctx {
   DecWeights dw;
   float *enc_Wr[3], *enc_scale[3], *enc_shift[3];
   float *post_Wr[5], *post_scale[5], *post_shift[5];
-  float *lstm_Wr, *lstm_bias, *lstm_WhhT;  // BiLSTM: [1][E][2*4Hh], [2*4Hh], [2][Hh][4Hh]
+  float *lstm_Wr, *lstm_bias, *lstm_Whh;  // BiLSTM: [1][E][2*4Hh], [2*4Hh], [2][4Hh][Hh]
   float* attenc_Wr;                        // [1][EF][A]
   unsigned long long* prof_buf;            // [16] device, decoder phase cycles
   // tensor-core decoder (decoder2)
@@ -331,7 +331,7 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   }
   c->lstm_Wr = ar.take<float>((size_t)E * 8 * Hh);
   c->lstm_bias = ar.take<float>(8 * Hh);
-  c->lstm_WhhT = ar.take<float>((size_t)2 * Hh * 4 * Hh);
+  c->lstm_Whh = ar.take<float>((size_t)2 * Hh * 4 * Hh);
   c->attenc_Wr = ar.take<float>((size_t)EF * A);
   float* tmp = ar.take<float>((size_t)8 * Hh * E);  // staging for the concatenated BiLSTM W_ih
   c->Watt_b = ar.take<__nv_bfloat16>((size_t)2 * 4 * H * d.KattP);
@@ -428,7 +428,8 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
     NEED(bhh, "encoder.lstm.bias_hh_l0" + sfx, 4 * Hh);
     T2_CHECK_CUDA(cudaMemcpyAsync(tmp + (size_t)dir * 4 * Hh * E, wih->ptr, (size_t)4 * Hh * E * sizeof(float),
                                   cudaMemcpyDeviceToDevice, st));
-    if ((rc = transpose_launch(whh->ptr, c->lstm_WhhT + (size_t)dir * Hh * 4 * Hh, 4 * Hh, Hh, st))) return rc;
+    T2_CHECK_CUDA(cudaMemcpyAsync(c->lstm_Whh + (size_t)dir * 4 * Hh * Hh, whh->ptr, (size_t)4 * Hh * Hh * sizeof(float),
+                                  cudaMemcpyDeviceToDevice, st));
     add_vec_kernel<<<(4 * Hh + 255) / 256, 256, 0, st>>>(bih->ptr, bhh->ptr, c->lstm_bias + dir * 4 * Hh, 4 * Hh);
   }
   if ((rc = transpose_launch(tmp, c->lstm_Wr, 8 * Hh, E, st))) return rc;
@@ -491,7 +492,7 @@ static int encoder_impl(t2_ctx* c, const long long* chars, const long long* lens
   }
   // BiLSTM input projection for both directions (k = 1), then the packed recurrence  model/encoder.py:59-65
   RC(conv_tc(c, cur, c->lstm_wmap, B, L, E, 8 * Hh, 1, 128, ACT_NONE, nullptr, c->lstm_bias, nullptr, 0, xproj, nullptr, st));
-  RC(bilstm_launch(xproj, c->lstm_WhhT, lens, encoded, B, L, Hh, st));
+  RC(bilstm_launch(xproj, c->lstm_Whh, lens, encoded, B, L, Hh, st));
   return T2_OK;
 }
 

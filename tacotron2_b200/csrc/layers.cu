@@ -109,46 +109,97 @@ __global__ void embed_kernel(const long long* idx, const float* table, float* ou
 }
 
 // ------------------------------------------------------------------------------------------
-// Packed BiLSTM recurrence (model/encoder.py:59-65).  One CTA per (direction, utterance); thread j
-// owns hidden unit j.  xproj already holds x W_ih^T + b_ih + b_hh.  The reverse direction starts at
-// the utterance's own last character; positions >= len are written as zeros.
-__global__ void __launch_bounds__(256) bilstm_kernel(const float* __restrict__ xproj, const float* __restrict__ WhhT,
-                                                     const long long* __restrict__ lens, float* __restrict__ out, int B,
-                                                     int L, int Hh) {
-  extern __shared__ float hs[];  // [Hh]
-  const int dir = blockIdx.x & 1, b = blockIdx.x >> 1;
-  const int n = (int)min((long long)L, max(0ll, lens[b]));
-  const float* W = WhhT + (size_t)dir * Hh * 4 * Hh;  // [k][4Hh]
-  for (int j = threadIdx.x; j < Hh; j += blockDim.x) hs[j] = 0.f;
-  for (int t = n + (int)threadIdx.x / Hh; t < L; t += blockDim.x / Hh) {  // zero the padded tail
-    for (int j = threadIdx.x % Hh; j < Hh; j += Hh) out[((size_t)b * L + t) * 2 * Hh + dir * Hh + j] = 0.f;
+// Packed BiLSTM recurrence (model/encoder.py:59-65).  One cluster of 8 CTAs per (direction, group of 8 utterances):
+// each CTA keeps the W_hh rows of Hh/8 hidden units (all four gates) resident in shared memory for the whole
+// sequence, computes their gates for the 8 utterances, and broadcasts the new hidden values to the 8 CTAs through
+// distributed shared memory; one cluster barrier per time step.  xproj already holds x W_ih^T + b_ih + b_hh.
+// The reverse direction starts at each utterance's own last character; positions >= len stay zero (pre-zeroed output).
+#define BL_NB 8
+#define BL_CL 8
+__global__ void __launch_bounds__(256, 1) bilstm_cluster_kernel(const float* __restrict__ xproj, const float* __restrict__ Whh,
+                                                                const long long* __restrict__ lens, float* __restrict__ out,
+                                                                int B, int L, int Hh) {
+  extern __shared__ __align__(16) float bsm[];
+  const int UPC = Hh / BL_CL, R = 4 * UPC, ldw = Hh + 1;
+  float* Ws = bsm;                              // [R][Hh+1]
+  float* hb = Ws + (size_t)R * ldw;             // [2][Hh][BL_NB]
+  hb += (4 - ((hb - bsm) & 3)) & 3;
+  float* gs = hb + 2 * Hh * BL_NB;              // [R][BL_NB+1]
+  __shared__ int len_s[BL_NB];
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const int cid = blockIdx.x / BL_CL, dir = cid & 1, grp = cid >> 1;
+  const int tid = threadIdx.x;
+  const float* W = Whh + (size_t)dir * 4 * Hh * Hh;  // [4Hh][Hh] of this direction
+  for (int i = tid; i < R * Hh; i += blockDim.x) {
+    const int lr = i / Hh, k = i - lr * Hh;
+    const int g = lr / UPC, ul = lr - g * UPC;
+    Ws[lr * ldw + k] = W[(size_t)(g * Hh + rank * UPC + ul) * Hh + k];
   }
-  float c = 0.f;
+  for (int i = tid; i < 2 * Hh * BL_NB; i += blockDim.x) hb[i] = 0.f;
+  if (tid < BL_NB) {
+    const int b = grp * BL_NB + tid;
+    len_s[tid] = b < B ? (int)min((long long)L, max(0ll, lens[b])) : 0;
+  }
   __syncthreads();
-  for (int s = 0; s < n; ++s) {
-    const int t = dir ? (n - 1 - s) : s;
-    const int j = threadIdx.x;
-    float hnew = 0.f;
-    if (j < Hh) {
-      const float* xp = xproj + (((size_t)b * L + t) * 2 + dir) * 4 * Hh;
-      float g0 = xp[j], g1 = xp[Hh + j], g2 = xp[2 * Hh + j], g3 = xp[3 * Hh + j];
-#pragma unroll 4
-      for (int k = 0; k < Hh; ++k) {
-        const float hk = hs[k];
-        const float* wr = W + (size_t)k * 4 * Hh;
-        g0 = fmaf(__ldg(wr + j), hk, g0);
-        g1 = fmaf(__ldg(wr + Hh + j), hk, g1);
-        g2 = fmaf(__ldg(wr + 2 * Hh + j), hk, g2);
-        g3 = fmaf(__ldg(wr + 3 * Hh + j), hk, g3);
+  int maxlen = 0;
+  for (int i = 0; i < BL_NB; ++i) maxlen = max(maxlen, len_s[i]);
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  const int r = tid % R, half = tid / R;          // gate-row role (needs 2R <= blockDim)
+  const int gq = r / UPC, uq = r - gq * UPC;
+  const int pu = tid % UPC, pb = tid / UPC;       // pointwise role: (unit, utterance), needs UPC * BL_NB <= blockDim
+  float c = 0.f, hprev = 0.f;
+  const uint32_t hb_addr = (uint32_t)__cvta_generic_to_shared(hb);
+  for (int s = 0; s < maxlen; ++s) {
+    const int cur = s & 1, nxt = cur ^ 1;
+    if (half < 2) {
+      float acc[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int bl = half * 4 + j, n = len_s[bl];
+        float x = 0.f;
+        if (s < n) {
+          const int t = dir ? (n - 1 - s) : s;
+          x = __ldg(xproj + (((size_t)(grp * BL_NB + bl) * L + t) * 2 + dir) * 4 * Hh + gq * Hh + rank * UPC + uq);
+        }
+        acc[j] = x;
       }
-      c = sigmoidf_(g1) * c + sigmoidf_(g0) * tanhf(g2);
-      hnew = sigmoidf_(g3) * tanhf(c);
-      out[((size_t)b * L + t) * 2 * Hh + dir * Hh + j] = hnew;
+      const float* wr = Ws + r * ldw;
+      const float* hc = hb + (size_t)cur * Hh * BL_NB + half * 4;
+#pragma unroll 8
+      for (int k = 0; k < Hh; ++k) {
+        const float w = wr[k];
+        const float4 h4 = *reinterpret_cast<const float4*>(hc + k * BL_NB);
+        acc[0] = fmaf(w, h4.x, acc[0]); acc[1] = fmaf(w, h4.y, acc[1]);
+        acc[2] = fmaf(w, h4.z, acc[2]); acc[3] = fmaf(w, h4.w, acc[3]);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) gs[r * (BL_NB + 1) + half * 4 + j] = acc[j];
     }
     __syncthreads();
-    if (j < Hh) hs[j] = hnew;
-    __syncthreads();
+    if (pb < BL_NB) {
+      const int n = len_s[pb];
+      float h = hprev;
+      if (s < n) {
+        const float gi = gs[(0 * UPC + pu) * (BL_NB + 1) + pb], gf = gs[(1 * UPC + pu) * (BL_NB + 1) + pb];
+        const float gg = gs[(2 * UPC + pu) * (BL_NB + 1) + pb], go = gs[(3 * UPC + pu) * (BL_NB + 1) + pb];
+        c = sigmoidf_(gf) * c + sigmoidf_(gi) * tanhf(gg);
+        h = sigmoidf_(go) * tanhf(c);
+        const int t = dir ? (n - 1 - s) : s;
+        out[((size_t)(grp * BL_NB + pb) * L + t) * 2 * Hh + dir * Hh + rank * UPC + pu] = h;
+      }
+      hprev = h;
+      const uint32_t off = hb_addr + (uint32_t)(((size_t)nxt * Hh * BL_NB + (size_t)(rank * UPC + pu) * BL_NB + pb) * 4);
+#pragma unroll
+      for (uint32_t pr = 0; pr < BL_CL; ++pr) {
+        uint32_t ra;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(off), "r"(pr));
+        asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(ra), "f"(h) : "memory");
+      }
+    }
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
   }
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
 // tanh(enc + speaker_emb) over ALL positions, then concat the description vector (model/tacotron2.py:201-212)
@@ -252,10 +303,23 @@ int embed_launch(const long long* idx, const float* table, float* out, int n_pos
   return T2_OK;
 }
 
-int bilstm_launch(const float* xproj, const float* WhhT, const long long* lens, float* out, int B, int L, int Hh, cudaStream_t st) {
-  T2_REQUIRE(Hh <= 256 && 256 % Hh == 0, T2_ERR_UNSUPPORTED, "bilstm: hidden %d unsupported (must divide 256)", Hh);
-  bilstm_kernel<<<2 * B, 256, Hh * sizeof(float), st>>>(xproj, WhhT, lens, out, B, L, Hh);
-  T2_CHECK_CUDA(cudaGetLastError());
+int bilstm_launch(const float* xproj, const float* Whh, const long long* lens, float* out, int B, int L, int Hh, cudaStream_t st) {
+  const int UPC = Hh / BL_CL;
+  T2_REQUIRE(Hh % BL_CL == 0 && 8 * UPC <= 256 && UPC * BL_NB <= 256 && Hh % 4 == 0, T2_ERR_UNSUPPORTED,
+             "bilstm: hidden size %d unsupported (needs Hh %% 8 == 0 and Hh <= 256)", Hh);
+  T2_CHECK_CUDA(cudaMemsetAsync(out, 0, (size_t)B * L * 2 * Hh * sizeof(float), st));
+  const size_t smem = ((size_t)4 * UPC * (Hh + 1) + 4 + 2 * (size_t)Hh * BL_NB + (size_t)4 * UPC * (BL_NB + 1)) * sizeof(float);
+  T2_CHECK_CUDA(cudaFuncSetAttribute(bilstm_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)(2 * ((B + BL_NB - 1) / BL_NB) * BL_CL));
+  cfg.blockDim = dim3(256);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = BL_CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  T2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, bilstm_cluster_kernel, xproj, Whh, lens, out, B, L, Hh));
   return T2_OK;
 }
 

@@ -20,7 +20,7 @@ struct ConvArgs {
 
 int conv1d_cl_launch(const ConvArgs& a, cudaStream_t st);
 int embed_launch(const long long* idx, const float* table, float* out, int n_pos, int E, int n_rows, cudaStream_t st);
-int bilstm_launch(const float* xproj /*[B][L][2][4Hh]*/, const float* WhhT /*[2][Hh][4Hh]*/, const long long* lens,
+int bilstm_launch(const float* xproj /*[B][L][2][4Hh]*/, const float* Whh /*[2][4Hh][Hh] (reference layout)*/, const long long* lens,
                   float* out /*[B][L][2Hh]*/, int B, int L, int Hh, cudaStream_t st);
 int condition_launch(const float* enc /*[B][L][E]*/, const float* spk_table, const long long* spk_id,
                      const float* desc_vec /*[B][D] already tanh(linear)*/, int D, float* out /*[B][L][E+D]*/, int B, int L,
