@@ -101,7 +101,8 @@ int t2_finalize(t2_ctx* ctx, float* mels, float* post, float* gates, const long 
                 void* stream);
 
 /* Debug: SM-clock cycles CTA 0 spent in each phase of the last decode call (host pointer, 16 slots;
- * synchronises the device).  Slots: 0 att-LSTM, 1 query, 2 attention, 3 dec-LSTM, 4 projection, 5 prenet1, 6 prenet2. */
+ * synchronises the device).  Slots: 0 att-LSTM tail, 1 query, 2 attention tail, 3 dec-LSTM tail, 4 projection, 5 prenet1,
+ * 6 prenet2, 7 extra barrier (T2B200_DEBUG_BARRIER), 8/9 att/dec gate GEMM, 10-14 attention conv/dense/sync/softmax/context. */
 int t2_debug_phase_cycles(t2_ctx* ctx, unsigned long long* host_out16);
 
 /* Debug: out (rows,64) = W (rows,K) * x (64,K)^T through the decoder's tcgen05 split-K path (TMA ring,

@@ -2,7 +2,6 @@
 #include "../../include/t2b200.h"
 #include "common.cuh"
 #include "decoder.cuh"
-#include "decoder2.cuh"
 #include "convtc.cuh"
 #include "layers.cuh"
 
@@ -27,17 +26,15 @@ struct t2_ctx {
   t2_model_config cfg;
   int device, num_sms;
   int EF, C, H, R, P, A, M, E, PD, KS;
-  DecDims dd;  // B, L filled per call
+  struct { int KattP, KdecP, KprojP; } dd;  // padded contraction lengths of the packed decoder operands
   std::map<std::string, Param> params;
   bool committed;
   // packed device memory (one slab)
   char* slab;
   size_t slab_bytes;
-  DecWeights dw;
-  float *enc_Wr[3], *enc_scale[3], *enc_shift[3];
-  float *post_Wr[5], *post_scale[5], *post_shift[5];
-  float *lstm_Wr, *lstm_bias, *lstm_Whh;  // BiLSTM: [1][E][2*4Hh], [2*4Hh], [2][4Hh][Hh]
-  float* attenc_Wr;                        // [1][EF][A]
+  float *enc_scale[3], *enc_shift[3];      // folded BatchNorm (+conv bias) of the encoder convs
+  float *post_scale[5], *post_shift[5];
+  float *lstm_bias, *lstm_Whh;  // BiLSTM: [1][E][2*4Hh], [2*4Hh], [2][4Hh][Hh]
   unsigned long long* prof_buf;            // [16] device, decoder phase cycles
   // tensor-core decoder (decoder2)
   __nv_bfloat16 *Watt_b, *Wdec_b;          // [2 hi/lo][4H permuted][KattP] / [2][4R][KdecP]
@@ -52,21 +49,6 @@ struct t2_ctx {
 };
 
 namespace {
-
-__global__ void pack_lstm_kernel(const float* Wih, const float* Whh, float* Wp, int H, int Kin, int KP) {
-  // Wp[tile][k][rr], rr = gate*8 + unit_in_tile  <-  row = gate*H + tile*8 + unit_in_tile
-  const long long n = (long long)(H / 8) * KP * 32;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-    const int rr = (int)(i % 32);
-    const int k = (int)((i / 32) % KP);
-    const int tile = (int)(i / (32ll * KP));
-    const int row = (rr / 8) * H + tile * 8 + (rr % 8);
-    float v = 0.f;
-    if (k < Kin) v = Wih[(size_t)row * Kin + k];
-    else if (k < Kin + H) v = Whh[(size_t)row * H + (k - Kin)];
-    Wp[i] = v;
-  }
-}
 
 __global__ void add_vec_kernel(const float* a, const float* b, float* o, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -88,15 +70,15 @@ __global__ void pack_proj_kernel(const float* Wmel, const float* Wgate, const fl
 
 // row-major (B,dim) -> k-major [dim][BP] rows at row offset, batch slots >= B zeroed
 __global__ void rm_to_km_kernel(const float* src, int ld, float* dst, int row0, int dim, int B) {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < dim * DEC_BP; i += gridDim.x * blockDim.x) {
-    const int r = i / DEC_BP, b = i % DEC_BP;
-    dst[(size_t)(row0 + r) * DEC_BP + b] = (b < B && src) ? src[(size_t)b * ld + r] : 0.f;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < dim * D2_BP; i += gridDim.x * blockDim.x) {
+    const int r = i / D2_BP, b = i % D2_BP;
+    dst[(size_t)(row0 + r) * D2_BP + b] = (b < B && src) ? src[(size_t)b * ld + r] : 0.f;
   }
 }
 __global__ void km_to_rm_kernel(const float* src, int row0, float* dst, int ld, int dim, int B) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < dim * B; i += gridDim.x * blockDim.x) {
     const int b = i / dim, r = i % dim;
-    dst[(size_t)b * ld + r] = src[(size_t)(row0 + r) * DEC_BP + b];
+    dst[(size_t)b * ld + r] = src[(size_t)(row0 + r) * D2_BP + b];
   }
 }
 __global__ void copy2d_kernel(const float* src, int lds, float* dst, int ldd, int rows, int cols) {
@@ -108,9 +90,9 @@ __global__ void copy2d_kernel(const float* src, int lds, float* dst, int ldd, in
 
 // prenet (model/tacotron2.py:85-92) on N independent rows, 8 rows per CTA pass.
 // mode 0: x (N,M) -> out (N,P), keep1/keep2 (N,P).
-// mode 1 (teacher forcing, model/tacotron2.py:255-257): row n = t*B + b, t in [0,T]; input is
+// mode 2 (teacher forcing, model/tacotron2.py:255-257): row n = t*B + b, t in [0,T]; input is
 //   mel_target[b][t-1] (zeros for t = 0, the F.pad row); keep = prenet_keep (T+1,2,B,P);
-//   output is k-major [T+1][P][DEC_BP] for the persistent decoder kernel.
+//   output is bf16 (hi,lo) [T+1][2][D2_BP][P], the layout the decoder's TMA descriptor reads.
 struct PrenetArgs {
   const float* x; const float* W1; const float* W2;
   const unsigned char* k1; const unsigned char* k2;
@@ -164,7 +146,6 @@ __global__ void __launch_bounds__(256) prenet_rows_kernel(PrenetArgs a) {
           const float v = (acc[r] > 0.f && keep) ? acc[r] * scale : 0.f;
           if (layer == 0) hs[r * P + o] = v;  // safe: each thread writes only its own o, read after the barrier
           else if (a.mode == 0) a.out[(size_t)n * P + o] = v;
-          else if (a.mode == 1) { const int t = n / a.B, b = n % a.B; a.out[((size_t)t * P + o) * DEC_BP + b] = v; }
           else {
             const int t = n / a.B, b = n % a.B;
             __nv_bfloat16 hi, lo;
@@ -267,16 +248,9 @@ extern "C" int t2_ctx_create(const t2_model_config* cfg, t2_ctx** out) {
   c->M = cfg->num_mels;
   c->PD = cfg->postnet_dim;
   c->KS = cfg->encoder_kernel_size;
-  DecDims& d = c->dd;
-  d.B = d.L = 0;
-  d.EF = c->EF; d.H = c->H; d.R = c->R; d.P = c->P; d.A = c->A; d.M = c->M; d.C = c->C;
-  d.Katt = c->P + c->EF + c->H;
-  d.KattP = (int)round_up64(d.Katt, 64);
-  d.Kdec = c->H + c->EF + c->C + c->R;
-  d.KdecP = (int)round_up64(d.Kdec, 64);
-  d.Kproj = c->R + c->EF + c->C;
-  d.KprojP = (int)round_up64(d.Kproj, 4);
-  d.p_prenet = cfg->dropout;
+  c->dd.KattP = (int)round_up64(c->P + c->EF + c->H, 64);
+  c->dd.KdecP = (int)round_up64(c->H + c->EF + c->C + c->R, 64);
+  c->dd.KprojP = (int)round_up64(c->R + c->EF + c->C, 4);
   c->npass = cfg->precision == 1 ? 1 : 3;
   c->committed = false;
   c->slab = nullptr;
@@ -309,30 +283,24 @@ extern "C" int t2_ctx_set_param(t2_ctx* c, const char* key, const float* ptr, lo
 
 static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   const bool sizing = ar.base == nullptr;
-  const DecDims& d = c->dd;
+  const auto& d = c->dd;
   const int H = c->H, R = c->R, P = c->P, A = c->A, M = c->M, E = c->E, EF = c->EF, C = c->C, PD = c->PD, KS = c->KS;
   const int Hh = E / 2;
-  float* Watt_p = ar.take<float>((size_t)(H / 8) * d.KattP * 32);
   float* batt = ar.take<float>(4 * H);
-  float* Wdec_p = ar.take<float>((size_t)(R / 8) * d.KdecP * 32);
   float* bdec = ar.take<float>(4 * R);
   float* Wproj = ar.take<float>((size_t)(M + 1) * d.KprojP);
   float* bproj = ar.take<float>(M + 1);
   int chans[6] = {M, PD, PD, PD, PD, M};
   for (int i = 0; i < 3; ++i) {
-    c->enc_Wr[i] = ar.take<float>((size_t)KS * E * E);
     c->enc_scale[i] = ar.take<float>(E);
     c->enc_shift[i] = ar.take<float>(E);
   }
   for (int i = 0; i < 5; ++i) {
-    c->post_Wr[i] = ar.take<float>((size_t)5 * chans[i] * chans[i + 1]);
     c->post_scale[i] = ar.take<float>(chans[i + 1]);
     c->post_shift[i] = ar.take<float>(chans[i + 1]);
   }
-  c->lstm_Wr = ar.take<float>((size_t)E * 8 * Hh);
   c->lstm_bias = ar.take<float>(8 * Hh);
   c->lstm_Whh = ar.take<float>((size_t)2 * Hh * 4 * Hh);
-  c->attenc_Wr = ar.take<float>((size_t)EF * A);
   float* tmp = ar.take<float>((size_t)8 * Hh * E);  // staging for the concatenated BiLSTM W_ih
   c->Watt_b = ar.take<__nv_bfloat16>((size_t)2 * 4 * H * d.KattP);
   c->Wdec_b = ar.take<__nv_bfloat16>((size_t)2 * 4 * R * d.KdecP);
@@ -366,14 +334,11 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   NEED(wae, "att_encoder.weight", (size_t)A * EF);
   T2_REQUIRE(H == R, T2_ERR_UNSUPPORTED, "att_rnn_dim != rnn_hidden_dim is not supported by the packed layout");
 
-  pack_lstm_kernel<<<gsz((long long)(H / 8) * d.KattP * 32), 256, 0, st>>>(att_ih->ptr, att_hh->ptr, Watt_p, H, P + EF, d.KattP);
-  pack_lstm_kernel<<<gsz((long long)(R / 8) * d.KdecP * 32), 256, 0, st>>>(dec_ih->ptr, dec_hh->ptr, Wdec_p, R, H + EF + C, d.KdecP);
   add_vec_kernel<<<(4 * H + 255) / 256, 256, 0, st>>>(att_bi->ptr, att_bh->ptr, batt, 4 * H);
   add_vec_kernel<<<(4 * R + 255) / 256, 256, 0, st>>>(dec_bi->ptr, dec_bh->ptr, bdec, 4 * R);
   pack_proj_kernel<<<gsz((long long)(M + 1) * d.KprojP), 256, 0, st>>>(wmel->ptr, wgate->ptr, bmel->ptr, bgate->ptr, Wproj, bproj, M,
                                                                       R + EF + C, R + EF, d.KprojP);
   T2_CHECK_CUDA(cudaGetLastError());
-  c->dw = DecWeights{Watt_p, batt, Wdec_p, bdec, wq->ptr, wv->ptr, lconv->ptr, ldense->ptr, Wproj, bproj, w1->ptr, w2->ptr};
   // tensor-core decoder operands
   pack_lstm_bf16_kernel<<<gsz(4ll * H * d.KattP), 256, 0, st>>>(att_ih->ptr, att_hh->ptr, c->Watt_b, H, P + EF, d.KattP);
   pack_lstm_bf16_kernel<<<gsz(4ll * R * d.KdecP), 256, 0, st>>>(dec_ih->ptr, dec_hh->ptr, c->Wdec_b, R, H + EF + C, d.KdecP);
@@ -402,7 +367,6 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
     NEED(bb, bn + ".bias", E);
     NEED(bm, bn + ".running_mean", E);
     NEED(bv, bn + ".running_var", E);
-    if ((rc = repack_conv_launch(cw->ptr, c->enc_Wr[i], E, E, KS, st))) return rc;
     if ((rc = pack_conv_w_launch(cw->ptr, c->enc_Wb[i], E, E, KS, st))) return rc;
     if ((rc = make_w_map(&c->enc_wmap[i], c->enc_Wb[i], E, E, KS, 128, c->npass))) return rc;
     if ((rc = bn_fold_launch(bw->ptr, bb->ptr, bm->ptr, bv->ptr, cb->ptr, c->enc_scale[i], c->enc_shift[i], E, st))) return rc;
@@ -414,7 +378,6 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
     NEED(bb, bn + ".bias", chans[i + 1]);
     NEED(bm, bn + ".running_mean", chans[i + 1]);
     NEED(bv, bn + ".running_var", chans[i + 1]);
-    if ((rc = repack_conv_launch(cw->ptr, c->post_Wr[i], chans[i + 1], chans[i], 5, st))) return rc;
     if ((rc = pack_conv_w_launch(cw->ptr, c->post_Wb[i], chans[i + 1], chans[i], 5, st))) return rc;
     if ((rc = make_w_map(&c->post_wmap[i], c->post_Wb[i], chans[i + 1], chans[i], 5, chans[i + 1] % 128 == 0 ? 128 : chans[i + 1], c->npass))) return rc;
     if ((rc = bn_fold_launch(bw->ptr, bb->ptr, bm->ptr, bv->ptr, nullptr, c->post_scale[i], c->post_shift[i], chans[i + 1], st))) return rc;
@@ -432,12 +395,10 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
                                   cudaMemcpyDeviceToDevice, st));
     add_vec_kernel<<<(4 * Hh + 255) / 256, 256, 0, st>>>(bih->ptr, bhh->ptr, c->lstm_bias + dir * 4 * Hh, 4 * Hh);
   }
-  if ((rc = transpose_launch(tmp, c->lstm_Wr, 8 * Hh, E, st))) return rc;
   if ((rc = pack_conv_w_launch(tmp, c->lstm_Wb, 8 * Hh, E, 1, st))) return rc;   // tmp = [8Hh][E] = conv weight with k = 1
   if ((rc = make_w_map(&c->lstm_wmap, c->lstm_Wb, 8 * Hh, E, 1, 128, c->npass))) return rc;
   if ((rc = pack_conv_w_launch(wae->ptr, c->attenc_Wb, A, EF, 1, st))) return rc;
   if ((rc = make_w_map(&c->attenc_wmap, c->attenc_Wb, A, EF, 1, A, c->npass))) return rc;
-  if ((rc = transpose_launch(wae->ptr, c->attenc_Wr, A, EF, st))) return rc;
   T2_CHECK_CUDA(cudaGetLastError());
   c->committed = true;
   return T2_OK;
@@ -541,84 +502,7 @@ extern "C" int t2_memory_fwd(t2_ctx* c, const float* encoded, const long long* s
   return memory_impl(c, encoded, speaker_id, description, B, L, memory, processed_memory, ar, (cudaStream_t)stream);
 }
 
-// Decoder state carve-out; everything between zero_begin and zero_end is memset to 0 before a run.
-struct StatePlan { DecState s; char* zero_begin; size_t zero_bytes; };
-static StatePlan plan_state(const DecDims& d, int L, Arena& ar) {
-  StatePlan pl{};
-  int64_t off0 = ar.off;
-  DecState& s = pl.s;
-  for (int i = 0; i < 2; ++i) s.xpre[i] = ar.take<float>((size_t)d.P * DEC_BP);
-  for (int i = 0; i < 2; ++i) s.xatt[i] = ar.take<float>((size_t)(d.KattP - d.P) * DEC_BP);
-  for (int i = 0; i < 2; ++i) s.xdec[i] = ar.take<float>((size_t)d.KdecP * DEC_BP);
-  s.att_c = ar.take<float>((size_t)d.H * DEC_BP);
-  s.rnn_c = ar.take<float>((size_t)d.R * DEC_BP);
-  s.att_h_rm = ar.take<float>((size_t)DEC_BP * d.H);
-  s.projin = ar.take<float>((size_t)DEC_BP * d.KprojP);
-  s.q = ar.take<float>((size_t)DEC_BP * d.A);
-  s.w_prev = ar.take<float>((size_t)2 * DEC_BP * L);
-  s.w_cum = ar.take<float>((size_t)2 * DEC_BP * L);
-  s.mel_cur = ar.take<float>((size_t)DEC_BP * d.M);
-  s.p1 = ar.take<float>((size_t)DEC_BP * d.P);
-  s.done = ar.take<int>(DEC_BP);
-  s.lengths = ar.take<long long>(DEC_BP);
-  s.n_frames = ar.take<int>(4);
-  s.barrier = ar.take<unsigned>(4);
-  pl.zero_begin = ar.base ? ar.base + off0 : nullptr;
-  pl.zero_bytes = (size_t)(ar.off - off0);
-  return pl;
-}
-
-static int fill_controls(const DecDims& d, DecState& s, const float* controls, int B, cudaStream_t st) {
-  if (d.C == 0) return T2_OK;
-  T2_REQUIRE(controls, T2_ERR_ARG, "Controls are enabled, but no control vector was passed to the model!");  // model/tacotron2.py:183-185
-  for (int i = 0; i < 2; ++i) rm_to_km_kernel<<<gsz(d.C * DEC_BP), 256, 0, st>>>(controls, d.C, s.xdec[i], d.H + d.EF, d.C, B);
-  copy2d_kernel<<<gsz(B * d.C), 256, 0, st>>>(controls, d.C, s.projin + d.R + d.EF, d.KprojP, B, d.C);
-  T2_CHECK_CUDA(cudaGetLastError());
-  return T2_OK;
-}
-
-static int decode_impl(t2_ctx* c, bool tf, const float* memory, const float* pmem, const unsigned char* mask, const float* controls,
-                       const float* mel_target, int B, int L, int T, const unsigned char* prenet_keep, int train,
-                       const unsigned char* att_keep, const unsigned char* rnn_keep, unsigned long long seed, float* mels,
-                       float* gates, float* aligns, long long* lengths, int* n_frames, Arena& ar, cudaStream_t st) {
-  DecDims d = c->dd;
-  d.B = B; d.L = L;
-  StatePlan pl = plan_state(d, L, ar);
-  float* tfp = tf ? ar.take<float>((size_t)(T + 1) * d.P * DEC_BP) : nullptr;
-  if (!ar.base) return T2_OK;
-  T2_REQUIRE(!ar.overflow, T2_ERR_WORKSPACE, "t2_decode: workspace too small");
-  T2_CHECK_CUDA(cudaMemsetAsync(pl.zero_begin, 0, pl.zero_bytes, st));
-  DecState s = pl.s;
-  s.prof = c->prof_buf;
-  T2_CHECK_CUDA(cudaMemsetAsync(c->prof_buf, 0, 16 * sizeof(unsigned long long), st));
-  RC(fill_controls(d, s, controls, B, st));
-  DecIO io{};
-  io.memory = memory; io.pmem = pmem; io.mask = mask; io.prenet_keep = prenet_keep;
-  io.att_keep = att_keep; io.rnn_keep = rnn_keep; io.mels = mels; io.gates = gates; io.aligns = aligns;
-  io.projin_all = nullptr; io.Tmax = T; io.n_steps = T; io.t0 = 0; io.seed = seed;
-  io.hidden_dropout = train ? 1 : 0;
-  if (tf) {
-    T2_CHECK_CUDA(cudaMemsetAsync(tfp, 0, (size_t)(T + 1) * d.P * DEC_BP * sizeof(float), st));
-    PrenetArgs pa{mel_target, c->dw.W1, c->dw.W2, prenet_keep, prenet_keep, seed, d.p_prenet, (T + 1) * B, d.M, d.P, 1, B, T, tfp, nullptr};
-    prenet_rows_kernel<<<std::min(((T + 1) * B + PN_ROWS - 1) / PN_ROWS, 148 * 4), 256, PN_ROWS * (d.M + d.P) * sizeof(float), st>>>(pa);
-    T2_CHECK_CUDA(cudaGetLastError());
-    io.tf_prenet = tfp; io.teacher_forcing = 1; io.stop_enabled = 0;
-  } else {
-    io.tf_prenet = nullptr; io.teacher_forcing = 0; io.stop_enabled = 1;
-    T2_CHECK_CUDA(cudaMemsetAsync(lengths, 0, (size_t)B * sizeof(long long), st));
-    s.lengths = lengths;
-    s.n_frames = n_frames;
-  }
-  return dec_launch(d, c->dw, s, io, c->num_sms, st);
-}
-
-// ------------------------------------------------------------------------------------------ tensor-core decoder (decoder2)
-static bool use_v2() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("T2B200_DECODER"); v = (e && e[0] == '1') ? 0 : 1; }
-  return v == 1;
-}
-
+// ------------------------------------------------------------------------------------------ decoder
 struct State2Plan { D2State s; char* zero_begin; size_t zero_bytes; };
 static State2Plan plan_state2(const D2Dims& d, int L, Arena& ar) {
   State2Plan pl{};
@@ -713,7 +597,7 @@ static int decode2_impl(t2_ctx* c, bool tf, const float* memory, const float* pm
   io.debug_barrier = getenv("T2B200_DEBUG_BARRIER") ? 1 : 0;
   if (tf) {
     T2_CHECK_CUDA(cudaMemsetAsync(tfp, 0, (size_t)(T + 1) * 2 * D2_BP * d.P * sizeof(__nv_bfloat16), st));
-    PrenetArgs pa{mel_target, c->dw.W1, c->dw.W2, prenet_keep, prenet_keep, seed, d.p_prenet, (T + 1) * B, d.M, d.P, 2, B, T, nullptr, tfp};
+    PrenetArgs pa{mel_target, c->d2w.W1, c->d2w.W2, prenet_keep, prenet_keep, seed, d.p_prenet, (T + 1) * B, d.M, d.P, 2, B, T, nullptr, tfp};
     prenet_rows_kernel<<<std::min(((T + 1) * B + PN_ROWS - 1) / PN_ROWS, 148 * 4), 256, PN_ROWS * (d.M + d.P) * sizeof(float), st>>>(pa);
     T2_CHECK_CUDA(cudaGetLastError());
     io.teacher_forcing = 1; io.stop_enabled = 0;
@@ -777,7 +661,7 @@ extern "C" int t2_decode_ar(t2_ctx* c, const float* memory, const float* process
              "t2_decode_ar: null argument");
   T2_REQUIRE(B > 0 && L > 0 && max_len > 0, T2_ERR_ARG, "t2_decode_ar: bad sizes B=%d L=%d max_len=%d", B, L, max_len);
   Arena ar(ws, ws_bytes);
-  return (use_v2() ? decode2_impl : decode_impl)(c, false, memory, processed_memory, mask, controls, nullptr, B, L, max_len, prenet_keep,
+  return decode2_impl(c, false, memory, processed_memory, mask, controls, nullptr, B, L, max_len, prenet_keep,
                                                  0, nullptr, nullptr, seed, mels, gates, alignments, lengths, n_frames, ar,
                                                  (cudaStream_t)stream);
 }
@@ -791,47 +675,9 @@ extern "C" int t2_decode_tf(t2_ctx* c, const float* memory, const float* process
              "Ground-truth Mel spectrogram is required for teacher forcing");  // model/tacotron2.py:168-170
   T2_REQUIRE(B > 0 && L > 0 && T > 0, T2_ERR_ARG, "t2_decode_tf: bad sizes");
   Arena ar(ws, ws_bytes);
-  return (use_v2() ? decode2_impl : decode_impl)(c, true, memory, processed_memory, mask, controls, mel_target, B, L, T, prenet_keep,
+  return decode2_impl(c, true, memory, processed_memory, mask, controls, mel_target, B, L, T, prenet_keep,
                                                  train, att_keep, rnn_keep, seed, mels, gates, alignments, nullptr, nullptr, ar,
                                                  (cudaStream_t)stream);
-}
-
-static int step_impl(t2_ctx* c, const float* prev, const float* att_h, const float* att_c, const float* ctx, const float* w,
-                     const float* w_cum, const float* rnn_h, const float* rnn_c, const float* memory, const float* pmem,
-                     const unsigned char* mask, const float* controls, int B, int L, float* mel_out, float* gate_out,
-                     float* att_h_out, float* att_c_out, float* ctx_out, float* w_out, float* w_cum_out, float* rnn_h_out,
-                     float* rnn_c_out, Arena& ar, cudaStream_t st) {
-  DecDims d = c->dd;
-  d.B = B; d.L = L;
-  StatePlan pl = plan_state(d, L, ar);
-  float* tfp = ar.take<float>((size_t)d.P * DEC_BP);
-  if (!ar.base) return T2_OK;
-  T2_REQUIRE(!ar.overflow, T2_ERR_WORKSPACE, "t2_decoder_step: workspace too small");
-  T2_CHECK_CUDA(cudaMemsetAsync(pl.zero_begin, 0, pl.zero_bytes, st));
-  DecState s = pl.s;
-  RC(fill_controls(d, s, controls, B, st));
-  // pack the caller's row-major state into the kernel's layout (parity 0 = "current")
-  rm_to_km_kernel<<<gsz(d.P * DEC_BP), 256, 0, st>>>(prev, d.P, tfp, 0, d.P, B);
-  rm_to_km_kernel<<<gsz(d.EF * DEC_BP), 256, 0, st>>>(ctx, d.EF, s.xatt[0], 0, d.EF, B);
-  rm_to_km_kernel<<<gsz(d.H * DEC_BP), 256, 0, st>>>(att_h, d.H, s.xatt[0], d.EF, d.H, B);
-  rm_to_km_kernel<<<gsz(d.H * DEC_BP), 256, 0, st>>>(att_c, d.H, s.att_c, 0, d.H, B);
-  rm_to_km_kernel<<<gsz(d.R * DEC_BP), 256, 0, st>>>(rnn_h, d.R, s.xdec[0], d.H + d.EF + d.C, d.R, B);
-  rm_to_km_kernel<<<gsz(d.R * DEC_BP), 256, 0, st>>>(rnn_c, d.R, s.rnn_c, 0, d.R, B);
-  copy2d_kernel<<<gsz(B * L), 256, 0, st>>>(w, L, s.w_prev, L, B, L);
-  copy2d_kernel<<<gsz(B * L), 256, 0, st>>>(w_cum, L, s.w_cum, L, B, L);
-  T2_CHECK_CUDA(cudaGetLastError());
-  DecIO io{};
-  io.memory = memory; io.pmem = pmem; io.mask = mask; io.tf_prenet = tfp; io.teacher_forcing = 1; io.stop_enabled = 0;
-  io.mels = mel_out; io.gates = gate_out; io.aligns = w_out; io.Tmax = 1; io.n_steps = 1; io.t0 = 0;
-  RC(dec_launch(d, c->dw, s, io, c->num_sms, st));
-  copy2d_kernel<<<gsz(B * d.H), 256, 0, st>>>(s.att_h_rm, d.H, att_h_out, d.H, B, d.H);
-  km_to_rm_kernel<<<gsz(B * d.H), 256, 0, st>>>(s.att_c, 0, att_c_out, d.H, d.H, B);
-  copy2d_kernel<<<gsz(B * d.EF), 256, 0, st>>>(s.projin + d.R, d.KprojP, ctx_out, d.EF, B, d.EF);
-  copy2d_kernel<<<gsz(B * L), 256, 0, st>>>(s.w_cum + (size_t)DEC_BP * L, L, w_cum_out, L, B, L);
-  copy2d_kernel<<<gsz(B * d.R), 256, 0, st>>>(s.projin, d.KprojP, rnn_h_out, d.R, B, d.R);
-  km_to_rm_kernel<<<gsz(B * d.R), 256, 0, st>>>(s.rnn_c, 0, rnn_c_out, d.R, d.R, B);
-  T2_CHECK_CUDA(cudaGetLastError());
-  return T2_OK;
 }
 
 extern "C" int t2_decoder_step(t2_ctx* c, const float* prev_mel_prenet, const float* att_h, const float* att_c, const float* att_ctx,
@@ -845,7 +691,7 @@ extern "C" int t2_decoder_step(t2_ctx* c, const float* prev_mel_prenet, const fl
                  mel_out && gate_out && att_h_out && att_c_out && att_ctx_out && w_out && w_cum_out && rnn_h_out && rnn_c_out && ws,
              T2_ERR_ARG, "t2_decoder_step: null argument");
   Arena ar(ws, ws_bytes);
-  return (use_v2() ? step2_impl : step_impl)(c, prev_mel_prenet, att_h, att_c, att_ctx, w, w_cum, rnn_h, rnn_c, memory, processed_memory,
+  return step2_impl(c, prev_mel_prenet, att_h, att_c, att_ctx, w, w_cum, rnn_h, rnn_c, memory, processed_memory,
                                              mask, controls, B, L, mel_out, gate_out, att_h_out, att_c_out, att_ctx_out, w_out,
                                              w_cum_out, rnn_h_out, rnn_c_out, ar, (cudaStream_t)stream);
 }
@@ -855,7 +701,7 @@ extern "C" int t2_prenet_fwd(t2_ctx* c, const float* x, const unsigned char* kee
   CHECK_CTX("t2_prenet_fwd");
   T2_REQUIRE(x && out && N > 0, T2_ERR_ARG, "t2_prenet_fwd: bad argument");
   (void)ws; (void)ws_bytes;
-  PrenetArgs pa{x, c->dw.W1, c->dw.W2, keep1, keep2, seed, c->cfg.dropout, N, c->M, c->P, 0, 0, 0, out, nullptr};
+  PrenetArgs pa{x, c->d2w.W1, c->d2w.W2, keep1, keep2, seed, c->cfg.dropout, N, c->M, c->P, 0, 0, 0, out, nullptr};
   prenet_rows_kernel<<<std::min((N + PN_ROWS - 1) / PN_ROWS, 148 * 4), 256, PN_ROWS * (c->M + c->P) * sizeof(float),
                        (cudaStream_t)stream>>>(pa);
   T2_CHECK_CUDA(cudaGetLastError());
@@ -910,8 +756,6 @@ extern "C" long long t2_workspace_bytes(const t2_ctx* cc, int B, int L, int T) {
   long long best = 0;
   { Arena a(nullptr, 0); encoder_impl(c, nullptr, nullptr, B, L, 0, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
   { Arena a(nullptr, 0); memory_impl(c, nullptr, nullptr, nullptr, B, L, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
-  { Arena a(nullptr, 0); decode_impl(c, true, nullptr, nullptr, nullptr, nullptr, nullptr, B, L, std::max(T, 1), nullptr, 0, nullptr, nullptr, 0,
-                                    nullptr, nullptr, nullptr, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
   { Arena a(nullptr, 0); decode2_impl(c, true, nullptr, nullptr, nullptr, nullptr, nullptr, B, L, std::max(T, 1), nullptr, 0, nullptr, nullptr, 0,
                                      nullptr, nullptr, nullptr, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
   { Arena a(nullptr, 0); postnet_impl(c, nullptr, std::max(T, 1), B, std::max(T, 1), 0, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }

@@ -1,43 +1,44 @@
-// Persistent autoregressive decoder kernel (one cooperative launch for the whole utterance
-// batch; grid = one CTA per SM).  Per frame it runs, separated by grid barriers:
-//   P1 attention LSTMCell     (model/decoder.py:70-75)
-//   P2 query projection       (model/attention.py:52)
-//   P3 location-sensitive attention: conv31 -> dense -> tanh energies -> masked softmax
-//      -> context, cumulative-weight update (model/attention.py:54-67, model/decoder.py:90)
-//   P4 decoder LSTMCell       (model/decoder.py:94-101)
-//   P5 mel / gate projection + stop logic (model/decoder.py:103-109, model/tacotron2.py:311-322)
-//   P6/P7 prenet layers on the emitted frame (model/tacotron2.py:85-92,324-325)
-// All arithmetic is fp32 FMA in this revision (exact-parity engine).
+// Persistent autoregressive decoder kernel.  One launch decodes the whole utterance
+// batch: 32 clusters x 4 CTAs (one CTA per SM), per frame
+//   P1 attention LSTMCell   gate GEMM on tcgen05 (TMA ring, split-K over the cluster, DSMEM reduce) + pointwise
+//   P2 query projection     (model/attention.py:52)
+//   P3 location-sensitive attention (model/attention.py:54-67, model/decoder.py:90)
+//   P4 decoder LSTMCell     same engine as P1 (model/decoder.py:94-101)
+//   P5 mel / gate projection + stop bookkeeping (model/decoder.py:103-109, model/tacotron2.py:311-322)
+//   P6/P7 prenet on the emitted frame (model/tacotron2.py:85-92,324-325)
+// separated by grid barriers.  Recurrent state never leaves the chip boundary it does not have to:
+// cell states live in shared memory, hidden states travel as bf16 (hi,lo) pairs for the next GEMM.
 #include "decoder.cuh"
 
 namespace {
 
-// ------------------------------------------------------------------------------------------
-// Grid barrier: monotonic arrival counter.  bar[0] = counter, bar[1] = abort flag.
-// Cooperative launch guarantees co-residency; the spin is bounded so a bug cannot hang the GPU.
 struct GridBar {
   unsigned* ctr;
   unsigned* abort_flag;
   unsigned nblocks;
   unsigned epoch;
-  __device__ bool sync() {  // returns false if the kernel must abort
+  // `fail` = this CTA hit a pipeline timeout: it raises the abort flag before arriving so every CTA leaves together.
+  // `wrote_x`: this phase stored GEMM operands with ordinary (generic-proxy) stores; they must be ordered before the
+  // TMA (async-proxy) reads of a later phase, hence the proxy fence on the writer side (the TMA producer thread
+  // issues the matching fence before its first load).
+  __device__ bool sync(bool fail, bool wrote_x) {
+    if (wrote_x) asm volatile("fence.proxy.async;" ::: "memory");
     __syncthreads();
     __shared__ int ok_s;
     if (threadIdx.x == 0) {
       ++epoch;
+      if (fail) atomicExch(abort_flag, 1u);
       __threadfence();
       atomicAdd(ctr, 1u);
       const unsigned target = epoch * nblocks;
       long long spins = 0;
-      int ok = 1;
       while (ld_acquire_u32(ctr) < target) {
-        if (++spins > (1ll << 26)) {
-          if (ld_acquire_u32(abort_flag) != 0u || spins > (1ll << 28)) { atomicExch(abort_flag, 1u); ok = 0; break; }
+        if (++spins > (1ll << 24)) {
+          if (ld_acquire_u32(abort_flag) != 0u || spins > (1ll << 27)) { atomicExch(abort_flag, 1u); break; }
         }
       }
-      if (ld_acquire_u32(abort_flag) != 0u) ok = 0;
+      ok_s = (ld_acquire_u32(abort_flag) == 0u);
       __threadfence();
-      ok_s = ok;
     }
     __syncthreads();
     return ok_s != 0;
@@ -45,202 +46,137 @@ struct GridBar {
 };
 
 // ------------------------------------------------------------------------------------------
-// Small dense phases: out[b][r] = sum_k W[r][k] * x[b][k], W row-major [rows][ldw], x row-major
-// [B][ldx] (mutable -> ld.global.cg).  One warp owns a 4x4 (rows x batch) tile, lanes split K in
-// float4 steps, butterfly reduction, then lane (i*4+j) applies the epilogue to output (r0+i, b0+j).
-template <typename Epi>
-__device__ __forceinline__ void warp_gemm_rm(const float* __restrict__ W, int ldw, int rows, const float* x, int ldx,
-                                             int B, int K, Epi epi) {
-  const int lane = threadIdx.x & 31;
-  const int gwarp = blockIdx.x * (DEC_THREADS / 32) + (threadIdx.x >> 5);
-  const int nwarps = gridDim.x * (DEC_THREADS / 32);
-  const int rt = (rows + 3) >> 2, bt = (B + 3) >> 2;
-  const int K4 = K >> 2;
-  for (int task = gwarp; task < rt * bt; task += nwarps) {
-    const int r0 = (task / bt) * 4, b0 = (task % bt) * 4;
-    float acc[4][4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-    const float* wp[4];
-    const float* xp[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      wp[i] = W + (size_t)min(r0 + i, rows - 1) * ldw;
-      xp[i] = x + (size_t)min(b0 + i, B - 1) * ldx;
-    }
-    for (int k4 = lane; k4 < K4; k4 += 32) {
-      float4 wv[4], xv[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        wv[i] = __ldg(reinterpret_cast<const float4*>(wp[i]) + k4);
-        xv[i] = __ldcg(reinterpret_cast<const float4*>(xp[i]) + k4);
-      }
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          acc[i][j] = fmaf(wv[i].x, xv[j].x, acc[i][j]);
-          acc[i][j] = fmaf(wv[i].y, xv[j].y, acc[i][j]);
-          acc[i][j] = fmaf(wv[i].z, xv[j].z, acc[i][j]);
-          acc[i][j] = fmaf(wv[i].w, xv[j].w, acc[i][j]);
-        }
-    }
-    float mine = 0.f;
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float s = warp_sum(acc[i][j]);
-        if (lane == i * 4 + j) mine = s;
-      }
-    if (lane < 16) {
-      const int r = r0 + (lane >> 2), b = b0 + (lane & 3);
-      if (r < rows && b < B) epi(r, b, mine);
-    }
-  }
-}
-
-// ------------------------------------------------------------------------------------------
-// LSTM gate tile: CTA `tile` owns 8 hidden units x 4 gates = 32 gate rows for all DEC_BP batch
-// slots.  gates[row][b] = sum_k Wp[tile][k][row] * x[k][b]; x is k-major and comes from up to
-// three row ranges (segments) so the prenet part can live in its own buffer.
-// 256 threads = 4 k-groups x (2 row-halves x 32 lanes); thread tile 4 rows x 8 batch.
-#define LT_KC 64
-#define LT_STAGES 3
-#define LT_STAGE_FLOATS (LT_KC * 32 + LT_KC * DEC_BP)
-
-struct XSeg { const float* ptr; int rows; };  // consecutive k-major row ranges forming x
-
-__device__ __forceinline__ const float* xrow(const XSeg* seg, int k) {
-  if (k < seg[0].rows) return seg[0].ptr + (size_t)k * DEC_BP;
-  k -= seg[0].rows;
-  return seg[1].ptr + (size_t)k * DEC_BP;
-}
-
-__device__ __forceinline__ void lt_fill(float* stage, const float* Wp_tile, const XSeg* seg, int k0) {
-  float* Ws = stage;                  // [KC][32]
-  float* xs = stage + LT_KC * 32;     // [KC][BP]
+// Small dense phases on CUDA cores: out[b][r] = sum_k W[r][k] x[b][k].  The 128 CTAs form a 16 x 8 grid of
+// (row group, batch group of 8); W rows and x rows are staged in shared memory (row stride K+4 floats:
+// conflict-free float4 reads), 128 outputs per CTA, two K-halves per output.  Returns this thread's output (if any);
+// the caller applies the phase-specific epilogue and must __syncthreads() before reusing the scratch.
+struct SmallOut { int r, b; float v; bool valid; };
+__device__ __forceinline__ SmallOut small_gemm(const float* __restrict__ W, int ldw, int rows, const float* x, int ldx, int B, int K,
+                                               float* scratch) {
+  SmallOut out{0, 0, 0.f, false};
   const int tid = threadIdx.x;
-  // W: KC*32 floats contiguous in the packed layout
-  const float* wsrc = Wp_tile + (size_t)k0 * 32;
-#pragma unroll
-  for (int i = 0; i < (LT_KC * 32 / 4) / DEC_THREADS; ++i) {
-    int idx = tid + i * DEC_THREADS;
-    cp_async16(Ws + idx * 4, wsrc + idx * 4);
+  const int rg = blockIdx.x >> 3, bg = blockIdx.x & 7;
+  const int rpc = (rows + 15) >> 4;           // rows per CTA (<= 16)
+  const int r0 = rg * rpc, b0 = bg * 8;
+  const int nr = max(0, min(rpc, rows - r0)), nb = max(0, min(8, B - b0));
+  if (blockIdx.x >= 128 || nr == 0 || nb == 0) return out;
+  const int ld = K + 4, K4 = K >> 2;
+  float* Ws = scratch;                        // [rpc][ld]
+  float* xs = scratch + rpc * ld;             // [8][ld]
+  float* red = xs + 8 * ld;                   // [128]
+#pragma unroll 1
+  for (int i = tid; i < (nr + nb) * K4; i += D2_THREADS) {
+    const int rr = i / K4, c = i - rr * K4;
+    const float* src = rr < nr ? W + (size_t)(r0 + rr) * ldw : x + (size_t)(b0 + rr - nr) * ldx;
+    float* dst = rr < nr ? Ws + rr * ld : xs + (rr - nr) * ld;
+    cp_async16(dst + c * 4, src + c * 4);
   }
-#pragma unroll
-  for (int i = 0; i < (LT_KC * DEC_BP / 4) / DEC_THREADS; ++i) {
-    int idx = tid + i * DEC_THREADS;  // float4 index
-    int k = idx / (DEC_BP / 4), c = idx % (DEC_BP / 4);
-    cp_async16(xs + k * DEC_BP + c * 4, xrow(seg, k0 + k) + c * 4);
-  }
-}
-
-// Result: red[4][32][BP] partial sums in shared memory (caller reduces over the 4 k-groups).
-__device__ void lstm_tile_gemm(const float* Wp_tile, const XSeg* seg, int KP, float* smem) {
-  float* red = smem;  // aliases the stages after the main loop (32 KB <= 3 stages)
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int kg = warp >> 1, wr = warp & 1;
-  const int tr = lane >> 3, tb = lane & 7;
-  const int row0 = wr * 16 + tr * 4, col0 = tb * 4;  // batch columns {col0..col0+3} and {32+col0..}
-  float acc[4][8];
-#pragma unroll
-  for (int i = 0; i < 4; ++i)
-#pragma unroll
-    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
-  const int nchunk = KP / LT_KC;
-#pragma unroll
-  for (int s = 0; s < LT_STAGES - 1; ++s) {
-    if (s < nchunk) lt_fill(smem + s * LT_STAGE_FLOATS, Wp_tile, seg, s * LT_KC);
-    cp_async_commit();
-  }
-  for (int c = 0; c < nchunk; ++c) {
-    cp_async_wait<LT_STAGES - 2>();
-    __syncthreads();
-    {
-      int nc = c + LT_STAGES - 1;
-      if (nc < nchunk) lt_fill(smem + (nc % LT_STAGES) * LT_STAGE_FLOATS, Wp_tile, seg, nc * LT_KC);
-      cp_async_commit();
-    }
-    const float* Ws = smem + (c % LT_STAGES) * LT_STAGE_FLOATS;
-    const float* xs = Ws + LT_KC * 32;
-#pragma unroll 4
-    for (int kk = 0; kk < LT_KC / 4; ++kk) {
-      const int k = kg * (LT_KC / 4) + kk;
-      const float4 w4 = *reinterpret_cast<const float4*>(Ws + k * 32 + row0);
-      const float4 xa = *reinterpret_cast<const float4*>(xs + k * DEC_BP + col0);
-      const float4 xb = *reinterpret_cast<const float4*>(xs + k * DEC_BP + 32 + col0);
-      const float wv[4] = {w4.x, w4.y, w4.z, w4.w};
-      const float xv[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(wv[i], xv[j], acc[i][j]);
-    }
-  }
+  cp_async_commit();
   cp_async_wait<0>();
   __syncthreads();
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    float* dst = red + ((size_t)kg * 32 + row0 + i) * DEC_BP + col0;
-    *reinterpret_cast<float4*>(dst) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
-    *reinterpret_cast<float4*>(dst + 32) = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
+  const int o = tid & 127, kh = tid >> 7;
+  const int r = o >> 3, b = o & 7;
+  float acc = 0.f;
+  if (r < nr && b < nb) {
+    const float4* wp = reinterpret_cast<const float4*>(Ws + r * ld);
+    const float4* xp = reinterpret_cast<const float4*>(xs + b * ld);
+    const int kbeg = kh * (K4 >> 1), kend = kh ? K4 : (K4 >> 1);
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll 4
+    for (int k = kbeg; k < kend; ++k) {
+      const float4 wv = wp[k], xv = xp[k];
+      a0 = fmaf(wv.x, xv.x, a0); a1 = fmaf(wv.y, xv.y, a1); a2 = fmaf(wv.z, xv.z, a2); a3 = fmaf(wv.w, xv.w, a3);
+    }
+    acc = (a0 + a1) + (a2 + a3);
   }
+  if (kh == 1) red[o] = acc;
   __syncthreads();
+  if (kh == 0 && r < nr && b < nb) { out.r = r0 + r; out.b = b0 + b; out.v = acc + red[o]; out.valid = true; }
+  return out;
 }
 
 // ------------------------------------------------------------------------------------------
-// LSTM pointwise on the reduced gate tile.  Thread handles (unit_in_tile, b) pairs.
-struct HDest {
-  float* km0; int km0_row;   // k-major destination [row][BP] (may be null)
-  float* km1; int km1_row;
-  float* rm;  int rm_ld, rm_col;  // row-major destination [b][ld]
-  float* rm2; int rm2_ld, rm2_col;
+// Shared-memory plan (bytes from the 1024-aligned base):
+//   [0, 3*48K)            TMA stage ring (also scratch for the CUDA-core phases, which never overlap it)
+//   part[128][68] f32     split-K partial accumulator (read by cluster peers)
+//   c_att[8][64], c_dec[8][64] f32   cell states of this CTA's 8 hidden units
+//   attention constants   conv_t[2*31*32] | dense[A*32] | v[A]
+//   barriers, tmem slot
+struct Smem {
+  uint8_t* stages;
+  float* part;
+  float* c_att;
+  float* c_dec;
+  float* conv_t;
+  float* dense;
+  float* v;
+  uint64_t* bars;
+  uint32_t* tmem_slot;
 };
 
-__device__ void lstm_pointwise(const float* red, const float* __restrict__ bias, int H, int tile, float* cbuf, int B,
-                               const HDest& hd, const unsigned char* keep, bool hidden_dropout, unsigned long long seed,
-                               unsigned long long rng_base) {
-  for (int idx = threadIdx.x; idx < 8 * DEC_BP; idx += DEC_THREADS) {
-    const int ul = idx / DEC_BP, b = idx % DEC_BP;
-    const int u = tile * 8 + ul;
-    float pre[4];
+__device__ __forceinline__ Smem carve(uint8_t* base, const D2Dims& d) {
+  Smem s;
+  s.stages = base;
+  uint8_t* p = base + D2_STAGES * TG_STAGE_BYTES;
+  s.part = reinterpret_cast<float*>(p);  p += TG_M * TG_PART_LD * 4;
+  s.c_att = reinterpret_cast<float*>(p); p += 8 * D2_BP * 4;
+  s.c_dec = reinterpret_cast<float*>(p); p += 8 * D2_BP * 4;
+  s.conv_t = reinterpret_cast<float*>(p); p += 2 * D2_LOC_K * D2_LOC_F * 4;
+  s.dense = reinterpret_cast<float*>(p); p += d.A * D2_LOC_F * 4;
+  s.v = reinterpret_cast<float*>(p);     p += d.A * 4;
+  s.bars = reinterpret_cast<uint64_t*>(p); p += (2 * D2_STAGES + 2) * 8;
+  s.tmem_slot = reinterpret_cast<uint32_t*>(p);
+  return s;
+}
+
+// ------------------------------------------------------------------------------------------
+// LSTM phase tail: split-K reduce over the cluster + gate nonlinearities for this CTA's 8 units.
+// Tile rows are packed so that rows [32*rank, 32*rank+32) = gates (i,f,g,o) x 8 units of CTA `rank`.
+struct HOut {
+  __nv_bfloat16* x0; int ld0, col0;   // bf16 (hi,lo) destination: element (b, col0+u) of [2][BP][ld0]; lo plane at +plane0
+  long long plane0;
+  __nv_bfloat16* x1; int ld1, col1;
+  long long plane1;
+  float* rm; int rm_ld, rm_col;       // fp32 row-major destination [b][rm_ld]
+};
+
+__device__ __forceinline__ void store_split(__nv_bfloat16* base, long long plane, int ld, int b, int col, float h) {
+  __nv_bfloat16 hi, lo;
+  tc::split_bf16(h, hi, lo);
+  base[(size_t)b * ld + col] = hi;
+  base[plane + (size_t)b * ld + col] = lo;
+}
+
+__device__ __forceinline__ void lstm_tail(const float* part, uint32_t rank, int unit0, const float* __restrict__ bias, int H,
+                                          float* cst, int B, const HOut& ho, const unsigned char* keep, bool hidden_dropout,
+                                          unsigned long long seed, unsigned long long rng_base) {
+  const int ul = threadIdx.x >> 5, bp = threadIdx.x & 31;
+  const int u = unit0 + ul;
+  float2 pre[4];
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
-      const int row = g * 8 + ul;
-      float s = red[(0 * 32 + row) * DEC_BP + b] + red[(1 * 32 + row) * DEC_BP + b];
-      s += red[(2 * 32 + row) * DEC_BP + b] + red[(3 * 32 + row) * DEC_BP + b];
-      pre[g] = s + __ldg(bias + g * H + u);
+  for (int g = 0; g < 4; ++g) {
+    pre[g] = tg::reduce4(part, 32 * (int)rank + g * 8 + ul, 2 * bp);
+    const float bv = __ldg(bias + g * H + u);
+    pre[g].x += bv; pre[g].y += bv;
+  }
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int b = 2 * bp + j;
+    if (b >= B) continue;
+    const float pi = j ? pre[0].y : pre[0].x, pf = j ? pre[1].y : pre[1].x;
+    const float pg = j ? pre[2].y : pre[2].x, po = j ? pre[3].y : pre[3].x;
+    const float c = sigmoid_fast(pf) * cst[ul * D2_BP + b] + sigmoid_fast(pi) * tanh_fast(pg);
+    float h = sigmoid_fast(po) * tanh_fast(c);
+    cst[ul * D2_BP + b] = c;
+    if (hidden_dropout) {  // nn.Dropout(0.1), train only (model/decoder.py:75,101)
+      const bool k = keep ? (keep[(size_t)b * H + u] != 0) : rng_keep(seed, rng_base + (unsigned long long)b * H + u, 0.1f);
+      h = k ? h * (1.0f / 0.9f) : 0.f;
     }
-    float h = 0.f, c = 0.f;
-    if (b < B) {
-      const float c_old = cbuf[(size_t)u * DEC_BP + b];
-      c = sigmoidf_(pre[1]) * c_old + sigmoidf_(pre[0]) * tanhf(pre[2]);
-      h = sigmoidf_(pre[3]) * tanhf(c);
-      if (hidden_dropout) {  // nn.Dropout(0.1), train only (model/decoder.py:75,101)
-        bool k = keep ? (keep[(size_t)b * H + u] != 0) : rng_keep(seed, rng_base + (unsigned long long)b * H + u, 0.1f);
-        h = k ? h * (1.0f / 0.9f) : 0.f;
-      }
-    }
-    cbuf[(size_t)u * DEC_BP + b] = c;
-    if (hd.km0) hd.km0[(size_t)(hd.km0_row + u) * DEC_BP + b] = h;
-    if (hd.km1) hd.km1[(size_t)(hd.km1_row + u) * DEC_BP + b] = h;
-    if (b < B) {
-      if (hd.rm) hd.rm[(size_t)b * hd.rm_ld + hd.rm_col + u] = h;
-      if (hd.rm2) hd.rm2[(size_t)b * hd.rm2_ld + hd.rm2_col + u] = h;
-    }
+    if (ho.x0) store_split(ho.x0, ho.plane0, ho.ld0, b, ho.col0 + u, h);
+    if (ho.x1) store_split(ho.x1, ho.plane1, ho.ld1, b, ho.col1 + u, h);
+    if (ho.rm) ho.rm[(size_t)b * ho.rm_ld + ho.rm_col + u] = h;
   }
 }
-
-// ------------------------------------------------------------------------------------------
-// Attention for one (batch element, column split).  Shared-memory plan (floats):
-//   att_w: conv[32*2*31] | dense[A*32] | v[A]          (loaded once per launch)
-//   att_s: q[A] | wp[L+30] | wc[L+30] | e[L] | red[64] | cred[4*colsmax]
-struct AttSmem {
-  float *conv, *dense, *v, *q, *wp, *wc, *e, *red, *cred;
-};
 
 __device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -250,278 +186,416 @@ __device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) 
   __syncthreads();
   float r = red[0];
 #pragma unroll
-  for (int i = 1; i < DEC_THREADS / 32; ++i) r = is_max ? fmaxf(r, red[i]) : r + red[i];
+  for (int i = 1; i < D2_THREADS / 32; ++i) r = is_max ? fmaxf(r, red[i]) : r + red[i];
   return r;
 }
 
-__device__ void attention_task(const DecDims& d, const DecState& s, const DecIO& io, const AttSmem& sm, int b, int split,
-                               int nsplit, int cur, int t_out) {
-  const int tid = threadIdx.x, L = d.L, A = d.A, EF = d.EF;
+// ------------------------------------------------------------------------------------------
+// Attention for batch element b, part `part` of `S` (the S CTAs of one b sit in the same cluster):
+// each part computes the energies of its L-slice, the slices are exchanged through DSMEM, every part
+// normalises the full row and reduces its slice of the context columns.
+// Scratch (floats, in the idle TMA ring): q[A] | wp[Lc+32] | wc[Lc+32] | fs[Lc][36] | e_slice[Lc] |
+//                                         e_full[L] | red[64] | cred[4*cols]
+#define ATT_MARK(slot) do { if (blockIdx.x == 0 && threadIdx.x == 0 && s.prof) { const long long now_ = clock64(); s.prof[slot] += (unsigned long long)(now_ - *prof_last); *prof_last = now_; } } while (0)
+__device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& io, const Smem& sm, float* scratch, bool active,
+                                int b, int part, int S, int cur, int t_out, long long* prof_last) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int L = d.L, A = d.A, EF = d.EF;
+  const int Lc = (L + S - 1) / S, l0 = part * Lc, l1 = min(L, l0 + Lc), nl = max(0, l1 - l0);
   const int nxt = cur ^ 1;
-  const float* wprev = s.w_prev + ((size_t)cur * DEC_BP + b) * L;
-  const float* wcum = s.w_cum + ((size_t)cur * DEC_BP + b) * L;
-  for (int i = tid; i < A; i += DEC_THREADS) sm.q[i] = ld_cg(s.q + (size_t)b * A + i);
-  for (int i = tid; i < L + 30; i += DEC_THREADS) {
-    const int l = i - 15;
-    const bool in = (l >= 0 && l < L);
-    sm.wp[i] = in ? ld_cg(wprev + l) : 0.f;
-    sm.wc[i] = in ? ld_cg(wcum + l) : 0.f;
-  }
-  __syncthreads();
-  const unsigned char* mk = io.mask + (size_t)b * L;
-  // energies
-  for (int l = tid; l < L; l += DEC_THREADS) {
-    float e = -INFINITY;
-    if (mk[l] == 0) {
-      float f[DEC_LOC_F];
+  float* q_s = scratch;
+  float* wp = q_s + A;                            // previous / cumulative weights with a 15-tap halo
+  float* wc = wp + ((Lc + 35) & ~3);
+  float* fs = wc + ((Lc + 35) & ~3);            // [Lc][36] conv features (row stride 36: conflict-free float4 rows)
+  float* e_slice = fs + (size_t)Lc * 36;
+  float* e_full = e_slice + ((Lc + 3) & ~3);
+  float* red = e_full + ((L + 3) & ~3);
+  float* cred = scratch + (((red + 64) - scratch + 3) & ~3);
+  if (active) {
+    const float* wprev = s.w_prev + ((size_t)cur * D2_BP + b) * L;
+    const float* wcum = s.w_cum + ((size_t)cur * D2_BP + b) * L;
+#pragma unroll 1
+    for (int i = tid; i < A; i += D2_THREADS) q_s[i] = ld_cg(s.q + (size_t)b * A + i);
+#pragma unroll 1
+    for (int i = tid; i < nl + 30; i += D2_THREADS) {
+      const int l = l0 + i - 15;
+      const bool in = (l >= 0 && l < L);
+      wp[i] = in ? ld_cg(wprev + l) : 0.f;
+      wc[i] = in ? ld_cg(wcum + l) : 0.f;
+    }
+    __syncthreads();
+    // location conv (model/attention.py:54): warp task = (32 positions, 8 filters); lane = position
+    {
+      const int nchunk = (nl + 31) >> 5;
+#pragma unroll 1
+      for (int task = warp; task < nchunk * 4; task += D2_THREADS / 32) {
+        const int li = (task >> 2) * 32 + lane, fg = task & 3;
+        float acc[8];
 #pragma unroll
-      for (int i = 0; i < DEC_LOC_F; ++i) f[i] = 0.f;
-      for (int j = 0; j < DEC_LOC_K; ++j) {
-        const float a0 = sm.wp[l + j], a1 = sm.wc[l + j];
-#pragma unroll
-        for (int i = 0; i < DEC_LOC_F; ++i) {
-          f[i] = fmaf(sm.conv[(i * 2 + 0) * DEC_LOC_K + j], a0, f[i]);
-          f[i] = fmaf(sm.conv[(i * 2 + 1) * DEC_LOC_K + j], a1, f[i]);
+        for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+        const int lw = min(li, nl - 1);
+#pragma unroll 1
+        for (int j = 0; j < D2_LOC_K; ++j) {
+          const float a0 = wp[lw + j], a1 = wc[lw + j];
+          const float4* w0 = reinterpret_cast<const float4*>(sm.conv_t + (0 * D2_LOC_K + j) * D2_LOC_F + fg * 8);
+          const float4* w1 = reinterpret_cast<const float4*>(sm.conv_t + (1 * D2_LOC_K + j) * D2_LOC_F + fg * 8);
+          const float4 p0 = w0[0], p1 = w0[1], r0 = w1[0], r1 = w1[1];
+          acc[0] = fmaf(p0.x, a0, acc[0]); acc[1] = fmaf(p0.y, a0, acc[1]); acc[2] = fmaf(p0.z, a0, acc[2]); acc[3] = fmaf(p0.w, a0, acc[3]);
+          acc[4] = fmaf(p1.x, a0, acc[4]); acc[5] = fmaf(p1.y, a0, acc[5]); acc[6] = fmaf(p1.z, a0, acc[6]); acc[7] = fmaf(p1.w, a0, acc[7]);
+          acc[0] = fmaf(r0.x, a1, acc[0]); acc[1] = fmaf(r0.y, a1, acc[1]); acc[2] = fmaf(r0.z, a1, acc[2]); acc[3] = fmaf(r0.w, a1, acc[3]);
+          acc[4] = fmaf(r1.x, a1, acc[4]); acc[5] = fmaf(r1.y, a1, acc[5]); acc[6] = fmaf(r1.z, a1, acc[6]); acc[7] = fmaf(r1.w, a1, acc[7]);
+        }
+        if (li < nl) {
+          float4* dst = reinterpret_cast<float4*>(fs + (size_t)li * 36 + fg * 8);
+          dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+          dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
         }
       }
-      const float* pm = io.pmem + ((size_t)b * L + l) * A;
-      e = 0.f;
-      for (int a = 0; a < A; a += 4) {
-        const float4 p4 = __ldg(reinterpret_cast<const float4*>(pm + a));
-        const float pv[4] = {p4.x, p4.y, p4.z, p4.w};
+    }
+    __syncthreads();
+    ATT_MARK(10);
+    // location dense + tanh energies (model/attention.py:55-62): warp task = 4 positions; lane = 4 attention dims.
+    // acc[l][a] = sum_f fs[l][f] * Wd^T[f][a] on a 4x4 register tile, then e[l] = sum_a v[a] tanh(q[a] + acc + pm[l][a]).
+    {
+      const unsigned char* mk = io.mask + (size_t)b * L;
+      const int a4 = lane * 4;
+      const bool lane_on = a4 < A;
+      const int ac = lane_on ? a4 : 0;
+      const float4 q4 = *reinterpret_cast<const float4*>(q_s + ac);
+      const float4 v4 = *reinterpret_cast<const float4*>(sm.v + ac);
+      const int ntile = (nl + 3) >> 2;
+#pragma unroll 1
+      for (int tl = warp; tl < ntile; tl += D2_THREADS / 32) {
+        const int lt = tl * 4;
+        float4 pm4[4];
 #pragma unroll
-        for (int aa = 0; aa < 4; ++aa) {
-          const float4* dr = reinterpret_cast<const float4*>(sm.dense + (a + aa) * DEC_LOC_F);
-          float loc = 0.f;
+        for (int l = 0; l < 4; ++l) {
+          const int lp = min(lt + l, nl - 1);
+          pm4[l] = __ldg(reinterpret_cast<const float4*>(io.pmem + ((size_t)b * L + l0 + lp) * A + ac));
+        }
+        float acc[4][4];
 #pragma unroll
-          for (int i = 0; i < DEC_LOC_F / 4; ++i) {
-            const float4 w4 = dr[i];
-            loc = fmaf(w4.x, f[4 * i + 0], loc);
-            loc = fmaf(w4.y, f[4 * i + 1], loc);
-            loc = fmaf(w4.z, f[4 * i + 2], loc);
-            loc = fmaf(w4.w, f[4 * i + 3], loc);
+        for (int l = 0; l < 4; ++l)
+#pragma unroll
+          for (int a = 0; a < 4; ++a) acc[l][a] = 0.f;
+#pragma unroll 2
+        for (int f4 = 0; f4 < D2_LOC_F / 4; ++f4) {
+          float4 fv[4];
+#pragma unroll
+          for (int l = 0; l < 4; ++l) fv[l] = *reinterpret_cast<const float4*>(fs + (size_t)min(lt + l, nl - 1) * 36 + f4 * 4);
+#pragma unroll
+          for (int ff = 0; ff < 4; ++ff) {
+            const float4 wv = *reinterpret_cast<const float4*>(sm.dense + (f4 * 4 + ff) * A + ac);
+#pragma unroll
+            for (int l = 0; l < 4; ++l) {
+              const float fl = ff == 0 ? fv[l].x : (ff == 1 ? fv[l].y : (ff == 2 ? fv[l].z : fv[l].w));
+              acc[l][0] = fmaf(fl, wv.x, acc[l][0]); acc[l][1] = fmaf(fl, wv.y, acc[l][1]);
+              acc[l][2] = fmaf(fl, wv.z, acc[l][2]); acc[l][3] = fmaf(fl, wv.w, acc[l][3]);
+            }
           }
-          e = fmaf(sm.v[a + aa], tanhf(sm.q[a + aa] + loc + pv[aa]), e);
+        }
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+          float e = v4.x * tanh_fast(q4.x + acc[l][0] + pm4[l].x);
+          e = fmaf(v4.y, tanh_fast(q4.y + acc[l][1] + pm4[l].y), e);
+          e = fmaf(v4.z, tanh_fast(q4.z + acc[l][2] + pm4[l].z), e);
+          e = fmaf(v4.w, tanh_fast(q4.w + acc[l][3] + pm4[l].w), e);
+          e = warp_sum(lane_on ? e : 0.f);
+          if (lane == 0 && lt + l < nl) e_slice[lt + l] = mk[l0 + lt + l] ? -INFINITY : e;  // masked_fill (model/attention.py:63)
         }
       }
     }
-    sm.e[l] = e;
   }
-  __syncthreads();
-  // masked softmax over L (model/attention.py:63-65)
-  float mx = -INFINITY;
-  for (int l = tid; l < L; l += DEC_THREADS) mx = fmaxf(mx, sm.e[l]);
-  mx = block_reduce(mx, sm.red, true);
-  float sum = 0.f;
-  for (int l = tid; l < L; l += DEC_THREADS) {
-    const float p = expf(sm.e[l] - mx);
-    sm.e[l] = p;
-    sum += p;
-  }
-  sum = block_reduce(sum, sm.red + 32, false);
-  const float inv = 1.0f / sum;
-  for (int l = tid; l < L; l += DEC_THREADS) {
-    const float w = sm.e[l] * inv;
-    sm.e[l] = w;
-    if (split == 0) {
-      s.w_prev[((size_t)nxt * DEC_BP + b) * L + l] = w;
-      s.w_cum[((size_t)nxt * DEC_BP + b) * L + l] = sm.wc[l + 15] + w;  // model/decoder.py:90
-      io.aligns[((size_t)b * io.Tmax + t_out) * L + l] = w;
+  ATT_MARK(11);
+  tc::cluster_sync();  // energy slices visible to the peers of this batch element
+  ATT_MARK(12);
+  if (active) {
+    // gather the full energy row from the S parts (cluster ranks base..base+S-1)
+    const uint32_t my_rank = tc::cluster_ctarank();
+    const uint32_t base_rank = my_rank - (uint32_t)part;
+    const uint32_t ea = tc::smem_u32(e_slice);
+#pragma unroll 1
+    for (int l = tid; l < L; l += D2_THREADS) {
+      const int pr = l / Lc, li = l - pr * Lc;
+      float v;
+      asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(tc::mapa(ea + 4u * (uint32_t)li, base_rank + (uint32_t)pr)) : "memory");
+      e_full[l] = v;
     }
-  }
-  __syncthreads();
-  // context columns [c0, c1) of this split (model/attention.py:66-67)
-  const int cols_per = ((EF + nsplit - 1) / nsplit + 3) & ~3;
-  const int c0 = split * cols_per, c1 = min(EF, c0 + cols_per);
-  const int nq = (c1 - c0 + 3) >> 2;  // float4 columns
-  const float* mem = io.memory + (size_t)b * L * EF;
-  const int lg = tid >> 6, cq0 = tid & 63;
-  for (int cq = cq0; cq < nq; cq += 64) {
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int l = lg; l < L; l += 4) {
-      const float w = sm.e[l];
-      if (w != 0.f) {
-        const float4 m4 = __ldg(reinterpret_cast<const float4*>(mem + (size_t)l * EF + c0) + cq);
+    __syncthreads();
+    float mx = -INFINITY;
+#pragma unroll 1
+    for (int l = tid; l < L; l += D2_THREADS) mx = fmaxf(mx, e_full[l]);
+    mx = block_reduce(mx, red, true);
+    float sum = 0.f;
+#pragma unroll 1
+    for (int l = tid; l < L; l += D2_THREADS) {
+      const float p = expf(e_full[l] - mx);
+      e_full[l] = p;
+      sum += p;
+    }
+    sum = block_reduce(sum, red + 32, false);
+    const float inv = 1.0f / sum;
+#pragma unroll 1
+    for (int l = tid; l < L; l += D2_THREADS) {
+      const float w = e_full[l] * inv;
+      e_full[l] = w;
+      if (l >= l0 && l < l1) {  // each part publishes its own slice
+        s.w_prev[((size_t)nxt * D2_BP + b) * L + l] = w;
+        s.w_cum[((size_t)nxt * D2_BP + b) * L + l] = wc[l - l0 + 15] + w;  // model/decoder.py:90
+        io.aligns[((size_t)b * io.Tmax + t_out) * L + l] = w;
+      }
+    }
+    __syncthreads();
+    ATT_MARK(13);
+    // context columns of this part (model/attention.py:66-67)
+    const int cols_per = ((EF + S - 1) / S + 3) & ~3;
+    const int c0 = part * cols_per, c1 = min(EF, c0 + cols_per);
+    const int nq = max(0, (c1 - c0 + 3) >> 2);
+    const float* mem = io.memory + (size_t)b * L * EF;
+    const int lg = tid >> 6, cq0 = tid & 63;
+    const unsigned char* mk2 = io.mask + (size_t)b * L;
+    int Leff = 0;  // positions beyond the last unmasked one carry weight exactly 0 (softmax of -inf): skip them
+#pragma unroll 1
+    for (int l = tid; l < L; l += D2_THREADS) if (mk2[l] == 0) Leff = max(Leff, l + 1);
+    Leff = (int)block_reduce((float)Leff, red, true);
+#pragma unroll 1
+    for (int cq = cq0; cq < nq; cq += 64) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4* mp = reinterpret_cast<const float4*>(mem + c0) + cq;
+      const size_t rs = (size_t)EF / 4;  // row stride in float4
+      int l = lg;
+      for (; l + 28 < Leff; l += 32) {  // 8 independent 16-byte loads in flight per thread
+        float4 m[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) m[u] = __ldg(mp + (size_t)(l + 4 * u) * rs);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const float w = e_full[l + 4 * u];
+          acc.x = fmaf(w, m[u].x, acc.x); acc.y = fmaf(w, m[u].y, acc.y);
+          acc.z = fmaf(w, m[u].z, acc.z); acc.w = fmaf(w, m[u].w, acc.w);
+        }
+      }
+      for (; l < Leff; l += 4) {
+        const float4 m4 = __ldg(mp + (size_t)l * rs);
+        const float w = e_full[l];
         acc.x = fmaf(w, m4.x, acc.x); acc.y = fmaf(w, m4.y, acc.y);
         acc.z = fmaf(w, m4.z, acc.z); acc.w = fmaf(w, m4.w, acc.w);
       }
+      *reinterpret_cast<float4*>(cred + (size_t)lg * cols_per + cq * 4) = acc;
     }
-    *reinterpret_cast<float4*>(sm.cred + ((size_t)lg * cols_per) + cq * 4) = acc;
+    __syncthreads();
+    const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
+    __nv_bfloat16* xa = s.xatt + (size_t)nxt * 2 * pa;   // next frame's attention-LSTM input
+    __nv_bfloat16* xd = s.xdec + (size_t)cur * 2 * pd;   // this frame's decoder-LSTM input
+#pragma unroll 1
+    for (int c = tid; c < c1 - c0; c += D2_THREADS) {
+      const float v = cred[c] + cred[cols_per + c] + cred[2 * cols_per + c] + cred[3 * cols_per + c];
+      const int col = c0 + c;
+      store_split(xa, pa, d.KattP, b, d.P + col, v);
+      store_split(xd, pd, d.KdecP, b, d.H + col, v);
+      s.projin[(size_t)b * d.KprojP + d.R + col] = v;
+    }
   }
-  __syncthreads();
-  for (int c = tid; c < c1 - c0; c += DEC_THREADS) {
-    const float v = sm.cred[c] + sm.cred[cols_per + c] + sm.cred[2 * cols_per + c] + sm.cred[3 * cols_per + c];
-    const int col = c0 + c;
-    s.xatt[nxt][(size_t)col * DEC_BP + b] = v;             // next frame's attention-LSTM input
-    s.xdec[cur][(size_t)(d.H + col) * DEC_BP + b] = v;     // this frame's decoder-LSTM input
-    s.projin[(size_t)b * d.KprojP + d.R + col] = v;        // this frame's projection input
-  }
-  __syncthreads();
+  ATT_MARK(14);
+  tc::cluster_sync();  // peers are done reading this CTA's energy slice before the scratch is reused
 }
 
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(DEC_THREADS, 1)
-decoder_persistent_kernel(DecDims d, DecWeights w, DecState s, DecIO io) {
-  extern __shared__ __align__(16) float smem[];
-  float* gemm_smem = smem;                                  // LT_STAGES * LT_STAGE_FLOATS
-  AttSmem sm;
-  float* p = smem + LT_STAGES * LT_STAGE_FLOATS;
-  sm.conv = p;  p += DEC_LOC_F * 2 * DEC_LOC_K;
-  sm.dense = p; p += d.A * DEC_LOC_F;
-  sm.v = p;     p += d.A;
-  sm.q = p;     p += d.A;
-  sm.wp = p;    p += d.L + 30 + 2;
-  sm.wc = p;    p += d.L + 30 + 2;
-  sm.e = p;     p += d.L + 4;
-  sm.red = p;   p += 64;
-  p = smem + (((p - smem) + 3) & ~3);
-  sm.cred = p;
+enum { PH_ATT_LSTM = 0, PH_QUERY, PH_ATTN, PH_DEC_LSTM, PH_PROJ, PH_PRE1, PH_PRE2, PH_COUNT };
 
+__global__ void __launch_bounds__(D2_THREADS, 1)
+decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weights w, D2State s, D2IO io) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // keep the pointer's shared-memory provenance (no integer round trip) so loads/stores compile to LDS/STS
+  uint8_t* base = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+  const Smem sm = carve(base, d);
+  float* scratch = reinterpret_cast<float*>(base);
   const int tid = threadIdx.x;
-  for (int i = tid; i < DEC_LOC_F * 2 * DEC_LOC_K; i += DEC_THREADS) sm.conv[i] = w.loc_conv[i];
-  for (int i = tid; i < d.A * DEC_LOC_F; i += DEC_THREADS) sm.dense[i] = w.loc_dense[i];
-  for (int i = tid; i < d.A; i += DEC_THREADS) sm.v[i] = w.v[i];
-  __syncthreads();
+  const uint32_t rank = tc::cluster_ctarank();
+  const int tile = blockIdx.x / D2_CLUSTER;       // 128-row gate tile = 32 hidden units
+  const int unit0 = tile * 32 + (int)rank * 8;    // this CTA's 8 hidden units (both LSTMs)
+  const int B = d.B;
+
+  if (tid == 0) {
+    tc::prefetch_tmap(&maps.w_att); tc::prefetch_tmap(&maps.w_dec); tc::prefetch_tmap(&maps.x_att);
+    tc::prefetch_tmap(&maps.x_att_rest); tc::prefetch_tmap(&maps.x_dec); tc::prefetch_tmap(&maps.tf_pre);
+  }
+#pragma unroll 1
+  for (int i = tid; i < 2 * D2_LOC_K * D2_LOC_F; i += D2_THREADS) sm.conv_t[i] = w.loc_conv_t[i];
+#pragma unroll 1
+  for (int i = tid; i < d.A * D2_LOC_F; i += D2_THREADS) sm.dense[i] = w.loc_dense[i];
+#pragma unroll 1
+  for (int i = tid; i < d.A; i += D2_THREADS) sm.v[i] = w.v[i];
+#pragma unroll 1
+  for (int i = tid; i < 8 * D2_BP; i += D2_THREADS) {
+    sm.c_att[i] = s.att_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP];
+    sm.c_dec[i] = s.rnn_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP];
+  }
+  tg::Pipe pipe;
+  tg::pipe_init(pipe, sm.bars, sm.stages, D2_STAGES, d.npass, sm.tmem_slot);
+  tc::cluster_sync();
 
   GridBar bar{s.barrier, s.barrier + 1, gridDim.x, 0u};
   long long prof_last = clock64();
   auto prof_mark = [&](int slot) {
-    if (blockIdx.x == 0 && threadIdx.x == 0 && s.prof) { const long long now = clock64(); s.prof[slot] += (unsigned long long)(now - prof_last); prof_last = now; }
+    if (blockIdx.x == 0 && tid == 0 && s.prof) { const long long now = clock64(); s.prof[slot] += (unsigned long long)(now - prof_last); prof_last = now; }
   };
-  const int B = d.B;
-  const int n_att_tiles = d.H / 8, n_dec_tiles = d.R / 8;
-  const int nsplit = max(1, min((int)gridDim.x / B, d.EF / 64));
+  // attention work split: S CTAs (same cluster) per batch element
+  const int S = (B * 4 <= (int)gridDim.x) ? 4 : ((B * 2 <= (int)gridDim.x) ? 2 : 1);
+  const int att_b = blockIdx.x / S, att_part = blockIdx.x % S;
+  const bool att_active = att_b < B;
+  const int nkb_att = d.KattP / TG_BK, nkb_dec = d.KdecP / TG_BK;
+  const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
   const float pscale = 1.0f / (1.0f - d.p_prenet);
+  const int nphase = io.teacher_forcing ? PH_PROJ + 1 : PH_COUNT;
   int frames = 0;
-  bool alive = true;
+  bool alive = true, fail = false, stop = false;
 
-  for (int t = 0; t < io.n_steps && alive; ++t) {
+#pragma unroll 1
+  for (int t = 0; t < io.n_steps && alive && !stop; ++t) {
     const int cur = t & 1, nxt = cur ^ 1;
-    const int tg = io.t0 + t;  // global frame index (mask / output row)
-
-    // ---- P1: attention LSTMCell -------------------------------------------------------
-    for (int tile = blockIdx.x; tile < n_att_tiles; tile += gridDim.x) {
-      XSeg seg[2];
-      seg[0].ptr = io.teacher_forcing ? io.tf_prenet + (size_t)tg * d.P * DEC_BP : s.xpre[cur];
-      seg[0].rows = d.P;
-      seg[1].ptr = s.xatt[cur];
-      seg[1].rows = d.KattP - d.P;
-      lstm_tile_gemm(w.Watt_p + (size_t)tile * d.KattP * 32, seg, d.KattP, gemm_smem);
-      HDest hd{s.xatt[nxt], d.EF, s.xdec[cur], 0, s.att_h_rm, d.H, 0, nullptr, 0, 0};
-      lstm_pointwise(gemm_smem, w.batt, d.H, tile, s.att_c, B, hd,
-                     io.att_keep ? io.att_keep + (size_t)tg * B * d.H : nullptr, io.hidden_dropout != 0, io.seed,
-                     (1ull << 40) + (unsigned long long)tg * B * d.H);
-      __syncthreads();
-    }
-    if (!(alive = bar.sync())) break;
-    prof_mark(0);
-
-    // ---- P2: query projection (model/attention.py:52) ---------------------------------
-    warp_gemm_rm(w.Wq, d.H, d.A, s.att_h_rm, d.H, B, d.H,
-                 [&](int r, int b, float v) { s.q[(size_t)b * d.A + r] = v; });
-    if (!(alive = bar.sync())) break;
-    prof_mark(1);
-
-    // ---- P3: location-sensitive attention ---------------------------------------------
-    for (int task = blockIdx.x; task < B * nsplit; task += gridDim.x)
-      attention_task(d, s, io, sm, task / nsplit, task % nsplit, nsplit, cur, tg);
-    if (!(alive = bar.sync())) break;
-    prof_mark(2);
-
-    // ---- P4: decoder LSTMCell ----------------------------------------------------------
-    for (int tile = blockIdx.x; tile < n_dec_tiles; tile += gridDim.x) {
-      XSeg seg[2];
-      seg[0].ptr = s.xdec[cur];
-      seg[0].rows = d.KdecP;
-      seg[1].ptr = s.xdec[cur];
-      seg[1].rows = 0;
-      lstm_tile_gemm(w.Wdec_p + (size_t)tile * d.KdecP * 32, seg, d.KdecP, gemm_smem);
-      HDest hd{s.xdec[nxt], d.H + d.EF + d.C, nullptr, 0, s.projin, d.KprojP, 0,
-               io.projin_all ? io.projin_all + (size_t)tg * B * d.KprojP : nullptr, d.KprojP, 0};
-      lstm_pointwise(gemm_smem, w.bdec, d.R, tile, s.rnn_c, B, hd,
-                     io.rnn_keep ? io.rnn_keep + (size_t)tg * B * d.R : nullptr, io.hidden_dropout != 0, io.seed,
-                     (2ull << 40) + (unsigned long long)tg * B * d.R);
-      __syncthreads();
-    }
-    if (!(alive = bar.sync())) break;
-    prof_mark(3);
-
-    // ---- P5: mel / gate projection + stop bookkeeping ----------------------------------
-    warp_gemm_rm(w.Wproj, d.KprojP, d.M + 1, s.projin, d.KprojP, B, d.KprojP, [&](int r, int b, float v) {
-      v += __ldg(w.bproj + r);
-      if (r < d.M) {
-        io.mels[((size_t)b * io.Tmax + tg) * d.M + r] = v;
-        s.mel_cur[(size_t)b * d.M + r] = v;
+    const int tg_ = io.t0 + t;
+#pragma unroll 1
+    for (int ph = 0; ph < nphase && alive && !stop; ++ph) {
+      bool wrote_x = false;  // this phase stored operands that a later phase reads through TMA
+      if (ph == PH_ATT_LSTM || ph == PH_DEC_LSTM) {
+        // ---- attention / decoder LSTMCell (model/decoder.py:70-75, 94-101): gate GEMM + split-K reduce + pointwise
+        const bool att = ph == PH_ATT_LSTM;
+        tg::XSrc xs;
+        if (att && io.teacher_forcing) xs = tg::XSrc{&maps.tf_pre, tg_ * 2, &maps.x_att_rest, cur * 2, d.P / TG_BK};
+        else if (att) xs = tg::XSrc{&maps.x_att, cur * 2, &maps.x_att, cur * 2, nkb_att};
+        else xs = tg::XSrc{&maps.x_dec, cur * 2, &maps.x_dec, cur * 2, nkb_dec};
+        const int nkb = att ? nkb_att : nkb_dec;
+        const uint32_t dcol = att ? 0u : 64u;
+        if (!tg::gemm(pipe, att ? &maps.w_att : &maps.w_dec, tile * TG_M, nkb, xs, (int)rank, nkb, D2_CLUSTER, dcol)) fail = true;
+        prof_mark(att ? 8 : 9);
+        tg::accum_to_smem(pipe, dcol, sm.part);
+        tc::cluster_sync();
+        HOut ho;
+        if (att) ho = HOut{s.xatt + (size_t)nxt * 2 * pa, d.KattP, d.P + d.EF, pa, s.xdec + (size_t)cur * 2 * pd, d.KdecP, 0, pd, s.att_h_rm, d.H, 0};
+        else ho = HOut{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, s.projin, d.KprojP, 0};
+        const unsigned char* keep = att ? io.att_keep : io.rnn_keep;
+        lstm_tail(sm.part, rank, unit0, att ? w.batt : w.bdec, d.H, att ? sm.c_att : sm.c_dec, B, ho,
+                  keep ? keep + (size_t)tg_ * B * d.H : nullptr, io.hidden_dropout != 0, io.seed,
+                  ((att ? 1ull : 2ull) << 40) + (unsigned long long)tg_ * B * d.H);
+        wrote_x = true;
+      } else if (ph == PH_ATTN) {
+        // ---- location-sensitive attention (model/attention.py:54-67, model/decoder.py:90)
+        attention_phase(d, s, io, sm, scratch, att_active, att_b, att_part, S, cur, tg_, &prof_last);
+        wrote_x = true;
       } else {
-        io.gates[(size_t)b * io.Tmax + tg] = v;
-        if (io.stop_enabled) {  // model/tacotron2.py:319-320
-          if (v < 0.0f) s.done[b] = 1;
-          if (v >= 0.0f) s.lengths[b] += 1;
+        // ---- small dense phases: query (model/attention.py:52), mel/gate projection (model/decoder.py:103-109),
+        //      prenet layers on the emitted frame (model/tacotron2.py:85-92,324-325)
+        const float* Wm; const float* xin; int ldw, rows, ldx, K;
+        if (ph == PH_QUERY)     { Wm = w.Wq;    ldw = d.H;      rows = d.A;     xin = s.att_h_rm; ldx = d.H;      K = d.H; }
+        else if (ph == PH_PROJ) { Wm = w.Wproj; ldw = d.KprojP; rows = d.M + 1; xin = s.projin;   ldx = d.KprojP; K = d.KprojP; }
+        else if (ph == PH_PRE1) { Wm = w.W1;    ldw = d.M;      rows = d.P;     xin = s.mel_cur;  ldx = d.M;      K = d.M; }
+        else                    { Wm = w.W2;    ldw = d.P;      rows = d.P;     xin = s.p1;       ldx = d.P;      K = d.P; }
+        const SmallOut o = small_gemm(Wm, ldw, rows, xin, ldx, B, K, scratch);
+        if (o.valid) {
+          const int r = o.r, b = o.b;
+          float v = o.v;
+          if (ph == PH_QUERY) {
+            s.q[(size_t)b * d.A + r] = v;
+          } else if (ph == PH_PROJ) {
+            v += __ldg(w.bproj + r);
+            if (r < d.M) {
+              io.mels[((size_t)b * io.Tmax + tg_) * d.M + r] = v;
+              s.mel_cur[(size_t)b * d.M + r] = v;
+            } else {
+              io.gates[(size_t)b * io.Tmax + tg_] = v;
+              if (io.stop_enabled) {  // model/tacotron2.py:319-320
+                if (v < 0.0f) s.done[b] = 1;
+                if (v >= 0.0f) s.lengths[b] += 1;
+              }
+            }
+          } else {
+            const int layer = ph == PH_PRE1 ? 0 : 1;
+            const size_t kidx = (((size_t)(tg_ + 1) * 2 + layer) * B + b) * d.P + r;
+            const bool keep = io.prenet_keep ? (io.prenet_keep[kidx] != 0) : rng_keep(io.seed, kidx, d.p_prenet);
+            v = (v > 0.f && keep) ? v * pscale : 0.f;
+            if (layer == 0) s.p1[(size_t)b * d.P + r] = v;
+            else { store_split(s.xatt + (size_t)nxt * 2 * pa, pa, d.KattP, b, r, v); wrote_x = true; }
+          }
         }
+        if (ph == PH_PROJ) frames = t + 1;
       }
-    });
-    // TF mode also stashes ctx / controls of projin for the backward pass
-    if (io.projin_all) {
-      for (int i = blockIdx.x * DEC_THREADS + tid; i < B * (d.KprojP - d.R); i += gridDim.x * DEC_THREADS) {
-        const int b = i / (d.KprojP - d.R), c = d.R + i % (d.KprojP - d.R);
-        io.projin_all[((size_t)tg * B + b) * d.KprojP + c] = ld_cg(s.projin + (size_t)b * d.KprojP + c);
+      if (!(alive = bar.sync(fail, wrote_x))) break;
+      prof_mark(ph);
+      if (ph == PH_PROJ && !io.teacher_forcing) {
+        if (io.stop_enabled) {  // model/tacotron2.py:321-322: leave once every utterance has fired its stop gate
+          int mine = 1;
+#pragma unroll 1
+          for (int b = tid; b < B; b += D2_THREADS) mine &= (ld_acquire_u32((const unsigned*)s.done + b) != 0u);
+          if (__syncthreads_and(mine)) stop = true;
+        }
+        if (t + 1 >= io.n_steps) stop = true;  // the last frame's prenet output is never used
+      }
+      if (ph == PH_PRE2 && io.debug_barrier) {  // measures the bare cost of one grid barrier (slot 7)
+        if (!(alive = bar.sync(fail, false))) break;
+        prof_mark(7);
       }
     }
-    frames = t + 1;
-    if (!(alive = bar.sync())) break;
-    prof_mark(4);
-    if (io.teacher_forcing) continue;
-
-    if (io.stop_enabled) {  // model/tacotron2.py:321-322: break once every item has fired
-      int mine = 1;
-      for (int b = tid; b < B; b += DEC_THREADS) mine &= (ld_acquire_u32((const unsigned*)s.done + b) != 0u);
-      if (__syncthreads_and(mine)) break;
-    }
-    if (t + 1 >= io.n_steps && io.n_steps > 1) break;  // last frame: its prenet output is never used
-
-    // ---- P6 / P7: prenet on the emitted frame (model/tacotron2.py:324-325) -------------
-    const unsigned char* k1 = io.prenet_keep ? io.prenet_keep + ((size_t)(tg + 1) * 2 + 0) * B * d.P : nullptr;
-    const unsigned char* k2 = io.prenet_keep ? io.prenet_keep + ((size_t)(tg + 1) * 2 + 1) * B * d.P : nullptr;
-    warp_gemm_rm(w.W1, d.M, d.P, s.mel_cur, d.M, B, d.M, [&](int r, int b, float v) {
-      const bool keep = k1 ? (k1[(size_t)b * d.P + r] != 0)
-                           : rng_keep(io.seed, ((unsigned long long)(tg + 1) * 2 + 0) * B * d.P + (size_t)b * d.P + r, d.p_prenet);
-      s.p1[(size_t)b * d.P + r] = (v > 0.f && keep) ? v * pscale : 0.f;
-    });
-    if (!(alive = bar.sync())) break;
-    prof_mark(5);
-    warp_gemm_rm(w.W2, d.P, d.P, s.p1, d.P, B, d.P, [&](int r, int b, float v) {
-      const bool keep = k2 ? (k2[(size_t)b * d.P + r] != 0)
-                           : rng_keep(io.seed, ((unsigned long long)(tg + 1) * 2 + 1) * B * d.P + (size_t)b * d.P + r, d.p_prenet);
-      s.xpre[nxt][(size_t)r * DEC_BP + b] = (v > 0.f && keep) ? v * pscale : 0.f;
-    });
-    if (!(alive = bar.sync())) break;
-    prof_mark(6);
   }
   if (blockIdx.x == 0 && tid == 0) *s.n_frames = alive ? frames : -1;
+  // write the cell states back (single-step API / resumable decoding)
+#pragma unroll 1
+  for (int i = tid; i < 8 * D2_BP; i += D2_THREADS) {
+    s.att_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP] = sm.c_att[i];
+    s.rnn_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP] = sm.c_dec[i];
+  }
+  tc::tc_fence_before();
+  tc::cluster_sync();  // no CTA exits while a peer may still read its shared memory
+  if ((tid >> 5) == 1) tc::tmem_dealloc<TG_TMEM_COLS>(pipe.tmem);
+}
+
+size_t att_scratch_floats(const D2Dims& d, int S) {
+  const int Lc = (d.L + S - 1) / S;
+  const int cols = (((d.EF + S - 1) / S) + 3) & ~3;
+  return (size_t)d.A + 2 * (size_t)((Lc + 35) & ~3) + (size_t)Lc * 36 + Lc + 4 + d.L + 4 + 64 + 8 + 4 * (size_t)cols;
 }
 
 }  // namespace
 
-size_t dec_smem_bytes(const DecDims& d) {
-  size_t f = (size_t)LT_STAGES * LT_STAGE_FLOATS + DEC_LOC_F * 2 * DEC_LOC_K + (size_t)d.A * DEC_LOC_F + 2 * d.A +
-             2 * (d.L + 32) + d.L + 4 + 64 + 8 + 4 * (size_t)((d.EF + 3) & ~3);
-  return f * sizeof(float);
+size_t d2_smem_bytes(const D2Dims& d) {
+  return 1024 + (size_t)D2_STAGES * TG_STAGE_BYTES + TG_M * TG_PART_LD * 4 + 2 * 8 * D2_BP * 4 + 2 * D2_LOC_K * D2_LOC_F * 4 +
+         (size_t)d.A * D2_LOC_F * 4 + d.A * 4 + (2 * D2_STAGES + 2) * 8 + 64;
 }
 
-int dec_launch(const DecDims& d, const DecWeights& w, const DecState& s, const DecIO& io, int num_sms, cudaStream_t stream) {
-  T2_REQUIRE(d.B >= 1 && d.B <= DEC_BP, T2_ERR_ARG, "decoder: batch %d not in [1,%d] per launch", d.B, DEC_BP);
-  T2_REQUIRE(d.H % 8 == 0 && d.R % 8 == 0 && d.EF % 4 == 0 && d.M % 4 == 0 && d.P % 4 == 0 && d.A <= DEC_MAX_A && d.A % 4 == 0,
+static int launch_cfg(const D2Dims& d, cudaLaunchConfig_t* cfg, cudaLaunchAttribute* at, size_t smem, cudaStream_t st) {
+  cfg->gridDim = dim3((unsigned)(d.H / 32) * D2_CLUSTER);
+  cfg->blockDim = dim3(D2_THREADS);
+  cfg->dynamicSmemBytes = smem;
+  cfg->stream = st;
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = D2_CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg->attrs = at;
+  cfg->numAttrs = 1;
+  return T2_OK;
+}
+
+int d2_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, const D2Maps& maps, cudaStream_t st) {
+  T2_REQUIRE(d.B >= 1 && d.B <= D2_BP, T2_ERR_ARG, "decoder: batch %d not in [1,%d] per launch", d.B, D2_BP);
+  T2_REQUIRE(d.H == d.R && d.H % 32 == 0 && d.P % TG_BK == 0 && d.EF % 4 == 0 && d.M % 4 == 0 && d.A % 32 == 0 && d.A <= D2_MAX_A,
              T2_ERR_UNSUPPORTED, "decoder: unsupported dims H=%d R=%d EF=%d M=%d P=%d A=%d", d.H, d.R, d.EF, d.M, d.P, d.A);
-  T2_REQUIRE(d.KattP % LT_KC == 0 && d.KdecP % LT_KC == 0 && d.P % LT_KC == 0, T2_ERR_UNSUPPORTED, "decoder: K padding");
-  const size_t smem = dec_smem_bytes(d);
-  T2_REQUIRE(smem <= 227 * 1024, T2_ERR_UNSUPPORTED, "decoder: L=%d needs %zu B shared memory", d.L, smem);
+  const int grid = (d.H / 32) * D2_CLUSTER;
+  T2_REQUIRE(grid == 128, T2_ERR_UNSUPPORTED, "decoder: this revision is laid out for 128 CTAs (att_rnn_dim = 1024), got %d", grid);
+  const int S = (d.B * 4 <= grid) ? 4 : ((d.B * 2 <= grid) ? 2 : 1);
+  const size_t ring = (size_t)D2_STAGES * TG_STAGE_BYTES;
+  T2_REQUIRE(att_scratch_floats(d, S) * 4 <= ring, T2_ERR_UNSUPPORTED, "decoder: L=%d too long for the attention scratch", d.L);
+  T2_REQUIRE(((size_t)(((d.M + 1 + 15) / 16) + 8) * (d.KprojP + 4) + 128) * 4 <= ring, T2_ERR_UNSUPPORTED, "decoder: projection staging");
+  const size_t smem = d2_smem_bytes(d);
+  T2_REQUIRE(smem <= 227 * 1024, T2_ERR_UNSUPPORTED, "decoder: %zu B shared memory", smem);
   T2_CHECK_CUDA(cudaFuncSetAttribute(decoder_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int per_sm = 0;
-  T2_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, decoder_persistent_kernel, DEC_THREADS, smem));
-  T2_REQUIRE(per_sm >= 1, T2_ERR_UNSUPPORTED, "decoder: kernel does not fit on an SM");
-  T2_CHECK_CUDA(cudaMemsetAsync(s.barrier, 0, 2 * sizeof(unsigned), stream));
-  DecDims dd = d; DecWeights ww = w; DecState ss = s; DecIO ii = io;
-  void* args[] = {&dd, &ww, &ss, &ii};
-  T2_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)decoder_persistent_kernel, dim3(num_sms), dim3(DEC_THREADS), args, smem, stream));
+  cudaLaunchConfig_t cfg{};
+  cudaLaunchAttribute at[1];
+  launch_cfg(d, &cfg, at, smem, st);
+  int nclusters = 0;
+  T2_CHECK_CUDA(cudaOccupancyMaxActiveClusters(&nclusters, decoder_persistent_kernel, &cfg));
+  T2_REQUIRE(nclusters * D2_CLUSTER >= grid, T2_ERR_UNSUPPORTED,
+             "decoder: only %d clusters of %d can be co-resident, %d needed (persistent kernel needs the whole grid resident)",
+             nclusters, D2_CLUSTER, grid / D2_CLUSTER);
+  T2_CHECK_CUDA(cudaMemsetAsync(s.barrier, 0, 2 * sizeof(unsigned), st));
+  T2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, decoder_persistent_kernel, maps, d, w, s, io));
   return T2_OK;
 }
