@@ -100,6 +100,17 @@ int t2_postnet_fwd(t2_ctx* ctx, const float* mels, int t_stride, int B, int T, i
 int t2_finalize(t2_ctx* ctx, float* mels, float* post, float* gates, const long long* lengths, int B, int T, int t_stride,
                 void* stream);
 
+/* Batched log-mel extraction: TacotronMelSpectrogram(n_mels, sample_rate)(wav) of datasets/tts_dataset.py:166-168,204
+ * (implementation external to the reference: speech_utils, un-vendored; parameters as stated in
+ * datasets/prosody_dataset.py:39-50,66-67 and run/say.py:161-171: n_fft 1024, win 1024, hop 256, center + reflect pad,
+ * periodic Hann, magnitude, slaney filterbank, log(clamp(1e-5)), transposed to (T, n_mels)).
+ * wav (B, wav_stride) fp32 zero padded, wav_len (B) int64 samples; window (n_fft); fb (n_mels, n_fft/2+1) fp32 filterbank,
+ * fb_range (n_mels, 2) int32 [lo,hi) non-zero bin range per filter.  out (B, t_stride, n_mels): frames
+ * t < 1 + wav_len/hop hold log-mels, the rest zeros (pad_sequence, datasets/tts_dataloader.py:28);
+ * n_frames (B) int64 or NULL receives the frame counts (mel_spectrogram_len, datasets/tts_dataset.py:209). */
+int t2_melspec(const float* wav, const long long* wav_len, int B, long long wav_stride, const float* window, const float* fb,
+               const int* fb_range, int n_fft, int hop, int n_mels, float* out, int t_stride, long long* n_frames, void* stream);
+
 /* Debug: SM-clock cycles CTA 0 spent in each phase of the last decode call (host pointer, 16 slots;
  * synchronises the device).  Slots: 0 att-LSTM tail, 1 query, 2 attention tail, 3 dec-LSTM tail, 4 projection, 5 prenet1,
  * 6 prenet2, 7 extra barrier (T2B200_DEBUG_BARRIER), 8/9 att/dec gate GEMM, 10-14 attention conv/dense/sync/softmax/context. */

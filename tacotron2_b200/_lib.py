@@ -42,6 +42,7 @@ SIGNATURES = {
     "t2_debug_phase_cycles": (_I, [_P, _P]),
     "t2_debug_tcgemm": (_I, [_P, _P, _P, _I, _I, _I, _P, _LL, _P]),
     "t2_finalize": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "t2_melspec": (_I, [_P, _P, _I, _LL, _P, _P, _P, _I, _I, _I, _P, _I, _P, _P]),
 }
 
 _lib = None

@@ -1,0 +1,134 @@
+// Batched log-mel extraction: the arithmetic of torchaudio MelSpectrogram(n_fft 1024, win 1024, hop 256,
+// center=True, pad_mode="reflect", periodic Hann, power 1, slaney mel scale + norm) followed by log(clamp(min=1e-5)) and a
+// transpose to (T, n_mels) -- the parameter statement of the reference (datasets/prosody_dataset.py:39-50,66-67; call site
+// datasets/tts_dataset.py:166-168,204; inverse run/say.py:161-171).
+//
+// One CTA = 256 threads = MS_FPC consecutive frames of one utterance.  The samples the frames share (75 % overlap) are
+// staged once in shared memory with the reflect padding applied; two real frames are packed into one 1024-point complex
+// radix-4 Stockham FFT (5 passes, twiddles from a shared-memory table), unpacked to |X_a|, |X_b| for bins 0..512, and the
+// triangular mel filters are applied by one warp per (frame, mel) with the per-filter [lo,hi) bin range.
+#include "../../include/t2b200.h"
+#include "common.cuh"
+
+#define MS_NFFT 1024
+#define MS_HOP 256
+#define MS_BINS 513
+#define MS_FPC 8          // frames per CTA (4 packed FFTs)
+#define MS_THREADS 256
+
+namespace {
+
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+
+__global__ void __launch_bounds__(MS_THREADS) melspec_kernel(const float* __restrict__ wav, const long long* __restrict__ wav_len,
+                                                             long long wav_stride, const float* __restrict__ window,
+                                                             const float* __restrict__ fb /*[n_mels][513]*/,
+                                                             const int* __restrict__ fb_range /*[n_mels][2]*/, int n_mels,
+                                                             float* __restrict__ out, int t_stride, long long* __restrict__ n_frames_out,
+                                                             float log_floor) {
+  __shared__ float2 bufA[MS_NFFT];
+  __shared__ float2 bufB[MS_NFFT];
+  __shared__ float2 tw[MS_NFFT];                                  // exp(-2 pi i m / 1024)
+  __shared__ float samples[MS_NFFT + (MS_FPC - 1) * MS_HOP];
+  __shared__ float win[MS_NFFT];
+  __shared__ float mag[2][MS_BINS + 3];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int b = blockIdx.y;
+  const long long S = wav_len[b];
+  const int T = S > 0 ? (int)(1 + S / MS_HOP) : 0;
+  const int f0 = blockIdx.x * MS_FPC;
+  if (blockIdx.x == 0 && tid == 0 && n_frames_out) n_frames_out[b] = T;
+  float* outb = out + (size_t)b * t_stride * n_mels;
+  if (f0 >= T) {  // pad_sequence zero padding of the batch (datasets/tts_dataloader.py:28)
+    for (int i = tid; i < MS_FPC * n_mels; i += MS_THREADS) {
+      const int f = f0 + i / n_mels;
+      if (f < t_stride) outb[(size_t)f * n_mels + i % n_mels] = 0.f;
+    }
+    return;
+  }
+  for (int i = tid; i < MS_NFFT; i += MS_THREADS) {
+    float s, c;
+    sincospif(-2.0f * (float)i / (float)MS_NFFT, &s, &c);
+    tw[i] = make_float2(c, s);
+    win[i] = window[i];
+  }
+  const float* x = wav + (size_t)b * wav_stride;
+  const long long base = (long long)f0 * MS_HOP - MS_NFFT / 2;
+  for (int i = tid; i < MS_NFFT + (MS_FPC - 1) * MS_HOP; i += MS_THREADS) {
+    long long n = base + i;
+    if (n < 0) n = -n;                         // reflect (no edge repeat), torch.stft center=True
+    if (n >= S) n = 2 * (S - 1) - n;
+    samples[i] = (n >= 0 && n < S) ? x[n] : 0.f;
+  }
+  __syncthreads();
+
+  for (int pair = 0; pair < MS_FPC / 2; ++pair) {
+    const int fa = f0 + 2 * pair;
+    if (fa >= T && fa >= t_stride) break;
+    // pack frame a (real) and frame b (imag)
+    for (int i = tid; i < MS_NFFT; i += MS_THREADS) {
+      const float w = win[i];
+      bufA[i] = make_float2(samples[(2 * pair) * MS_HOP + i] * w, samples[(2 * pair + 1) * MS_HOP + i] * w);
+    }
+    __syncthreads();
+    float2* src = bufA;
+    float2* dst = bufB;
+#pragma unroll
+    for (int pass = 0; pass < 5; ++pass) {
+      const int Ns = 1 << (2 * pass);
+      const int j = tid, k = j & (Ns - 1);
+      const int tstep = k * (MS_NFFT / (Ns * 4));  // twiddle index for r = 1
+      float2 v0 = src[j], v1 = src[j + 256], v2 = src[j + 512], v3 = src[j + 768];
+      if (pass > 0) {
+        v1 = cmul(v1, tw[tstep]);
+        v2 = cmul(v2, tw[2 * tstep]);
+        v3 = cmul(v3, tw[3 * tstep]);
+      }
+      const float2 a = make_float2(v0.x + v2.x, v0.y + v2.y), bb = make_float2(v0.x - v2.x, v0.y - v2.y);
+      const float2 c = make_float2(v1.x + v3.x, v1.y + v3.y), d = make_float2(v1.x - v3.x, v1.y - v3.y);
+      const float2 dr = make_float2(d.y, -d.x);  // -i * d
+      const int o = (j / Ns) * Ns * 4 + k;
+      dst[o] = make_float2(a.x + c.x, a.y + c.y);
+      dst[o + Ns] = make_float2(bb.x + dr.x, bb.y + dr.y);
+      dst[o + 2 * Ns] = make_float2(a.x - c.x, a.y - c.y);
+      dst[o + 3 * Ns] = make_float2(bb.x - dr.x, bb.y - dr.y);
+      __syncthreads();
+      float2* t = src; src = dst; dst = t;
+    }
+    // src holds Z = FFT(a + i b) in natural order: X_a[k] = (Z[k] + conj Z[N-k]) / 2, X_b[k] = (Z[k] - conj Z[N-k]) / (2i)
+    for (int k = tid; k < MS_BINS; k += MS_THREADS) {
+      const float2 z = src[k], zc = src[(MS_NFFT - k) & (MS_NFFT - 1)];
+      const float ar = 0.5f * (z.x + zc.x), ai = 0.5f * (z.y - zc.y);
+      const float br = 0.5f * (z.y + zc.y), bi = -0.5f * (z.x - zc.x);
+      mag[0][k] = sqrtf(ar * ar + ai * ai);   // power = 1: magnitude
+      mag[1][k] = sqrtf(br * br + bi * bi);
+    }
+    __syncthreads();
+    for (int o = warp; o < 2 * n_mels; o += MS_THREADS / 32) {
+      const int which = o / n_mels, m = o - which * n_mels;
+      const int f = fa + which;
+      const int lo = fb_range[2 * m], hi = fb_range[2 * m + 1];
+      float acc = 0.f;
+      for (int k = lo + lane; k < hi; k += 32) acc = fmaf(mag[which][k], __ldg(fb + (size_t)m * MS_BINS + k), acc);
+      acc = warp_sum(acc);
+      if (lane == 0 && f < t_stride) outb[(size_t)f * n_mels + m] = f < T ? logf(fmaxf(acc, log_floor)) : 0.f;
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace
+
+extern "C" int t2_melspec(const float* wav, const long long* wav_len, int B, long long wav_stride, const float* window,
+                          const float* fb, const int* fb_range, int n_fft, int hop, int n_mels, float* out, int t_stride,
+                          long long* n_frames, void* stream) {
+  T2_REQUIRE(wav && wav_len && window && fb && fb_range && out, T2_ERR_ARG, "t2_melspec: null argument");
+  T2_REQUIRE(n_fft == MS_NFFT && hop == MS_HOP, T2_ERR_UNSUPPORTED,
+             "t2_melspec: specialised for n_fft=1024, hop=256 (datasets/prosody_dataset.py:39-50), got %d/%d", n_fft, hop);
+  T2_REQUIRE(B > 0 && n_mels > 0 && t_stride > 0 && wav_stride > 0, T2_ERR_ARG, "t2_melspec: bad sizes");
+  dim3 grid((unsigned)((t_stride + MS_FPC - 1) / MS_FPC), (unsigned)B);
+  melspec_kernel<<<grid, MS_THREADS, 0, (cudaStream_t)stream>>>(wav, wav_len, wav_stride, window, fb, fb_range, n_mels, out, t_stride,
+                                                                n_frames, 1e-5f);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}

@@ -212,3 +212,19 @@ def synth_masks(a: ModelArgs, B: int, L: int, T: int, seed: int = 7, train: bool
         m["encoder"] = torch.from_numpy((g.random((3, B, L, a.encoded_dim)) >= a.dropout).astype(np.uint8))
         m["postnet"] = torch.from_numpy((g.random((5, B, T, a.postnet_dim)) >= a.dropout).astype(np.uint8))
     return m
+
+
+MEL_GOLDEN_LENGTHS = (22050, 5000, 1024, 777, 256 * 40)  # samples; tests/golden/melspec.npz
+
+
+def synth_wav(n_samples: int, seed: int = 0) -> np.ndarray:
+    """Speech-like synthetic waveform: a few decaying harmonics with vibrato + band noise + a silent tail, in [-1, 1]."""
+    g = _rng("wav", seed)
+    t = np.arange(n_samples) / 22050.0
+    f0 = 110.0 + 40.0 * g.random() + 8.0 * np.sin(2 * np.pi * 5.0 * t)
+    ph = 2 * np.pi * np.cumsum(f0) / 22050.0
+    x = sum((0.6 ** h) * np.sin((h + 1) * ph + g.random() * 6.28) for h in range(12))
+    env = 0.5 + 0.5 * np.sin(2 * np.pi * 2.3 * t + g.random() * 6.28)
+    x = 0.2 * x * env + 0.02 * g.standard_normal(n_samples)
+    x[int(0.9 * n_samples):] *= 0.001  # near-silence: exercises the log floor
+    return np.clip(x, -1, 1).astype(np.float32)
