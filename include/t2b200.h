@@ -100,6 +100,36 @@ int t2_postnet_fwd(t2_ctx* ctx, const float* mels, int t_stride, int B, int T, i
 int t2_finalize(t2_ctx* ctx, float* mels, float* post, float* gates, const long long* lengths, int B, int T, int t_stride,
                 void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------------
+ * Training path.  The reference gets its backward pass from autograd over
+ * Tacotron2.forward (training_step, model/tts_model.py:165-202); here every module has a train-mode forward that records
+ * a caller-owned "tape" (sized by t2_*_tape_bytes) and a backward that consumes it.  Parameter gradients are WRITTEN
+ * (not accumulated) to the destinations registered per state-dict key with t2_ctx_set_grad.  Dropout keep-masks follow the
+ * forward's convention: explicit uint8 masks or NULL = counter RNG from `seed` (the backward regenerates the same draws).
+ * ------------------------------------------------------------------------------------------------------------------ */
+int t2_ctx_set_grad(t2_ctx* ctx, const char* key, float* ptr, long long numel);   /* ptr NULL unregisters */
+long long t2_train_workspace_bytes(const t2_ctx* ctx, int B, int L, int T);
+
+/* Postnet.forward under train() (model/postnet.py:8-52): BatchNorm batch statistics over all (b,t), running statistics
+ * updated in place (momentum 0.1), dropout after every layer.  keep (5,B,T,postnet_dim) or NULL. */
+long long t2_postnet_tape_bytes(const t2_ctx* ctx, int B, int T);
+int t2_postnet_train_fwd(t2_ctx* ctx, const float* mels, int t_stride, int B, int T, const unsigned char* keep, unsigned long long seed,
+                         float* out, void* tape, long long tape_bytes, void* ws, long long ws_bytes, void* stream);
+/* d_out (B,T,M): gradient w.r.t. the postnet output; d_mels_in (B,T,M) or NULL is added to the input gradient;
+ * d_mels (B,T,M) receives the total.  Writes postnet.postnet.* gradients. */
+int t2_postnet_bwd(t2_ctx* ctx, int B, int T, const unsigned char* keep, unsigned long long seed, const float* d_out,
+                   const float* d_mels_in, const void* tape, long long tape_bytes, float* d_mels, void* ws, long long ws_bytes,
+                   void* stream);
+
+/* training_step loss (model/tts_model.py:197-201): BCEWithLogits(gates) + MSE(mels) + MSE(mels_post), plain means over the
+ * padded tensors; loss (1) device scalar; d_mels/d_post (B,T,M), d_gates (B,T) may be NULL.  ws >= 4 KB. */
+int t2_loss_fwd_bwd(t2_ctx* ctx, const float* mels, const float* post, const float* gates, const float* mel_target,
+                    const float* gate_target, int B, int T, float* loss, float* d_mels, float* d_post, float* d_gates, void* ws,
+                    long long ws_bytes, void* stream);
+/* Backward of t2_finalize (model/tacotron2.py:333-345).  Inputs may be NULL (= zero gradient). */
+int t2_finalize_bwd(t2_ctx* ctx, const float* d_mels, const float* d_post, const float* d_gates, const long long* lengths, int B, int T,
+                    float* d_mels_raw, float* d_postnet_out, float* d_gates_raw, void* stream);
+
 /* Batched log-mel extraction: TacotronMelSpectrogram(n_mels, sample_rate)(wav) of datasets/tts_dataset.py:166-168,204
  * (implementation external to the reference: speech_utils, un-vendored; parameters as stated in
  * datasets/prosody_dataset.py:39-50,66-67 and run/say.py:161-171: n_fft 1024, win 1024, hop 256, center + reflect pad,

@@ -42,6 +42,13 @@ SIGNATURES = {
     "t2_debug_phase_cycles": (_I, [_P, _P]),
     "t2_debug_tcgemm": (_I, [_P, _P, _P, _I, _I, _I, _P, _LL, _P]),
     "t2_finalize": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "t2_ctx_set_grad": (_I, [_P, C.c_char_p, _P, _LL]),
+    "t2_train_workspace_bytes": (_LL, [_P, _I, _I, _I]),
+    "t2_postnet_tape_bytes": (_LL, [_P, _I, _I]),
+    "t2_postnet_train_fwd": (_I, [_P, _P, _I, _I, _I, _P, _ULL, _P, _P, _LL, _P, _LL, _P]),
+    "t2_postnet_bwd": (_I, [_P, _I, _I, _P, _ULL, _P, _P, _P, _LL, _P, _P, _LL, _P]),
+    "t2_loss_fwd_bwd": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _P, _LL, _P]),
+    "t2_finalize_bwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P]),
     "t2_melspec": (_I, [_P, _P, _I, _LL, _P, _P, _P, _I, _I, _I, _P, _I, _P, _P]),
 }
 

@@ -1,0 +1,120 @@
+"""torch.autograd glue for the training path.
+
+Each ``Function`` below is a thin binding: forward calls a ``t2_*_train_fwd`` entry point of libt2b200 that records a
+tape, backward calls the matching ``t2_*_bwd``.  No arithmetic happens in Python.  Parameters are passed to ``apply`` so
+autograd routes their gradients; the C side writes them into a freshly allocated flat buffer per module ("bucket"),
+registered key by key with ``t2_ctx_set_grad``.  A bucket is also the unit of the data-parallel gradient all-reduce
+(``tacotron2_b200.parallel``): its NCCL all-reduce is enqueued the moment the module's backward has been launched, so it
+overlaps with the backward of the modules upstream.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+
+P = _lib.ptr
+
+
+def _stream():
+    import ctypes as C
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _bucket(owner, lib, params: dict):
+    """Allocate one flat gradient buffer for ``params`` (key -> Parameter), register the slices, return views in order."""
+    n = sum(p.numel() for p in params.values())
+    dev = next(iter(params.values())).device
+    flat = torch.empty(n, dtype=torch.float32, device=dev)
+    views, off = [], 0
+    for k, p in params.items():
+        v = flat[off:off + p.numel()]
+        _lib.check(lib.t2_ctx_set_grad(owner._ctx, k.encode(), P(v), p.numel()), "t2_ctx_set_grad")
+        views.append(v.view_as(p))
+        off += p.numel()
+    return flat, views
+
+
+def _after_bucket(owner, flat):
+    hook = getattr(owner, "_grad_bucket_hook", None)
+    if hook is not None:
+        hook(flat)  # data-parallel: async all-reduce of this bucket (parallel.py)
+
+
+class PostnetFn(torch.autograd.Function):
+    """Postnet.forward under train() (model/postnet.py:8-52) on channels-last (B,T,M)."""
+
+    @staticmethod
+    def forward(ctx, owner, keep, seed, mels_cl, *params):
+        lib = owner._ready(mels_cl.device)
+        B, T, M = mels_cl.shape
+        x = mels_cl.contiguous()
+        tape = torch.empty(lib.t2_postnet_tape_bytes(owner._ctx, B, T), dtype=torch.uint8, device=x.device)
+        ws = owner._train_workspace(lib, x.device, B, 1, T)
+        out = torch.empty(B, T, M, device=x.device)
+        _lib.check(lib.t2_postnet_train_fwd(owner._ctx, P(x), T, B, T, P(keep), seed, P(out), P(tape), tape.numel(), P(ws), ws.numel(),
+                                            _stream()), "t2_postnet_train_fwd")
+        owner._sig = None  # running statistics changed in place: re-fold them before the next eval() forward
+        ctx.owner, ctx.keep, ctx.seed, ctx.tape, ctx.shape = owner, keep, seed, tape, (B, T, M)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        owner = ctx.owner
+        B, T, M = ctx.shape
+        lib = owner._ready(d_out.device)
+        flat, views = _bucket(owner, lib, owner._group_params("postnet"))
+        ws = owner._train_workspace(lib, d_out.device, B, 1, T)
+        d_mels = torch.empty(B, T, M, device=d_out.device)
+        _lib.check(lib.t2_postnet_bwd(owner._ctx, B, T, P(ctx.keep), ctx.seed, P(d_out.contiguous()), None, P(ctx.tape), ctx.tape.numel(),
+                                      P(d_mels), P(ws), ws.numel(), _stream()), "t2_postnet_bwd")
+        _after_bucket(owner, flat)
+        return (None, None, None, d_mels, *views)
+
+
+class FinalizeFn(torch.autograd.Function):
+    """mels_post = mels + postnet_out, then the three output masks (model/tacotron2.py:333-345)."""
+
+    @staticmethod
+    def forward(ctx, owner, lengths, mels_raw, post_out, gates_raw):
+        lib = owner._ready(mels_raw.device)
+        B, T, M = mels_raw.shape
+        mels, post, gates = mels_raw.clone(), post_out.clone(), gates_raw.clone()
+        _lib.check(lib.t2_finalize(owner._ctx, P(mels), P(post), P(gates), P(lengths), B, T, T, _stream()), "t2_finalize")
+        ctx.owner, ctx.lengths, ctx.shape = owner, lengths, (B, T, M)
+        return mels, post, gates
+
+    @staticmethod
+    def backward(ctx, d_mels, d_post, d_gates):
+        owner = ctx.owner
+        B, T, M = ctx.shape
+        lib = _lib.load()
+        dev = ctx.lengths.device
+        c = lambda t: None if t is None else t.contiguous()  # noqa: E731
+        d_raw, d_po, d_g = torch.empty(B, T, M, device=dev), torch.empty(B, T, M, device=dev), torch.empty(B, T, device=dev)
+        _lib.check(lib.t2_finalize_bwd(owner._ctx, P(c(d_mels)), P(c(d_post)), P(c(d_gates)), P(ctx.lengths), B, T, P(d_raw), P(d_po),
+                                       P(d_g), _stream()), "t2_finalize_bwd")
+        return None, None, d_raw, d_po, d_g
+
+
+class LossFn(torch.autograd.Function):
+    """training_step loss (model/tts_model.py:197-201) with its gradient computed in the same kernel."""
+
+    @staticmethod
+    def forward(ctx, owner, mels, post, gates, mel_target, gate_target):
+        lib = owner._ready(mels.device)
+        B, T, M = mels.shape
+        dev = mels.device
+        loss = torch.empty((), device=dev)
+        d_m, d_p, d_g = torch.empty(B, T, M, device=dev), torch.empty(B, T, M, device=dev), torch.empty(B, T, 1, device=dev)
+        ws = owner._train_workspace(lib, dev, B, 1, T)
+        f = lambda t: t.to(device=dev, dtype=torch.float32).contiguous()  # noqa: E731
+        _lib.check(lib.t2_loss_fwd_bwd(owner._ctx, P(f(mels)), P(f(post)), P(f(gates)), P(f(mel_target)), P(f(gate_target)), B, T, P(loss),
+                                       P(d_m), P(d_p), P(d_g), P(ws), ws.numel(), _stream()), "t2_loss_fwd_bwd")
+        ctx.save_for_backward(d_m, d_p, d_g)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        d_m, d_p, d_g = ctx.saved_tensors
+        return None, d_m * g, d_p * g, d_g * g, None, None

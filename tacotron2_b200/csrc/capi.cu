@@ -4,10 +4,9 @@
 #include "decoder.cuh"
 #include "convtc.cuh"
 #include "layers.cuh"
+#include "ctx.cuh"
 
 #include <cstdarg>
-#include <map>
-#include <string>
 #include <vector>
 
 static thread_local char g_err[1024] = "";
@@ -19,34 +18,6 @@ void t2_set_error(const char* fmt, ...) {
 }
 extern "C" const char* t2_last_error(void) { return g_err; }
 extern "C" int t2_abi_version(void) { return 1; }
-
-struct Param { const float* ptr; long long numel; };
-
-struct t2_ctx {
-  t2_model_config cfg;
-  int device, num_sms;
-  int EF, C, H, R, P, A, M, E, PD, KS;
-  struct { int KattP, KdecP, KprojP; } dd;  // padded contraction lengths of the packed decoder operands
-  std::map<std::string, Param> params;
-  bool committed;
-  // packed device memory (one slab)
-  char* slab;
-  size_t slab_bytes;
-  float *enc_scale[3], *enc_shift[3];      // folded BatchNorm (+conv bias) of the encoder convs
-  float *post_scale[5], *post_shift[5];
-  float *lstm_bias, *lstm_Whh;  // BiLSTM: [1][E][2*4Hh], [2*4Hh], [2][4Hh][Hh]
-  unsigned long long* prof_buf;            // [16] device, decoder phase cycles
-  // tensor-core decoder (decoder2)
-  __nv_bfloat16 *Watt_b, *Wdec_b;          // [2 hi/lo][4H permuted][KattP] / [2][4R][KdecP]
-  float* loc_conv_t;                       // [2][31][32]
-  float* loc_dense_t;                      // [32][A]
-  D2Weights d2w;
-  CUtensorMap map_w_att, map_w_dec;
-  int npass;
-  // tensor-core conv operands (bf16 hi/lo [2][Cout][k][Cin]) and their TMA descriptors
-  __nv_bfloat16 *enc_Wb[3], *post_Wb[5], *lstm_Wb, *attenc_Wb;
-  CUtensorMap enc_wmap[3], post_wmap[5], lstm_wmap, attenc_wmap;
-};
 
 namespace {
 
@@ -183,6 +154,53 @@ __global__ void pack_lstm_bf16_kernel(const float* Wih, const float* Whh, __nv_b
     out[n + i] = lo;
   }
 }
+// transposed pack for the in-loop input-gradient GEMM dx[k][b] = sum_p W[row(p)][k] dg[b][p]:
+// tile-major [ktile][pblock][128 k][64 p], p = packed gate-row index (same permutation as pack_lstm_bf16_kernel)
+__global__ void pack_lstm_T_bf16_kernel(const float* Wih, const float* Whh, __nv_bfloat16* out, int H, int Kin, int KT) {
+  const long long n = 4ll * H * KT;
+  const int npb = 4 * H / 64;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int pp = (int)(i % 64);
+    const int kk = (int)((i / 64) % 128);
+    const int pb = (int)((i / (64 * 128)) % npb);
+    const int kt = (int)(i / (64ll * 128 * npb));
+    const int k = kt * 128 + kk, p = pb * 64 + pp;
+    const int tile = p >> 7, rr = p & 127;
+    const int j = (rr >> 5) & 3, g = (rr >> 3) & 3, ul = rr & 7;
+    const int row = g * H + tile * 32 + j * 8 + ul;
+    float v = 0.f;
+    if (k < Kin) v = Wih[(size_t)row * Kin + k];
+    else if (k < Kin + H) v = Whh[(size_t)row * H + (k - Kin)];
+    __nv_bfloat16 hi, lo;
+    tc::split_bf16(v, hi, lo);
+    out[i] = hi;
+    out[n + i] = lo;
+  }
+}
+// dst[2][rows_out][ld]: dst[k][r] = r < rows_in ? W[r][k] : 0   (fp32 [rows_in][ldw] -> transposed bf16 hi/lo)
+__global__ void pack_T_kernel(const float* W, int rows_in, int ldw, __nv_bfloat16* dst, int rows_out, int ld) {
+  const long long n = (long long)rows_out * ld;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(i % ld), k = (int)(i / ld);
+    __nv_bfloat16 hi, lo;
+    tc::split_bf16(r < rows_in ? W[(size_t)r * ldw + k] : 0.f, hi, lo);
+    dst[i] = hi;
+    dst[n + i] = lo;
+  }
+}
+// conv weight [Cout][Cin][k] -> bf16 (hi,lo) [2][Cin][k][Cout] with the taps flipped (input-gradient conv)
+__global__ void pack_conv_wT_kernel(const float* W, __nv_bfloat16* dst, int Cout, int Cin, int k) {
+  const long long n = (long long)Cout * Cin * k;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int co = (int)(i % Cout);
+    const int jj = (int)((i / Cout) % k);
+    const int ci = (int)(i / ((long long)Cout * k));
+    __nv_bfloat16 hi, lo;
+    tc::split_bf16(W[((size_t)co * Cin + ci) * k + (k - 1 - jj)], hi, lo);
+    dst[i] = hi;
+    dst[n + i] = lo;
+  }
+}
 __global__ void conv_t_kernel(const float* w /*[32][2][31]*/, float* out /*[2][31][32]*/) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= 32 * 2 * 31) return;
@@ -200,27 +218,22 @@ __global__ void rm_to_xsplit_kernel(const float* src, int lds, __nv_bfloat16* ds
   }
 }
 
-static int make_w_map(CUtensorMap* m, const __nv_bfloat16* w, int Cout, int Cin, int k, int NT, int npass) {
+inline int gsz(long long n) { return (int)std::min<long long>((n + 255) / 256, 148 * 8); }
+
+}  // namespace
+
+int make_w_map(CUtensorMap* m, const __nv_bfloat16* w, int Cout, int Cin, int k, int NT, int npass) {
   unsigned long long dims[4] = {(unsigned long long)Cin, (unsigned long long)k, (unsigned long long)Cout, 2ull};
   unsigned long long st[3] = {(unsigned long long)Cin * 2, (unsigned long long)k * Cin * 2, (unsigned long long)Cout * k * Cin * 2};
   unsigned box[4] = {64u, 1u, (unsigned)NT, npass == 3 ? 2u : 1u};
   return tc_make_tmap_bf16(m, w, 4, dims, st, box);
 }
-static int make_in_map(CUtensorMap* m, const __nv_bfloat16* x, int B, int T, int Cin, int npass) {
+int make_in_map(CUtensorMap* m, const __nv_bfloat16* x, int B, int T, int Cin, int npass) {
   unsigned long long dims[4] = {(unsigned long long)Cin, (unsigned long long)T, (unsigned long long)B, 2ull};
   unsigned long long st[3] = {(unsigned long long)Cin * 2, (unsigned long long)T * Cin * 2, (unsigned long long)B * T * Cin * 2};
   unsigned box[4] = {64u, 128u, 1u, npass == 3 ? 2u : 1u};
   return tc_make_tmap_bf16(m, x, 4, dims, st, box);
 }
-
-const Param* find(const t2_ctx* c, const std::string& k) {
-  auto it = c->params.find(k);
-  return it == c->params.end() ? nullptr : &it->second;
-}
-
-inline int gsz(long long n) { return (int)std::min<long long>((n + 255) / 256, 148 * 8); }
-
-}  // namespace
 
 // ------------------------------------------------------------------------------------------ context
 extern "C" int t2_ctx_create(const t2_model_config* cfg, t2_ctx** out) {
@@ -310,6 +323,16 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   for (int i = 0; i < 5; ++i) c->post_Wb[i] = ar.take<__nv_bfloat16>((size_t)2 * chans[i + 1] * 5 * chans[i]);
   c->lstm_Wb = ar.take<__nv_bfloat16>((size_t)2 * 8 * Hh * E);
   c->attenc_Wb = ar.take<__nv_bfloat16>((size_t)2 * A * EF);
+  for (int i = 0; i < 3; ++i) c->enc_WTb[i] = ar.take<__nv_bfloat16>((size_t)2 * E * KS * E);
+  for (int i = 0; i < 5; ++i) c->post_WTb[i] = ar.take<__nv_bfloat16>((size_t)2 * chans[i + 1] * 5 * chans[i]);
+  c->lstm_WTb = ar.take<__nv_bfloat16>((size_t)2 * 8 * Hh * E);
+  c->attenc_WTb = ar.take<__nv_bfloat16>((size_t)2 * A * EF);
+  c->KattT = (int)round_up64(P + EF + H, 128);
+  c->KdecT = (int)round_up64(H + EF + C + R, 128);
+  c->WTatt_b = ar.take<__nv_bfloat16>((size_t)2 * 4 * H * c->KattT);
+  c->WTdec_b = ar.take<__nv_bfloat16>((size_t)2 * 4 * R * c->KdecT);
+  c->WprojT_b = ar.take<__nv_bfloat16>((size_t)2 * d.KprojP * PROJ_LD);
+  c->W2T_b = ar.take<__nv_bfloat16>((size_t)2 * P * P);
   if (sizing) return T2_OK;
   T2_REQUIRE(!ar.overflow, T2_ERR_STATE, "t2_ctx_commit: slab overflow");
 
@@ -346,6 +369,24 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   T2_CHECK_CUDA(cudaGetLastError());
   { int rc3; if ((rc3 = transpose_launch(ldense->ptr, c->loc_dense_t, A, 32, st))) return rc3; }
   c->d2w = D2Weights{batt, bdec, wq->ptr, wv->ptr, c->loc_conv_t, c->loc_dense_t, Wproj, bproj, w1->ptr, w2->ptr};
+  // training operands
+  T2_REQUIRE(M + 1 <= PROJ_LD, T2_ERR_UNSUPPORTED, "num_mels %d too large for the projection-gradient pack", M);
+  pack_lstm_T_bf16_kernel<<<gsz(4ll * H * c->KattT), 256, 0, st>>>(att_ih->ptr, att_hh->ptr, c->WTatt_b, H, P + EF, c->KattT);
+  pack_lstm_T_bf16_kernel<<<gsz(4ll * R * c->KdecT), 256, 0, st>>>(dec_ih->ptr, dec_hh->ptr, c->WTdec_b, R, H + EF + C, c->KdecT);
+  pack_T_kernel<<<gsz((long long)d.KprojP * PROJ_LD), 256, 0, st>>>(Wproj, M + 1, d.KprojP, c->WprojT_b, d.KprojP, PROJ_LD);
+  pack_T_kernel<<<gsz((long long)P * P), 256, 0, st>>>(w2->ptr, P, P, c->W2T_b, P, P);
+  T2_CHECK_CUDA(cudaGetLastError());
+  {
+    const unsigned zb = c->npass == 3 ? 2u : 1u;
+    unsigned box[3] = {TG_BK, TG_M, zb};
+    int rc2;
+    unsigned long long dims[3] = {64ull, (unsigned long long)c->KattT * (4 * H / 64), 2ull};
+    unsigned long long strides[2] = {128ull, 4ull * H * c->KattT * 2};
+    if ((rc2 = tc_make_tmap_bf16(&c->map_wt_att, c->WTatt_b, 3, dims, strides, box))) return rc2;
+    unsigned long long dims2[3] = {64ull, (unsigned long long)c->KdecT * (4 * R / 64), 2ull};
+    unsigned long long strides2[2] = {128ull, 4ull * R * c->KdecT * 2};
+    if ((rc2 = tc_make_tmap_bf16(&c->map_wt_dec, c->WTdec_b, 3, dims2, strides2, box))) return rc2;
+  }
   {
     const unsigned zb = c->npass == 3 ? 2u : 1u;
     unsigned long long dims[3] = {64ull, 4ull * H * (d.KattP / 64), 2ull};
@@ -370,6 +411,8 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
     if ((rc = pack_conv_w_launch(cw->ptr, c->enc_Wb[i], E, E, KS, st))) return rc;
     if ((rc = make_w_map(&c->enc_wmap[i], c->enc_Wb[i], E, E, KS, 128, c->npass))) return rc;
     if ((rc = bn_fold_launch(bw->ptr, bb->ptr, bm->ptr, bv->ptr, cb->ptr, c->enc_scale[i], c->enc_shift[i], E, st))) return rc;
+    pack_conv_wT_kernel<<<gsz((long long)E * E * KS), 256, 0, st>>>(cw->ptr, c->enc_WTb[i], E, E, KS);
+    if ((rc = make_w_map(&c->enc_wtmap[i], c->enc_WTb[i], E, E, KS, 128, c->npass))) return rc;
   }
   for (int i = 0; i < 5; ++i) {
     const std::string cv = "postnet.postnet." + std::to_string(4 * i), bn = "postnet.postnet." + std::to_string(4 * i + 1);
@@ -381,6 +424,8 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
     if ((rc = pack_conv_w_launch(cw->ptr, c->post_Wb[i], chans[i + 1], chans[i], 5, st))) return rc;
     if ((rc = make_w_map(&c->post_wmap[i], c->post_Wb[i], chans[i + 1], chans[i], 5, chans[i + 1] % 128 == 0 ? 128 : chans[i + 1], c->npass))) return rc;
     if ((rc = bn_fold_launch(bw->ptr, bb->ptr, bm->ptr, bv->ptr, nullptr, c->post_scale[i], c->post_shift[i], chans[i + 1], st))) return rc;
+    pack_conv_wT_kernel<<<gsz((long long)chans[i + 1] * chans[i] * 5), 256, 0, st>>>(cw->ptr, c->post_WTb[i], chans[i + 1], chans[i], 5);
+    if ((rc = make_w_map(&c->post_wtmap[i], c->post_WTb[i], chans[i], chans[i + 1], 5, chans[i] % 128 == 0 ? 128 : chans[i], c->npass))) return rc;
   }
   // BiLSTM: input projection for both directions as one k=1 "conv": Wr [E][8Hh]; recurrent W_hh^T per direction
   for (int dir = 0; dir < 2; ++dir) {
@@ -399,6 +444,10 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   if ((rc = make_w_map(&c->lstm_wmap, c->lstm_Wb, 8 * Hh, E, 1, 128, c->npass))) return rc;
   if ((rc = pack_conv_w_launch(wae->ptr, c->attenc_Wb, A, EF, 1, st))) return rc;
   if ((rc = make_w_map(&c->attenc_wmap, c->attenc_Wb, A, EF, 1, A, c->npass))) return rc;
+  pack_conv_wT_kernel<<<gsz((long long)8 * Hh * E), 256, 0, st>>>(tmp, c->lstm_WTb, 8 * Hh, E, 1);
+  if ((rc = make_w_map(&c->lstm_wtmap, c->lstm_WTb, E, 8 * Hh, 1, 128, c->npass))) return rc;
+  pack_conv_wT_kernel<<<gsz((long long)A * EF), 256, 0, st>>>(wae->ptr, c->attenc_WTb, A, EF, 1);
+  if ((rc = make_w_map(&c->attenc_wtmap, c->attenc_WTb, EF, A, 1, 128, c->npass))) return rc;
   T2_CHECK_CUDA(cudaGetLastError());
   c->committed = true;
   return T2_OK;
@@ -417,12 +466,7 @@ extern "C" int t2_ctx_commit(t2_ctx* c, void* stream) {
 }
 
 // ------------------------------------------------------------------------------------------ ops
-#define CHECK_CTX(name)                                                                        \
-  T2_REQUIRE(c, T2_ERR_ARG, name ": null context");                                            \
-  T2_REQUIRE(c->committed, T2_ERR_STATE, name ": weights not committed (call t2_ctx_commit)")
-#define RC(x) do { int _rc = (x); if (_rc) return _rc; } while (0)
-
-static int conv_tc(t2_ctx* c, const __nv_bfloat16* in, const CUtensorMap& wmap, int B, int T, int Cin, int Cout, int k, int NT, int act,
+int conv_tc(t2_ctx* c, const __nv_bfloat16* in, const CUtensorMap& wmap, int B, int T, int Cin, int Cout, int k, int NT, int act,
                    const float* scale, const float* shift, const unsigned char* keep, int keep_ld, float* out_f32,
                    __nv_bfloat16* out_b16, cudaStream_t st) {
   ConvTcArgs a{};

@@ -1,0 +1,73 @@
+// Context object shared by the C-ABI translation units (capi.cu, train_capi.cu).
+#pragma once
+#include "../../include/t2b200.h"
+#include "common.cuh"
+#include "decoder.cuh"
+#include "convtc.cuh"
+#include "layers.cuh"
+
+#include <map>
+#include <string>
+
+struct Param { const float* ptr; long long numel; };
+struct GradSlot { float* ptr; long long numel; };
+
+struct t2_ctx {
+  t2_model_config cfg;
+  int device, num_sms;
+  int EF, C, H, R, P, A, M, E, PD, KS;
+  struct { int KattP, KdecP, KprojP; } dd;  // padded contraction lengths of the packed decoder operands
+  std::map<std::string, Param> params;
+  std::map<std::string, GradSlot> grads;   // destination of each parameter gradient (t2_ctx_set_grad)
+  bool committed;
+  // packed device memory (one slab)
+  char* slab;
+  size_t slab_bytes;
+  float *enc_scale[3], *enc_shift[3];      // folded BatchNorm (+conv bias) of the encoder convs
+  float *post_scale[5], *post_shift[5];
+  float *lstm_bias, *lstm_Whh;  // BiLSTM: [1][E][2*4Hh], [2*4Hh], [2][4Hh][Hh]
+  unsigned long long* prof_buf;            // [16] device, decoder phase cycles
+  // tensor-core decoder (decoder2)
+  __nv_bfloat16 *Watt_b, *Wdec_b;          // [2 hi/lo][4H permuted][KattP] / [2][4R][KdecP]
+  float* loc_conv_t;                       // [2][31][32]
+  float* loc_dense_t;                      // [32][A]
+  D2Weights d2w;
+  CUtensorMap map_w_att, map_w_dec;
+  int npass;
+  // tensor-core conv operands (bf16 hi/lo [2][Cout][k][Cin]) and their TMA descriptors
+  __nv_bfloat16 *enc_Wb[3], *post_Wb[5], *lstm_Wb, *attenc_Wb;
+  CUtensorMap enc_wmap[3], post_wmap[5], lstm_wmap, attenc_wmap;
+  // training: transposed (+tap-flipped) conv packs for the input gradients, [2][Cin][k][Cout]
+  __nv_bfloat16 *enc_WTb[3], *post_WTb[5], *lstm_WTb, *attenc_WTb;
+  CUtensorMap enc_wtmap[3], post_wtmap[5], lstm_wtmap, attenc_wtmap;
+  // training: transposed LSTMCell packs (tile-major [ktile][pblock][128][64], packed gate-row order) for the in-loop
+  // input-gradient GEMM; projection / prenet transposes for the bulk input gradients
+  __nv_bfloat16 *WTatt_b, *WTdec_b;
+  CUtensorMap map_wt_att, map_wt_dec;
+  int KattT, KdecT;                        // K padded to 128
+  __nv_bfloat16 *WprojT_b;                 // [2][KprojP][PROJ_LD]  (row k, contraction r = mel rows + gate row)
+  __nv_bfloat16 *W2T_b;                    // [2][P][P]  prenet.3.weight transposed
+};
+#define PROJ_LD 96
+
+
+inline const Param* find(const t2_ctx* c, const std::string& k) {
+  auto it = c->params.find(k);
+  return it == c->params.end() ? nullptr : &it->second;
+}
+inline float* find_grad(const t2_ctx* c, const std::string& k, long long numel) {
+  auto it = c->grads.find(k);
+  return (it == c->grads.end() || it->second.numel != numel) ? nullptr : it->second.ptr;
+}
+
+#define CHECK_CTX(name)                                                                        \
+  T2_REQUIRE(c, T2_ERR_ARG, name ": null context");                                            \
+  T2_REQUIRE(c->committed, T2_ERR_STATE, name ": weights not committed (call t2_ctx_commit)")
+#define RC(x) do { int _rc = (x); if (_rc) return _rc; } while (0)
+
+// implicit-GEMM conv on the tensor cores (capi.cu); scale/shift/keep/act as in ConvTcArgs
+int conv_tc(t2_ctx* c, const __nv_bfloat16* in, const CUtensorMap& wmap, int B, int T, int Cin, int Cout, int k, int NT, int act,
+            const float* scale, const float* shift, const unsigned char* keep, int keep_ld, float* out_f32,
+            __nv_bfloat16* out_b16, cudaStream_t st);
+int make_w_map(CUtensorMap* m, const __nv_bfloat16* w, int Cout, int Cin, int k, int NT, int npass);
+int make_in_map(CUtensorMap* m, const __nv_bfloat16* x, int B, int T, int Cin, int npass);

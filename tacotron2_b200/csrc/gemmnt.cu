@@ -1,0 +1,228 @@
+// Bulk NT GEMM on tcgen05 (see gemmnt.cuh).  One CTA per (128 x NT output tile, batch z, K split):
+// warp 0 = TMA producer, warp 1 = MMA issuer, all 8 warps = epilogue (TMEM -> registers -> fp32 partial slab).
+#include "gemmnt.cuh"
+
+#define GN_STAGES 3
+#define GN_A_TILE (128 * 64 * 2)
+#define GN_STAGE_BYTES (4 * GN_A_TILE)
+#define GN_TMEM_COLS 128
+
+namespace {
+
+__global__ void __launch_bounds__(256, 1) gemm_nt_kernel(const __grid_constant__ GemmNtArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* base = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint64_t* full = reinterpret_cast<uint64_t*>(base + GN_STAGES * GN_STAGE_BYTES);
+  uint64_t* empty = full + GN_STAGES;
+  uint64_t* accum = empty + GN_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 1);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int Nt = (a.N + a.NT - 1) / a.NT, Mt = (a.M + 127) >> 7;
+  const int mt = blockIdx.x / Nt, nt = blockIdx.x - mt * Nt;
+  const int z = blockIdx.y, sp = blockIdx.z;
+  const int m0 = mt * 128, n0 = nt * a.NT;
+  const int kin_blocks = (a.Kin + 63) >> 6;
+  const long long nkb_all = (long long)a.Kout * kin_blocks;
+  const int kb0 = (int)(nkb_all * sp / a.splitk), kb1 = (int)(nkb_all * (sp + 1) / a.splitk);
+  const int shift = a.shift0 + z * a.shift_step;
+  const uint32_t b_tile = (uint32_t)a.NT * 128u;
+
+  if (tid == 0) {
+    tc::prefetch_tmap(&a.a_map);
+    tc::prefetch_tmap(&a.b_map);
+    for (int i = 0; i < GN_STAGES; ++i) { tc::mbar_init(full + i, 1); tc::mbar_init(empty + i, 1); }
+    tc::mbar_init(accum, 1);
+    tc::fence_barrier_init();
+  }
+  if (warp == 1) tc::tmem_alloc<GN_TMEM_COLS>(tmem_slot);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  bool ok = true;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("fence.proxy.async;" ::: "memory");
+    int st = 0; uint32_t ph = 0;
+    const uint32_t tx = (uint32_t)(a.npass == 3 ? 2 : 1) * (GN_A_TILE + b_tile);
+    for (int kb = kb0; kb < kb1; ++kb) {
+      const int ko = kb / kin_blocks, ki = (kb - ko * kin_blocks) * 64;
+      if (!tc::mbar_wait(empty + st, ph ^ 1)) { ok = false; break; }
+      uint8_t* sp_ = base + (size_t)st * GN_STAGE_BYTES;
+      tc::mbar_arrive_expect_tx(full + st, tx);
+      tc::tma_load_4d(sp_, &a.a_map, full + st, ki, ko, m0 + z * a.a_zrow, 0);
+      tc::tma_load_4d(sp_ + 2 * GN_A_TILE, &a.b_map, full + st, ki + shift, ko, n0 + z * a.b_zrow, 0);
+      if (++st == GN_STAGES) { st = 0; ph ^= 1; }
+    }
+  } else if (warp == 1 && lane == 0) {
+    int st = 0; uint32_t ph = 0, acc = 0;
+    const uint32_t idesc = tc::idesc_bf16_f32(128, a.NT);
+    for (int kb = kb0; kb < kb1; ++kb) {
+      if (!tc::mbar_wait(full + st, ph)) { ok = false; break; }
+      tc::tc_fence_after();
+      const uint32_t sb = tc::smem_u32(base + (size_t)st * GN_STAGE_BYTES);
+      const uint64_t ahi = tc::smem_desc_sw128(sb), alo = tc::smem_desc_sw128(sb + GN_A_TILE);
+      const uint64_t bhi = tc::smem_desc_sw128(sb + 2 * GN_A_TILE), blo = tc::smem_desc_sw128(sb + 2 * GN_A_TILE + b_tile);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint64_t adv = (uint64_t)(k * 2);
+        if (a.npass == 3) {
+          tc::umma_bf16(tmem, alo + adv, bhi + adv, idesc, acc);
+          tc::umma_bf16(tmem, ahi + adv, blo + adv, idesc, 1u);
+          tc::umma_bf16(tmem, ahi + adv, bhi + adv, idesc, 1u);
+        } else {
+          tc::umma_bf16(tmem, ahi + adv, bhi + adv, idesc, acc);
+        }
+        acc = 1u;
+      }
+      tc::umma_commit(empty + st);
+      if (++st == GN_STAGES) { st = 0; ph ^= 1; }
+    }
+    tc::umma_commit(accum);
+  }
+  __syncwarp();
+  if (!tc::mbar_wait(accum, 0)) ok = false;
+  tc::tc_fence_after();
+  ok = __syncthreads_and(ok ? 1 : 0) != 0;
+
+  // epilogue: thread = output row (TMEM lane); 16-column chunks alternate between the two warp groups
+  const int q = warp & 3, row = 32 * q + lane;
+  const size_t ldp = (size_t)Nt * a.NT;
+  float* dst_row = a.partial + (((size_t)sp * a.nz + z) * Mt * 128 + m0 + row) * ldp + n0;
+  const bool empty_k = kb1 <= kb0;   // nothing accumulated: TMEM is undefined, write zeros
+#pragma unroll 1
+  for (int c = warp >> 2; c < a.NT / 16; c += 2) {
+    float v[16];
+    tc::tmem_ld16(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(c * 16), v);
+    tc::tmem_ld_wait();
+    float4* dst = reinterpret_cast<float4*>(dst_row + c * 16);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      dst[i] = (ok && !empty_k) ? make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tc::tmem_dealloc<GN_TMEM_COLS>(tmem);
+}
+
+__global__ void gemm_nt_reduce_kernel(const float* __restrict__ partial, int splitk, int nz, int Mp, int Np, int M, int N, GemmNtOut o) {
+  const long long total = (long long)nz * M * N;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int n = (int)(i % N);
+    const int m = (int)((i / N) % M);
+    const int z = (int)(i / ((long long)N * M));
+    float s = 0.f;
+    for (int sp = 0; sp < splitk; ++sp) s += partial[(((size_t)sp * nz + z) * Mp + m) * Np + n];
+    float* d = o.out + (size_t)m * o.ldm + (size_t)n * o.ldn + (size_t)z * o.ldz;
+    *d = o.accumulate ? *d + o.alpha * s : o.alpha * s;
+  }
+}
+
+// fp32 [nb][R][C] -> bf16 (hi,lo) [2][C][dst_ld] with batch bb at column offset bb*dst_boff (transposed); 32x32 tiles
+__global__ void transpose_split_kernel(const float* __restrict__ src, long long ld, long long src_bstride,
+                                       __nv_bfloat16* __restrict__ dst, int R, int C, int R_ld, long long dst_ld, long long dst_boff) {
+  __shared__ float tile[32][33];
+  const long long plane = (long long)C * dst_ld;
+  const int bb = blockIdx.z;
+  const float* s = src + (size_t)bb * src_bstride;
+  __nv_bfloat16* d = dst + (size_t)bb * dst_boff;
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int r = blockIdx.y * 32 + i;
+    tile[i][threadIdx.x] = (r < R && c < C) ? s[(size_t)r * ld + c] : 0.f;
+  }
+  __syncthreads();
+  const int r2 = blockIdx.y * 32 + threadIdx.x;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c2 = blockIdx.x * 32 + i;
+    if (r2 < R_ld && c2 < C) {
+      __nv_bfloat16 hi, lo;
+      tc::split_bf16(r2 < R ? tile[threadIdx.x][i] : 0.f, hi, lo);
+      d[(size_t)c2 * dst_ld + r2] = hi;
+      d[plane + (size_t)c2 * dst_ld + r2] = lo;
+    }
+  }
+}
+
+__global__ void transpose_bf16_kernel(const __nv_bfloat16* __restrict__ src, long long src_ld, long long src_bstride, long long src_plane,
+                                      __nv_bfloat16* __restrict__ dst, int R, int C, int R_ld, long long dst_ld, long long dst_boff) {
+  __shared__ __nv_bfloat16 tile[32][34];
+  const long long plane = (long long)C * dst_ld;
+  const int pl = blockIdx.z & 1, bb = blockIdx.z >> 1;
+  const __nv_bfloat16* s = src + (size_t)pl * src_plane + (size_t)bb * src_bstride;
+  __nv_bfloat16* d = dst + (size_t)pl * plane + (size_t)bb * dst_boff;
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int r = blockIdx.y * 32 + i;
+    tile[i][threadIdx.x] = (r < R && c < C) ? s[(size_t)r * src_ld + c] : __float2bfloat16(0.f);
+  }
+  __syncthreads();
+  const int r2 = blockIdx.y * 32 + threadIdx.x;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c2 = blockIdx.x * 32 + i;
+    if (r2 < R_ld && c2 < C) d[(size_t)c2 * dst_ld + r2] = r2 < R ? tile[threadIdx.x][i] : __float2bfloat16(0.f);
+  }
+}
+
+}  // namespace
+
+long long gemmnt_partial_floats(GemmNtArgs& a, int num_sms) {
+  const int Nt = (a.N + a.NT - 1) / a.NT, Mt = (a.M + 127) / 128;
+  const long long nkb = (long long)a.Kout * ((a.Kin + 63) / 64);
+  if (a.splitk <= 0) {
+    const long long tiles = (long long)Mt * Nt * a.nz;
+    long long sk = (2ll * num_sms + tiles - 1) / tiles;          // ~2 waves
+    sk = std::min<long long>(sk, std::max<long long>(1, nkb / 8));   // at least 8 K-blocks per CTA
+    sk = std::max<long long>(1, std::min<long long>(sk, 64));
+    a.splitk = (int)sk;
+  }
+  return (long long)a.splitk * a.nz * Mt * 128 * Nt * a.NT;
+}
+
+int gemmnt_launch(const GemmNtArgs& a, const GemmNtOut& o, cudaStream_t st) {
+  T2_REQUIRE(a.NT % 16 == 0 && a.NT >= 16 && a.NT <= 128 && a.splitk >= 1 && a.nz >= 1 && a.partial && o.out, T2_ERR_ARG,
+             "gemmnt: bad arguments NT=%d splitk=%d nz=%d", a.NT, a.splitk, a.nz);
+  if (a.M <= 0 || a.N <= 0) return T2_OK;
+  const int Nt = (a.N + a.NT - 1) / a.NT, Mt = (a.M + 127) / 128;
+  const size_t smem = 1024 + (size_t)GN_STAGES * GN_STAGE_BYTES + 128;
+  static bool attr_set = false;
+  if (!attr_set) {
+    T2_CHECK_CUDA(cudaFuncSetAttribute(gemm_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  dim3 grid((unsigned)(Mt * Nt), (unsigned)a.nz, (unsigned)a.splitk);
+  gemm_nt_kernel<<<grid, 256, smem, st>>>(a);
+  T2_CHECK_CUDA(cudaGetLastError());
+  const long long total = (long long)a.nz * a.M * a.N;
+  const int g = (int)std::min<long long>((total + 255) / 256, 148 * 8);
+  gemm_nt_reduce_kernel<<<g, 256, 0, st>>>(a.partial, a.splitk, a.nz, Mt * 128, Nt * a.NT, a.M, a.N, o);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+
+int gemmnt_make_map(CUtensorMap* m, const __nv_bfloat16* base, int Kin, int kin_ld, int Kout, int rows, long long plane_elems,
+                    int box_rows, int npass) {
+  T2_REQUIRE(kin_ld % 8 == 0 && ((uintptr_t)base & 15) == 0, T2_ERR_ARG, "gemmnt: operand stride %d / base not 16-byte aligned", kin_ld);
+  unsigned long long dims[4] = {(unsigned long long)Kin, (unsigned long long)Kout, (unsigned long long)rows, 2ull};
+  unsigned long long st[3] = {(unsigned long long)kin_ld * 2, (unsigned long long)Kout * kin_ld * 2, (unsigned long long)plane_elems * 2};
+  unsigned box[4] = {64u, 1u, (unsigned)box_rows, npass == 3 ? 2u : 1u};
+  return tc_make_tmap_bf16(m, base, 4, dims, st, box);
+}
+
+int transpose_split_launch(const float* src, long long ld, long long src_bstride, __nv_bfloat16* dst, int R, int C, int R_ld,
+                           long long dst_ld, long long dst_boff, int nbatch, cudaStream_t st) {
+  if (R_ld <= 0 || C <= 0 || nbatch <= 0) return T2_OK;
+  dim3 grid((C + 31) / 32, (R_ld + 31) / 32, nbatch), block(32, 8);
+  transpose_split_kernel<<<grid, block, 0, st>>>(src, ld, src_bstride, dst, R, C, R_ld, dst_ld, dst_boff);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+
+int transpose_bf16_launch(const __nv_bfloat16* src, long long src_ld, long long src_bstride, long long src_plane, __nv_bfloat16* dst,
+                          int R, int C, int R_ld, long long dst_ld, long long dst_boff, int nbatch, cudaStream_t st) {
+  if (R_ld <= 0 || C <= 0 || nbatch <= 0) return T2_OK;
+  dim3 grid((C + 31) / 32, (R_ld + 31) / 32, 2 * nbatch), block(32, 8);
+  transpose_bf16_kernel<<<grid, block, 0, st>>>(src, src_ld, src_bstride, src_plane, dst, R, C, R_ld, dst_ld, dst_boff);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}

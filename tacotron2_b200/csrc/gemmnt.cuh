@@ -1,0 +1,43 @@
+// Bulk "NT" GEMM on tcgen05 for the training path: C[z][m][n] = sum_k A[m + z*a_zrow][k] * B[n + z*b_zrow][k(+shift_z)]
+// with BOTH operands K-major bf16 (hi,lo) planes fetched by TMA.  The contraction index is two-level (kin, kout), e.g.
+// (time, utterance): per kout the kin range is walked in 64-element blocks and the B operand's kin coordinate can be
+// shifted per z (conv taps, the h_{t-1} shift of a recurrent weight gradient); out-of-range elements are zero-filled by
+// TMA, which is exactly the conv zero padding / the zero initial state.  Split-K partials go to fp32 slabs that a second
+// kernel reduces in a fixed order (deterministic) into an arbitrarily strided destination.
+// Used for: LSTMCell / BiLSTM / conv / linear weight gradients and the bulk input gradients of the teacher-forced
+// backward pass (the reference gets these from autograd over model/tacotron2.py:155-347).
+#pragma once
+#include "tc.cuh"
+
+struct GemmNtArgs {
+  CUtensorMap a_map;   // dims {Kin, Kout, Mrows, 2}, box {64, 1, 128, npass==3 ? 2 : 1}
+  CUtensorMap b_map;   // dims {Kin, Kout, Nrows, 2}, box {64, 1, NT, ...}
+  int M, N, NT;        // logical output size; tiles = ceil(M/128) x ceil(N/NT)
+  int Kin, Kout;
+  int nz, shift0, shift_step;   // B kin shift for batch z: shift0 + z*shift_step
+  int a_zrow, b_zrow;           // operand row offsets per z
+  int splitk, npass;
+  float* partial;               // [splitk][nz][Mt*128][Nt*NT]
+};
+
+struct GemmNtOut {
+  float* out;
+  long long ldm, ldn, ldz;   // element strides of the destination
+  float alpha;
+  int accumulate;            // 1: out += alpha * sum, 0: out = alpha * sum
+};
+
+// Chooses splitk (stored into a.splitk) unless already > 0; returns partial-buffer floats needed.
+long long gemmnt_partial_floats(GemmNtArgs& a, int num_sms);
+int gemmnt_launch(const GemmNtArgs& a, const GemmNtOut& o, cudaStream_t st);
+
+// Operand maps for a K-major bf16 (hi,lo) matrix stored as [2][rows][Kout][kin_ld] (kin contiguous, kin_ld % 8 == 0).
+int gemmnt_make_map(CUtensorMap* m, const __nv_bfloat16* base, int Kin, int kin_ld, int Kout, int rows, long long plane_elems,
+                    int box_rows, int npass);
+
+// Batched transposes into K-major operands.  Batch bb reads src + bb*src_bstride ([R][C], row stride ld) and writes
+// dst[plane][c][bb*dst_boff + r] for r < R_ld (zeros for r >= R); dst row stride dst_ld, plane stride C*dst_ld.
+int transpose_split_launch(const float* src, long long ld, long long src_bstride, __nv_bfloat16* dst, int R, int C, int R_ld,
+                           long long dst_ld, long long dst_boff, int nbatch, cudaStream_t st);
+int transpose_bf16_launch(const __nv_bfloat16* src, long long src_ld, long long src_bstride, long long src_plane, __nv_bfloat16* dst,
+                          int R, int C, int R_ld, long long dst_ld, long long dst_boff, int nbatch, cudaStream_t st);

@@ -126,10 +126,15 @@ class Postnet(nn.Module):
             layers.append(nn.Dropout(dropout))
         self.postnet = nn.Sequential(*layers)
 
-    def forward(self, X):
-        """X (B,M,T) -> (B,M,T), as the reference; internally channels-last."""
+    def forward(self, X, dropout_keep=None):
+        """X (B,M,T) -> (B,M,T), as the reference; internally channels-last.  ``dropout_keep``: optional (5,B,T,postnet_dim)
+        uint8 keep-masks for the train-mode dropouts (parity tests)."""
         o = _owner_of(self)
         x = X.transpose(1, 2).contiguous()
+        if self.training:
+            from .autograd import PostnetFn
+            keep = None if dropout_keep is None else dropout_keep.to(device=x.device, dtype=torch.uint8).contiguous()
+            return PostnetFn.apply(o, keep, o._draw_seed(), x, *o._group_params("postnet").values()).transpose(1, 2)
         return o._postnet(x, x.shape[1], None).transpose(1, 2)
 
 
@@ -235,6 +240,35 @@ class Tacotron2(nn.Module):
         if self._ws is None or self._ws.numel() < need or self._ws.device != device:
             self._ws = torch.empty(need, dtype=torch.uint8, device=device)
         return self._ws
+
+    _GROUPS = {
+        "postnet": ("postnet.",),
+        "decoder": ("decoder.", "prenet."),
+        "memory": ("att_encoder.", "speaker_embedding.", "description_embeddings_linear."),
+        "encoder": ("encoder.",),
+    }
+
+    def _group_params(self, group):
+        """Parameters of one gradient bucket, in registration order (key -> Parameter)."""
+        pre = self._GROUPS[group]
+        return {k: p for k, p in self.named_parameters() if k.startswith(pre)}
+
+    def _train_workspace(self, lib, device, B, L, T):
+        need = lib.t2_train_workspace_bytes(self._ctx, B, L, T)
+        if need < 0:
+            raise RuntimeError("t2_train_workspace_bytes failed")
+        if self._ws is None or self._ws.numel() < need or self._ws.device != device:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=device)
+        return self._ws
+
+    @staticmethod
+    def _draw_seed():
+        return int(torch.randint(0, 2**62, (1,)).item())  # CPU generator: follows torch.manual_seed like run/say.py:40
+
+    def loss(self, mels, mels_post, gates, mel_target, gate_target):
+        """training_step loss (model/tts_model.py:197-201) as one kernel: BCEWithLogits + MSE + MSE."""
+        from .autograd import LossFn
+        return LossFn.apply(self, mels, mels_post, gates, mel_target, gate_target)
 
     @staticmethod
     def _u8(t, device):
