@@ -54,7 +54,7 @@ class PostnetFn(torch.autograd.Function):
         out = torch.empty(B, T, M, device=x.device)
         _lib.check(lib.t2_postnet_train_fwd(owner._ctx, P(x), T, B, T, P(keep), seed, P(out), P(tape), tape.numel(), P(ws), ws.numel(),
                                             _stream()), "t2_postnet_train_fwd")
-        owner._sig = None  # running statistics changed in place: re-fold them before the next eval() forward
+        owner._bn_dirty = True  # running statistics changed in place: re-fold them before the next eval() forward
         ctx.owner, ctx.keep, ctx.seed, ctx.tape, ctx.shape = owner, keep, seed, tape, (B, T, M)
         return out
 

@@ -69,6 +69,7 @@ struct PrenetArgs {
   const unsigned char* k1; const unsigned char* k2;
   unsigned long long seed; float p; int N, M, P, mode, B, T; float* out;
   __nv_bfloat16* out_b;  // mode 2: bf16 (hi,lo) [T+1][2][D2_BP][P] for the tensor-core decoder
+  float* p1_out;         // optional [N][P]: layer-1 output after dropout (training tape)
 };
 #define PN_ROWS 8
 __global__ void __launch_bounds__(256) prenet_rows_kernel(PrenetArgs a) {
@@ -115,7 +116,7 @@ __global__ void __launch_bounds__(256) prenet_rows_kernel(PrenetArgs a) {
           const unsigned char* km = layer ? a.k2 : a.k1;
           const bool keep = km ? (km[kidx] != 0) : rng_keep(a.seed, ridx, a.p);
           const float v = (acc[r] > 0.f && keep) ? acc[r] * scale : 0.f;
-          if (layer == 0) hs[r * P + o] = v;  // safe: each thread writes only its own o, read after the barrier
+          if (layer == 0) { hs[r * P + o] = v; if (a.p1_out) a.p1_out[(size_t)n * P + o] = v; }  // each thread writes only its own o
           else if (a.mode == 0) a.out[(size_t)n * P + o] = v;
           else {
             const int t = n / a.B, b = n % a.B;
@@ -206,6 +207,17 @@ __global__ void conv_t_kernel(const float* w /*[32][2][31]*/, float* out /*[2][3
   if (i >= 32 * 2 * 31) return;
   const int f = i % 32, j = (i / 32) % 31, c = i / (32 * 31);
   out[i] = w[(f * 2 + c) * 31 + j];
+}
+// controls (B,C) -> bf16 (hi,lo) columns [col0, col0+C) of every slot of x[nslots][2][BP][ld]
+__global__ void controls_slots_kernel(const float* src, int C, __nv_bfloat16* dst, long long plane, int ld, int col0, int B, int nslots) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)nslots * B * C; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C), b = (int)((i / C) % B), sl = (int)(i / ((long long)C * B));
+    __nv_bfloat16 hi, lo;
+    tc::split_bf16(src[(size_t)b * C + c], hi, lo);
+    __nv_bfloat16* x = dst + (size_t)sl * 2 * plane;
+    x[(size_t)b * ld + col0 + c] = hi;
+    x[plane + (size_t)b * ld + col0 + c] = lo;
+  }
 }
 // fp32 row-major (B,dim) -> bf16 (hi,lo) columns [col0, col0+dim) of x[2][BP][ld]
 __global__ void rm_to_xsplit_kernel(const float* src, int lds, __nv_bfloat16* dst, long long plane, int ld, int col0, int dim, int B) {
@@ -572,7 +584,7 @@ static State2Plan plan_state2(const D2Dims& d, int L, Arena& ar) {
   return pl;
 }
 
-static D2Dims dims2(const t2_ctx* c, int B, int L) {
+D2Dims dims2(const t2_ctx* c, int B, int L) {
   D2Dims d{};
   d.B = B; d.L = L; d.EF = c->EF; d.H = c->H; d.R = c->R; d.P = c->P; d.A = c->A; d.M = c->M; d.C = c->C;
   d.KattP = c->dd.KattP; d.KdecP = c->dd.KdecP; d.KprojP = c->dd.KprojP;
@@ -581,19 +593,19 @@ static D2Dims dims2(const t2_ctx* c, int B, int L) {
 }
 
 // activation tensor maps: x[4 = parity*2 + hl][BP][K] bf16, box {64, 64, 1|2}
-static int make_xmaps(const t2_ctx* c, const D2Dims& d, const D2State& s, const __nv_bfloat16* tfp, int T1, D2Maps* m) {
+static int make_xmaps(const t2_ctx* c, const D2Dims& d, const D2State& s, const __nv_bfloat16* tfp, int T1, D2Maps* m, int nslots = 2) {
   const unsigned zb = d.npass == 3 ? 2u : 1u;
   unsigned box[3] = {TG_BK, TG_N, zb};
   int rc;
   {
-    unsigned long long dims[3] = {(unsigned long long)d.KattP, (unsigned long long)D2_BP, 4ull};
+    unsigned long long dims[3] = {(unsigned long long)d.KattP, (unsigned long long)D2_BP, 2ull * nslots};
     unsigned long long st[2] = {(unsigned long long)d.KattP * 2, (unsigned long long)D2_BP * d.KattP * 2};
     if ((rc = tc_make_tmap_bf16(&m->x_att, s.xatt, 3, dims, st, box))) return rc;
-    unsigned long long dims_r[3] = {(unsigned long long)(d.KattP - d.P), (unsigned long long)D2_BP, 4ull};
+    unsigned long long dims_r[3] = {(unsigned long long)(d.KattP - d.P), (unsigned long long)D2_BP, 2ull * nslots};
     if ((rc = tc_make_tmap_bf16(&m->x_att_rest, s.xatt + d.P, 3, dims_r, st, box))) return rc;
   }
   {
-    unsigned long long dims[3] = {(unsigned long long)d.KdecP, (unsigned long long)D2_BP, 4ull};
+    unsigned long long dims[3] = {(unsigned long long)d.KdecP, (unsigned long long)D2_BP, 2ull * nslots};
     unsigned long long st[2] = {(unsigned long long)d.KdecP * 2, (unsigned long long)D2_BP * d.KdecP * 2};
     if ((rc = tc_make_tmap_bf16(&m->x_dec, s.xdec, 3, dims, st, box))) return rc;
   }
@@ -609,12 +621,11 @@ static int make_xmaps(const t2_ctx* c, const D2Dims& d, const D2State& s, const 
   return T2_OK;
 }
 
-static int fill_controls2(const D2Dims& d, D2State& s, const float* controls, int B, cudaStream_t st) {
+static int fill_controls2(const D2Dims& d, D2State& s, const float* controls, int B, cudaStream_t st, int nslots = 2) {
   if (d.C == 0) return T2_OK;
   T2_REQUIRE(controls, T2_ERR_ARG, "Controls are enabled, but no control vector was passed to the model!");  // model/tacotron2.py:183-185
   const long long pd = (long long)D2_BP * d.KdecP;
-  for (int par = 0; par < 2; ++par)
-    rm_to_xsplit_kernel<<<gsz(B * d.C), 256, 0, st>>>(controls, d.C, s.xdec + (size_t)par * 2 * pd, pd, d.KdecP, d.H + d.EF, d.C, B);
+  controls_slots_kernel<<<gsz((long long)nslots * B * d.C), 256, 0, st>>>(controls, d.C, s.xdec, pd, d.KdecP, d.H + d.EF, B, nslots);
   copy2d_kernel<<<gsz(B * d.C), 256, 0, st>>>(controls, d.C, s.projin + d.R + d.EF, d.KprojP, B, d.C);
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
@@ -623,25 +634,34 @@ static int fill_controls2(const D2Dims& d, D2State& s, const float* controls, in
 static int decode2_impl(t2_ctx* c, bool tf, const float* memory, const float* pmem, const unsigned char* mask, const float* controls,
                         const float* mel_target, int B, int L, int T, const unsigned char* prenet_keep, int train,
                         const unsigned char* att_keep, const unsigned char* rnn_keep, unsigned long long seed, float* mels,
-                        float* gates, float* aligns, long long* lengths, int* n_frames, Arena& ar, cudaStream_t st) {
+                        float* gates, float* aligns, long long* lengths, int* n_frames, Arena& ar, cudaStream_t st,
+                        const DecTape* tape) {
   D2Dims d = dims2(c, B, L);
   State2Plan pl = plan_state2(d, L, ar);
-  __nv_bfloat16* tfp = tf ? ar.take<__nv_bfloat16>((size_t)(T + 1) * 2 * D2_BP * d.P) : nullptr;
+  __nv_bfloat16* tfp = (tf && !tape) ? ar.take<__nv_bfloat16>((size_t)(T + 1) * 2 * D2_BP * d.P) : nullptr;
   if (!ar.base) return T2_OK;
   T2_REQUIRE(!ar.overflow, T2_ERR_WORKSPACE, "t2_decode: workspace too small");
   T2_CHECK_CUDA(cudaMemsetAsync(pl.zero_begin, 0, pl.zero_bytes, st));
   D2State s = pl.s;
   s.prof = c->prof_buf;
   T2_CHECK_CUDA(cudaMemsetAsync(c->prof_buf, 0, 16 * sizeof(unsigned long long), st));
-  RC(fill_controls2(d, s, controls, B, st));
+  const int nslots = tape ? T + 1 : 2;
+  if (tape) {  // training: every per-frame buffer keeps its whole history
+    T2_CHECK_CUDA(cudaMemsetAsync(tape->zero_begin, 0, tape->zero_bytes, st));
+    tfp = tape->tfp;
+    s.xatt = tape->xatt; s.xdec = tape->xdec; s.q = tape->q; s.w_prev = tape->w_hist; s.w_cum = tape->wcum_hist;
+    s.sav_att = tape->sav_att; s.sav_dec = tape->sav_dec;
+  }
+  RC(fill_controls2(d, s, controls, B, st, nslots));
   D2IO io{};
   io.memory = memory; io.pmem = pmem; io.mask = mask; io.prenet_keep = prenet_keep;
   io.att_keep = att_keep; io.rnn_keep = rnn_keep; io.mels = mels; io.gates = gates; io.aligns = aligns;
   io.Tmax = T; io.n_steps = T; io.t0 = 0; io.seed = seed; io.hidden_dropout = train ? 1 : 0;
   io.debug_barrier = getenv("T2B200_DEBUG_BARRIER") ? 1 : 0;
+  io.hist = tape ? 1 : 0;
   if (tf) {
-    T2_CHECK_CUDA(cudaMemsetAsync(tfp, 0, (size_t)(T + 1) * 2 * D2_BP * d.P * sizeof(__nv_bfloat16), st));
-    PrenetArgs pa{mel_target, c->d2w.W1, c->d2w.W2, prenet_keep, prenet_keep, seed, d.p_prenet, (T + 1) * B, d.M, d.P, 2, B, T, nullptr, tfp};
+    if (!tape) T2_CHECK_CUDA(cudaMemsetAsync(tfp, 0, (size_t)(T + 1) * 2 * D2_BP * d.P * sizeof(__nv_bfloat16), st));
+    PrenetArgs pa{mel_target, c->d2w.W1, c->d2w.W2, prenet_keep, prenet_keep, seed, d.p_prenet, (T + 1) * B, d.M, d.P, 2, B, T, nullptr, tfp, tape ? tape->p1 : nullptr};
     prenet_rows_kernel<<<std::min(((T + 1) * B + PN_ROWS - 1) / PN_ROWS, 148 * 4), 256, PN_ROWS * (d.M + d.P) * sizeof(float), st>>>(pa);
     T2_CHECK_CUDA(cudaGetLastError());
     io.teacher_forcing = 1; io.stop_enabled = 0;
@@ -652,7 +672,7 @@ static int decode2_impl(t2_ctx* c, bool tf, const float* memory, const float* pm
     s.n_frames = n_frames;
   }
   D2Maps maps;
-  RC(make_xmaps(c, d, s, tfp, T + 1, &maps));
+  RC(make_xmaps(c, d, s, tfp, T + 1, &maps, nslots));
   return d2_launch(d, c->d2w, s, io, maps, st);
 }
 
@@ -707,7 +727,7 @@ extern "C" int t2_decode_ar(t2_ctx* c, const float* memory, const float* process
   Arena ar(ws, ws_bytes);
   return decode2_impl(c, false, memory, processed_memory, mask, controls, nullptr, B, L, max_len, prenet_keep,
                                                  0, nullptr, nullptr, seed, mels, gates, alignments, lengths, n_frames, ar,
-                                                 (cudaStream_t)stream);
+                                                 (cudaStream_t)stream, nullptr);
 }
 
 extern "C" int t2_decode_tf(t2_ctx* c, const float* memory, const float* processed_memory, const unsigned char* mask,
@@ -721,7 +741,33 @@ extern "C" int t2_decode_tf(t2_ctx* c, const float* memory, const float* process
   Arena ar(ws, ws_bytes);
   return decode2_impl(c, true, memory, processed_memory, mask, controls, mel_target, B, L, T, prenet_keep,
                                                  train, att_keep, rnn_keep, seed, mels, gates, alignments, nullptr, nullptr, ar,
-                                                 (cudaStream_t)stream);
+                                                 (cudaStream_t)stream, nullptr);
+}
+
+extern "C" long long t2_decode_tape_bytes(const t2_ctx* c, int B, int L, int T) {
+  if (!c || B <= 0 || L <= 0 || T <= 0) return -1;
+  Arena ar(nullptr, 0);
+  plan_dec_tape(dims2(c, B, L), B, L, T, ar);
+  return ar.off + 1024;
+}
+
+// Teacher-forced frame loop under train(): same kernel in history mode (every per-frame buffer, the LSTM gate activations,
+// queries and attention weights are kept on the tape for t2_decode_tf_bwd); hidden-state dropouts p = 0.1 are active.
+extern "C" int t2_decode_tf_train_fwd(t2_ctx* c, const float* memory, const float* processed_memory, const unsigned char* mask,
+                                      const float* controls, const float* mel_target, int B, int L, int T,
+                                      const unsigned char* prenet_keep, const unsigned char* att_keep, const unsigned char* rnn_keep,
+                                      unsigned long long seed, float* mels, float* gates, float* alignments, void* tape,
+                                      long long tape_bytes, void* ws, long long ws_bytes, void* stream) {
+  CHECK_CTX("t2_decode_tf_train_fwd");
+  T2_REQUIRE(memory && processed_memory && mask && mel_target && mels && gates && alignments && ws && tape, T2_ERR_ARG,
+             "Ground-truth Mel spectrogram is required for teacher forcing");
+  T2_REQUIRE(B > 0 && L > 0 && T > 0, T2_ERR_ARG, "t2_decode_tf_train_fwd: bad sizes");
+  Arena ta(tape, tape_bytes);
+  DecTape tp = plan_dec_tape(dims2(c, B, L), B, L, T, ta);
+  T2_REQUIRE(!ta.overflow, T2_ERR_WORKSPACE, "t2_decode_tf_train_fwd: tape too small");
+  Arena ar(ws, ws_bytes);
+  return decode2_impl(c, true, memory, processed_memory, mask, controls, mel_target, B, L, T, prenet_keep, 1, att_keep, rnn_keep, seed,
+                      mels, gates, alignments, nullptr, nullptr, ar, (cudaStream_t)stream, &tp);
 }
 
 extern "C" int t2_decoder_step(t2_ctx* c, const float* prev_mel_prenet, const float* att_h, const float* att_c, const float* att_ctx,
@@ -745,7 +791,7 @@ extern "C" int t2_prenet_fwd(t2_ctx* c, const float* x, const unsigned char* kee
   CHECK_CTX("t2_prenet_fwd");
   T2_REQUIRE(x && out && N > 0, T2_ERR_ARG, "t2_prenet_fwd: bad argument");
   (void)ws; (void)ws_bytes;
-  PrenetArgs pa{x, c->d2w.W1, c->d2w.W2, keep1, keep2, seed, c->cfg.dropout, N, c->M, c->P, 0, 0, 0, out, nullptr};
+  PrenetArgs pa{x, c->d2w.W1, c->d2w.W2, keep1, keep2, seed, c->cfg.dropout, N, c->M, c->P, 0, 0, 0, out, nullptr, nullptr};
   prenet_rows_kernel<<<std::min((N + PN_ROWS - 1) / PN_ROWS, 148 * 4), 256, PN_ROWS * (c->M + c->P) * sizeof(float),
                        (cudaStream_t)stream>>>(pa);
   T2_CHECK_CUDA(cudaGetLastError());
@@ -801,7 +847,7 @@ extern "C" long long t2_workspace_bytes(const t2_ctx* cc, int B, int L, int T) {
   { Arena a(nullptr, 0); encoder_impl(c, nullptr, nullptr, B, L, 0, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
   { Arena a(nullptr, 0); memory_impl(c, nullptr, nullptr, nullptr, B, L, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
   { Arena a(nullptr, 0); decode2_impl(c, true, nullptr, nullptr, nullptr, nullptr, nullptr, B, L, std::max(T, 1), nullptr, 0, nullptr, nullptr, 0,
-                                     nullptr, nullptr, nullptr, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
+                                     nullptr, nullptr, nullptr, nullptr, nullptr, a, nullptr, nullptr); best = std::max<long long>(best, a.off); }
   { Arena a(nullptr, 0); postnet_impl(c, nullptr, std::max(T, 1), B, std::max(T, 1), 0, nullptr, nullptr, a, nullptr); best = std::max<long long>(best, a.off); }
   return best + 1024;
 }

@@ -71,3 +71,34 @@ int conv_tc(t2_ctx* c, const __nv_bfloat16* in, const CUtensorMap& wmap, int B, 
             __nv_bfloat16* out_b16, cudaStream_t st);
 int make_w_map(CUtensorMap* m, const __nv_bfloat16* w, int Cout, int Cin, int k, int NT, int npass);
 int make_in_map(CUtensorMap* m, const __nv_bfloat16* x, int B, int T, int Cin, int npass);
+
+// ---- teacher-forced decoder tape (history-mode buffers written by the forward, read by the backward)
+struct DecTape {
+  __nv_bfloat16* tfp;    // [T+1][2][BP][P]      prenet outputs (bf16 hi,lo)
+  __nv_bfloat16* xatt;   // [T+1][2][BP][KattP]  slot t = attention-LSTM input of frame t: [- | ctx_{t-1} | att_h_{t-1}]
+  __nv_bfloat16* xdec;   // [T+1][2][BP][KdecP]  slot t = decoder-LSTM input of frame t: [att_h_t | ctx_t | controls | rnn_h_{t-1}]
+  float* p1;             // [(T+1)*B][P]         prenet layer-1 output (after dropout), row n = t*B + b
+  float* sav_att;        // [T][5][H][BP]
+  float* sav_dec;        // [T][5][R][BP]
+  float* q;              // [T][BP][A]
+  float* w_hist;         // [T+1][BP][L]
+  float* wcum_hist;      // [T+1][BP][L]
+  char* zero_begin; size_t zero_bytes;   // region that must be zeroed before the forward
+};
+inline DecTape plan_dec_tape(const D2Dims& d, int B, int L, int T, Arena& ar) {
+  DecTape t{};
+  const int64_t off0 = ar.off;
+  t.tfp = ar.take<__nv_bfloat16>((size_t)(T + 1) * 2 * D2_BP * d.P);
+  t.xatt = ar.take<__nv_bfloat16>((size_t)(T + 1) * 2 * D2_BP * d.KattP);
+  t.xdec = ar.take<__nv_bfloat16>((size_t)(T + 1) * 2 * D2_BP * d.KdecP);
+  t.w_hist = ar.take<float>((size_t)(T + 1) * D2_BP * L);
+  t.wcum_hist = ar.take<float>((size_t)(T + 1) * D2_BP * L);
+  t.zero_begin = ar.base ? ar.base + off0 : nullptr;
+  t.zero_bytes = (size_t)(ar.off - off0);
+  t.p1 = ar.take<float>((size_t)(T + 1) * B * d.P);
+  t.sav_att = ar.take<float>((size_t)T * 5 * d.H * D2_BP);
+  t.sav_dec = ar.take<float>((size_t)T * 5 * d.R * D2_BP);
+  t.q = ar.take<float>((size_t)T * D2_BP * d.A);
+  return t;
+}
+D2Dims dims2(const t2_ctx* c, int B, int L);

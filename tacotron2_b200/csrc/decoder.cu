@@ -149,7 +149,7 @@ __device__ __forceinline__ void store_split(__nv_bfloat16* base, long long plane
 
 __device__ __forceinline__ void lstm_tail(const float* part, uint32_t rank, int unit0, const float* __restrict__ bias, int H,
                                           float* cst, int B, const HOut& ho, const unsigned char* keep, bool hidden_dropout,
-                                          unsigned long long seed, unsigned long long rng_base) {
+                                          unsigned long long seed, unsigned long long rng_base, float* sav) {
   const int ul = threadIdx.x >> 5, bp = threadIdx.x & 31;
   const int u = unit0 + ul;
   float2 pre[4];
@@ -165,9 +165,14 @@ __device__ __forceinline__ void lstm_tail(const float* part, uint32_t rank, int 
     if (b >= B) continue;
     const float pi = j ? pre[0].y : pre[0].x, pf = j ? pre[1].y : pre[1].x;
     const float pg = j ? pre[2].y : pre[2].x, po = j ? pre[3].y : pre[3].x;
-    const float c = sigmoid_fast(pf) * cst[ul * D2_BP + b] + sigmoid_fast(pi) * tanh_fast(pg);
-    float h = sigmoid_fast(po) * tanh_fast(c);
+    const float si = sigmoid_fast(pi), sf = sigmoid_fast(pf), tg = tanh_fast(pg), so = sigmoid_fast(po);
+    const float c = sf * cst[ul * D2_BP + b] + si * tg;
+    float h = so * tanh_fast(c);
     cst[ul * D2_BP + b] = c;
+    if (sav) {  // training tape: [5][H][BP]
+      const size_t o = (size_t)u * D2_BP + b, gs = (size_t)H * D2_BP;
+      sav[o] = si; sav[gs + o] = sf; sav[2 * gs + o] = tg; sav[3 * gs + o] = so; sav[4 * gs + o] = c;
+    }
     if (hidden_dropout) {  // nn.Dropout(0.1), train only (model/decoder.py:75,101)
       const bool k = keep ? (keep[(size_t)b * H + u] != 0) : rng_keep(seed, rng_base + (unsigned long long)b * H + u, 0.1f);
       h = k ? h * (1.0f / 0.9f) : 0.f;
@@ -198,11 +203,10 @@ __device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) 
 //                                         e_full[L] | red[64] | cred[4*cols]
 #define ATT_MARK(slot) do { if (blockIdx.x == 0 && threadIdx.x == 0 && s.prof) { const long long now_ = clock64(); s.prof[slot] += (unsigned long long)(now_ - *prof_last); *prof_last = now_; } } while (0)
 __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& io, const Smem& sm, float* scratch, bool active,
-                                int b, int part, int S, int cur, int t_out, long long* prof_last) {
+                                int b, int part, int S, int cur, int nxt, int t_out, long long* prof_last) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int L = d.L, A = d.A, EF = d.EF;
   const int Lc = (L + S - 1) / S, l0 = part * Lc, l1 = min(L, l0 + Lc), nl = max(0, l1 - l0);
-  const int nxt = cur ^ 1;
   float* q_s = scratch;
   float* wp = q_s + A;                            // previous / cumulative weights with a 15-tap halo
   float* wc = wp + ((Lc + 35) & ~3);
@@ -215,7 +219,7 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
     const float* wprev = s.w_prev + ((size_t)cur * D2_BP + b) * L;
     const float* wcum = s.w_cum + ((size_t)cur * D2_BP + b) * L;
 #pragma unroll 1
-    for (int i = tid; i < A; i += D2_THREADS) q_s[i] = ld_cg(s.q + (size_t)b * A + i);
+    for (int i = tid; i < A; i += D2_THREADS) q_s[i] = ld_cg(s.q + (io.hist ? (size_t)t_out * D2_BP * A : 0) + (size_t)b * A + i);
 #pragma unroll 1
     for (int i = tid; i < nl + 30; i += D2_THREADS) {
       const int l = l0 + i - 15;
@@ -453,8 +457,8 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
 
 #pragma unroll 1
   for (int t = 0; t < io.n_steps && alive && !stop; ++t) {
-    const int cur = t & 1, nxt = cur ^ 1;
     const int tg_ = io.t0 + t;
+    const int cur = io.hist ? tg_ : (t & 1), nxt = io.hist ? tg_ + 1 : (cur ^ 1);
 #pragma unroll 1
     for (int ph = 0; ph < nphase && alive && !stop; ++ph) {
       bool wrote_x = false;  // this phase stored operands that a later phase reads through TMA
@@ -477,11 +481,12 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
         const unsigned char* keep = att ? io.att_keep : io.rnn_keep;
         lstm_tail(sm.part, rank, unit0, att ? w.batt : w.bdec, d.H, att ? sm.c_att : sm.c_dec, B, ho,
                   keep ? keep + (size_t)tg_ * B * d.H : nullptr, io.hidden_dropout != 0, io.seed,
-                  ((att ? 1ull : 2ull) << 40) + (unsigned long long)tg_ * B * d.H);
+                  ((att ? 1ull : 2ull) << 40) + (unsigned long long)tg_ * B * d.H,
+                  (att ? s.sav_att : s.sav_dec) ? (att ? s.sav_att : s.sav_dec) + (size_t)tg_ * 5 * d.H * D2_BP : nullptr);
         wrote_x = true;
       } else if (ph == PH_ATTN) {
         // ---- location-sensitive attention (model/attention.py:54-67, model/decoder.py:90)
-        attention_phase(d, s, io, sm, scratch, att_active, att_b, att_part, S, cur, tg_, &prof_last);
+        attention_phase(d, s, io, sm, scratch, att_active, att_b, att_part, S, cur, nxt, tg_, &prof_last);
         wrote_x = true;
       } else {
         // ---- small dense phases: query (model/attention.py:52), mel/gate projection (model/decoder.py:103-109),
@@ -496,7 +501,7 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
           const int r = o.r, b = o.b;
           float v = o.v;
           if (ph == PH_QUERY) {
-            s.q[(size_t)b * d.A + r] = v;
+            s.q[(io.hist ? (size_t)tg_ * D2_BP * d.A : 0) + (size_t)b * d.A + r] = v;
           } else if (ph == PH_PROJ) {
             v += __ldg(w.bproj + r);
             if (r < d.M) {

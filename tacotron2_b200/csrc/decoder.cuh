@@ -52,6 +52,9 @@ struct D2State {
   int* n_frames;         // [1]
   unsigned* barrier;     // [2]
   unsigned long long* prof;  // [16] or null
+  // history mode (training tape): xatt/xdec/w_prev/w_cum hold T+1 slots and q holds T slots instead of two parities
+  float* sav_att;        // [T][5][H][BP] i,f,g,o (post-activation), c of the attention LSTMCell, or null
+  float* sav_dec;        // [T][5][R][BP]
 };
 
 struct D2IO {
@@ -67,6 +70,7 @@ struct D2IO {
   int Tmax, n_steps, t0;
   int teacher_forcing, hidden_dropout, stop_enabled;
   int debug_barrier;  // adds one empty grid barrier per frame and times it (profiling only)
+  int hist;           // 1: state buffers are indexed by frame (slot t / t+1) instead of parity -- the training tape
   unsigned long long seed;
 };
 

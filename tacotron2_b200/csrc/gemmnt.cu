@@ -145,7 +145,8 @@ __global__ void transpose_split_kernel(const float* __restrict__ src, long long 
 }
 
 __global__ void transpose_bf16_kernel(const __nv_bfloat16* __restrict__ src, long long src_ld, long long src_bstride, long long src_plane,
-                                      __nv_bfloat16* __restrict__ dst, int R, int C, int R_ld, long long dst_ld, long long dst_boff) {
+                                      __nv_bfloat16* __restrict__ dst, int R, int C, int R_ld, long long dst_ld, long long dst_boff,
+                                      int row_shift) {
   __shared__ __nv_bfloat16 tile[32][34];
   const long long plane = (long long)C * dst_ld;
   const int pl = blockIdx.z & 1, bb = blockIdx.z >> 1;
@@ -153,14 +154,14 @@ __global__ void transpose_bf16_kernel(const __nv_bfloat16* __restrict__ src, lon
   __nv_bfloat16* d = dst + (size_t)pl * plane + (size_t)bb * dst_boff;
   const int c = blockIdx.x * 32 + threadIdx.x;
   for (int i = threadIdx.y; i < 32; i += blockDim.y) {
-    const int r = blockIdx.y * 32 + i;
-    tile[i][threadIdx.x] = (r < R && c < C) ? s[(size_t)r * src_ld + c] : __float2bfloat16(0.f);
+    const int r = blockIdx.y * 32 + i + row_shift;   // dst row r' holds src row r' + row_shift (zero outside [0,R))
+    tile[i][threadIdx.x] = (r >= 0 && r < R && c < C) ? s[(size_t)r * src_ld + c] : __float2bfloat16(0.f);
   }
   __syncthreads();
   const int r2 = blockIdx.y * 32 + threadIdx.x;
   for (int i = threadIdx.y; i < 32; i += blockDim.y) {
     const int c2 = blockIdx.x * 32 + i;
-    if (r2 < R_ld && c2 < C) d[(size_t)c2 * dst_ld + r2] = r2 < R ? tile[threadIdx.x][i] : __float2bfloat16(0.f);
+    if (r2 < R_ld && c2 < C) d[(size_t)c2 * dst_ld + r2] = tile[threadIdx.x][i];
   }
 }
 
@@ -219,10 +220,10 @@ int transpose_split_launch(const float* src, long long ld, long long src_bstride
 }
 
 int transpose_bf16_launch(const __nv_bfloat16* src, long long src_ld, long long src_bstride, long long src_plane, __nv_bfloat16* dst,
-                          int R, int C, int R_ld, long long dst_ld, long long dst_boff, int nbatch, cudaStream_t st) {
+                          int R, int C, int R_ld, long long dst_ld, long long dst_boff, int nbatch, int row_shift, cudaStream_t st) {
   if (R_ld <= 0 || C <= 0 || nbatch <= 0) return T2_OK;
   dim3 grid((C + 31) / 32, (R_ld + 31) / 32, 2 * nbatch), block(32, 8);
-  transpose_bf16_kernel<<<grid, block, 0, st>>>(src, src_ld, src_bstride, src_plane, dst, R, C, R_ld, dst_ld, dst_boff);
+  transpose_bf16_kernel<<<grid, block, 0, st>>>(src, src_ld, src_bstride, src_plane, dst, R, C, R_ld, dst_ld, dst_boff, row_shift);
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }

@@ -14,7 +14,7 @@ struct GemmNtArgs {
   CUtensorMap b_map;   // dims {Kin, Kout, Nrows, 2}, box {64, 1, NT, ...}
   int M, N, NT;        // logical output size; tiles = ceil(M/128) x ceil(N/NT)
   int Kin, Kout;
-  int nz, shift0, shift_step;   // B kin shift for batch z: shift0 + z*shift_step
+  int nz, shift0, shift_step;   // B kin shift for batch z: shift0 + z*shift_step (must be a multiple of 8 elements)
   int a_zrow, b_zrow;           // operand row offsets per z
   int splitk, npass;
   float* partial;               // [splitk][nz][Mt*128][Nt*NT]
@@ -39,5 +39,7 @@ int gemmnt_make_map(CUtensorMap* m, const __nv_bfloat16* base, int Kin, int kin_
 // dst[plane][c][bb*dst_boff + r] for r < R_ld (zeros for r >= R); dst row stride dst_ld, plane stride C*dst_ld.
 int transpose_split_launch(const float* src, long long ld, long long src_bstride, __nv_bfloat16* dst, int R, int C, int R_ld,
                            long long dst_ld, long long dst_boff, int nbatch, cudaStream_t st);
+// row_shift: dst column r holds src row r + row_shift (zeros outside [0,R)) -- a TMA box may only start at a 16-byte
+// aligned element of the innermost dimension, so conv-tap / recurrence shifts are materialised as shifted copies.
 int transpose_bf16_launch(const __nv_bfloat16* src, long long src_ld, long long src_bstride, long long src_plane, __nv_bfloat16* dst,
-                          int R, int C, int R_ld, long long dst_ld, long long dst_boff, int nbatch, cudaStream_t st);
+                          int R, int C, int R_ld, long long dst_ld, long long dst_boff, int nbatch, int row_shift, cudaStream_t st);

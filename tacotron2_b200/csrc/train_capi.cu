@@ -26,34 +26,43 @@ namespace {
 inline int gsz(long long n) { return (int)std::max<long long>(1, std::min<long long>((n + 255) / 256, 148 * 8)); }
 inline int round8(int x) { return (x + 7) & ~7; }
 
+// channels-last bf16 (hi,lo) [2][B][T][C] -> K-major [2][C][B][Tp], optionally time-shifted: dst[c][b][t] = x[b][t+shift][c]
+int to_kmajor(const __nv_bfloat16* x, __nv_bfloat16* xT, int B, int T, int Tp, int C, cudaStream_t st, int shift = 0,
+              long long dst_plane_rows = 0) {
+  (void)dst_plane_rows;
+  return transpose_bf16_launch(x, C, (long long)T * C, (long long)B * T * C, xT, T, C, Tp, (long long)B * Tp, Tp, B, shift, st);
+}
+
 // conv weight gradient dW[co][ci][j] = sum_{b,t} dz[b][t][co] x[b][t+j-pad][ci] on the tensor cores.
-// dzT [2][Cout][B][Tp], xT [2][Cin][B][Tp] (K-major in time).
-int conv_wgrad(t2_ctx* c, const __nv_bfloat16* dzT, const __nv_bfloat16* xT, int B, int T, int Tp, int Cout, int Cin, int k, float* dW,
-               float* partial, long long partial_floats, cudaStream_t st) {
+// dzT [2][Cout][B][Tp] K-major in time; x channels-last [2][B][T][Cin]; xTk = scratch for the k time-shifted K-major copies
+// of x, [k][2][Cin][B][Tp] (tap shifts cannot be TMA coordinates: 16-byte alignment of the innermost dimension).
+int conv_wgrad(t2_ctx* c, const __nv_bfloat16* dzT, const __nv_bfloat16* x, __nv_bfloat16* xTk, int B, int T, int Tp, int Cout, int Cin,
+               int k, float* dW, float* partial, long long partial_floats, cudaStream_t st) {
   GemmNtArgs a{};
   a.M = Cout; a.N = Cin; a.NT = Cin % 128 == 0 ? 128 : ((Cin + 15) & ~15);
   T2_REQUIRE(a.NT <= 128, T2_ERR_UNSUPPORTED, "conv_wgrad: Cin=%d", Cin);
-  a.Kin = T; a.Kout = B; a.nz = k; a.shift0 = -((k - 1) / 2); a.shift_step = 1; a.a_zrow = 0; a.b_zrow = 0;
+  a.Kin = T; a.Kout = B; a.nz = 1; a.shift0 = 0; a.shift_step = 0; a.a_zrow = 0; a.b_zrow = 0;
   a.splitk = 0; a.npass = c->npass;
   const long long need = gemmnt_partial_floats(a, c->num_sms);
-  if (!partial) return T2_OK;
   T2_REQUIRE(need <= partial_floats, T2_ERR_WORKSPACE, "conv_wgrad: partial buffer too small");
   a.partial = partial;
   RC(gemmnt_make_map(&a.a_map, dzT, T, Tp, B, Cout, (long long)Cout * B * Tp, 128, c->npass));
-  RC(gemmnt_make_map(&a.b_map, xT, T, Tp, B, Cin, (long long)Cin * B * Tp, a.NT, c->npass));
-  GemmNtOut o{dW, (long long)Cin * k, (long long)k, 1ll, 1.0f, 0};
-  return gemmnt_launch(a, o, st);
+  const int pad = (k - 1) / 2;
+  const size_t copy = (size_t)2 * Cin * B * Tp;
+  for (int j = 0; j < k; ++j) RC(to_kmajor(x, xTk + j * copy, B, T, Tp, Cin, st, j - pad));
+  for (int j = 0; j < k; ++j) {
+    RC(gemmnt_make_map(&a.b_map, xTk + j * copy, T, Tp, B, Cin, (long long)Cin * B * Tp, a.NT, c->npass));
+    GemmNtOut o{dW + j, (long long)Cin * k, (long long)k, 0ll, 1.0f, 0};
+    RC(gemmnt_launch(a, o, st));
+  }
+  return T2_OK;
 }
 long long conv_wgrad_partial_floats(t2_ctx* c, int B, int T, int Cout, int Cin, int k) {
   GemmNtArgs a{};
   a.M = Cout; a.N = Cin; a.NT = Cin % 128 == 0 ? 128 : ((Cin + 15) & ~15);
-  a.Kin = T; a.Kout = B; a.nz = k; a.splitk = 0;
+  a.Kin = T; a.Kout = B; a.nz = 1; a.splitk = 0;
+  (void)k;
   return gemmnt_partial_floats(a, c->num_sms);
-}
-
-// channels-last bf16 (hi,lo) [2][B][T][C] -> K-major [2][C][B][Tp]
-int to_kmajor(const __nv_bfloat16* x, __nv_bfloat16* xT, int B, int T, int Tp, int C, cudaStream_t st) {
-  return transpose_bf16_launch(x, C, (long long)T * C, (long long)B * T * C, xT, T, C, Tp, (long long)B * Tp, Tp, B, st);
 }
 
 int conv_tc_res(t2_ctx* c, const __nv_bfloat16* in, const CUtensorMap& wmap, int B, int T, int Cin, int Cout, int k, int NT,
@@ -140,7 +149,7 @@ static int postnet_bwd_impl(t2_ctx* c, int B, int T, const unsigned char* keep, 
   float* dyB = wa.take<float>((size_t)B * T * PD);
   __nv_bfloat16* dz = wa.take<__nv_bfloat16>((size_t)2 * B * T * PD);
   __nv_bfloat16* dzT = wa.take<__nv_bfloat16>((size_t)2 * PD * B * Tp);
-  __nv_bfloat16* xT = wa.take<__nv_bfloat16>((size_t)2 * PD * B * Tp);
+  __nv_bfloat16* xT = wa.take<__nv_bfloat16>((size_t)5 * 2 * PD * B * Tp);
   long long pf = 0;
   for (int i = 0; i < 5; ++i) pf = std::max(pf, conv_wgrad_partial_floats(c, B, T, chans[i + 1], chans[i], 5));
   float* partial = wa.take<float>(pf);
@@ -159,8 +168,7 @@ static int postnet_bwd_impl(t2_ctx* c, int B, int T, const unsigned char* keep, 
     BnLayer L = post_layer(c, tp, i, B, T, keep, seed, bw->ptr, bb->ptr);
     RC(bn_bwd_launch(L, dy, (long long)B * T, gg, gb, dz, nullptr, scratch, st));
     RC(to_kmajor(dz, dzT, B, T, Tp, Cout, st));
-    RC(to_kmajor(tp.x[i], xT, B, T, Tp, Cin, st));
-    RC(conv_wgrad(c, dzT, xT, B, T, Tp, Cout, Cin, 5, gW, partial, pf, st));
+    RC(conv_wgrad(c, dzT, tp.x[i], xT, B, T, Tp, Cout, Cin, 5, gW, partial, pf, st));
     float* dst = i == 0 ? d_mels : bufs[i & 1];
     RC(conv_tc_res(c, dz, c->post_wtmap[i], B, T, Cout, Cin, 5, Cin % 128 == 0 ? 128 : Cin, i == 0 ? d_mels_in : nullptr,
                    (long long)T * Cin, dst, st));

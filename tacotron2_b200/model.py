@@ -222,7 +222,8 @@ class Tacotron2(nn.Module):
                 h = C.c_void_p()
                 _lib.check(lib.t2_ctx_create(C.byref(self._cfg), C.byref(h)), "t2_ctx_create")
                 self._ctx = h
-            if sig != self._sig:
+            if sig != self._sig or (getattr(self, "_bn_dirty", False) and not self.training):
+                self._bn_dirty = False
                 for k, v in tensors.items():
                     _lib.check(lib.t2_ctx_set_param(self._ctx, k.encode(), _lib.ptr(v), v.numel()), "t2_ctx_set_param")
                 _lib.check(lib.t2_ctx_commit(self._ctx, self._stream()), "t2_ctx_commit")
