@@ -121,6 +121,21 @@ int t2_postnet_bwd(t2_ctx* ctx, int B, int T, const unsigned char* keep, unsigne
                    const float* d_mels_in, const void* tape, long long tape_bytes, float* d_mels, void* ws, long long ws_bytes,
                    void* stream);
 
+/* Teacher-forced frame loop under train() (model/tacotron2.py:255-258,276-317; hidden-state dropouts p = 0.1 active,
+ * model/decoder.py:75,101): same persistent kernel in history mode.  Arguments as t2_decode_tf; tape from t2_decode_tape_bytes. */
+long long t2_decode_tape_bytes(const t2_ctx* ctx, int B, int L, int T);
+int t2_decode_tf_train_fwd(t2_ctx* ctx, const float* memory, const float* processed_memory, const unsigned char* mask,
+                           const float* controls, const float* mel_target, int B, int L, int T, const unsigned char* prenet_keep,
+                           const unsigned char* att_keep, const unsigned char* rnn_keep, unsigned long long seed, float* mels,
+                           float* gates, float* alignments, void* tape, long long tape_bytes, void* ws, long long ws_bytes, void* stream);
+/* Backward (BPTT) of the frame loop: one persistent kernel for the recurrent chain + bulk tensor-core GEMMs for everything
+ * off the chain.  d_mels (B,T,M), d_gates (B,T): gradients w.r.t. the raw decoder outputs; alignments (B,T,L) from the forward.
+ * Outputs d_memory (B,L,EF), d_processed_memory (B,L,A); writes decoder.* and prenet.* parameter gradients. */
+int t2_decode_tf_bwd(t2_ctx* ctx, const float* memory, const float* processed_memory, const unsigned char* mask, const float* mel_target,
+                     int B, int L, int T, const unsigned char* att_keep, const unsigned char* rnn_keep, unsigned long long seed,
+                     const float* alignments, const float* d_mels, const float* d_gates, const void* tape, long long tape_bytes,
+                     float* d_memory, float* d_processed_memory, void* ws, long long ws_bytes, void* stream);
+
 /* training_step loss (model/tts_model.py:197-201): BCEWithLogits(gates) + MSE(mels) + MSE(mels_post), plain means over the
  * padded tensors; loss (1) device scalar; d_mels/d_post (B,T,M), d_gates (B,T) may be NULL.  ws >= 4 KB. */
 int t2_loss_fwd_bwd(t2_ctx* ctx, const float* mels, const float* post, const float* gates, const float* mel_target,

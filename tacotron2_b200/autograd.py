@@ -72,6 +72,46 @@ class PostnetFn(torch.autograd.Function):
         return (None, None, None, d_mels, *views)
 
 
+class DecodeTfFn(torch.autograd.Function):
+    """The teacher-forced frame loop under train() (model/tacotron2.py:255-258,276-317) for <= 64 utterances."""
+
+    @staticmethod
+    def forward(ctx, owner, mask, ctrl, target, pk, ak, rk, seed, memory, pmem, *params):
+        dev = memory.device
+        lib = owner._ready(dev)
+        B, L, _ = memory.shape
+        T, M = target.shape[1], target.shape[2]
+        memory, pmem = memory.contiguous(), pmem.contiguous()
+        tape = torch.empty(lib.t2_decode_tape_bytes(owner._ctx, B, L, T), dtype=torch.uint8, device=dev)
+        ws = owner._train_workspace(lib, dev, B, L, T)
+        mels, gates, aligns = torch.empty(B, T, M, device=dev), torch.empty(B, T, device=dev), torch.empty(B, T, L, device=dev)
+        _lib.check(lib.t2_decode_tf_train_fwd(owner._ctx, P(memory), P(pmem), P(mask), P(ctrl), P(target), B, L, T, P(pk), P(ak), P(rk), seed,
+                                              P(mels), P(gates), P(aligns), P(tape), tape.numel(), P(ws), ws.numel(), _stream()),
+                   "t2_decode_tf_train_fwd")
+        ctx.owner, ctx.tape, ctx.seed, ctx.dims = owner, tape, seed, (B, L, T, M)
+        ctx.keep = (mask, target, ak, rk, memory, pmem, aligns)
+        ctx.mark_non_differentiable(aligns)
+        return mels, gates, aligns
+
+    @staticmethod
+    def backward(ctx, d_mels, d_gates, _d_aligns):
+        owner = ctx.owner
+        B, L, T, M = ctx.dims
+        mask, target, ak, rk, memory, pmem, aligns = ctx.keep
+        dev = memory.device
+        lib = owner._ready(dev)
+        flat, views = _bucket(owner, lib, owner._group_params("decoder"))
+        ws = owner._train_workspace(lib, dev, B, L, T)
+        z = lambda t, *s: torch.zeros(*s, device=dev) if t is None else t.contiguous()  # noqa: E731
+        d_mels, d_gates = z(d_mels, B, T, M), z(d_gates, B, T)
+        d_memory, d_pmem = torch.empty_like(memory), torch.empty_like(pmem)
+        _lib.check(lib.t2_decode_tf_bwd(owner._ctx, P(memory), P(pmem), P(mask), P(target), B, L, T, P(ak), P(rk), ctx.seed, P(aligns),
+                                        P(d_mels), P(d_gates), P(ctx.tape), ctx.tape.numel(), P(d_memory), P(d_pmem), P(ws), ws.numel(),
+                                        _stream()), "t2_decode_tf_bwd")
+        _after_bucket(owner, flat)
+        return (None,) * 8 + (d_memory, d_pmem, *views)
+
+
 class FinalizeFn(torch.autograd.Function):
     """mels_post = mels + postnet_out, then the three output masks (model/tacotron2.py:333-345)."""
 

@@ -1,0 +1,175 @@
+// Persistent backward kernel of the teacher-forced decoder loop (BPTT over model/tacotron2.py:276-317 with
+// model/decoder.py:53-119 and model/attention.py:34-69).  Same grid as the forward: 32 clusters x 4 CTAs, one CTA per SM.
+// Per frame t (descending) three phases separated by grid barriers:
+//   G  input-gradient GEMMs on tcgen05: dx_dec(t) = W_dec^T dgates_dec(t) and dx_att(t+1) = W_att^T dgates_att(t+1)
+//      (transposed tile-major weight packs, split-K over the cluster, DSMEM reduce) -- both in the same phase
+//   A  attention backward for frame t: context / softmax / energies / location features, recomputing the forward's
+//      tanh arguments; accumulates the small attention weight gradients in registers for the whole utterance
+//   P  pointwise LSTMCell backward: attention cell of frame t (needs dq from A) and decoder cell of frame t-1
+// Everything that is not on the recurrent dependency chain is left to bulk tensor-core GEMMs after the loop (weight
+// gradients from the saved dgates^T, memory gradient from the saved d ctx, prenet backward).
+#include "train.cuh"
+
+namespace {
+
+struct GridBar {
+  unsigned* ctr;
+  unsigned* abort_flag;
+  unsigned nblocks;
+  unsigned epoch;
+  __device__ bool sync(bool fail, bool wrote_x) {
+    if (wrote_x) asm volatile("fence.proxy.async;" ::: "memory");
+    __syncthreads();
+    __shared__ int ok_s;
+    if (threadIdx.x == 0) {
+      ++epoch;
+      if (fail) atomicExch(abort_flag, 1u);
+      __threadfence();
+      atomicAdd(ctr, 1u);
+      const unsigned target = epoch * nblocks;
+      long long spins = 0;
+      while (ld_acquire_u32(ctr) < target) {
+        if (++spins > (1ll << 24)) {
+          if (ld_acquire_u32(abort_flag) != 0u || spins > (1ll << 27)) { atomicExch(abort_flag, 1u); break; }
+        }
+      }
+      ok_s = (ld_acquire_u32(abort_flag) == 0u);
+      __threadfence();
+    }
+    __syncthreads();
+    return ok_s != 0;
+  }
+};
+
+struct BSmem {
+  uint8_t* stages;    // TMA ring / phase scratch
+  float* part;        // [128][68] split-K partial
+  float* dc_att;      // [8][64] carried d/d c of this CTA's units
+  float* dc_dec;
+  float* conv_t;      // [2][31][32]
+  float* dense;       // [32][A]   (f-major, as the forward)
+  float* dense_af;    // [A][33]   (a-major copy for d f = ds * Wd)
+  float* v;           // [A]
+  uint64_t* bars;
+  uint32_t* tmem_slot;
+};
+
+__device__ __forceinline__ BSmem carve(uint8_t* base, const D2Dims& d) {
+  BSmem s;
+  s.stages = base;
+  uint8_t* p = base + D2_STAGES * TG_STAGE_BYTES;
+  s.part = reinterpret_cast<float*>(p);    p += TG_M * TG_PART_LD * 4;
+  s.dc_att = reinterpret_cast<float*>(p);  p += 8 * D2_BP * 4;
+  s.dc_dec = reinterpret_cast<float*>(p);  p += 8 * D2_BP * 4;
+  s.conv_t = reinterpret_cast<float*>(p);  p += 2 * D2_LOC_K * D2_LOC_F * 4;
+  s.dense = reinterpret_cast<float*>(p);   p += d.A * D2_LOC_F * 4;
+  s.dense_af = reinterpret_cast<float*>(p); p += d.A * 33 * 4;
+  s.v = reinterpret_cast<float*>(p);       p += d.A * 4;
+  s.bars = reinterpret_cast<uint64_t*>(p); p += (2 * D2_STAGES + 2) * 8;
+  s.tmem_slot = reinterpret_cast<uint32_t*>(p);
+  return s;
+}
+
+size_t bsmem_bytes(const D2Dims& d) {
+  return 1024 + (size_t)D2_STAGES * TG_STAGE_BYTES + TG_M * TG_PART_LD * 4 + 2 * 8 * D2_BP * 4 + 2 * D2_LOC_K * D2_LOC_F * 4 +
+         (size_t)d.A * D2_LOC_F * 4 + (size_t)d.A * 33 * 4 + d.A * 4 + (2 * D2_STAGES + 2) * 8 + 64;
+}
+
+__device__ __forceinline__ float block_reduce_sum(float v, float* red) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  v = warp_sum(v);
+  __syncthreads();
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float r = red[0];
+#pragma unroll
+  for (int i = 1; i < D2_THREADS / 32; ++i) r += red[i];
+  return r;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Pointwise LSTMCell backward for this CTA's 8 units x 64 utterances (thread = (unit = warp, utterance pair = lane)).
+// dh_extra: optional per-thread additive term (query backward).  Writes dgates to the packed operand buffer (through
+// `stg`, 16-byte stores) and to the K-major weight-gradient operand; carries d c in shared memory; accumulates bias sums.
+struct PwArgs {
+  const float* sav;        // [5][H][BP] of this frame
+  const float* cprev;      // [H][BP] c of the previous frame or null (zero state)
+  const float* dh0;        // [..][BP] k-major rows: dh0[(row0 + u)][b]  (may be null)
+  const float* dh1;        // second k-major source (may be null)
+  int row0, row1;
+  const float* dh_rm;      // row-major [BP][ld_rm] source, column col_rm + u (may be null)
+  int ld_rm, col_rm;
+  const unsigned char* keep;  // [B][H] of this frame or null
+  bool hidden_dropout;
+  unsigned long long seed, rng_base;
+  __nv_bfloat16* dg;       // [2 hl][BP][4H] packed row order
+  __nv_bfloat16* dgT;      // [2 hl][4H][ldT] reference row order, column tcol + b
+  long long ldT; long long tcol;
+};
+
+__device__ __forceinline__ void lstm_pointwise_bwd(const PwArgs& a, int H, int B, int unit0, int pbase, float* dcs, float* stg,
+                                                   const float* dh_extra2, float* bias_acc /*[4]*/) {
+  const int ul = threadIdx.x >> 5, bp = threadIdx.x & 31;
+  const int u = unit0 + ul;
+  const size_t gs = (size_t)H * D2_BP;
+  float dgv[4][2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int b = 2 * bp + j;
+    float di = 0.f, df = 0.f, dg_ = 0.f, do_ = 0.f;
+    if (b < B) {
+      const size_t o = (size_t)u * D2_BP + b;
+      const float si = a.sav[o], sf = a.sav[gs + o], tg = a.sav[2 * gs + o], so = a.sav[3 * gs + o], c = a.sav[4 * gs + o];
+      const float cp = a.cprev ? a.cprev[o] : 0.f;
+      float dh = dh_extra2 ? dh_extra2[j] : 0.f;
+      if (a.dh0) dh += ld_cg(a.dh0 + (size_t)(a.row0 + u) * D2_BP + b);
+      if (a.dh1) dh += ld_cg(a.dh1 + (size_t)(a.row1 + u) * D2_BP + b);
+      if (a.dh_rm) dh += ld_cg(a.dh_rm + (size_t)b * a.ld_rm + a.col_rm + u);
+      if (a.hidden_dropout) {  // nn.Dropout(0.1) on h (model/decoder.py:75,101): same draw as the forward
+        const bool k = a.keep ? (a.keep[(size_t)b * H + u] != 0) : rng_keep(a.seed, a.rng_base + (unsigned long long)b * H + u, 0.1f);
+        dh = k ? dh * (1.0f / 0.9f) : 0.f;
+      }
+      const float tc_ = tanh_fast(c);
+      do_ = dh * tc_ * so * (1.f - so);
+      const float dc = dh * so * (1.f - tc_ * tc_) + dcs[ul * D2_BP + b];
+      di = dc * tg * si * (1.f - si);
+      df = dc * cp * sf * (1.f - sf);
+      dg_ = dc * si * (1.f - tg * tg);
+      dcs[ul * D2_BP + b] = dc * sf;
+    }
+    dgv[0][j] = di; dgv[1][j] = df; dgv[2][j] = dg_; dgv[3][j] = do_;
+  }
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    bias_acc[g] += dgv[g][0] + dgv[g][1];
+    // K-major weight-gradient operand: row g*H + u, columns tcol + 2bp, +1  (4-byte store, 128 B per warp)
+    __nv_bfloat16 h0, l0, h1, l1;
+    tc::split_bf16(dgv[g][0], h0, l0);
+    tc::split_bf16(dgv[g][1], h1, l1);
+    const size_t ro = (size_t)(g * H + u) * a.ldT + a.tcol + 2 * bp;
+    *reinterpret_cast<__nv_bfloat162*>(a.dgT + ro) = __halves2bfloat162(h0, h1);
+    *reinterpret_cast<__nv_bfloat162*>(a.dgT + (size_t)4 * H * a.ldT + ro) = __halves2bfloat162(l0, l1);
+    stg[(2 * bp) * 33 + g * 8 + ul] = dgv[g][0];
+    stg[(2 * bp + 1) * 33 + g * 8 + ul] = dgv[g][1];
+  }
+  __syncthreads();
+  // packed operand: rows [pbase, pbase+32) of every utterance, both planes: 64 x 2 x 4 chunks of 8 bf16
+#pragma unroll 1
+  for (int i = threadIdx.x; i < D2_BP * 2 * 4; i += D2_THREADS) {
+    const int ch = i & 3, hl = (i >> 2) & 1, b = i >> 3;
+    __align__(16) __nv_bfloat16 v8[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      __nv_bfloat16 hi, lo;
+      tc::split_bf16(stg[b * 33 + ch * 8 + e], hi, lo);
+      v8[e] = hl ? lo : hi;
+    }
+    *reinterpret_cast<uint4*>(a.dg + ((size_t)hl * D2_BP + b) * 4 * H + pbase + ch * 8) = *reinterpret_cast<const uint4*>(v8);
+  }
+  __syncthreads();
+}
+
+}  // namespace
+
+#include "bwd_decoder_att.inl"
+#include "bwd_decoder_main.inl"

@@ -1,0 +1,329 @@
+// Attention backward for one frame (included by bwd_decoder.cu).  CTA = (utterance b, part `part` of S; the S parts of one
+// utterance sit in the same cluster).  Forward being differentiated (model/attention.py:52-67, model/decoder.py:78-90):
+//   f = conv1d([w_{t-1}; cum_{t-1}]) (2->32, k 31);  s = tanh(q + f Wd^T + pm);  e = s . v (masked);  w = softmax(e);
+//   ctx = w^T memory;  cum_t = cum_{t-1} + w.
+namespace {
+
+struct AttAcc {           // per-thread accumulators that live for the whole utterance
+  float wd[16];           // d location_dense: (a-quad = lane, f-quad = warp) 4x4 tile
+  float wc[8];            // d location_conv:  (f-quad = tid&7, cj = tid>>3 and +32)
+  float dv[4];            // d v: lane's 4 attention dims (partial over the positions this warp handled)
+};
+
+// scratch (floats): q[A] | wp[Lh4] | wc[Lh4] | fs[Lc][36] | dctx[EF] | ws[Lc4] | gw[Lc4] | de[Lc4] | red[64] | xch[8] |
+//                   dqw[8][A] | ds[Lc][A+4] | dfe[Lc+30][36]
+__device__ __forceinline__ size_t att_bwd_scratch_floats(int L, int S, int A, int EF) {
+  const int Lc = (L + S - 1) / S, Lh4 = (Lc + 30 + 3) & ~3, Lc4 = (Lc + 3) & ~3;
+  return (size_t)A + 2 * Lh4 + (size_t)Lc * 36 + EF + 3 * Lc4 + 64 + 8 + 8 * (size_t)A + (size_t)Lc * (A + 4) + (size_t)(Lc + 30) * 36;
+}
+
+__device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBWork& wk, const BSmem& sm, float* scratch, bool active,
+                                    int b, int part, int S, int t, int T, bool have_att_next, int KattT, int KdecT, AttAcc& acc) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int L = d.L, A = d.A, EF = d.EF;
+  const int Lc = (L + S - 1) / S, l0 = min(L, part * Lc), l1 = min(L, l0 + Lc), nl = l1 - l0;
+  const int Lh4 = (Lc + 30 + 3) & ~3, Lc4 = (Lc + 3) & ~3;
+  float* q_s = scratch;
+  float* wp = q_s + A;
+  float* wc = wp + Lh4;
+  float* fs = wc + Lh4;
+  float* dctx = fs + (size_t)Lc * 36;
+  float* w_s = dctx + EF;
+  float* gw = w_s + Lc4;
+  float* de = gw + Lc4;
+  float* red = de + Lc4;
+  float* xch = red + 64;
+  float* dqw = xch + 8;
+  float* ds = dqw + 8 * A;
+  float* dfe = ds + (size_t)Lc * (A + 4);
+  const int ldd = A + 4;
+  const uint32_t my_rank = tc::cluster_ctarank();
+  const uint32_t base_rank = my_rank - (uint32_t)part;
+
+  if (active) {
+    // ---- stage: q_t, wcat of this frame (w_{t-1}, cum_{t-1}) with halo, total d ctx_t, w_t slice
+    const float* wprev = tp.w_hist + ((size_t)t * D2_BP + b) * L;
+    const float* wcum = tp.wcum_hist + ((size_t)t * D2_BP + b) * L;
+    const float* wcur = tp.w_hist + ((size_t)(t + 1) * D2_BP + b) * L;
+#pragma unroll 1
+    for (int i = tid; i < A; i += D2_THREADS) q_s[i] = tp.q[((size_t)t * D2_BP + b) * A + i];
+#pragma unroll 1
+    for (int i = tid; i < nl + 30; i += D2_THREADS) {
+      const int l = l0 + i - 15;
+      const bool in = (l >= 0 && l < L);
+      wp[i] = in ? wprev[l] : 0.f;
+      wc[i] = in ? wcum[l] : 0.f;
+    }
+#pragma unroll 1
+    for (int c = tid; c < EF; c += D2_THREADS) {
+      float v = ld_cg(wk.dprojin + ((size_t)t * D2_BP + b) * d.KprojP + d.R + c) + ld_cg(wk.dx_dec + (size_t)(d.H + c) * D2_BP + b);
+      if (have_att_next) v += ld_cg(wk.dx_att + (size_t)(d.P + c) * D2_BP + b);
+      dctx[c] = v;
+      if (part == 0) wk.dctx_tot[((size_t)t * D2_BP + b) * EF + c] = v;
+    }
+#pragma unroll 1
+    for (int i = tid; i < nl; i += D2_THREADS) w_s[i] = wcur[l0 + i];
+    __syncthreads();
+
+    // ---- recompute the location conv features of this slice (as the forward)
+    {
+      const int nchunk = (nl + 31) >> 5;
+#pragma unroll 1
+      for (int task = warp; task < nchunk * 4; task += D2_THREADS / 32) {
+        const int li = (task >> 2) * 32 + lane, fg = task & 3;
+        float a8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a8[i] = 0.f;
+        const int lw = min(li, max(nl - 1, 0));
+#pragma unroll 1
+        for (int j = 0; j < D2_LOC_K; ++j) {
+          const float a0 = wp[lw + j], a1 = wc[lw + j];
+          const float4* w0 = reinterpret_cast<const float4*>(sm.conv_t + (0 * D2_LOC_K + j) * D2_LOC_F + fg * 8);
+          const float4* w1 = reinterpret_cast<const float4*>(sm.conv_t + (1 * D2_LOC_K + j) * D2_LOC_F + fg * 8);
+          const float4 p0 = w0[0], p1 = w0[1], r0 = w1[0], r1 = w1[1];
+          a8[0] = fmaf(p0.x, a0, a8[0]); a8[1] = fmaf(p0.y, a0, a8[1]); a8[2] = fmaf(p0.z, a0, a8[2]); a8[3] = fmaf(p0.w, a0, a8[3]);
+          a8[4] = fmaf(p1.x, a0, a8[4]); a8[5] = fmaf(p1.y, a0, a8[5]); a8[6] = fmaf(p1.z, a0, a8[6]); a8[7] = fmaf(p1.w, a0, a8[7]);
+          a8[0] = fmaf(r0.x, a1, a8[0]); a8[1] = fmaf(r0.y, a1, a8[1]); a8[2] = fmaf(r0.z, a1, a8[2]); a8[3] = fmaf(r0.w, a1, a8[3]);
+          a8[4] = fmaf(r1.x, a1, a8[4]); a8[5] = fmaf(r1.y, a1, a8[5]); a8[6] = fmaf(r1.z, a1, a8[6]); a8[7] = fmaf(r1.w, a1, a8[7]);
+        }
+        if (li < nl) {
+          float4* dst = reinterpret_cast<float4*>(fs + (size_t)li * 36 + fg * 8);
+          dst[0] = make_float4(a8[0], a8[1], a8[2], a8[3]);
+          dst[1] = make_float4(a8[4], a8[5], a8[6], a8[7]);
+        }
+      }
+    }
+
+    // ---- g_w[l] = d ctx . memory[l] + d conv ch0 (from frame t+1) + g_cum;  g_cum += d conv ch1   (warp per position)
+    {
+      const float* mem = tp.memory + (size_t)b * L * EF;
+      float* dc0 = wk.dconv + ((size_t)0 * D2_BP + b) * L;
+      float* dc1 = wk.dconv + ((size_t)1 * D2_BP + b) * L;
+      float* gc = wk.gcum + (size_t)b * L;
+#pragma unroll 1
+      for (int li = warp; li < nl; li += D2_THREADS / 32) {
+        const float4* mp = reinterpret_cast<const float4*>(mem + (size_t)(l0 + li) * EF);
+        float s = 0.f;
+        for (int c4 = lane; c4 < EF / 4; c4 += 32) {
+          const float4 m4 = __ldg(mp + c4);
+          const float4 d4 = *reinterpret_cast<const float4*>(dctx + c4 * 4);
+          s = fmaf(m4.x, d4.x, s); s = fmaf(m4.y, d4.y, s); s = fmaf(m4.z, d4.z, s); s = fmaf(m4.w, d4.w, s);
+        }
+        s = warp_sum(s);
+        if (lane == 0) {
+          const int l = l0 + li;
+          float g = gc[l];
+          if (t + 1 < T) { g += dc1[l]; s += dc0[l]; }   // contributions of frame t+1's location conv
+          gc[l] = g;                                      // d/d cum_t (cum_t feeds cum_{t+1} and conv channel 1 of t+1)
+          gw[li] = s + g;                                 // w_t also enters cum_t
+        }
+      }
+    }
+    __syncthreads();
+    // ---- softmax backward: de = w * (g_w - sum_l w g_w); the dot needs all parts
+    float pd = 0.f;
+#pragma unroll 1
+    for (int i = tid; i < nl; i += D2_THREADS) pd = fmaf(w_s[i], gw[i], pd);
+    pd = block_reduce_sum(pd, red);
+    if (tid == 0) xch[0] = pd;
+  }
+  tc::cluster_sync();
+  if (active) {
+    float tot = 0.f;
+    {
+      const uint32_t xa = tc::smem_u32(xch);
+      for (int pr = 0; pr < S; ++pr) {
+        float v;
+        asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(tc::mapa(xa, base_rank + (uint32_t)pr)) : "memory");
+        tot += v;
+      }
+    }
+#pragma unroll 1
+    for (int i = tid; i < nl; i += D2_THREADS) de[i] = w_s[i] * (gw[i] - tot);   // masked positions have w = 0 -> de = 0
+    __syncthreads();
+
+    // ---- recompute s = tanh(q + f Wd^T + pm); ds = de * v * (1 - s^2); accumulate dv, dq, d pm   (warp = 4 positions, lane = 4 dims)
+    {
+      const int a4 = lane * 4;
+      const bool lane_on = a4 < A;
+      const int ac = lane_on ? a4 : 0;
+      const float4 q4 = *reinterpret_cast<const float4*>(q_s + ac);
+      const float4 v4 = *reinterpret_cast<const float4*>(sm.v + ac);
+      float dq4[4] = {0.f, 0.f, 0.f, 0.f};
+      float dvl[4] = {acc.dv[0], acc.dv[1], acc.dv[2], acc.dv[3]};   // register copies (acc may alias the scratch for the compiler)
+      const int ntile = (nl + 3) >> 2;
+#pragma unroll 1
+      for (int tl = warp; tl < ntile; tl += D2_THREADS / 32) {
+        const int lt = tl * 4;
+        float4 pm4[4];
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+          const int lp = min(lt + l, nl - 1);
+          pm4[l] = __ldg(reinterpret_cast<const float4*>(tp.pmem + ((size_t)b * L + l0 + lp) * A + ac));
+        }
+        float ac4[4][4];
+#pragma unroll
+        for (int l = 0; l < 4; ++l)
+#pragma unroll
+          for (int a = 0; a < 4; ++a) ac4[l][a] = 0.f;
+#pragma unroll 2
+        for (int f4 = 0; f4 < D2_LOC_F / 4; ++f4) {
+          float4 fv[4];
+#pragma unroll
+          for (int l = 0; l < 4; ++l) fv[l] = *reinterpret_cast<const float4*>(fs + (size_t)min(lt + l, nl - 1) * 36 + f4 * 4);
+#pragma unroll
+          for (int ff = 0; ff < 4; ++ff) {
+            const float4 wv = *reinterpret_cast<const float4*>(sm.dense + (f4 * 4 + ff) * A + ac);
+#pragma unroll
+            for (int l = 0; l < 4; ++l) {
+              const float fl = ff == 0 ? fv[l].x : (ff == 1 ? fv[l].y : (ff == 2 ? fv[l].z : fv[l].w));
+              ac4[l][0] = fmaf(fl, wv.x, ac4[l][0]); ac4[l][1] = fmaf(fl, wv.y, ac4[l][1]);
+              ac4[l][2] = fmaf(fl, wv.z, ac4[l][2]); ac4[l][3] = fmaf(fl, wv.w, ac4[l][3]);
+            }
+          }
+        }
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+          if (lt + l >= nl || !lane_on) continue;
+          const float del = de[lt + l];
+          const float s0 = tanh_fast(q4.x + ac4[l][0] + pm4[l].x), s1 = tanh_fast(q4.y + ac4[l][1] + pm4[l].y);
+          const float s2 = tanh_fast(q4.z + ac4[l][2] + pm4[l].z), s3 = tanh_fast(q4.w + ac4[l][3] + pm4[l].w);
+          dvl[0] = fmaf(del, s0, dvl[0]); dvl[1] = fmaf(del, s1, dvl[1]);
+          dvl[2] = fmaf(del, s2, dvl[2]); dvl[3] = fmaf(del, s3, dvl[3]);
+          const float4 d4 = make_float4(del * v4.x * (1.f - s0 * s0), del * v4.y * (1.f - s1 * s1), del * v4.z * (1.f - s2 * s2),
+                                        del * v4.w * (1.f - s3 * s3));
+          dq4[0] += d4.x; dq4[1] += d4.y; dq4[2] += d4.z; dq4[3] += d4.w;
+          *reinterpret_cast<float4*>(ds + (size_t)(lt + l) * ldd + ac) = d4;
+          float4* pmg = reinterpret_cast<float4*>(wk.dpm + ((size_t)b * L + l0 + lt + l) * A + ac);   // this thread owns (l, a) in every frame
+          float4 o = *pmg;
+          o.x += d4.x; o.y += d4.y; o.z += d4.z; o.w += d4.w;
+          *pmg = o;
+        }
+      }
+      acc.dv[0] = dvl[0]; acc.dv[1] = dvl[1]; acc.dv[2] = dvl[2]; acc.dv[3] = dvl[3];
+      if (lane_on) *reinterpret_cast<float4*>(dqw + warp * A + ac) = make_float4(dq4[0], dq4[1], dq4[2], dq4[3]);
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (int a = tid; a < A; a += D2_THREADS) {
+      float s = 0.f;
+#pragma unroll
+      for (int w8 = 0; w8 < D2_THREADS / 32; ++w8) s += dqw[w8 * A + a];
+      wk.dq[(((size_t)t * S + part) * D2_BP + b) * A + a] = s;
+    }
+
+    // ---- d f[l][f] = sum_a ds[l][a] Wd[a][f]   (warp = 16 positions; lane -> position quad lane>>3, filter quad lane&7)
+    {
+      const int fq = (lane & 7) * 4, lq = lane >> 3;
+      const int ngrp = (nl + 15) >> 4;
+#pragma unroll 1
+      for (int g = warp; g < ngrp; g += D2_THREADS / 32) {
+        const int lb = g * 16 + lq * 4;
+        float o[4][4];
+#pragma unroll
+        for (int l = 0; l < 4; ++l)
+#pragma unroll
+          for (int f = 0; f < 4; ++f) o[l][f] = 0.f;
+#pragma unroll 4
+        for (int a = 0; a < A; ++a) {
+          const float w0 = sm.dense_af[a * 33 + fq], w1 = sm.dense_af[a * 33 + fq + 1], w2 = sm.dense_af[a * 33 + fq + 2],
+                      w3 = sm.dense_af[a * 33 + fq + 3];
+#pragma unroll
+          for (int l = 0; l < 4; ++l) {
+            const float x = ds[(size_t)min(lb + l, nl - 1) * ldd + a];
+            o[l][0] = fmaf(x, w0, o[l][0]); o[l][1] = fmaf(x, w1, o[l][1]); o[l][2] = fmaf(x, w2, o[l][2]); o[l][3] = fmaf(x, w3, o[l][3]);
+          }
+        }
+#pragma unroll
+        for (int l = 0; l < 4; ++l)
+          if (lb + l < nl) *reinterpret_cast<float4*>(dfe + (size_t)(15 + lb + l) * 36 + fq) = make_float4(o[l][0], o[l][1], o[l][2], o[l][3]);
+      }
+    }
+
+    // ---- d location_dense[a][f] += sum_l ds[l][a] f[l][f]   (thread tile: a-quad = lane, f-quad = warp)
+    {
+      const int a4 = lane * 4, f4 = warp * 4;
+      if (a4 < A) {
+        float wd[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) wd[i] = acc.wd[i];
+#pragma unroll 2
+        for (int l = 0; l < nl; ++l) {
+          const float4 dv4 = *reinterpret_cast<const float4*>(ds + (size_t)l * ldd + a4);
+          const float4 fv = *reinterpret_cast<const float4*>(fs + (size_t)l * 36 + f4);
+          wd[0] = fmaf(dv4.x, fv.x, wd[0]);  wd[1] = fmaf(dv4.x, fv.y, wd[1]);
+          wd[2] = fmaf(dv4.x, fv.z, wd[2]);  wd[3] = fmaf(dv4.x, fv.w, wd[3]);
+          wd[4] = fmaf(dv4.y, fv.x, wd[4]);  wd[5] = fmaf(dv4.y, fv.y, wd[5]);
+          wd[6] = fmaf(dv4.y, fv.z, wd[6]);  wd[7] = fmaf(dv4.y, fv.w, wd[7]);
+          wd[8] = fmaf(dv4.z, fv.x, wd[8]);  wd[9] = fmaf(dv4.z, fv.y, wd[9]);
+          wd[10] = fmaf(dv4.z, fv.z, wd[10]); wd[11] = fmaf(dv4.z, fv.w, wd[11]);
+          wd[12] = fmaf(dv4.w, fv.x, wd[12]); wd[13] = fmaf(dv4.w, fv.y, wd[13]);
+          wd[14] = fmaf(dv4.w, fv.z, wd[14]); wd[15] = fmaf(dv4.w, fv.w, wd[15]);
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) acc.wd[i] = wd[i];
+      }
+    }
+  }
+  tc::cluster_sync();   // every part's d f slice is in its shared memory
+  if (active) {
+    // ---- halo rows of d f from the neighbouring parts (15 positions each side)
+#pragma unroll 1
+    for (int i = tid; i < 30 * 8; i += D2_THREADS) {
+      const int e = i >> 3, f4 = (i & 7) * 4;
+      const int row = e < 15 ? e : nl + e;                 // rows [0,15) and [15+nl, 30+nl)
+      const int l = l0 - 15 + row;                          // global position of that row
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (l >= 0 && l < L) {
+        const int pr = l / Lc, li = l - pr * Lc;
+        const uint32_t ra = tc::mapa(tc::smem_u32(dfe + (size_t)(15 + li) * 36 + f4), base_rank + (uint32_t)pr);
+        v = tc::ld_dsmem4(ra);
+      }
+      *reinterpret_cast<float4*>(dfe + (size_t)row * 36 + f4) = v;
+    }
+    __syncthreads();
+    // ---- d location_conv[c][j][f] += sum_{l in slice} d f[l][f] * wcat[c][l + j - 15]
+    {
+      const int f4 = (tid & 7) * 4, cj0 = tid >> 3;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int cj = cj0 + 32 * h;
+        if (cj >= 2 * D2_LOC_K) continue;
+        const int c = cj / D2_LOC_K, j = cj - c * D2_LOC_K;
+        const float* wsrc = (c ? wc : wp) + j;
+        float o0 = 0.f, o1 = 0.f, o2 = 0.f, o3 = 0.f;
+#pragma unroll 4
+        for (int l = 0; l < nl; ++l) {
+          const float x = wsrc[l];
+          const float4 fv = *reinterpret_cast<const float4*>(dfe + (size_t)(15 + l) * 36 + f4);
+          o0 = fmaf(x, fv.x, o0); o1 = fmaf(x, fv.y, o1); o2 = fmaf(x, fv.z, o2); o3 = fmaf(x, fv.w, o3);
+        }
+        acc.wc[4 * h + 0] += o0; acc.wc[4 * h + 1] += o1; acc.wc[4 * h + 2] += o2; acc.wc[4 * h + 3] += o3;
+      }
+    }
+    // ---- d wcat[c][l'] = sum_j sum_f d f[l' - j + 15][f] Wc[c][j][f]  for the slice (warp task = (32 positions, channel))
+    {
+      const int nchunk = (nl + 31) >> 5;
+#pragma unroll 1
+      for (int task = warp; task < nchunk * 2; task += D2_THREADS / 32) {
+        const int c = task & 1, li = (task >> 1) * 32 + lane;
+        const int lw = min(li, max(nl - 1, 0));
+        float o = 0.f;
+#pragma unroll 1
+        for (int j = 0; j < D2_LOC_K; ++j) {
+          const float4* fr = reinterpret_cast<const float4*>(dfe + (size_t)(lw - j + 30) * 36);
+          const float4* wr = reinterpret_cast<const float4*>(sm.conv_t + (c * D2_LOC_K + j) * D2_LOC_F);
+#pragma unroll
+          for (int f4 = 0; f4 < 8; ++f4) {
+            const float4 x = fr[f4], w = wr[f4];
+            o = fmaf(x.x, w.x, o); o = fmaf(x.y, w.y, o); o = fmaf(x.z, w.z, o); o = fmaf(x.w, w.w, o);
+          }
+        }
+        if (li < nl) wk.dconv[((size_t)c * D2_BP + b) * L + l0 + li] = o;
+      }
+    }
+  }
+  tc::cluster_sync();   // peers are done reading this CTA's d f rows before the scratch is reused
+}
+
+}  // namespace

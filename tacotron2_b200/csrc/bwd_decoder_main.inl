@@ -1,0 +1,264 @@
+// Persistent kernel + launch (included by bwd_decoder.cu).
+namespace {
+
+struct DBParams {
+  D2Dims d;
+  int T, KattT, KdecT, S;
+  DBWeights w;
+  DBTape tp;
+  DBWork wk;
+  unsigned long long* prof;   // [8] or null: cycles of CTA 0 in G / A / P
+};
+
+// one 128-row tile of an input-gradient GEMM: dx[k0 + r][b] = sum_p WT[k0 + r][p] dg[b][p]
+__device__ __forceinline__ bool dx_tile(tg::Pipe& pipe, const BSmem& sm, const CUtensorMap* wmap, const CUtensorMap* dgmap, int ktile,
+                                        int npb, uint32_t rank, float* dx /*[K][BP]*/, float* dpre_t /*[BP][P] or null*/, int P) {
+  tg::XSrc xs{dgmap, 0, dgmap, 0, npb};
+  const bool ok = tg::gemm(pipe, wmap, ktile * TG_M, npb, xs, (int)rank, npb, D2_CLUSTER, 0u);
+  tg::accum_to_smem(pipe, 0u, sm.part);
+  tc::cluster_sync();
+  // CTA `rank` reduces rows [32*rank, 32*rank+32) of the tile over the four partials
+#pragma unroll 1
+  for (int i = threadIdx.x; i < 32 * (TG_N / 2); i += D2_THREADS) {
+    const int row = 32 * (int)rank + i / (TG_N / 2), col = 2 * (i % (TG_N / 2));
+    const float2 s = tg::reduce4(sm.part, row, col);
+    const int k = ktile * TG_M + row;
+    if (dpre_t && k < P) {   // prenet-output gradient goes straight to its per-frame history (row-major for the bulk prenet backward)
+      dpre_t[(size_t)col * P + k] = s.x;
+      dpre_t[(size_t)(col + 1) * P + k] = s.y;
+    } else {
+      *reinterpret_cast<float2*>(dx + (size_t)k * D2_BP + col) = s;
+    }
+  }
+  tc::cluster_sync();   // peers are done reading this CTA's partial before it is overwritten
+  return ok;
+}
+
+__global__ void __launch_bounds__(D2_THREADS, 1)
+decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* base = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+  const D2Dims& d = p.d;
+  const BSmem sm = carve(base, d);
+  float* scratch = reinterpret_cast<float*>(base);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t rank = tc::cluster_ctarank();
+  const int cl = blockIdx.x / D2_CLUSTER;
+  const int unit0 = cl * 32 + (int)rank * 8;
+  const int pbase = cl * 128 + (int)rank * 32;
+  const int B = d.B, H = d.H, T = p.T;
+  const DBWork& wk = p.wk;
+  const DBTape& tp = p.tp;
+
+  if (tid == 0) {
+    tc::prefetch_tmap(&maps.wt_att); tc::prefetch_tmap(&maps.wt_dec); tc::prefetch_tmap(&maps.dg_att); tc::prefetch_tmap(&maps.dg_dec);
+  }
+#pragma unroll 1
+  for (int i = tid; i < 2 * D2_LOC_K * D2_LOC_F; i += D2_THREADS) sm.conv_t[i] = p.w.loc_conv_t[i];
+#pragma unroll 1
+  for (int i = tid; i < d.A * D2_LOC_F; i += D2_THREADS) {
+    const float v = p.w.loc_dense[i];           // [f][a]
+    sm.dense[i] = v;
+    sm.dense_af[(i % d.A) * 33 + i / d.A] = v;  // [a][f]
+  }
+#pragma unroll 1
+  for (int i = tid; i < d.A; i += D2_THREADS) sm.v[i] = p.w.v[i];
+#pragma unroll 1
+  for (int i = tid; i < 8 * D2_BP; i += D2_THREADS) { sm.dc_att[i] = 0.f; sm.dc_dec[i] = 0.f; }
+  tg::Pipe pipe;
+  tg::pipe_init(pipe, sm.bars, sm.stages, D2_STAGES, d.npass, sm.tmem_slot);
+  tc::cluster_sync();
+
+  GridBar bar{wk.barrier, wk.barrier + 1, gridDim.x, 0u};
+  long long prof_last = clock64();
+  auto prof_mark = [&](int slot) {
+    if (blockIdx.x == 0 && tid == 0 && p.prof) { const long long now = clock64(); p.prof[slot] += (unsigned long long)(now - prof_last); prof_last = now; }
+  };
+  const int S = p.S;
+  const int att_b = blockIdx.x / S, att_part = blockIdx.x % S;
+  const bool att_active = att_b < B;
+  const int npb = 4 * H / TG_BK;
+  const int ntile_dec = p.KdecT / TG_M, ntile_att = p.KattT / TG_M;
+  const int nclusters = gridDim.x / D2_CLUSTER;
+  AttAcc acc;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) acc.wd[i] = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc.wc[i] = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) acc.dv[i] = 0.f;
+  float bias_att[4] = {0.f, 0.f, 0.f, 0.f}, bias_dec[4] = {0.f, 0.f, 0.f, 0.f};
+  float* stg = scratch;                       // [64][33] staging of the pointwise phase
+  float* dq_s = scratch + 64 * 33 + 16;       // [A][64] summed d query, utterance-minor
+  float* wq_s = dq_s + d.A * D2_BP;           // [A][8]  query weight columns of this CTA's 8 units (reloaded per frame: L2 hit)
+  bool alive = true, fail = false;
+
+  auto pw_dec = [&](int t, bool have_next) {   // decoder LSTMCell of frame t
+    PwArgs a{};
+    a.sav = tp.sav_dec + (size_t)t * 5 * H * D2_BP;
+    a.cprev = t > 0 ? tp.sav_dec + ((size_t)(t - 1) * 5 + 4) * H * D2_BP : nullptr;
+    a.dh0 = have_next ? wk.dx_dec : nullptr; a.row0 = d.H + d.EF + d.C;     // d rnn_h_t from the decoder cell of frame t+1
+    a.dh_rm = wk.dprojin + (size_t)t * D2_BP * d.KprojP; a.ld_rm = d.KprojP; a.col_rm = 0;   // from the mel / gate projection
+    a.keep = tp.rnn_keep ? tp.rnn_keep + (size_t)t * B * H : nullptr;
+    a.hidden_dropout = tp.hidden_dropout != 0; a.seed = tp.seed; a.rng_base = (2ull << 40) + (unsigned long long)t * B * H;
+    a.dg = wk.dg_dec; a.dgT = wk.dgT_dec; a.ldT = (long long)T * D2_BP; a.tcol = (long long)t * D2_BP;
+    lstm_pointwise_bwd(a, H, B, unit0, pbase, sm.dc_dec, stg, nullptr, bias_dec);
+  };
+  auto pw_att = [&](int t, bool have_next) {   // attention LSTMCell of frame t (its h also feeds the query and the decoder cell)
+    // d query summed over the attention parts, transposed to [a][b]
+#pragma unroll 1
+    for (int i = tid; i < d.A * D2_BP; i += D2_THREADS) {
+      const int a_ = i % d.A, b = i / d.A;
+      float s = 0.f;
+      for (int pr = 0; pr < S; ++pr) s += ld_cg(wk.dq + (((size_t)t * S + pr) * D2_BP + b) * d.A + a_);
+      dq_s[a_ * D2_BP + b] = b < B ? s : 0.f;
+    }
+#pragma unroll 1
+    for (int i = tid; i < d.A * 8; i += D2_THREADS) wq_s[i] = __ldg(p.w.Wq + (size_t)(i >> 3) * H + unit0 + (i & 7));
+    __syncthreads();
+    float ex[2] = {0.f, 0.f};
+    {
+      const int ul = warp, bp = lane;
+#pragma unroll 4
+      for (int a_ = 0; a_ < d.A; ++a_) {
+        const float wv = wq_s[a_ * 8 + ul];
+        const float2 q2 = *reinterpret_cast<const float2*>(dq_s + a_ * D2_BP + 2 * bp);
+        ex[0] = fmaf(wv, q2.x, ex[0]); ex[1] = fmaf(wv, q2.y, ex[1]);
+      }
+    }
+    PwArgs a{};
+    a.sav = tp.sav_att + (size_t)t * 5 * H * D2_BP;
+    a.cprev = t > 0 ? tp.sav_att + ((size_t)(t - 1) * 5 + 4) * H * D2_BP : nullptr;
+    a.dh0 = wk.dx_dec; a.row0 = 0;                                         // att_h_t is the first input block of the decoder cell
+    a.dh1 = have_next ? wk.dx_att : nullptr; a.row1 = d.P + d.EF;          // recurrent input of the attention cell of frame t+1
+    a.keep = tp.att_keep ? tp.att_keep + (size_t)t * B * H : nullptr;
+    a.hidden_dropout = tp.hidden_dropout != 0; a.seed = tp.seed; a.rng_base = (1ull << 40) + (unsigned long long)t * B * H;
+    a.dg = wk.dg_att; a.dgT = wk.dgT_att; a.ldT = (long long)T * D2_BP; a.tcol = (long long)t * D2_BP;
+    lstm_pointwise_bwd(a, H, B, unit0, pbase, sm.dc_att, stg, ex, bias_att);
+  };
+
+  // prologue: decoder cell of the last frame
+  pw_dec(T - 1, false);
+  alive = bar.sync(fail, true);
+  prof_mark(2);
+
+#pragma unroll 1
+  for (int t = T - 1; t >= -1 && alive; --t) {
+    // ---- G: dx_dec(t) and dx_att(t+1)
+    const bool have_att_next = t + 1 <= T - 1;
+    {
+      const int n_dec = t >= 0 ? ntile_dec : 0, n_att = have_att_next ? ntile_att : 0;
+#pragma unroll 1
+      for (int tile = cl; tile < n_dec + n_att; tile += nclusters) {
+        bool ok;
+        if (tile < n_dec) ok = dx_tile(pipe, sm, &maps.wt_dec, &maps.dg_dec, tile, npb, rank, wk.dx_dec, nullptr, 0);
+        else ok = dx_tile(pipe, sm, &maps.wt_att, &maps.dg_att, tile - n_dec, npb, rank, wk.dx_att,
+                          wk.dpre + (size_t)(t + 1) * D2_BP * d.P, d.P);
+        if (!ok) fail = true;
+      }
+    }
+    if (!(alive = bar.sync(fail, false))) break;
+    prof_mark(0);
+    if (t < 0) break;   // epilogue iteration: only dx_att(0) (prenet gradient of frame 0) was needed
+    // ---- A: attention backward of frame t
+    attention_bwd_phase(d, tp, wk, sm, scratch, att_active, att_b, att_part, S, t, T, have_att_next, p.KattT, p.KdecT, acc);
+    if (!(alive = bar.sync(fail, false))) break;
+    prof_mark(1);
+    // ---- P: attention cell of frame t, decoder cell of frame t-1
+    pw_att(t, have_att_next);
+    if (t > 0) pw_dec(t - 1, true);
+    if (!(alive = bar.sync(fail, true))) break;
+    prof_mark(2);
+  }
+
+  // ---- per-CTA partials of the small attention weight gradients, bias gradients
+  {
+    float* sp = wk.small_partial + (size_t)blockIdx.x * (d.A * 32 + 2 * D2_LOC_K * D2_LOC_F + d.A);
+    const int a4 = lane * 4, f4 = warp * 4;
+    if (a4 < d.A)
+#pragma unroll
+      for (int i = 0; i < 16; ++i) sp[(a4 + (i >> 2)) * 32 + f4 + (i & 3)] = acc.wd[i];            // [a][f] = location_dense.weight layout
+    float* spc = sp + d.A * 32;
+    const int ff = (tid & 7) * 4, cj0 = tid >> 3;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int cj = cj0 + 32 * h;
+      if (cj >= 2 * D2_LOC_K) continue;
+      const int c = cj / D2_LOC_K, j = cj - c * D2_LOC_K;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) spc[((ff + i) * 2 + c) * D2_LOC_K + j] = acc.wc[4 * h + i];       // [f][c][j] = location_conv.weight layout
+    }
+    __syncthreads();
+    float* red = scratch;   // [8][A]
+    if (a4 < d.A) *reinterpret_cast<float4*>(red + warp * d.A + a4) = make_float4(acc.dv[0], acc.dv[1], acc.dv[2], acc.dv[3]);
+    __syncthreads();
+    float* spv = spc + 2 * D2_LOC_K * D2_LOC_F;
+#pragma unroll 1
+    for (int a_ = tid; a_ < d.A; a_ += D2_THREADS) {
+      float s = 0.f;
+      for (int w8 = 0; w8 < D2_THREADS / 32; ++w8) s += red[w8 * d.A + a_];
+      spv[a_] = s;
+    }
+    // bias gradients: this warp's unit, sum over the 64 utterances
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const float sa = warp_sum(bias_att[g]), sd = warp_sum(bias_dec[g]);
+      if (lane == 0) {
+        wk.dbias[g * H + unit0 + warp] = sa;
+        wk.dbias[4 * H + g * H + unit0 + warp] = sd;
+      }
+    }
+  }
+  if (blockIdx.x == 0 && tid == 0) wk.barrier[2] = alive ? 0u : 1u;
+  tc::tc_fence_before();
+  tc::cluster_sync();
+  if ((tid >> 5) == 1) tc::tmem_dealloc<TG_TMEM_COLS>(pipe.tmem);
+}
+
+}  // namespace
+
+int db_parts(const D2Dims& d) {
+  const int grid = (d.H / 32) * D2_CLUSTER;
+  return (d.B * 4 <= grid) ? 4 : ((d.B * 2 <= grid) ? 2 : 1);
+}
+size_t db_small_floats(const D2Dims& d) { return (size_t)d.A * 32 + 2 * D2_LOC_K * D2_LOC_F + d.A; }
+
+static size_t att_bwd_scratch_floats_host(int L, int S, int A, int EF) {
+  const int Lc = (L + S - 1) / S, Lh4 = (Lc + 30 + 3) & ~3, Lc4 = (Lc + 3) & ~3;
+  return (size_t)A + 2 * Lh4 + (size_t)Lc * 36 + EF + 3 * Lc4 + 64 + 8 + 8 * (size_t)A + (size_t)Lc * (A + 4) + (size_t)(Lc + 30) * 36;
+}
+
+int db_launch(const D2Dims& d, int T, int KattT, int KdecT, const DBWeights& w, const DBTape& tp, const DBWork& wk, const DBMaps& maps,
+              unsigned long long* prof, cudaStream_t st) {
+  T2_REQUIRE(d.B >= 1 && d.B <= D2_BP && T >= 1, T2_ERR_ARG, "decoder backward: batch %d not in [1,%d] per launch", d.B, D2_BP);
+  T2_REQUIRE(d.H == d.R && d.H % 32 == 0 && d.P % TG_M == 0 && d.EF % 4 == 0 && d.A % 32 == 0 && d.A <= D2_MAX_A, T2_ERR_UNSUPPORTED,
+             "decoder backward: unsupported dims H=%d R=%d EF=%d P=%d A=%d", d.H, d.R, d.EF, d.P, d.A);
+  const int grid = (d.H / 32) * D2_CLUSTER;
+  T2_REQUIRE(grid == 128, T2_ERR_UNSUPPORTED, "decoder backward: laid out for 128 CTAs (att_rnn_dim = 1024), got %d", grid);
+  const int S = db_parts(d);
+  const size_t ring = (size_t)D2_STAGES * TG_STAGE_BYTES;
+  T2_REQUIRE(att_bwd_scratch_floats_host(d.L, S, d.A, d.EF) * 4 <= ring, T2_ERR_UNSUPPORTED,
+             "decoder backward: L=%d too long for the attention scratch", d.L);
+  T2_REQUIRE((size_t)(64 * 33 + 16 + d.A * D2_BP + d.A * 8) * 4 <= ring, T2_ERR_UNSUPPORTED, "decoder backward: pointwise staging");
+  const size_t smem = bsmem_bytes(d);
+  T2_REQUIRE(smem <= 227 * 1024, T2_ERR_UNSUPPORTED, "decoder backward: %zu B shared memory", smem);
+  T2_CHECK_CUDA(cudaFuncSetAttribute(decoder_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaLaunchConfig_t cfg{};
+  cudaLaunchAttribute at[1];
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(D2_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = D2_CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  int nclusters = 0;
+  T2_CHECK_CUDA(cudaOccupancyMaxActiveClusters(&nclusters, decoder_bwd_kernel, &cfg));
+  T2_REQUIRE(nclusters * D2_CLUSTER >= grid, T2_ERR_UNSUPPORTED, "decoder backward: only %d clusters co-resident, %d needed", nclusters,
+             grid / D2_CLUSTER);
+  T2_CHECK_CUDA(cudaMemsetAsync(wk.barrier, 0, 4 * sizeof(unsigned), st));
+  DBParams p{d, T, KattT, KdecT, S, w, tp, wk, prof};
+  T2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, decoder_bwd_kernel, maps, p));
+  return T2_OK;
+}

@@ -113,3 +113,249 @@ int finalize_bwd_launch(const float* d_mels, const float* d_post, const float* d
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }
+
+// ------------------------------------------------------------------------------------------ decoder-backward helpers
+namespace {
+
+// mel / gate output gradients (B,T,M), (B,T) -> bf16 (hi,lo) operands of the projection backward:
+//   dP  [2][T*BP][ld]  rows (t, b), columns r (mel rows, then the gate row), zero padded
+//   dPT [2][ld][T*BP]  transposed
+__global__ void build_dproj_kernel(const float* __restrict__ d_mels, const float* __restrict__ d_gates, int B, int T, int M, int ld,
+                                   __nv_bfloat16* __restrict__ dP, __nv_bfloat16* __restrict__ dPT) {
+  const long long rows = (long long)T * D2_BP, n = rows * ld;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(i % ld);
+    const long long tb = i / ld;
+    const int b = (int)(tb % D2_BP), t = (int)(tb / D2_BP);
+    float v = 0.f;
+    if (b < B) {
+      if (r < M) v = d_mels[((size_t)b * T + t) * M + r];
+      else if (r == M) v = d_gates[(size_t)b * T + t];
+    }
+    __nv_bfloat16 hi, lo;
+    tc::split_bf16(v, hi, lo);
+    dP[i] = hi; dP[n + i] = lo;
+    dPT[(size_t)r * rows + tb] = hi; dPT[n + (size_t)r * rows + tb] = lo;
+  }
+}
+
+// dq [T][S][BP][A] -> sum over S, transposed bf16 (hi,lo) [2][A][T*BP]
+__global__ void dq_sumT_kernel(const float* __restrict__ dq, int T, int S, int A, int B, __nv_bfloat16* __restrict__ out) {
+  const long long cols = (long long)T * D2_BP, n = cols * A;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const long long tb = i % cols;
+    const int a = (int)(i / cols);
+    const int b = (int)(tb % D2_BP), t = (int)(tb / D2_BP);
+    float s = 0.f;
+    if (b < B)
+      for (int p = 0; p < S; ++p) s += dq[(((size_t)t * S + p) * D2_BP + b) * A + a];
+    __nv_bfloat16 hi, lo;
+    tc::split_bf16(s, hi, lo);
+    out[i] = hi; out[n + i] = lo;
+  }
+}
+
+__global__ void partial_sum_kernel(const float* __restrict__ partial, int nparts, int n, float* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float s = 0.f;
+  for (int p = 0; p < nparts; ++p) s += partial[(size_t)p * n + i];
+  out[i] = s;
+}
+
+__global__ void copy2_kernel(const float* __restrict__ src, float* __restrict__ a, float* __restrict__ b, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) { const float v = src[i]; a[i] = v; if (b) b[i] = v; }
+}
+
+// prenet backward, layer 2: d2[n][o] = (prenet output > 0) ? dpre * 1/(1-p) : 0 with n = t*B + b, t < T
+// (output > 0 <=> ReLU passed and the AlwaysDropout kept it, model/tacotron2.py:85-92)
+__global__ void prenet_d2_kernel(const float* __restrict__ dpre /*[T][BP][P]*/, const __nv_bfloat16* __restrict__ tfp /*[T+1][2][BP][P]*/,
+                                 int B, int T, int P, float scale, float* __restrict__ d2 /*[T*B][P]*/) {
+  const long long n = (long long)T * B * P;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int o = (int)(i % P);
+    const long long tb = i / P;
+    const int b = (int)(tb % B), t = (int)(tb / B);
+    const float y = __bfloat162float(tfp[(((size_t)t * 2) * D2_BP + b) * P + o]);
+    d2[i] = y > 0.f ? dpre[((size_t)t * D2_BP + b) * P + o] * scale : 0.f;
+  }
+}
+__global__ void prenet_d1_kernel(const float* __restrict__ dp1, const float* __restrict__ p1, long long n, float scale, float* __restrict__ d1) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    d1[i] = p1[i] > 0.f ? dp1[i] * scale : 0.f;
+}
+// prenet input of row n = t*B + b: mel_target[b][t-1] (zeros for t = 0), transposed bf16 (hi,lo) [2][M][Np]
+__global__ void prenet_xT_kernel(const float* __restrict__ mel_target, int B, int T, int M, int Np, __nv_bfloat16* __restrict__ xT) {
+  const long long n = (long long)M * Np;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(i % Np), m = (int)(i / Np);
+    float v = 0.f;
+    if (r < T * B) {
+      const int b = r % B, t = r / B;
+      if (t > 0) v = mel_target[((size_t)b * T + (t - 1)) * M + m];
+    }
+    __nv_bfloat16 hi, lo;
+    tc::split_bf16(v, hi, lo);
+    xT[i] = hi; xT[n + i] = lo;
+  }
+}
+
+}  // namespace
+
+int build_dproj_launch(const float* d_mels, const float* d_gates, int B, int T, int M, int ld, __nv_bfloat16* dP, __nv_bfloat16* dPT,
+                       cudaStream_t st) {
+  build_dproj_kernel<<<gs((long long)T * D2_BP * ld), 256, 0, st>>>(d_mels, d_gates, B, T, M, ld, dP, dPT);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+int dq_sumT_launch(const float* dq, int T, int S, int A, int B, __nv_bfloat16* out, cudaStream_t st) {
+  dq_sumT_kernel<<<gs((long long)T * D2_BP * A), 256, 0, st>>>(dq, T, S, A, B, out);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+int partial_sum_launch(const float* partial, int nparts, int n, float* out, cudaStream_t st) {
+  partial_sum_kernel<<<(n + 255) / 256, 256, 0, st>>>(partial, nparts, n, out);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+int copy2_launch(const float* src, float* a, float* b, int n, cudaStream_t st) {
+  copy2_kernel<<<(n + 255) / 256, 256, 0, st>>>(src, a, b, n);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+int prenet_d2_launch(const float* dpre, const __nv_bfloat16* tfp, int B, int T, int P, float scale, float* d2, cudaStream_t st) {
+  prenet_d2_kernel<<<gs((long long)T * B * P), 256, 0, st>>>(dpre, tfp, B, T, P, scale, d2);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+int prenet_d1_launch(const float* dp1, const float* p1, long long n, float scale, float* d1, cudaStream_t st) {
+  prenet_d1_kernel<<<gs(n), 256, 0, st>>>(dp1, p1, n, scale, d1);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+int prenet_xT_launch(const float* mel_target, int B, int T, int M, int Np, __nv_bfloat16* xT, cudaStream_t st) {
+  prenet_xT_kernel<<<gs((long long)M * Np), 256, 0, st>>>(mel_target, B, T, M, Np, xT);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+
+// ------------------------------------------------------------------------------------------ packed BiLSTM backward
+// Mirror of bilstm_cluster_kernel (layers.cu): one cluster of 8 CTAs per (direction, 8 utterances).  CTA `rank` owns the
+// same 32 hidden units: it holds their d h / d c, computes their gate gradients, broadcasts them to the 8 CTAs through
+// distributed shared memory, and -- with the W_hh COLUMNS of its units resident in shared memory for the whole sequence --
+// computes d h_{prev}[own units] = sum over all 4*Hh gate rows.  One cluster barrier per character.
+namespace {
+#define BB_NB 8
+#define BB_CL 8
+__global__ void __launch_bounds__(256, 1) bilstm_bwd_cluster_kernel(const float* __restrict__ sav, const float* __restrict__ Whh,
+                                                                    const long long* __restrict__ lens, const float* __restrict__ d_out,
+                                                                    float* __restrict__ dgates, int B, int L, int Hh) {
+  extern __shared__ __align__(16) float bsm[];
+  const int UPC = Hh / BB_CL, G4 = 4 * Hh;
+  float* Wc = bsm;                                  // [4Hh rows][UPC]  W_hh[row][rank*UPC + k]
+  float* dgb = Wc + (size_t)G4 * UPC;               // [2][4Hh][BB_NB]
+  float* dhr = dgb + (size_t)2 * G4 * BB_NB;        // [UPC][BB_NB] recurrent d h of the own units
+  __shared__ int len_s[BB_NB];
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const int cid = blockIdx.x / BB_CL, dir = cid & 1, grp = cid >> 1;
+  const int tid = threadIdx.x;
+  const float* W = Whh + (size_t)dir * G4 * Hh;
+  for (int i = tid; i < G4 * UPC; i += blockDim.x) {
+    const int row = i / UPC, k = i - row * UPC;
+    Wc[i] = W[(size_t)row * Hh + rank * UPC + k];
+  }
+  for (int i = tid; i < 2 * G4 * BB_NB; i += blockDim.x) dgb[i] = 0.f;
+  for (int i = tid; i < UPC * BB_NB; i += blockDim.x) dhr[i] = 0.f;
+  if (tid < BB_NB) {
+    const int b = grp * BB_NB + tid;
+    len_s[tid] = b < B ? (int)min((long long)L, max(0ll, lens[b])) : 0;
+  }
+  __syncthreads();
+  int maxlen = 0;
+  for (int i = 0; i < BB_NB; ++i) maxlen = max(maxlen, len_s[i]);
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  const int pu = tid % UPC, pb = tid / UPC;         // pointwise role (unit, utterance): UPC * BB_NB == blockDim
+  const int mk = tid & 31, mu = tid >> 5;           // mat-vec role: (own unit k = lane, utterance = warp) when UPC == 32
+  float dc = 0.f;
+  const uint32_t dgb_addr = (uint32_t)__cvta_generic_to_shared(dgb);
+  for (int s = maxlen - 1; s >= 0; --s) {
+    const int cur = s & 1;
+    // ---- pointwise: gate gradients of the own units at forward step s
+    {
+      const int n = len_s[pb];
+      float dg4[4] = {0.f, 0.f, 0.f, 0.f};
+      if (s < n) {
+        const int b = grp * BB_NB + pb;
+        const int t = dir ? (n - 1 - s) : s;
+        const int u = rank * UPC + pu;
+        const float* sv = sav + (((size_t)b * L + t) * 2 + dir) * 5 * Hh + u;
+        const float si = sv[0], sf = sv[Hh], tg = sv[2 * Hh], so = sv[3 * Hh], c = sv[4 * Hh];
+        float cp = 0.f;
+        if (s > 0) {
+          const int tp = dir ? t + 1 : t - 1;
+          cp = sav[(((size_t)b * L + tp) * 2 + dir) * 5 * Hh + 4 * Hh + u];
+        }
+        const float dh = d_out[((size_t)b * L + t) * 2 * Hh + dir * Hh + u] + dhr[pu * BB_NB + pb];
+        const float tc_ = tanhf(c);
+        dg4[3] = dh * tc_ * so * (1.f - so);
+        const float dct = dh * so * (1.f - tc_ * tc_) + dc;
+        dg4[0] = dct * tg * si * (1.f - si);
+        dg4[1] = dct * cp * sf * (1.f - sf);
+        dg4[2] = dct * si * (1.f - tg * tg);
+        dc = dct * sf;
+        float* o = dgates + (((size_t)b * L + t) * 2 + dir) * G4 + u;
+        o[0] = dg4[0]; o[Hh] = dg4[1]; o[2 * Hh] = dg4[2]; o[3 * Hh] = dg4[3];
+      }
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const uint32_t off = dgb_addr + (uint32_t)((((size_t)cur * G4 + g * Hh + rank * UPC + pu) * BB_NB + pb) * 4);
+#pragma unroll
+        for (uint32_t pr = 0; pr < BB_CL; ++pr) {
+          uint32_t ra;
+          asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(off), "r"(pr));
+          asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(ra), "f"(dg4[g]) : "memory");
+        }
+      }
+    }
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    // ---- d h_{prev}[own unit k][utterance] = sum_rows W_hh[row][k] * dg[row][utterance]
+    {
+      const float* dg = dgb + (size_t)cur * G4 * BB_NB + mu;
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll 4
+      for (int r = 0; r < G4; r += 4) {
+        a0 = fmaf(Wc[(r + 0) * UPC + mk], dg[(r + 0) * BB_NB], a0);
+        a1 = fmaf(Wc[(r + 1) * UPC + mk], dg[(r + 1) * BB_NB], a1);
+        a2 = fmaf(Wc[(r + 2) * UPC + mk], dg[(r + 2) * BB_NB], a2);
+        a3 = fmaf(Wc[(r + 3) * UPC + mk], dg[(r + 3) * BB_NB], a3);
+      }
+      __syncthreads();   // everyone has read dhr of this step
+      dhr[mk * BB_NB + mu] = (a0 + a1) + (a2 + a3);
+    }
+    __syncthreads();
+  }
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+}  // namespace
+
+int bilstm_bwd_launch(const float* sav, const float* Whh, const long long* lens, const float* d_out, float* dgates, int B, int L, int Hh,
+                      cudaStream_t st) {
+  const int UPC = Hh / BB_CL;
+  T2_REQUIRE(Hh % BB_CL == 0 && UPC == 32, T2_ERR_UNSUPPORTED, "bilstm backward: hidden size %d unsupported (needs Hh == 256)", Hh);
+  T2_CHECK_CUDA(cudaMemsetAsync(dgates, 0, (size_t)B * L * 8 * Hh * sizeof(float), st));
+  const size_t smem = ((size_t)4 * Hh * UPC + (size_t)2 * 4 * Hh * BB_NB + (size_t)UPC * BB_NB) * sizeof(float);
+  T2_CHECK_CUDA(cudaFuncSetAttribute(bilstm_bwd_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)(2 * ((B + BB_NB - 1) / BB_NB) * BB_CL));
+  cfg.blockDim = dim3(256);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = BB_CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  T2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, bilstm_bwd_cluster_kernel, sav, Whh, lens, d_out, dgates, B, L, Hh));
+  return T2_OK;
+}

@@ -95,6 +95,18 @@ __global__ void __launch_bounds__(256, 1) gemm_nt_kernel(const __grid_constant__
     float v[16];
     tc::tmem_ld16(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(c * 16), v);
     tc::tmem_ld_wait();
+    if (a.direct_out) {
+      const int m = m0 + row;
+      if (m < a.M) {
+        float* drow = a.direct_out + (size_t)m * a.direct_ldm;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int n = n0 + c * 16 + i;
+          if (n < a.N) drow[n] = (ok && !empty_k) ? v[i] : 0.f;
+        }
+      }
+      continue;
+    }
     float4* dst = reinterpret_cast<float4*>(dst_row + c * 16);
 #pragma unroll
     for (int i = 0; i < 4; ++i)
@@ -120,9 +132,9 @@ __global__ void gemm_nt_reduce_kernel(const float* __restrict__ partial, int spl
 
 // fp32 [nb][R][C] -> bf16 (hi,lo) [2][C][dst_ld] with batch bb at column offset bb*dst_boff (transposed); 32x32 tiles
 __global__ void transpose_split_kernel(const float* __restrict__ src, long long ld, long long src_bstride,
-                                       __nv_bfloat16* __restrict__ dst, int R, int C, int R_ld, long long dst_ld, long long dst_boff) {
+                                       __nv_bfloat16* __restrict__ dst, int R, int C, int R_ld, long long dst_ld, long long dst_boff,
+                                       long long plane) {
   __shared__ float tile[32][33];
-  const long long plane = (long long)C * dst_ld;
   const int bb = blockIdx.z;
   const float* s = src + (size_t)bb * src_bstride;
   __nv_bfloat16* d = dst + (size_t)bb * dst_boff;
@@ -146,9 +158,8 @@ __global__ void transpose_split_kernel(const float* __restrict__ src, long long 
 
 __global__ void transpose_bf16_kernel(const __nv_bfloat16* __restrict__ src, long long src_ld, long long src_bstride, long long src_plane,
                                       __nv_bfloat16* __restrict__ dst, int R, int C, int R_ld, long long dst_ld, long long dst_boff,
-                                      int row_shift) {
+                                      int row_shift, long long plane) {
   __shared__ __nv_bfloat16 tile[32][34];
-  const long long plane = (long long)C * dst_ld;
   const int pl = blockIdx.z & 1, bb = blockIdx.z >> 1;
   const __nv_bfloat16* s = src + (size_t)pl * src_plane + (size_t)bb * src_bstride;
   __nv_bfloat16* d = dst + (size_t)pl * plane + (size_t)bb * dst_boff;
@@ -181,8 +192,9 @@ long long gemmnt_partial_floats(GemmNtArgs& a, int num_sms) {
 }
 
 int gemmnt_launch(const GemmNtArgs& a, const GemmNtOut& o, cudaStream_t st) {
-  T2_REQUIRE(a.NT % 16 == 0 && a.NT >= 16 && a.NT <= 128 && a.splitk >= 1 && a.nz >= 1 && a.partial && o.out, T2_ERR_ARG,
+  T2_REQUIRE(a.NT % 16 == 0 && a.NT >= 16 && a.NT <= 128 && a.splitk >= 1 && a.nz >= 1 && (a.partial || a.direct_out), T2_ERR_ARG,
              "gemmnt: bad arguments NT=%d splitk=%d nz=%d", a.NT, a.splitk, a.nz);
+  T2_REQUIRE(!a.direct_out || (a.splitk == 1 && a.nz == 1), T2_ERR_ARG, "gemmnt: direct output needs splitk == 1 and nz == 1");
   if (a.M <= 0 || a.N <= 0) return T2_OK;
   const int Nt = (a.N + a.NT - 1) / a.NT, Mt = (a.M + 127) / 128;
   const size_t smem = 1024 + (size_t)GN_STAGES * GN_STAGE_BYTES + 128;
@@ -194,6 +206,7 @@ int gemmnt_launch(const GemmNtArgs& a, const GemmNtOut& o, cudaStream_t st) {
   dim3 grid((unsigned)(Mt * Nt), (unsigned)a.nz, (unsigned)a.splitk);
   gemm_nt_kernel<<<grid, 256, smem, st>>>(a);
   T2_CHECK_CUDA(cudaGetLastError());
+  if (a.direct_out) return T2_OK;
   const long long total = (long long)a.nz * a.M * a.N;
   const int g = (int)std::min<long long>((total + 255) / 256, 148 * 8);
   gemm_nt_reduce_kernel<<<g, 256, 0, st>>>(a.partial, a.splitk, a.nz, Mt * 128, Nt * a.NT, a.M, a.N, o);
@@ -211,19 +224,20 @@ int gemmnt_make_map(CUtensorMap* m, const __nv_bfloat16* base, int Kin, int kin_
 }
 
 int transpose_split_launch(const float* src, long long ld, long long src_bstride, __nv_bfloat16* dst, int R, int C, int R_ld,
-                           long long dst_ld, long long dst_boff, int nbatch, cudaStream_t st) {
+                           long long dst_ld, long long dst_boff, int nbatch, long long dst_plane, cudaStream_t st) {
   if (R_ld <= 0 || C <= 0 || nbatch <= 0) return T2_OK;
   dim3 grid((C + 31) / 32, (R_ld + 31) / 32, nbatch), block(32, 8);
-  transpose_split_kernel<<<grid, block, 0, st>>>(src, ld, src_bstride, dst, R, C, R_ld, dst_ld, dst_boff);
+  transpose_split_kernel<<<grid, block, 0, st>>>(src, ld, src_bstride, dst, R, C, R_ld, dst_ld, dst_boff, dst_plane);
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }
 
 int transpose_bf16_launch(const __nv_bfloat16* src, long long src_ld, long long src_bstride, long long src_plane, __nv_bfloat16* dst,
-                          int R, int C, int R_ld, long long dst_ld, long long dst_boff, int nbatch, int row_shift, cudaStream_t st) {
+                          int R, int C, int R_ld, long long dst_ld, long long dst_boff, int nbatch, int row_shift, long long dst_plane,
+                          cudaStream_t st) {
   if (R_ld <= 0 || C <= 0 || nbatch <= 0) return T2_OK;
   dim3 grid((C + 31) / 32, (R_ld + 31) / 32, 2 * nbatch), block(32, 8);
-  transpose_bf16_kernel<<<grid, block, 0, st>>>(src, src_ld, src_bstride, src_plane, dst, R, C, R_ld, dst_ld, dst_boff, row_shift);
+  transpose_bf16_kernel<<<grid, block, 0, st>>>(src, src_ld, src_bstride, src_plane, dst, R, C, R_ld, dst_ld, dst_boff, row_shift, dst_plane);
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }

@@ -15,7 +15,7 @@ namespace {
 #define BL_CL 8
 __global__ void __launch_bounds__(256, 1) bilstm_cluster_kernel(const float* __restrict__ xproj, const float* __restrict__ Whh,
                                                                 const long long* __restrict__ lens, float* __restrict__ out,
-                                                                int B, int L, int Hh) {
+                                                                int B, int L, int Hh, float* __restrict__ sav) {
   extern __shared__ __align__(16) float bsm[];
   const int UPC = Hh / BL_CL, R = 4 * UPC, ldw = Hh + 1;
   float* Ws = bsm;                              // [R][Hh+1]
@@ -80,9 +80,14 @@ __global__ void __launch_bounds__(256, 1) bilstm_cluster_kernel(const float* __r
       if (s < n) {
         const float gi = gs[(0 * UPC + pu) * (BL_NB + 1) + pb], gf = gs[(1 * UPC + pu) * (BL_NB + 1) + pb];
         const float gg = gs[(2 * UPC + pu) * (BL_NB + 1) + pb], go = gs[(3 * UPC + pu) * (BL_NB + 1) + pb];
-        c = sigmoidf_(gf) * c + sigmoidf_(gi) * tanhf(gg);
-        h = sigmoidf_(go) * tanhf(c);
+        const float si = sigmoidf_(gi), sf = sigmoidf_(gf), tg = tanhf(gg), so = sigmoidf_(go);
+        c = sf * c + si * tg;
+        h = so * tanhf(c);
         const int t = dir ? (n - 1 - s) : s;
+        if (sav) {  // training tape: [B][L][2][5][Hh] = i, f, g, o (post-activation), c
+          float* sv = sav + (((size_t)(grp * BL_NB + pb) * L + t) * 2 + dir) * 5 * Hh + rank * UPC + pu;
+          sv[0] = si; sv[Hh] = sf; sv[2 * Hh] = tg; sv[3 * Hh] = so; sv[4 * Hh] = c;
+        }
         out[((size_t)(grp * BL_NB + pb) * L + t) * 2 * Hh + dir * Hh + rank * UPC + pu] = h;
       }
       hprev = h;
@@ -174,7 +179,8 @@ inline int gs(long long n, int bs) { long long g = (n + bs - 1) / bs; return (in
 
 }  // namespace
 
-int bilstm_launch(const float* xproj, const float* Whh, const long long* lens, float* out, int B, int L, int Hh, cudaStream_t st) {
+int bilstm_launch(const float* xproj, const float* Whh, const long long* lens, float* out, int B, int L, int Hh, cudaStream_t st,
+                  float* sav) {
   const int UPC = Hh / BL_CL;
   T2_REQUIRE(Hh % BL_CL == 0 && 8 * UPC <= 256 && UPC * BL_NB <= 256 && Hh % 4 == 0, T2_ERR_UNSUPPORTED,
              "bilstm: hidden size %d unsupported (needs Hh %% 8 == 0 and Hh <= 256)", Hh);
@@ -190,7 +196,7 @@ int bilstm_launch(const float* xproj, const float* Whh, const long long* lens, f
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = BL_CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
-  T2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, bilstm_cluster_kernel, xproj, Whh, lens, out, B, L, Hh));
+  T2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, bilstm_cluster_kernel, xproj, Whh, lens, out, B, L, Hh, sav));
   return T2_OK;
 }
 

@@ -5,7 +5,8 @@
 enum { ACT_NONE = 0, ACT_RELU = 1, ACT_TANH = 2 };
 
 int bilstm_launch(const float* xproj /*[B][L][2][4Hh]*/, const float* Whh /*[2][4Hh][Hh] (reference layout)*/, const long long* lens,
-                  float* out /*[B][L][2Hh]*/, int B, int L, int Hh, cudaStream_t st);
+                  float* out /*[B][L][2Hh]*/, int B, int L, int Hh, cudaStream_t st,
+                  float* sav = nullptr /*training tape [B][L][2][5][Hh] or null*/);
 int condition_launch(const float* enc /*[B][L][E]*/, const float* spk_table, const long long* spk_id,
                      const float* desc_vec /*[B][D] already tanh(linear)*/, int D, float* out /*[B][L][E+D]*/, int B, int L,
                      int E, cudaStream_t st);

@@ -76,14 +76,12 @@ struct DBMaps {
 };
 
 int db_launch(const D2Dims& d, int T, int KattT, int KdecT, const DBWeights& w, const DBTape& tp, const DBWork& wk, const DBMaps& maps,
-              cudaStream_t st);
+              unsigned long long* prof, cudaStream_t st);
 int db_parts(const D2Dims& d);        // S: CTAs per utterance in the attention backward
 size_t db_small_floats(const D2Dims& d);
 
 // ---- BiLSTM backward (bwd_layers.cu) ------------------------------------------------------------------------------
 // sav [B][L][2][5][Hh] (i,f,g,o,c) from the train-mode forward; d_out [B][L][2Hh]; dgates out [B][L][2][4Hh] (zeros at t >= len)
-int bilstm_train_fwd_launch(const float* xproj, const float* Whh, const long long* lens, float* out, float* sav, int B, int L, int Hh,
-                            cudaStream_t st);
 int bilstm_bwd_launch(const float* sav, const float* Whh, const long long* lens, const float* d_out, float* dgates, int B, int L, int Hh,
                       cudaStream_t st);
 
@@ -93,3 +91,11 @@ int loss_launch(const float* mels, const float* post, const float* gates, const 
                 long long n_gate, float* loss, float* d_mels, float* d_post, float* d_gates, void* scratch /*>= 4 KB*/, cudaStream_t st);
 int finalize_bwd_launch(const float* d_mels, const float* d_post, const float* d_gates, const long long* lengths, int B, int T, int M,
                         float* d_mels_raw, float* d_postout, float* d_gates_raw, cudaStream_t st);
+int build_dproj_launch(const float* d_mels, const float* d_gates, int B, int T, int M, int ld, __nv_bfloat16* dP, __nv_bfloat16* dPT,
+                       cudaStream_t st);
+int dq_sumT_launch(const float* dq, int T, int S, int A, int B, __nv_bfloat16* out, cudaStream_t st);
+int partial_sum_launch(const float* partial, int nparts, int n, float* out, cudaStream_t st);
+int copy2_launch(const float* src, float* a, float* b, int n, cudaStream_t st);
+int prenet_d2_launch(const float* dpre, const __nv_bfloat16* tfp, int B, int T, int P, float scale, float* d2, cudaStream_t st);
+int prenet_d1_launch(const float* dp1, const float* p1, long long n, float scale, float* d1, cudaStream_t st);
+int prenet_xT_launch(const float* mel_target, int B, int T, int M, int Np, __nv_bfloat16* xT, cudaStream_t st);

@@ -30,7 +30,7 @@ inline int round8(int x) { return (x + 7) & ~7; }
 int to_kmajor(const __nv_bfloat16* x, __nv_bfloat16* xT, int B, int T, int Tp, int C, cudaStream_t st, int shift = 0,
               long long dst_plane_rows = 0) {
   (void)dst_plane_rows;
-  return transpose_bf16_launch(x, C, (long long)T * C, (long long)B * T * C, xT, T, C, Tp, (long long)B * Tp, Tp, B, shift, st);
+  return transpose_bf16_launch(x, C, (long long)T * C, (long long)B * T * C, xT, T, C, Tp, (long long)B * Tp, Tp, B, shift, (long long)C * B * Tp, st);
 }
 
 // conv weight gradient dW[co][ci][j] = sum_{b,t} dz[b][t][co] x[b][t+j-pad][ci] on the tensor cores.
@@ -218,10 +218,237 @@ extern "C" int t2_finalize_bwd(t2_ctx* c, const float* d_mels, const float* d_po
   return finalize_bwd_launch(d_mels, d_post, d_gates, lengths, B, T, c->M, d_mels_raw, d_postnet_out, d_gates_raw, (cudaStream_t)stream);
 }
 
+// ------------------------------------------------------------------------------------------ decoder (teacher forced) backward
+namespace {
+
+struct Opnd { const __nv_bfloat16* base; int Kin, kin_ld, Kout, rows; long long plane; };
+
+#define BULK_PARTIAL_FLOATS (24ll << 20)   // 96 MB of split-K slabs shared by all bulk weight-gradient GEMMs
+
+// C[z][m][n] = sum_k A[m + z*a_zrow][k] B[n + z*b_zrow][k + shiftB]  (see gemmnt.cuh)
+int bulk_gemm(t2_ctx* c, const Opnd& A, const Opnd& Bo, int M, int N, int shiftB, const GemmNtOut& o, float* partial, cudaStream_t st,
+              int nz = 1, int a_zrow = 0, int b_zrow = 0, bool direct = false) {
+  GemmNtArgs a{};
+  a.M = M; a.N = N; a.NT = (N >= 128 || N % 16) ? (N >= 128 ? 128 : ((N + 15) & ~15)) : N;
+  a.Kin = A.Kin; a.Kout = A.Kout; a.nz = nz; a.shift0 = shiftB; a.shift_step = 0; a.a_zrow = a_zrow; a.b_zrow = b_zrow;
+  a.npass = c->npass;
+  T2_REQUIRE(shiftB % 8 == 0, T2_ERR_ARG, "bulk_gemm: operand shift must be a multiple of 8 elements");
+  if (direct) { a.splitk = 1; a.direct_out = o.out; a.direct_ldm = o.ldm; }
+  else {
+    a.splitk = 0;
+    const long long need = gemmnt_partial_floats(a, c->num_sms);
+    T2_REQUIRE(need <= BULK_PARTIAL_FLOATS, T2_ERR_WORKSPACE, "bulk_gemm: split-K slab of %lld floats exceeds the reserved %lld", need,
+               (long long)BULK_PARTIAL_FLOATS);
+    a.partial = partial;
+  }
+  RC(gemmnt_make_map(&a.a_map, A.base, A.Kin, A.kin_ld, A.Kout, A.rows, A.plane, 128, c->npass));
+  RC(gemmnt_make_map(&a.b_map, Bo.base, Bo.Kin, Bo.kin_ld, Bo.Kout, Bo.rows, Bo.plane, a.NT, c->npass));
+  return gemmnt_launch(a, o, st);
+}
+
+int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const unsigned char* mask, const float* mel_target, int B, int L,
+                    int T, const unsigned char* att_keep, const unsigned char* rnn_keep, unsigned long long seed, const float* aligns,
+                    const float* d_mels, const float* d_gates, const DecTape& tp, float* d_memory, float* d_pmem, Arena& wa,
+                    cudaStream_t st) {
+  const D2Dims d = dims2(c, B, L);
+  const int H = d.H, R = d.R, P = d.P, A = d.A, M = d.M, EF = d.EF, C = d.C;
+  const int S = db_parts(d);
+  const long long TB = (long long)T * D2_BP, TB1 = (long long)(T + 1) * D2_BP;
+  const int Tp = round8(T);
+  const int Nn = T * B, Np = round8(Nn);
+  const int nsmall = (int)db_small_floats(d);
+  // ---- workspace
+  void* scratch = wa.take<char>(bn_scratch_bytes(std::max(M, 128)));
+  __nv_bfloat16* dP = wa.take<__nv_bfloat16>((size_t)2 * TB * PROJ_LD);
+  __nv_bfloat16* dPT = wa.take<__nv_bfloat16>((size_t)2 * PROJ_LD * TB);
+  float* dprojin = wa.take<float>((size_t)TB * d.KprojP);
+  __nv_bfloat16* dg_att = wa.take<__nv_bfloat16>((size_t)2 * D2_BP * 4 * H);
+  __nv_bfloat16* dg_dec = wa.take<__nv_bfloat16>((size_t)2 * D2_BP * 4 * R);
+  __nv_bfloat16* dgT_att = wa.take<__nv_bfloat16>((size_t)2 * 4 * H * TB);
+  __nv_bfloat16* dgT_dec = wa.take<__nv_bfloat16>((size_t)2 * 4 * R * TB);
+  const int64_t zoff0 = wa.off;
+  float* dx_att = wa.take<float>((size_t)c->KattT * D2_BP);
+  float* dx_dec = wa.take<float>((size_t)c->KdecT * D2_BP);
+  float* dconv = wa.take<float>((size_t)2 * D2_BP * L);
+  float* gcum = wa.take<float>((size_t)D2_BP * L);
+  unsigned* barrier = wa.take<unsigned>(4);
+  float* dbias = wa.take<float>((size_t)8 * H);
+  const int64_t zoff1 = wa.off;
+  float* dpre = wa.take<float>((size_t)TB * P);
+  float* dctx_tot = wa.take<float>((size_t)TB * EF);
+  float* dq = wa.take<float>((size_t)T * S * D2_BP * A);
+  float* small_partial = wa.take<float>((size_t)128 * nsmall);
+  float* small_sum = wa.take<float>(nsmall);
+  __nv_bfloat16* xT_att = wa.take<__nv_bfloat16>((size_t)2 * d.KattP * TB1);
+  __nv_bfloat16* xT_dec = wa.take<__nv_bfloat16>((size_t)2 * d.KdecP * TB1);
+  __nv_bfloat16* dqT = wa.take<__nv_bfloat16>((size_t)2 * A * TB);
+  __nv_bfloat16* alT = wa.take<__nv_bfloat16>((size_t)2 * B * L * Tp);
+  __nv_bfloat16* dcT = wa.take<__nv_bfloat16>((size_t)2 * B * EF * Tp);
+  float* d2 = wa.take<float>((size_t)Nn * P);
+  float* dp1 = wa.take<float>((size_t)Nn * P);
+  __nv_bfloat16* d2b = wa.take<__nv_bfloat16>((size_t)2 * Nn * P);
+  __nv_bfloat16* d2T = wa.take<__nv_bfloat16>((size_t)2 * P * Np);
+  __nv_bfloat16* p1T = wa.take<__nv_bfloat16>((size_t)2 * P * Np);
+  __nv_bfloat16* xT = wa.take<__nv_bfloat16>((size_t)2 * M * Np);
+  float* wtmp = wa.take<float>((size_t)(M + 1) * d.KprojP);
+  float* partial = wa.take<float>(BULK_PARTIAL_FLOATS);
+  if (!wa.base) return T2_OK;
+  T2_REQUIRE(!wa.overflow, T2_ERR_WORKSPACE, "t2_decode_tf_bwd: workspace too small");
+
+  NEED_PARAM(wq, "decoder.attention.query_layer.weight", (size_t)A * H);
+  NEED_PARAM(wv, "decoder.attention.v.weight", A);
+  NEED_GRAD(g_att_ih, "decoder.att_rnn.weight_ih", (size_t)4 * H * (P + EF));
+  NEED_GRAD(g_att_hh, "decoder.att_rnn.weight_hh", (size_t)4 * H * H);
+  NEED_GRAD(g_att_bi, "decoder.att_rnn.bias_ih", 4 * H);
+  NEED_GRAD(g_att_bh, "decoder.att_rnn.bias_hh", 4 * H);
+  NEED_GRAD(g_dec_ih, "decoder.lstm.weight_ih", (size_t)4 * R * (H + EF + C));
+  NEED_GRAD(g_dec_hh, "decoder.lstm.weight_hh", (size_t)4 * R * R);
+  NEED_GRAD(g_dec_bi, "decoder.lstm.bias_ih", 4 * R);
+  NEED_GRAD(g_dec_bh, "decoder.lstm.bias_hh", 4 * R);
+  NEED_GRAD(g_wq, "decoder.attention.query_layer.weight", (size_t)A * H);
+  NEED_GRAD(g_v, "decoder.attention.v.weight", A);
+  NEED_GRAD(g_lconv, "decoder.attention.location_conv.weight", 32 * 2 * 31);
+  NEED_GRAD(g_ldense, "decoder.attention.location_dense.weight", (size_t)A * 32);
+  NEED_GRAD(g_wmel, "decoder.mel_out.weight", (size_t)M * (R + EF + C));
+  NEED_GRAD(g_bmel, "decoder.mel_out.bias", M);
+  NEED_GRAD(g_wgate, "decoder.gate.weight", R + EF);
+  NEED_GRAD(g_bgate, "decoder.gate.bias", 1);
+  NEED_GRAD(g_w1, "prenet.0.weight", (size_t)P * M);
+  NEED_GRAD(g_w2, "prenet.3.weight", (size_t)P * P);
+
+  // ---- projection backward (bulk): d[rnn_h | ctx | controls] for every frame; bias gradients
+  RC(build_dproj_launch(d_mels, d_gates, B, T, M, PROJ_LD, dP, dPT, st));
+  {
+    Opnd Aop{dP, M + 1, PROJ_LD, 1, (int)TB, TB * PROJ_LD};
+    Opnd Bop{c->WprojT_b, M + 1, PROJ_LD, 1, d.KprojP, (long long)d.KprojP * PROJ_LD};
+    RC(bulk_gemm(c, Aop, Bop, (int)TB, d.KprojP, 0, GemmNtOut{dprojin, d.KprojP, 1, 0, 1.f, 0}, nullptr, st, 1, 0, 0, true));
+  }
+  RC(colsum_launch(d_mels, (long long)B * T, M, M, g_bmel, scratch, st));
+  RC(colsum_launch(d_gates, (long long)B * T, 1, 1, g_bgate, scratch, st));
+
+  // ---- the sequential part
+  T2_CHECK_CUDA(cudaMemsetAsync(wa.base + zoff0, 0, (size_t)(zoff1 - zoff0), st));
+  T2_CHECK_CUDA(cudaMemsetAsync(d_pmem, 0, (size_t)B * L * A * sizeof(float), st));
+  DBWeights w{wq->ptr, wv->ptr, c->loc_conv_t, c->loc_dense_t};
+  DBTape t{};
+  t.sav_att = tp.sav_att; t.sav_dec = tp.sav_dec; t.q = tp.q; t.w_hist = tp.w_hist; t.wcum_hist = tp.wcum_hist;
+  t.memory = memory; t.pmem = pmem; t.mask = mask; t.att_keep = att_keep; t.rnn_keep = rnn_keep; t.seed = seed; t.hidden_dropout = 1;
+  DBWork k{};
+  k.dprojin = dprojin; k.dg_att = dg_att; k.dg_dec = dg_dec; k.dgT_att = dgT_att; k.dgT_dec = dgT_dec; k.dx_att = dx_att; k.dx_dec = dx_dec;
+  k.dpre = dpre; k.dctx_tot = dctx_tot; k.dq = dq; k.dpm = d_pmem; k.dconv = dconv; k.gcum = gcum; k.small_partial = small_partial;
+  k.dbias = dbias; k.barrier = barrier;
+  DBMaps maps;
+  maps.wt_att = c->map_wt_att; maps.wt_dec = c->map_wt_dec;
+  {
+    const unsigned zb = c->npass == 3 ? 2u : 1u;
+    unsigned box[3] = {TG_BK, TG_N, zb};
+    unsigned long long dims[3] = {4ull * H, (unsigned long long)D2_BP, 2ull};
+    unsigned long long sb[2] = {4ull * H * 2, 4ull * H * D2_BP * 2};
+    RC(tc_make_tmap_bf16(&maps.dg_att, dg_att, 3, dims, sb, box));
+    RC(tc_make_tmap_bf16(&maps.dg_dec, dg_dec, 3, dims, sb, box));
+  }
+  T2_CHECK_CUDA(cudaMemsetAsync(c->prof_buf, 0, 16 * sizeof(unsigned long long), st));
+  RC(db_launch(d, T, c->KattT, c->KdecT, w, t, k, maps, c->prof_buf + 8, st));
+
+  // ---- small attention weights, biases
+  RC(partial_sum_launch(small_partial, 128, nsmall, small_sum, st));
+  RC(copy2_launch(small_sum, g_ldense, nullptr, A * 32, st));
+  RC(copy2_launch(small_sum + A * 32, g_lconv, nullptr, 2 * 31 * 32, st));
+  RC(copy2_launch(small_sum + A * 32 + 2 * 31 * 32, g_v, nullptr, A, st));
+  RC(copy2_launch(dbias, g_att_bi, g_att_bh, 4 * H, st));
+  RC(copy2_launch(dbias + 4 * H, g_dec_bi, g_dec_bh, 4 * R, st));
+
+  // ---- K-major copies of the per-frame LSTM inputs: xT[k][slot*64 + b]
+  RC(transpose_bf16_launch(tp.xatt, d.KattP, (long long)2 * D2_BP * d.KattP, (long long)D2_BP * d.KattP, xT_att, D2_BP, d.KattP, D2_BP, TB1,
+                           D2_BP, T + 1, 0, (long long)d.KattP * TB1, st));
+  RC(transpose_bf16_launch(tp.tfp, P, (long long)2 * D2_BP * P, (long long)D2_BP * P, xT_att, D2_BP, P, D2_BP, TB1, D2_BP, T + 1, 0,
+                           (long long)d.KattP * TB1, st));   // teacher forcing: the prenet block of the input lives in tfp
+  RC(transpose_bf16_launch(tp.xdec, d.KdecP, (long long)2 * D2_BP * d.KdecP, (long long)D2_BP * d.KdecP, xT_dec, D2_BP, d.KdecP, D2_BP, TB1,
+                           D2_BP, T + 1, 0, (long long)d.KdecP * TB1, st));
+  auto xrows = [&](const __nv_bfloat16* xTb, int KP, int row0, int rows, bool all_slots = false) {
+    return Opnd{xTb + (size_t)row0 * TB1, (int)(all_slots ? TB1 : TB), (int)TB1, 1, rows, (long long)KP * TB1};
+  };
+  {  // LSTMCell weight gradients  dW[r][k] = sum_{t,b} dgates[t,b][r] x[t,b][k]
+    Opnd Ga{dgT_att, (int)TB, (int)TB, 1, 4 * H, 4ll * H * TB}, Gd{dgT_dec, (int)TB, (int)TB, 1, 4 * R, 4ll * R * TB};
+    RC(bulk_gemm(c, Ga, xrows(xT_att, d.KattP, 0, P + EF), 4 * H, P + EF, 0, GemmNtOut{g_att_ih, P + EF, 1, 0, 1.f, 0}, partial, st));
+    RC(bulk_gemm(c, Ga, xrows(xT_att, d.KattP, P + EF, H), 4 * H, H, 0, GemmNtOut{g_att_hh, H, 1, 0, 1.f, 0}, partial, st));
+    RC(bulk_gemm(c, Gd, xrows(xT_dec, d.KdecP, 0, H + EF + C), 4 * R, H + EF + C, 0, GemmNtOut{g_dec_ih, H + EF + C, 1, 0, 1.f, 0}, partial, st));
+    RC(bulk_gemm(c, Gd, xrows(xT_dec, d.KdecP, H + EF + C, R), 4 * R, R, 0, GemmNtOut{g_dec_hh, R, 1, 0, 1.f, 0}, partial, st));
+  }
+  {  // query layer: dWq[a][h] = sum dq[t,b][a] att_h_t[b][h]   (att_h_t = first block of the decoder-cell input of frame t)
+    RC(dq_sumT_launch(dq, T, S, A, B, dqT, st));
+    Opnd Q{dqT, (int)TB, (int)TB, 1, A, (long long)A * TB};
+    RC(bulk_gemm(c, Q, xrows(xT_dec, d.KdecP, 0, H), A, H, 0, GemmNtOut{g_wq, H, 1, 0, 1.f, 0}, partial, st));
+  }
+  {  // mel / gate projection weights: input [rnn_h_t | ctx_t | controls]; rnn_h_t sits in slot t+1 of the decoder-cell input
+    Opnd Pm{dPT, (int)TB, (int)TB, 1, M + 1, (long long)PROJ_LD * TB};
+    RC(bulk_gemm(c, Pm, xrows(xT_dec, d.KdecP, H + EF + C, R, true), M + 1, R, D2_BP, GemmNtOut{wtmp, d.KprojP, 1, 0, 1.f, 0}, partial, st));
+    RC(bulk_gemm(c, Pm, xrows(xT_dec, d.KdecP, H, EF + C), M + 1, EF + C, 0, GemmNtOut{wtmp + R, d.KprojP, 1, 0, 1.f, 0}, partial, st));
+    T2_CHECK_CUDA(cudaMemcpy2DAsync(g_wmel, (size_t)(R + EF + C) * 4, wtmp, (size_t)d.KprojP * 4, (size_t)(R + EF + C) * 4, M,
+                                    cudaMemcpyDeviceToDevice, st));
+    T2_CHECK_CUDA(cudaMemcpyAsync(g_wgate, wtmp + (size_t)M * d.KprojP, (size_t)(R + EF) * 4, cudaMemcpyDeviceToDevice, st));
+  }
+  {  // attention memory: d memory[b][l][c] = sum_t w_t[b][l] dctx_t[b][c]   (one GEMM per utterance, batched over z = b)
+    RC(transpose_split_launch(aligns, L, (long long)T * L, alT, T, L, Tp, Tp, (long long)L * Tp, B, (long long)B * L * Tp, st));
+    RC(transpose_split_launch(dctx_tot, (long long)D2_BP * EF, EF, dcT, T, EF, Tp, Tp, (long long)EF * Tp, B, (long long)B * EF * Tp, st));
+    Opnd Aw{alT, T, Tp, 1, B * L, (long long)B * L * Tp}, Dc{dcT, T, Tp, 1, B * EF, (long long)B * EF * Tp};
+    RC(bulk_gemm(c, Aw, Dc, L, EF, 0, GemmNtOut{d_memory, EF, 1, (long long)L * EF, 1.f, 0}, partial, st, B, L, EF));
+  }
+  {  // prenet backward (model/tacotron2.py:85-92), rows n = t*B + b, t < T (the T+1-th prenet frame is never used, :317)
+    const float scale = 1.0f / (1.0f - c->cfg.dropout);
+    RC(prenet_d2_launch(dpre, tp.tfp, B, T, P, scale, d2, st));
+    RC(split_cl_launch(d2, (long long)Nn * P, d2b, 1, Nn, P, st));
+    RC(transpose_split_launch(d2, P, 0, d2T, Nn, P, Np, Np, 0, 1, (long long)P * Np, st));
+    RC(transpose_split_launch(tp.p1, P, 0, p1T, Nn, P, Np, Np, 0, 1, (long long)P * Np, st));
+    Opnd D2T{d2T, Nn, Np, 1, P, (long long)P * Np}, P1T{p1T, Nn, Np, 1, P, (long long)P * Np};
+    RC(bulk_gemm(c, D2T, P1T, P, P, 0, GemmNtOut{g_w2, P, 1, 0, 1.f, 0}, partial, st));
+    Opnd D2{d2b, P, P, 1, Nn, (long long)Nn * P}, W2T{c->W2T_b, P, P, 1, P, (long long)P * P};
+    RC(bulk_gemm(c, D2, W2T, Nn, P, 0, GemmNtOut{dp1, P, 1, 0, 1.f, 0}, nullptr, st, 1, 0, 0, true));
+    RC(prenet_d1_launch(dp1, tp.p1, (long long)Nn * P, scale, d2, st));   // d2 buffer reused for d1
+    RC(transpose_split_launch(d2, P, 0, d2T, Nn, P, Np, Np, 0, 1, (long long)P * Np, st));
+    RC(prenet_xT_launch(mel_target, B, T, M, Np, xT, st));
+    Opnd XT{xT, Nn, Np, 1, M, (long long)M * Np};
+    RC(bulk_gemm(c, D2T, XT, P, M, 0, GemmNtOut{g_w1, M, 1, 0, 1.f, 0}, partial, st));
+  }
+  return T2_OK;
+}
+
+}  // namespace
+
+// Backward of the teacher-forced frame loop.  d_mels (B,T,M) / d_gates (B,T): gradients w.r.t. the raw decoder outputs;
+// alignments (B,T,L) as returned by the forward.  Outputs: d_memory (B,L,EF), d_processed_memory (B,L,A); decoder.* and
+// prenet.* parameter gradients go to their registered destinations.
+extern "C" int t2_decode_tf_bwd(t2_ctx* c, const float* memory, const float* processed_memory, const unsigned char* mask,
+                                const float* mel_target, int B, int L, int T, const unsigned char* att_keep, const unsigned char* rnn_keep,
+                                unsigned long long seed, const float* alignments, const float* d_mels, const float* d_gates, const void* tape,
+                                long long tape_bytes, float* d_memory, float* d_processed_memory, void* ws, long long ws_bytes,
+                                void* stream) {
+  CHECK_CTX("t2_decode_tf_bwd");
+  T2_REQUIRE(memory && processed_memory && mask && mel_target && alignments && d_mels && d_gates && tape && d_memory && d_processed_memory && ws,
+             T2_ERR_ARG, "t2_decode_tf_bwd: null argument");
+  T2_REQUIRE(B > 0 && B <= D2_BP && L > 0 && T > 0, T2_ERR_ARG, "t2_decode_tf_bwd: bad sizes");
+  Arena ta(const_cast<void*>(tape), tape_bytes);
+  DecTape tp = plan_dec_tape(dims2(c, B, L), B, L, T, ta);
+  T2_REQUIRE(!ta.overflow, T2_ERR_WORKSPACE, "t2_decode_tf_bwd: tape too small");
+  Arena wa(ws, ws_bytes);
+  return decode_bwd_impl(c, memory, processed_memory, mask, mel_target, B, L, T, att_keep, rnn_keep, seed, alignments, d_mels, d_gates, tp,
+                         d_memory, d_processed_memory, wa, (cudaStream_t)stream);
+}
+
+long long decode_bwd_ws_bytes(t2_ctx* c, int B, int L, int T) {
+  Arena wa(nullptr, 0);
+  DecTape tp{};
+  decode_bwd_impl(c, nullptr, nullptr, nullptr, nullptr, std::min(B, D2_BP), L, T, nullptr, nullptr, 0, nullptr, nullptr, nullptr, tp, nullptr,
+                  nullptr, wa, nullptr);
+  return wa.off;
+}
+
 extern "C" long long t2_train_workspace_bytes(const t2_ctx* cc, int B, int L, int T) {
   t2_ctx* c = const_cast<t2_ctx*>(cc);
   if (!c || B <= 0 || L <= 0 || T <= 0) return -1;
   long long best = t2_workspace_bytes(cc, B, L, T);
   best = std::max(best, postnet_bwd_ws_bytes(c, B, T) + bn_scratch_bytes(c->PD));
+  best = std::max(best, decode_bwd_ws_bytes(c, B, L, T));
   return best + 4096;
 }
+

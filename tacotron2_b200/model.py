@@ -266,6 +266,27 @@ class Tacotron2(nn.Module):
     def _draw_seed():
         return int(torch.randint(0, 2**62, (1,)).item())  # CPU generator: follows torch.manual_seed like run/say.py:40
 
+    def _decode_tf_train(self, memory, pmem, mask, ctrl, target, masks):
+        """Teacher-forced frame loop under train() with autograd (<= 64 utterances per launch; larger batches are chunked --
+        utterances are independent inside the loop, and autograd sums the per-chunk parameter gradients)."""
+        from .autograd import DecodeTfFn
+        dev = memory.device
+        B = memory.shape[0]
+        pk, ak, rk = (self._u8(masks.get(k), dev) for k in ("prenet", "att_h", "rnn_h"))
+        params = list(self._group_params("decoder").values())
+        seed = self._draw_seed()
+        outs = []
+        for b0 in range(0, B, _MAX_DECODE_BATCH):
+            b1 = min(B, b0 + _MAX_DECODE_BATCH)
+            whole = b0 == 0 and b1 == B
+            sl = (lambda t: t) if whole else (lambda t: None if t is None else t[b0:b1].contiguous())
+            sk = (lambda t: t) if whole else (lambda t: None if t is None else t[:, :, b0:b1].contiguous())
+            sh = (lambda t: t) if whole else (lambda t: None if t is None else t[:, b0:b1].contiguous())
+            outs.append(DecodeTfFn.apply(self, sl(mask), sl(ctrl), sl(target), sk(pk), sh(ak), sh(rk), seed + b0, sl(memory), sl(pmem), *params))
+        if len(outs) == 1:
+            return outs[0]
+        return tuple(torch.cat([o[i] for o in outs], 0) for i in range(3))
+
     def loss(self, mels, mels_post, gates, mel_target, gate_target):
         """training_step loss (model/tts_model.py:197-201) as one kernel: BCEWithLogits + MSE + MSE."""
         from .autograd import LossFn

@@ -93,3 +93,58 @@ def test_postnet_train_fwd_bwd(B, T):
     st = m.state_dict()
     assert float((st["postnet.postnet.1.running_mean"].cpu() - rm).abs().max()) <= 1e-5
     assert float((st["postnet.postnet.1.running_var"].cpu() - rv).abs().max()) <= 1e-5
+
+
+def _oracle_decode_tf(sd, a, memory, pmem, mask, target, masks, controls=None):
+    """model/tacotron2.py:255-258,276-317 in train() mode from given attention memory (oracle building blocks)."""
+    B, L, _ = memory.shape
+    T = target.shape[1]
+    pk = masks["prenet"]
+    dec_in = torch.nn.functional.pad(target, (0, 0, 1, 0))
+    pre = [O.prenet(sd, dec_in[:, t], pk[t, 0], pk[t, 1], a.dropout) for t in range(T + 1)]
+    state = O.init_state(B, L, a.att_rnn_dim, a.rnn_hidden_dim, a.encoded_full_dim)
+    mels, gates, als = [], [], []
+    for t in range(T):
+        mel, gate, state = O.decoder_step(sd, pre[t], state, memory, pmem, mask, controls, masks["att_h"][t], masks["rnn_h"][t])
+        mels.append(mel), gates.append(gate[:, 0]), als.append(state["w"])
+    return torch.stack(mels, 1), torch.stack(gates, 1), torch.stack(als, 1)
+
+
+@pytest.mark.parametrize("args,B,L,T", [(synth.VANILLA, 3, 29, 17), (synth.VANILLA, 40, 70, 9), (synth.CONDITIONED, 2, 18, 9),
+                                        (synth.VANILLA, 64, 45, 5)])
+def test_decoder_tf_train_fwd_bwd(args, B, L, T):
+    a = args
+    sd = synth.synth_state_dict(a)
+    m = _model(a, sd)
+    masks = synth.synth_masks(a, B, L, T, seed=13, train=True)
+    batch = synth.synth_batch(a, B, L, T, seed=77)
+    g = torch.Generator().manual_seed(9)
+    EF = a.encoded_full_dim
+    memory = torch.randn(B, L, EF, generator=g) * 0.3
+    pmem = torch.randn(B, L, a.att_dim, generator=g) * 0.5
+    lens = batch["chars_idx_len"]
+    mask = torch.arange(L)[None, :] >= lens[:, None]
+    target = batch["mel_spectrogram"]
+    ctrl = batch.get("controls")
+    dm, dg = torch.randn(B, T, a.num_mels, generator=g), torch.randn(B, T, generator=g)
+    # oracle
+    sdg = _sd_grad(sd)
+    mo, po = memory.clone().requires_grad_(True), pmem.clone().requires_grad_(True)
+    w_mels, w_gates, w_al = _oracle_decode_tf(sdg, a, mo, po, mask, target, masks, ctrl)
+    ((w_mels * dm).sum() + (w_gates * dg).sum()).backward()
+    # CUDA
+    dev = _dev()
+    mc, pc = memory.clone().to(dev).requires_grad_(True), pmem.clone().to(dev).requires_grad_(True)
+    m._ready(dev)
+    mels, gates, al = m._decode_tf_train(mc, pc, mask.to(dev).to(torch.uint8).contiguous(), None if ctrl is None else ctrl.to(dev),
+                                         target.to(dev).contiguous(), masks)
+    ((mels * dm.to(dev)).sum() + (gates * dg.to(dev)).sum()).backward()
+    assert float((mels.detach().cpu() - w_mels.detach()).abs().max()) <= 1e-3
+    assert float((al.detach().cpu() - w_al.detach()).abs().max()) <= 1e-4
+    assert float((gates.detach().cpu() - w_gates.detach()).abs().max()) <= 1e-3
+    for name, got, want in (("d_memory", mc.grad, mo.grad), ("d_pmem", pc.grad, po.grad)):
+        scale = float(want.abs().max())
+        err = float((got.cpu() - want).abs().max())
+        assert err <= GTOL * scale, (name, err, scale)
+    _check_grads(m, sdg, "decoder.")
+    _check_grads(m, sdg, "prenet.")
