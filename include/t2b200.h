@@ -121,6 +121,21 @@ int t2_postnet_bwd(t2_ctx* ctx, int B, int T, const unsigned char* keep, unsigne
                    const float* d_mels_in, const void* tape, long long tape_bytes, float* d_mels, void* ws, long long ws_bytes,
                    void* stream);
 
+/* Encoder.forward under train() (model/encoder.py:54-67) and its backward.  keep (3,B,L,E) uint8 or NULL (counter RNG).
+ * `encoded` in t2_encoder_bwd is the forward's output (the BiLSTM hidden states, needed for the recurrent weight gradient). */
+long long t2_encoder_tape_bytes(const t2_ctx* ctx, int B, int L);
+int t2_encoder_train_fwd(t2_ctx* ctx, const long long* chars_idx, const long long* lens, int B, int L, const unsigned char* keep,
+                         unsigned long long seed, float* encoded, void* tape, long long tape_bytes, void* ws, long long ws_bytes,
+                         void* stream);
+int t2_encoder_bwd(t2_ctx* ctx, const long long* chars_idx, const long long* lens, int B, int L, const unsigned char* keep,
+                   unsigned long long seed, const float* encoded, const float* d_encoded, const void* tape, long long tape_bytes, void* ws,
+                   long long ws_bytes, void* stream);
+/* Backward of t2_memory_fwd (conditioning + att_encoder, model/tacotron2.py:201-212,229): d_memory (B,L,EF),
+ * d_processed_memory (B,L,A) -> d_encoded (B,L,E); writes att_encoder / speaker_embedding / description_embeddings_linear
+ * gradients.  `memory` is the forward's output. */
+int t2_memory_bwd(t2_ctx* ctx, const float* memory, const long long* speaker_id, const float* description, const float* d_memory,
+                  const float* d_processed_memory, int B, int L, float* d_encoded, void* ws, long long ws_bytes, void* stream);
+
 /* Teacher-forced frame loop under train() (model/tacotron2.py:255-258,276-317; hidden-state dropouts p = 0.1 active,
  * model/decoder.py:75,101): same persistent kernel in history mode.  Arguments as t2_decode_tf; tape from t2_decode_tape_bytes. */
 long long t2_decode_tape_bytes(const t2_ctx* ctx, int B, int L, int T);

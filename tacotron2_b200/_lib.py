@@ -47,6 +47,10 @@ SIGNATURES = {
     "t2_postnet_tape_bytes": (_LL, [_P, _I, _I]),
     "t2_postnet_train_fwd": (_I, [_P, _P, _I, _I, _I, _P, _ULL, _P, _P, _LL, _P, _LL, _P]),
     "t2_postnet_bwd": (_I, [_P, _I, _I, _P, _ULL, _P, _P, _P, _LL, _P, _P, _LL, _P]),
+    "t2_encoder_tape_bytes": (_LL, [_P, _I, _I]),
+    "t2_encoder_train_fwd": (_I, [_P, _P, _P, _I, _I, _P, _ULL, _P, _P, _LL, _P, _LL, _P]),
+    "t2_encoder_bwd": (_I, [_P, _P, _P, _I, _I, _P, _ULL, _P, _P, _P, _LL, _P, _LL, _P]),
+    "t2_memory_bwd": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _LL, _P]),
     "t2_decode_tape_bytes": (_LL, [_P, _I, _I, _I]),
     "t2_decode_tf_train_fwd": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _P, _ULL, _P, _P, _P, _P, _LL, _P, _LL, _P]),
     "t2_decode_tf_bwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _ULL, _P, _P, _P, _P, _LL, _P, _P, _P, _LL, _P]),

@@ -72,6 +72,66 @@ class PostnetFn(torch.autograd.Function):
         return (None, None, None, d_mels, *views)
 
 
+class EncoderFn(torch.autograd.Function):
+    """Encoder.forward under train() (model/encoder.py:54-67)."""
+
+    @staticmethod
+    def forward(ctx, owner, chars, lens, keep, seed, *params):
+        dev = chars.device
+        lib = owner._ready(dev)
+        B, L = chars.shape
+        tape = torch.empty(lib.t2_encoder_tape_bytes(owner._ctx, B, L), dtype=torch.uint8, device=dev)
+        ws = owner._train_workspace(lib, dev, B, L, 1)
+        out = torch.empty(B, L, owner.embedding_dim, device=dev)
+        _lib.check(lib.t2_encoder_train_fwd(owner._ctx, P(chars), P(lens), B, L, P(keep), seed, P(out), P(tape), tape.numel(), P(ws),
+                                            ws.numel(), _stream()), "t2_encoder_train_fwd")
+        owner._bn_dirty = True
+        ctx.owner, ctx.args, ctx.tape, ctx.out = owner, (chars, lens, keep, seed, B, L), tape, out
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        owner = ctx.owner
+        chars, lens, keep, seed, B, L = ctx.args
+        lib = owner._ready(chars.device)
+        flat, views = _bucket(owner, lib, owner._group_params("encoder"))
+        ws = owner._train_workspace(lib, chars.device, B, L, 1)
+        _lib.check(lib.t2_encoder_bwd(owner._ctx, P(chars), P(lens), B, L, P(keep), seed, P(ctx.out), P(d_out.contiguous()), P(ctx.tape),
+                                      ctx.tape.numel(), P(ws), ws.numel(), _stream()), "t2_encoder_bwd")
+        _after_bucket(owner, flat)
+        return (None,) * 5 + tuple(views)
+
+
+class MemoryFn(torch.autograd.Function):
+    """Conditioning + att_encoder (model/tacotron2.py:201-212,229): encoded -> (memory, processed_memory)."""
+
+    @staticmethod
+    def forward(ctx, owner, spk, desc, encoded, *params):
+        memory, pmem = owner._memory(encoded, spk, desc)
+        ctx.owner, ctx.args = owner, (spk, desc, memory)
+        return memory, pmem
+
+    @staticmethod
+    def backward(ctx, d_memory, d_pmem):
+        owner = ctx.owner
+        spk, desc, memory = ctx.args
+        dev = memory.device
+        B, L, _ = memory.shape
+        lib = owner._ready(dev)
+        flat, views = _bucket(owner, lib, owner._group_params("memory"))
+        ws = owner._train_workspace(lib, dev, B, L, 1)
+        z = lambda t, like: torch.zeros_like(like) if t is None else t.contiguous()  # noqa: E731
+        d_memory = z(d_memory, memory)
+        d_pmem = torch.zeros(B, L, owner.att_dim, device=dev) if d_pmem is None else d_pmem.contiguous()
+        d_enc = torch.empty(B, L, owner.embedding_dim, device=dev)
+        spk_c = None if spk is None else spk.to(device=dev, dtype=torch.int64).contiguous()
+        desc_c = None if desc is None else desc.to(device=dev, dtype=torch.float32).contiguous()
+        _lib.check(lib.t2_memory_bwd(owner._ctx, P(memory), P(spk_c), P(desc_c), P(d_memory), P(d_pmem), B, L, P(d_enc), P(ws), ws.numel(),
+                                     _stream()), "t2_memory_bwd")
+        _after_bucket(owner, flat)
+        return (None, None, None, d_enc, *views)
+
+
 class DecodeTfFn(torch.autograd.Function):
     """The teacher-forced frame loop under train() (model/tacotron2.py:255-258,276-317) for <= 64 utterances."""
 

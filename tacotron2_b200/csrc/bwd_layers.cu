@@ -359,3 +359,100 @@ int bilstm_bwd_launch(const float* sav, const float* Whh, const long long* lens,
   T2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, bilstm_bwd_cluster_kernel, sav, Whh, lens, d_out, dgates, B, L, Hh));
   return T2_OK;
 }
+
+// ------------------------------------------------------------------------------------------ conditioning / embedding backward
+namespace {
+
+// backward of tanh(enc + speaker_emb) (model/tacotron2.py:201-202): de = dmem * (1 - mem^2) on the first E channels
+__global__ void condition_bwd_kernel(const float* __restrict__ dmem, const float* __restrict__ mem, int speaker, float* __restrict__ d_enc,
+                                     long long rows, int E, int EF) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < rows * E; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % E);
+    const long long r = i / E;
+    float g = dmem[r * EF + c];
+    if (speaker) { const float m = mem[r * EF + c]; g *= 1.f - m * m; }
+    d_enc[i] = g;
+  }
+}
+// d speaker_embedding[s][c] = sum over utterances with speaker s, all positions, of d_enc  (one block per (s), thread per c)
+__global__ void speaker_grad_kernel(const float* __restrict__ d_enc, const long long* __restrict__ spk, int B, int L, int E, float* __restrict__ out) {
+  const int s = blockIdx.x;
+  for (int c = threadIdx.x; c < E; c += blockDim.x) {
+    float acc = 0.f;
+    for (int b = 0; b < B; ++b) {
+      if (spk[b] != s) continue;
+      for (int l = 0; l < L; ++l) acc += d_enc[((size_t)b * L + l) * E + c];
+    }
+    out[(size_t)s * E + c] = acc;
+  }
+}
+// description path: dpre[b][j] = (sum_l dmem[b][l][E+j]) * (1 - dvec^2), dvec = memory[b][0][E+j]
+__global__ void desc_dpre_kernel(const float* __restrict__ dmem, const float* __restrict__ mem, int B, int L, int E, int D, float* __restrict__ dpre) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * D) return;
+  const int b = i / D, j = i % D;
+  float acc = 0.f;
+  for (int l = 0; l < L; ++l) acc += dmem[((size_t)b * L + l) * (E + D) + E + j];
+  const float v = mem[((size_t)b * L) * (E + D) + E + j];
+  dpre[i] = acc * (1.f - v * v);
+}
+__global__ void desc_wgrad_kernel(const float* __restrict__ dpre, const float* __restrict__ desc, int B, int D, int Din, float* __restrict__ dW,
+                                  float* __restrict__ db) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < D * Din) {
+    const int j = i / Din, k = i % Din;
+    float acc = 0.f;
+    for (int b = 0; b < B; ++b) acc = fmaf(dpre[b * D + j], desc[(size_t)b * Din + k], acc);
+    dW[i] = acc;
+  }
+  if (i < D) {
+    float acc = 0.f;
+    for (int b = 0; b < B; ++b) acc += dpre[b * D + i];
+    db[i] = acc;
+  }
+}
+// d embedding[row][c] = sum over positions with chars == row (row 0 = padding_idx gets no gradient, model/encoder.py:25)
+__global__ void embedding_grad_kernel(const float* __restrict__ dx, const long long* __restrict__ chars, long long npos, int E, int nrows,
+                                      float* __restrict__ out) {
+  const int row = blockIdx.x;
+  for (int c = threadIdx.x; c < E; c += blockDim.x) {
+    float acc = 0.f;
+    if (row > 0)
+      for (long long p = 0; p < npos; ++p)
+        if (chars[p] == row) acc += dx[p * E + c];
+    out[(size_t)row * E + c] = acc;
+  }
+}
+__global__ void zero_kernel(float* p, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) p[i] = 0.f;
+}
+
+}  // namespace
+
+int condition_bwd_launch(const float* dmem, const float* mem, int speaker, float* d_enc, long long rows, int E, int EF, cudaStream_t st) {
+  condition_bwd_kernel<<<gs(rows * E), 256, 0, st>>>(dmem, mem, speaker, d_enc, rows, E, EF);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+int speaker_grad_launch(const float* d_enc, const long long* spk, int B, int L, int E, int nspk, float* out, cudaStream_t st) {
+  speaker_grad_kernel<<<nspk, 256, 0, st>>>(d_enc, spk, B, L, E, out);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+int desc_bwd_launch(const float* dmem, const float* mem, const float* desc, int B, int L, int E, int D, int Din, float* dpre, float* dW,
+                    float* db, cudaStream_t st) {
+  desc_dpre_kernel<<<(B * D + 127) / 128, 128, 0, st>>>(dmem, mem, B, L, E, D, dpre);
+  desc_wgrad_kernel<<<(D * Din + 255) / 256, 256, 0, st>>>(dpre, desc, B, D, Din, dW, db);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+int embedding_grad_launch(const float* dx, const long long* chars, long long npos, int E, int nrows, float* out, cudaStream_t st) {
+  embedding_grad_kernel<<<nrows, 256, 0, st>>>(dx, chars, npos, E, nrows, out);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+int zero_launch(float* p, long long n, cudaStream_t st) {
+  zero_kernel<<<gs(n), 256, 0, st>>>(p, n);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}

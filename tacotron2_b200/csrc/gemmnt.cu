@@ -133,15 +133,15 @@ __global__ void gemm_nt_reduce_kernel(const float* __restrict__ partial, int spl
 // fp32 [nb][R][C] -> bf16 (hi,lo) [2][C][dst_ld] with batch bb at column offset bb*dst_boff (transposed); 32x32 tiles
 __global__ void transpose_split_kernel(const float* __restrict__ src, long long ld, long long src_bstride,
                                        __nv_bfloat16* __restrict__ dst, int R, int C, int R_ld, long long dst_ld, long long dst_boff,
-                                       long long plane) {
+                                       long long plane, int row_shift) {
   __shared__ float tile[32][33];
   const int bb = blockIdx.z;
   const float* s = src + (size_t)bb * src_bstride;
   __nv_bfloat16* d = dst + (size_t)bb * dst_boff;
   const int c = blockIdx.x * 32 + threadIdx.x;
   for (int i = threadIdx.y; i < 32; i += blockDim.y) {
-    const int r = blockIdx.y * 32 + i;
-    tile[i][threadIdx.x] = (r < R && c < C) ? s[(size_t)r * ld + c] : 0.f;
+    const int r = blockIdx.y * 32 + i + row_shift;
+    tile[i][threadIdx.x] = (r >= 0 && r < R && c < C) ? s[(size_t)r * ld + c] : 0.f;
   }
   __syncthreads();
   const int r2 = blockIdx.y * 32 + threadIdx.x;
@@ -149,7 +149,7 @@ __global__ void transpose_split_kernel(const float* __restrict__ src, long long 
     const int c2 = blockIdx.x * 32 + i;
     if (r2 < R_ld && c2 < C) {
       __nv_bfloat16 hi, lo;
-      tc::split_bf16(r2 < R ? tile[threadIdx.x][i] : 0.f, hi, lo);
+      tc::split_bf16(tile[threadIdx.x][i], hi, lo);
       d[(size_t)c2 * dst_ld + r2] = hi;
       d[plane + (size_t)c2 * dst_ld + r2] = lo;
     }
@@ -224,10 +224,10 @@ int gemmnt_make_map(CUtensorMap* m, const __nv_bfloat16* base, int Kin, int kin_
 }
 
 int transpose_split_launch(const float* src, long long ld, long long src_bstride, __nv_bfloat16* dst, int R, int C, int R_ld,
-                           long long dst_ld, long long dst_boff, int nbatch, long long dst_plane, cudaStream_t st) {
+                           long long dst_ld, long long dst_boff, int nbatch, long long dst_plane, cudaStream_t st, int row_shift) {
   if (R_ld <= 0 || C <= 0 || nbatch <= 0) return T2_OK;
   dim3 grid((C + 31) / 32, (R_ld + 31) / 32, nbatch), block(32, 8);
-  transpose_split_kernel<<<grid, block, 0, st>>>(src, ld, src_bstride, dst, R, C, R_ld, dst_ld, dst_boff, dst_plane);
+  transpose_split_kernel<<<grid, block, 0, st>>>(src, ld, src_bstride, dst, R, C, R_ld, dst_ld, dst_boff, dst_plane, row_shift);
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }

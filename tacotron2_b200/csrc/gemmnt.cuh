@@ -40,7 +40,7 @@ int gemmnt_make_map(CUtensorMap* m, const __nv_bfloat16* base, int Kin, int kin_
 // Batched transposes into K-major operands.  Batch bb reads src + bb*src_bstride ([R][C], row stride ld) and writes
 // dst[plane][c][bb*dst_boff + r] for r < R_ld (zeros for r >= R); dst row stride dst_ld, plane stride dst_plane elements.
 int transpose_split_launch(const float* src, long long ld, long long src_bstride, __nv_bfloat16* dst, int R, int C, int R_ld,
-                           long long dst_ld, long long dst_boff, int nbatch, long long dst_plane, cudaStream_t st);
+                           long long dst_ld, long long dst_boff, int nbatch, long long dst_plane, cudaStream_t st, int row_shift = 0);
 // row_shift: dst column r holds src row r + row_shift (zeros outside [0,R)) -- a TMA box may only start at a 16-byte
 // aligned element of the innermost dimension, so conv-tap / recurrence shifts are materialised as shifted copies.
 int transpose_bf16_launch(const __nv_bfloat16* src, long long src_ld, long long src_bstride, long long src_plane, __nv_bfloat16* dst,

@@ -443,12 +443,221 @@ long long decode_bwd_ws_bytes(t2_ctx* c, int B, int L, int T) {
   return wa.off;
 }
 
+// ------------------------------------------------------------------------------------------ encoder (train fwd / bwd)
+namespace {
+
+struct EncTape { __nv_bfloat16* x[4]; float* z[3]; float* mean[3]; float* rstd[3]; float* lstm_sav; };
+EncTape plan_enc_tape(const t2_ctx* c, int B, int L, Arena& ar) {
+  EncTape t{};
+  const int E = c->E, Hh = E / 2;
+  for (int i = 0; i < 4; ++i) t.x[i] = ar.take<__nv_bfloat16>((size_t)2 * B * L * E);
+  for (int i = 0; i < 3; ++i) {
+    t.z[i] = ar.take<float>((size_t)B * L * E);
+    t.mean[i] = ar.take<float>(E);
+    t.rstd[i] = ar.take<float>(E);
+  }
+  t.lstm_sav = ar.take<float>((size_t)B * L * 2 * 5 * Hh);
+  return t;
+}
+BnLayer enc_layer(const t2_ctx* c, const EncTape& tp, int i, int B, int L, const unsigned char* keep, unsigned long long seed,
+                  const float* gamma, const float* beta) {
+  BnLayer Ly{};
+  Ly.z = tp.z[i]; Ly.mean = tp.mean[i]; Ly.rstd = tp.rstd[i]; Ly.gamma = gamma; Ly.beta = beta;
+  Ly.C = c->E; Ly.act = ACT_RELU; Ly.dropout = 1;
+  Ly.keep = keep ? keep + (size_t)i * B * L * c->E : nullptr; Ly.keep_ld = c->E; Ly.p = c->cfg.dropout;
+  Ly.seed = seed; Ly.rng_base = (0x60ull + i) << 40;
+  return Ly;
+}
+
+int encoder_bwd_impl(t2_ctx* c, const long long* chars, const long long* lens, int B, int L, const unsigned char* keep,
+                     unsigned long long seed, const float* encoded, const float* d_encoded, const EncTape& tp, Arena& wa, cudaStream_t st) {
+  const int E = c->E, Hh = E / 2, KS = c->KS, Lp = round8(L), G8 = 8 * Hh;
+  void* scratch = wa.take<char>(bn_scratch_bytes(G8));
+  float* dgates = wa.take<float>((size_t)B * L * G8);
+  __nv_bfloat16* dgb = wa.take<__nv_bfloat16>((size_t)2 * B * L * G8);
+  __nv_bfloat16* dgT = wa.take<__nv_bfloat16>((size_t)2 * G8 * B * Lp);
+  __nv_bfloat16* hT = wa.take<__nv_bfloat16>((size_t)2 * 2 * Hh * B * Lp);     // per direction: shifted h_{prev}, K-major
+  __nv_bfloat16* xT = wa.take<__nv_bfloat16>((size_t)std::max(KS, 1) * 2 * E * B * Lp);
+  float* wtmp = wa.take<float>((size_t)G8 * E);
+  float* btmp = wa.take<float>(G8);
+  float* dyA = wa.take<float>((size_t)B * L * E);
+  float* dyB = wa.take<float>((size_t)B * L * E);
+  float* dzf = wa.take<float>((size_t)B * L * E);
+  __nv_bfloat16* dz = wa.take<__nv_bfloat16>((size_t)2 * B * L * E);
+  __nv_bfloat16* dzT = wa.take<__nv_bfloat16>((size_t)2 * E * B * Lp);
+  float* partial = wa.take<float>(BULK_PARTIAL_FLOATS);
+  if (!wa.base) return T2_OK;
+  T2_REQUIRE(!wa.overflow, T2_ERR_WORKSPACE, "t2_encoder_bwd: workspace too small");
+
+  // ---- packed BiLSTM (model/encoder.py:59-65)
+  RC(bilstm_bwd_launch(tp.lstm_sav, c->lstm_Whh, lens, d_encoded, dgates, B, L, Hh, st));
+  RC(colsum_launch(dgates, (long long)B * L, G8, G8, btmp, scratch, st));
+  RC(transpose_split_launch(dgates, G8, (long long)L * G8, dgT, L, G8, Lp, (long long)B * Lp, Lp, B, (long long)G8 * B * Lp, st));
+  RC(to_kmajor(tp.x[3], xT, B, L, Lp, E, st));
+  {  // W_ih of both directions in one GEMM: rows [dir*4Hh, +4Hh)
+    Opnd G{dgT, L, Lp, B, G8, (long long)G8 * B * Lp}, X{xT, L, Lp, B, E, (long long)E * B * Lp};
+    RC(bulk_gemm(c, G, X, G8, E, 0, GemmNtOut{wtmp, E, 1, 0, 1.f, 0}, partial, st));
+  }
+  for (int dir = 0; dir < 2; ++dir) {
+    const std::string sfx = dir ? "_reverse" : "";
+    NEED_GRAD(g_ih, "encoder.lstm.weight_ih_l0" + sfx, (size_t)4 * Hh * E);
+    NEED_GRAD(g_hh, "encoder.lstm.weight_hh_l0" + sfx, (size_t)4 * Hh * Hh);
+    NEED_GRAD(g_bi, "encoder.lstm.bias_ih_l0" + sfx, 4 * Hh);
+    NEED_GRAD(g_bh, "encoder.lstm.bias_hh_l0" + sfx, 4 * Hh);
+    T2_CHECK_CUDA(cudaMemcpyAsync(g_ih, wtmp + (size_t)dir * 4 * Hh * E, (size_t)4 * Hh * E * 4, cudaMemcpyDeviceToDevice, st));
+    RC(copy2_launch(btmp + dir * 4 * Hh, g_bi, g_bh, 4 * Hh, st));
+    // recurrent weights: h_{prev}[b][t] = out[b][t-1] (forward) / out[b][t+1] (reverse), zero at the sequence ends
+    __nv_bfloat16* hTd = hT + (size_t)dir * 2 * Hh * B * Lp;
+    RC(transpose_split_launch(encoded + dir * Hh, 2 * Hh, (long long)L * 2 * Hh, hTd, L, Hh, Lp, (long long)B * Lp, Lp, B,
+                              (long long)Hh * B * Lp, st, dir ? 1 : -1));
+    Opnd G{dgT + (size_t)dir * 4 * Hh * B * Lp, L, Lp, B, 4 * Hh, (long long)G8 * B * Lp}, Hp{hTd, L, Lp, B, Hh, (long long)Hh * B * Lp};
+    RC(bulk_gemm(c, G, Hp, 4 * Hh, Hh, 0, GemmNtOut{g_hh, Hh, 1, 0, 1.f, 0}, partial, st));
+  }
+  // d (conv stack output) = dgates W_ih  (k = 1 "convolution" with the transposed pack)
+  RC(split_cl_launch(dgates, (long long)L * G8, dgb, B, L, G8, st));
+  RC(conv_tc_res(c, dgb, c->lstm_wtmap, B, L, G8, E, 1, 128, nullptr, 0, dyA, st));
+
+  // ---- 3 x [Conv1d k5 + BatchNorm + ReLU + Dropout] (model/encoder.py:31-46)
+  const float* dy = dyA;
+  float* bufs[2] = {dyB, dyA};
+  for (int i = 2; i >= 0; --i) {
+    const std::string cv = "encoder.convolutions." + std::to_string(4 * i), bn = "encoder.convolutions." + std::to_string(4 * i + 1);
+    NEED_PARAM(bw, bn + ".weight", E);
+    NEED_PARAM(bb, bn + ".bias", E);
+    NEED_GRAD(gW, cv + ".weight", (size_t)E * E * KS);
+    NEED_GRAD(gB, cv + ".bias", E);
+    NEED_GRAD(gg, bn + ".weight", E);
+    NEED_GRAD(gb, bn + ".bias", E);
+    BnLayer Ly = enc_layer(c, tp, i, B, L, keep, seed, bw->ptr, bb->ptr);
+    RC(bn_bwd_launch(Ly, dy, (long long)B * L, gg, gb, dz, dzf, scratch, st));
+    RC(colsum_launch(dzf, (long long)B * L, E, E, gB, scratch, st));   // conv bias (mathematically 0 through BatchNorm; kept as computed)
+    RC(to_kmajor(dz, dzT, B, L, Lp, E, st));
+    RC(conv_wgrad(c, dzT, tp.x[i], xT, B, L, Lp, E, E, KS, gW, partial, BULK_PARTIAL_FLOATS, st));
+    float* dst = bufs[i & 1];
+    RC(conv_tc_res(c, dz, c->enc_wtmap[i], B, L, E, E, KS, 128, nullptr, 0, dst, st));
+    dy = dst;
+  }
+  NEED_GRAD(gE, "encoder.embedding.weight", (size_t)(c->cfg.num_chars + 1) * E);
+  RC(embedding_grad_launch(dy, chars, (long long)B * L, E, c->cfg.num_chars + 1, gE, st));
+  return T2_OK;
+}
+
+}  // namespace
+
+extern "C" long long t2_encoder_tape_bytes(const t2_ctx* c, int B, int L) {
+  if (!c || B <= 0 || L <= 0) return -1;
+  Arena ar(nullptr, 0);
+  plan_enc_tape(c, B, L, ar);
+  return ar.off + 1024;
+}
+
+// Encoder.forward under train() (model/encoder.py:54-67): BatchNorm batch statistics over all (b, l) incl. padding,
+// running statistics updated in place, dropout after each conv block.  keep (3,B,L,E) or NULL.
+extern "C" int t2_encoder_train_fwd(t2_ctx* c, const long long* chars_idx, const long long* lens, int B, int L, const unsigned char* keep,
+                                    unsigned long long seed, float* encoded, void* tape, long long tape_bytes, void* ws, long long ws_bytes,
+                                    void* stream) {
+  CHECK_CTX("t2_encoder_train_fwd");
+  T2_REQUIRE(chars_idx && lens && encoded && tape && ws && B > 0 && L > 0, T2_ERR_ARG, "t2_encoder_train_fwd: bad argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int E = c->E, Hh = E / 2;
+  Arena ta(tape, tape_bytes);
+  EncTape tp = plan_enc_tape(c, B, L, ta);
+  T2_REQUIRE(!ta.overflow, T2_ERR_WORKSPACE, "t2_encoder_train_fwd: tape too small");
+  Arena wa(ws, ws_bytes);
+  void* scratch = wa.take<char>(bn_scratch_bytes(E));
+  float* xproj = wa.take<float>((size_t)B * L * 8 * Hh);
+  T2_REQUIRE(!wa.overflow, T2_ERR_WORKSPACE, "t2_encoder_train_fwd: workspace too small");
+  NEED_PARAM(emb, "encoder.embedding.weight", (size_t)(c->cfg.num_chars + 1) * E);
+  RC(embed_split_launch(chars_idx, emb->ptr, tp.x[0], B * L, E, c->cfg.num_chars + 1, st));
+  for (int i = 0; i < 3; ++i) {
+    const std::string cv = "encoder.convolutions." + std::to_string(4 * i), bn = "encoder.convolutions." + std::to_string(4 * i + 1);
+    NEED_PARAM(cb, cv + ".bias", E);
+    NEED_PARAM(bw, bn + ".weight", E);
+    NEED_PARAM(bb, bn + ".bias", E);
+    NEED_PARAM(bm, bn + ".running_mean", E);
+    NEED_PARAM(bv, bn + ".running_var", E);
+    RC(conv_tc(c, tp.x[i], c->enc_wmap[i], B, L, E, E, c->KS, 128, ACT_NONE, nullptr, cb->ptr, nullptr, 0, tp.z[i], nullptr, st));
+    RC(bn_stats_launch(tp.z[i], (long long)B * L, E, tp.mean[i], tp.rstd[i], const_cast<float*>(bm->ptr), const_cast<float*>(bv->ptr), scratch, st));
+    BnLayer Ly = enc_layer(c, tp, i, B, L, keep, seed, bw->ptr, bb->ptr);
+    RC(bn_apply_launch(Ly, (long long)B * L, nullptr, tp.x[i + 1], st));
+  }
+  RC(conv_tc(c, tp.x[3], c->lstm_wmap, B, L, E, 8 * Hh, 1, 128, ACT_NONE, nullptr, c->lstm_bias, nullptr, 0, xproj, nullptr, st));
+  RC(bilstm_launch(xproj, c->lstm_Whh, lens, encoded, B, L, Hh, st, tp.lstm_sav));
+  return T2_OK;
+}
+
+// Backward of Encoder.forward: d_encoded (B,L,E) -> encoder.* parameter gradients.  `encoded` is the forward's output.
+extern "C" int t2_encoder_bwd(t2_ctx* c, const long long* chars_idx, const long long* lens, int B, int L, const unsigned char* keep,
+                              unsigned long long seed, const float* encoded, const float* d_encoded, const void* tape, long long tape_bytes,
+                              void* ws, long long ws_bytes, void* stream) {
+  CHECK_CTX("t2_encoder_bwd");
+  T2_REQUIRE(chars_idx && lens && encoded && d_encoded && tape && ws && B > 0 && L > 0, T2_ERR_ARG, "t2_encoder_bwd: bad argument");
+  Arena ta(const_cast<void*>(tape), tape_bytes);
+  EncTape tp = plan_enc_tape(c, B, L, ta);
+  T2_REQUIRE(!ta.overflow, T2_ERR_WORKSPACE, "t2_encoder_bwd: tape too small");
+  Arena wa(ws, ws_bytes);
+  return encoder_bwd_impl(c, chars_idx, lens, B, L, keep, seed, encoded, d_encoded, tp, wa, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------ conditioning + att_encoder backward
+static int memory_bwd_impl(t2_ctx* c, const float* memory, const long long* spk, const float* desc, const float* d_memory, const float* d_pmem,
+                           int B, int L, float* d_encoded, Arena& wa, cudaStream_t st) {
+  const int E = c->E, EF = c->EF, A = c->A, D = EF - E, Lp = round8(L);
+  __nv_bfloat16* dpb = wa.take<__nv_bfloat16>((size_t)2 * B * L * A);
+  __nv_bfloat16* dpT = wa.take<__nv_bfloat16>((size_t)2 * A * B * Lp);
+  __nv_bfloat16* memT = wa.take<__nv_bfloat16>((size_t)2 * EF * B * Lp);
+  float* dmem = wa.take<float>((size_t)B * L * EF);
+  float* dpre = wa.take<float>((size_t)B * 128);
+  float* partial = wa.take<float>(BULK_PARTIAL_FLOATS);
+  if (!wa.base) return T2_OK;
+  T2_REQUIRE(!wa.overflow, T2_ERR_WORKSPACE, "t2_memory_bwd: workspace too small");
+  NEED_GRAD(g_ae, "att_encoder.weight", (size_t)A * EF);
+  // d memory (total) = d_memory + d_pmem W_ae ; d W_ae[a][c] = sum_{b,l} d_pmem[b,l][a] memory[b,l][c]   (model/tacotron2.py:229)
+  RC(split_cl_launch(d_pmem, (long long)L * A, dpb, B, L, A, st));
+  RC(conv_tc_res(c, dpb, c->attenc_wtmap, B, L, A, EF, 1, 128, d_memory, (long long)L * EF, dmem, st));
+  RC(to_kmajor(dpb, dpT, B, L, Lp, A, st));
+  RC(transpose_split_launch(memory, EF, (long long)L * EF, memT, L, EF, Lp, (long long)B * Lp, Lp, B, (long long)EF * B * Lp, st));
+  {
+    Opnd Pm{dpT, L, Lp, B, A, (long long)A * B * Lp}, Mm{memT, L, Lp, B, EF, (long long)EF * B * Lp};
+    RC(bulk_gemm(c, Pm, Mm, A, EF, 0, GemmNtOut{g_ae, EF, 1, 0, 1.f, 0}, partial, st));
+  }
+  // conditioning (model/tacotron2.py:201-212)
+  const bool speaker = c->cfg.num_speakers > 0;
+  RC(condition_bwd_launch(dmem, memory, speaker ? 1 : 0, d_encoded, (long long)B * L, E, EF, st));
+  if (speaker) {
+    T2_REQUIRE(spk, T2_ERR_ARG, "speaker_id tensor required when speaker tokens are active!");
+    NEED_GRAD(g_spk, "speaker_embedding.weight", (size_t)c->cfg.num_speakers * E);
+    RC(speaker_grad_launch(d_encoded, spk, B, L, E, c->cfg.num_speakers, g_spk, st));
+  }
+  if (D > 0) {
+    T2_REQUIRE(desc, T2_ERR_ARG, "description tensor required when description tokens are active!");
+    NEED_GRAD(g_dw, "description_embeddings_linear.0.weight", (size_t)D * c->cfg.description_dim);
+    NEED_GRAD(g_db, "description_embeddings_linear.0.bias", D);
+    RC(desc_bwd_launch(dmem, memory, desc, B, L, E, D, c->cfg.description_dim, dpre, g_dw, g_db, st));
+  }
+  return T2_OK;
+}
+
+// Backward of t2_memory_fwd: d_memory (B,L,EF), d_processed_memory (B,L,A) -> d_encoded (B,L,E); writes att_encoder.weight,
+// speaker_embedding.weight and description_embeddings_linear.0.* gradients.  `memory` is the forward's output.
+extern "C" int t2_memory_bwd(t2_ctx* c, const float* memory, const long long* speaker_id, const float* description, const float* d_memory,
+                             const float* d_processed_memory, int B, int L, float* d_encoded, void* ws, long long ws_bytes, void* stream) {
+  CHECK_CTX("t2_memory_bwd");
+  T2_REQUIRE(memory && d_memory && d_processed_memory && d_encoded && ws && B > 0 && L > 0, T2_ERR_ARG, "t2_memory_bwd: bad argument");
+  Arena wa(ws, ws_bytes);
+  return memory_bwd_impl(c, memory, speaker_id, description, d_memory, d_processed_memory, B, L, d_encoded, wa, (cudaStream_t)stream);
+}
+
 extern "C" long long t2_train_workspace_bytes(const t2_ctx* cc, int B, int L, int T) {
   t2_ctx* c = const_cast<t2_ctx*>(cc);
   if (!c || B <= 0 || L <= 0 || T <= 0) return -1;
   long long best = t2_workspace_bytes(cc, B, L, T);
   best = std::max(best, postnet_bwd_ws_bytes(c, B, T) + bn_scratch_bytes(c->PD));
   best = std::max(best, decode_bwd_ws_bytes(c, B, L, T));
+  { Arena wa(nullptr, 0); EncTape tp{}; encoder_bwd_impl(c, nullptr, nullptr, B, L, nullptr, 0, nullptr, nullptr, tp, wa, nullptr); best = std::max<long long>(best, wa.off); }
+  { Arena wa(nullptr, 0); memory_bwd_impl(c, nullptr, nullptr, nullptr, nullptr, nullptr, B, L, nullptr, wa, nullptr); best = std::max<long long>(best, wa.off); }
+  best = std::max<long long>(best, bn_scratch_bytes(c->E) + (long long)B * L * 8 * (c->E / 2) * 4 + 4096);
   return best + 4096;
 }
+
 

