@@ -35,10 +35,10 @@ def _bucket(owner, lib, params: dict):
     return flat, views
 
 
-def _after_bucket(owner, flat):
+def _after_bucket(owner, flat, group, views):
     hook = getattr(owner, "_grad_bucket_hook", None)
-    if hook is not None:
-        hook(flat)  # data-parallel: async all-reduce of this bucket (parallel.py)
+    if hook is not None:  # data-parallel: async all-reduce of this bucket (parallel.py)
+        hook(flat, list(owner._group_params(group).values()), views)
 
 
 class PostnetFn(torch.autograd.Function):
@@ -68,7 +68,7 @@ class PostnetFn(torch.autograd.Function):
         d_mels = torch.empty(B, T, M, device=d_out.device)
         _lib.check(lib.t2_postnet_bwd(owner._ctx, B, T, P(ctx.keep), ctx.seed, P(d_out.contiguous()), None, P(ctx.tape), ctx.tape.numel(),
                                       P(d_mels), P(ws), ws.numel(), _stream()), "t2_postnet_bwd")
-        _after_bucket(owner, flat)
+        _after_bucket(owner, flat, "postnet", views)
         return (None, None, None, d_mels, *views)
 
 
@@ -98,7 +98,7 @@ class EncoderFn(torch.autograd.Function):
         ws = owner._train_workspace(lib, chars.device, B, L, 1)
         _lib.check(lib.t2_encoder_bwd(owner._ctx, P(chars), P(lens), B, L, P(keep), seed, P(ctx.out), P(d_out.contiguous()), P(ctx.tape),
                                       ctx.tape.numel(), P(ws), ws.numel(), _stream()), "t2_encoder_bwd")
-        _after_bucket(owner, flat)
+        _after_bucket(owner, flat, "encoder", views)
         return (None,) * 5 + tuple(views)
 
 
@@ -128,7 +128,7 @@ class MemoryFn(torch.autograd.Function):
         desc_c = None if desc is None else desc.to(device=dev, dtype=torch.float32).contiguous()
         _lib.check(lib.t2_memory_bwd(owner._ctx, P(memory), P(spk_c), P(desc_c), P(d_memory), P(d_pmem), B, L, P(d_enc), P(ws), ws.numel(),
                                      _stream()), "t2_memory_bwd")
-        _after_bucket(owner, flat)
+        _after_bucket(owner, flat, "memory", views)
         return (None, None, None, d_enc, *views)
 
 
@@ -168,7 +168,7 @@ class DecodeTfFn(torch.autograd.Function):
         _lib.check(lib.t2_decode_tf_bwd(owner._ctx, P(memory), P(pmem), P(mask), P(target), B, L, T, P(ak), P(rk), ctx.seed, P(aligns),
                                         P(d_mels), P(d_gates), P(ctx.tape), ctx.tape.numel(), P(d_memory), P(d_pmem), P(ws), ws.numel(),
                                         _stream()), "t2_decode_tf_bwd")
-        _after_bucket(owner, flat)
+        _after_bucket(owner, flat, "decoder", views)
         return (None,) * 8 + (d_memory, d_pmem, *views)
 
 
