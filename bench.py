@@ -90,6 +90,109 @@ def oracle_sample(frames, threads):
     return B * frames / dt, dt
 
 
+TRAIN_B, TRAIN_L, TRAIN_T = 64, 150, 800
+TRAIN_WORKLOAD = ("C3: vanilla-lj-hifi-stop (speaker tokens, 4 speakers) teacher-forced training step, batch 64/GPU x 150 chars x 800 frames, "
+                  "fp32-parity arithmetic: forward + loss + backward (BPTT) + gradient all-reduce (N>1) + grad-clip 1.0 + Adam(1e-3, wd 1e-6)")
+
+
+def train_bench(dev, rank, world, steps, warmup=2):
+    """BASELINE.json metric, training half: mel frames/s of the whole training step (model/tts_model.py:165-202 +
+    run/train.py:239-240 settings) on synthetic C3 batches; weak scaling (64 utterances per GPU), gradients averaged over NCCL."""
+    import torch.distributed as dist
+    from tacotron2_b200.model import Tacotron2
+    from tacotron2_b200.parallel import GradSync
+
+    a = synth.HIFI
+    model = Tacotron2(**a.kwargs()).to(dev).train()
+    model.load_state_dict(synth.synth_state_dict(a, seed=0))
+    sync = GradSync(model) if world > 1 else None
+    batch = synth.synth_batch(a, TRAIN_B, TRAIN_L, TRAIN_T, seed=1234 + rank, ragged=False)
+    host = {k: v.pin_memory() for k, v in batch.items()}
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3, weight_decay=1e-6, fused=True)
+    params = [p for p in model.parameters()]
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+    phase = [0.0, 0.0, 0.0, 0.0]
+    loss_h = torch.empty((), pin_memory=True)
+
+    def step(timed):
+        b = {k: v.to(dev, non_blocking=True) for k, v in host.items()}  # host -> device copy of the step's inputs (e2e)
+        opt.zero_grad(set_to_none=True)
+        ev[0].record()
+        mels, post, gates, _ = model(b["chars_idx"], b["chars_idx_len"], True, b["mel_spectrogram"], b["mel_spectrogram_len"],
+                                     speaker_id=b["speaker_id"])
+        loss = model.loss(mels, post, gates, b["mel_spectrogram"], b["gate"])
+        ev[1].record()
+        loss.backward()
+        ev[2].record()
+        if sync is not None:
+            sync.finish()
+        ev[3].record()
+        torch.nn.utils.clip_grad_norm_(params, 1.0, foreach=True)
+        opt.step()
+        ev[4].record()
+        loss_h.copy_(loss.detach(), non_blocking=True)  # device -> host read of the step's result
+        torch.cuda.current_stream().synchronize()
+        if timed:
+            for i in range(4):
+                phase[i] += ev[i].elapsed_time(ev[i + 1])
+        return float(loss_h)
+
+    for _ in range(warmup):
+        step(False)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    losses = [step(True) for _ in range(steps)]
+    t1.record()
+    t1.synchronize()
+    total = t0.elapsed_time(t1)
+    if world > 1:
+        tt = torch.tensor([total], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        total = float(tt[0])
+    out = {"metric": "mel_frames_per_sec_train_step", "unit": "frames/s", "value": world * TRAIN_B * TRAIN_T * steps / (total * 1e-3),
+           "ms_per_step": total / steps, "steps": steps, "config": {"workload": TRAIN_WORKLOAD, "utterances_per_gpu": TRAIN_B,
+                                                                    "parallelism": f"dp{world}" + (", NCCL bucketed all-reduce overlapped with backward" if world > 1 else "")},
+           "phase_ms": {"forward_loss": phase[0] / steps, "backward": phase[1] / steps, "allreduce_exposed": phase[2] / steps,
+                        "clip_adam": phase[3] / steps},
+           "h2d_bytes_per_step": sum(v.numel() * v.element_size() for v in host.values()), "d2h_bytes_per_step": 4,
+           "loss_first_last": [losses[0], losses[-1]], "grad_bytes_allreduced_per_step": 4 * sum(p.numel() for p in params) if world > 1 else 0}
+    try:
+        import ctypes
+        from tacotron2_b200 import _lib
+        cyc = (ctypes.c_ulonglong * 16)()
+        _lib.check(_lib.load().t2_debug_phase_cycles(model._ctx, cyc))
+        out["decoder_bwd_phase_cycles_per_frame"] = {"input_grad_gemms": cyc[8] / TRAIN_T, "attention_bwd": cyc[9] / TRAIN_T,
+                                                     "lstm_pointwise": cyc[10] / TRAIN_T}
+    except Exception as e:  # noqa: BLE001
+        out["decoder_bwd_phase_cycles_per_frame"] = str(e)
+    if sync is not None:
+        sync.detach()
+    del model, opt
+    torch.cuda.empty_cache()
+    return out
+
+
+def oracle_train_sample(threads, B=8, L=150, T=24):
+    """CPU baseline of the training half: the oracle's teacher-forced forward + loss + backward (torch CPU autograd), bounded sample."""
+    from oracle import tacotron2_oracle as O
+
+    torch.set_num_threads(threads)
+    a = synth.VANILLA
+    sd = synth.synth_state_dict(a, seed=0)
+    sd = {k: (v.clone().requires_grad_(True) if v.is_floating_point() and "running_" not in k else v) for k, v in sd.items()}
+    b = synth.synth_batch(a, B, L, T, seed=1234, ragged=False)
+    masks = synth.synth_masks(a, B, L, T, seed=7, train=True)
+    t0 = time.perf_counter()
+    mels, post, gates, _ = O.tacotron2_forward(sd, a, b["chars_idx"], b["chars_idx_len"], True, b["mel_spectrogram"], b["mel_spectrogram_len"],
+                                               masks=masks, train=True)
+    O.loss_fn(mels, post, gates, b["mel_spectrogram"], b["gate"]).backward()
+    dt = time.perf_counter() - t0
+    return B * T / dt, dt, f"vanilla B={B} L={L} T={T} teacher-forced fwd + loss + bwd, torch CPU fp32 autograd over the oracle, {dt:.1f} s"
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -120,6 +223,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-train", action="store_true", help="skip the training-step measurement (extra `train` object of the JSON line)")
+    ap.add_argument("--train-only", action="store_true", help="print only the training-step measurement (profiling aid)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -140,6 +245,14 @@ def main():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    if args.train_only:
+        out = train_bench(dev, rank, world, max(args.steps, 1))
+        if rank == 0:
+            print(json.dumps(out))
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     a = synth.VANILLA
     model = Tacotron2(**a.kwargs()).to(dev).eval()
@@ -196,6 +309,14 @@ def main():
         tt = torch.tensor([t_res, t_e2e, t_dec], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         t_res, t_e2e, t_dec = (float(x) for x in tt)
+    train = None
+    if not args.no_train:
+        del flush
+        torch.cuda.empty_cache()
+        try:
+            train = train_bench(dev, rank, world, max(2, min(args.steps, 5)))
+        except Exception as e:  # noqa: BLE001  (the AR line must still be printed)
+            train = {"error": f"{type(e).__name__}: {e}"}
     if rank != 0:
         dist.destroy_process_group()
         return
@@ -234,8 +355,14 @@ def main():
         line["config"]["phase_us_per_frame"] = {n: round(cyc[i] / mhz / T, 2) for i, n in enumerate(names)}
     except Exception as e:  # noqa: BLE001
         line["config"]["phase_us_per_frame"] = str(e)
+    if train is not None:
+        line["train"] = train
     if not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
+        if train is not None and "error" not in train:
+            oracle_train_sample(threads, T=4)  # warm-up
+            v, dt, sample = oracle_train_sample(threads)
+            train["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample}
         oracle_sample(4, threads)  # warm-up
         v, dt = oracle_sample(150, threads)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
