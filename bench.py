@@ -164,10 +164,11 @@ def train_bench(dev, rank, world, steps, warmup=2):
         from tacotron2_b200 import _lib
         cyc = (ctypes.c_ulonglong * 16)()
         _lib.check(_lib.load().t2_debug_phase_cycles(model._ctx, cyc))
-        out["decoder_bwd_phase_cycles_per_frame"] = {"input_grad_gemms": cyc[8] / TRAIN_T, "attention_bwd": cyc[9] / TRAIN_T,
-                                                     "lstm_pointwise": cyc[10] / TRAIN_T}
+        names = ["input_grad_gemms", "attention_bwd_tail", "lstm_pointwise", "att_stage_conv", "att_ctx_dot", "att_softmax_dense_ds",
+                 "att_df_dWd", "att_halo_dWc_dwcat"]
+        out["decoder_bwd_phase_us_per_frame"] = {n: round(cyc[8 + i] / 1965.0 / TRAIN_T, 2) for i, n in enumerate(names)}
     except Exception as e:  # noqa: BLE001
-        out["decoder_bwd_phase_cycles_per_frame"] = str(e)
+        out["decoder_bwd_phase_us_per_frame"] = str(e)
     if sync is not None:
         sync.detach()
     del model, opt

@@ -17,8 +17,10 @@ __device__ __forceinline__ size_t att_bwd_scratch_floats(int L, int S, int A, in
   return (size_t)A + 2 * Lh4 + (size_t)Lc * 36 + EF + 3 * Lc4 + 64 + 8 + 8 * (size_t)A + (size_t)Lc * (A + 4) + (size_t)(Lc + 30) * 36;
 }
 
+#define ABW_MARK(slot) do { if (blockIdx.x == 0 && threadIdx.x == 0 && prof) { const long long now_ = clock64(); prof[slot] += (unsigned long long)(now_ - *prof_last); *prof_last = now_; } } while (0)
 __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBWork& wk, const BSmem& sm, float* scratch, bool active,
-                                    int b, int part, int S, int t, int T, bool have_att_next, int KattT, int KdecT, AttAcc& acc) {
+                                    int b, int part, int S, int t, int T, bool have_att_next, int KattT, int KdecT, AttAcc& acc,
+                                    unsigned long long* prof, long long* prof_last) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int L = d.L, A = d.A, EF = d.EF;
   const int Lc = (L + S - 1) / S, l0 = min(L, part * Lc), l1 = min(L, l0 + Lc), nl = l1 - l0;
@@ -94,32 +96,51 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
       }
     }
 
-    // ---- g_w[l] = d ctx . memory[l] + d conv ch0 (from frame t+1) + g_cum;  g_cum += d conv ch1   (warp per position)
+    ABW_MARK(3);
+    // ---- g_w[l] = d ctx . memory[l] + d conv ch0 (from frame t+1) + g_cum;  g_cum += d conv ch1
+    // warp per position, two positions in flight per warp (8 independent 16-byte loads per lane); the per-position scalars
+    // (g_cum, d conv) are staged by all threads first so that no lane-0 load chain sits on the critical path
     {
       const float* mem = tp.memory + (size_t)b * L * EF;
-      float* dc0 = wk.dconv + ((size_t)0 * D2_BP + b) * L;
-      float* dc1 = wk.dconv + ((size_t)1 * D2_BP + b) * L;
       float* gc = wk.gcum + (size_t)b * L;
 #pragma unroll 1
-      for (int li = warp; li < nl; li += D2_THREADS / 32) {
-        const float4* mp = reinterpret_cast<const float4*>(mem + (size_t)(l0 + li) * EF);
-        float s = 0.f;
-        for (int c4 = lane; c4 < EF / 4; c4 += 32) {
-          const float4 m4 = __ldg(mp + c4);
-          const float4 d4 = *reinterpret_cast<const float4*>(dctx + c4 * 4);
-          s = fmaf(m4.x, d4.x, s); s = fmaf(m4.y, d4.y, s); s = fmaf(m4.z, d4.z, s); s = fmaf(m4.w, d4.w, s);
+      for (int i = tid; i < nl; i += D2_THREADS) {
+        const int l = l0 + i;
+        float g = gc[l], s0 = 0.f;
+        if (t + 1 < T) { g += wk.dconv[((size_t)1 * D2_BP + b) * L + l]; s0 = wk.dconv[((size_t)0 * D2_BP + b) * L + l]; }
+        gc[l] = g;             // d/d cum_t (cum_t feeds cum_{t+1} and conv channel 1 of frame t+1)
+        gw[i] = s0 + g;        // w_t also enters cum_t; the context term is added below
+      }
+      __syncthreads();
+      const int nq = EF / 4;
+#pragma unroll 1
+      for (int li = 2 * warp; li < nl; li += 2 * (D2_THREADS / 32)) {
+        const int li1 = min(li + 1, nl - 1);
+        const float4* mp0 = reinterpret_cast<const float4*>(mem + (size_t)(l0 + li) * EF);
+        const float4* mp1 = reinterpret_cast<const float4*>(mem + (size_t)(l0 + li1) * EF);
+        float s0 = 0.f, s1 = 0.f;
+#pragma unroll 1
+        for (int c4 = lane; c4 < nq; c4 += 128) {
+          float4 m0[4], m1[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int cc = min(c4 + 32 * u, nq - 1);
+            m0[u] = __ldg(mp0 + cc); m1[u] = __ldg(mp1 + cc);
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            if (c4 + 32 * u >= nq) continue;
+            const float4 d4 = *reinterpret_cast<const float4*>(dctx + (c4 + 32 * u) * 4);
+            s0 = fmaf(m0[u].x, d4.x, s0); s0 = fmaf(m0[u].y, d4.y, s0); s0 = fmaf(m0[u].z, d4.z, s0); s0 = fmaf(m0[u].w, d4.w, s0);
+            s1 = fmaf(m1[u].x, d4.x, s1); s1 = fmaf(m1[u].y, d4.y, s1); s1 = fmaf(m1[u].z, d4.z, s1); s1 = fmaf(m1[u].w, d4.w, s1);
+          }
         }
-        s = warp_sum(s);
-        if (lane == 0) {
-          const int l = l0 + li;
-          float g = gc[l];
-          if (t + 1 < T) { g += dc1[l]; s += dc0[l]; }   // contributions of frame t+1's location conv
-          gc[l] = g;                                      // d/d cum_t (cum_t feeds cum_{t+1} and conv channel 1 of t+1)
-          gw[li] = s + g;                                 // w_t also enters cum_t
-        }
+        s0 = warp_sum(s0); s1 = warp_sum(s1);
+        if (lane == 0) { gw[li] += s0; if (li + 1 < nl) gw[li + 1] += s1; }
       }
     }
     __syncthreads();
+    ABW_MARK(4);
     // ---- softmax backward: de = w * (g_w - sum_l w g_w); the dot needs all parts
     float pd = 0.f;
 #pragma unroll 1
@@ -212,6 +233,7 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
       wk.dq[(((size_t)t * S + part) * D2_BP + b) * A + a] = s;
     }
 
+    ABW_MARK(5);
     // ---- d f[l][f] = sum_a ds[l][a] Wd[a][f]   (warp = 16 positions; lane -> position quad lane>>3, filter quad lane&7)
     {
       const int fq = (lane & 7) * 4, lq = lane >> 3;
@@ -265,6 +287,7 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
       }
     }
   }
+  ABW_MARK(6);
   tc::cluster_sync();   // every part's d f slice is in its shared memory
   if (active) {
     // ---- halo rows of d f from the neighbouring parts (15 positions each side)
@@ -323,6 +346,7 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
       }
     }
   }
+  ABW_MARK(7);
   tc::cluster_sync();   // peers are done reading this CTA's d f rows before the scratch is reused
 }
 

@@ -12,7 +12,7 @@ struct DBParams {
 
 // one 128-row tile of an input-gradient GEMM: dx[k0 + r][b] = sum_p WT[k0 + r][p] dg[b][p]
 __device__ __forceinline__ bool dx_tile(tg::Pipe& pipe, const BSmem& sm, const CUtensorMap* wmap, const CUtensorMap* dgmap, int ktile,
-                                        int npb, uint32_t rank, float* dx /*[K][BP]*/, float* dpre_t /*[BP][P] or null*/, int P) {
+                                        int npb, uint32_t rank, float* dx /*[K][BP]*/) {
   tg::XSrc xs{dgmap, 0, dgmap, 0, npb};
   const bool ok = tg::gemm(pipe, wmap, ktile * TG_M, npb, xs, (int)rank, npb, D2_CLUSTER, 0u);
   tg::accum_to_smem(pipe, 0u, sm.part);
@@ -23,12 +23,7 @@ __device__ __forceinline__ bool dx_tile(tg::Pipe& pipe, const BSmem& sm, const C
     const int row = 32 * (int)rank + i / (TG_N / 2), col = 2 * (i % (TG_N / 2));
     const float2 s = tg::reduce4(sm.part, row, col);
     const int k = ktile * TG_M + row;
-    if (dpre_t && k < P) {   // prenet-output gradient goes straight to its per-frame history (row-major for the bulk prenet backward)
-      dpre_t[(size_t)col * P + k] = s.x;
-      dpre_t[(size_t)(col + 1) * P + k] = s.y;
-    } else {
-      *reinterpret_cast<float2*>(dx + (size_t)k * D2_BP + col) = s;
-    }
+    *reinterpret_cast<float2*>(dx + (size_t)k * D2_BP + col) = s;
   }
   tc::cluster_sync();   // peers are done reading this CTA's partial before it is overwritten
   return ok;
@@ -78,7 +73,10 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
   const int att_b = blockIdx.x / S, att_part = blockIdx.x % S;
   const bool att_active = att_b < B;
   const int npb = 4 * H / TG_BK;
-  const int ntile_dec = p.KdecT / TG_M, ntile_att = p.KattT / TG_M;
+  // the prenet block of the attention-cell input (first P rows of dx_att) is off the recurrent chain: its gradient is one
+  // bulk GEMM after the loop, so the in-loop GEMM skips those tiles (vanilla: 20 + 12 = 32 tiles = one per cluster)
+  const int att_tile0 = d.P / TG_M;
+  const int ntile_dec = p.KdecT / TG_M, ntile_att = p.KattT / TG_M - att_tile0;
   const int nclusters = gridDim.x / D2_CLUSTER;
   AttAcc acc;
 #pragma unroll
@@ -105,13 +103,40 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
     lstm_pointwise_bwd(a, H, B, unit0, pbase, sm.dc_dec, stg, nullptr, bias_dec);
   };
   auto pw_att = [&](int t, bool have_next) {   // attention LSTMCell of frame t (its h also feeds the query and the decoder cell)
-    // d query summed over the attention parts, transposed to [a][b]
+    // d query summed over the attention parts, transposed to [a][b].  All loads of a chunk are issued before any use
+    // (a one-load-per-iteration loop pays the full L2 latency 32 times and dominated this phase).
+    {
+      const int n4 = d.A * B / 4;                  // float4 elements of the (B, A) block; rows b >= B are never read
+      const size_t pstride = (size_t)D2_BP * d.A;  // floats between parts
+      const float* src = wk.dq + (size_t)t * S * pstride;
 #pragma unroll 1
-    for (int i = tid; i < d.A * D2_BP; i += D2_THREADS) {
-      const int a_ = i % d.A, b = i / d.A;
-      float s = 0.f;
-      for (int pr = 0; pr < S; ++pr) s += ld_cg(wk.dq + (((size_t)t * S + pr) * D2_BP + b) * d.A + a_);
-      dq_s[a_ * D2_BP + b] = b < B ? s : 0.f;
+      for (int i0 = 0; i0 < n4; i0 += 4 * D2_THREADS) {
+        float4 v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int i = i0 + k * D2_THREADS + tid;
+          v[k] = i < n4 ? ld_cg4(src + (size_t)i * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        for (int pr = 1; pr < S; ++pr) {
+          float4 w4[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int i = i0 + k * D2_THREADS + tid;
+            w4[k] = i < n4 ? ld_cg4(src + pr * pstride + (size_t)i * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+#pragma unroll
+          for (int k = 0; k < 4; ++k) { v[k].x += w4[k].x; v[k].y += w4[k].y; v[k].z += w4[k].z; v[k].w += w4[k].w; }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int i = i0 + k * D2_THREADS + tid;
+          if (i < n4) {
+            const int b = (i * 4) / d.A, a_ = (i * 4) - b * d.A;
+            dq_s[(a_ + 0) * D2_BP + b] = v[k].x; dq_s[(a_ + 1) * D2_BP + b] = v[k].y;
+            dq_s[(a_ + 2) * D2_BP + b] = v[k].z; dq_s[(a_ + 3) * D2_BP + b] = v[k].w;
+          }
+        }
+      }
     }
 #pragma unroll 1
     for (int i = tid; i < d.A * 8; i += D2_THREADS) wq_s[i] = __ldg(p.w.Wq + (size_t)(i >> 3) * H + unit0 + (i & 7));
@@ -125,6 +150,8 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
         const float2 q2 = *reinterpret_cast<const float2*>(dq_s + a_ * D2_BP + 2 * bp);
         ex[0] = fmaf(wv, q2.x, ex[0]); ex[1] = fmaf(wv, q2.y, ex[1]);
       }
+      if (2 * bp >= B) ex[0] = 0.f;        // utterance slots >= B hold stale scratch
+      if (2 * bp + 1 >= B) ex[1] = 0.f;
     }
     PwArgs a{};
     a.sav = tp.sav_att + (size_t)t * 5 * H * D2_BP;
@@ -143,7 +170,7 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
   prof_mark(2);
 
 #pragma unroll 1
-  for (int t = T - 1; t >= -1 && alive; --t) {
+  for (int t = T - 1; t >= 0 && alive; --t) {
     // ---- G: dx_dec(t) and dx_att(t+1)
     const bool have_att_next = t + 1 <= T - 1;
     {
@@ -151,17 +178,15 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
 #pragma unroll 1
       for (int tile = cl; tile < n_dec + n_att; tile += nclusters) {
         bool ok;
-        if (tile < n_dec) ok = dx_tile(pipe, sm, &maps.wt_dec, &maps.dg_dec, tile, npb, rank, wk.dx_dec, nullptr, 0);
-        else ok = dx_tile(pipe, sm, &maps.wt_att, &maps.dg_att, tile - n_dec, npb, rank, wk.dx_att,
-                          wk.dpre + (size_t)(t + 1) * D2_BP * d.P, d.P);
+        if (tile < n_dec) ok = dx_tile(pipe, sm, &maps.wt_dec, &maps.dg_dec, tile, npb, rank, wk.dx_dec);
+        else ok = dx_tile(pipe, sm, &maps.wt_att, &maps.dg_att, tile - n_dec + att_tile0, npb, rank, wk.dx_att);
         if (!ok) fail = true;
       }
     }
     if (!(alive = bar.sync(fail, false))) break;
     prof_mark(0);
-    if (t < 0) break;   // epilogue iteration: only dx_att(0) (prenet gradient of frame 0) was needed
     // ---- A: attention backward of frame t
-    attention_bwd_phase(d, tp, wk, sm, scratch, att_active, att_b, att_part, S, t, T, have_att_next, p.KattT, p.KdecT, acc);
+    attention_bwd_phase(d, tp, wk, sm, scratch, att_active, att_b, att_part, S, t, T, have_att_next, p.KattT, p.KdecT, acc, p.prof, &prof_last);
     if (!(alive = bar.sync(fail, false))) break;
     prof_mark(1);
     // ---- P: attention cell of frame t, decoder cell of frame t-1

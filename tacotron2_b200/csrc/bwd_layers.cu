@@ -256,6 +256,7 @@ __global__ void __launch_bounds__(256, 1) bilstm_bwd_cluster_kernel(const float*
   float* Wc = bsm;                                  // [4Hh rows][UPC]  W_hh[row][rank*UPC + k]
   float* dgb = Wc + (size_t)G4 * UPC;               // [2][4Hh][BB_NB]
   float* dhr = dgb + (size_t)2 * G4 * BB_NB;        // [UPC][BB_NB] recurrent d h of the own units
+  float* red8 = dhr + UPC * BB_NB;                  // [8 warps][BB_NB][UPC] partial sums of the mat-vec
   __shared__ int len_s[BB_NB];
   uint32_t rank;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
@@ -321,18 +322,28 @@ __global__ void __launch_bounds__(256, 1) bilstm_bwd_cluster_kernel(const float*
     }
     asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
     // ---- d h_{prev}[own unit k][utterance] = sum_rows W_hh[row][k] * dg[row][utterance]
+    // thread = (own unit k = lane, row slice = warp): 8 utterances per thread so one weight load feeds 8 FMAs, then an
+    // 8-way cross-warp reduction through shared memory
     {
-      const float* dg = dgb + (size_t)cur * G4 * BB_NB + mu;
-      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+      const int rows_per = G4 / 8;
+      const float* dg = dgb + (size_t)cur * G4 * BB_NB;
+      float a8[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) a8[i] = 0.f;
 #pragma unroll 4
-      for (int r = 0; r < G4; r += 4) {
-        a0 = fmaf(Wc[(r + 0) * UPC + mk], dg[(r + 0) * BB_NB], a0);
-        a1 = fmaf(Wc[(r + 1) * UPC + mk], dg[(r + 1) * BB_NB], a1);
-        a2 = fmaf(Wc[(r + 2) * UPC + mk], dg[(r + 2) * BB_NB], a2);
-        a3 = fmaf(Wc[(r + 3) * UPC + mk], dg[(r + 3) * BB_NB], a3);
+      for (int r = mu * rows_per; r < (mu + 1) * rows_per; ++r) {
+        const float w = Wc[r * UPC + mk];
+        const float4 g0 = *reinterpret_cast<const float4*>(dg + r * BB_NB), g1 = *reinterpret_cast<const float4*>(dg + r * BB_NB + 4);
+        a8[0] = fmaf(w, g0.x, a8[0]); a8[1] = fmaf(w, g0.y, a8[1]); a8[2] = fmaf(w, g0.z, a8[2]); a8[3] = fmaf(w, g0.w, a8[3]);
+        a8[4] = fmaf(w, g1.x, a8[4]); a8[5] = fmaf(w, g1.y, a8[5]); a8[6] = fmaf(w, g1.z, a8[6]); a8[7] = fmaf(w, g1.w, a8[7]);
       }
-      __syncthreads();   // everyone has read dhr of this step
-      dhr[mk * BB_NB + mu] = (a0 + a1) + (a2 + a3);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) red8[(mu * BB_NB + i) * UPC + mk] = a8[i];
+      __syncthreads();   // partials complete; everyone has also read dhr of this step
+      float sacc = 0.f;
+#pragma unroll
+      for (int w8 = 0; w8 < 8; ++w8) sacc += red8[(w8 * BB_NB + mu) * UPC + mk];
+      dhr[mk * BB_NB + mu] = sacc;
     }
     __syncthreads();
   }
@@ -345,7 +356,7 @@ int bilstm_bwd_launch(const float* sav, const float* Whh, const long long* lens,
   const int UPC = Hh / BB_CL;
   T2_REQUIRE(Hh % BB_CL == 0 && UPC == 32, T2_ERR_UNSUPPORTED, "bilstm backward: hidden size %d unsupported (needs Hh == 256)", Hh);
   T2_CHECK_CUDA(cudaMemsetAsync(dgates, 0, (size_t)B * L * 8 * Hh * sizeof(float), st));
-  const size_t smem = ((size_t)4 * Hh * UPC + (size_t)2 * 4 * Hh * BB_NB + (size_t)UPC * BB_NB) * sizeof(float);
+  const size_t smem = ((size_t)4 * Hh * UPC + (size_t)2 * 4 * Hh * BB_NB + (size_t)UPC * BB_NB + (size_t)8 * BB_NB * UPC) * sizeof(float);
   T2_CHECK_CUDA(cudaFuncSetAttribute(bilstm_bwd_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((unsigned)(2 * ((B + BB_NB - 1) / BB_NB) * BB_CL));

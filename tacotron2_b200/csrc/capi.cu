@@ -345,6 +345,7 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   c->WTdec_b = ar.take<__nv_bfloat16>((size_t)2 * 4 * R * c->KdecT);
   c->WprojT_b = ar.take<__nv_bfloat16>((size_t)2 * d.KprojP * PROJ_LD);
   c->W2T_b = ar.take<__nv_bfloat16>((size_t)2 * P * P);
+  c->WpreT_b = ar.take<__nv_bfloat16>((size_t)2 * P * 4 * H);
   if (sizing) return T2_OK;
   T2_REQUIRE(!ar.overflow, T2_ERR_STATE, "t2_ctx_commit: slab overflow");
 
@@ -387,6 +388,7 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   pack_lstm_T_bf16_kernel<<<gsz(4ll * R * c->KdecT), 256, 0, st>>>(dec_ih->ptr, dec_hh->ptr, c->WTdec_b, R, H + EF + C, c->KdecT);
   pack_T_kernel<<<gsz((long long)d.KprojP * PROJ_LD), 256, 0, st>>>(Wproj, M + 1, d.KprojP, c->WprojT_b, d.KprojP, PROJ_LD);
   pack_T_kernel<<<gsz((long long)P * P), 256, 0, st>>>(w2->ptr, P, P, c->W2T_b, P, P);
+  pack_T_kernel<<<gsz((long long)P * 4 * H), 256, 0, st>>>(att_ih->ptr, 4 * H, P + EF, c->WpreT_b, P, 4 * H);
   T2_CHECK_CUDA(cudaGetLastError());
   {
     const unsigned zb = c->npass == 3 ? 2u : 1u;

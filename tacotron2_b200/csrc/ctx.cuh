@@ -47,6 +47,7 @@ struct t2_ctx {
   int KattT, KdecT;                        // K padded to 128
   __nv_bfloat16 *WprojT_b;                 // [2][KprojP][PROJ_LD]  (row k, contraction r = mel rows + gate row)
   __nv_bfloat16 *W2T_b;                    // [2][P][P]  prenet.3.weight transposed
+  __nv_bfloat16 *WpreT_b;                  // [2][P][4H] att_rnn.weight_ih[:, :P] transposed (bulk prenet-output gradient)
 };
 #define PROJ_LD 96
 

@@ -291,6 +291,7 @@ int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const uns
   __nv_bfloat16* p1T = wa.take<__nv_bfloat16>((size_t)2 * P * Np);
   __nv_bfloat16* xT = wa.take<__nv_bfloat16>((size_t)2 * M * Np);
   float* wtmp = wa.take<float>((size_t)(M + 1) * d.KprojP);
+  __nv_bfloat16* dgH = wa.take<__nv_bfloat16>((size_t)2 * TB * 4 * H);
   float* partial = wa.take<float>(BULK_PARTIAL_FLOATS);
   if (!wa.base) return T2_OK;
   T2_REQUIRE(!wa.overflow, T2_ERR_WORKSPACE, "t2_decode_tf_bwd: workspace too small");
@@ -393,6 +394,11 @@ int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const uns
     RC(transpose_split_launch(dctx_tot, (long long)D2_BP * EF, EF, dcT, T, EF, Tp, Tp, (long long)EF * Tp, B, (long long)B * EF * Tp, st));
     Opnd Aw{alT, T, Tp, 1, B * L, (long long)B * L * Tp}, Dc{dcT, T, Tp, 1, B * EF, (long long)B * EF * Tp};
     RC(bulk_gemm(c, Aw, Dc, L, EF, 0, GemmNtOut{d_memory, EF, 1, (long long)L * EF, 1.f, 0}, partial, st, B, L, EF));
+  }
+  {  // d prenet output [t][b][k] = sum_r dgates_att[t,b][r] W_ih[r][k], k < P: off the recurrent chain, one bulk GEMM
+    RC(transpose_bf16_launch(dgT_att, TB, 0, 4ll * H * TB, dgH, 4 * H, (int)TB, 4 * H, 4 * H, 0, 1, 0, TB * 4 * H, st));
+    Opnd Gh{dgH, 4 * H, 4 * H, 1, (int)TB, TB * 4 * H}, Wp{c->WpreT_b, 4 * H, 4 * H, 1, P, (long long)P * 4 * H};
+    RC(bulk_gemm(c, Gh, Wp, (int)TB, P, 0, GemmNtOut{dpre, P, 1, 0, 1.f, 0}, nullptr, st, 1, 0, 0, true));
   }
   {  // prenet backward (model/tacotron2.py:85-92), rows n = t*B + b, t < T (the T+1-th prenet frame is never used, :317)
     const float scale = 1.0f / (1.0f - c->cfg.dropout);
