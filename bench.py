@@ -240,6 +240,8 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         import torch.distributed as dist
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"   # keep NCCL's version banner off stdout: rank 0 prints exactly one JSON line
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -374,4 +376,12 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    # Anything a library writes to fd 1 (NCCL's version banner, ...) goes to stderr; the JSON line alone reaches stdout.
+    sys.stdout.flush()
+    _out = os.dup(1)
+    os.dup2(2, 1)
+    _real, sys.stdout = sys.stdout, open(_out, "w", closefd=False)
+    try:
+        main()
+    finally:
+        sys.stdout.flush()
