@@ -354,7 +354,7 @@ def main():
         cyc = (ctypes.c_ulonglong * 16)()
         _lib.check(_lib.load().t2_debug_phase_cycles(model._ctx, cyc))
         mhz = clocks.get("sm_mhz") or 1965
-        names = ["att_lstm_tail", "query", "attention", "dec_lstm_tail", "proj", "prenet1", "prenet2", "extra_barrier", "att_lstm_gemm", "dec_lstm_gemm", "attn_conv", "attn_dense", "attn_csync", "attn_softmax", "attn_context"]
+        names = ["att_lstm_tail", "query_partials_barrier", "attention", "dec_lstm_tail", "proj", "prenet1", "prenet2", "extra_barrier", "att_lstm_gemm", "dec_lstm_gemm", "attn_conv", "attn_dense", "attn_csync", "attn_softmax", "attn_context"]
         line["config"]["phase_us_per_frame"] = {n: round(cyc[i] / mhz / T, 2) for i, n in enumerate(names)}
     except Exception as e:  # noqa: BLE001
         line["config"]["phase_us_per_frame"] = str(e)

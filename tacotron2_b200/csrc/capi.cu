@@ -189,6 +189,17 @@ __global__ void pack_T_kernel(const float* W, int rows_in, int ldw, __nv_bfloat1
     dst[n + i] = lo;
   }
 }
+// dst[2][rows][K]: dst[m][j] = W[m][src_off + j - lead] for 0 <= j - lead < src_n, else 0  (column window of an fp32 matrix -> bf16 hi/lo)
+__global__ void pack_cols_kernel(const float* W, int rows, int ldw, int src_off, int src_n, int lead, __nv_bfloat16* dst, int K) {
+  const long long n = (long long)rows * K;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int j = (int)(i % K) - lead, m = (int)(i / K);
+    __nv_bfloat16 hi, lo;
+    tc::split_bf16((j >= 0 && j < src_n) ? W[(size_t)m * ldw + src_off + j] : 0.f, hi, lo);
+    dst[i] = hi;
+    dst[n + i] = lo;
+  }
+}
 // conv weight [Cout][Cin][k] -> bf16 (hi,lo) [2][Cin][k][Cout] with the taps flipped (input-gradient conv)
 __global__ void pack_conv_wT_kernel(const float* W, __nv_bfloat16* dst, int Cout, int Cin, int k) {
   const long long n = (long long)Cout * Cin * k;
@@ -344,6 +355,11 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   c->WTatt_b = ar.take<__nv_bfloat16>((size_t)2 * 4 * H * c->KattT);
   c->WTdec_b = ar.take<__nv_bfloat16>((size_t)2 * 4 * R * c->KdecT);
   c->WprojT_b = ar.take<__nv_bfloat16>((size_t)2 * d.KprojP * PROJ_LD);
+  c->projA_col0 = (H + EF + C) & ~7;
+  c->KprojA = d.KdecP - c->projA_col0;
+  c->KprojB = (EF + C + 7) & ~7;
+  c->WprojA_b = ar.take<__nv_bfloat16>((size_t)2 * (M + 1) * c->KprojA);
+  c->WprojB_b = ar.take<__nv_bfloat16>((size_t)2 * (M + 1) * c->KprojB);
   c->W2T_b = ar.take<__nv_bfloat16>((size_t)2 * P * P);
   c->WpreT_b = ar.take<__nv_bfloat16>((size_t)2 * P * 4 * H);
   if (sizing) return T2_OK;
@@ -387,6 +403,9 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   pack_lstm_T_bf16_kernel<<<gsz(4ll * H * c->KattT), 256, 0, st>>>(att_ih->ptr, att_hh->ptr, c->WTatt_b, H, P + EF, c->KattT);
   pack_lstm_T_bf16_kernel<<<gsz(4ll * R * c->KdecT), 256, 0, st>>>(dec_ih->ptr, dec_hh->ptr, c->WTdec_b, R, H + EF + C, c->KdecT);
   pack_T_kernel<<<gsz((long long)d.KprojP * PROJ_LD), 256, 0, st>>>(Wproj, M + 1, d.KprojP, c->WprojT_b, d.KprojP, PROJ_LD);
+  pack_cols_kernel<<<gsz((long long)(M + 1) * c->KprojA), 256, 0, st>>>(Wproj, M + 1, d.KprojP, 0, R, H + EF + C - c->projA_col0, c->WprojA_b,
+                                                                       c->KprojA);
+  pack_cols_kernel<<<gsz((long long)(M + 1) * c->KprojB), 256, 0, st>>>(Wproj, M + 1, d.KprojP, R, EF + C, 0, c->WprojB_b, c->KprojB);
   pack_T_kernel<<<gsz((long long)P * P), 256, 0, st>>>(w2->ptr, P, P, c->W2T_b, P, P);
   pack_T_kernel<<<gsz((long long)P * 4 * H), 256, 0, st>>>(att_ih->ptr, 4 * H, P + EF, c->WpreT_b, P, 4 * H);
   T2_CHECK_CUDA(cudaGetLastError());
@@ -572,7 +591,7 @@ static State2Plan plan_state2(const D2Dims& d, int L, Arena& ar) {
   s.rnn_c = ar.take<float>((size_t)d.R * D2_BP);
   s.att_h_rm = ar.take<float>((size_t)D2_BP * d.H);
   s.projin = ar.take<float>((size_t)D2_BP * d.KprojP);
-  s.q = ar.take<float>((size_t)D2_BP * d.A);
+  s.q = nullptr;
   s.w_prev = ar.take<float>((size_t)2 * D2_BP * L);
   s.w_cum = ar.take<float>((size_t)2 * D2_BP * L);
   s.mel_cur = ar.take<float>((size_t)D2_BP * d.M);
@@ -583,8 +602,11 @@ static State2Plan plan_state2(const D2Dims& d, int L, Arena& ar) {
   s.barrier = ar.take<unsigned>(4);
   pl.zero_begin = ar.base ? ar.base + off0 : nullptr;
   pl.zero_bytes = (size_t)(ar.off - off0);
+  s.qpart = ar.take<float>((size_t)D2_BP * 128 * d.A);   // fully rewritten every frame: not part of the zeroed region
   return pl;
 }
+
+int decode_proj_bulk(t2_ctx* c, const __nv_bfloat16* xdec_tape, int B, int T, float* mels, float* gates, float* tmp, cudaStream_t st);  // train_capi.cu
 
 D2Dims dims2(const t2_ctx* c, int B, int L) {
   D2Dims d{};
@@ -641,6 +663,7 @@ static int decode2_impl(t2_ctx* c, bool tf, const float* memory, const float* pm
   D2Dims d = dims2(c, B, L);
   State2Plan pl = plan_state2(d, L, ar);
   __nv_bfloat16* tfp = (tf && !tape) ? ar.take<__nv_bfloat16>((size_t)(T + 1) * 2 * D2_BP * d.P) : nullptr;
+  float* proj_tmp = tape ? ar.take<float>((size_t)(d.M + 1) * T * D2_BP) : nullptr;
   if (!ar.base) return T2_OK;
   T2_REQUIRE(!ar.overflow, T2_ERR_WORKSPACE, "t2_decode: workspace too small");
   T2_CHECK_CUDA(cudaMemsetAsync(pl.zero_begin, 0, pl.zero_bytes, st));
@@ -675,7 +698,9 @@ static int decode2_impl(t2_ctx* c, bool tf, const float* memory, const float* pm
   }
   D2Maps maps;
   RC(make_xmaps(c, d, s, tfp, T + 1, &maps, nslots));
-  return d2_launch(d, c->d2w, s, io, maps, st);
+  RC(d2_launch(d, c->d2w, s, io, maps, st));
+  if (tape) RC(decode_proj_bulk(c, tape->xdec, B, T, mels, gates, proj_tmp, st));
+  return T2_OK;
 }
 
 static int step2_impl(t2_ctx* c, const float* prev, const float* att_h, const float* att_c, const float* ctx, const float* w,

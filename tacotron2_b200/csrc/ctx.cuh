@@ -46,6 +46,11 @@ struct t2_ctx {
   CUtensorMap map_wt_att, map_wt_dec;
   int KattT, KdecT;                        // K padded to 128
   __nv_bfloat16 *WprojT_b;                 // [2][KprojP][PROJ_LD]  (row k, contraction r = mel rows + gate row)
+  // bulk mel/gate projection of the teacher-forced training forward, laid out over the decoder-cell input rows of the tape:
+  // WprojA_b[2][M+1][KprojA] multiplies columns [projA_col0, KdecP) of slot t+1 (rnn_h_t), WprojB_b[2][M+1][KprojB] multiplies
+  // columns [H, H+KprojB) of slot t (ctx_t | controls); columns outside the segment carry zero weights.
+  __nv_bfloat16 *WprojA_b, *WprojB_b;
+  int KprojA, KprojB, projA_col0;
   __nv_bfloat16 *W2T_b;                    // [2][P][P]  prenet.3.weight transposed
   __nv_bfloat16 *WpreT_b;                  // [2][P][4H] att_rnn.weight_ih[:, :P] transposed (bulk prenet-output gradient)
 };

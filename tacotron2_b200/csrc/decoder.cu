@@ -101,6 +101,8 @@ __device__ __forceinline__ SmallOut small_gemm(const float* __restrict__ W, int 
 //   part[128][68] f32     split-K partial accumulator (read by cluster peers)
 //   c_att[8][64], c_dec[8][64] f32   cell states of this CTA's 8 hidden units
 //   attention constants   conv_t[2*31*32] | dense[A*32] | v[A]
+//   wq[8][A] f32          query-layer columns of this CTA's 8 attention-LSTM units (resident for the whole launch)
+//   h_s[8][64] f32        this frame's new hidden values, staged for packed 16-byte stores and the query partials
 //   barriers, tmem slot
 struct Smem {
   uint8_t* stages;
@@ -110,6 +112,8 @@ struct Smem {
   float* conv_t;
   float* dense;
   float* v;
+  float* wq;
+  float* h_s;
   uint64_t* bars;
   uint32_t* tmem_slot;
 };
@@ -124,6 +128,8 @@ __device__ __forceinline__ Smem carve(uint8_t* base, const D2Dims& d) {
   s.conv_t = reinterpret_cast<float*>(p); p += 2 * D2_LOC_K * D2_LOC_F * 4;
   s.dense = reinterpret_cast<float*>(p); p += d.A * D2_LOC_F * 4;
   s.v = reinterpret_cast<float*>(p);     p += d.A * 4;
+  s.wq = reinterpret_cast<float*>(p);    p += 8 * d.A * 4;
+  s.h_s = reinterpret_cast<float*>(p);   p += 8 * D2_BP * 4;
   s.bars = reinterpret_cast<uint64_t*>(p); p += (2 * D2_STAGES + 2) * 8;
   s.tmem_slot = reinterpret_cast<uint32_t*>(p);
   return s;
@@ -147,9 +153,32 @@ __device__ __forceinline__ void store_split(__nv_bfloat16* base, long long plane
   base[plane + (size_t)b * ld + col] = lo;
 }
 
+__device__ __forceinline__ uint32_t pack2_bf16(__nv_bfloat16 a, __nv_bfloat16 b) {
+  return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(b) << 16);
+}
+
+// One plane (hi or lo) of 8 consecutive hidden values -> one 16-byte store when the destination allows it.
+__device__ __forceinline__ void store_plane8(__nv_bfloat16* dst, const float* h8, int lo_plane, bool vec) {
+  __nv_bfloat16 o[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    __nv_bfloat16 hi, lo;
+    tc::split_bf16(h8[i], hi, lo);
+    o[i] = lo_plane ? lo : hi;
+  }
+  if (vec) {
+    *reinterpret_cast<uint4*>(dst) = make_uint4(pack2_bf16(o[0], o[1]), pack2_bf16(o[2], o[3]), pack2_bf16(o[4], o[5]), pack2_bf16(o[6], o[7]));
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) dst[i] = o[i];
+  }
+}
+
+// Pointwise part: thread (unit ul, utterance pair bp).  The new hidden values are staged in h_s[8][64] and leave the CTA as
+// one 16-byte store per (utterance, destination, plane) instead of 2-byte scattered stores.
 __device__ __forceinline__ void lstm_tail(const float* part, uint32_t rank, int unit0, const float* __restrict__ bias, int H,
                                           float* cst, int B, const HOut& ho, const unsigned char* keep, bool hidden_dropout,
-                                          unsigned long long seed, unsigned long long rng_base, float* sav) {
+                                          unsigned long long seed, unsigned long long rng_base, float* sav, float* h_s) {
   const int ul = threadIdx.x >> 5, bp = threadIdx.x & 31;
   const int u = unit0 + ul;
   float2 pre[4];
@@ -159,28 +188,79 @@ __device__ __forceinline__ void lstm_tail(const float* part, uint32_t rank, int 
     const float bv = __ldg(bias + g * H + u);
     pre[g].x += bv; pre[g].y += bv;
   }
+  float hv[2], sv[5][2];
 #pragma unroll
   for (int j = 0; j < 2; ++j) {
     const int b = 2 * bp + j;
-    if (b >= B) continue;
     const float pi = j ? pre[0].y : pre[0].x, pf = j ? pre[1].y : pre[1].x;
     const float pg = j ? pre[2].y : pre[2].x, po = j ? pre[3].y : pre[3].x;
     const float si = sigmoid_fast(pi), sf = sigmoid_fast(pf), tg = tanh_fast(pg), so = sigmoid_fast(po);
     const float c = sf * cst[ul * D2_BP + b] + si * tg;
     float h = so * tanh_fast(c);
-    cst[ul * D2_BP + b] = c;
-    if (sav) {  // training tape: [5][H][BP]
-      const size_t o = (size_t)u * D2_BP + b, gs = (size_t)H * D2_BP;
-      sav[o] = si; sav[gs + o] = sf; sav[2 * gs + o] = tg; sav[3 * gs + o] = so; sav[4 * gs + o] = c;
-    }
-    if (hidden_dropout) {  // nn.Dropout(0.1), train only (model/decoder.py:75,101)
+    if (b < B) cst[ul * D2_BP + b] = c;
+    sv[0][j] = si; sv[1][j] = sf; sv[2][j] = tg; sv[3][j] = so; sv[4][j] = c;
+    if (hidden_dropout && b < B) {  // nn.Dropout(0.1), train only (model/decoder.py:75,101)
       const bool k = keep ? (keep[(size_t)b * H + u] != 0) : rng_keep(seed, rng_base + (unsigned long long)b * H + u, 0.1f);
       h = k ? h * (1.0f / 0.9f) : 0.f;
     }
-    if (ho.x0) store_split(ho.x0, ho.plane0, ho.ld0, b, ho.col0 + u, h);
-    if (ho.x1) store_split(ho.x1, ho.plane1, ho.ld1, b, ho.col1 + u, h);
-    if (ho.rm) ho.rm[(size_t)b * ho.rm_ld + ho.rm_col + u] = h;
+    hv[j] = b < B ? h : 0.f;
   }
+  if (sav) {  // training tape: [5][H][BP]
+    const size_t o = (size_t)u * D2_BP + 2 * bp, gs = (size_t)H * D2_BP;
+    if (2 * bp + 1 < B) {
+#pragma unroll
+      for (int g = 0; g < 5; ++g) *reinterpret_cast<float2*>(sav + g * gs + o) = make_float2(sv[g][0], sv[g][1]);
+    } else if (2 * bp < B) {
+#pragma unroll
+      for (int g = 0; g < 5; ++g) sav[g * gs + o] = sv[g][0];
+    }
+  }
+  *reinterpret_cast<float2*>(h_s + ul * D2_BP + 2 * bp) = make_float2(hv[0], hv[1]);
+  __syncthreads();
+  const int b = threadIdx.x & 63, w = threadIdx.x >> 6;
+  if (b < B) {
+    float h8[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) h8[i] = h_s[i * D2_BP + b];
+    __nv_bfloat16* x = w < 2 ? ho.x0 : ho.x1;
+    if (x) {
+      const long long plane = w < 2 ? ho.plane0 : ho.plane1;
+      const int ld = w < 2 ? ho.ld0 : ho.ld1, col = (w < 2 ? ho.col0 : ho.col1) + unit0;
+      store_plane8(x + (w & 1) * plane + (size_t)b * ld + col, h8, w & 1, ((ld | col) & 7) == 0);
+    }
+    if (ho.rm && (ho.x1 ? w < 2 : w >= 2)) {
+      float* dst = ho.rm + (size_t)b * ho.rm_ld + ho.rm_col + unit0 + (w & 1) * 4;
+      const float* src = h8 + (w & 1) * 4;
+      if (((ho.rm_ld | (ho.rm_col + unit0)) & 3) == 0) *reinterpret_cast<float4*>(dst) = make_float4(src[0], src[1], src[2], src[3]);
+      else { dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2]; dst[3] = src[3]; }
+    }
+  }
+}
+
+// Query projection (model/attention.py:52) folded into the attention-LSTM phase: this CTA's 8 hidden units contribute
+// qp[b][a] = sum_u Wq[a][unit0+u] h[u][b]; the attention phase adds the 128 per-CTA partials in a fixed order.
+// Thread = (4 attention dims, 8 utterances); h_s is the staging buffer lstm_tail just filled.
+__device__ __forceinline__ void query_partial(const float* h_s, const float* wq_s, int A, int B, float* qp, size_t bstride) {
+  const int a4 = (threadIdx.x & 31) * 4, b0 = (threadIdx.x >> 5) * 8;
+  if (a4 >= A) return;
+  float acc[8][4];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { acc[j][0] = 0.f; acc[j][1] = 0.f; acc[j][2] = 0.f; acc[j][3] = 0.f; }
+#pragma unroll
+  for (int uu = 0; uu < 8; ++uu) {
+    const float4 w4 = *reinterpret_cast<const float4*>(wq_s + uu * A + a4);
+    const float4 ha = *reinterpret_cast<const float4*>(h_s + uu * D2_BP + b0);
+    const float4 hb = *reinterpret_cast<const float4*>(h_s + uu * D2_BP + b0 + 4);
+    const float hj[8] = {ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      acc[j][0] = fmaf(hj[j], w4.x, acc[j][0]); acc[j][1] = fmaf(hj[j], w4.y, acc[j][1]);
+      acc[j][2] = fmaf(hj[j], w4.z, acc[j][2]); acc[j][3] = fmaf(hj[j], w4.w, acc[j][3]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    if (b0 + j < B) *reinterpret_cast<float4*>(qp + (size_t)(b0 + j) * bstride + a4) = make_float4(acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
 }
 
 __device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) {
@@ -199,7 +279,7 @@ __device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) 
 // Attention for batch element b, part `part` of `S` (the S CTAs of one b sit in the same cluster):
 // each part computes the energies of its L-slice, the slices are exchanged through DSMEM, every part
 // normalises the full row and reduces its slice of the context columns.
-// Scratch (floats, in the idle TMA ring): q[A] | wp[Lc+32] | wc[Lc+32] | fs[Lc][36] | e_slice[Lc] |
+// Scratch (floats, in the idle TMA ring): q[A] | qh[2A] | wp[Lc+32] | wc[Lc+32] | fs[Lc][36] | e_slice[Lc] |
 //                                         e_full[L] | red[64] | cred[4*cols]
 #define ATT_MARK(slot) do { if (blockIdx.x == 0 && threadIdx.x == 0 && s.prof) { const long long now_ = clock64(); s.prof[slot] += (unsigned long long)(now_ - *prof_last); *prof_last = now_; } } while (0)
 __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& io, const Smem& sm, float* scratch, bool active,
@@ -208,7 +288,8 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
   const int L = d.L, A = d.A, EF = d.EF;
   const int Lc = (L + S - 1) / S, l0 = part * Lc, l1 = min(L, l0 + Lc), nl = max(0, l1 - l0);
   float* q_s = scratch;
-  float* wp = q_s + A;                            // previous / cumulative weights with a 15-tap halo
+  float* qh = q_s + A;                            // two half-sums of the per-CTA query partials
+  float* wp = qh + 2 * A;                         // previous / cumulative weights with a 15-tap halo
   float* wc = wp + ((Lc + 35) & ~3);
   float* fs = wc + ((Lc + 35) & ~3);            // [Lc][36] conv features (row stride 36: conflict-free float4 rows)
   float* e_slice = fs + (size_t)Lc * 36;
@@ -218,8 +299,20 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
   if (active) {
     const float* wprev = s.w_prev + ((size_t)cur * D2_BP + b) * L;
     const float* wcum = s.w_cum + ((size_t)cur * D2_BP + b) * L;
+    if (tid < 2 * A) {  // processed query = sum of the 128 per-CTA partials, always in the same order (bit-deterministic)
+      const int a = tid < A ? tid : tid - A, half = tid < A ? 0 : 1;
+      const float* qp = s.qpart + ((size_t)b * 128 + half * 64) * A + a;
+      float acc = 0.f;
 #pragma unroll 1
-    for (int i = tid; i < A; i += D2_THREADS) q_s[i] = ld_cg(s.q + (io.hist ? (size_t)t_out * D2_BP * A : 0) + (size_t)b * A + i);
+      for (int c0 = 0; c0 < 64; c0 += 16) {
+        float v[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = ld_cg(qp + (size_t)(c0 + i) * A);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) acc += v[i];
+      }
+      qh[tid] = acc;
+    }
 #pragma unroll 1
     for (int i = tid; i < nl + 30; i += D2_THREADS) {
       const int l = l0 + i - 15;
@@ -228,6 +321,11 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
       wc[i] = in ? ld_cg(wcum + l) : 0.f;
     }
     __syncthreads();
+    if (tid < A) {
+      const float qv = qh[tid] + qh[A + tid];
+      q_s[tid] = qv;
+      if (io.hist && part == 0) s.q[((size_t)t_out * D2_BP + b) * A + tid] = qv;   // training tape
+    }
     // location conv (model/attention.py:54): warp task = (32 positions, 8 filters); lane = position
     {
       const int nchunk = (nl + 31) >> 5;
@@ -397,7 +495,7 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
       const int col = c0 + c;
       store_split(xa, pa, d.KattP, b, d.P + col, v);
       store_split(xd, pd, d.KdecP, b, d.H + col, v);
-      s.projin[(size_t)b * d.KprojP + d.R + col] = v;
+      if (!io.hist) s.projin[(size_t)b * d.KprojP + d.R + col] = v;
     }
   }
   ATT_MARK(14);
@@ -405,7 +503,9 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
 }
 
 // ------------------------------------------------------------------------------------------
-enum { PH_ATT_LSTM = 0, PH_QUERY, PH_ATTN, PH_DEC_LSTM, PH_PROJ, PH_PRE1, PH_PRE2, PH_COUNT };
+enum { PH_ATT_LSTM = 0, PH_ATTN, PH_DEC_LSTM, PH_PROJ, PH_PRE1, PH_PRE2, PH_COUNT };
+// profiling slot of each phase (slot 1 = query partials + the barrier of the attention-LSTM phase)
+__device__ __constant__ int kPhaseSlot[PH_COUNT] = {1, 2, 3, 4, 5, 6};
 
 __global__ void __launch_bounds__(D2_THREADS, 1)
 decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weights w, D2State s, D2IO io) {
@@ -431,6 +531,8 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
 #pragma unroll 1
   for (int i = tid; i < d.A; i += D2_THREADS) sm.v[i] = w.v[i];
 #pragma unroll 1
+  for (int i = tid; i < 8 * d.A; i += D2_THREADS) sm.wq[i] = w.Wq[(size_t)(i % d.A) * d.H + unit0 + i / d.A];
+#pragma unroll 1
   for (int i = tid; i < 8 * D2_BP; i += D2_THREADS) {
     sm.c_att[i] = s.att_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP];
     sm.c_dec[i] = s.rnn_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP];
@@ -451,7 +553,8 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
   const int nkb_att = d.KattP / TG_BK, nkb_dec = d.KdecP / TG_BK;
   const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
   const float pscale = 1.0f / (1.0f - d.p_prenet);
-  const int nphase = io.teacher_forcing ? PH_PROJ + 1 : PH_COUNT;
+  // history mode (training): the mel/gate projection is off the recurrence and runs as one bulk GEMM after this kernel
+  const int nphase = io.teacher_forcing ? (io.hist ? PH_DEC_LSTM + 1 : PH_PROJ + 1) : PH_COUNT;
   int frames = 0;
   bool alive = true, fail = false, stop = false;
 
@@ -477,12 +580,17 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
         tc::cluster_sync();
         HOut ho;
         if (att) ho = HOut{s.xatt + (size_t)nxt * 2 * pa, d.KattP, d.P + d.EF, pa, s.xdec + (size_t)cur * 2 * pd, d.KdecP, 0, pd, s.att_h_rm, d.H, 0};
-        else ho = HOut{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, s.projin, d.KprojP, 0};
+        else ho = HOut{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, io.hist ? nullptr : s.projin, d.KprojP, 0};
+        if (!att && io.hist) frames = t + 1;
         const unsigned char* keep = att ? io.att_keep : io.rnn_keep;
         lstm_tail(sm.part, rank, unit0, att ? w.batt : w.bdec, d.H, att ? sm.c_att : sm.c_dec, B, ho,
                   keep ? keep + (size_t)tg_ * B * d.H : nullptr, io.hidden_dropout != 0, io.seed,
                   ((att ? 1ull : 2ull) << 40) + (unsigned long long)tg_ * B * d.H,
-                  (att ? s.sav_att : s.sav_dec) ? (att ? s.sav_att : s.sav_dec) + (size_t)tg_ * 5 * d.H * D2_BP : nullptr);
+                  (att ? s.sav_att : s.sav_dec) ? (att ? s.sav_att : s.sav_dec) + (size_t)tg_ * 5 * d.H * D2_BP : nullptr, sm.h_s);
+        if (att) {
+          prof_mark(0);
+          query_partial(sm.h_s, sm.wq, d.A, B, s.qpart + (size_t)blockIdx.x * d.A, (size_t)128 * d.A);
+        }
         wrote_x = true;
       } else if (ph == PH_ATTN) {
         // ---- location-sensitive attention (model/attention.py:54-67, model/decoder.py:90)
@@ -492,17 +600,14 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
         // ---- small dense phases: query (model/attention.py:52), mel/gate projection (model/decoder.py:103-109),
         //      prenet layers on the emitted frame (model/tacotron2.py:85-92,324-325)
         const float* Wm; const float* xin; int ldw, rows, ldx, K;
-        if (ph == PH_QUERY)     { Wm = w.Wq;    ldw = d.H;      rows = d.A;     xin = s.att_h_rm; ldx = d.H;      K = d.H; }
-        else if (ph == PH_PROJ) { Wm = w.Wproj; ldw = d.KprojP; rows = d.M + 1; xin = s.projin;   ldx = d.KprojP; K = d.KprojP; }
+        if (ph == PH_PROJ) { Wm = w.Wproj; ldw = d.KprojP; rows = d.M + 1; xin = s.projin;   ldx = d.KprojP; K = d.KprojP; }
         else if (ph == PH_PRE1) { Wm = w.W1;    ldw = d.M;      rows = d.P;     xin = s.mel_cur;  ldx = d.M;      K = d.M; }
         else                    { Wm = w.W2;    ldw = d.P;      rows = d.P;     xin = s.p1;       ldx = d.P;      K = d.P; }
         const SmallOut o = small_gemm(Wm, ldw, rows, xin, ldx, B, K, scratch);
         if (o.valid) {
           const int r = o.r, b = o.b;
           float v = o.v;
-          if (ph == PH_QUERY) {
-            s.q[(io.hist ? (size_t)tg_ * D2_BP * d.A : 0) + (size_t)b * d.A + r] = v;
-          } else if (ph == PH_PROJ) {
+          if (ph == PH_PROJ) {
             v += __ldg(w.bproj + r);
             if (r < d.M) {
               io.mels[((size_t)b * io.Tmax + tg_) * d.M + r] = v;
@@ -526,7 +631,7 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
         if (ph == PH_PROJ) frames = t + 1;
       }
       if (!(alive = bar.sync(fail, wrote_x))) break;
-      prof_mark(ph);
+      prof_mark(kPhaseSlot[ph]);
       if (ph == PH_PROJ && !io.teacher_forcing) {
         if (io.stop_enabled) {  // model/tacotron2.py:321-322: leave once every utterance has fired its stop gate
           int mine = 1;
@@ -557,14 +662,14 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
 size_t att_scratch_floats(const D2Dims& d, int S) {
   const int Lc = (d.L + S - 1) / S;
   const int cols = (((d.EF + S - 1) / S) + 3) & ~3;
-  return (size_t)d.A + 2 * (size_t)((Lc + 35) & ~3) + (size_t)Lc * 36 + Lc + 4 + d.L + 4 + 64 + 8 + 4 * (size_t)cols;
+  return 3 * (size_t)d.A + 2 * (size_t)((Lc + 35) & ~3) + (size_t)Lc * 36 + Lc + 4 + d.L + 4 + 64 + 8 + 4 * (size_t)cols;
 }
 
 }  // namespace
 
 size_t d2_smem_bytes(const D2Dims& d) {
   return 1024 + (size_t)D2_STAGES * TG_STAGE_BYTES + TG_M * TG_PART_LD * 4 + 2 * 8 * D2_BP * 4 + 2 * D2_LOC_K * D2_LOC_F * 4 +
-         (size_t)d.A * D2_LOC_F * 4 + d.A * 4 + (2 * D2_STAGES + 2) * 8 + 64;
+         (size_t)d.A * D2_LOC_F * 4 + d.A * 4 + 8 * d.A * 4 + 8 * D2_BP * 4 + (2 * D2_STAGES + 2) * 8 + 64;
 }
 
 static int launch_cfg(const D2Dims& d, cudaLaunchConfig_t* cfg, cudaLaunchAttribute* at, size_t smem, cudaStream_t st) {

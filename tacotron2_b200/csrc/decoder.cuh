@@ -42,7 +42,8 @@ struct D2State {
   float* rnn_c;          // [R][BP]
   float* att_h_rm;       // [BP][H]
   float* projin;         // [BP][KprojP]
-  float* q;              // [BP][A]
+  float* q;              // history mode only: [T][BP][A] processed query of every frame (training tape)
+  float* qpart;          // [BP][128 CTAs][A] per-CTA partial sums of the query projection (each CTA owns 8 units of att_h)
   float* w_prev;         // [2][BP][L]
   float* w_cum;          // [2][BP][L]
   float* mel_cur;        // [BP][M]

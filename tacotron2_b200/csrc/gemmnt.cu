@@ -22,8 +22,10 @@ __global__ void __launch_bounds__(256, 1) gemm_nt_kernel(const __grid_constant__
   const int z = blockIdx.y, sp = blockIdx.z;
   const int m0 = mt * 128, n0 = nt * a.NT;
   const int kin_blocks = (a.Kin + 63) >> 6;
-  const long long nkb_all = (long long)a.Kout * kin_blocks;
+  const long long nkb_seg1 = (long long)a.Kout * kin_blocks;
+  const long long nkb_all = nkb_seg1 + ((a.Kin2 + 63) >> 6);
   const int kb0 = (int)(nkb_all * sp / a.splitk), kb1 = (int)(nkb_all * (sp + 1) / a.splitk);
+  const int brow0 = nt * (a.b_row_step ? a.b_row_step : a.NT);
   const int shift = a.shift0 + z * a.shift_step;
   const uint32_t b_tile = (uint32_t)a.NT * 128u;
 
@@ -46,12 +48,18 @@ __global__ void __launch_bounds__(256, 1) gemm_nt_kernel(const __grid_constant__
     int st = 0; uint32_t ph = 0;
     const uint32_t tx = (uint32_t)(a.npass == 3 ? 2 : 1) * (GN_A_TILE + b_tile);
     for (int kb = kb0; kb < kb1; ++kb) {
-      const int ko = kb / kin_blocks, ki = (kb - ko * kin_blocks) * 64;
       if (!tc::mbar_wait(empty + st, ph ^ 1)) { ok = false; break; }
       uint8_t* sp_ = base + (size_t)st * GN_STAGE_BYTES;
       tc::mbar_arrive_expect_tx(full + st, tx);
-      tc::tma_load_4d(sp_, &a.a_map, full + st, ki, ko, m0 + z * a.a_zrow, 0);
-      tc::tma_load_4d(sp_ + 2 * GN_A_TILE, &a.b_map, full + st, ki + shift, ko, n0 + z * a.b_zrow, 0);
+      if (kb < nkb_seg1) {
+        const int ko = kb / kin_blocks, ki = (kb - ko * kin_blocks) * 64;
+        tc::tma_load_4d(sp_, &a.a_map, full + st, ki, ko, m0 + z * a.a_zrow, 0);
+        tc::tma_load_4d(sp_ + 2 * GN_A_TILE, &a.b_map, full + st, ki + shift, ko, brow0 + z * a.b_zrow, 0);
+      } else {
+        const int ki = (int)(kb - nkb_seg1) * 64;
+        tc::tma_load_4d(sp_, &a.a_map2, full + st, ki, 0, m0 + z * a.a_zrow, 0);
+        tc::tma_load_4d(sp_ + 2 * GN_A_TILE, &a.b_map2, full + st, ki, 0, brow0 + z * a.b_zrow, 0);
+      }
       if (++st == GN_STAGES) { st = 0; ph ^= 1; }
     }
   } else if (warp == 1 && lane == 0) {
@@ -180,7 +188,7 @@ __global__ void transpose_bf16_kernel(const __nv_bfloat16* __restrict__ src, lon
 
 long long gemmnt_partial_floats(GemmNtArgs& a, int num_sms) {
   const int Nt = (a.N + a.NT - 1) / a.NT, Mt = (a.M + 127) / 128;
-  const long long nkb = (long long)a.Kout * ((a.Kin + 63) / 64);
+  const long long nkb = (long long)a.Kout * ((a.Kin + 63) / 64) + (a.Kin2 + 63) / 64;
   if (a.splitk <= 0) {
     const long long tiles = (long long)Mt * Nt * a.nz;
     long long sk = (2ll * num_sms + tiles - 1) / tiles;          // ~2 waves

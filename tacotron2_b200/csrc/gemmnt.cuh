@@ -20,6 +20,11 @@ struct GemmNtArgs {
   float* partial;               // [splitk][nz][Mt*128][Nt*NT]
   float* direct_out;            // splitk == 1 && nz == 1 only: write C[m][n] straight to direct_out[m*direct_ldm + n] (no partial slab)
   long long direct_ldm;
+  // optional second contraction segment (own operand maps, Kout = 1, no shift): C += A2 * B2^T over Kin2 -- lets one launch
+  // contract over two column windows that live in different places (e.g. different time slots of a tape)
+  CUtensorMap a_map2, b_map2;
+  int Kin2;
+  int b_row_step;               // B-operand row coordinate of N-tile nt is nt*b_row_step (0: nt*NT) -- rows interleaved with other data
 };
 
 struct GemmNtOut {

@@ -77,6 +77,10 @@ struct DBMaps {
 
 int db_launch(const D2Dims& d, int T, int KattT, int KdecT, const DBWeights& w, const DBTape& tp, const DBWork& wk, const DBMaps& maps,
               unsigned long long* prof, cudaStream_t st);
+// Bulk mel/gate projection of the teacher-forced training forward (model/decoder.py:103-109 for all T frames at once, off the
+// recurrence): reads rnn_h_t / ctx_t / controls from the decoder-cell operand rows of the tape.  tmp: (M+1) * T*64 floats.
+struct t2_ctx;
+int decode_proj_bulk(t2_ctx* c, const __nv_bfloat16* xdec_tape, int B, int T, float* mels, float* gates, float* tmp, cudaStream_t st);
 int db_parts(const D2Dims& d);        // S: CTAs per utterance in the attention backward
 size_t db_small_floats(const D2Dims& d);
 

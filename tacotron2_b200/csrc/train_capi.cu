@@ -246,6 +246,48 @@ int bulk_gemm(t2_ctx* c, const Opnd& A, const Opnd& Bo, int M, int N, int shiftB
   return gemmnt_launch(a, o, st);
 }
 
+// tmp[m][t*64 + b] (+ bias) -> mels[b][t][m], gates[b][t]; one CTA per frame, transposed through shared memory
+__global__ void proj_finish_kernel(const float* __restrict__ tmp, const float* __restrict__ bias, int B, int T, int M, float* __restrict__ mels,
+                                   float* __restrict__ gates) {
+  extern __shared__ float tile[];   // [M+1][65]
+  const int t = blockIdx.x;
+  const long long N = (long long)T * D2_BP;
+  for (int i = threadIdx.x; i < (M + 1) * D2_BP; i += blockDim.x) {
+    const int m = i / D2_BP, b = i % D2_BP;
+    tile[m * 65 + b] = tmp[(size_t)m * N + (size_t)t * D2_BP + b] + bias[m];
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < B * M; i += blockDim.x) {
+    const int b = i / M, m = i % M;
+    mels[((size_t)b * T + t) * M + m] = tile[m * 65 + b];
+  }
+  for (int b = threadIdx.x; b < B; b += blockDim.x) gates[(size_t)b * T + t] = tile[M * 65 + b];
+}
+
+}  // namespace
+
+int decode_proj_bulk(t2_ctx* c, const __nv_bfloat16* xdec, int B, int T, float* mels, float* gates, float* tmp, cudaStream_t st) {
+  const int M = c->M, KdecP = c->dd.KdecP;
+  const long long slot = 2ll * D2_BP * KdecP, plane = (long long)D2_BP * KdecP;
+  GemmNtArgs a{};
+  a.M = M + 1; a.N = T * D2_BP; a.NT = 64; a.nz = 1; a.splitk = 1; a.npass = c->npass;
+  a.b_row_step = 2 * D2_BP;   // rows of one slot: 64 hi rows then 64 lo rows
+  a.direct_out = tmp; a.direct_ldm = (long long)T * D2_BP;
+  // segment 1: rnn_h_t = columns [projA_col0, KdecP) of slot t+1;  segment 2: [ctx_t | controls] = columns [H, H+KprojB) of slot t
+  a.Kin = c->KprojA; a.Kout = 1;
+  RC(gemmnt_make_map(&a.a_map, c->WprojA_b, c->KprojA, c->KprojA, 1, M + 1, (long long)(M + 1) * c->KprojA, 128, c->npass));
+  RC(gemmnt_make_map(&a.b_map, xdec + slot + c->projA_col0, c->KprojA, KdecP, 1, T * 2 * D2_BP, plane, 64, c->npass));
+  a.Kin2 = c->KprojB;
+  RC(gemmnt_make_map(&a.a_map2, c->WprojB_b, c->KprojB, c->KprojB, 1, M + 1, (long long)(M + 1) * c->KprojB, 128, c->npass));
+  RC(gemmnt_make_map(&a.b_map2, xdec + c->H, c->KprojB, KdecP, 1, T * 2 * D2_BP, plane, 64, c->npass));
+  RC(gemmnt_launch(a, GemmNtOut{}, st));
+  proj_finish_kernel<<<T, 256, (size_t)(M + 1) * 65 * sizeof(float), st>>>(tmp, c->d2w.bproj, B, T, M, mels, gates);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+
+namespace {
+
 int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const unsigned char* mask, const float* mel_target, int B, int L,
                     int T, const unsigned char* att_keep, const unsigned char* rnn_keep, unsigned long long seed, const float* aligns,
                     const float* d_mels, const float* d_gates, const DecTape& tp, float* d_memory, float* d_pmem, Arena& wa,
@@ -657,7 +699,7 @@ extern "C" int t2_memory_bwd(t2_ctx* c, const float* memory, const long long* sp
 extern "C" long long t2_train_workspace_bytes(const t2_ctx* cc, int B, int L, int T) {
   t2_ctx* c = const_cast<t2_ctx*>(cc);
   if (!c || B <= 0 || L <= 0 || T <= 0) return -1;
-  long long best = t2_workspace_bytes(cc, B, L, T);
+  long long best = t2_workspace_bytes(cc, B, L, T) + (long long)(c->M + 1) * T * D2_BP * 4 + 256;   // + bulk-projection staging of the train forward
   best = std::max(best, postnet_bwd_ws_bytes(c, B, T) + bn_scratch_bytes(c->PD));
   best = std::max(best, decode_bwd_ws_bytes(c, B, L, T));
   { Arena wa(nullptr, 0); EncTape tp{}; encoder_bwd_impl(c, nullptr, nullptr, B, L, nullptr, 0, nullptr, nullptr, tp, wa, nullptr); best = std::max<long long>(best, wa.off); }
