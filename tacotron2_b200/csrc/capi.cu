@@ -603,6 +603,10 @@ static State2Plan plan_state2(const D2Dims& d, int L, Arena& ar) {
   pl.zero_begin = ar.base ? ar.base + off0 : nullptr;
   pl.zero_bytes = (size_t)(ar.off - off0);
   s.qpart = ar.take<float>((size_t)D2_BP * 128 * d.A);   // fully rewritten every frame: not part of the zeroed region
+  {
+    const int S = d2_att_parts(d.B);
+    s.accpm = ar.take<float>((size_t)128 * ((L + S - 1) / S) * d.A);
+  }
   return pl;
 }
 

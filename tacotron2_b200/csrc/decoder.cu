@@ -114,11 +114,16 @@ struct Smem {
   float* v;
   float* wq;
   float* h_s;
+  float* pre;        // attention precompute scratch (only when io.precompute): wp | wc (with halo) | 6 per-warp conv tiles [8][36]
   uint64_t* bars;
   uint32_t* tmem_slot;
 };
 
-__device__ __forceinline__ Smem carve(uint8_t* base, const D2Dims& d) {
+__host__ __device__ __forceinline__ int d2_parts(int B, int grid) { return (B * 4 <= grid) ? 4 : ((B * 2 <= grid) ? 2 : 1); }
+__host__ __device__ __forceinline__ int pre_wlen(int L, int S) { return ((((L + S - 1) / S) + 7) & ~7) + 32; }
+__host__ __device__ __forceinline__ size_t pre_floats(int L, int S) { return 2 * (size_t)pre_wlen(L, S) + 6 * 8 * 36; }
+
+__device__ __forceinline__ Smem carve(uint8_t* base, const D2Dims& d, int pre_f) {
   Smem s;
   s.stages = base;
   uint8_t* p = base + D2_STAGES * TG_STAGE_BYTES;
@@ -130,6 +135,7 @@ __device__ __forceinline__ Smem carve(uint8_t* base, const D2Dims& d) {
   s.v = reinterpret_cast<float*>(p);     p += d.A * 4;
   s.wq = reinterpret_cast<float*>(p);    p += 8 * d.A * 4;
   s.h_s = reinterpret_cast<float*>(p);   p += 8 * D2_BP * 4;
+  s.pre = reinterpret_cast<float*>(p);   p += (size_t)pre_f * 4;
   s.bars = reinterpret_cast<uint64_t*>(p); p += (2 * D2_STAGES + 2) * 8;
   s.tmem_slot = reinterpret_cast<uint32_t*>(p);
   return s;
@@ -276,6 +282,90 @@ __device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) 
 }
 
 // ------------------------------------------------------------------------------------------
+// Location term of the attention energies, hoisted out of the attention phase: everything in
+//   processed_attention + processed_memory   (model/attention.py:54-56,62)
+// depends only on the previous frame's attention weights, so warps 2..7 compute it for this CTA's L-slice while warps 0/1
+// run the attention-LSTM gate GEMM of the same frame.  Warp task = 8 positions: location conv with lane = filter (weights
+// conflict-free, the two 38-sample input windows in registers), the 8x32 feature tile goes through a per-warp shared-memory
+// tile into the location dense with lane = 4 attention dims, processed memory is added and the [8][A] block is written to
+// this CTA's private L2-resident scratch.
+__device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2IO& io, const Smem& sm, int b, int part, int S, int cur) {
+  const int ptid = threadIdx.x - 64, lane = threadIdx.x & 31, pw = (threadIdx.x >> 5) - 2;
+  const int L = d.L, A = d.A;
+  const int Lc = (L + S - 1) / S, l0 = part * Lc, l1 = min(L, l0 + Lc), nl = max(0, l1 - l0);
+  const int ntile = (nl + 7) >> 3, wlen = pre_wlen(L, S);
+  float* wp = sm.pre;
+  float* wc = wp + wlen;
+  float* fsw = wc + wlen + pw * (8 * 36);
+  const float* wprev = s.w_prev + ((size_t)cur * D2_BP + b) * L;
+  const float* wcum = s.w_cum + ((size_t)cur * D2_BP + b) * L;
+#pragma unroll 1
+  for (int i = ptid; i < ntile * 8 + 32; i += 192) {
+    const int l = l0 + i - 15;
+    const bool in = (l >= 0 && l < L);
+    wp[i] = in ? ld_cg(wprev + l) : 0.f;
+    wc[i] = in ? ld_cg(wcum + l) : 0.f;
+  }
+  asm volatile("bar.sync 1, 192;" ::: "memory");
+  float* out = s.accpm + (size_t)blockIdx.x * Lc * A;
+  const int a4 = lane * 4;
+  const bool lane_on = a4 < A;
+  const int ac = lane_on ? a4 : 0;
+#pragma unroll 1
+  for (int tl = pw; tl < ntile; tl += 6) {
+    const int lt = tl * 8;
+    float4 pm4[8];
+#pragma unroll
+    for (int p = 0; p < 8; ++p)
+      pm4[p] = __ldg(reinterpret_cast<const float4*>(io.pmem + ((size_t)b * L + l0 + min(lt + p, nl - 1)) * A + ac));
+    float xw[40], xc[40];
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+      const float4 u4 = *reinterpret_cast<const float4*>(wp + lt + 4 * i), c4 = *reinterpret_cast<const float4*>(wc + lt + 4 * i);
+      xw[4 * i] = u4.x; xw[4 * i + 1] = u4.y; xw[4 * i + 2] = u4.z; xw[4 * i + 3] = u4.w;
+      xc[4 * i] = c4.x; xc[4 * i + 1] = c4.y; xc[4 * i + 2] = c4.z; xc[4 * i + 3] = c4.w;
+    }
+    float acc[8];
+#pragma unroll
+    for (int p = 0; p < 8; ++p) acc[p] = 0.f;
+#pragma unroll
+    for (int j = 0; j < D2_LOC_K; ++j) {
+      const float w0 = sm.conv_t[j * D2_LOC_F + lane], w1 = sm.conv_t[(D2_LOC_K + j) * D2_LOC_F + lane];
+#pragma unroll
+      for (int p = 0; p < 8; ++p) { acc[p] = fmaf(w0, xw[p + j], acc[p]); acc[p] = fmaf(w1, xc[p + j], acc[p]); }
+    }
+#pragma unroll
+    for (int p = 0; p < 8; ++p) fsw[p * 36 + lane] = acc[p];
+    __syncwarp();
+    float o[8][4];
+#pragma unroll
+    for (int p = 0; p < 8; ++p) { o[p][0] = 0.f; o[p][1] = 0.f; o[p][2] = 0.f; o[p][3] = 0.f; }
+#pragma unroll 2
+    for (int f4 = 0; f4 < D2_LOC_F / 4; ++f4) {
+      float4 fv[8];
+#pragma unroll
+      for (int p = 0; p < 8; ++p) fv[p] = *reinterpret_cast<const float4*>(fsw + p * 36 + f4 * 4);
+#pragma unroll
+      for (int ff = 0; ff < 4; ++ff) {
+        const float4 wv = *reinterpret_cast<const float4*>(sm.dense + (f4 * 4 + ff) * A + ac);
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {
+          const float fl = ff == 0 ? fv[p].x : (ff == 1 ? fv[p].y : (ff == 2 ? fv[p].z : fv[p].w));
+          o[p][0] = fmaf(fl, wv.x, o[p][0]); o[p][1] = fmaf(fl, wv.y, o[p][1]);
+          o[p][2] = fmaf(fl, wv.z, o[p][2]); o[p][3] = fmaf(fl, wv.w, o[p][3]);
+        }
+      }
+    }
+#pragma unroll
+    for (int p = 0; p < 8; ++p)
+      if (lane_on && lt + p < nl)
+        *reinterpret_cast<float4*>(out + (size_t)(lt + p) * A + a4) =
+            make_float4(o[p][0] + pm4[p].x, o[p][1] + pm4[p].y, o[p][2] + pm4[p].z, o[p][3] + pm4[p].w);
+    __syncwarp();
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // Attention for batch element b, part `part` of `S` (the S CTAs of one b sit in the same cluster):
 // each part computes the energies of its L-slice, the slices are exchanged through DSMEM, every part
 // normalises the full row and reduces its slice of the context columns.
@@ -313,12 +403,14 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
       }
       qh[tid] = acc;
     }
+    if (!io.precompute) {
 #pragma unroll 1
-    for (int i = tid; i < nl + 30; i += D2_THREADS) {
-      const int l = l0 + i - 15;
-      const bool in = (l >= 0 && l < L);
-      wp[i] = in ? ld_cg(wprev + l) : 0.f;
-      wc[i] = in ? ld_cg(wcum + l) : 0.f;
+      for (int i = tid; i < nl + 30; i += D2_THREADS) {
+        const int l = l0 + i - 15;
+        const bool in = (l >= 0 && l < L);
+        wp[i] = in ? ld_cg(wprev + l) : 0.f;
+        wc[i] = in ? ld_cg(wcum + l) : 0.f;
+      }
     }
     __syncthreads();
     if (tid < A) {
@@ -326,6 +418,35 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
       q_s[tid] = qv;
       if (io.hist && part == 0) s.q[((size_t)t_out * D2_BP + b) * A + tid] = qv;   // training tape
     }
+    if (io.precompute) {
+      // energies from the precomputed location term (attention_precompute): e[l] = sum_a v[a] tanh(q[a] + x[l][a])
+      __syncthreads();
+      ATT_MARK(10);
+      const unsigned char* mk = io.mask + (size_t)b * L;
+      const float* xin = s.accpm + (size_t)blockIdx.x * Lc * A;
+      const int a4 = lane * 4;
+      const bool lane_on = a4 < A;
+      const int ac = lane_on ? a4 : 0;
+      const float4 q4 = *reinterpret_cast<const float4*>(q_s + ac);
+      const float4 v4 = *reinterpret_cast<const float4*>(sm.v + ac);
+      const int ntile = (nl + 7) >> 3;
+#pragma unroll 1
+      for (int tl = warp; tl < ntile; tl += D2_THREADS / 32) {
+        const int lt = tl * 8;
+        float4 x4[8];
+#pragma unroll
+        for (int l = 0; l < 8; ++l) x4[l] = __ldcg(reinterpret_cast<const float4*>(xin + (size_t)min(lt + l, nl - 1) * A + ac));
+#pragma unroll
+        for (int l = 0; l < 8; ++l) {
+          float e = v4.x * tanh_fast(q4.x + x4[l].x);
+          e = fmaf(v4.y, tanh_fast(q4.y + x4[l].y), e);
+          e = fmaf(v4.z, tanh_fast(q4.z + x4[l].z), e);
+          e = fmaf(v4.w, tanh_fast(q4.w + x4[l].w), e);
+          e = warp_sum(lane_on ? e : 0.f);
+          if (lane == 0 && lt + l < nl) e_slice[lt + l] = mk[l0 + lt + l] ? -INFINITY : e;  // masked_fill (model/attention.py:63)
+        }
+      }
+    } else {
     // location conv (model/attention.py:54): warp task = (32 positions, 8 filters); lane = position
     {
       const int nchunk = (nl + 31) >> 5;
@@ -407,6 +528,7 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
         }
       }
     }
+    }  // !precompute
   }
   ATT_MARK(11);
   tc::cluster_sync();  // energy slices visible to the peers of this batch element
@@ -443,7 +565,7 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
       e_full[l] = w;
       if (l >= l0 && l < l1) {  // each part publishes its own slice
         s.w_prev[((size_t)nxt * D2_BP + b) * L + l] = w;
-        s.w_cum[((size_t)nxt * D2_BP + b) * L + l] = wc[l - l0 + 15] + w;  // model/decoder.py:90
+        s.w_cum[((size_t)nxt * D2_BP + b) * L + l] = (io.precompute ? ld_cg(s.w_cum + ((size_t)cur * D2_BP + b) * L + l) : wc[l - l0 + 15]) + w;  // model/decoder.py:90
         io.aligns[((size_t)b * io.Tmax + t_out) * L + l] = w;
       }
     }
@@ -512,7 +634,8 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // keep the pointer's shared-memory provenance (no integer round trip) so loads/stores compile to LDS/STS
   uint8_t* base = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
-  const Smem sm = carve(base, d);
+  const int S = d2_parts(d.B, (int)gridDim.x);   // attention work split: S CTAs (same cluster) per batch element
+  const Smem sm = carve(base, d, io.precompute ? (int)pre_floats(d.L, S) : 0);
   float* scratch = reinterpret_cast<float*>(base);
   const int tid = threadIdx.x;
   const uint32_t rank = tc::cluster_ctarank();
@@ -546,8 +669,6 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
   auto prof_mark = [&](int slot) {
     if (blockIdx.x == 0 && tid == 0 && s.prof) { const long long now = clock64(); s.prof[slot] += (unsigned long long)(now - prof_last); prof_last = now; }
   };
-  // attention work split: S CTAs (same cluster) per batch element
-  const int S = (B * 4 <= (int)gridDim.x) ? 4 : ((B * 2 <= (int)gridDim.x) ? 2 : 1);
   const int att_b = blockIdx.x / S, att_part = blockIdx.x % S;
   const bool att_active = att_b < B;
   const int nkb_att = d.KattP / TG_BK, nkb_dec = d.KdecP / TG_BK;
@@ -574,7 +695,14 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
         else xs = tg::XSrc{&maps.x_dec, cur * 2, &maps.x_dec, cur * 2, nkb_dec};
         const int nkb = att ? nkb_att : nkb_dec;
         const uint32_t dcol = att ? 0u : 64u;
-        if (!tg::gemm(pipe, att ? &maps.w_att : &maps.w_dec, tile * TG_M, nkb, xs, (int)rank, nkb, D2_CLUSTER, dcol)) fail = true;
+        bool gok;
+        if (att && io.precompute && att_active) {
+          gok = tg::gemm(pipe, &maps.w_att, tile * TG_M, nkb, xs, (int)rank, nkb, D2_CLUSTER, dcol,
+                         [&]() { attention_precompute(d, s, io, sm, att_b, att_part, S, cur); });
+        } else {
+          gok = tg::gemm(pipe, att ? &maps.w_att : &maps.w_dec, tile * TG_M, nkb, xs, (int)rank, nkb, D2_CLUSTER, dcol);
+        }
+        if (!gok) fail = true;
         prof_mark(att ? 8 : 9);
         tg::accum_to_smem(pipe, dcol, sm.part);
         tc::cluster_sync();
@@ -667,6 +795,8 @@ size_t att_scratch_floats(const D2Dims& d, int S) {
 
 }  // namespace
 
+int d2_att_parts(int B) { return d2_parts(B, 128); }
+
 size_t d2_smem_bytes(const D2Dims& d) {
   return 1024 + (size_t)D2_STAGES * TG_STAGE_BYTES + TG_M * TG_PART_LD * 4 + 2 * 8 * D2_BP * 4 + 2 * D2_LOC_K * D2_LOC_F * 4 +
          (size_t)d.A * D2_LOC_F * 4 + d.A * 4 + 8 * d.A * 4 + 8 * D2_BP * 4 + (2 * D2_STAGES + 2) * 8 + 64;
@@ -684,18 +814,21 @@ static int launch_cfg(const D2Dims& d, cudaLaunchConfig_t* cfg, cudaLaunchAttrib
   return T2_OK;
 }
 
-int d2_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, const D2Maps& maps, cudaStream_t st) {
+int d2_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io_in, const D2Maps& maps, cudaStream_t st) {
   T2_REQUIRE(d.B >= 1 && d.B <= D2_BP, T2_ERR_ARG, "decoder: batch %d not in [1,%d] per launch", d.B, D2_BP);
   T2_REQUIRE(d.H == d.R && d.H % 32 == 0 && d.P % TG_BK == 0 && d.EF % 4 == 0 && d.M % 4 == 0 && d.A % 32 == 0 && d.A <= D2_MAX_A,
              T2_ERR_UNSUPPORTED, "decoder: unsupported dims H=%d R=%d EF=%d M=%d P=%d A=%d", d.H, d.R, d.EF, d.M, d.P, d.A);
   const int grid = (d.H / 32) * D2_CLUSTER;
   T2_REQUIRE(grid == 128, T2_ERR_UNSUPPORTED, "decoder: this revision is laid out for 128 CTAs (att_rnn_dim = 1024), got %d", grid);
-  const int S = (d.B * 4 <= grid) ? 4 : ((d.B * 2 <= grid) ? 2 : 1);
+  const int S = d2_parts(d.B, grid);
   const size_t ring = (size_t)D2_STAGES * TG_STAGE_BYTES;
   T2_REQUIRE(att_scratch_floats(d, S) * 4 <= ring, T2_ERR_UNSUPPORTED, "decoder: L=%d too long for the attention scratch", d.L);
   T2_REQUIRE(((size_t)(((d.M + 1 + 15) / 16) + 8) * (d.KprojP + 4) + 128) * 4 <= ring, T2_ERR_UNSUPPORTED, "decoder: projection staging");
-  const size_t smem = d2_smem_bytes(d);
+  size_t smem = d2_smem_bytes(d);
   T2_REQUIRE(smem <= 227 * 1024, T2_ERR_UNSUPPORTED, "decoder: %zu B shared memory", smem);
+  D2IO io = io_in;
+  io.precompute = (s.accpm && smem + pre_floats(d.L, S) * 4 <= 227 * 1024 && !getenv("T2B200_NO_PRECOMPUTE")) ? 1 : 0;
+  if (io.precompute) smem += pre_floats(d.L, S) * 4;
   T2_CHECK_CUDA(cudaFuncSetAttribute(decoder_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg{};
   cudaLaunchAttribute at[1];

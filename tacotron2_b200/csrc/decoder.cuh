@@ -43,6 +43,8 @@ struct D2State {
   float* att_h_rm;       // [BP][H]
   float* projin;         // [BP][KprojP]
   float* q;              // history mode only: [T][BP][A] processed query of every frame (training tape)
+  float* accpm;          // [128 CTAs][ceil(L/S)][A] location term + processed memory of each CTA's attention slice (precomputed
+                         // during the attention-LSTM GEMM of the same frame, consumed by the attention phase)
   float* qpart;          // [BP][128 CTAs][A] per-CTA partial sums of the query projection (each CTA owns 8 units of att_h)
   float* w_prev;         // [2][BP][L]
   float* w_cum;          // [2][BP][L]
@@ -71,6 +73,7 @@ struct D2IO {
   int Tmax, n_steps, t0;
   int teacher_forcing, hidden_dropout, stop_enabled;
   int debug_barrier;  // adds one empty grid barrier per frame and times it (profiling only)
+  int precompute;     // set by d2_launch: shared memory allows the location conv + dense to run beside the attention-LSTM GEMM
   int hist;           // 1: state buffers are indexed by frame (slot t / t+1) instead of parity -- the training tape
   unsigned long long seed;
 };
@@ -86,3 +89,4 @@ struct D2Maps {  // TMA descriptors (bf16, 128-B swizzle, box 64 x rows x {1|2})
 int d2_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, const D2Maps& maps, cudaStream_t stream);
 int d2_max_clusters(int* out);
 size_t d2_smem_bytes(const D2Dims& d);
+int d2_att_parts(int B);   // S: CTAs per utterance in the attention phase

@@ -57,8 +57,12 @@ __device__ __forceinline__ void pipe_init(Pipe& p, uint64_t* bars, uint8_t* stag
 // [d_col, d_col+64).  All threads of the CTA must call it; returns false on a pipeline timeout.
 // w_nkb > 0: W is stored tile-major ([tile][kb][128][64], every TMA box one contiguous 16 KB chunk) with w_nkb K-blocks per
 // tile; w_nkb == 0: W is a plain row-major [rows][K] matrix.
+// `side` runs on warps 2..7 (192 threads, named barrier 1 is theirs) while warps 0/1 stream and issue the GEMM: work that does not
+// depend on this GEMM's result and needs no part of the stage ring.
+struct NoSide { __device__ __forceinline__ void operator()() const {} };
+template <class Side>
 __device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row0, int w_nkb, const XSrc& xs, int kb_begin, int kb_end,
-                                     int kb_stride, uint32_t d_col) {
+                                     int kb_stride, uint32_t d_col, Side side) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   bool ok = true;
   const uint32_t stage_tx = (uint32_t)(p.npass == 3 ? TG_STAGE_BYTES : TG_W_TILE + TG_X_TILE);
@@ -103,6 +107,8 @@ __device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row
       if (++p.c_stage == p.nstages) { p.c_stage = 0; p.c_phase ^= 1; }
     }
     tc::umma_commit(p.accum);  // accumulator complete
+  } else if (warp >= 2) {
+    side();
   }
   __syncwarp();
   // everyone waits for the accumulator
@@ -110,6 +116,11 @@ __device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row
   p.a_phase ^= 1;
   tc::tc_fence_after();
   return __syncthreads_and(ok ? 1 : 0) != 0;
+}
+
+__device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row0, int w_nkb, const XSrc& xs, int kb_begin, int kb_end,
+                                     int kb_stride, uint32_t d_col) {
+  return gemm(p, wmap, w_row0, w_nkb, xs, kb_begin, kb_end, kb_stride, d_col, NoSide{});
 }
 
 // TMEM accumulator columns [d_col, d_col+64) -> this CTA's partial buffer part[128][TG_PART_LD] (shared memory).
