@@ -10,6 +10,8 @@
 // cell states live in shared memory, hidden states travel as bf16 (hi,lo) pairs for the next GEMM.
 #include "decoder.cuh"
 
+#define D2_LOC_KP 32   // location-conv taps padded to a multiple of 8 (zero tap) for the blocked conv loop
+
 namespace {
 
 struct GridBar {
@@ -46,53 +48,44 @@ struct GridBar {
 };
 
 // ------------------------------------------------------------------------------------------
-// Small dense phases on CUDA cores: out[b][r] = sum_k W[r][k] x[b][k].  The 128 CTAs form a 16 x 8 grid of
-// (row group, batch group of 8); W rows and x rows are staged in shared memory (row stride K+4 floats:
-// conflict-free float4 reads), 128 outputs per CTA, two K-halves per output.  Returns this thread's output (if any);
-// the caller applies the phase-specific epilogue and must __syncthreads() before reusing the scratch.
-struct SmallOut { int r, b; float v; bool valid; };
-__device__ __forceinline__ SmallOut small_gemm(const float* __restrict__ W, int ldw, int rows, const float* x, int ldx, int B, int K,
-                                               float* scratch) {
-  SmallOut out{0, 0, 0.f, false};
-  const int tid = threadIdx.x;
-  const int rg = blockIdx.x >> 3, bg = blockIdx.x & 7;
-  const int rpc = (rows + 15) >> 4;           // rows per CTA (<= 16)
-  const int r0 = rg * rpc, b0 = bg * 8;
-  const int nr = max(0, min(rpc, rows - r0)), nb = max(0, min(8, B - b0));
-  if (blockIdx.x >= 128 || nr == 0 || nb == 0) return out;
-  const int ld = K + 4, K4 = K >> 2;
-  float* Ws = scratch;                        // [rpc][ld]
-  float* xs = scratch + rpc * ld;             // [8][ld]
-  float* red = xs + 8 * ld;                   // [128]
+// Small dense layers of the output phase on CUDA cores: y_j[r] = sum_k W[r][k] x_j[k] for the two utterances (j = 0,1) a
+// cluster owns.  One warp per block of consecutive rows [rb, re), four rows in flight, lanes stride the row in 16-byte loads
+// (coalesced, weights straight from L2), fixed-order warp reduction; lane 0 leaves the sums in y[j*ys + r - ybase] (shared
+// memory).  One out-of-line copy serves all three layers (instruction-cache footprint).
+__device__ __noinline__ void rows_dot2(const float* __restrict__ W, int ldw, int K4, int rb, int re, const float* x0, const float* x1, float* y,
+                                       int ybase, int ys) {
+  const int lane = threadIdx.x & 31;
 #pragma unroll 1
-  for (int i = tid; i < (nr + nb) * K4; i += D2_THREADS) {
-    const int rr = i / K4, c = i - rr * K4;
-    const float* src = rr < nr ? W + (size_t)(r0 + rr) * ldw : x + (size_t)(b0 + rr - nr) * ldx;
-    float* dst = rr < nr ? Ws + rr * ld : xs + (rr - nr) * ld;
-    cp_async16(dst + c * 4, src + c * 4);
-  }
-  cp_async_commit();
-  cp_async_wait<0>();
-  __syncthreads();
-  const int o = tid & 127, kh = tid >> 7;
-  const int r = o >> 3, b = o & 7;
-  float acc = 0.f;
-  if (r < nr && b < nb) {
-    const float4* wp = reinterpret_cast<const float4*>(Ws + r * ld);
-    const float4* xp = reinterpret_cast<const float4*>(xs + b * ld);
-    const int kbeg = kh * (K4 >> 1), kend = kh ? K4 : (K4 >> 1);
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-#pragma unroll 4
-    for (int k = kbeg; k < kend; ++k) {
-      const float4 wv = wp[k], xv = xp[k];
-      a0 = fmaf(wv.x, xv.x, a0); a1 = fmaf(wv.y, xv.y, a1); a2 = fmaf(wv.z, xv.z, a2); a3 = fmaf(wv.w, xv.w, a3);
+  for (int r = rb; r < re; r += 4) {
+    float a0[4] = {0.f, 0.f, 0.f, 0.f}, a1[4] = {0.f, 0.f, 0.f, 0.f};
+    const float4* w0 = reinterpret_cast<const float4*>(W + (size_t)min(r + 0, re - 1) * ldw);
+    const float4* w1 = reinterpret_cast<const float4*>(W + (size_t)min(r + 1, re - 1) * ldw);
+    const float4* w2 = reinterpret_cast<const float4*>(W + (size_t)min(r + 2, re - 1) * ldw);
+    const float4* w3 = reinterpret_cast<const float4*>(W + (size_t)min(r + 3, re - 1) * ldw);
+#pragma unroll 2
+    for (int k = lane; k < K4; k += 32) {
+      const float4 xa = *reinterpret_cast<const float4*>(x0 + 4 * k), xb = *reinterpret_cast<const float4*>(x1 + 4 * k);
+      const float4 wv[4] = {__ldg(w0 + k), __ldg(w1 + k), __ldg(w2 + k), __ldg(w3 + k)};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        a0[i] = fmaf(wv[i].x, xa.x, a0[i]); a0[i] = fmaf(wv[i].y, xa.y, a0[i]); a0[i] = fmaf(wv[i].z, xa.z, a0[i]); a0[i] = fmaf(wv[i].w, xa.w, a0[i]);
+        a1[i] = fmaf(wv[i].x, xb.x, a1[i]); a1[i] = fmaf(wv[i].y, xb.y, a1[i]); a1[i] = fmaf(wv[i].z, xb.z, a1[i]); a1[i] = fmaf(wv[i].w, xb.w, a1[i]);
+      }
     }
-    acc = (a0 + a1) + (a2 + a3);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float y0 = warp_sum(a0[i]), y1 = warp_sum(a1[i]);
+      if (lane == 0 && r + i < re) { y[r + i - ybase] = y0; y[ys + r + i - ybase] = y1; }
+    }
   }
-  if (kh == 1) red[o] = acc;
-  __syncthreads();
-  if (kh == 0 && r < nr && b < nb) { out.r = r0 + r; out.b = b0 + b; out.v = acc + red[o]; out.valid = true; }
-  return out;
+  __syncwarp();
+}
+
+// value -> the same shared-memory word of all CTAs of the cluster (DSMEM broadcast)
+__device__ __forceinline__ void st_cluster_all(float* p, float v) {
+  const uint32_t a = tc::smem_u32(p);
+#pragma unroll
+  for (uint32_t r = 0; r < D2_CLUSTER; ++r) asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(tc::mapa(a, r)), "f"(v) : "memory");
 }
 
 // ------------------------------------------------------------------------------------------
@@ -100,7 +93,7 @@ __device__ __forceinline__ SmallOut small_gemm(const float* __restrict__ W, int 
 //   [0, 3*48K)            TMA stage ring (also scratch for the CUDA-core phases, which never overlap it)
 //   part[128][68] f32     split-K partial accumulator (read by cluster peers)
 //   c_att[8][64], c_dec[8][64] f32   cell states of this CTA's 8 hidden units
-//   attention constants   conv_t[2*31*32] | dense[A*32] | v[A]
+//   attention constants   conv_t[2*32*32] (taps padded to 32) | dense[A*32] | v[A]
 //   wq[8][A] f32          query-layer columns of this CTA's 8 attention-LSTM units (resident for the whole launch)
 //   h_s[8][64] f32        this frame's new hidden values, staged for packed 16-byte stores and the query partials
 //   barriers, tmem slot
@@ -121,7 +114,7 @@ struct Smem {
 
 __host__ __device__ __forceinline__ int d2_parts(int B, int grid) { return (B * 4 <= grid) ? 4 : ((B * 2 <= grid) ? 2 : 1); }
 __host__ __device__ __forceinline__ int pre_wlen(int L, int S) { return ((((L + S - 1) / S) + 7) & ~7) + 32; }
-__host__ __device__ __forceinline__ size_t pre_floats(int L, int S) { return 2 * (size_t)pre_wlen(L, S) + 6 * 8 * 36; }
+__host__ __device__ __forceinline__ size_t pre_floats(int L, int S) { return 2 * (size_t)pre_wlen(L, S) + 6 * 8 * 36 + 4; }
 
 __device__ __forceinline__ Smem carve(uint8_t* base, const D2Dims& d, int pre_f) {
   Smem s;
@@ -130,7 +123,7 @@ __device__ __forceinline__ Smem carve(uint8_t* base, const D2Dims& d, int pre_f)
   s.part = reinterpret_cast<float*>(p);  p += TG_M * TG_PART_LD * 4;
   s.c_att = reinterpret_cast<float*>(p); p += 8 * D2_BP * 4;
   s.c_dec = reinterpret_cast<float*>(p); p += 8 * D2_BP * 4;
-  s.conv_t = reinterpret_cast<float*>(p); p += 2 * D2_LOC_K * D2_LOC_F * 4;
+  s.conv_t = reinterpret_cast<float*>(p); p += 2 * D2_LOC_KP * D2_LOC_F * 4;
   s.dense = reinterpret_cast<float*>(p); p += d.A * D2_LOC_F * 4;
   s.v = reinterpret_cast<float*>(p);     p += d.A * 4;
   s.wq = reinterpret_cast<float*>(p);    p += 8 * d.A * 4;
@@ -252,7 +245,7 @@ __device__ __forceinline__ void query_partial(const float* h_s, const float* wq_
   float acc[8][4];
 #pragma unroll
   for (int j = 0; j < 8; ++j) { acc[j][0] = 0.f; acc[j][1] = 0.f; acc[j][2] = 0.f; acc[j][3] = 0.f; }
-#pragma unroll
+#pragma unroll 2
   for (int uu = 0; uu < 8; ++uu) {
     const float4 w4 = *reinterpret_cast<const float4*>(wq_s + uu * A + a4);
     const float4 ha = *reinterpret_cast<const float4*>(h_s + uu * D2_BP + b0);
@@ -297,8 +290,12 @@ __device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2
   float* wp = sm.pre;
   float* wc = wp + wlen;
   float* fsw = wc + wlen + pw * (8 * 36);
+  int* next_tile = reinterpret_cast<int*>(wc + wlen + 6 * 8 * 36);   // tiles are handed out dynamically: the six warps do not
+  if (ptid == 0) *next_tile = 0;                                      // share the four schedulers evenly (warps 0/1 mostly sleep)
   const float* wprev = s.w_prev + ((size_t)cur * D2_BP + b) * L;
   const float* wcum = s.w_cum + ((size_t)cur * D2_BP + b) * L;
+  const bool timing = blockIdx.x == 0 && ptid == 0 && s.prof;
+  const long long tm0 = timing ? clock64() : 0;
 #pragma unroll 1
   for (int i = ptid; i < ntile * 8 + 32; i += 192) {
     const int l = l0 + i - 15;
@@ -307,32 +304,42 @@ __device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2
     wc[i] = in ? ld_cg(wcum + l) : 0.f;
   }
   asm volatile("bar.sync 1, 192;" ::: "memory");
+  const long long tm1 = timing ? clock64() : 0;
   float* out = s.accpm + (size_t)blockIdx.x * Lc * A;
   const int a4 = lane * 4;
   const bool lane_on = a4 < A;
   const int ac = lane_on ? a4 : 0;
 #pragma unroll 1
-  for (int tl = pw; tl < ntile; tl += 6) {
+  for (;;) {
+    int tl = 0;
+    if (lane == 0) tl = atomicAdd(next_tile, 1);
+    tl = __shfl_sync(0xffffffffu, tl, 0);
+    if (tl >= ntile) break;
     const int lt = tl * 8;
     float4 pm4[8];
 #pragma unroll
     for (int p = 0; p < 8; ++p)
       pm4[p] = __ldg(reinterpret_cast<const float4*>(io.pmem + ((size_t)b * L + l0 + min(lt + p, nl - 1)) * A + ac));
-    float xw[40], xc[40];
-#pragma unroll
-    for (int i = 0; i < 10; ++i) {
-      const float4 u4 = *reinterpret_cast<const float4*>(wp + lt + 4 * i), c4 = *reinterpret_cast<const float4*>(wc + lt + 4 * i);
-      xw[4 * i] = u4.x; xw[4 * i + 1] = u4.y; xw[4 * i + 2] = u4.z; xw[4 * i + 3] = u4.w;
-      xc[4 * i] = c4.x; xc[4 * i + 1] = c4.y; xc[4 * i + 2] = c4.z; xc[4 * i + 3] = c4.w;
-    }
+    // Loops below are kept compact on purpose: the instruction cache (L0 ~6 KB, L1.5 32 KB) does not hold long unrolled
+    // bodies, and six warps streaming through straight-line code starve on instruction fetch.
     float acc[8];
 #pragma unroll
     for (int p = 0; p < 8; ++p) acc[p] = 0.f;
+#pragma unroll 1
+    for (int jb = 0; jb < D2_LOC_KP / 8; ++jb) {   // 8 taps per pass over a 16-sample window of each input channel
+      float xw[16], xc[16];
 #pragma unroll
-    for (int j = 0; j < D2_LOC_K; ++j) {
-      const float w0 = sm.conv_t[j * D2_LOC_F + lane], w1 = sm.conv_t[(D2_LOC_K + j) * D2_LOC_F + lane];
+      for (int i = 0; i < 4; ++i) {
+        const float4 u4 = *reinterpret_cast<const float4*>(wp + lt + 8 * jb + 4 * i), c4 = *reinterpret_cast<const float4*>(wc + lt + 8 * jb + 4 * i);
+        xw[4 * i] = u4.x; xw[4 * i + 1] = u4.y; xw[4 * i + 2] = u4.z; xw[4 * i + 3] = u4.w;
+        xc[4 * i] = c4.x; xc[4 * i + 1] = c4.y; xc[4 * i + 2] = c4.z; xc[4 * i + 3] = c4.w;
+      }
 #pragma unroll
-      for (int p = 0; p < 8; ++p) { acc[p] = fmaf(w0, xw[p + j], acc[p]); acc[p] = fmaf(w1, xc[p + j], acc[p]); }
+      for (int i = 0; i < 8; ++i) {
+        const float w0 = sm.conv_t[(8 * jb + i) * D2_LOC_F + lane], w1 = sm.conv_t[(D2_LOC_KP + 8 * jb + i) * D2_LOC_F + lane];
+#pragma unroll
+        for (int p = 0; p < 8; ++p) { acc[p] = fmaf(w0, xw[p + i], acc[p]); acc[p] = fmaf(w1, xc[p + i], acc[p]); }
+      }
     }
 #pragma unroll
     for (int p = 0; p < 8; ++p) fsw[p * 36 + lane] = acc[p];
@@ -340,7 +347,7 @@ __device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2
     float o[8][4];
 #pragma unroll
     for (int p = 0; p < 8; ++p) { o[p][0] = 0.f; o[p][1] = 0.f; o[p][2] = 0.f; o[p][3] = 0.f; }
-#pragma unroll 2
+#pragma unroll 1
     for (int f4 = 0; f4 < D2_LOC_F / 4; ++f4) {
       float4 fv[8];
 #pragma unroll
@@ -363,6 +370,7 @@ __device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2
             make_float4(o[p][0] + pm4[p].x, o[p][1] + pm4[p].y, o[p][2] + pm4[p].z, o[p][3] + pm4[p].w);
     __syncwarp();
   }
+  if (timing) { s.prof[7] += (unsigned long long)(tm1 - tm0); s.prof[15] += (unsigned long long)(clock64() - tm1); }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -460,8 +468,8 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
 #pragma unroll 1
         for (int j = 0; j < D2_LOC_K; ++j) {
           const float a0 = wp[lw + j], a1 = wc[lw + j];
-          const float4* w0 = reinterpret_cast<const float4*>(sm.conv_t + (0 * D2_LOC_K + j) * D2_LOC_F + fg * 8);
-          const float4* w1 = reinterpret_cast<const float4*>(sm.conv_t + (1 * D2_LOC_K + j) * D2_LOC_F + fg * 8);
+          const float4* w0 = reinterpret_cast<const float4*>(sm.conv_t + (0 * D2_LOC_KP + j) * D2_LOC_F + fg * 8);
+          const float4* w1 = reinterpret_cast<const float4*>(sm.conv_t + (1 * D2_LOC_KP + j) * D2_LOC_F + fg * 8);
           const float4 p0 = w0[0], p1 = w0[1], r0 = w1[0], r1 = w1[1];
           acc[0] = fmaf(p0.x, a0, acc[0]); acc[1] = fmaf(p0.y, a0, acc[1]); acc[2] = fmaf(p0.z, a0, acc[2]); acc[3] = fmaf(p0.w, a0, acc[3]);
           acc[4] = fmaf(p1.x, a0, acc[4]); acc[5] = fmaf(p1.y, a0, acc[5]); acc[6] = fmaf(p1.z, a0, acc[6]); acc[7] = fmaf(p1.w, a0, acc[7]);
@@ -625,9 +633,94 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
 }
 
 // ------------------------------------------------------------------------------------------
-enum { PH_ATT_LSTM = 0, PH_ATTN, PH_DEC_LSTM, PH_PROJ, PH_PRE1, PH_PRE2, PH_COUNT };
-// profiling slot of each phase (slot 1 = query partials + the barrier of the attention-LSTM phase)
-__device__ __constant__ int kPhaseSlot[PH_COUNT] = {1, 2, 3, 4, 5, 6};
+// ------------------------------------------------------------------------------------------
+// Output phase, cluster-local: cluster c owns utterances 2c and 2c+1 and runs, without a grid barrier in between,
+//   mel / gate projection + stop bookkeeping   (model/decoder.py:103-109, model/tacotron2.py:311-322)
+//   prenet layer 1, prenet layer 2 on the emitted frame (model/tacotron2.py:85-92,324-325)      [autoregressive only]
+// Each CTA computes a quarter of every layer's rows for both utterances and broadcasts its results to the peers'
+// shared memory (DSMEM); the layers are separated by cluster barriers only.  Weights stream from L2 (coalesced 16-byte loads).
+// Scratch (floats, in the idle TMA ring): x[2][KprojP] | mel[2][MP] | p1[2][P] | out[8 warps][2][8] | y[2][64]
+__device__ void output_phase(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, float* scratch, uint32_t rank,
+                             int cluster, int tg_, int nxt, long long* prof_last) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NW = D2_THREADS / 32;
+  const int B = d.B, M = d.M, P = d.P, KP = d.KprojP, MP = (M + 1 + 3) & ~3;
+  float* xs = scratch;
+  float* mel_s = xs + 2 * KP;
+  float* p1_s = mel_s + 2 * MP;
+  float* out_s = p1_s + 2 * P;
+  float* y_s = out_s + NW * 2 * 8;   // [2][64] row sums of the layer in flight
+  const int b0 = 2 * cluster;
+  const bool any = b0 < B;
+  const int j = lane & 1, b = b0 + j;   // epilogues: lane = (row of this warp's block, utterance)
+  if (any) {
+#pragma unroll 1
+    for (int i = tid; i < 2 * (KP >> 2); i += D2_THREADS) {
+      const int jj = i / (KP >> 2), k = i - jj * (KP >> 2);
+      reinterpret_cast<float4*>(xs)[i] = (b0 + jj < B) ? __ldcg(reinterpret_cast<const float4*>(s.projin + (size_t)(b0 + jj) * KP) + k)
+                                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    __syncthreads();
+    const int rows_per = (M + 1 + D2_CLUSTER - 1) / D2_CLUSTER, r0 = (int)rank * rows_per, nr = max(0, min(rows_per, M + 1 - r0));
+    const int rpw = (nr + NW - 1) / NW, rb = r0 + warp * rpw, re = min(r0 + nr, rb + rpw);
+    rows_dot2(w.Wproj, KP, KP >> 2, rb, re, xs, xs + KP, y_s, r0, 64);
+    const int r = rb + (lane >> 1);
+    if (r < re && b < B) {
+      const float v = y_s[j * 64 + r - r0] + __ldg(w.bproj + r);
+      if (r < M) {
+        io.mels[((size_t)b * io.Tmax + tg_) * M + r] = v;
+        if (!io.teacher_forcing) st_cluster_all(mel_s + j * MP + r, v);
+      } else {
+        io.gates[(size_t)b * io.Tmax + tg_] = v;
+        if (io.stop_enabled) {  // model/tacotron2.py:319-320
+          if (v < 0.0f) s.done[b] = 1;
+          if (v >= 0.0f) s.lengths[b] += 1;
+        }
+      }
+    }
+  }
+  if (io.teacher_forcing) return;
+  ATT_MARK(4);
+  tc::cluster_sync();
+  const float pscale = 1.0f / (1.0f - d.p_prenet);
+  const int rq = P / D2_CLUSTER, pr0 = (int)rank * rq;
+  const int rpw = (rq + NW - 1) / NW, rb = pr0 + warp * rpw, re = min(pr0 + rq, rb + rpw);
+  const int r = rb + (lane >> 1);
+  if (any) {
+    rows_dot2(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y_s, pr0, 64);
+    if (r < re && b < B) {
+      const size_t kidx = (((size_t)(tg_ + 1) * 2 + 0) * B + b) * P + r;
+      const bool keep = io.prenet_keep ? (io.prenet_keep[kidx] != 0) : rng_keep(io.seed, kidx, d.p_prenet);
+      const float v = y_s[j * 64 + r - pr0];
+      st_cluster_all(p1_s + j * P + r, (v > 0.f && keep) ? v * pscale : 0.f);
+    }
+  }
+  ATT_MARK(5);
+  tc::cluster_sync();
+  if (any) {
+    const long long pa = (long long)D2_BP * d.KattP;
+    __nv_bfloat16* xa = s.xatt + (size_t)nxt * 2 * pa;   // next frame's attention-LSTM input, prenet columns
+    const bool vec = rpw == 8 && (d.KattP & 7) == 0;
+    rows_dot2(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y_s, pr0, 64);
+    if (r < re && b < B) {
+      const size_t kidx = (((size_t)(tg_ + 1) * 2 + 1) * B + b) * P + r;
+      const bool keep = io.prenet_keep ? (io.prenet_keep[kidx] != 0) : rng_keep(io.seed, kidx, d.p_prenet);
+      float v = y_s[j * 64 + r - pr0];
+      v = (v > 0.f && keep) ? v * pscale : 0.f;
+      if (vec) out_s[(warp * 2 + j) * 8 + (r - rb)] = v;
+      else store_split(xa, pa, d.KattP, b, r, v);
+    }
+    if (vec) {
+      __syncwarp();
+      if (lane < 4 && b0 + (lane >> 1) < B)
+        store_plane8(xa + (lane & 1) * pa + (size_t)(b0 + (lane >> 1)) * d.KattP + rb, out_s + (warp * 2 + (lane >> 1)) * 8, lane & 1, true);
+    }
+  }
+}
+
+enum { PH_ATT_LSTM = 0, PH_ATTN, PH_DEC_LSTM, PH_OUT, PH_COUNT };
+// profiling slot of each phase (slot 1 = query partials + the barrier of the attention-LSTM phase; the output phase marks
+// 4 = projection, 5 = prenet layer 1, 6 = prenet layer 2 + barrier; with teacher forcing 4 = projection + barrier)
+__device__ __constant__ int kPhaseSlot[PH_COUNT] = {1, 2, 3, 6};
 
 __global__ void __launch_bounds__(D2_THREADS, 1)
 decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weights w, D2State s, D2IO io) {
@@ -648,7 +741,10 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
     tc::prefetch_tmap(&maps.x_att_rest); tc::prefetch_tmap(&maps.x_dec); tc::prefetch_tmap(&maps.tf_pre);
   }
 #pragma unroll 1
-  for (int i = tid; i < 2 * D2_LOC_K * D2_LOC_F; i += D2_THREADS) sm.conv_t[i] = w.loc_conv_t[i];
+  for (int i = tid; i < 2 * D2_LOC_KP * D2_LOC_F; i += D2_THREADS) {   // taps padded 31 -> 32 with a zero tap
+    const int f = i % D2_LOC_F, j = (i / D2_LOC_F) % D2_LOC_KP, c = i / (D2_LOC_F * D2_LOC_KP);
+    sm.conv_t[i] = j < D2_LOC_K ? w.loc_conv_t[(c * D2_LOC_K + j) * D2_LOC_F + f] : 0.f;
+  }
 #pragma unroll 1
   for (int i = tid; i < d.A * D2_LOC_F; i += D2_THREADS) sm.dense[i] = w.loc_dense[i];
 #pragma unroll 1
@@ -675,7 +771,7 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
   const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
   const float pscale = 1.0f / (1.0f - d.p_prenet);
   // history mode (training): the mel/gate projection is off the recurrence and runs as one bulk GEMM after this kernel
-  const int nphase = io.teacher_forcing ? (io.hist ? PH_DEC_LSTM + 1 : PH_PROJ + 1) : PH_COUNT;
+  const int nphase = (io.teacher_forcing && io.hist) ? PH_DEC_LSTM + 1 : PH_COUNT;
   int frames = 0;
   bool alive = true, fail = false, stop = false;
 
@@ -725,42 +821,13 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
         attention_phase(d, s, io, sm, scratch, att_active, att_b, att_part, S, cur, nxt, tg_, &prof_last);
         wrote_x = true;
       } else {
-        // ---- small dense phases: query (model/attention.py:52), mel/gate projection (model/decoder.py:103-109),
-        //      prenet layers on the emitted frame (model/tacotron2.py:85-92,324-325)
-        const float* Wm; const float* xin; int ldw, rows, ldx, K;
-        if (ph == PH_PROJ) { Wm = w.Wproj; ldw = d.KprojP; rows = d.M + 1; xin = s.projin;   ldx = d.KprojP; K = d.KprojP; }
-        else if (ph == PH_PRE1) { Wm = w.W1;    ldw = d.M;      rows = d.P;     xin = s.mel_cur;  ldx = d.M;      K = d.M; }
-        else                    { Wm = w.W2;    ldw = d.P;      rows = d.P;     xin = s.p1;       ldx = d.P;      K = d.P; }
-        const SmallOut o = small_gemm(Wm, ldw, rows, xin, ldx, B, K, scratch);
-        if (o.valid) {
-          const int r = o.r, b = o.b;
-          float v = o.v;
-          if (ph == PH_PROJ) {
-            v += __ldg(w.bproj + r);
-            if (r < d.M) {
-              io.mels[((size_t)b * io.Tmax + tg_) * d.M + r] = v;
-              s.mel_cur[(size_t)b * d.M + r] = v;
-            } else {
-              io.gates[(size_t)b * io.Tmax + tg_] = v;
-              if (io.stop_enabled) {  // model/tacotron2.py:319-320
-                if (v < 0.0f) s.done[b] = 1;
-                if (v >= 0.0f) s.lengths[b] += 1;
-              }
-            }
-          } else {
-            const int layer = ph == PH_PRE1 ? 0 : 1;
-            const size_t kidx = (((size_t)(tg_ + 1) * 2 + layer) * B + b) * d.P + r;
-            const bool keep = io.prenet_keep ? (io.prenet_keep[kidx] != 0) : rng_keep(io.seed, kidx, d.p_prenet);
-            v = (v > 0.f && keep) ? v * pscale : 0.f;
-            if (layer == 0) s.p1[(size_t)b * d.P + r] = v;
-            else { store_split(s.xatt + (size_t)nxt * 2 * pa, pa, d.KattP, b, r, v); wrote_x = true; }
-          }
-        }
-        if (ph == PH_PROJ) frames = t + 1;
+        output_phase(d, w, s, io, scratch, rank, tile, tg_, nxt, &prof_last);
+        wrote_x = !io.teacher_forcing;
+        frames = t + 1;
       }
       if (!(alive = bar.sync(fail, wrote_x))) break;
-      prof_mark(kPhaseSlot[ph]);
-      if (ph == PH_PROJ && !io.teacher_forcing) {
+      prof_mark((ph == PH_OUT && io.teacher_forcing) ? 4 : kPhaseSlot[ph]);
+      if (ph == PH_OUT && !io.teacher_forcing) {
         if (io.stop_enabled) {  // model/tacotron2.py:321-322: leave once every utterance has fired its stop gate
           int mine = 1;
 #pragma unroll 1
@@ -769,7 +836,7 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
         }
         if (t + 1 >= io.n_steps) stop = true;  // the last frame's prenet output is never used
       }
-      if (ph == PH_PRE2 && io.debug_barrier) {  // measures the bare cost of one grid barrier (slot 7)
+      if (ph == PH_OUT && io.debug_barrier) {  // measures the bare cost of one grid barrier (slot 7)
         if (!(alive = bar.sync(fail, false))) break;
         prof_mark(7);
       }
@@ -798,7 +865,7 @@ size_t att_scratch_floats(const D2Dims& d, int S) {
 int d2_att_parts(int B) { return d2_parts(B, 128); }
 
 size_t d2_smem_bytes(const D2Dims& d) {
-  return 1024 + (size_t)D2_STAGES * TG_STAGE_BYTES + TG_M * TG_PART_LD * 4 + 2 * 8 * D2_BP * 4 + 2 * D2_LOC_K * D2_LOC_F * 4 +
+  return 1024 + (size_t)D2_STAGES * TG_STAGE_BYTES + TG_M * TG_PART_LD * 4 + 2 * 8 * D2_BP * 4 + 2 * D2_LOC_KP * D2_LOC_F * 4 +
          (size_t)d.A * D2_LOC_F * 4 + d.A * 4 + 8 * d.A * 4 + 8 * D2_BP * 4 + (2 * D2_STAGES + 2) * 8 + 64;
 }
 
@@ -823,7 +890,9 @@ int d2_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO&
   const int S = d2_parts(d.B, grid);
   const size_t ring = (size_t)D2_STAGES * TG_STAGE_BYTES;
   T2_REQUIRE(att_scratch_floats(d, S) * 4 <= ring, T2_ERR_UNSUPPORTED, "decoder: L=%d too long for the attention scratch", d.L);
-  T2_REQUIRE(((size_t)(((d.M + 1 + 15) / 16) + 8) * (d.KprojP + 4) + 128) * 4 <= ring, T2_ERR_UNSUPPORTED, "decoder: projection staging");
+  T2_REQUIRE(((size_t)2 * d.KprojP + 2 * (d.M + 4) + 2 * d.P + 128 + 128) * 4 <= ring && d.P % (4 * D2_CLUSTER) == 0 && d.KprojP % 4 == 0 &&
+                 d.P / D2_CLUSTER <= 64 && (d.M + 1 + D2_CLUSTER - 1) / D2_CLUSTER <= 64 && d.P <= 16 * D2_CLUSTER * (D2_THREADS / 32),
+             T2_ERR_UNSUPPORTED, "decoder: output-phase staging");
   size_t smem = d2_smem_bytes(d);
   T2_REQUIRE(smem <= 227 * 1024, T2_ERR_UNSUPPORTED, "decoder: %zu B shared memory", smem);
   D2IO io = io_in;
