@@ -14,7 +14,8 @@ struct DBParams {
 __device__ __forceinline__ bool dx_tile(tg::Pipe& pipe, const BSmem& sm, const CUtensorMap* wmap, const CUtensorMap* dgmap, int ktile,
                                         int npb, uint32_t rank, float* dx /*[K][BP]*/) {
   tg::XSrc xs{dgmap, 0, dgmap, 0, npb};
-  const bool ok = tg::gemm(pipe, wmap, ktile * TG_M, npb, xs, (int)rank, npb, D2_CLUSTER, 0u);
+  // transposed weights stream through L2 evict-first (see d2_launch): the per-frame working set of the attention backward stays resident
+  const bool ok = tg::gemm(pipe, wmap, ktile * TG_M, npb, xs, (int)rank, npb, D2_CLUSTER, 0u, 1);
   tg::accum_to_smem(pipe, 0u, sm.part);
   tc::cluster_sync();
   // CTA `rank` reduces rows [32*rank, 32*rank+32) of the tile over the four partials

@@ -74,6 +74,7 @@ struct D2IO {
   int teacher_forcing, hidden_dropout, stop_enabled;
   int debug_barrier;  // adds one empty grid barrier per frame and times it (profiling only)
   int precompute;     // set by d2_launch: shared memory allows the location conv + dense to run beside the attention-LSTM GEMM
+  int w_policy_att, w_policy_dec;  // set by d2_launch: L2 eviction priority of the LSTM weight tiles (0 default, 1 evict-first, 2 evict-last)
   int hist;           // 1: state buffers are indexed by frame (slot t / t+1) instead of parity -- the training tape
   unsigned long long seed;
 };

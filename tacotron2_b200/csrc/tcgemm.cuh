@@ -60,15 +60,19 @@ __device__ __forceinline__ void pipe_init(Pipe& p, uint64_t* bars, uint8_t* stag
 // `side` runs on warps 2..7 (192 threads, named barrier 1 is theirs) while warps 0/1 stream and issue the GEMM: work that does not
 // depend on this GEMM's result and needs no part of the stage ring.
 struct NoSide { __device__ __forceinline__ void operator()() const {} };
+// w_policy: L2 eviction priority of the W tiles: 0 = default, 1 = evict-first (pure stream), 2 = evict-last (keep resident)
 template <class Side>
 __device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row0, int w_nkb, const XSrc& xs, int kb_begin, int kb_end,
-                                     int kb_stride, uint32_t d_col, Side side) {
+                                     int kb_stride, uint32_t d_col, Side side, int w_policy = 0) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   bool ok = true;
   const uint32_t stage_tx = (uint32_t)(p.npass == 3 ? TG_STAGE_BYTES : TG_W_TILE + TG_X_TILE);
   if (warp == 0 && lane == 0) {
     // ---------------- TMA producer
     asm volatile("fence.proxy.async;" ::: "memory");  // operands written by generic stores in an earlier phase
+    // The weight stream (tens of MB per frame, each byte used once per frame by one SM) must not push the small per-frame
+    // working set (attention memory, processed memory, partial sums) out of L2: evict-first.
+    const uint64_t wpol = w_policy == 2 ? tc::l2_policy_evict_last() : tc::l2_policy_evict_first();
     for (int kb = kb_begin; kb < kb_end; kb += kb_stride) {
       if (!tc::mbar_wait(p.empty + p.p_stage, p.p_phase ^ 1)) { ok = false; break; }
       uint8_t* st = p.stages + (size_t)p.p_stage * TG_STAGE_BYTES;
@@ -77,7 +81,8 @@ __device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row
       const CUtensorMap* xm = first ? xs.map0 : xs.map1;
       const int xk = (first ? kb : kb - xs.split) * TG_BK, xz = first ? xs.z0 : xs.z1;
       const int wc0 = w_nkb ? 0 : kb * TG_BK, wc1 = w_nkb ? ((w_row0 / TG_M) * w_nkb + kb) * TG_M : w_row0;
-      tc::tma_load_3d(st, wmap, p.full + p.p_stage, wc0, wc1, 0);                 // [hi|lo] 32 KB (hi only when box z = 1)
+      if (w_policy) tc::tma_load_3d_hint(st, wmap, p.full + p.p_stage, wc0, wc1, 0, wpol);   // [hi|lo] 32 KB (hi only when box z = 1)
+      else tc::tma_load_3d(st, wmap, p.full + p.p_stage, wc0, wc1, 0);
       tc::tma_load_3d(st + 2 * TG_W_TILE, xm, p.full + p.p_stage, xk, 0, xz);      // [hi|lo] 16 KB
       if (++p.p_stage == p.nstages) { p.p_stage = 0; p.p_phase ^= 1; }
     }
@@ -119,8 +124,8 @@ __device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row
 }
 
 __device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row0, int w_nkb, const XSrc& xs, int kb_begin, int kb_end,
-                                     int kb_stride, uint32_t d_col) {
-  return gemm(p, wmap, w_row0, w_nkb, xs, kb_begin, kb_end, kb_stride, d_col, NoSide{});
+                                     int kb_stride, uint32_t d_col, int w_policy = 0) {
+  return gemm(p, wmap, w_row0, w_nkb, xs, kb_begin, kb_end, kb_stride, d_col, NoSide{}, w_policy);
 }
 
 // TMEM accumulator columns [d_col, d_col+64) -> this CTA's partial buffer part[128][TG_PART_LD] (shared memory).
