@@ -164,9 +164,9 @@ def train_bench(dev, rank, world, steps, warmup=2):
         from tacotron2_b200 import _lib
         cyc = (ctypes.c_ulonglong * 16)()
         _lib.check(_lib.load().t2_debug_phase_cycles(model._ctx, cyc))
-        names = ["input_grad_gemms", "attention_bwd_tail", "lstm_pointwise", "att_stage_conv", "att_ctx_dot", "att_softmax_dense_ds",
-                 "att_df_dWd", "att_halo_dWc_dwcat"]
-        out["decoder_bwd_phase_us_per_frame"] = {n: round(cyc[8 + i] / 1965.0 / TRAIN_T, 2) for i, n in enumerate(names)}
+        names = ["input_grad_gemms", "attention_bwd_tail", "pointwise_dec_and_barrier", "att_stage_conv", "att_ctx_dot", "att_softmax_dense_ds",
+                 "att_df_dWd", "att_halo_dWc_dwcat", "pointwise_dq_stage", "pointwise_query_bwd", "pointwise_att"]
+        out["decoder_bwd_phase_us_per_frame"] = {n: round(cyc[i] / 1965.0 / TRAIN_T, 2) for i, n in enumerate(names)}
     except Exception as e:  # noqa: BLE001
         out["decoder_bwd_phase_us_per_frame"] = str(e)
     if sync is not None:

@@ -113,17 +113,28 @@ __device__ __forceinline__ void lstm_pointwise_bwd(const PwArgs& a, int H, int B
   const int u = unit0 + ul;
   const size_t gs = (size_t)H * D2_BP;
   float dgv[4][2];
+  // tape and gradient rows of both utterances of this thread: 8-byte loads; the tape is read once -> streaming (evict-first)
+  const size_t o2 = (size_t)u * D2_BP + 2 * bp;
+  const float2 zero2 = make_float2(0.f, 0.f);
+  const bool any = 2 * bp < B;
+  const float2 si2 = any ? __ldcs(reinterpret_cast<const float2*>(a.sav + o2)) : zero2;
+  const float2 sf2 = any ? __ldcs(reinterpret_cast<const float2*>(a.sav + gs + o2)) : zero2;
+  const float2 tg2 = any ? __ldcs(reinterpret_cast<const float2*>(a.sav + 2 * gs + o2)) : zero2;
+  const float2 so2 = any ? __ldcs(reinterpret_cast<const float2*>(a.sav + 3 * gs + o2)) : zero2;
+  const float2 c2 = any ? __ldcs(reinterpret_cast<const float2*>(a.sav + 4 * gs + o2)) : zero2;
+  const float2 cp2 = (any && a.cprev) ? __ldcg(reinterpret_cast<const float2*>(a.cprev + o2)) : zero2;   // read again as c of the next iteration
+  const float2 d02 = (any && a.dh0) ? __ldcg(reinterpret_cast<const float2*>(a.dh0 + (size_t)(a.row0 + u) * D2_BP + 2 * bp)) : zero2;
+  const float2 d12 = (any && a.dh1) ? __ldcg(reinterpret_cast<const float2*>(a.dh1 + (size_t)(a.row1 + u) * D2_BP + 2 * bp)) : zero2;
 #pragma unroll
   for (int j = 0; j < 2; ++j) {
     const int b = 2 * bp + j;
     float di = 0.f, df = 0.f, dg_ = 0.f, do_ = 0.f;
     if (b < B) {
-      const size_t o = (size_t)u * D2_BP + b;
-      const float si = a.sav[o], sf = a.sav[gs + o], tg = a.sav[2 * gs + o], so = a.sav[3 * gs + o], c = a.sav[4 * gs + o];
-      const float cp = a.cprev ? a.cprev[o] : 0.f;
+      const float si = j ? si2.y : si2.x, sf = j ? sf2.y : sf2.x, tg = j ? tg2.y : tg2.x, so = j ? so2.y : so2.x, c = j ? c2.y : c2.x;
+      const float cp = j ? cp2.y : cp2.x;
       float dh = dh_extra2 ? dh_extra2[j] : 0.f;
-      if (a.dh0) dh += ld_cg(a.dh0 + (size_t)(a.row0 + u) * D2_BP + b);
-      if (a.dh1) dh += ld_cg(a.dh1 + (size_t)(a.row1 + u) * D2_BP + b);
+      dh += j ? d02.y : d02.x;
+      dh += j ? d12.y : d12.x;
       if (a.dh_rm) dh += ld_cg(a.dh_rm + (size_t)b * a.ld_rm + a.col_rm + u);
       if (a.hidden_dropout) {  // nn.Dropout(0.1) on h (model/decoder.py:75,101): same draw as the forward
         const bool k = a.keep ? (a.keep[(size_t)b * H + u] != 0) : rng_keep(a.seed, a.rng_base + (unsigned long long)b * H + u, 0.1f);
@@ -147,8 +158,10 @@ __device__ __forceinline__ void lstm_pointwise_bwd(const PwArgs& a, int H, int B
     tc::split_bf16(dgv[g][0], h0, l0);
     tc::split_bf16(dgv[g][1], h1, l1);
     const size_t ro = (size_t)(g * H + u) * a.ldT + a.tcol + 2 * bp;
-    *reinterpret_cast<__nv_bfloat162*>(a.dgT + ro) = __halves2bfloat162(h0, h1);
-    *reinterpret_cast<__nv_bfloat162*>(a.dgT + (size_t)4 * H * a.ldT + ro) = __halves2bfloat162(l0, l1);
+    // consumed only by the bulk weight-gradient GEMMs after the kernel: streaming stores
+    const __nv_bfloat162 hv = __halves2bfloat162(h0, h1), lv = __halves2bfloat162(l0, l1);
+    __stcs(reinterpret_cast<unsigned*>(a.dgT + ro), *reinterpret_cast<const unsigned*>(&hv));
+    __stcs(reinterpret_cast<unsigned*>(a.dgT + (size_t)4 * H * a.ldT + ro), *reinterpret_cast<const unsigned*>(&lv));
     stg[(2 * bp) * 33 + g * 8 + ul] = dgv[g][0];
     stg[(2 * bp + 1) * 33 + g * 8 + ul] = dgv[g][1];
   }

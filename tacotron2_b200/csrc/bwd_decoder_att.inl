@@ -230,7 +230,7 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
       float s = 0.f;
 #pragma unroll
       for (int w8 = 0; w8 < D2_THREADS / 32; ++w8) s += dqw[w8 * A + a];
-      wk.dq[(((size_t)t * S + part) * D2_BP + b) * A + a] = s;
+      wk.dq[(((size_t)t * S + part) * A + a) * D2_BP + b] = s;   // [t][part][a][b]: utterance-minor, the layout phase P stages
     }
 
     ABW_MARK(5);

@@ -7,7 +7,7 @@ struct DBParams {
   DBWeights w;
   DBTape tp;
   DBWork wk;
-  unsigned long long* prof;   // [8] or null: cycles of CTA 0 in G / A / P
+  unsigned long long* prof;   // [16] or null: cycles of CTA 0 (0 G, 1 A tail, 2 P decoder cell + barrier, 3..7 inside A, 8..10 inside P)
 };
 
 // one 128-row tile of an input-gradient GEMM: dx[k0 + r][b] = sum_p WT[k0 + r][p] dg[b][p]
@@ -104,10 +104,13 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
     lstm_pointwise_bwd(a, H, B, unit0, pbase, sm.dc_dec, stg, nullptr, bias_dec);
   };
   auto pw_att = [&](int t, bool have_next) {   // attention LSTMCell of frame t (its h also feeds the query and the decoder cell)
-    // d query summed over the attention parts, transposed to [a][b].  All loads of a chunk are issued before any use
-    // (a one-load-per-iteration loop pays the full L2 latency 32 times and dominated this phase).
+    // d query [a][b] summed over the attention parts (the parts write it utterance-minor, so it is staged as it lies: 16-byte
+    // loads and stores, no transposition).  The query-weight columns are requested first so both latencies overlap, and all
+    // loads of a chunk are issued before any use (a one-load-per-iteration loop pays the full L2 latency every time).
+#pragma unroll 1
+    for (int i = tid; i < d.A * 8; i += D2_THREADS) wq_s[i] = __ldg(p.w.Wq + (size_t)(i >> 3) * H + unit0 + (i & 7));
     {
-      const int n4 = d.A * B / 4;                  // float4 elements of the (B, A) block; rows b >= B are never read
+      const int n4 = d.A * D2_BP / 4;              // float4 elements of one part's (A, 64) block; columns b >= B are stale, never used
       const size_t pstride = (size_t)D2_BP * d.A;  // floats between parts
       const float* src = wk.dq + (size_t)t * S * pstride;
 #pragma unroll 1
@@ -131,17 +134,12 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           const int i = i0 + k * D2_THREADS + tid;
-          if (i < n4) {
-            const int b = (i * 4) / d.A, a_ = (i * 4) - b * d.A;
-            dq_s[(a_ + 0) * D2_BP + b] = v[k].x; dq_s[(a_ + 1) * D2_BP + b] = v[k].y;
-            dq_s[(a_ + 2) * D2_BP + b] = v[k].z; dq_s[(a_ + 3) * D2_BP + b] = v[k].w;
-          }
+          if (i < n4) *reinterpret_cast<float4*>(dq_s + (size_t)i * 4) = v[k];
         }
       }
     }
-#pragma unroll 1
-    for (int i = tid; i < d.A * 8; i += D2_THREADS) wq_s[i] = __ldg(p.w.Wq + (size_t)(i >> 3) * H + unit0 + (i & 7));
     __syncthreads();
+    prof_mark(8);
     float ex[2] = {0.f, 0.f};
     {
       const int ul = warp, bp = lane;
@@ -154,6 +152,7 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
       if (2 * bp >= B) ex[0] = 0.f;        // utterance slots >= B hold stale scratch
       if (2 * bp + 1 >= B) ex[1] = 0.f;
     }
+    prof_mark(9);
     PwArgs a{};
     a.sav = tp.sav_att + (size_t)t * 5 * H * D2_BP;
     a.cprev = t > 0 ? tp.sav_att + ((size_t)(t - 1) * 5 + 4) * H * D2_BP : nullptr;
@@ -163,6 +162,7 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
     a.hidden_dropout = tp.hidden_dropout != 0; a.seed = tp.seed; a.rng_base = (1ull << 40) + (unsigned long long)t * B * H;
     a.dg = wk.dg_att; a.dgT = wk.dgT_att; a.ldT = (long long)T * D2_BP; a.tcol = (long long)t * D2_BP;
     lstm_pointwise_bwd(a, H, B, unit0, pbase, sm.dc_att, stg, ex, bias_att);
+    prof_mark(10);
   };
 
   // prologue: decoder cell of the last frame

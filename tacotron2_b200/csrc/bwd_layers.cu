@@ -148,7 +148,7 @@ __global__ void dq_sumT_kernel(const float* __restrict__ dq, int T, int S, int A
     const int b = (int)(tb % D2_BP), t = (int)(tb / D2_BP);
     float s = 0.f;
     if (b < B)
-      for (int p = 0; p < S; ++p) s += dq[(((size_t)t * S + p) * D2_BP + b) * A + a];
+      for (int p = 0; p < S; ++p) s += dq[(((size_t)t * S + p) * A + a) * D2_BP + b];
     __nv_bfloat16 hi, lo;
     tc::split_bf16(s, hi, lo);
     out[i] = hi; out[n + i] = lo;

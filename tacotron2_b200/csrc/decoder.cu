@@ -208,7 +208,7 @@ __device__ __forceinline__ void lstm_tail(const float* part, uint32_t rank, int 
     const size_t o = (size_t)u * D2_BP + 2 * bp, gs = (size_t)H * D2_BP;
     if (2 * bp + 1 < B) {
 #pragma unroll
-      for (int g = 0; g < 5; ++g) *reinterpret_cast<float2*>(sav + g * gs + o) = make_float2(sv[g][0], sv[g][1]);
+      for (int g = 0; g < 5; ++g) __stcs(reinterpret_cast<float2*>(sav + g * gs + o), make_float2(sv[g][0], sv[g][1]));   // write-once tape
     } else if (2 * bp < B) {
 #pragma unroll
       for (int g = 0; g < 5; ++g) sav[g * gs + o] = sv[g][0];

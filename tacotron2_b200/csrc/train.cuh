@@ -61,7 +61,7 @@ struct DBWork {
   float* dx_dec;            // [2 parity][KdecT][BP]
   float* dpre;              // [T][BP][P]     d/d prenet output
   float* dctx_tot;          // [T][BP][EF]    total d/d ctx_t (for the bulk memory gradient)
-  float* dq;                // [T][S][BP][A]  per-part partial d/d query
+  float* dq;                // [T][S][A][BP]  per-part partial d/d query (utterance-minor)
   float* dpm;               // [B][L][A]      accumulated d/d processed memory
   float* dconv;             // [2 parity][2 ch][BP][L]   d/d (w_{t-1}, cum_{t-1}) from the location conv
   float* gcum;              // [BP][L]        running d/d cum

@@ -391,7 +391,7 @@ int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const uns
     RC(tc_make_tmap_bf16(&maps.dg_dec, dg_dec, 3, dims, sb, box));
   }
   T2_CHECK_CUDA(cudaMemsetAsync(c->prof_buf, 0, 16 * sizeof(unsigned long long), st));
-  RC(db_launch(d, T, c->KattT, c->KdecT, w, t, k, maps, c->prof_buf + 8, st));
+  RC(db_launch(d, T, c->KattT, c->KdecT, w, t, k, maps, c->prof_buf, st));
 
   // ---- small attention weights, biases
   RC(partial_sum_launch(small_partial, 128, nsmall, small_sum, st));
