@@ -41,6 +41,7 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
   const int ldd = A + 4;
   const uint32_t my_rank = tc::cluster_ctarank();
   const uint32_t base_rank = my_rank - (uint32_t)part;
+  const float* xloc = tp.xloc ? tp.xloc + ((size_t)t * 128 + blockIdx.x) * Lc * A : nullptr;   // this CTA's slice of frame t
 
   if (active) {
     // ---- stage: q_t, wcat of this frame (w_{t-1}, cum_{t-1}) with halo, total d ctx_t, w_t slice
@@ -67,8 +68,13 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
     for (int i = tid; i < nl; i += D2_THREADS) w_s[i] = wcur[l0 + i];
     __syncthreads();
 
-    // ---- recompute the location conv features of this slice (as the forward)
-    {
+    // ---- location conv features of this slice: from the forward's tape when it has them, else recomputed (as the forward)
+    if (tp.floc) {
+      const float4* fsrc = reinterpret_cast<const float4*>(tp.floc + ((size_t)t * 128 + blockIdx.x) * Lc * D2_LOC_F);
+#pragma unroll 1
+      for (int i = tid; i < nl * (D2_LOC_F / 4); i += D2_THREADS)
+        *reinterpret_cast<float4*>(fs + (size_t)(i >> 3) * 36 + (i & 7) * 4) = __ldcs(fsrc + i);
+    } else {
       const int nchunk = (nl + 31) >> 5;
 #pragma unroll 1
       for (int task = warp; task < nchunk * 4; task += D2_THREADS / 32) {
@@ -180,7 +186,8 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
 #pragma unroll
         for (int l = 0; l < 4; ++l) {
           const int lp = min(lt + l, nl - 1);
-          pm4[l] = __ldg(reinterpret_cast<const float4*>(tp.pmem + ((size_t)b * L + l0 + lp) * A + ac));
+          pm4[l] = xloc ? __ldcs(reinterpret_cast<const float4*>(xloc + (size_t)lp * A + ac))   // taped f Wd^T + pm (read once)
+                        : __ldg(reinterpret_cast<const float4*>(tp.pmem + ((size_t)b * L + l0 + lp) * A + ac));
         }
         float ac4[4][4];
 #pragma unroll
@@ -188,7 +195,7 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
 #pragma unroll
           for (int a = 0; a < 4; ++a) ac4[l][a] = 0.f;
 #pragma unroll 2
-        for (int f4 = 0; f4 < D2_LOC_F / 4; ++f4) {
+        for (int f4 = 0; f4 < (xloc ? 0 : D2_LOC_F / 4); ++f4) {
           float4 fv[4];
 #pragma unroll
           for (int l = 0; l < 4; ++l) fv[l] = *reinterpret_cast<const float4*>(fs + (size_t)min(lt + l, nl - 1) * 36 + f4 * 4);

@@ -680,6 +680,7 @@ static int decode2_impl(t2_ctx* c, bool tf, const float* memory, const float* pm
     tfp = tape->tfp;
     s.xatt = tape->xatt; s.xdec = tape->xdec; s.q = tape->q; s.w_prev = tape->w_hist; s.w_cum = tape->wcum_hist;
     s.sav_att = tape->sav_att; s.sav_dec = tape->sav_dec;
+    s.accpm = tape->xloc; s.floc = tape->floc;
   }
   RC(fill_controls2(d, s, controls, B, st, nslots));
   D2IO io{};

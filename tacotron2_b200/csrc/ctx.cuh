@@ -89,6 +89,8 @@ struct DecTape {
   float* q;              // [T][BP][A]
   float* w_hist;         // [T+1][BP][L]
   float* wcum_hist;      // [T+1][BP][L]
+  float* xloc;           // [T][128 CTAs][ceil(L/S)][A]  location term + processed memory of every frame (pre-tanh energy argument - q)
+  float* floc;           // [T][128 CTAs][ceil(L/S)][32] location conv features of every frame
   char* zero_begin; size_t zero_bytes;   // region that must be zeroed before the forward
 };
 inline DecTape plan_dec_tape(const D2Dims& d, int B, int L, int T, Arena& ar) {
@@ -102,6 +104,11 @@ inline DecTape plan_dec_tape(const D2Dims& d, int B, int L, int T, Arena& ar) {
   t.zero_begin = ar.base ? ar.base + off0 : nullptr;
   t.zero_bytes = (size_t)(ar.off - off0);
   t.p1 = ar.take<float>((size_t)(T + 1) * B * d.P);
+  {
+    const int S = d2_att_parts(d.B), Lc = (L + S - 1) / S;
+    t.xloc = ar.take<float>((size_t)T * 128 * Lc * d.A);
+    t.floc = ar.take<float>((size_t)T * 128 * Lc * D2_LOC_F);
+  }
   t.sav_att = ar.take<float>((size_t)T * 5 * d.H * D2_BP);
   t.sav_dec = ar.take<float>((size_t)T * 5 * d.R * D2_BP);
   t.q = ar.take<float>((size_t)T * D2_BP * d.A);

@@ -282,7 +282,8 @@ __device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) 
 // conflict-free, the two 38-sample input windows in registers), the 8x32 feature tile goes through a per-warp shared-memory
 // tile into the location dense with lane = 4 attention dims, processed memory is added and the [8][A] block is written to
 // this CTA's private L2-resident scratch.
-__device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2IO& io, const Smem& sm, int b, int part, int S, int cur) {
+__device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2IO& io, const Smem& sm, int b, int part, int S, int cur,
+                                     int t_out) {
   const int ptid = threadIdx.x - 64, lane = threadIdx.x & 31, pw = (threadIdx.x >> 5) - 2;
   const int L = d.L, A = d.A;
   const int Lc = (L + S - 1) / S, l0 = part * Lc, l1 = min(L, l0 + Lc), nl = max(0, l1 - l0);
@@ -305,7 +306,9 @@ __device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2
   }
   asm volatile("bar.sync 1, 192;" ::: "memory");
   const long long tm1 = timing ? clock64() : 0;
-  float* out = s.accpm + (size_t)blockIdx.x * Lc * A;
+  const size_t slot = (io.hist ? (size_t)t_out * 128 : 0) + blockIdx.x;   // training keeps every frame (tape for the backward)
+  float* out = s.accpm + slot * Lc * A;
+  float* fout = s.floc ? s.floc + slot * Lc * D2_LOC_F : nullptr;
   const int a4 = lane * 4;
   const bool lane_on = a4 < A;
   const int ac = lane_on ? a4 : 0;
@@ -343,6 +346,10 @@ __device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2
     }
 #pragma unroll
     for (int p = 0; p < 8; ++p) fsw[p * 36 + lane] = acc[p];
+    if (fout) {
+#pragma unroll
+      for (int p = 0; p < 8; ++p) if (lt + p < nl) __stcs(fout + (size_t)(lt + p) * D2_LOC_F + lane, acc[p]);
+    }
     __syncwarp();
     float o[8][4];
 #pragma unroll
@@ -431,7 +438,7 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
       __syncthreads();
       ATT_MARK(10);
       const unsigned char* mk = io.mask + (size_t)b * L;
-      const float* xin = s.accpm + (size_t)blockIdx.x * Lc * A;
+      const float* xin = s.accpm + ((io.hist ? (size_t)t_out * 128 : 0) + blockIdx.x) * Lc * A;
       const int a4 = lane * 4;
       const bool lane_on = a4 < A;
       const int ac = lane_on ? a4 : 0;
@@ -794,7 +801,7 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
         bool gok;
         if (att && io.precompute && att_active) {
           gok = tg::gemm(pipe, &maps.w_att, tile * TG_M, nkb, xs, (int)rank, nkb, D2_CLUSTER, dcol,
-                         [&]() { attention_precompute(d, s, io, sm, att_b, att_part, S, cur); }, io.w_policy_att);
+                         [&]() { attention_precompute(d, s, io, sm, att_b, att_part, S, cur, tg_); }, io.w_policy_att);
         } else {
           gok = tg::gemm(pipe, att ? &maps.w_att : &maps.w_dec, tile * TG_M, nkb, xs, (int)rank, nkb, D2_CLUSTER, dcol,
                          att ? io.w_policy_att : io.w_policy_dec);
@@ -865,6 +872,10 @@ size_t att_scratch_floats(const D2Dims& d, int S) {
 
 int d2_att_parts(int B) { return d2_parts(B, 128); }
 
+bool d2_precompute_fits(const D2Dims& d) {
+  return d2_smem_bytes(d) + pre_floats(d.L, d2_parts(d.B, 128)) * 4 <= 227 * 1024 && !getenv("T2B200_NO_PRECOMPUTE");
+}
+
 size_t d2_smem_bytes(const D2Dims& d) {
   return 1024 + (size_t)D2_STAGES * TG_STAGE_BYTES + TG_M * TG_PART_LD * 4 + 2 * 8 * D2_BP * 4 + 2 * D2_LOC_KP * D2_LOC_F * 4 +
          (size_t)d.A * D2_LOC_F * 4 + d.A * 4 + 8 * d.A * 4 + 8 * D2_BP * 4 + (2 * D2_STAGES + 2) * 8 + 64;
@@ -901,7 +912,7 @@ int d2_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO&
   // with an evict-first hint so that they do not push the per-frame working set (attention memory, processed memory,
   // location terms, query partials, small weights: ~50 MB) out of L2.  Measured: 63.8 -> 56.6 us/frame at C2.
   io.w_policy_att = io.w_policy_dec = getenv("T2B200_NO_EVICT_FIRST") ? 0 : 1;
-  io.precompute = (s.accpm && smem + pre_floats(d.L, S) * 4 <= 227 * 1024 && !getenv("T2B200_NO_PRECOMPUTE")) ? 1 : 0;
+  io.precompute = (s.accpm && d2_precompute_fits(d)) ? 1 : 0;
   if (io.precompute) smem += pre_floats(d.L, S) * 4;
   T2_CHECK_CUDA(cudaFuncSetAttribute(decoder_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg{};

@@ -45,6 +45,8 @@ struct D2State {
   float* q;              // history mode only: [T][BP][A] processed query of every frame (training tape)
   float* accpm;          // [128 CTAs][ceil(L/S)][A] location term + processed memory of each CTA's attention slice (precomputed
                          // during the attention-LSTM GEMM of the same frame, consumed by the attention phase)
+  float* floc;           // history mode only: [T][128 CTAs][ceil(L/S)][32] location conv features (training tape), else null;
+                         // accpm then also holds every frame: [T][128 CTAs][ceil(L/S)][A]
   float* qpart;          // [BP][128 CTAs][A] per-CTA partial sums of the query projection (each CTA owns 8 units of att_h)
   float* w_prev;         // [2][BP][L]
   float* w_cum;          // [2][BP][L]
@@ -91,3 +93,4 @@ int d2_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO&
 int d2_max_clusters(int* out);
 size_t d2_smem_bytes(const D2Dims& d);
 int d2_att_parts(int B);   // S: CTAs per utterance in the attention phase
+bool d2_precompute_fits(const D2Dims& d);   // the location term is computed beside the attention-LSTM GEMM (and, in training, taped)

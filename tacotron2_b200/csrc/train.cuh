@@ -40,6 +40,8 @@ struct DBTape {             // written by the teacher-forced forward in history 
   const float* sav_att;     // [T][5][H][BP]  i,f,g,o (post-activation), c
   const float* sav_dec;     // [T][5][R][BP]
   const float* q;           // [T][BP][A]
+  const float* xloc;        // [T][128][ceil(L/S)][A]  taped location term + processed memory, or null (recompute)
+  const float* floc;        // [T][128][ceil(L/S)][32] taped location conv features, or null (recompute)
   const float* w_hist;      // [T+1][BP][L]  slot t+1 = w_t, slot 0 = zeros
   const float* wcum_hist;   // [T+1][BP][L]  slot t+1 = cum_t
   const float* memory;      // [B][L][EF]
