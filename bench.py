@@ -26,6 +26,10 @@ from tacotron2_b200 import synth  # noqa: E402
 
 B, L, T = 64, 200, 1000
 METRIC, UNIT = "mel_frames_per_sec_ar_decode", "frames/s"
+# dram__bytes_read.sum + dram__bytes_write.sum of decoder_persistent_kernel from the committed ncu --set full capture, per decoded
+# frame (the capture is a 200-frame launch of the same C2 batch; traffic is linear in the frame count)
+NCU_DRAM_BYTES_PER_FRAME = (13.777717e9 + 50.530048e6) / 200
+NCU_DRAM_SOURCE = "profiles/r01_v6_decoder_fwd_full_raw.csv (ncu --set full, 200-frame launch; per frame x frames)"
 WORKLOAD = "C2: vanilla-ljspeech-stop AR inference, batch 64 x 200 chars x 1000 frames, fp32, stop gate evaluated (never fires)"
 # kernels launched by one Tacotron2.forward (AR): embed 1, encoder conv 3, BiLSTM input proj 1, BiLSTM 1, memory split 1,
 # att_encoder 1, persistent decoder 1, mel split 1, postnet conv 5, finalize 1  (memsets / memcpys not counted)
@@ -167,6 +171,19 @@ def train_bench(dev, rank, world, steps, warmup=2):
         names = ["input_grad_gemms", "attention_bwd_tail", "pointwise_dec_and_barrier", "att_stage_conv", "att_ctx_dot", "att_softmax_dense_ds",
                  "att_df_dWd", "att_halo_dWc_dwcat", "pointwise_dq_stage", "pointwise_query_bwd", "pointwise_att"]
         out["decoder_bwd_phase_us_per_frame"] = {n: round(cyc[i] / 1965.0 / TRAIN_T, 2) for i, n in enumerate(names)}
+        # roofline of the step's dominant kernel (decoder_bwd_kernel): algorithmic bytes per frame for 64 utterances at C3 =
+        # transposed LSTM weights 71.3 MB + memory / processed memory 24.6 MB + gate tapes 5.2 MB + operand rows 2.4 MB +
+        # taped location term and conv features 6.1 MB; kernel time = CTA 0's cycle counters over all phases
+        try:
+            peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0))
+        except Exception:  # noqa: BLE001
+            peak = 6650.0
+        kernel_ms = sum(cyc[i] for i in range(len(names))) / 1965.0 / 1e3
+        alg = 109.6e6 * TRAIN_T
+        out["roofline"] = {"kernel": "decoder_bwd_kernel", "bound": "hbm", "achieved": alg / (kernel_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                           "frac": alg / (kernel_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_launch": alg, "kernel_ms": kernel_ms,
+                           "share_of_step": kernel_ms / (total / steps), "traffic": 55.707967e9 + 1.999782e9,
+                           "traffic_source": "profiles/r01_v6_decoder_bwd_full_raw.csv (ncu --set full, same launch shape)"}
     except Exception as e:  # noqa: BLE001
         out["decoder_bwd_phase_us_per_frame"] = str(e)
     if sync is not None:
@@ -345,7 +362,8 @@ def main():
         "gpu_launches": LAUNCHES_PER_STEP * args.steps,
         "clocks": clocks,
         "roofline": {"kernel": "decoder_persistent_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": "measured" if peaks else "fallback",
+                     "frac": achieved / peak, "traffic": NCU_DRAM_BYTES_PER_FRAME * T, "traffic_source": NCU_DRAM_SOURCE,
+                     "peak_source": "measured" if peaks else "fallback",
                      "algorithmic_bytes_per_launch": bytes_launch, "kernel_ms": dec_ms, "share_of_step": dec_ms / ms},
     }
     try:  # per-phase breakdown of the last decode launch (CTA 0's SM-clock cycles -> us per frame)
@@ -354,7 +372,9 @@ def main():
         cyc = (ctypes.c_ulonglong * 16)()
         _lib.check(_lib.load().t2_debug_phase_cycles(model._ctx, cyc))
         mhz = clocks.get("sm_mhz") or 1965
-        names = ["att_lstm_tail", "query_partials_barrier", "attention", "dec_lstm_tail", "proj", "prenet1", "prenet2", "extra_barrier", "att_lstm_gemm", "dec_lstm_gemm", "attn_conv", "attn_dense", "attn_csync", "attn_softmax", "attn_context"]
+        names = ["att_lstm_tail", "query_partials_barrier", "attention_ctx_store_barrier", "dec_lstm_tail_barrier", "proj", "prenet1", "prenet2_barrier",
+                 "precompute_stage(beside att gemm)", "att_lstm_gemm", "dec_lstm_gemm", "attn_query_sum", "attn_energies", "attn_csync", "attn_softmax",
+                 "attn_context", "precompute_tiles(beside att gemm)"]
         line["config"]["phase_us_per_frame"] = {n: round(cyc[i] / mhz / T, 2) for i, n in enumerate(names)}
     except Exception as e:  # noqa: BLE001
         line["config"]["phase_us_per_frame"] = str(e)
