@@ -48,7 +48,7 @@ struct BSmem {
   float* dc_dec;
   float* conv_t;      // [2][31][32]
   float* dense;       // [32][A]   (f-major, as the forward)
-  float* dense_af;    // [A][33]   (a-major copy for d f = ds * Wd)
+  float* dense_af;    // [A][36]   (a-major copy for d f = ds * Wd: 16-byte rows over f)
   float* v;           // [A]
   uint64_t* bars;
   uint32_t* tmem_slot;
@@ -63,7 +63,7 @@ __device__ __forceinline__ BSmem carve(uint8_t* base, const D2Dims& d) {
   s.dc_dec = reinterpret_cast<float*>(p);  p += 8 * D2_BP * 4;
   s.conv_t = reinterpret_cast<float*>(p);  p += 2 * D2_LOC_K * D2_LOC_F * 4;
   s.dense = reinterpret_cast<float*>(p);   p += d.A * D2_LOC_F * 4;
-  s.dense_af = reinterpret_cast<float*>(p); p += d.A * 33 * 4;
+  s.dense_af = reinterpret_cast<float*>(p); p += d.A * 36 * 4;
   s.v = reinterpret_cast<float*>(p);       p += d.A * 4;
   s.bars = reinterpret_cast<uint64_t*>(p); p += (2 * D2_STAGES + 2) * 8;
   s.tmem_slot = reinterpret_cast<uint32_t*>(p);
@@ -72,7 +72,7 @@ __device__ __forceinline__ BSmem carve(uint8_t* base, const D2Dims& d) {
 
 size_t bsmem_bytes(const D2Dims& d) {
   return 1024 + (size_t)D2_STAGES * TG_STAGE_BYTES + TG_M * TG_PART_LD * 4 + 2 * 8 * D2_BP * 4 + 2 * D2_LOC_K * D2_LOC_F * 4 +
-         (size_t)d.A * D2_LOC_F * 4 + (size_t)d.A * 33 * 4 + d.A * 4 + (2 * D2_STAGES + 2) * 8 + 64;
+         (size_t)d.A * D2_LOC_F * 4 + (size_t)d.A * 36 * 4 + d.A * 4 + (2 * D2_STAGES + 2) * 8 + 64;
 }
 
 __device__ __forceinline__ float block_reduce_sum(float v, float* red) {

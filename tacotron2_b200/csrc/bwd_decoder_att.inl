@@ -11,10 +11,10 @@ struct AttAcc {           // per-thread accumulators that live for the whole utt
 };
 
 // scratch (floats): q[A] | wp[Lh4] | wc[Lh4] | fs[Lc][36] | dctx[EF] | ws[Lc4] | gw[Lc4] | de[Lc4] | red[64] | xch[8] |
-//                   dqw[8][A] | ds[Lc][A+4] | dfe[Lc+30][36]
+//                   dqw[8][A] | ds[Lc][A+4] | dfe[Lc+30][36] | gsm[2][31][Lc+30]
 __device__ __forceinline__ size_t att_bwd_scratch_floats(int L, int S, int A, int EF) {
   const int Lc = (L + S - 1) / S, Lh4 = (Lc + 30 + 3) & ~3, Lc4 = (Lc + 3) & ~3;
-  return (size_t)A + 2 * Lh4 + (size_t)Lc * 36 + EF + 3 * Lc4 + 64 + 8 + 8 * (size_t)A + (size_t)Lc * (A + 4) + (size_t)(Lc + 30) * 36;
+  return (size_t)A + 2 * Lh4 + (size_t)Lc * 36 + EF + 3 * Lc4 + 64 + 8 + 8 * (size_t)A + (size_t)Lc * (A + 4) + (size_t)(Lc + 30) * 36 + (size_t)(Lc + 30) * 64;
 }
 
 #define ABW_MARK(slot) do { if (blockIdx.x == 0 && threadIdx.x == 0 && prof) { const long long now_ = clock64(); prof[slot] += (unsigned long long)(now_ - *prof_last); *prof_last = now_; } } while (0)
@@ -38,6 +38,7 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
   float* dqw = xch + 8;
   float* ds = dqw + 8 * A;
   float* dfe = ds + (size_t)Lc * (A + 4);
+  float* gsm = dfe + (size_t)(Lc + 30) * 36;
   const int ldd = A + 4;
   const uint32_t my_rank = tc::cluster_ctarank();
   const uint32_t base_rank = my_rank - (uint32_t)part;
@@ -253,14 +254,25 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
         for (int l = 0; l < 4; ++l)
 #pragma unroll
           for (int f = 0; f < 4; ++f) o[l][f] = 0.f;
-#pragma unroll 4
-        for (int a = 0; a < A; ++a) {
-          const float w0 = sm.dense_af[a * 33 + fq], w1 = sm.dense_af[a * 33 + fq + 1], w2 = sm.dense_af[a * 33 + fq + 2],
-                      w3 = sm.dense_af[a * 33 + fq + 3];
+        // four attention dims per pass: 4 + 4 conflict-free 16-byte shared loads feed 64 FMAs (ds rows are 16-byte aligned:
+        // ldd = A + 4; the weights come from the a-major copy of location_dense, row stride 36)
+#pragma unroll 2
+        for (int a = 0; a < A; a += 4) {
+          float4 w4[4], x4[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) w4[i] = *reinterpret_cast<const float4*>(sm.dense_af + (size_t)(a + i) * 36 + fq);
+#pragma unroll
+          for (int l = 0; l < 4; ++l) x4[l] = *reinterpret_cast<const float4*>(ds + (size_t)min(lb + l, nl - 1) * ldd + a);
 #pragma unroll
           for (int l = 0; l < 4; ++l) {
-            const float x = ds[(size_t)min(lb + l, nl - 1) * ldd + a];
-            o[l][0] = fmaf(x, w0, o[l][0]); o[l][1] = fmaf(x, w1, o[l][1]); o[l][2] = fmaf(x, w2, o[l][2]); o[l][3] = fmaf(x, w3, o[l][3]);
+            o[l][0] = fmaf(x4[l].x, w4[0].x, o[l][0]); o[l][1] = fmaf(x4[l].x, w4[0].y, o[l][1]);
+            o[l][2] = fmaf(x4[l].x, w4[0].z, o[l][2]); o[l][3] = fmaf(x4[l].x, w4[0].w, o[l][3]);
+            o[l][0] = fmaf(x4[l].y, w4[1].x, o[l][0]); o[l][1] = fmaf(x4[l].y, w4[1].y, o[l][1]);
+            o[l][2] = fmaf(x4[l].y, w4[1].z, o[l][2]); o[l][3] = fmaf(x4[l].y, w4[1].w, o[l][3]);
+            o[l][0] = fmaf(x4[l].z, w4[2].x, o[l][0]); o[l][1] = fmaf(x4[l].z, w4[2].y, o[l][1]);
+            o[l][2] = fmaf(x4[l].z, w4[2].z, o[l][2]); o[l][3] = fmaf(x4[l].z, w4[2].w, o[l][3]);
+            o[l][0] = fmaf(x4[l].w, w4[3].x, o[l][0]); o[l][1] = fmaf(x4[l].w, w4[3].y, o[l][1]);
+            o[l][2] = fmaf(x4[l].w, w4[3].z, o[l][2]); o[l][3] = fmaf(x4[l].w, w4[3].w, o[l][3]);
           }
         }
 #pragma unroll
@@ -296,6 +308,7 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
   }
   ABW_MARK(6);
   tc::cluster_sync();   // every part's d f slice is in its shared memory
+  ABW_MARK(11);
   if (active) {
     // ---- halo rows of d f from the neighbouring parts (15 positions each side)
 #pragma unroll 1
@@ -312,6 +325,7 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
       *reinterpret_cast<float4*>(dfe + (size_t)row * 36 + f4) = v;
     }
     __syncthreads();
+    ABW_MARK(12);
     // ---- d location_conv[c][j][f] += sum_{l in slice} d f[l][f] * wcat[c][l + j - 15]
     {
       const int f4 = (tid & 7) * 4, cj0 = tid >> 3;
@@ -331,25 +345,43 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
         acc.wc[4 * h + 0] += o0; acc.wc[4 * h + 1] += o1; acc.wc[4 * h + 2] += o2; acc.wc[4 * h + 3] += o3;
       }
     }
-    // ---- d wcat[c][l'] = sum_j sum_f d f[l' - j + 15][f] Wc[c][j][f]  for the slice (warp task = (32 positions, channel))
+    ABW_MARK(13);
+    // ---- d wcat[c][l'] = sum_j sum_f d f[l' - j + 15][f] Wc[c][j][f]  for the slice, in two steps so that every d f row is
+    // read from shared memory once instead of 31 times (the direct form was shared-memory-bandwidth bound):
+    //   G[m][c][j] = d f[m] . Wc[c][j]   (thread = (row m incl. halo, channel c): row in registers, weights broadcast)
+    //   d wcat[c][l'] = sum_j G[l' - j + 30][c][j]
     {
-      const int nchunk = (nl + 31) >> 5;
+      const int nrow = nl + 30, c = tid >> 7, m = tid & 127, MR = Lc + 30;
+      __syncthreads();   // gsm aliases nothing live, but every warp must be done with the d f halo writes above
 #pragma unroll 1
-      for (int task = warp; task < nchunk * 2; task += D2_THREADS / 32) {
-        const int c = task & 1, li = (task >> 1) * 32 + lane;
-        const int lw = min(li, max(nl - 1, 0));
-        float o = 0.f;
-#pragma unroll 1
-        for (int j = 0; j < D2_LOC_K; ++j) {
-          const float4* fr = reinterpret_cast<const float4*>(dfe + (size_t)(lw - j + 30) * 36);
-          const float4* wr = reinterpret_cast<const float4*>(sm.conv_t + (c * D2_LOC_K + j) * D2_LOC_F);
+      for (int m0 = 0; m0 < nrow; m0 += 128) {
+        const int mm = m0 + m;
+        if (mm < nrow) {
+          float4 x[8];
 #pragma unroll
-          for (int f4 = 0; f4 < 8; ++f4) {
-            const float4 x = fr[f4], w = wr[f4];
-            o = fmaf(x.x, w.x, o); o = fmaf(x.y, w.y, o); o = fmaf(x.z, w.z, o); o = fmaf(x.w, w.w, o);
+          for (int f4 = 0; f4 < 8; ++f4) x[f4] = *reinterpret_cast<const float4*>(dfe + (size_t)mm * 36 + f4 * 4);
+          float* gout = gsm + (size_t)c * D2_LOC_K * MR + mm;   // [c][j][m]: lanes = consecutive rows -> conflict-free
+#pragma unroll 1
+          for (int j = 0; j < D2_LOC_K; ++j) {
+            const float4* wr = reinterpret_cast<const float4*>(sm.conv_t + (c * D2_LOC_K + j) * D2_LOC_F);
+            float o0 = 0.f, o1 = 0.f, o2 = 0.f, o3 = 0.f;
+#pragma unroll
+            for (int f4 = 0; f4 < 8; ++f4) {
+              const float4 w = wr[f4];
+              o0 = fmaf(x[f4].x, w.x, o0); o1 = fmaf(x[f4].y, w.y, o1); o2 = fmaf(x[f4].z, w.z, o2); o3 = fmaf(x[f4].w, w.w, o3);
+            }
+            gout[(size_t)j * MR] = (o0 + o1) + (o2 + o3);
           }
         }
-        if (li < nl) wk.dconv[((size_t)c * D2_BP + b) * L + l0 + li] = o;
+      }
+      __syncthreads();
+#pragma unroll 1
+      for (int i = tid; i < 2 * nl; i += D2_THREADS) {
+        const int cc = i / nl, li = i - cc * nl;
+        float o = 0.f;
+#pragma unroll 1
+        for (int j = 0; j < D2_LOC_K; ++j) o += gsm[((size_t)cc * D2_LOC_K + j) * MR + (li - j + 30)];
+        wk.dconv[((size_t)cc * D2_BP + b) * L + l0 + li] = o;
       }
     }
   }

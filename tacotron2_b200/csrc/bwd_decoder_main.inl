@@ -55,7 +55,7 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
   for (int i = tid; i < d.A * D2_LOC_F; i += D2_THREADS) {
     const float v = p.w.loc_dense[i];           // [f][a]
     sm.dense[i] = v;
-    sm.dense_af[(i % d.A) * 33 + i / d.A] = v;  // [a][f]
+    sm.dense_af[(i % d.A) * 36 + i / d.A] = v;  // [a][f]
   }
 #pragma unroll 1
   for (int i = tid; i < d.A; i += D2_THREADS) sm.v[i] = p.w.v[i];
@@ -251,7 +251,7 @@ size_t db_small_floats(const D2Dims& d) { return (size_t)d.A * 32 + 2 * D2_LOC_K
 
 static size_t att_bwd_scratch_floats_host(int L, int S, int A, int EF) {
   const int Lc = (L + S - 1) / S, Lh4 = (Lc + 30 + 3) & ~3, Lc4 = (Lc + 3) & ~3;
-  return (size_t)A + 2 * Lh4 + (size_t)Lc * 36 + EF + 3 * Lc4 + 64 + 8 + 8 * (size_t)A + (size_t)Lc * (A + 4) + (size_t)(Lc + 30) * 36;
+  return (size_t)A + 2 * Lh4 + (size_t)Lc * 36 + EF + 3 * Lc4 + 64 + 8 + 8 * (size_t)A + (size_t)Lc * (A + 4) + (size_t)(Lc + 30) * 36 + (size_t)(Lc + 30) * 64;
 }
 
 int db_launch(const D2Dims& d, int T, int KattT, int KdecT, const DBWeights& w, const DBTape& tp, const DBWork& wk, const DBMaps& maps,
