@@ -188,3 +188,57 @@ def test_rng_dropout_statistics():
     frac_zero = float((out == 0).float().mean())
     base_zero = float((ref == 0).float().mean())
     assert 0.45 <= (frac_zero - base_zero) / max(1e-6, 1 - base_zero) <= 0.62
+
+
+def test_c4_shape_vs_oracle():
+    """BASELINE config C4: speaker tokens + 5 controls + 768-d description embeddings (E = 640, K = 896 / 1669 / 1664), batch 32 x 200
+    characters, autoregressive: first 24 frames against the CPU oracle, stop decisions on a gate-shifted copy of the weights."""
+    args, B, L, T = synth.CONDITIONED, 32, 200, 24
+    b = synth.synth_batch(args, B, L, 8, seed=4321)
+    bc = _cuda(b)
+    masks = synth.synth_masks(args, B, L, T, seed=9)
+    for shift, scale in ((5.0, 1.0), (-35.35, -1000.0)):   # never stops / stops at varied frames
+        sd = synth.synth_state_dict(args, seed=0, gate_shift=shift, gate_scale=scale)
+        m = _model(args, sd)
+        kw = dict(speaker_id=bc["speaker_id"], controls=bc["controls"], description_embeddings=bc["description_embeddings"])
+        with torch.no_grad():
+            mels, post, gates, al = m(bc["chars_idx"], bc["chars_idx_len"], False, max_len_override=T, dropout_masks=masks, **kw)
+        want = O.tacotron2_forward(sd, args, b["chars_idx"], b["chars_idx_len"], False, speaker_id=b["speaker_id"], controls=b["controls"],
+                                   description_embeddings=b["description_embeddings"], max_len_override=T, masks=masks)
+        assert mels.shape == want[0].shape, (mels.shape, want[0].shape)   # same number of emitted frames = same stop step
+        assert _err(al, want[3]) <= ATT_TOL and _err(mels, want[0]) <= MEL_TOL and _err(post, want[1]) <= MEL_TOL
+        assert torch.equal(gates.cpu() == -1000.0, want[2] == -1000.0), "stop decisions differ"
+
+
+def test_c5_long_form():
+    """BASELINE config C5 (long-form stress): batch 16 x 600 characters.  fp32-parity arithmetic: first 12 frames against the CPU
+    oracle and the size-independent properties on the full 3000-frame run.  bf16 mode (single tensor-core pass, the mode C5 names):
+    stated looser tolerance on the same 12 frames (mel <= 5e-2, attention <= 5e-3) and the same properties at 3000 frames."""
+    args, B, L, T, TL = synth.VANILLA, 16, 600, 12, 3000
+    sd = synth.synth_state_dict(args, seed=0, gate_shift=5.0)
+    b = synth.synth_batch(args, B, L, 8, seed=77)
+    bc = _cuda(b)
+    masks = synth.synth_masks(args, B, L, TL, seed=3)
+    want = O.tacotron2_forward(sd, args, b["chars_idx"], b["chars_idx_len"], False, max_len_override=T, masks=masks)
+    pad = torch.arange(L, device=_dev())[None, :] >= bc["chars_idx_len"][:, None]
+    old = os.environ.get("T2B200_PRECISION")
+    try:
+        for mode, mel_tol, att_tol in (("fp32", MEL_TOL, ATT_TOL), ("bf16", 5e-2, 5e-3)):
+            os.environ["T2B200_PRECISION"] = mode
+            m = _model(args, sd)
+            with torch.no_grad():
+                mels, post, gates, al = m(bc["chars_idx"], bc["chars_idx_len"], False, max_len_override=T, dropout_masks=masks)
+                assert _err(al, want[3]) <= att_tol and _err(mels, want[0]) <= mel_tol and _err(post, want[1]) <= mel_tol, mode
+                mels2, post2, _, al2 = m(bc["chars_idx"], bc["chars_idx_len"], False, max_len_override=TL, dropout_masks=masks)
+                mels3, _, _, al3 = m(bc["chars_idx"], bc["chars_idx_len"], False, max_len_override=TL, dropout_masks=masks)
+            assert mels2.shape == (B, TL, 80) and al2.shape == (B, TL, L)
+            assert torch.equal(mels2, mels3) and torch.equal(al2, al3), "persistent kernel is not deterministic"
+            assert torch.equal(mels2[:, :T], mels), "prefix of the long run differs from the short run"
+            assert float((al2.sum(-1) - 1).abs().max()) <= 1e-5
+            assert float(al2.masked_select(pad[:, None, :].expand_as(al2)).abs().max()) == 0.0
+            assert torch.isfinite(mels2).all() and torch.isfinite(post2).all()
+    finally:
+        if old is None:
+            os.environ.pop("T2B200_PRECISION", None)
+        else:
+            os.environ["T2B200_PRECISION"] = old
