@@ -17,6 +17,7 @@ import sys
 import threading
 import time
 
+import numpy as np
 import torch
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -97,6 +98,35 @@ def oracle_sample(frames, threads):
 TRAIN_B, TRAIN_L, TRAIN_T = 64, 150, 800
 TRAIN_WORKLOAD = ("C3: vanilla-lj-hifi-stop (speaker tokens, 4 speakers) teacher-forced training step, batch 64/GPU x 150 chars x 800 frames, "
                   "fp32-parity arithmetic: forward + loss + backward (BPTT) + gradient all-reduce (N>1) + grad-clip 1.0 + Adam(1e-3, wd 1e-6)")
+
+
+def melspec_bench(dev, steps=5):
+    """Log-mel extraction for one C3-sized batch: 64 waveforms of 800 frames (204,800 samples each), resident in HBM.
+    Reported as frames/s and as achieved HBM traffic (waveform read once + log-mel written once) against the measured copy peak --
+    the kernel is FFT / shared-memory bound, the fraction says how far from the HBM floor it sits."""
+    from tacotron2_b200.melspec import TacotronMelSpectrogram
+    B, Tm = 64, 800
+    S = (Tm - 1) * 256
+    wav = torch.from_numpy(np.stack([synth.synth_wav(S, seed=i % 4) for i in range(4)])).repeat(B // 4, 1).to(dev)
+    lens = torch.full((B,), S, dtype=torch.int64, device=dev)
+    tr = TacotronMelSpectrogram().to(dev)
+    for _ in range(3):
+        out, n = tr.batch(wav, lens)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        out, n = tr.batch(wav, lens)
+    e1.record()
+    e1.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    frames = int(n.sum())
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0))
+    except Exception:  # noqa: BLE001
+        peak = 6650.0
+    gbs = (wav.numel() * 4 + frames * 80 * 4) / (ms * 1e-3) / 1e9
+    return {"workload": "64 waveforms x 204,800 samples -> 64 x 800 x 80 log-mel, inputs resident", "ms": ms, "frames_per_s": frames / (ms * 1e-3),
+            "achieved_gbs": gbs, "hbm_peak_gbs": peak, "frac_of_hbm": gbs / peak}
 
 
 def train_bench(dev, rank, world, steps, warmup=2):
@@ -380,6 +410,10 @@ def main():
         line["config"]["phase_us_per_frame"] = str(e)
     if train is not None:
         line["train"] = train
+    try:
+        line["melspec"] = melspec_bench(dev)
+    except Exception as e:  # noqa: BLE001
+        line["melspec"] = {"error": f"{type(e).__name__}: {e}"}
     if not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         if train is not None and "error" not in train:

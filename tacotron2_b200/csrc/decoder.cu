@@ -384,39 +384,46 @@ __device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2
 // Attention for batch element b, part `part` of `S` (the S CTAs of one b sit in the same cluster):
 // each part computes the energies of its L-slice, the slices are exchanged through DSMEM, every part
 // normalises the full row and reduces its slice of the context columns.
-// Scratch (floats, in the idle TMA ring): q[A] | qh[2A] | wp[Lc+32] | wc[Lc+32] | fs[Lc][36] | e_slice[Lc] |
-//                                         e_full[L] | red[64] | cred[4*cols]
+// Scratch (floats, in the idle TMA ring): q[A] | qh[8A] | wp[Lc+32] | wc[Lc+32] | fs[Lc][36] | e_slice[Lc] |
+//                                         e_full[L] | red[64] | cred[4*cols] | xs[Lc][A]
 #define ATT_MARK(slot) do { if (blockIdx.x == 0 && threadIdx.x == 0 && s.prof) { const long long now_ = clock64(); s.prof[slot] += (unsigned long long)(now_ - *prof_last); *prof_last = now_; } } while (0)
 __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& io, const Smem& sm, float* scratch, bool active,
-                                int b, int part, int S, int cur, int nxt, int t_out, long long* prof_last) {
+                                int b, int part, int S, int cur, int nxt, int t_out, uint32_t mbits, long long* prof_last) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int L = d.L, A = d.A, EF = d.EF;
   const int Lc = (L + S - 1) / S, l0 = part * Lc, l1 = min(L, l0 + Lc), nl = max(0, l1 - l0);
   float* q_s = scratch;
-  float* qh = q_s + A;                            // two half-sums of the per-CTA query partials
-  float* wp = qh + 2 * A;                         // previous / cumulative weights with a 15-tap halo
+  float* qh = q_s + A;                            // eight group sums of the per-CTA query partials
+  float* wp = qh + 8 * A;                         // previous / cumulative weights with a 15-tap halo
   float* wc = wp + ((Lc + 35) & ~3);
   float* fs = wc + ((Lc + 35) & ~3);            // [Lc][36] conv features (row stride 36: conflict-free float4 rows)
   float* e_slice = fs + (size_t)Lc * 36;
   float* e_full = e_slice + ((Lc + 3) & ~3);
   float* red = e_full + ((L + 3) & ~3);
   float* cred = scratch + (((red + 64) - scratch + 3) & ~3);
+  float* xs_s = cred + 4 * (size_t)((((EF + S - 1) / S) + 3) & ~3);   // [Lc][A] staged location term (precompute path)
   if (active) {
+    if (io.precompute) {  // all 16-byte chunks of this CTA's location term in flight at once, overlapped with the query sum below
+      const float* xin = s.accpm + ((io.hist ? (size_t)t_out * 128 : 0) + blockIdx.x) * Lc * A;
+#pragma unroll 1
+      for (int i = tid; i < nl * (A >> 2); i += D2_THREADS) cp_async16(xs_s + (size_t)i * 4, xin + (size_t)i * 4);
+      cp_async_commit();
+    }
     const float* wprev = s.w_prev + ((size_t)cur * D2_BP + b) * L;
     const float* wcum = s.w_cum + ((size_t)cur * D2_BP + b) * L;
-    if (tid < 2 * A) {  // processed query = sum of the 128 per-CTA partials, always in the same order (bit-deterministic)
-      const int a = tid < A ? tid : tid - A, half = tid < A ? 0 : 1;
-      const float* qp = s.qpart + ((size_t)b * 128 + half * 64) * A + a;
-      float acc = 0.f;
-#pragma unroll 1
-      for (int c0 = 0; c0 < 64; c0 += 16) {
-        float v[16];
+    {  // processed query = sum of the 128 per-CTA partials, always in the same order (bit-deterministic): eight groups of 16 CTAs,
+       // one round of sixteen independent 16-byte loads per thread, then the groups in order
+      const int a4 = lane * 4;
+      if (a4 < A) {
+        const float* qp = s.qpart + ((size_t)b * 128 + warp * 16) * A + a4;
+        float4 v[16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = ld_cg(qp + (size_t)(c0 + i) * A);
+        for (int i = 0; i < 16; ++i) v[i] = __ldcg(reinterpret_cast<const float4*>(qp + (size_t)i * A));
+        float4 acc = v[0];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) acc += v[i];
+        for (int i = 1; i < 16; ++i) { acc.x += v[i].x; acc.y += v[i].y; acc.z += v[i].z; acc.w += v[i].w; }
+        *reinterpret_cast<float4*>(qh + warp * A + a4) = acc;
       }
-      qh[tid] = acc;
     }
     if (!io.precompute) {
 #pragma unroll 1
@@ -429,36 +436,43 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
     }
     __syncthreads();
     if (tid < A) {
-      const float qv = qh[tid] + qh[A + tid];
+      float qv = qh[tid];
+#pragma unroll
+      for (int g = 1; g < D2_THREADS / 32; ++g) qv += qh[g * A + tid];
       q_s[tid] = qv;
       if (io.hist && part == 0) s.q[((size_t)t_out * D2_BP + b) * A + tid] = qv;   // training tape
     }
     if (io.precompute) {
-      // energies from the precomputed location term (attention_precompute): e[l] = sum_a v[a] tanh(q[a] + x[l][a])
+      // energies from the precomputed location term (attention_precompute): e[l] = sum_a v[a] tanh(q[a] + x[l][a]), read from
+      // the shared-memory copy; two positions per pass in a compact loop (an 8-position unrolled body does not fit the
+      // instruction cache and ran at 3-4 cycles per instruction)
+      cp_async_wait<0>();
       __syncthreads();
       ATT_MARK(10);
-      const unsigned char* mk = io.mask + (size_t)b * L;
-      const float* xin = s.accpm + ((io.hist ? (size_t)t_out * 128 : 0) + blockIdx.x) * Lc * A;
       const int a4 = lane * 4;
       const bool lane_on = a4 < A;
       const int ac = lane_on ? a4 : 0;
       const float4 q4 = *reinterpret_cast<const float4*>(q_s + ac);
       const float4 v4 = *reinterpret_cast<const float4*>(sm.v + ac);
-      const int ntile = (nl + 7) >> 3;
+      const unsigned char* mk = io.mask + (size_t)b * L;
+      constexpr int NW = D2_THREADS / 32;
 #pragma unroll 1
-      for (int tl = warp; tl < ntile; tl += D2_THREADS / 32) {
-        const int lt = tl * 8;
-        float4 x4[8];
-#pragma unroll
-        for (int l = 0; l < 8; ++l) x4[l] = __ldcg(reinterpret_cast<const float4*>(xin + (size_t)min(lt + l, nl - 1) * A + ac));
-#pragma unroll
-        for (int l = 0; l < 8; ++l) {
-          float e = v4.x * tanh_fast(q4.x + x4[l].x);
-          e = fmaf(v4.y, tanh_fast(q4.y + x4[l].y), e);
-          e = fmaf(v4.z, tanh_fast(q4.z + x4[l].z), e);
-          e = fmaf(v4.w, tanh_fast(q4.w + x4[l].w), e);
-          e = warp_sum(lane_on ? e : 0.f);
-          if (lane == 0 && lt + l < nl) e_slice[lt + l] = mk[l0 + lt + l] ? -INFINITY : e;  // masked_fill (model/attention.py:63)
+      for (int l = warp, k = 0; l < nl; l += 2 * NW, ++k) {
+        const int lb = l + NW;
+        const float4 xa = *reinterpret_cast<const float4*>(xs_s + (size_t)l * A + ac);
+        const float4 xb = *reinterpret_cast<const float4*>(xs_s + (size_t)min(lb, nl - 1) * A + ac);
+        float ea = v4.x * tanh_fast(q4.x + xa.x), eb = v4.x * tanh_fast(q4.x + xb.x);
+        ea = fmaf(v4.y, tanh_fast(q4.y + xa.y), ea); eb = fmaf(v4.y, tanh_fast(q4.y + xb.y), eb);
+        ea = fmaf(v4.z, tanh_fast(q4.z + xa.z), ea); eb = fmaf(v4.z, tanh_fast(q4.z + xb.z), eb);
+        ea = fmaf(v4.w, tanh_fast(q4.w + xa.w), ea); eb = fmaf(v4.w, tanh_fast(q4.w + xb.w), eb);
+        ea = warp_sum(lane_on ? ea : 0.f);
+        eb = warp_sum(lane_on ? eb : 0.f);
+        // masked_fill (model/attention.py:63): the mask bits of this warp's first 32 positions were read once at kernel start
+        const bool ma = 2 * k < 32 ? ((mbits >> (2 * k)) & 1u) != 0u : (mk[l0 + l] != 0);
+        const bool mb = 2 * k + 1 < 32 ? ((mbits >> (2 * k + 1)) & 1u) != 0u : (mk[l0 + min(lb, nl - 1)] != 0);
+        if (lane == 0) {
+          e_slice[l] = ma ? -INFINITY : ea;
+          if (lb < nl) e_slice[lb] = mb ? -INFINITY : eb;
         }
       }
     } else {
@@ -774,6 +788,13 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
   };
   const int att_b = blockIdx.x / S, att_part = blockIdx.x % S;
   const bool att_active = att_b < B;
+  uint32_t att_mbits = 0;   // padding-mask bits of the positions this warp owns in the energy step: bit j = position warp + 8 j
+  if (att_active) {
+    const int Lc_ = (d.L + S - 1) / S, l0_ = att_part * Lc_, nl_ = max(0, min(d.L, l0_ + Lc_) - l0_);
+    const int pos = (tid >> 5) + (D2_THREADS / 32) * (tid & 31);
+    const bool mk_ = pos < nl_ && io.mask[(size_t)att_b * d.L + l0_ + pos] != 0;
+    att_mbits = __ballot_sync(0xffffffffu, mk_);
+  }
   const int nkb_att = d.KattP / TG_BK, nkb_dec = d.KdecP / TG_BK;
   const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
   const float pscale = 1.0f / (1.0f - d.p_prenet);
@@ -826,7 +847,7 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
         wrote_x = true;
       } else if (ph == PH_ATTN) {
         // ---- location-sensitive attention (model/attention.py:54-67, model/decoder.py:90)
-        attention_phase(d, s, io, sm, scratch, att_active, att_b, att_part, S, cur, nxt, tg_, &prof_last);
+        attention_phase(d, s, io, sm, scratch, att_active, att_b, att_part, S, cur, nxt, tg_, att_mbits, &prof_last);
         wrote_x = true;
       } else {
         output_phase(d, w, s, io, scratch, rank, tile, tg_, nxt, &prof_last);
@@ -865,7 +886,8 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
 size_t att_scratch_floats(const D2Dims& d, int S) {
   const int Lc = (d.L + S - 1) / S;
   const int cols = (((d.EF + S - 1) / S) + 3) & ~3;
-  return 3 * (size_t)d.A + 2 * (size_t)((Lc + 35) & ~3) + (size_t)Lc * 36 + Lc + 4 + d.L + 4 + 64 + 8 + 4 * (size_t)cols;
+  return 9 * (size_t)d.A + 2 * (size_t)((Lc + 35) & ~3) + (size_t)Lc * 36 + Lc + 4 + d.L + 4 + 64 + 8 + 4 * (size_t)cols + 8 +
+         (size_t)Lc * d.A;
 }
 
 }  // namespace
