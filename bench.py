@@ -142,8 +142,9 @@ def train_bench(dev, rank, world, steps, warmup=2):
     sync = GradSync(model) if world > 1 else None
     batch = synth.synth_batch(a, TRAIN_B, TRAIN_L, TRAIN_T, seed=1234 + rank, ragged=False)
     host = {k: v.pin_memory() for k, v in batch.items()}
-    opt = torch.optim.Adam(model.parameters(), lr=1e-3, weight_decay=1e-6, fused=True)
+    from tacotron2_b200.optim import ClipAdam
     params = [p for p in model.parameters()]
+    opt = ClipAdam(params, lr=1e-3, weight_decay=1e-6, max_norm=1.0)   # model/tts_model.py:78-91 + run/train.py:239-240, 3 launches
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
     phase = [0.0, 0.0, 0.0, 0.0]
     loss_h = torch.empty((), pin_memory=True)
@@ -161,7 +162,6 @@ def train_bench(dev, rank, world, steps, warmup=2):
         if sync is not None:
             sync.finish()
         ev[3].record()
-        torch.nn.utils.clip_grad_norm_(params, 1.0, foreach=True)
         opt.step()
         ev[4].record()
         loss_h.copy_(loss.detach(), non_blocking=True)  # device -> host read of the step's result

@@ -160,6 +160,20 @@ int t2_loss_fwd_bwd(t2_ctx* ctx, const float* mels, const float* post, const flo
 int t2_finalize_bwd(t2_ctx* ctx, const float* d_mels, const float* d_post, const float* d_gates, const long long* lengths, int B, int T,
                     float* d_mels_raw, float* d_postnet_out, float* d_gates_raw, void* stream);
 
+/* Training-step shell: torch.nn.utils.clip_grad_norm_(params, max_norm) followed by
+ * torch.optim.Adam(lr, betas, eps, weight_decay).step() -- the optimizer contract of model/tts_model.py:78-91 (Adam, lr 1e-3,
+ * L2 weight decay 1e-6) with run/train.py:239-240 (gradient_clip_val 1.0) -- over a list of fp32 device tensors, three launches,
+ * no host synchronisation (the clip coefficient stays on the device).  params / grads / exp_avg / exp_avg_sq: host arrays of
+ * n_tensors device pointers; numel: host array.  step = 1 for the first update (bias correction).  max_norm <= 0 disables
+ * clipping.  table_cached != 0: the tensor count and sizes are the same as in the previous call on this workspace (skips the
+ * re-upload of the chunk table).  grad_norm_out: device float or NULL, receives the pre-clip global 2-norm.
+ * ws: t2_clip_adam_workspace_bytes(n_tensors, t2_clip_adam_chunks(n_tensors, numel)) bytes, kept by the caller across steps. */
+long long t2_clip_adam_chunks(int n_tensors, const long long* numel);
+long long t2_clip_adam_workspace_bytes(int n_tensors, long long total_chunks);
+int t2_clip_adam_step(int n_tensors, float* const* params, float* const* grads, float* const* exp_avg, float* const* exp_avg_sq,
+                      const long long* numel, float lr, float beta1, float beta2, float eps, float weight_decay, float max_norm,
+                      long long step, int table_cached, float* grad_norm_out, void* ws, long long ws_bytes, void* stream);
+
 /* Batched log-mel extraction: TacotronMelSpectrogram(n_mels, sample_rate)(wav) of datasets/tts_dataset.py:166-168,204
  * (implementation external to the reference: speech_utils, un-vendored; parameters as stated in
  * datasets/prosody_dataset.py:39-50,66-67 and run/say.py:161-171: n_fft 1024, win 1024, hop 256, center + reflect pad,

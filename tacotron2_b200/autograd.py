@@ -35,6 +35,22 @@ def _bucket(owner, lib, params: dict):
     return flat, views
 
 
+def _take_tape(owner, nbytes: int, dev):
+    """The decoder tape is several GB per 64-utterance chunk: keep the buffers on the model between steps instead of going
+    through the allocator every step.  A buffer is checked out by a forward and handed back by its backward."""
+    pool = owner.__dict__.setdefault("_tape_pool", [])
+    for i, t in enumerate(pool):
+        if t.device == dev and t.numel() >= nbytes:
+            return pool.pop(i)
+    return torch.empty(nbytes, dtype=torch.uint8, device=dev)
+
+
+def _give_tape(owner, tape):
+    pool = owner.__dict__.setdefault("_tape_pool", [])
+    if len(pool) < 8:
+        pool.append(tape)
+
+
 def _after_bucket(owner, flat, group, views):
     hook = getattr(owner, "_grad_bucket_hook", None)
     if hook is not None:  # data-parallel: async all-reduce of this bucket (parallel.py)
@@ -142,7 +158,7 @@ class DecodeTfFn(torch.autograd.Function):
         B, L, _ = memory.shape
         T, M = target.shape[1], target.shape[2]
         memory, pmem = memory.contiguous(), pmem.contiguous()
-        tape = torch.empty(lib.t2_decode_tape_bytes(owner._ctx, B, L, T), dtype=torch.uint8, device=dev)
+        tape = _take_tape(owner, lib.t2_decode_tape_bytes(owner._ctx, B, L, T), dev)
         ws = owner._train_workspace(lib, dev, B, L, T)
         mels, gates, aligns = torch.empty(B, T, M, device=dev), torch.empty(B, T, device=dev), torch.empty(B, T, L, device=dev)
         _lib.check(lib.t2_decode_tf_train_fwd(owner._ctx, P(memory), P(pmem), P(mask), P(ctrl), P(target), B, L, T, P(pk), P(ak), P(rk), seed,
@@ -169,6 +185,8 @@ class DecodeTfFn(torch.autograd.Function):
                                         P(d_mels), P(d_gates), P(ctx.tape), ctx.tape.numel(), P(d_memory), P(d_pmem), P(ws), ws.numel(),
                                         _stream()), "t2_decode_tf_bwd")
         _after_bucket(owner, flat, "decoder", views)
+        _give_tape(owner, ctx.tape)   # stream-ordered: the next forward's writes are enqueued behind this backward
+        ctx.tape = None
         return (None,) * 8 + (d_memory, d_pmem, *views)
 
 
