@@ -511,9 +511,10 @@ def main():
         cyc = (ctypes.c_ulonglong * 16)()
         _lib.check(_lib.load().t2_debug_phase_cycles(model._ctx, cyc))
         mhz = clocks.get("sm_mhz") or 1965
-        names = ["att_lstm_tail", "query_partials_barrier", "attention_ctx_store_barrier", "dec_lstm_tail_barrier", "proj", "prenet1", "prenet2_barrier",
-                 "precompute_stage(beside att gemm)", "att_lstm_gemm", "dec_lstm_gemm", "attn_query_sum", "attn_energies", "attn_csync", "attn_softmax",
-                 "attn_context", "precompute_tiles(beside att gemm)"]
+        names = ["att_lstm_tail", "query_partials_barrier", "attention_ctx_store_barrier", "dec_lstm_tail_barrier", "proj(beside att gemm)",
+                 "prenet1(beside att gemm)", "prenet2(beside att gemm)", "x_barrier_and_prenet_kblock_gemm", "att_lstm_gemm_with_output_stage_beside",
+                 "dec_lstm_gemm", "attn_query_sum", "attn_energies", "attn_csync", "attn_softmax", "attn_context",
+                 "location_precompute(beside dec gemm)"]
         line["config"]["phase_us_per_frame"] = {n: round(cyc[i] / mhz / T, 2) for i, n in enumerate(names)}
     except Exception as e:  # noqa: BLE001
         line["config"]["phase_us_per_frame"] = str(e)

@@ -12,35 +12,6 @@
 
 namespace {
 
-struct GridBar {
-  unsigned* ctr;
-  unsigned* abort_flag;
-  unsigned nblocks;
-  unsigned epoch;
-  __device__ bool sync(bool fail, bool wrote_x) {
-    if (wrote_x) asm volatile("fence.proxy.async;" ::: "memory");
-    __syncthreads();
-    __shared__ int ok_s;
-    if (threadIdx.x == 0) {
-      ++epoch;
-      if (fail) atomicExch(abort_flag, 1u);
-      __threadfence();
-      atomicAdd(ctr, 1u);
-      const unsigned target = epoch * nblocks;
-      long long spins = 0;
-      while (ld_acquire_u32(ctr) < target) {
-        if (++spins > (1ll << 24)) {
-          if (ld_acquire_u32(abort_flag) != 0u || spins > (1ll << 27)) { atomicExch(abort_flag, 1u); break; }
-        }
-      }
-      ok_s = (ld_acquire_u32(abort_flag) == 0u);
-      __threadfence();
-    }
-    __syncthreads();
-    return ok_s != 0;
-  }
-};
-
 struct BSmem {
   uint8_t* stages;    // TMA ring / phase scratch
   float* part;        // [128][68] split-K partial

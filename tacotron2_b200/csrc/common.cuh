@@ -61,6 +61,45 @@ __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
   return v;
 }
 
+// Software grid barrier of the persistent kernels (all CTAs co-resident: one CTA per SM, grid <= #SMs).  One counter: every CTA
+// adds 1 with release semantics and polls it with acquire loads until it reaches epoch * nblocks; bit 31 of the same word is the
+// abort flag, so leaving the barrier costs no second round trip to L2.
+// `fail` = this CTA hit a pipeline timeout: it raises the abort bit before arriving so every CTA leaves together.
+// `wrote_x`: this phase stored GEMM operands with ordinary (generic-proxy) stores; they must be ordered before the TMA
+// (async-proxy) reads of a later phase, hence the proxy fence on the writer side (the TMA producer thread issues the matching
+// fence before its first load).
+struct GridBar {
+  unsigned* ctr;
+  unsigned* abort_flag;   // host-visible copy of the abort state
+  unsigned nblocks;
+  unsigned epoch;
+  __device__ bool sync(bool fail, bool wrote_x) {
+    if (wrote_x) asm volatile("fence.proxy.async;" ::: "memory");
+    fail = __syncthreads_or(fail ? 1 : 0) != 0;   // a pipeline timeout seen by any role thread aborts the grid
+    __shared__ int ok_s;
+    if (threadIdx.x == 0) {
+      ++epoch;
+      if (fail) { atomicExch(abort_flag, 1u); atomicOr(ctr, 0x80000000u); }
+      // release: cumulative over the CTA's writes that the bar.sync above ordered before this thread
+      asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+      const unsigned target = epoch * nblocks;
+      unsigned v;
+      long long spins = 0;
+      while ((((v = ld_acquire_u32(ctr)) & 0x7fffffffu) < target) && !(v & 0x80000000u)) {
+        if (++spins > (1ll << 24)) {   // ~10 s: a peer died; never hang the GPU
+          atomicExch(abort_flag, 1u);
+          atomicOr(ctr, 0x80000000u);
+          v = 0x80000000u;
+          break;
+        }
+      }
+      ok_s = (v & 0x80000000u) == 0u;
+    }
+    __syncthreads();
+    return ok_s != 0;
+  }
+};
+
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
   unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gsrc) : "memory");

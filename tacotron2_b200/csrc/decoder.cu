@@ -14,39 +14,6 @@
 
 namespace {
 
-struct GridBar {
-  unsigned* ctr;
-  unsigned* abort_flag;
-  unsigned nblocks;
-  unsigned epoch;
-  // `fail` = this CTA hit a pipeline timeout: it raises the abort flag before arriving so every CTA leaves together.
-  // `wrote_x`: this phase stored GEMM operands with ordinary (generic-proxy) stores; they must be ordered before the
-  // TMA (async-proxy) reads of a later phase, hence the proxy fence on the writer side (the TMA producer thread
-  // issues the matching fence before its first load).
-  __device__ bool sync(bool fail, bool wrote_x) {
-    if (wrote_x) asm volatile("fence.proxy.async;" ::: "memory");
-    fail = __syncthreads_or(fail ? 1 : 0) != 0;   // a pipeline timeout seen by any role thread aborts the grid
-    __shared__ int ok_s;
-    if (threadIdx.x == 0) {
-      ++epoch;
-      if (fail) atomicExch(abort_flag, 1u);
-      __threadfence();
-      atomicAdd(ctr, 1u);
-      const unsigned target = epoch * nblocks;
-      long long spins = 0;
-      while (ld_acquire_u32(ctr) < target) {
-        if (++spins > (1ll << 24)) {
-          if (ld_acquire_u32(abort_flag) != 0u || spins > (1ll << 27)) { atomicExch(abort_flag, 1u); break; }
-        }
-      }
-      ok_s = (ld_acquire_u32(abort_flag) == 0u);
-      __threadfence();
-    }
-    __syncthreads();
-    return ok_s != 0;
-  }
-};
-
 // ------------------------------------------------------------------------------------------
 // Small dense layers of the output phase on CUDA cores: y_j[r] = sum_k W[r][k] x_j[k] for the two utterances (j = 0,1) a
 // cluster owns.  One warp per block of consecutive rows [rb, re), four rows in flight, lanes stride the row in 16-byte loads
@@ -81,6 +48,44 @@ __device__ __noinline__ void rows_dot2(const float* __restrict__ W, int ldw, int
   __syncwarp();
 }
 
+// Short-row variant (K4 <= 32 * NK float4 per row): NR rows and all their loads in flight at once, so a layer costs one or two
+// L2 round trips instead of one per group of four rows.
+template <int NR, int NK>
+__device__ __noinline__ void rows_short(const float* __restrict__ W, int ldw, int K4, int rb, int re, const float* x0, const float* x1, float* y,
+                                        int ybase, int ys) {
+  const int lane = threadIdx.x & 31;
+  float4 xa[NK], xb[NK];
+#pragma unroll
+  for (int k = 0; k < NK; ++k) {
+    const int kk = lane + 32 * k;
+    xa[k] = kk < K4 ? *reinterpret_cast<const float4*>(x0 + 4 * kk) : make_float4(0.f, 0.f, 0.f, 0.f);
+    xb[k] = kk < K4 ? *reinterpret_cast<const float4*>(x1 + 4 * kk) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+#pragma unroll 1
+  for (int r = rb; r < re; r += NR) {
+    float4 wv[NR][NK];
+#pragma unroll
+    for (int i = 0; i < NR; ++i)
+#pragma unroll
+      for (int k = 0; k < NK; ++k) {
+        const int kk = lane + 32 * k;
+        wv[i][k] = kk < K4 ? __ldg(reinterpret_cast<const float4*>(W + (size_t)min(r + i, re - 1) * ldw) + kk) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+    for (int i = 0; i < NR; ++i) {
+      float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+      for (int k = 0; k < NK; ++k) {
+        a0 = fmaf(wv[i][k].x, xa[k].x, a0); a0 = fmaf(wv[i][k].y, xa[k].y, a0); a0 = fmaf(wv[i][k].z, xa[k].z, a0); a0 = fmaf(wv[i][k].w, xa[k].w, a0);
+        a1 = fmaf(wv[i][k].x, xb[k].x, a1); a1 = fmaf(wv[i][k].y, xb[k].y, a1); a1 = fmaf(wv[i][k].z, xb[k].z, a1); a1 = fmaf(wv[i][k].w, xb[k].w, a1);
+      }
+      const float y0 = warp_sum(a0), y1 = warp_sum(a1);
+      if (lane == 0 && r + i < re) { y[r + i - ybase] = y0; y[ys + r + i - ybase] = y1; }
+    }
+  }
+  __syncwarp();
+}
+
 // value -> the same shared-memory word of all CTAs of the cluster (DSMEM broadcast)
 __device__ __forceinline__ void st_cluster_all(float* p, float v) {
   const uint32_t a = tc::smem_u32(p);
@@ -107,6 +112,7 @@ struct Smem {
   float* v;
   float* wq;
   float* h_s;
+  float* octx;       // [2][64] context half of the mel/gate projection of this cluster's two utterances (computed a phase early)
   float* pre;        // attention precompute scratch (only when io.precompute): wp | wc (with halo) | 6 per-warp conv tiles [8][36]
   uint64_t* bars;
   uint32_t* tmem_slot;
@@ -128,8 +134,9 @@ __device__ __forceinline__ Smem carve(uint8_t* base, const D2Dims& d, int pre_f)
   s.v = reinterpret_cast<float*>(p);     p += d.A * 4;
   s.wq = reinterpret_cast<float*>(p);    p += 8 * d.A * 4;
   s.h_s = reinterpret_cast<float*>(p);   p += 8 * D2_BP * 4;
+  s.octx = reinterpret_cast<float*>(p);  p += 2 * 64 * 4;
   s.pre = reinterpret_cast<float*>(p);   p += (size_t)pre_f * 4;
-  s.bars = reinterpret_cast<uint64_t*>(p); p += (2 * D2_STAGES + 2) * 8;
+  s.bars = reinterpret_cast<uint64_t*>(p); p += (2 * D2_STAGES + 4) * 8;   // ring full/empty, accumulator, 2 side-warp rendezvous
   s.tmem_slot = reinterpret_cast<uint32_t*>(p);
   return s;
 }
@@ -305,7 +312,6 @@ __device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2
     wc[i] = in ? ld_cg(wcum + l) : 0.f;
   }
   asm volatile("bar.sync 1, 192;" ::: "memory");
-  const long long tm1 = timing ? clock64() : 0;
   const size_t slot = (io.hist ? (size_t)t_out * 128 : 0) + blockIdx.x;   // training keeps every frame (tape for the backward)
   float* out = s.accpm + slot * Lc * A;
   float* fout = s.floc ? s.floc + slot * Lc * D2_LOC_F : nullptr;
@@ -377,7 +383,7 @@ __device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2
             make_float4(o[p][0] + pm4[p].x, o[p][1] + pm4[p].y, o[p][2] + pm4[p].z, o[p][3] + pm4[p].w);
     __syncwarp();
   }
-  if (timing) { s.prof[7] += (unsigned long long)(tm1 - tm0); s.prof[15] += (unsigned long long)(clock64() - tm1); }
+  if (timing) s.prof[15] += (unsigned long long)(clock64() - tm0);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -654,39 +660,83 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
 }
 
 // ------------------------------------------------------------------------------------------
-// ------------------------------------------------------------------------------------------
-// Output phase, cluster-local: cluster c owns utterances 2c and 2c+1 and runs, without a grid barrier in between,
+// Output stage of frame `tg_`, cluster-local, on warps 2..7 (192 threads) BESIDE the next frame's attention-LSTM gate GEMM
+// (warps 0/1): cluster c owns utterances 2c and 2c+1 and runs
 //   mel / gate projection + stop bookkeeping   (model/decoder.py:103-109, model/tacotron2.py:311-322)
 //   prenet layer 1, prenet layer 2 on the emitted frame (model/tacotron2.py:85-92,324-325)      [autoregressive only]
-// Each CTA computes a quarter of every layer's rows for both utterances and broadcasts its results to the peers'
-// shared memory (DSMEM); the layers are separated by cluster barriers only.  Weights stream from L2 (coalesced 16-byte loads).
-// Scratch (floats, in the idle TMA ring): x[2][KprojP] | mel[2][MP] | p1[2][P] | out[8 warps][2][8] | y[2][64]
-__device__ void output_phase(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, float* scratch, uint32_t rank,
-                             int cluster, int tg_, int nxt, long long* prof_last) {
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NW = D2_THREADS / 32;
+// Only the prenet K-blocks of the next attention-LSTM contraction depend on this stage; the ctx / att_h K-blocks (6 of 7) stream
+// meanwhile.  Each CTA computes a quarter of every layer's rows for both utterances and broadcasts its results to the peers'
+// shared memory (DSMEM); the layers are separated by a cluster rendezvous of the side warps only (mbarriers, 4 x 6 warp
+// arrivals -- barrier.cluster would need the GEMM warps too; the two rendezvous of a frame use two different barriers so an
+// early arrival for the second can never be counted towards a peer's first).  Weights stream from L2 (coalesced 16-byte loads).
+// Scratch (floats, in the split-K partial buffer, idle until this GEMM's accumulator is read):
+//   x[2][KprojP] | mel[2][MP] | p1[2][P] | out[2][P/4] | y[2][64]
+__device__ __forceinline__ bool side_cluster_sync(uint64_t* cbar, uint32_t& phase) {
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) {
+    const uint32_t a = tc::smem_u32(cbar);
+#pragma unroll
+    for (uint32_t r = 0; r < D2_CLUSTER; ++r) tc::mbar_arrive_cluster(tc::mapa(a, r));
+  }
+  const bool ok = tc::mbar_wait_cluster(cbar, phase);
+  phase ^= 1u;
+  return ok;
+}
+
+// Context half of the mel / gate projection (model/decoder.py:103-109: the columns of mel_out / gate that multiply
+// ctx_t and the controls), on warps 2..7 beside the decoder-LSTM gate GEMM of the same frame: ctx_t is known since the attention
+// phase, so these K columns leave the dependent chain of the output stage.  Result: octx[j][row - r0] in shared memory.
+__device__ void proj_ctx_side(const D2Dims& d, const D2Weights& w, const D2State& s, const Smem& sm, uint32_t rank, int cluster) {
+  const int ptid = threadIdx.x - 64, pw = (threadIdx.x >> 5) - 2, NW = 6;
+  const int B = d.B, M = d.M, KP = d.KprojP, Kc = KP - d.H;
+  const int b0 = 2 * cluster;
+  if (b0 >= B) return;
+  float* xs = sm.part;   // [2][Kc]; the split-K partial buffer is idle while the GEMM streams
+#pragma unroll 1
+  for (int i = ptid; i < 2 * (Kc >> 2); i += 192) {
+    const int jj = i / (Kc >> 2), k = i - jj * (Kc >> 2);
+    reinterpret_cast<float4*>(xs)[i] = (b0 + jj < B) ? __ldcg(reinterpret_cast<const float4*>(s.projin + (size_t)(b0 + jj) * KP + d.H) + k)
+                                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  asm volatile("bar.sync 1, 192;" ::: "memory");
+  const int rows_per = (M + 1 + D2_CLUSTER - 1) / D2_CLUSTER, r0 = (int)rank * rows_per, nr = max(0, min(rows_per, M + 1 - r0));
+  const int rpw = (nr + NW - 1) / NW, rb = r0 + pw * rpw, re = min(r0 + nr, rb + rpw);
+  rows_dot2(w.Wproj + d.H, KP, Kc >> 2, rb, re, xs, xs + Kc, sm.octx, r0, 64);
+  asm volatile("bar.sync 1, 192;" ::: "memory");   // xs is reused by the caller's next side task
+}
+
+__device__ void output_side(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, const Smem& sm, uint32_t rank,
+                            int cluster, int tg_, int nxt, uint32_t& cphase) {
+  const int ptid = threadIdx.x - 64, lane = threadIdx.x & 31, pw = (threadIdx.x >> 5) - 2, NW = 6;
   const int B = d.B, M = d.M, P = d.P, KP = d.KprojP, MP = (M + 1 + 3) & ~3;
-  float* xs = scratch;
+  const int rq = P / D2_CLUSTER;
+  float* xs = sm.part;
   float* mel_s = xs + 2 * KP;
   float* p1_s = mel_s + 2 * MP;
-  float* out_s = p1_s + 2 * P;
-  float* y_s = out_s + NW * 2 * 8;   // [2][64] row sums of the layer in flight
+  float* out_s = p1_s + 2 * P;      // [2][rq] prenet layer-2 outputs of this CTA's rows, staged for 16-byte stores
+  float* y_s = out_s + 2 * rq;      // [2][YS] row sums of the layer in flight
+  const int YS = max(64, rq);
   const int b0 = 2 * cluster;
-  const bool any = b0 < B;
+  if (b0 >= B) return;              // uniform over the cluster: none of its CTAs joins the rendezvous
   const int j = lane & 1, b = b0 + j;   // epilogues: lane = (row of this warp's block, utterance)
-  if (any) {
+  const bool timing = blockIdx.x == 0 && ptid == 0 && s.prof;
+  long long tm = timing ? clock64() : 0;
+  auto mark = [&](int slot) { if (timing) { const long long now = clock64(); s.prof[slot] += (unsigned long long)(now - tm); tm = now; } };
+  const int H4 = d.H >> 2;   // the rnn_h columns; the ctx / controls columns were reduced beside the decoder-LSTM GEMM (octx)
 #pragma unroll 1
-    for (int i = tid; i < 2 * (KP >> 2); i += D2_THREADS) {
-      const int jj = i / (KP >> 2), k = i - jj * (KP >> 2);
-      reinterpret_cast<float4*>(xs)[i] = (b0 + jj < B) ? __ldcg(reinterpret_cast<const float4*>(s.projin + (size_t)(b0 + jj) * KP) + k)
-                                                       : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    __syncthreads();
+  for (int i = ptid; i < 2 * H4; i += 192) {
+    const int jj = i / H4, k = i - jj * H4;
+    reinterpret_cast<float4*>(xs)[i] = (b0 + jj < B) ? __ldcg(reinterpret_cast<const float4*>(s.projin + (size_t)(b0 + jj) * KP) + k)
+                                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  asm volatile("bar.sync 1, 192;" ::: "memory");
+  {
     const int rows_per = (M + 1 + D2_CLUSTER - 1) / D2_CLUSTER, r0 = (int)rank * rows_per, nr = max(0, min(rows_per, M + 1 - r0));
-    const int rpw = (nr + NW - 1) / NW, rb = r0 + warp * rpw, re = min(r0 + nr, rb + rpw);
-    rows_dot2(w.Wproj, KP, KP >> 2, rb, re, xs, xs + KP, y_s, r0, 64);
-    const int r = rb + (lane >> 1);
-    if (r < re && b < B) {
-      const float v = y_s[j * 64 + r - r0] + __ldg(w.bproj + r);
+    const int rpw = (nr + NW - 1) / NW, rb = r0 + pw * rpw, re = min(r0 + nr, rb + rpw);
+    rows_dot2(w.Wproj, KP, H4, rb, re, xs, xs + d.H, y_s, r0, YS);
+#pragma unroll 1
+    for (int r = rb + (lane >> 1); r < re && b < B; r += 16) {
+      const float v = y_s[j * YS + r - r0] + sm.octx[j * 64 + r - r0] + __ldg(w.bproj + r);
       if (r < M) {
         io.mels[((size_t)b * io.Tmax + tg_) * M + r] = v;
         if (!io.teacher_forcing) st_cluster_all(mel_s + j * MP + r, v);
@@ -699,50 +749,58 @@ __device__ void output_phase(const D2Dims& d, const D2Weights& w, const D2State&
       }
     }
   }
+  mark(4);
   if (io.teacher_forcing) return;
-  ATT_MARK(4);
-  tc::cluster_sync();
   const float pscale = 1.0f / (1.0f - d.p_prenet);
-  const int rq = P / D2_CLUSTER, pr0 = (int)rank * rq;
-  const int rpw = (rq + NW - 1) / NW, rb = pr0 + warp * rpw, re = min(pr0 + rq, rb + rpw);
-  const int r = rb + (lane >> 1);
-  if (any) {
-    rows_dot2(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y_s, pr0, 64);
-    if (r < re && b < B) {
-      const size_t kidx = (((size_t)(tg_ + 1) * 2 + 0) * B + b) * P + r;
-      const bool keep = io.prenet_keep ? (io.prenet_keep[kidx] != 0) : rng_keep(io.seed, kidx, d.p_prenet);
-      const float v = y_s[j * 64 + r - pr0];
-      st_cluster_all(p1_s + j * P + r, (v > 0.f && keep) ? v * pscale : 0.f);
-    }
+  const int pr0 = (int)rank * rq;
+  const int rpw = (rq + NW - 1) / NW, rb = pr0 + pw * rpw, re = min(pr0 + rq, rb + rpw);
+  uint32_t ph1 = cphase;
+  side_cluster_sync(sm.bars + 2 * D2_STAGES + 1, ph1);
+  if ((M >> 2) <= 32) rows_short<12, 1>(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y_s, pr0, YS);
+  else rows_dot2(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y_s, pr0, YS);
+#pragma unroll 1
+  for (int r = rb + (lane >> 1); r < re && b < B; r += 16) {
+    const size_t kidx = (((size_t)(tg_ + 1) * 2 + 0) * B + b) * P + r;
+    const bool keep = io.prenet_keep ? (io.prenet_keep[kidx] != 0) : rng_keep(io.seed, kidx, d.p_prenet);
+    const float v = y_s[j * YS + r - pr0];
+    st_cluster_all(p1_s + j * P + r, (v > 0.f && keep) ? v * pscale : 0.f);
   }
-  ATT_MARK(5);
-  tc::cluster_sync();
-  if (any) {
-    const long long pa = (long long)D2_BP * d.KattP;
-    __nv_bfloat16* xa = s.xatt + (size_t)nxt * 2 * pa;   // next frame's attention-LSTM input, prenet columns
-    const bool vec = rpw == 8 && (d.KattP & 7) == 0;
-    rows_dot2(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y_s, pr0, 64);
-    if (r < re && b < B) {
+  mark(5);
+  side_cluster_sync(sm.bars + 2 * D2_STAGES + 2, cphase);
+  const long long pa = (long long)D2_BP * d.KattP;
+  __nv_bfloat16* xa = s.xatt + (size_t)nxt * 2 * pa;   // next frame's attention-LSTM input, prenet columns
+  const bool vec = (rq & 7) == 0 && (d.KattP & 7) == 0;
+  if ((P >> 2) <= 64) rows_short<6, 2>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y_s, pr0, YS);
+  else rows_dot2(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y_s, pr0, YS);
+#pragma unroll 1
+  for (int r = rb + (lane >> 1); r < re; r += 16) {
+    float v = 0.f;
+    if (b < B) {
       const size_t kidx = (((size_t)(tg_ + 1) * 2 + 1) * B + b) * P + r;
       const bool keep = io.prenet_keep ? (io.prenet_keep[kidx] != 0) : rng_keep(io.seed, kidx, d.p_prenet);
-      float v = y_s[j * 64 + r - pr0];
+      v = y_s[j * YS + r - pr0];
       v = (v > 0.f && keep) ? v * pscale : 0.f;
-      if (vec) out_s[(warp * 2 + j) * 8 + (r - rb)] = v;
-      else store_split(xa, pa, d.KattP, b, r, v);
+      if (!vec) store_split(xa, pa, d.KattP, b, r, v);
     }
-    if (vec) {
-      __syncwarp();
-      if (lane < 4 && b0 + (lane >> 1) < B)
-        store_plane8(xa + (lane & 1) * pa + (size_t)(b0 + (lane >> 1)) * d.KattP + rb, out_s + (warp * 2 + (lane >> 1)) * 8, lane & 1, true);
+    if (vec) out_s[j * rq + r - pr0] = v;
+  }
+  if (vec) {
+    asm volatile("bar.sync 1, 192;" ::: "memory");
+#pragma unroll 1
+    for (int i = ptid; i < 4 * (rq >> 3); i += 192) {   // (plane, utterance, 8-column chunk)
+      const int pl = i & 1, jj = (i >> 1) & 1, c8 = i >> 2;
+      if (b0 + jj < B) store_plane8(xa + pl * pa + (size_t)(b0 + jj) * d.KattP + pr0 + 8 * c8, out_s + jj * rq + 8 * c8, pl, true);
     }
   }
+  mark(6);
 }
 
-enum { PH_ATT_LSTM = 0, PH_ATTN, PH_DEC_LSTM, PH_OUT, PH_COUNT };
-// profiling slot of each phase (slot 1 = query partials + the barrier of the attention-LSTM phase; the output phase marks
-// 4 = projection, 5 = prenet layer 1, 6 = prenet layer 2 + barrier; with teacher forcing 4 = projection + barrier)
-__device__ __constant__ int kPhaseSlot[PH_COUNT] = {1, 2, 3, 6};
-
+// Profiling slots (CTA 0; SM-clock cycles summed over the launch), thread 0 unless noted:
+//   8 attention-LSTM GEMM (all K-blocks, or the ctx / att_h K-blocks when the output stage of the previous frame runs beside it)
+//   4/5/6 output stage beside it: projection, prenet layer 1, prenet layer 2 (thread 64)
+//   7 grid barrier that publishes the prenet columns + the prenet K-block of the GEMM      [autoregressive]
+//   0 attention-LSTM pointwise tail, 1 query partials + barrier, 10..14 attention, 2 context store + barrier,
+//   9 decoder-LSTM GEMM, 15 location-term precompute beside it (thread 64), 3 decoder-LSTM tail + barrier
 __global__ void __launch_bounds__(D2_THREADS, 1)
 decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weights w, D2State s, D2IO io) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -777,8 +835,12 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
     sm.c_att[i] = s.att_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP];
     sm.c_dec[i] = s.rnn_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP];
   }
+  if (tid == 0) {   // rendezvous of the side warps of the cluster (output stage)
+    tc::mbar_init(sm.bars + 2 * D2_STAGES + 1, D2_CLUSTER * 6);
+    tc::mbar_init(sm.bars + 2 * D2_STAGES + 2, D2_CLUSTER * 6);
+  }
   tg::Pipe pipe;
-  tg::pipe_init(pipe, sm.bars, sm.stages, D2_STAGES, d.npass, sm.tmem_slot);
+  tg::pipe_init(pipe, sm.bars, sm.stages, D2_STAGES, d.npass, sm.tmem_slot);   // fences the barrier inits
   tc::cluster_sync();
 
   GridBar bar{s.barrier, s.barrier + 1, gridDim.x, 0u};
@@ -797,79 +859,100 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
   }
   const int nkb_att = d.KattP / TG_BK, nkb_dec = d.KdecP / TG_BK;
   const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
-  const float pscale = 1.0f / (1.0f - d.p_prenet);
   // history mode (training): the mel/gate projection is off the recurrence and runs as one bulk GEMM after this kernel
-  const int nphase = (io.teacher_forcing && io.hist) ? PH_DEC_LSTM + 1 : PH_COUNT;
+  const bool has_out = !(io.teacher_forcing && io.hist);
+  const int npre = d.P / TG_BK;   // the prenet K-blocks lead the attention-LSTM operand row
   int frames = 0;
   bool alive = true, fail = false, stop = false;
+  bool out_pending = false;   // output stage of the previous frame not run yet (it runs beside this frame's attention-LSTM GEMM)
+  bool pre_done = false;      // this frame's location term was computed beside the previous frame's decoder-LSTM GEMM
+  uint32_t cphase = 0;        // parity of the side warps' cluster rendezvous
+  int last_tg = io.t0, last_nxt = 0;
 
 #pragma unroll 1
   for (int t = 0; t < io.n_steps && alive && !stop; ++t) {
     const int tg_ = io.t0 + t;
     const int cur = io.hist ? tg_ : (t & 1), nxt = io.hist ? tg_ + 1 : (cur ^ 1);
-#pragma unroll 1
-    for (int ph = 0; ph < nphase && alive && !stop; ++ph) {
-      bool wrote_x = false;  // this phase stored operands that a later phase reads through TMA
-      if (ph == PH_ATT_LSTM || ph == PH_DEC_LSTM) {
-        // ---- attention / decoder LSTMCell (model/decoder.py:70-75, 94-101): gate GEMM + split-K reduce + pointwise
-        const bool att = ph == PH_ATT_LSTM;
-        tg::XSrc xs;
-        if (att && io.teacher_forcing) xs = tg::XSrc{&maps.tf_pre, tg_ * 2, &maps.x_att_rest, cur * 2, d.P / TG_BK};
-        else if (att) xs = tg::XSrc{&maps.x_att, cur * 2, &maps.x_att, cur * 2, nkb_att};
-        else xs = tg::XSrc{&maps.x_dec, cur * 2, &maps.x_dec, cur * 2, nkb_dec};
-        const int nkb = att ? nkb_att : nkb_dec;
-        const uint32_t dcol = att ? 0u : 64u;
-        bool gok;
-        if (att && io.precompute && att_active) {
-          gok = tg::gemm(pipe, &maps.w_att, tile * TG_M, nkb, xs, (int)rank, nkb, D2_CLUSTER, dcol,
-                         [&]() { attention_precompute(d, s, io, sm, att_b, att_part, S, cur, tg_); }, io.w_policy_att);
-        } else {
-          gok = tg::gemm(pipe, att ? &maps.w_att : &maps.w_dec, tile * TG_M, nkb, xs, (int)rank, nkb, D2_CLUSTER, dcol,
-                         att ? io.w_policy_att : io.w_policy_dec);
-        }
-        if (!gok) fail = true;
-        prof_mark(att ? 8 : 9);
-        tg::accum_to_smem(pipe, dcol, sm.part);
-        tc::cluster_sync();
-        HOut ho;
-        if (att) ho = HOut{s.xatt + (size_t)nxt * 2 * pa, d.KattP, d.P + d.EF, pa, s.xdec + (size_t)cur * 2 * pd, d.KdecP, 0, pd, s.att_h_rm, d.H, 0};
-        else ho = HOut{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, io.hist ? nullptr : s.projin, d.KprojP, 0};
-        if (!att && io.hist) frames = t + 1;
-        const unsigned char* keep = att ? io.att_keep : io.rnn_keep;
-        lstm_tail(sm.part, rank, unit0, att ? w.batt : w.bdec, d.H, att ? sm.c_att : sm.c_dec, B, ho,
-                  keep ? keep + (size_t)tg_ * B * d.H : nullptr, io.hidden_dropout != 0, io.seed,
-                  ((att ? 1ull : 2ull) << 40) + (unsigned long long)tg_ * B * d.H,
-                  (att ? s.sav_att : s.sav_dec) ? (att ? s.sav_att : s.sav_dec) + (size_t)tg_ * 5 * d.H * D2_BP : nullptr, sm.h_s);
-        if (att) {
-          prof_mark(0);
-          query_partial(sm.h_s, sm.wq, d.A, B, s.qpart + (size_t)blockIdx.x * d.A, (size_t)128 * d.A);
-        }
-        wrote_x = true;
-      } else if (ph == PH_ATTN) {
-        // ---- location-sensitive attention (model/attention.py:54-67, model/decoder.py:90)
-        attention_phase(d, s, io, sm, scratch, att_active, att_b, att_part, S, cur, nxt, tg_, att_mbits, &prof_last);
-        wrote_x = true;
-      } else {
-        output_phase(d, w, s, io, scratch, rank, tile, tg_, nxt, &prof_last);
-        wrote_x = !io.teacher_forcing;
-        frames = t + 1;
-      }
-      if (!(alive = bar.sync(fail, wrote_x))) break;
-      prof_mark((ph == PH_OUT && io.teacher_forcing) ? 4 : kPhaseSlot[ph]);
-      if (ph == PH_OUT && !io.teacher_forcing) {
+    last_tg = tg_; last_nxt = nxt;
+    // ================= attention LSTMCell (model/decoder.py:70-75): gate GEMM + split-K reduce + pointwise
+    {
+      tg::XSrc xs;
+      if (io.teacher_forcing) xs = tg::XSrc{&maps.tf_pre, tg_ * 2, &maps.x_att_rest, cur * 2, npre};
+      else xs = tg::XSrc{&maps.x_att, cur * 2, &maps.x_att, cur * 2, nkb_att};
+      // autoregressive: the prenet columns of this frame's input are still being produced by the output stage running beside
+      // the GEMM, so the K-blocks that read them are issued after it (second call, same accumulator)
+      const bool split = out_pending && !io.teacher_forcing;
+      int kb0 = (int)rank;
+      if (split) while (kb0 < npre) kb0 += D2_CLUSTER;
+      const bool do_out = out_pending, do_pre = io.precompute && att_active && !pre_done;
+      bool gok = tg::gemm(pipe, &maps.w_att, tile * TG_M, nkb_att, xs, kb0, nkb_att, D2_CLUSTER, 0u,
+                          [&]() {
+                            if (do_out) output_side(d, w, s, io, sm, rank, tile, tg_ - 1, cur, cphase);
+                            if (do_pre) attention_precompute(d, s, io, sm, att_b, att_part, S, cur, tg_);
+                          }, io.w_policy_att, 0u, (split && (int)rank < npre) ? (int)rank : -1);
+      if (!gok) fail = true;
+      prof_mark(8);
+      if (do_out) frames = t;
+      out_pending = false;
+      if (split) {
+        if (!(alive = bar.sync(fail, true))) break;
         if (io.stop_enabled) {  // model/tacotron2.py:321-322: leave once every utterance has fired its stop gate
           int mine = 1;
 #pragma unroll 1
           for (int b = tid; b < B; b += D2_THREADS) mine &= (ld_acquire_u32((const unsigned*)s.done + b) != 0u);
           if (__syncthreads_and(mine)) stop = true;
         }
-        if (t + 1 >= io.n_steps) stop = true;  // the last frame's prenet output is never used
-      }
-      if (ph == PH_OUT && io.debug_barrier) {  // measures the bare cost of one grid barrier (slot 7)
-        if (!(alive = bar.sync(fail, false))) break;
+        // (also when stopping: the weight box of this K-block is already in flight and its stage must be completed)
+        if (!tg::gemm(pipe, &maps.w_att, tile * TG_M, nkb_att, xs, (int)rank, min(npre, nkb_att), D2_CLUSTER, 0u, tg::NoSide{},
+                      io.w_policy_att, 1u, -1, gok && (int)rank < npre))
+          fail = true;
         prof_mark(7);
+        if (stop) break;
       }
+      tg::accum_to_smem(pipe, 0u, sm.part);
+      tc::cluster_sync();
+      const HOut ho{s.xatt + (size_t)nxt * 2 * pa, d.KattP, d.P + d.EF, pa, s.xdec + (size_t)cur * 2 * pd, d.KdecP, 0, pd, s.att_h_rm, d.H, 0};
+      lstm_tail(sm.part, rank, unit0, w.batt, d.H, sm.c_att, B, ho, io.att_keep ? io.att_keep + (size_t)tg_ * B * d.H : nullptr,
+                io.hidden_dropout != 0, io.seed, (1ull << 40) + (unsigned long long)tg_ * B * d.H,
+                s.sav_att ? s.sav_att + (size_t)tg_ * 5 * d.H * D2_BP : nullptr, sm.h_s);
+      prof_mark(0);
+      query_partial(sm.h_s, sm.wq, d.A, B, s.qpart + (size_t)blockIdx.x * d.A, (size_t)128 * d.A);
+      if (!(alive = bar.sync(fail, true))) break;
+      prof_mark(1);
     }
+    // ================= location-sensitive attention (model/attention.py:54-67, model/decoder.py:90)
+    attention_phase(d, s, io, sm, scratch, att_active, att_b, att_part, S, cur, nxt, tg_, att_mbits, &prof_last);
+    if (!(alive = bar.sync(fail, true))) break;
+    prof_mark(2);
+    // ================= decoder LSTMCell (model/decoder.py:94-101); the next frame's location term runs beside its GEMM
+    {
+      const tg::XSrc xs{&maps.x_dec, cur * 2, &maps.x_dec, cur * 2, nkb_dec};
+      const bool pre_next = io.precompute && att_active && t + 1 < io.n_steps;
+      const bool gok = tg::gemm(pipe, &maps.w_dec, tile * TG_M, nkb_dec, xs, (int)rank, nkb_dec, D2_CLUSTER, 64u,
+                                [&]() {
+                                  if (has_out) proj_ctx_side(d, w, s, sm, rank, tile);
+                                  if (pre_next) attention_precompute(d, s, io, sm, att_b, att_part, S, nxt, tg_ + 1);
+                                }, io.w_policy_dec);
+      pre_done = pre_next;
+      if (!gok) fail = true;
+      prof_mark(9);
+      tg::accum_to_smem(pipe, 64u, sm.part);
+      tc::cluster_sync();
+      const HOut ho{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, io.hist ? nullptr : s.projin, d.KprojP, 0};
+      if (io.hist) frames = t + 1;
+      lstm_tail(sm.part, rank, unit0, w.bdec, d.H, sm.c_dec, B, ho, io.rnn_keep ? io.rnn_keep + (size_t)tg_ * B * d.H : nullptr,
+                io.hidden_dropout != 0, io.seed, (2ull << 40) + (unsigned long long)tg_ * B * d.H,
+                s.sav_dec ? s.sav_dec + (size_t)tg_ * 5 * d.H * D2_BP : nullptr, sm.h_s);
+      if (!(alive = bar.sync(fail, true))) break;
+      prof_mark(3);
+      out_pending = has_out;
+    }
+  }
+  // The last frame's output stage has no GEMM to hide behind (it also leaves the prenet columns for a follow-up launch).
+  if (alive && !stop && out_pending) {
+    if ((tid >> 5) >= 2) output_side(d, w, s, io, sm, rank, tile, last_tg, last_nxt, cphase);
+    frames = io.n_steps;
+    __syncthreads();
   }
   if (blockIdx.x == 0 && tid == 0) *s.n_frames = alive ? frames : -1;
   // write the cell states back (single-step API / resumable decoding)
@@ -900,7 +983,7 @@ bool d2_precompute_fits(const D2Dims& d) {
 
 size_t d2_smem_bytes(const D2Dims& d) {
   return 1024 + (size_t)D2_STAGES * TG_STAGE_BYTES + TG_M * TG_PART_LD * 4 + 2 * 8 * D2_BP * 4 + 2 * D2_LOC_KP * D2_LOC_F * 4 +
-         (size_t)d.A * D2_LOC_F * 4 + d.A * 4 + 8 * d.A * 4 + 8 * D2_BP * 4 + (2 * D2_STAGES + 2) * 8 + 64;
+         (size_t)d.A * D2_LOC_F * 4 + d.A * 4 + 8 * d.A * 4 + 8 * D2_BP * 4 + 2 * 64 * 4 + (2 * D2_STAGES + 4) * 8 + 64;
 }
 
 static int launch_cfg(const D2Dims& d, cudaLaunchConfig_t* cfg, cudaLaunchAttribute* at, size_t smem, cudaStream_t st) {

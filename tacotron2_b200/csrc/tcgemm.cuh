@@ -61,9 +61,15 @@ __device__ __forceinline__ void pipe_init(Pipe& p, uint64_t* bars, uint8_t* stag
 // depend on this GEMM's result and needs no part of the stage ring.
 struct NoSide { __device__ __forceinline__ void operator()() const {} };
 // w_policy: L2 eviction priority of the W tiles: 0 = default, 1 = evict-first (pure stream), 2 = evict-last (keep resident)
+// acc_init: 0 = the first MMA overwrites the accumulator columns, 1 = continue a sum an earlier call left there (a contraction
+// issued in two parts because some K-blocks of x become available later than the others)
+// prefetch_w_kb >= 0: after its own K-blocks the producer also claims the next ring stage and starts the W box of that K-block
+// (the x box of it is not ready yet); the follow-up call passes first_w_issued = true and only adds the x box of its first
+// K-block to that stage.  The follow-up call MUST be made (the stage's transaction count is otherwise never met).
 template <class Side>
 __device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row0, int w_nkb, const XSrc& xs, int kb_begin, int kb_end,
-                                     int kb_stride, uint32_t d_col, Side side, int w_policy = 0) {
+                                     int kb_stride, uint32_t d_col, Side side, int w_policy = 0, uint32_t acc_init = 0u,
+                                     int prefetch_w_kb = -1, bool first_w_issued = false) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   bool ok = true;
   const uint32_t stage_tx = (uint32_t)(p.npass == 3 ? TG_STAGE_BYTES : TG_W_TILE + TG_X_TILE);
@@ -73,23 +79,35 @@ __device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row
     // The weight stream (tens of MB per frame, each byte used once per frame by one SM) must not push the small per-frame
     // working set (attention memory, processed memory, partial sums) out of L2: evict-first.
     const uint64_t wpol = w_policy == 2 ? tc::l2_policy_evict_last() : tc::l2_policy_evict_first();
-    for (int kb = kb_begin; kb < kb_end; kb += kb_stride) {
-      if (!tc::mbar_wait(p.empty + p.p_stage, p.p_phase ^ 1)) { ok = false; break; }
-      uint8_t* st = p.stages + (size_t)p.p_stage * TG_STAGE_BYTES;
-      tc::mbar_arrive_expect_tx(p.full + p.p_stage, stage_tx);
-      const bool first = kb < xs.split;
-      const CUtensorMap* xm = first ? xs.map0 : xs.map1;
-      const int xk = (first ? kb : kb - xs.split) * TG_BK, xz = first ? xs.z0 : xs.z1;
+    auto load_w = [&](uint8_t* st, int kb) {
       const int wc0 = w_nkb ? 0 : kb * TG_BK, wc1 = w_nkb ? ((w_row0 / TG_M) * w_nkb + kb) * TG_M : w_row0;
       if (w_policy) tc::tma_load_3d_hint(st, wmap, p.full + p.p_stage, wc0, wc1, 0, wpol);   // [hi|lo] 32 KB (hi only when box z = 1)
       else tc::tma_load_3d(st, wmap, p.full + p.p_stage, wc0, wc1, 0);
+    };
+    for (int kb = kb_begin; kb < kb_end; kb += kb_stride) {
+      uint8_t* st = p.stages + (size_t)p.p_stage * TG_STAGE_BYTES;
+      if (!(first_w_issued && kb == kb_begin)) {
+        if (!tc::mbar_wait(p.empty + p.p_stage, p.p_phase ^ 1)) { ok = false; break; }
+        tc::mbar_arrive_expect_tx(p.full + p.p_stage, stage_tx);
+        load_w(st, kb);
+      }
+      const bool first = kb < xs.split;
+      const CUtensorMap* xm = first ? xs.map0 : xs.map1;
+      const int xk = (first ? kb : kb - xs.split) * TG_BK, xz = first ? xs.z0 : xs.z1;
       tc::tma_load_3d(st + 2 * TG_W_TILE, xm, p.full + p.p_stage, xk, 0, xz);      // [hi|lo] 16 KB
       if (++p.p_stage == p.nstages) { p.p_stage = 0; p.p_phase ^= 1; }
+    }
+    if (ok && prefetch_w_kb >= 0) {
+      if (!tc::mbar_wait(p.empty + p.p_stage, p.p_phase ^ 1)) ok = false;
+      else {
+        tc::mbar_arrive_expect_tx(p.full + p.p_stage, stage_tx);
+        load_w(p.stages + (size_t)p.p_stage * TG_STAGE_BYTES, prefetch_w_kb);
+      }
     }
   } else if (warp == 1 && lane == 0) {
     // ---------------- MMA issuer
     const uint32_t idesc = tc::idesc_bf16_f32(TG_M, TG_N);
-    uint32_t acc = 0;
+    uint32_t acc = acc_init;
     for (int kb = kb_begin; kb < kb_end; kb += kb_stride) {
       if (!tc::mbar_wait(p.full + p.c_stage, p.c_phase)) { ok = false; break; }
       tc::tc_fence_after();

@@ -9,8 +9,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from tacotron2_b200 import _lib, synth  # noqa: E402
 from tacotron2_b200.model import Tacotron2  # noqa: E402
 
-NAMES = ["att_tail", "qpart+bar", "attention", "dec_tail", "proj", "pre1", "pre2", "pre_stage", "att_gemm", "dec_gemm", "a_conv", "a_dense",
-         "a_csync", "a_softmax", "a_ctx", "pre_tiles"]
+NAMES = ["att_tail", "qpart+bar", "attention", "dec_tail", "proj(side)", "pre1(side)", "pre2(side)", "xbar+kb0", "att_gemm", "dec_gemm", "a_qsum",
+         "a_energy", "a_csync", "a_softmax", "a_ctx", "precompute(side)"]
 
 
 def main():
