@@ -29,8 +29,8 @@ B, L, T = 64, 200, 1000
 METRIC, UNIT = "mel_frames_per_sec_ar_decode", "frames/s"
 # dram__bytes_read.sum + dram__bytes_write.sum of decoder_persistent_kernel from the committed ncu --set full capture, per decoded
 # frame (the capture is a 200-frame launch of the same C2 batch; traffic is linear in the frame count)
-NCU_DRAM_BYTES_PER_FRAME = (13.777717e9 + 50.530048e6) / 200
-NCU_DRAM_SOURCE = "profiles/r01_v6_decoder_fwd_full_raw.csv (ncu --set full, 200-frame launch; per frame x frames)"
+NCU_DRAM_BYTES_PER_FRAME = (13.768351e9 + 49.030912e6) / 200
+NCU_DRAM_SOURCE = "profiles/r01_v9_decoder_fwd_full_raw.csv (ncu --set full, 200-frame launch; per frame x frames)"
 WORKLOAD = "C2: vanilla-ljspeech-stop AR inference, batch 64 x 200 chars x 1000 frames, fp32, stop gate evaluated (never fires)"
 # kernels launched by one Tacotron2.forward (AR): embed 1, encoder conv 3, BiLSTM input proj 1, BiLSTM 1, memory split 1,
 # att_encoder 1, persistent decoder 1, mel split 1, postnet conv 5, finalize 1  (memsets / memcpys not counted)
@@ -377,6 +377,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-train", action="store_true", help="skip the training-step measurement (extra `train` object of the JSON line)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the log-mel, bf16-mode and torch-eager side measurements (profiling runs)")
     ap.add_argument("--train-only", action="store_true", help="print only the training-step measurement (profiling aid)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -520,11 +521,9 @@ def main():
         line["config"]["phase_us_per_frame"] = str(e)
     if train is not None:
         line["train"] = train
-    try:
-        line["melspec"] = melspec_bench(dev)
-    except Exception as e:  # noqa: BLE001
-        line["melspec"] = {"error": f"{type(e).__name__}: {e}"}
-    for key, fn in (("bf16_mode_us_per_decoder_step", bf16_mode_us_per_step), ("torch_cuda_eager", torch_eager_cuda_step)):
+    extras = () if args.no_extras else (("melspec", melspec_bench), ("bf16_mode_us_per_decoder_step", bf16_mode_us_per_step),
+                                        ("torch_cuda_eager", torch_eager_cuda_step))
+    for key, fn in extras:
         try:
             line[key] = fn(dev)
         except Exception as e:  # noqa: BLE001
