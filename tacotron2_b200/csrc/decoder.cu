@@ -113,14 +113,14 @@ struct Smem {
   float* wq;
   float* h_s;
   float* octx;       // [2][64] context half of the mel/gate projection of this cluster's two utterances (computed a phase early)
-  float* pre;        // attention precompute scratch (only when io.precompute): wp | wc (with halo) | 6 per-warp conv tiles [8][36]
+  float* pre;        // attention precompute scratch (only when io.precompute): (wp, wc) pairs with halo | 6 per-warp conv tiles [32][12]
   uint64_t* bars;
   uint32_t* tmem_slot;
 };
 
 __host__ __device__ __forceinline__ int d2_parts(int B, int grid) { return (B * 4 <= grid) ? 4 : ((B * 2 <= grid) ? 2 : 1); }
 __host__ __device__ __forceinline__ int pre_wlen(int L, int S) { return ((((L + S - 1) / S) + 7) & ~7) + 32; }
-__host__ __device__ __forceinline__ size_t pre_floats(int L, int S) { return 2 * (size_t)pre_wlen(L, S) + 6 * 8 * 36 + 4; }
+__host__ __device__ __forceinline__ size_t pre_floats(int L, int S) { return 2 * (size_t)pre_wlen(L, S) + 6 * 32 * 12 + 4; }
 
 __device__ __forceinline__ Smem carve(uint8_t* base, const D2Dims& d, int pre_f) {
   Smem s;
@@ -295,11 +295,12 @@ __device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2
   const int L = d.L, A = d.A;
   const int Lc = (L + S - 1) / S, l0 = part * Lc, l1 = min(L, l0 + Lc), nl = max(0, l1 - l0);
   const int ntile = (nl + 7) >> 3, wlen = pre_wlen(L, S);
-  float* wp = sm.pre;
-  float* wc = wp + wlen;
-  float* fsw = wc + wlen + pw * (8 * 36);
-  int* next_tile = reinterpret_cast<int*>(wc + wlen + 6 * 8 * 36);   // tiles are handed out dynamically: the six warps do not
-  if (ptid == 0) *next_tile = 0;                                      // share the four schedulers evenly (warps 0/1 mostly sleep)
+  // fp32 FMAs issue at half rate on sm_100 unless packed (FFMA2, two lanes of a 64-bit register pair per instruction): the
+  // conv pairs the two input channels, the dense pairs neighbouring positions.
+  float2* wpc = reinterpret_cast<float2*>(sm.pre);             // (previous, cumulative) weights, interleaved, 15-sample halo
+  float* fsw = sm.pre + 2 * wlen + pw * (32 * 12);             // this warp's conv features [filter][8 positions (+4 pad)]
+  int* next_tile = reinterpret_cast<int*>(sm.pre + 2 * wlen + 6 * 32 * 12);   // tiles are handed out dynamically: the six warps do
+  if (ptid == 0) *next_tile = 0;                                               // not share the four schedulers evenly
   const float* wprev = s.w_prev + ((size_t)cur * D2_BP + b) * L;
   const float* wcum = s.w_cum + ((size_t)cur * D2_BP + b) * L;
   const bool timing = blockIdx.x == 0 && ptid == 0 && s.prof;
@@ -308,8 +309,7 @@ __device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2
   for (int i = ptid; i < ntile * 8 + 32; i += 192) {
     const int l = l0 + i - 15;
     const bool in = (l >= 0 && l < L);
-    wp[i] = in ? ld_cg(wprev + l) : 0.f;
-    wc[i] = in ? ld_cg(wcum + l) : 0.f;
+    wpc[i] = in ? make_float2(ld_cg(wprev + l), ld_cg(wcum + l)) : make_float2(0.f, 0.f);
   }
   asm volatile("bar.sync 1, 192;" ::: "memory");
   const size_t slot = (io.hist ? (size_t)t_out * 128 : 0) + blockIdx.x;   // training keeps every frame (tape for the backward)
@@ -331,56 +331,57 @@ __device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2
       pm4[p] = __ldg(reinterpret_cast<const float4*>(io.pmem + ((size_t)b * L + l0 + min(lt + p, nl - 1)) * A + ac));
     // Loops below are kept compact on purpose: the instruction cache (L0 ~6 KB, L1.5 32 KB) does not hold long unrolled
     // bodies, and six warps streaming through straight-line code starve on instruction fetch.
-    float acc[8];
+    float2 acc2[8];   // (previous-weights channel, cumulative-weights channel) partial sums of filter `lane`
 #pragma unroll
-    for (int p = 0; p < 8; ++p) acc[p] = 0.f;
+    for (int p = 0; p < 8; ++p) acc2[p] = make_float2(0.f, 0.f);
 #pragma unroll 1
-    for (int jb = 0; jb < D2_LOC_KP / 8; ++jb) {   // 8 taps per pass over a 16-sample window of each input channel
-      float xw[16], xc[16];
+    for (int jb = 0; jb < D2_LOC_KP / 8; ++jb) {   // 8 taps per pass over a 16-sample window
+      float2 xin[16];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const float4 u4 = *reinterpret_cast<const float4*>(wp + lt + 8 * jb + 4 * i), c4 = *reinterpret_cast<const float4*>(wc + lt + 8 * jb + 4 * i);
-        xw[4 * i] = u4.x; xw[4 * i + 1] = u4.y; xw[4 * i + 2] = u4.z; xw[4 * i + 3] = u4.w;
-        xc[4 * i] = c4.x; xc[4 * i + 1] = c4.y; xc[4 * i + 2] = c4.z; xc[4 * i + 3] = c4.w;
+      for (int i = 0; i < 8; ++i) {
+        const float4 u4 = *reinterpret_cast<const float4*>(wpc + lt + 8 * jb + 2 * i);
+        xin[2 * i] = make_float2(u4.x, u4.y); xin[2 * i + 1] = make_float2(u4.z, u4.w);
       }
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        const float w0 = sm.conv_t[(8 * jb + i) * D2_LOC_F + lane], w1 = sm.conv_t[(D2_LOC_KP + 8 * jb + i) * D2_LOC_F + lane];
+        const float2 w01 = make_float2(sm.conv_t[(8 * jb + i) * D2_LOC_F + lane], sm.conv_t[(D2_LOC_KP + 8 * jb + i) * D2_LOC_F + lane]);
 #pragma unroll
-        for (int p = 0; p < 8; ++p) { acc[p] = fmaf(w0, xw[p + i], acc[p]); acc[p] = fmaf(w1, xc[p + i], acc[p]); }
+        for (int p = 0; p < 8; ++p) acc2[p] = __ffma2_rn(w01, xin[p + i], acc2[p]);
       }
     }
+    float acc[8];
 #pragma unroll
-    for (int p = 0; p < 8; ++p) fsw[p * 36 + lane] = acc[p];
+    for (int p = 0; p < 8; ++p) acc[p] = acc2[p].x + acc2[p].y;
+    *reinterpret_cast<float4*>(fsw + lane * 12) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    *reinterpret_cast<float4*>(fsw + lane * 12 + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
     if (fout) {
 #pragma unroll
       for (int p = 0; p < 8; ++p) if (lt + p < nl) __stcs(fout + (size_t)(lt + p) * D2_LOC_F + lane, acc[p]);
     }
     __syncwarp();
-    float o[8][4];
+    float2 o2[4][4];   // [position pair][attention dim of this lane's quad] = (position 2pp, position 2pp+1)
 #pragma unroll
-    for (int p = 0; p < 8; ++p) { o[p][0] = 0.f; o[p][1] = 0.f; o[p][2] = 0.f; o[p][3] = 0.f; }
-#pragma unroll 1
-    for (int f4 = 0; f4 < D2_LOC_F / 4; ++f4) {
-      float4 fv[8];
+    for (int pp = 0; pp < 4; ++pp) { o2[pp][0] = o2[pp][1] = o2[pp][2] = o2[pp][3] = make_float2(0.f, 0.f); }
+#pragma unroll 2
+    for (int f = 0; f < D2_LOC_F; ++f) {
+      const float4 fa = *reinterpret_cast<const float4*>(fsw + f * 12), fb = *reinterpret_cast<const float4*>(fsw + f * 12 + 4);
+      const float2 fp[4] = {make_float2(fa.x, fa.y), make_float2(fa.z, fa.w), make_float2(fb.x, fb.y), make_float2(fb.z, fb.w)};
+      const float4 wv = *reinterpret_cast<const float4*>(sm.dense + f * A + ac);
+      const float2 wd[4] = {make_float2(wv.x, wv.x), make_float2(wv.y, wv.y), make_float2(wv.z, wv.z), make_float2(wv.w, wv.w)};
 #pragma unroll
-      for (int p = 0; p < 8; ++p) fv[p] = *reinterpret_cast<const float4*>(fsw + p * 36 + f4 * 4);
+      for (int pp = 0; pp < 4; ++pp) {
 #pragma unroll
-      for (int ff = 0; ff < 4; ++ff) {
-        const float4 wv = *reinterpret_cast<const float4*>(sm.dense + (f4 * 4 + ff) * A + ac);
-#pragma unroll
-        for (int p = 0; p < 8; ++p) {
-          const float fl = ff == 0 ? fv[p].x : (ff == 1 ? fv[p].y : (ff == 2 ? fv[p].z : fv[p].w));
-          o[p][0] = fmaf(fl, wv.x, o[p][0]); o[p][1] = fmaf(fl, wv.y, o[p][1]);
-          o[p][2] = fmaf(fl, wv.z, o[p][2]); o[p][3] = fmaf(fl, wv.w, o[p][3]);
-        }
+        for (int c = 0; c < 4; ++c) o2[pp][c] = __ffma2_rn(wd[c], fp[pp], o2[pp][c]);
       }
     }
 #pragma unroll
     for (int p = 0; p < 8; ++p)
-      if (lane_on && lt + p < nl)
+      if (lane_on && lt + p < nl) {
+        const int pp = p >> 1;
         *reinterpret_cast<float4*>(out + (size_t)(lt + p) * A + a4) =
-            make_float4(o[p][0] + pm4[p].x, o[p][1] + pm4[p].y, o[p][2] + pm4[p].z, o[p][3] + pm4[p].w);
+            (p & 1) ? make_float4(o2[pp][0].y + pm4[p].x, o2[pp][1].y + pm4[p].y, o2[pp][2].y + pm4[p].z, o2[pp][3].y + pm4[p].w)
+                    : make_float4(o2[pp][0].x + pm4[p].x, o2[pp][1].x + pm4[p].y, o2[pp][2].x + pm4[p].z, o2[pp][3].x + pm4[p].w);
+      }
     __syncwarp();
   }
   if (timing) s.prof[15] += (unsigned long long)(clock64() - tm0);
