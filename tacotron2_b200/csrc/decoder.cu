@@ -19,6 +19,10 @@ namespace {
 // cluster owns.  One warp per block of consecutive rows [rb, re), four rows in flight, lanes stride the row in 16-byte loads
 // (coalesced, weights straight from L2), fixed-order warp reduction; lane 0 leaves the sums in y[j*ys + r - ybase] (shared
 // memory).  One out-of-line copy serves all three layers (instruction-cache footprint).
+// XG: the two input rows are read straight from global memory (L2-coherent loads, they were written by other CTAs before the
+// last grid barrier) in the same batch as the weight loads, instead of being staged in shared memory first (one L2 round trip
+// and a barrier less on the dependent chain).
+template <bool XG>
 __device__ __noinline__ void rows_dot2(const float* __restrict__ W, int ldw, int K4, int rb, int re, const float* x0, const float* x1, float* y,
                                        int ybase, int ys) {
   const int lane = threadIdx.x & 31;
@@ -29,9 +33,10 @@ __device__ __noinline__ void rows_dot2(const float* __restrict__ W, int ldw, int
     const float4* w1 = reinterpret_cast<const float4*>(W + (size_t)min(r + 1, re - 1) * ldw);
     const float4* w2 = reinterpret_cast<const float4*>(W + (size_t)min(r + 2, re - 1) * ldw);
     const float4* w3 = reinterpret_cast<const float4*>(W + (size_t)min(r + 3, re - 1) * ldw);
-#pragma unroll 2
+#pragma unroll 4
     for (int k = lane; k < K4; k += 32) {
-      const float4 xa = *reinterpret_cast<const float4*>(x0 + 4 * k), xb = *reinterpret_cast<const float4*>(x1 + 4 * k);
+      const float4 xa = XG ? __ldcg(reinterpret_cast<const float4*>(x0) + k) : *reinterpret_cast<const float4*>(x0 + 4 * k);
+      const float4 xb = XG ? __ldcg(reinterpret_cast<const float4*>(x1) + k) : *reinterpret_cast<const float4*>(x1 + 4 * k);
       const float4 wv[4] = {__ldg(w0 + k), __ldg(w1 + k), __ldg(w2 + k), __ldg(w3 + k)};
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
@@ -50,7 +55,7 @@ __device__ __noinline__ void rows_dot2(const float* __restrict__ W, int ldw, int
 
 // Short-row variant (K4 <= 32 * NK float4 per row): NR rows and all their loads in flight at once, so a layer costs one or two
 // L2 round trips instead of one per group of four rows.
-template <int NR, int NK>
+template <int NR, int NK, bool WS>   // WS: the weight rows are in shared memory
 __device__ __noinline__ void rows_short(const float* __restrict__ W, int ldw, int K4, int rb, int re, const float* x0, const float* x1, float* y,
                                         int ybase, int ys) {
   const int lane = threadIdx.x & 31;
@@ -69,7 +74,8 @@ __device__ __noinline__ void rows_short(const float* __restrict__ W, int ldw, in
 #pragma unroll
       for (int k = 0; k < NK; ++k) {
         const int kk = lane + 32 * k;
-        wv[i][k] = kk < K4 ? __ldg(reinterpret_cast<const float4*>(W + (size_t)min(r + i, re - 1) * ldw) + kk) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4* wp = reinterpret_cast<const float4*>(W + (ptrdiff_t)min(r + i, re - 1) * ldw) + kk;
+        wv[i][k] = kk < K4 ? (WS ? *wp : __ldg(wp)) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
 #pragma unroll
     for (int i = 0; i < NR; ++i) {
@@ -86,11 +92,11 @@ __device__ __noinline__ void rows_short(const float* __restrict__ W, int ldw, in
   __syncwarp();
 }
 
-// value -> the same shared-memory word of all CTAs of the cluster (DSMEM broadcast)
-__device__ __forceinline__ void st_cluster_all(float* p, float v) {
-  const uint32_t a = tc::smem_u32(p);
+// value -> the same word of all CTAs of the cluster, each copy counted on the receiver's transaction barrier `bar`
+__device__ __forceinline__ void st_async_all(float* p, float v, uint64_t* bar) {
+  const uint32_t a = tc::smem_u32(p), b = tc::smem_u32(bar);
 #pragma unroll
-  for (uint32_t r = 0; r < D2_CLUSTER; ++r) asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(tc::mapa(a, r)), "f"(v) : "memory");
+  for (uint32_t r = 0; r < D2_CLUSTER; ++r) tc::st_async_f32(tc::mapa(a, r), v, tc::mapa(b, r));
 }
 
 // ------------------------------------------------------------------------------------------
@@ -667,43 +673,25 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
 //   prenet layer 1, prenet layer 2 on the emitted frame (model/tacotron2.py:85-92,324-325)      [autoregressive only]
 // Only the prenet K-blocks of the next attention-LSTM contraction depend on this stage; the ctx / att_h K-blocks (6 of 7) stream
 // meanwhile.  Each CTA computes a quarter of every layer's rows for both utterances and broadcasts its results to the peers'
-// shared memory (DSMEM); the layers are separated by a cluster rendezvous of the side warps only (mbarriers, 4 x 6 warp
-// arrivals -- barrier.cluster would need the GEMM warps too; the two rendezvous of a frame use two different barriers so an
-// early arrival for the second can never be counted towards a peer's first).  Weights stream from L2 (coalesced 16-byte loads).
+// shared memory with `st.async` (DSMEM store that also counts its bytes on the receiver's transaction mbarrier): a layer's input
+// is complete when the receiver's barrier has seen all its bytes -- one trip through the SM-to-SM network per exchange, no
+// release fence + arrive round, and barrier.cluster (which would need the GEMM warps too) is not involved.
+// Weights stream from L2 (coalesced 16-byte loads); the layer-1 rows come by one bulk copy issued when the stage starts.
 // Scratch (floats, in the split-K partial buffer, idle until this GEMM's accumulator is read):
-//   x[2][KprojP] | mel[2][MP] | p1[2][P] | out[2][P/4] | y[2][64]
-__device__ __forceinline__ bool side_cluster_sync(uint64_t* cbar, uint32_t& phase) {
-  __syncwarp();
-  if ((threadIdx.x & 31) == 0) {
-    const uint32_t a = tc::smem_u32(cbar);
-#pragma unroll
-    for (uint32_t r = 0; r < D2_CLUSTER; ++r) tc::mbar_arrive_cluster(tc::mapa(a, r));
-  }
-  const bool ok = tc::mbar_wait_cluster(cbar, phase);
-  phase ^= 1u;
-  return ok;
-}
-
+//   mel[2][MP] | p1[2][P] | out[2][P/4] | y[3 layers][2][64] | W1 rows [P/4][M]
 // Context half of the mel / gate projection (model/decoder.py:103-109: the columns of mel_out / gate that multiply
 // ctx_t and the controls), on warps 2..7 beside the decoder-LSTM gate GEMM of the same frame: ctx_t is known since the attention
 // phase, so these K columns leave the dependent chain of the output stage.  Result: octx[j][row - r0] in shared memory.
 __device__ void proj_ctx_side(const D2Dims& d, const D2Weights& w, const D2State& s, const Smem& sm, uint32_t rank, int cluster) {
-  const int ptid = threadIdx.x - 64, pw = (threadIdx.x >> 5) - 2, NW = 6;
+  const int pw = (threadIdx.x >> 5) - 2, NW = 6;
   const int B = d.B, M = d.M, KP = d.KprojP, Kc = KP - d.H;
   const int b0 = 2 * cluster;
   if (b0 >= B) return;
-  float* xs = sm.part;   // [2][Kc]; the split-K partial buffer is idle while the GEMM streams
-#pragma unroll 1
-  for (int i = ptid; i < 2 * (Kc >> 2); i += 192) {
-    const int jj = i / (Kc >> 2), k = i - jj * (Kc >> 2);
-    reinterpret_cast<float4*>(xs)[i] = (b0 + jj < B) ? __ldcg(reinterpret_cast<const float4*>(s.projin + (size_t)(b0 + jj) * KP + d.H) + k)
-                                                     : make_float4(0.f, 0.f, 0.f, 0.f);
-  }
-  asm volatile("bar.sync 1, 192;" ::: "memory");
+  const float* x0 = s.projin + (size_t)b0 * KP + d.H;
+  const float* x1 = s.projin + (size_t)min(b0 + 1, B - 1) * KP + d.H;   // odd batch: the second column is computed and ignored
   const int rows_per = (M + 1 + D2_CLUSTER - 1) / D2_CLUSTER, r0 = (int)rank * rows_per, nr = max(0, min(rows_per, M + 1 - r0));
   const int rpw = (nr + NW - 1) / NW, rb = r0 + pw * rpw, re = min(r0 + nr, rb + rpw);
-  rows_dot2(w.Wproj + d.H, KP, Kc >> 2, rb, re, xs, xs + Kc, sm.octx, r0, 64);
-  asm volatile("bar.sync 1, 192;" ::: "memory");   // xs is reused by the caller's next side task
+  rows_dot2<true>(w.Wproj + d.H, KP, Kc >> 2, rb, re, x0, x1, sm.octx, r0, 64);
 }
 
 __device__ void output_side(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, const Smem& sm, uint32_t rank,
@@ -711,36 +699,43 @@ __device__ void output_side(const D2Dims& d, const D2Weights& w, const D2State& 
   const int ptid = threadIdx.x - 64, lane = threadIdx.x & 31, pw = (threadIdx.x >> 5) - 2, NW = 6;
   const int B = d.B, M = d.M, P = d.P, KP = d.KprojP, MP = (M + 1 + 3) & ~3;
   const int rq = P / D2_CLUSTER;
-  float* xs = sm.part;
-  float* mel_s = xs + 2 * KP;
+  float* mel_s = sm.part;
   float* p1_s = mel_s + 2 * MP;
   float* out_s = p1_s + 2 * P;      // [2][rq] prenet layer-2 outputs of this CTA's rows, staged for 16-byte stores
-  float* y_s = out_s + 2 * rq;      // [2][YS] row sums of the layer in flight
   const int YS = max(64, rq);
+  float* y_s = out_s + 2 * rq;      // [3][2][YS] row sums, one buffer per layer (no warp waits for another to consume its sums)
+  float* w1_s = y_s + 6 * YS;       // [rq][M] this CTA's rows of prenet layer 1, fetched by one bulk copy while the projection runs
+  const int w1_off = 2 * MP + 2 * P + 2 * rq + 6 * YS;
+  const bool w1_smem = !io.teacher_forcing && (M >> 2) <= 32 && (w1_off & 3) == 0 && w1_off + rq * M <= TG_M * TG_PART_LD;
+  uint64_t* mel_bar = sm.bars + 2 * D2_STAGES + 1;   // transaction barriers: all bytes of the mel frame / of prenet layer 1 are here
+  uint64_t* p1_bar = sm.bars + 2 * D2_STAGES + 2;
+  uint64_t* wbar = sm.bars + 2 * D2_STAGES + 3;
   const int b0 = 2 * cluster;
   if (b0 >= B) return;              // uniform over the cluster: none of its CTAs joins the rendezvous
   const int j = lane & 1, b = b0 + j;   // epilogues: lane = (row of this warp's block, utterance)
   const bool timing = blockIdx.x == 0 && ptid == 0 && s.prof;
   long long tm = timing ? clock64() : 0;
   auto mark = [&](int slot) { if (timing) { const long long now = clock64(); s.prof[slot] += (unsigned long long)(now - tm); tm = now; } };
-  const int H4 = d.H >> 2;   // the rnn_h columns; the ctx / controls columns were reduced beside the decoder-LSTM GEMM (octx)
-#pragma unroll 1
-  for (int i = ptid; i < 2 * H4; i += 192) {
-    const int jj = i / H4, k = i - jj * H4;
-    reinterpret_cast<float4*>(xs)[i] = (b0 + jj < B) ? __ldcg(reinterpret_cast<const float4*>(s.projin + (size_t)(b0 + jj) * KP) + k)
-                                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+  if (!io.teacher_forcing && ptid == 0) {
+    const uint32_t nu = (uint32_t)min(2, B - b0);   // peers may deliver before this arrives: the transaction count is signed
+    tc::mbar_arrive_expect_tx(mel_bar, nu * (uint32_t)M * 4u);
+    tc::mbar_arrive_expect_tx(p1_bar, nu * (uint32_t)P * 4u);
+    if (w1_smem) {
+      tc::mbar_arrive_expect_tx(wbar, (uint32_t)(rq * M * 4));
+      tc::bulk_load_1d(w1_s, w.W1 + (size_t)rank * rq * M, (uint32_t)(rq * M * 4), wbar);
+    }
   }
-  asm volatile("bar.sync 1, 192;" ::: "memory");
+  const int H4 = d.H >> 2;   // the rnn_h columns; the ctx / controls columns were reduced beside the decoder-LSTM GEMM (octx)
   {
     const int rows_per = (M + 1 + D2_CLUSTER - 1) / D2_CLUSTER, r0 = (int)rank * rows_per, nr = max(0, min(rows_per, M + 1 - r0));
     const int rpw = (nr + NW - 1) / NW, rb = r0 + pw * rpw, re = min(r0 + nr, rb + rpw);
-    rows_dot2(w.Wproj, KP, H4, rb, re, xs, xs + d.H, y_s, r0, YS);
+    rows_dot2<true>(w.Wproj, KP, H4, rb, re, s.projin + (size_t)b0 * KP, s.projin + (size_t)min(b0 + 1, B - 1) * KP, y_s, r0, YS);
 #pragma unroll 1
     for (int r = rb + (lane >> 1); r < re && b < B; r += 16) {
       const float v = y_s[j * YS + r - r0] + sm.octx[j * 64 + r - r0] + __ldg(w.bproj + r);
       if (r < M) {
         io.mels[((size_t)b * io.Tmax + tg_) * M + r] = v;
-        if (!io.teacher_forcing) st_cluster_all(mel_s + j * MP + r, v);
+        if (!io.teacher_forcing) st_async_all(mel_s + j * MP + r, v, mel_bar);
       } else {
         io.gates[(size_t)b * io.Tmax + tg_] = v;
         if (io.stop_enabled) {  // model/tacotron2.py:319-320
@@ -755,31 +750,36 @@ __device__ void output_side(const D2Dims& d, const D2Weights& w, const D2State& 
   const float pscale = 1.0f / (1.0f - d.p_prenet);
   const int pr0 = (int)rank * rq;
   const int rpw = (rq + NW - 1) / NW, rb = pr0 + pw * rpw, re = min(pr0 + rq, rb + rpw);
-  uint32_t ph1 = cphase;
-  side_cluster_sync(sm.bars + 2 * D2_STAGES + 1, ph1);
-  if ((M >> 2) <= 32) rows_short<12, 1>(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y_s, pr0, YS);
-  else rows_dot2(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y_s, pr0, YS);
+  float* y1 = y_s + 2 * YS;
+  float* y2 = y_s + 4 * YS;
+  tc::mbar_wait_cluster(mel_bar, cphase);   // the whole mel frame of both utterances has arrived (one exchange per frame: same parity)
+  if (w1_smem) {
+    tc::mbar_wait(wbar, cphase);
+    rows_short<12, 1, true>(w1_s - (ptrdiff_t)pr0 * M, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
+  } else if ((M >> 2) <= 32) rows_short<12, 1, false>(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
+  else rows_dot2<false>(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
 #pragma unroll 1
   for (int r = rb + (lane >> 1); r < re && b < B; r += 16) {
     const size_t kidx = (((size_t)(tg_ + 1) * 2 + 0) * B + b) * P + r;
     const bool keep = io.prenet_keep ? (io.prenet_keep[kidx] != 0) : rng_keep(io.seed, kidx, d.p_prenet);
-    const float v = y_s[j * YS + r - pr0];
-    st_cluster_all(p1_s + j * P + r, (v > 0.f && keep) ? v * pscale : 0.f);
+    const float v = y1[j * YS + r - pr0];
+    st_async_all(p1_s + j * P + r, (v > 0.f && keep) ? v * pscale : 0.f, p1_bar);
   }
   mark(5);
-  side_cluster_sync(sm.bars + 2 * D2_STAGES + 2, cphase);
+  tc::mbar_wait_cluster(p1_bar, cphase);
+  cphase ^= 1u;
   const long long pa = (long long)D2_BP * d.KattP;
   __nv_bfloat16* xa = s.xatt + (size_t)nxt * 2 * pa;   // next frame's attention-LSTM input, prenet columns
   const bool vec = (rq & 7) == 0 && (d.KattP & 7) == 0;
-  if ((P >> 2) <= 64) rows_short<6, 2>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y_s, pr0, YS);
-  else rows_dot2(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y_s, pr0, YS);
+  if ((P >> 2) <= 64) rows_short<6, 2, false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
+  else rows_dot2<false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
 #pragma unroll 1
   for (int r = rb + (lane >> 1); r < re; r += 16) {
     float v = 0.f;
     if (b < B) {
       const size_t kidx = (((size_t)(tg_ + 1) * 2 + 1) * B + b) * P + r;
       const bool keep = io.prenet_keep ? (io.prenet_keep[kidx] != 0) : rng_keep(io.seed, kidx, d.p_prenet);
-      v = y_s[j * YS + r - pr0];
+      v = y2[j * YS + r - pr0];
       v = (v > 0.f && keep) ? v * pscale : 0.f;
       if (!vec) store_split(xa, pa, d.KattP, b, r, v);
     }
@@ -837,8 +837,9 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
     sm.c_dec[i] = s.rnn_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP];
   }
   if (tid == 0) {   // rendezvous of the side warps of the cluster (output stage)
-    tc::mbar_init(sm.bars + 2 * D2_STAGES + 1, D2_CLUSTER * 6);
-    tc::mbar_init(sm.bars + 2 * D2_STAGES + 2, D2_CLUSTER * 6);
+    tc::mbar_init(sm.bars + 2 * D2_STAGES + 1, 1);   // transaction barriers of the output stage's two exchanges
+    tc::mbar_init(sm.bars + 2 * D2_STAGES + 2, 1);
+    tc::mbar_init(sm.bars + 2 * D2_STAGES + 3, 1);   // bulk copy of the prenet layer-1 rows (output stage)
   }
   tg::Pipe pipe;
   tg::pipe_init(pipe, sm.bars, sm.stages, D2_STAGES, d.npass, sm.tmem_slot);   // fences the barrier inits
