@@ -142,7 +142,7 @@ __device__ __forceinline__ Smem carve(uint8_t* base, const D2Dims& d, int pre_f)
   s.h_s = reinterpret_cast<float*>(p);   p += 8 * D2_BP * 4;
   s.octx = reinterpret_cast<float*>(p);  p += 2 * 64 * 4;
   s.pre = reinterpret_cast<float*>(p);   p += (size_t)pre_f * 4;
-  s.bars = reinterpret_cast<uint64_t*>(p); p += (2 * D2_STAGES + 4) * 8;   // ring full/empty, accumulator, 2 side-warp rendezvous
+  s.bars = reinterpret_cast<uint64_t*>(p); p += (2 * D2_STAGES + 5) * 8;   // ring full/empty, accumulator, 3 output-stage barriers, location-term copy
   s.tmem_slot = reinterpret_cast<uint32_t*>(p);
   return s;
 }
@@ -399,29 +399,51 @@ __device__ void attention_precompute(const D2Dims& d, const D2State& s, const D2
 // normalises the full row and reduces its slice of the context columns.
 // Scratch (floats, in the idle TMA ring): q[A] | qh[8A] | wp[Lc+32] | wc[Lc+32] | fs[Lc][36] | e_slice[Lc] |
 //                                         e_full[L] | red[64] | cred[4*cols] | xs[Lc][A]
+struct AttScratch { float *q_s, *qh, *wp, *wc, *fs, *e_slice, *e_full, *red, *cred, *xs_s; };
+__device__ __forceinline__ AttScratch att_scratch(float* scratch, int L, int A, int EF, int S) {
+  const int Lc = (L + S - 1) / S;
+  AttScratch a;
+  a.q_s = scratch;
+  a.qh = a.q_s + A;                            // eight group sums of the per-CTA query partials
+  a.wp = a.qh + 8 * A;                         // previous / cumulative weights with a 15-tap halo
+  a.wc = a.wp + ((Lc + 35) & ~3);
+  a.fs = a.wc + ((Lc + 35) & ~3);              // [Lc][36] conv features (row stride 36: conflict-free float4 rows)
+  a.e_slice = a.fs + (size_t)Lc * 36;
+  a.e_full = a.e_slice + ((Lc + 3) & ~3);
+  a.red = a.e_full + ((L + 3) & ~3);
+  a.cred = scratch + (((a.red + 64) - scratch + 3) & ~3);
+  a.xs_s = a.cred + 4 * (size_t)((((EF + S - 1) / S) + 3) & ~3);   // [Lc][A] staged location term (precompute path)
+  return a;
+}
+// Location term of this CTA's attention slice (attention_precompute left it in L2) -> shared memory, as ONE bulk copy issued by
+// one thread as soon as the attention-LSTM GEMM has released the stage ring: it lands behind the LSTM tail and the grid barrier
+// instead of at the head of the attention phase.  Completion: transaction barrier `bar` (one phase per frame).
+__device__ __forceinline__ void attention_prefetch(const D2Dims& d, const D2State& s, const D2IO& io, float* scratch, int part, int S, int t_out,
+                                                   uint64_t* bar, bool fence) {
+  const int L = d.L, A = d.A;
+  const int Lc = (L + S - 1) / S, l0 = part * Lc, nl = max(0, min(L, l0 + Lc) - l0);
+  if (nl == 0) return;
+  float* xs_s = att_scratch(scratch, L, A, d.EF, S).xs_s;
+  const float* xin = s.accpm + ((io.hist ? (size_t)t_out * 128 : 0) + blockIdx.x) * Lc * A;
+  // The source was written by generic stores of this CTA's side warps.  Normally a grid barrier (which carries the proxy fence)
+  // lies between them and this copy; `fence` is set when the term was computed beside the GEMM that has just ended.
+  if (fence) asm volatile("fence.proxy.async;" ::: "memory");
+  tc::mbar_arrive_expect_tx(bar, (uint32_t)(nl * A * 4));
+  tc::bulk_load_1d(xs_s, xin, (uint32_t)(nl * A * 4), bar);
+}
+
 #define ATT_MARK(slot) do { if (blockIdx.x == 0 && threadIdx.x == 0 && s.prof) { const long long now_ = clock64(); s.prof[slot] += (unsigned long long)(now_ - *prof_last); *prof_last = now_; } } while (0)
 __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& io, const Smem& sm, float* scratch, bool active,
-                                int b, int part, int S, int cur, int nxt, int t_out, uint32_t mbits, long long* prof_last) {
+                                int b, int part, int S, int cur, int nxt, int t_out, uint32_t mbits, int Leff, uint64_t* xbar, uint32_t xphase,
+                                long long* prof_last) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int L = d.L, A = d.A, EF = d.EF;
   const int Lc = (L + S - 1) / S, l0 = part * Lc, l1 = min(L, l0 + Lc), nl = max(0, l1 - l0);
-  float* q_s = scratch;
-  float* qh = q_s + A;                            // eight group sums of the per-CTA query partials
-  float* wp = qh + 8 * A;                         // previous / cumulative weights with a 15-tap halo
-  float* wc = wp + ((Lc + 35) & ~3);
-  float* fs = wc + ((Lc + 35) & ~3);            // [Lc][36] conv features (row stride 36: conflict-free float4 rows)
-  float* e_slice = fs + (size_t)Lc * 36;
-  float* e_full = e_slice + ((Lc + 3) & ~3);
-  float* red = e_full + ((L + 3) & ~3);
-  float* cred = scratch + (((red + 64) - scratch + 3) & ~3);
-  float* xs_s = cred + 4 * (size_t)((((EF + S - 1) / S) + 3) & ~3);   // [Lc][A] staged location term (precompute path)
+  const AttScratch as = att_scratch(scratch, L, A, EF, S);
+  float *q_s = as.q_s, *qh = as.qh, *wp = as.wp, *wc = as.wc, *fs = as.fs, *e_slice = as.e_slice, *e_full = as.e_full, *red = as.red,
+        *cred = as.cred, *xs_s = as.xs_s;
   if (active) {
-    if (io.precompute) {  // all 16-byte chunks of this CTA's location term in flight at once, overlapped with the query sum below
-      const float* xin = s.accpm + ((io.hist ? (size_t)t_out * 128 : 0) + blockIdx.x) * Lc * A;
-#pragma unroll 1
-      for (int i = tid; i < nl * (A >> 2); i += D2_THREADS) cp_async16(xs_s + (size_t)i * 4, xin + (size_t)i * 4);
-      cp_async_commit();
-    }
+    // (precompute path: the location term is already on its way into xs_s, see attention_prefetch)
     const float* wprev = s.w_prev + ((size_t)cur * D2_BP + b) * L;
     const float* wcum = s.w_cum + ((size_t)cur * D2_BP + b) * L;
     {  // processed query = sum of the 128 per-CTA partials, always in the same order (bit-deterministic): eight groups of 16 CTAs,
@@ -459,34 +481,36 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
       // energies from the precomputed location term (attention_precompute): e[l] = sum_a v[a] tanh(q[a] + x[l][a]), read from
       // the shared-memory copy; two positions per pass in a compact loop (an 8-position unrolled body does not fit the
       // instruction cache and ran at 3-4 cycles per instruction)
-      cp_async_wait<0>();
+      if (nl > 0) tc::mbar_wait(xbar, xphase);   // the location term has landed (attention_prefetch)
       __syncthreads();
       ATT_MARK(10);
-      const int a4 = lane * 4;
-      const bool lane_on = a4 < A;
-      const int ac = lane_on ? a4 : 0;
-      const float4 q4 = *reinterpret_cast<const float4*>(q_s + ac);
-      const float4 v4 = *reinterpret_cast<const float4*>(sm.v + ac);
-      const unsigned char* mk = io.mask + (size_t)b * L;
-      constexpr int NW = D2_THREADS / 32;
+      // thread = (position, quarter of the attention dims): 32 tanh terms per thread with independent chains, the four quarter
+      // sums meet in two shuffles (a warp per position spent more time in the 5-step warp reduction than in the tanh terms)
+      // Rows are unpadded (one bulk copy): odd positions walk their 16-byte chunks in swapped pairs, so the eight lanes of a
+      // quarter-warp (2 positions x 4 quarters) still touch eight different bank groups.
+      const int q = tid & 3, pp = tid >> 2, sw = pp & 1;
+      constexpr int PPP = D2_THREADS / 4;   // positions per pass
+      uint32_t mb = mbits;
 #pragma unroll 1
-      for (int l = warp, k = 0; l < nl; l += 2 * NW, ++k) {
-        const int lb = l + NW;
-        const float4 xa = *reinterpret_cast<const float4*>(xs_s + (size_t)l * A + ac);
-        const float4 xb = *reinterpret_cast<const float4*>(xs_s + (size_t)min(lb, nl - 1) * A + ac);
-        float ea = v4.x * tanh_fast(q4.x + xa.x), eb = v4.x * tanh_fast(q4.x + xb.x);
-        ea = fmaf(v4.y, tanh_fast(q4.y + xa.y), ea); eb = fmaf(v4.y, tanh_fast(q4.y + xb.y), eb);
-        ea = fmaf(v4.z, tanh_fast(q4.z + xa.z), ea); eb = fmaf(v4.z, tanh_fast(q4.z + xb.z), eb);
-        ea = fmaf(v4.w, tanh_fast(q4.w + xa.w), ea); eb = fmaf(v4.w, tanh_fast(q4.w + xb.w), eb);
-        ea = warp_sum(lane_on ? ea : 0.f);
-        eb = warp_sum(lane_on ? eb : 0.f);
-        // masked_fill (model/attention.py:63): the mask bits of this warp's first 32 positions were read once at kernel start
-        const bool ma = 2 * k < 32 ? ((mbits >> (2 * k)) & 1u) != 0u : (mk[l0 + l] != 0);
-        const bool mb = 2 * k + 1 < 32 ? ((mbits >> (2 * k + 1)) & 1u) != 0u : (mk[l0 + min(lb, nl - 1)] != 0);
-        if (lane == 0) {
-          e_slice[l] = ma ? -INFINITY : ea;
-          if (lb < nl) e_slice[lb] = mb ? -INFINITY : eb;
+      for (int l = pp; l - pp < nl; l += PPP, mb >>= 1) {
+        const float* xr = xs_s + (size_t)l * A;
+        float e = 0.f;
+        if (l < nl)   // (whole warps drop out of the last pass: a warp covers 8 consecutive positions)
+#pragma unroll 4
+        for (int i = 0; i < (A >> 4); ++i) {
+          const int a = 4 * q + 16 * (i ^ sw);
+          const float4 x4 = *reinterpret_cast<const float4*>(xr + a);
+          const float4 q4 = *reinterpret_cast<const float4*>(q_s + a);
+          const float4 v4 = *reinterpret_cast<const float4*>(sm.v + a);
+          e = fmaf(v4.x, tanh_fast(q4.x + x4.x), e);
+          e = fmaf(v4.y, tanh_fast(q4.y + x4.y), e);
+          e = fmaf(v4.z, tanh_fast(q4.z + x4.z), e);
+          e = fmaf(v4.w, tanh_fast(q4.w + x4.w), e);
         }
+        e += __shfl_xor_sync(0xffffffffu, e, 1);
+        e += __shfl_xor_sync(0xffffffffu, e, 2);
+        // masked_fill (model/attention.py:63): the mask bits of this thread's positions were read once at kernel start
+        if (q == 0 && l < nl) e_slice[l] = (mb & 1u) ? -INFINITY : e;
       }
     } else {
     // location conv (model/attention.py:54): warp task = (32 positions, 8 filters); lane = position
@@ -580,18 +604,23 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
     const uint32_t my_rank = tc::cluster_ctarank();
     const uint32_t base_rank = my_rank - (uint32_t)part;
     const uint32_t ea = tc::smem_u32(e_slice);
+    // Softmax over the full row (model/attention.py:65).  Every thread keeps to its own positions l = tid, tid + 256, ... through
+    // the three passes, so only the two block-wide reductions and the hand-over to the context step need a CTA barrier.
+    float mx = -INFINITY;
 #pragma unroll 1
     for (int l = tid; l < L; l += D2_THREADS) {
       const int pr = l / Lc, li = l - pr * Lc;
       float v;
       asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(tc::mapa(ea + 4u * (uint32_t)li, base_rank + (uint32_t)pr)) : "memory");
       e_full[l] = v;
+      mx = fmaxf(mx, v);
     }
+    mx = warp_max(mx);
+    if (lane == 0) red[warp] = mx;
     __syncthreads();
-    float mx = -INFINITY;
-#pragma unroll 1
-    for (int l = tid; l < L; l += D2_THREADS) mx = fmaxf(mx, e_full[l]);
-    mx = block_reduce(mx, red, true);
+    mx = red[0];
+#pragma unroll
+    for (int i = 1; i < D2_THREADS / 32; ++i) mx = fmaxf(mx, red[i]);
     float sum = 0.f;
 #pragma unroll 1
     for (int l = tid; l < L; l += D2_THREADS) {
@@ -599,7 +628,12 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
       e_full[l] = p;
       sum += p;
     }
-    sum = block_reduce(sum, red + 32, false);
+    sum = warp_sum(sum);
+    if (lane == 0) red[32 + warp] = sum;
+    __syncthreads();
+    sum = red[32];
+#pragma unroll
+    for (int i = 1; i < D2_THREADS / 32; ++i) sum += red[32 + i];
     const float inv = 1.0f / sum;
 #pragma unroll 1
     for (int l = tid; l < L; l += D2_THREADS) {
@@ -619,11 +653,8 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
     const int nq = max(0, (c1 - c0 + 3) >> 2);
     const float* mem = io.memory + (size_t)b * L * EF;
     const int lg = tid >> 6, cq0 = tid & 63;
-    const unsigned char* mk2 = io.mask + (size_t)b * L;
-    int Leff = 0;  // positions beyond the last unmasked one carry weight exactly 0 (softmax of -inf): skip them
-#pragma unroll 1
-    for (int l = tid; l < L; l += D2_THREADS) if (mk2[l] == 0) Leff = max(Leff, l + 1);
-    Leff = (int)block_reduce((float)Leff, red, true);
+    // (Leff: positions beyond the last unmasked one carry weight exactly 0 (softmax of -inf) and are skipped; the padding mask
+    //  does not change during a launch, so the kernel computes it once)
 #pragma unroll 1
     for (int cq = cq0; cq < nq; cq += 64) {
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -840,11 +871,13 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
     tc::mbar_init(sm.bars + 2 * D2_STAGES + 1, 1);   // transaction barriers of the output stage's two exchanges
     tc::mbar_init(sm.bars + 2 * D2_STAGES + 2, 1);
     tc::mbar_init(sm.bars + 2 * D2_STAGES + 3, 1);   // bulk copy of the prenet layer-1 rows (output stage)
+    tc::mbar_init(sm.bars + 2 * D2_STAGES + 4, 1);   // bulk copy of the location term (attention_prefetch)
   }
   tg::Pipe pipe;
   tg::pipe_init(pipe, sm.bars, sm.stages, D2_STAGES, d.npass, sm.tmem_slot);   // fences the barrier inits
   tc::cluster_sync();
 
+  uint64_t* xs_bar = sm.bars + 2 * D2_STAGES + 4;
   GridBar bar{s.barrier, s.barrier + 1, gridDim.x, 0u};
   long long prof_last = clock64();
   auto prof_mark = [&](int slot) {
@@ -852,12 +885,20 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
   };
   const int att_b = blockIdx.x / S, att_part = blockIdx.x % S;
   const bool att_active = att_b < B;
-  uint32_t att_mbits = 0;   // padding-mask bits of the positions this warp owns in the energy step: bit j = position warp + 8 j
+  uint32_t att_mbits = 0;   // padding-mask bits of the positions this thread owns in the energy step: bit k = position (tid >> 2) + 64 k
+  int att_leff = 0;         // 1 + last unmasked position of this CTA's utterance: the context sum stops there
   if (att_active) {
     const int Lc_ = (d.L + S - 1) / S, l0_ = att_part * Lc_, nl_ = max(0, min(d.L, l0_ + Lc_) - l0_);
-    const int pos = (tid >> 5) + (D2_THREADS / 32) * (tid & 31);
-    const bool mk_ = pos < nl_ && io.mask[(size_t)att_b * d.L + l0_ + pos] != 0;
-    att_mbits = __ballot_sync(0xffffffffu, mk_);
+    const unsigned char* mk_ = io.mask + (size_t)att_b * d.L;
+#pragma unroll 1
+    for (int k = 0; k < 32; ++k) {
+      const int pos = (tid >> 2) + (D2_THREADS / 4) * k;
+      if (pos < nl_ && mk_[l0_ + pos] != 0) att_mbits |= 1u << k;
+    }
+    int le = 0;
+#pragma unroll 1
+    for (int l = tid; l < d.L; l += D2_THREADS) if (mk_[l] == 0) le = max(le, l + 1);
+    att_leff = (int)block_reduce((float)le, reinterpret_cast<float*>(sm.part), true);   // (the partial buffer is idle here)
   }
   const int nkb_att = d.KattP / TG_BK, nkb_dec = d.KdecP / TG_BK;
   const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
@@ -919,11 +960,13 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
                 s.sav_att ? s.sav_att + (size_t)tg_ * 5 * d.H * D2_BP : nullptr, sm.h_s);
       prof_mark(0);
       query_partial(sm.h_s, sm.wq, d.A, B, s.qpart + (size_t)blockIdx.x * d.A, (size_t)128 * d.A);
+      // the stage ring has been idle since the GEMM ended: the location term of this CTA's attention slice comes in behind the barrier
+      if (io.precompute && att_active && tid == 32) attention_prefetch(d, s, io, scratch, att_part, S, tg_, xs_bar, do_pre && !split);
       if (!(alive = bar.sync(fail, true))) break;
       prof_mark(1);
     }
     // ================= location-sensitive attention (model/attention.py:54-67, model/decoder.py:90)
-    attention_phase(d, s, io, sm, scratch, att_active, att_b, att_part, S, cur, nxt, tg_, att_mbits, &prof_last);
+    attention_phase(d, s, io, sm, scratch, att_active, att_b, att_part, S, cur, nxt, tg_, att_mbits, att_leff, xs_bar, (uint32_t)(t & 1), &prof_last);
     if (!(alive = bar.sync(fail, true))) break;
     prof_mark(2);
     // ================= decoder LSTMCell (model/decoder.py:94-101); the next frame's location term runs beside its GEMM
@@ -985,7 +1028,7 @@ bool d2_precompute_fits(const D2Dims& d) {
 
 size_t d2_smem_bytes(const D2Dims& d) {
   return 1024 + (size_t)D2_STAGES * TG_STAGE_BYTES + TG_M * TG_PART_LD * 4 + 2 * 8 * D2_BP * 4 + 2 * D2_LOC_KP * D2_LOC_F * 4 +
-         (size_t)d.A * D2_LOC_F * 4 + d.A * 4 + 8 * d.A * 4 + 8 * D2_BP * 4 + 2 * 64 * 4 + (2 * D2_STAGES + 4) * 8 + 64;
+         (size_t)d.A * D2_LOC_F * 4 + d.A * 4 + 8 * d.A * 4 + 8 * D2_BP * 4 + 2 * 64 * 4 + (2 * D2_STAGES + 5) * 8 + 64;
 }
 
 static int launch_cfg(const D2Dims& d, cudaLaunchConfig_t* cfg, cudaLaunchAttribute* at, size_t smem, cudaStream_t st) {

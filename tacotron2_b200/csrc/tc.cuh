@@ -34,6 +34,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 // Bounded wait: returns false (and the caller aborts the kernel) instead of hanging the GPU on a bug.
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
+#pragma unroll 1   // the compiler otherwise unrolls the poll 64x (1.3 KB per wait site in an instruction-cache-bound kernel)
   for (uint32_t i = 0; i < (1u << 24); ++i)
     if (mbar_try_wait(bar, parity)) return true;
   return false;
@@ -45,6 +46,7 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 __device__ __forceinline__ bool mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+#pragma unroll 1
   for (uint32_t i = 0; i < (1u << 24); ++i) {
     uint32_t ok;
     asm volatile(
