@@ -231,6 +231,41 @@ def melspec_bench(dev, steps=5):
             "achieved_gbs": gbs, "hbm_peak_gbs": peak, "frac_of_hbm": gbs / peak}
 
 
+def collate_bench(dev, steps=20):
+    """Batch assembly of one C3-sized batch: 64 ragged items (<= 800 frames, <= 150 characters), items
+    resident in HBM; one t2_collate launch pads characters and mels and writes the gate targets.  HBM-bound byte movement: achieved
+    = (valid bytes read + padded bytes written) / kernel time.  Beside it: the reference's own pad_sequence collate on the host."""
+    from tacotron2_b200.collate import CollatePlan
+    g = torch.Generator().manual_seed(3)
+    Ts = torch.randint(400, 801, (64,), generator=g).tolist()
+    Ls = torch.randint(75, 151, (64,), generator=g).tolist()
+    Ts[0], Ls[0] = 800, 150
+    mel_h = [torch.randn(t, 80, generator=g) for t in Ts]
+    chr_h = [torch.randint(1, 40, (l,), generator=g, dtype=torch.int64) for l in Ls]
+    plan = CollatePlan({"chars_idx": [c.to(dev) for c in chr_h], "mel_spectrogram": [m.to(dev) for m in mel_h]}, dev, gate_from="mel_spectrogram")
+    for _ in range(3):
+        plan.launch()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        plan.launch()
+    e1.record()
+    e1.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    t0 = time.perf_counter()
+    for _ in range(3):   # datasets/tts_dataloader.py:27-28 on the host cores
+        torch.nn.utils.rnn.pad_sequence(mel_h, batch_first=True), torch.nn.utils.rnn.pad_sequence(chr_h, batch_first=True)
+    cpu_ms = (time.perf_counter() - t0) / 3 * 1e3
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0))
+    except Exception:  # noqa: BLE001
+        peak = 6650.0
+    gbs = (plan.bytes_read + plan.bytes_written) / (ms * 1e-3) / 1e9
+    return {"workload": "64 ragged items (400..800 frames x 80 mels, 75..150 chars) -> padded chars, mels, gate targets; items resident",
+            "ms": ms, "bytes_read": plan.bytes_read, "bytes_written": plan.bytes_written, "achieved_gbs": gbs, "hbm_peak_gbs": peak,
+            "frac_of_hbm": gbs / peak, "cpu_pad_sequence_ms": cpu_ms, "note": "one launch, 20 MB: launch latency, not bandwidth, sets the time"}
+
+
 def train_bench(dev, rank, world, steps, warmup=3):
     """BASELINE.json metric, training half: mel frames/s of the whole training step (model/tts_model.py:165-202 +
     run/train.py:239-240 settings) on synthetic C3 batches; weak scaling (64 utterances per GPU), gradients averaged over NCCL."""
@@ -521,7 +556,7 @@ def main():
         line["config"]["phase_us_per_frame"] = str(e)
     if train is not None:
         line["train"] = train
-    extras = () if args.no_extras else (("melspec", melspec_bench), ("bf16_mode_us_per_decoder_step", bf16_mode_us_per_step),
+    extras = () if args.no_extras else (("melspec", melspec_bench), ("collate", collate_bench), ("bf16_mode_us_per_decoder_step", bf16_mode_us_per_step),
                                         ("torch_cuda_eager", torch_eager_cuda_step))
     for key, fn in extras:
         try:

@@ -185,6 +185,17 @@ int t2_clip_adam_step(int n_tensors, float* const* params, float* const* grads, 
 int t2_melspec(const float* wav, const long long* wav_len, int B, long long wav_stride, const float* window, const float* fb,
                const int* fb_range, int n_fft, int hop, int n_mels, float* out, int t_stride, long long* n_frames, void* stream);
 
+/* Batch assembly: `_collate` of datasets/tts_dataloader.py:8-35 -- nn.utils.rnn.pad_sequence(batch_first=True) over every data
+ * key of the batch (chars_idx (L,) int64, mel_spectrogram (T, n_mels) fp32, gate (T, 1) fp32, ...) -- plus the gate targets of
+ * datasets/tts_dataset.py:211-214 (ones, last valid frame 0), in one launch.  Field f: src[f] = the B items' rows concatenated
+ * (device memory, item b = rows off[f][b] .. off[f][b+1]), row_bytes[f] bytes per row (multiple of 4; any dtype),
+ * out[f] (B, max_rows[f], row_bytes[f]): rows beyond an item's length are zero.  The four tables are HOST arrays of n_fields
+ * entries (n_fields <= 8); off[f] points to (B+1) int64 on the device.  gate (B, gate_T) fp32 with gate_len (B) int64 on the
+ * device, or both NULL: gate[b][t] = 1 for t < gate_len[b]-1, else 0.  Asynchronous on `stream`; no allocation. */
+int t2_collate(int n_fields, const void* const* src, const long long* const* off, const long long* row_bytes,
+               const long long* max_rows, void* const* out, int B, const long long* gate_len, float* gate, long long gate_T,
+               void* stream);
+
 /* Debug: SM-clock cycles CTA 0 spent in each phase of the last decode call (host pointer, 16 slots;
  * synchronises the device).  Slots: 0 att-LSTM tail, 1 query, 2 attention tail, 3 dec-LSTM tail, 4 projection, 5 prenet1,
  * 6 prenet2, 7 extra barrier (T2B200_DEBUG_BARRIER), 8/9 att/dec gate GEMM, 10-14 attention conv/dense/sync/softmax/context. */

@@ -57,6 +57,7 @@ SIGNATURES = {
     "t2_loss_fwd_bwd": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _P, _LL, _P]),
     "t2_finalize_bwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P]),
     "t2_melspec": (_I, [_P, _P, _I, _LL, _P, _P, _P, _I, _I, _I, _P, _I, _P, _P]),
+    "t2_collate": (_I, [_I, _P, _P, _P, _P, _P, _I, _P, _P, _LL, _P]),
     "t2_clip_adam_chunks": (_LL, [_I, _P]),
     "t2_clip_adam_workspace_bytes": (_LL, [_I, _LL]),
     "t2_clip_adam_step": (_I, [_I, _P, _P, _P, _P, _P, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, _LL, _I, _P, _P,

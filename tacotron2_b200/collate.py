@@ -1,0 +1,132 @@
+"""GPU batch assembly behind the reference's collate interface (datasets/tts_dataloader.py:8-35).
+
+``collate(data, device)`` takes what the reference's ``_collate`` takes -- a list of ``(data, lengths, extra)`` dict triples as
+``TTSDataset.__getitem__`` returns them (datasets/tts_dataset.py:226-302) -- and returns the same ``(tts_data, tts_data_len,
+tts_data_extra)`` triple, with the padded batch built on the GPU by one ``t2_collate`` launch: each field's items are concatenated
+into one pinned host buffer, copied once, and padded on the device (rows beyond an item's length are zero, exactly
+``pad_sequence(batch_first=True)``).  ``gate`` may be omitted from the items: it is then generated on the device from the
+mel lengths (ones, last valid frame 0: datasets/tts_dataset.py:211-214).  No CPU fallback: without the CUDA library this raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from collections import defaultdict
+
+import torch
+
+from . import _lib
+
+MAX_FIELDS = 8
+
+
+def _table(ctype, vals):
+    return (ctype * len(vals))(*vals)
+
+
+class CollatePlan:
+    """One prepared ``t2_collate`` launch: the concatenated fields and offset tables are on the device, the outputs are allocated."""
+
+    def __init__(self, fields: dict, device, gate_from: str | None = None):
+        self.lib = _lib.load()
+        device = torch.device(device)
+        if device.type != "cuda":
+            raise RuntimeError("tacotron2_b200.collate: CUDA device required (no CPU fallback)")
+        names = list(fields)
+        if len(names) > MAX_FIELDS:
+            raise ValueError(f"at most {MAX_FIELDS} fields per launch")
+        self.device, self.B = device, (len(fields[names[0]]) if names else 0)
+        B = self.B
+        self.keep, src, off, rowb, maxr, outp, self.outs = [], [], [], [], [], [], {}
+        self.bytes_read = self.bytes_written = 0
+        gate_len = None
+        for k in names:
+            items = fields[k]
+            assert len(items) == B, f"field {k}: {len(items)} items, expected {B}"
+            v0 = items[0]
+            trailing = tuple(v0.shape[1:])
+            row_elems = 1
+            for t in trailing:
+                row_elems *= int(t)
+            row_bytes = v0.element_size() * row_elems
+            if row_bytes % 4:
+                raise ValueError(f"field {k}: row size {row_bytes} B is not a multiple of 4")
+            lens = [int(v.shape[0]) for v in items]
+            o = torch.zeros(B + 1, dtype=torch.int64)
+            o[1:] = torch.tensor(lens).cumsum(0)
+            cat = torch.cat([v.reshape(v.shape[0], -1) for v in items]).contiguous()
+            if cat.device.type != "cuda":
+                cat = cat.pin_memory().to(device, non_blocking=True)
+            od = o.to(device, non_blocking=True)
+            out = torch.empty((B, max(lens)) + trailing, dtype=v0.dtype, device=device)
+            self.keep += [cat, od]
+            src.append(_lib.ptr(cat)); off.append(_lib.ptr(od)); rowb.append(row_bytes); maxr.append(max(lens)); outp.append(_lib.ptr(out))
+            self.outs[k] = out
+            self.bytes_read += sum(lens) * row_bytes
+            self.bytes_written += out.numel() * out.element_size()
+            if k == gate_from:
+                gate_len = (od[1:] - od[:-1]).contiguous()
+                self.keep.append(gate_len)
+        self.gate = None
+        if gate_from is not None:
+            assert gate_len is not None, f"gate_from={gate_from!r} is not a field"
+            self.gate = torch.empty((B, self.outs[gate_from].shape[1], 1), dtype=torch.float32, device=device)
+            self.outs["gate"] = self.gate
+            self.bytes_written += self.gate.numel() * 4
+        self.gate_len = gate_len if self.gate is not None else None
+        self.tables = (_table(C.c_void_p, src), _table(C.c_void_p, off), _table(C.c_longlong, rowb), _table(C.c_longlong, maxr),
+                       _table(C.c_void_p, outp))
+        self.n = len(names)
+
+    def launch(self, stream=None):
+        st = stream if stream is not None else torch.cuda.current_stream(self.device).cuda_stream
+        t = [C.cast(x, C.c_void_p) for x in self.tables]
+        _lib.check(self.lib.t2_collate(self.n, t[0], t[1], t[2], t[3], t[4], self.B, _lib.ptr(self.gate_len) if self.gate is not None else None,
+                                       _lib.ptr(self.gate) if self.gate is not None else None,
+                                       self.gate.shape[1] if self.gate is not None else 0, st), "t2_collate")
+        return self.outs
+
+
+def pad_fields(fields: dict, device, gate_from: str | None = None, stream=None):
+    """fields: name -> list of B tensors (same dtype and trailing shape, ragged first dim).  Returns name -> (B, max, ...) device
+    tensors; with ``gate_from`` = a field name also ``"gate"`` (B, max, 1) generated from that field's lengths."""
+    return CollatePlan(fields, device, gate_from).launch(stream)
+
+
+def collate(data, device="cuda:0"):
+    """Drop-in for ``_collate`` (datasets/tts_dataloader.py:8-35) that assembles the batch on the GPU."""
+    cols, lens, extra = defaultdict(list), defaultdict(list), defaultdict(list)
+    for d, n, e in data:
+        for k, v in d.items():
+            cols[k].append(v)
+        for k, v in n.items():
+            lens[k].append(v)
+        for k, v in e.items():
+            extra[k].append(v)
+    gen_gate = "gate" not in cols and "mel_spectrogram" in cols
+    tts_data = pad_fields(dict(cols), device, gate_from="mel_spectrogram" if gen_gate else None)
+    tts_data_len = {k: torch.stack(v).squeeze(1).to(device, non_blocking=True) for k, v in lens.items()}
+    return tts_data, tts_data_len, dict(extra)
+
+
+def TTSDataLoader(dataset, batch_size=1, num_workers=0, pin_memory=False, pin_memory_device="", shuffle=None, prefetch_factor=None,
+                  persistent_workers=False, drop_last=True, device="cuda:0"):
+    """datasets/tts_dataloader.py:38-60 with the padding moved to the GPU: the worker processes only return the item triples
+    (no pad_sequence on the host), the batch is assembled by ``collate`` in the consuming process."""
+    from torch.utils.data import DataLoader
+
+    loader = DataLoader(dataset, batch_size=batch_size, collate_fn=(lambda items: items) if batch_size > 1 else None,
+                        num_workers=num_workers, pin_memory=pin_memory, pin_memory_device=pin_memory_device, shuffle=shuffle,
+                        prefetch_factor=prefetch_factor if num_workers > 0 else None, persistent_workers=persistent_workers,
+                        drop_last=drop_last)
+    if batch_size <= 1:
+        return loader
+
+    class _GpuBatches:
+        def __len__(self):
+            return len(loader)
+
+        def __iter__(self):
+            for items in loader:
+                yield collate(items, device)
+
+    return _GpuBatches()

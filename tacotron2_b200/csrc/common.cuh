@@ -74,7 +74,9 @@ struct GridBar {
   unsigned nblocks;
   unsigned epoch;
   __device__ bool sync(bool fail, bool wrote_x) {
-    if (wrote_x) asm volatile("fence.proxy.async;" ::: "memory");
+    // the GEMM operands the CTA wrote with generic stores are read by TMA (async proxy) after this barrier; they live in global
+    // memory, so the fence is restricted to that state space (ncu: the unrestricted form was 4.8% of all stall samples)
+    if (wrote_x) asm volatile("fence.proxy.async.global;" ::: "memory");
     fail = __syncthreads_or(fail ? 1 : 0) != 0;   // a pipeline timeout seen by any role thread aborts the grid
     __shared__ int ok_s;
     if (threadIdx.x == 0) {

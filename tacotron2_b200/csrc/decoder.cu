@@ -194,11 +194,20 @@ __device__ __forceinline__ void lstm_tail(const float* part, uint32_t rank, int 
   const int ul = threadIdx.x >> 5, bp = threadIdx.x & 31;
   const int u = unit0 + ul;
   float2 pre[4];
+  {  // all sixteen remote loads of the split-K exchange in flight before the first sum (one DSMEM round trip, not four)
+    float2 pv[4][4];
 #pragma unroll
-  for (int g = 0; g < 4; ++g) {
-    pre[g] = tg::reduce4(part, 32 * (int)rank + g * 8 + ul, 2 * bp);
-    const float bv = __ldg(bias + g * H + u);
-    pre[g].x += bv; pre[g].y += bv;
+    for (int g = 0; g < 4; ++g) {
+      const uint32_t a = tc::smem_u32(part + (size_t)(32 * (int)rank + g * 8 + ul) * TG_PART_LD + 2 * bp);
+#pragma unroll
+      for (uint32_t r = 0; r < 4; ++r) pv[g][r] = tc::ld_dsmem2(tc::mapa(a, r));
+    }
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {   // same order as tg::reduce4: ranks 0..3
+      const float bv = __ldg(bias + g * H + u);
+      pre[g].x = ((pv[g][0].x + pv[g][1].x) + pv[g][2].x) + pv[g][3].x + bv;
+      pre[g].y = ((pv[g][0].y + pv[g][1].y) + pv[g][2].y) + pv[g][3].y + bv;
+    }
   }
   float hv[2], sv[5][2];
 #pragma unroll
@@ -694,7 +703,8 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
     }
   }
   ATT_MARK(14);
-  tc::cluster_sync();  // peers are done reading this CTA's energy slice before the scratch is reused
+  // No cluster barrier here: the caller's grid barrier follows, and the scratch (the peers read this CTA's energy slice from it)
+  // is not written again before that barrier has been passed by every CTA.
 }
 
 // ------------------------------------------------------------------------------------------
