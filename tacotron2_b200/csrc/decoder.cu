@@ -10,6 +10,10 @@
 // cell states live in shared memory, hidden states travel as bf16 (hi,lo) pairs for the next GEMM.
 #include "decoder.cuh"
 
+#ifndef D2_ENERGY_UNROLL
+#define D2_ENERGY_UNROLL 2   // 16-byte chunks (4 tanh terms each) per thread in flight in the energy step; 2, 4, 8 measured within noise, 2 is the smallest code
+#endif
+constexpr int kEnergyUnroll = D2_ENERGY_UNROLL;
 #define D2_LOC_KP 32   // location-conv taps padded to a multiple of 8 (zero tap) for the blocked conv loop
 
 namespace {
@@ -505,7 +509,7 @@ __device__ void attention_phase(const D2Dims& d, const D2State& s, const D2IO& i
         const float* xr = xs_s + (size_t)l * A;
         float e = 0.f;
         if (l < nl)   // (whole warps drop out of the last pass: a warp covers 8 consecutive positions)
-#pragma unroll 4
+#pragma unroll kEnergyUnroll
         for (int i = 0; i < (A >> 4); ++i) {
           const int a = 4 * q + 16 * (i ^ sw);
           const float4 x4 = *reinterpret_cast<const float4*>(xr + a);
@@ -949,16 +953,18 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
       out_pending = false;
       if (split) {
         if (!(alive = bar.sync(fail, true))) break;
-        if (io.stop_enabled) {  // model/tacotron2.py:321-322: leave once every utterance has fired its stop gate
-          int mine = 1;
+        // model/tacotron2.py:321-322: leave once every utterance has fired its stop gate.  The flags are read here and judged after
+        // the prenet K-block below (which has to run anyway: its weight box is already in flight and its stage must be completed),
+        // so the L2 round trip of the flag loads hides behind it.
+        int mine = 1;
+        if (io.stop_enabled) {
 #pragma unroll 1
           for (int b = tid; b < B; b += D2_THREADS) mine &= (ld_acquire_u32((const unsigned*)s.done + b) != 0u);
-          if (__syncthreads_and(mine)) stop = true;
         }
-        // (also when stopping: the weight box of this K-block is already in flight and its stage must be completed)
         if (!tg::gemm(pipe, &maps.w_att, tile * TG_M, nkb_att, xs, (int)rank, min(npre, nkb_att), D2_CLUSTER, 0u, tg::NoSide{},
                       io.w_policy_att, 1u, -1, gok && (int)rank < npre))
           fail = true;
+        if (io.stop_enabled && __syncthreads_and(mine)) stop = true;
         prof_mark(7);
         if (stop) break;
       }
