@@ -29,8 +29,8 @@ B, L, T = 64, 200, 1000
 METRIC, UNIT = "mel_frames_per_sec_ar_decode", "frames/s"
 # dram__bytes_read.sum + dram__bytes_write.sum of decoder_persistent_kernel from the committed ncu --set full capture, per decoded
 # frame (the capture is a 200-frame launch of the same C2 batch; traffic is linear in the frame count)
-NCU_DRAM_BYTES_PER_FRAME = (13.768351e9 + 49.030912e6) / 200
-NCU_DRAM_SOURCE = "profiles/r01_v9_decoder_fwd_full_raw.csv (ncu --set full, 200-frame launch; per frame x frames)"
+NCU_DRAM_BYTES_PER_FRAME = (13.752162e9 + 50.168320e6) / 200
+NCU_DRAM_SOURCE = "profiles/r01_v12_decoder_fwd_full_raw.csv (ncu --set full, 200-frame launch; per frame x frames)"
 WORKLOAD = "C2: vanilla-ljspeech-stop AR inference, batch 64 x 200 chars x 1000 frames, fp32, stop gate evaluated (never fires)"
 # kernels launched by one Tacotron2.forward (AR): embed 1, encoder conv 3, BiLSTM input proj 1, BiLSTM 1, memory split 1,
 # att_encoder 1, persistent decoder 1, mel split 1, postnet conv 5, finalize 1  (memsets / memcpys not counted)
@@ -231,6 +231,38 @@ def melspec_bench(dev, steps=5):
             "achieved_gbs": gbs, "hbm_peak_gbs": peak, "frac_of_hbm": gbs / peak}
 
 
+def postnet_bench(dev, steps=10):
+    """The tensor-pipe piece of the path with the simplest roofline: Postnet.forward (model/postnet.py:51-52; five k=5 convs as
+    implicit GEMMs on tcgen05) on one C2-sized batch, 64 x 1000 frames, inputs resident.  FLOPs per frame 8.68 M (SURVEY 8d);
+    fp32-parity arithmetic issues three bf16 passes, so the tensor pipe executes 3x that -- both rates are reported against the
+    measured dense bf16 peak."""
+    from tacotron2_b200.model import Tacotron2
+    m = Tacotron2(**synth.VANILLA.kwargs()).to(dev).eval()
+    m.load_state_dict(synth.synth_state_dict(synth.VANILLA, seed=0))
+    x = torch.randn(B, 80, T, device=dev)
+    with torch.no_grad():
+        for _ in range(3):
+            y = m.postnet(x)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            y = m.postnet(x)
+        e1.record()
+        e1.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    assert y.shape == x.shape
+    flops = 2 * 5 * (80 * 512 + 3 * 512 * 512 + 512 * 80) * B * T
+    try:
+        pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        peak = float(pk.get("bf16_tflops_sustained", pk.get("bf16_tflops", 1342.0)))
+    except Exception:  # noqa: BLE001
+        peak = 1342.0
+    tf = flops / (ms * 1e-3) / 1e12
+    return {"workload": f"Postnet.forward eval, {B} x {T} frames (5 convs k=5, BN folded, tanh), fp32-parity = 3 bf16 passes; includes the two layout transposes",
+            "ms": ms, "frames_per_s": B * T / (ms * 1e-3), "algorithmic_tflops": tf, "issued_bf16_tflops": 3 * tf, "bound": "tensor",
+            "peak_tflops": peak, "frac_algorithmic": tf / peak, "frac_issued": 3 * tf / peak}
+
+
 def collate_bench(dev, steps=20):
     """Batch assembly of one C3-sized batch: 64 ragged items (<= 800 frames, <= 150 characters), items
     resident in HBM; one t2_collate launch pads characters and mels and writes the gate targets.  HBM-bound byte movement: achieved
@@ -263,7 +295,7 @@ def collate_bench(dev, steps=20):
     gbs = (plan.bytes_read + plan.bytes_written) / (ms * 1e-3) / 1e9
     return {"workload": "64 ragged items (400..800 frames x 80 mels, 75..150 chars) -> padded chars, mels, gate targets; items resident",
             "ms": ms, "bytes_read": plan.bytes_read, "bytes_written": plan.bytes_written, "achieved_gbs": gbs, "hbm_peak_gbs": peak,
-            "frac_of_hbm": gbs / peak, "cpu_pad_sequence_ms": cpu_ms, "note": "one launch, 20 MB: launch latency, not bandwidth, sets the time"}
+            "frac_of_hbm": gbs / peak, "cpu_pad_sequence_ms": cpu_ms, "note": "one launch moves 29 MB; repeated launches find the items in L2, and launch latency rather than bandwidth sets the time"}
 
 
 def train_bench(dev, rank, world, steps, warmup=3):
@@ -556,7 +588,7 @@ def main():
         line["config"]["phase_us_per_frame"] = str(e)
     if train is not None:
         line["train"] = train
-    extras = () if args.no_extras else (("melspec", melspec_bench), ("collate", collate_bench), ("bf16_mode_us_per_decoder_step", bf16_mode_us_per_step),
+    extras = () if args.no_extras else (("melspec", melspec_bench), ("collate", collate_bench), ("postnet", postnet_bench), ("bf16_mode_us_per_decoder_step", bf16_mode_us_per_step),
                                         ("torch_cuda_eager", torch_eager_cuda_step))
     for key, fn in extras:
         try:
