@@ -989,7 +989,7 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
     {
       const tg::XSrc xs{&maps.x_dec, cur * 2, &maps.x_dec, cur * 2, nkb_dec};
       const bool pre_next = io.precompute && att_active && t + 1 < io.n_steps;
-      const bool gok = tg::gemm(pipe, &maps.w_dec, tile * TG_M, nkb_dec, xs, (int)rank, nkb_dec, D2_CLUSTER, 64u,
+      const bool gok = tg::gemm(pipe, &maps.w_dec, tile * TG_M, nkb_dec, xs, (int)rank, nkb_dec, D2_CLUSTER, 128u,
                                 [&]() {
                                   if (has_out) proj_ctx_side(d, w, s, sm, rank, tile);
                                   if (pre_next) attention_precompute(d, s, io, sm, att_b, att_part, S, nxt, tg_ + 1);
@@ -997,7 +997,7 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
       pre_done = pre_next;
       if (!gok) fail = true;
       prof_mark(9);
-      tg::accum_to_smem(pipe, 64u, sm.part);
+      tg::accum_to_smem(pipe, 128u, sm.part);
       tc::cluster_sync();
       const HOut ho{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, io.hist ? nullptr : s.projin, d.KprojP, 0};
       if (io.hist) frames = t + 1;

@@ -11,7 +11,7 @@
 #define TG_W_TILE (TG_M * TG_BK * 2)  // bytes of one bf16 W tile (16 KB)
 #define TG_X_TILE (TG_N * TG_BK * 2)  // bytes of one bf16 x tile (8 KB)
 #define TG_STAGE_BYTES (2 * TG_W_TILE + 2 * TG_X_TILE)  // hi+lo of both operands (48 KB)
-#define TG_TMEM_COLS 128
+#define TG_TMEM_COLS 256   // two accumulators of 128 columns: [Whi*xhi + Wlo*xhi | Whi*xlo] each
 #define TG_PART_LD 68  // floats per row of the split-K partial buffer (64 + 4 pad: conflict-free float4 rows)
 
 #ifdef __CUDACC__
@@ -54,7 +54,7 @@ __device__ __forceinline__ void pipe_init(Pipe& p, uint64_t* bars, uint8_t* stag
 }
 
 // Runs the K-blocks kb = kb_begin, kb_begin+kb_stride, ... < kb_end of one 128-row tile into TMEM columns
-// [d_col, d_col+64).  All threads of the CTA must call it; returns false on a pipeline timeout.
+// [d_col, d_col+64) (bf16 mode) or [d_col, d_col+128) (fp32-parity mode, two half sums).  All threads of the CTA must call it; returns false on a pipeline timeout.
 // w_nkb > 0: W is stored tile-major ([tile][kb][128][64], every TMA box one contiguous 16 KB chunk) with w_nkb K-blocks per
 // tile; w_nkb == 0: W is a plain row-major [rows][K] matrix.
 // `side` runs on warps 2..7 (192 threads, named barrier 1 is theirs) while warps 0/1 stream and issue the GEMM: work that does not
@@ -106,7 +106,7 @@ __device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row
     }
   } else if (warp == 1 && lane == 0) {
     // ---------------- MMA issuer
-    const uint32_t idesc = tc::idesc_bf16_f32(TG_M, TG_N);
+    const uint32_t idesc = tc::idesc_bf16_f32(TG_M, TG_N), idesc2 = tc::idesc_bf16_f32(TG_M, 2 * TG_N);
     uint32_t acc = acc_init;
     for (int kb = kb_begin; kb < kb_end; kb += kb_stride) {
       if (!tc::mbar_wait(p.full + p.c_stage, p.c_phase)) { ok = false; break; }
@@ -118,9 +118,11 @@ __device__ __forceinline__ bool gemm(Pipe& p, const CUtensorMap* wmap, int w_row
       for (int k = 0; k < TG_BK / 16; ++k) {
         const uint64_t adv = (uint64_t)(k * 32 >> 4);  // 16 bf16 = 32 B along K inside the 128-B swizzle atom
         if (p.npass == 3) {
-          tc::umma_bf16(p.tmem + d_col, wlo + adv, xhi + adv, idesc, acc);
-          tc::umma_bf16(p.tmem + d_col, whi + adv, xlo + adv, idesc, 1u);
-          tc::umma_bf16(p.tmem + d_col, whi + adv, xhi + adv, idesc, 1u);
+          // The x stage holds the hi tile and the lo tile back to back (64 + 64 rows of one K-major swizzled tile): ONE N = 128
+          // MMA gives Whi*xhi in columns [0,64) and Whi*xlo in columns [64,128) and reads the Whi tile from shared memory once
+          // instead of twice; Wlo*xhi then adds into columns [0,64).  The epilogue sums the two halves (accum_to_smem).
+          tc::umma_bf16(p.tmem + d_col, whi + adv, xhi + adv, idesc2, acc);
+          tc::umma_bf16(p.tmem + d_col, wlo + adv, xhi + adv, idesc, 1u);
         } else {
           tc::umma_bf16(p.tmem + d_col, whi + adv, xhi + adv, idesc, acc);
         }
@@ -154,6 +156,13 @@ __device__ __forceinline__ void accum_to_smem(const Pipe& p, uint32_t d_col, flo
     const int lane0 = 32 * (warp & 3), col0 = 32 * (warp >> 2);
     float v[32];
     tc::tmem_ld32(p.tmem + ((uint32_t)lane0 << 16) + d_col + col0, v);
+    if (p.npass == 3) {   // fp32-parity mode: columns [64,128) hold the Whi*xlo part of the sum
+      float u[32];
+      tc::tmem_ld32(p.tmem + ((uint32_t)lane0 << 16) + d_col + TG_N + col0, u);
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] += u[i];
+    }
     tc::tmem_ld_wait();
     float* dst = part + (size_t)(lane0 + lane) * TG_PART_LD + col0;
 #pragma unroll
