@@ -29,8 +29,8 @@ B, L, T = 64, 200, 1000
 METRIC, UNIT = "mel_frames_per_sec_ar_decode", "frames/s"
 # dram__bytes_read.sum + dram__bytes_write.sum of decoder_persistent_kernel from the committed ncu --set full capture, per decoded
 # frame (the capture is a 200-frame launch of the same C2 batch; traffic is linear in the frame count)
-NCU_DRAM_BYTES_PER_FRAME = (13.752162e9 + 50.168320e6) / 200
-NCU_DRAM_SOURCE = "profiles/r01_v12_decoder_fwd_full_raw.csv (ncu --set full, 200-frame launch; per frame x frames)"
+NCU_DRAM_BYTES_PER_FRAME = (13.756307e9 + 81.929216e6) / 200
+NCU_DRAM_SOURCE = "profiles/r01_v13_decoder_fwd_full_raw.csv (ncu --set full, 200-frame launch; per frame x frames)"
 WORKLOAD = "C2: vanilla-ljspeech-stop AR inference, batch 64 x 200 chars x 1000 frames, fp32, stop gate evaluated (never fires)"
 # kernels launched by one Tacotron2.forward (AR): embed 1, encoder conv 3, BiLSTM input proj 1, BiLSTM 1, memory split 1,
 # att_encoder 1, persistent decoder 1, mel split 1, postnet conv 5, finalize 1  (memsets / memcpys not counted)
