@@ -386,7 +386,8 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
     }
   }
   ABW_MARK(7);
-  tc::cluster_sync();   // peers are done reading this CTA's d f rows before the scratch is reused
+  // No cluster barrier here: the caller's grid barrier follows, and the scratch (the peers read this CTA's d f rows from it) is not
+  // written again before every CTA has passed that barrier.
 }
 
 }  // namespace
