@@ -6,7 +6,9 @@
 // One CTA = 256 threads = MS_FPC consecutive frames of one utterance.  The samples the frames share (75 % overlap) are
 // staged once in shared memory with the reflect padding applied; two real frames are packed into one 1024-point complex
 // radix-4 Stockham FFT (5 passes, twiddles from a shared-memory table), unpacked to |X_a|, |X_b| for bins 0..512, and the
-// triangular mel filters are applied by one warp per (frame, mel) with the per-filter [lo,hi) bin range.
+// triangular mel filters are applied by one THREAD per (frame, mel) over the filter's [lo,hi) bin range, weights from a compact
+// shared-memory copy of the non-zero part of the filterbank (the kernel is instruction-issue bound: a warp per filter spent 45
+// instructions, most of them the warp reduction, on 6..40 multiply-adds).
 #include "../../include/t2b200.h"
 #include "common.cuh"
 
@@ -15,6 +17,8 @@
 #define MS_BINS 513
 #define MS_FPC 8          // frames per CTA (4 packed FFTs)
 #define MS_THREADS 256
+#define MS_FBC 1024       // capacity of the compact filterbank (sum of the filters' bin ranges; slaney 80 x 513: ~760)
+#define MS_MAXMEL 128
 
 namespace {
 
@@ -28,10 +32,12 @@ __global__ void __launch_bounds__(MS_THREADS) melspec_kernel(const float* __rest
                                                              float log_floor) {
   __shared__ float2 bufA[MS_NFFT];
   __shared__ float2 bufB[MS_NFFT];
-  __shared__ float2 tw[MS_NFFT];                                  // exp(-2 pi i m / 1024)
+  __shared__ float2 tw[3 * MS_NFFT / 4];                          // exp(-2 pi i m / 1024), m < 768 (largest index used: 3 * 255)
   __shared__ float samples[MS_NFFT + (MS_FPC - 1) * MS_HOP];
-  __shared__ float win[MS_NFFT];
   __shared__ float mag[2][MS_BINS + 3];
+  __shared__ float fbc[MS_FBC];            // non-zero ranges of the filters, back to back
+  __shared__ int fb_off[MS_MAXMEL + 1];    // start of filter m in fbc
+  __shared__ int fb_lo[MS_MAXMEL];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int b = blockIdx.y;
   const long long S = wav_len[b];
@@ -46,11 +52,37 @@ __global__ void __launch_bounds__(MS_THREADS) melspec_kernel(const float* __rest
     }
     return;
   }
-  for (int i = tid; i < MS_NFFT; i += MS_THREADS) {
-    float s, c;
-    sincospif(-2.0f * (float)i / (float)MS_NFFT, &s, &c);
-    tw[i] = make_float2(c, s);
-    win[i] = window[i];
+  {  // exp(-2 pi i m / 1024): one accurate sincos per thread (m < 256), the next two quadrants by rotation (x -i, x -1)
+    float sn, cs;
+    sincospif(-2.0f * (float)tid / (float)MS_NFFT, &sn, &cs);
+    tw[tid] = make_float2(cs, sn);
+    tw[tid + 256] = make_float2(sn, -cs);
+    tw[tid + 512] = make_float2(-cs, -sn);
+  }
+  // compact filterbank: filter m occupies fbc[fb_off[m] .. fb_off[m+1]) = fb[m][lo_m .. hi_m)
+  if (warp == 0) {
+    int run = 0;
+    for (int m0 = 0; m0 < n_mels; m0 += 32) {
+      const int m = m0 + lane;
+      const int lo = m < n_mels ? fb_range[2 * m] : 0, n = m < n_mels ? max(0, fb_range[2 * m + 1] - lo) : 0;
+      int inc = n;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+      }
+      if (m < n_mels) { fb_off[m] = run + inc - n; fb_lo[m] = lo; }
+      run += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    if (lane == 0) fb_off[n_mels] = run;
+  }
+  __syncthreads();
+  const bool fb_compact = fb_off[n_mels] <= MS_FBC;
+  if (fb_compact) {
+    for (int m = warp; m < n_mels; m += MS_THREADS / 32) {
+      const int o = fb_off[m], n = fb_off[m + 1] - o, lo = fb_lo[m];
+      for (int i = lane; i < n; i += 32) fbc[o + i] = __ldg(fb + (size_t)m * MS_BINS + lo + i);
+    }
   }
   const float* x = wav + (size_t)b * wav_stride;
   const long long base = (long long)f0 * MS_HOP - MS_NFFT / 2;
@@ -67,7 +99,7 @@ __global__ void __launch_bounds__(MS_THREADS) melspec_kernel(const float* __rest
     if (fa >= T && fa >= t_stride) break;
     // pack frame a (real) and frame b (imag)
     for (int i = tid; i < MS_NFFT; i += MS_THREADS) {
-      const float w = win[i];
+      const float w = __ldg(window + i);   // 4 KB, L1-resident
       bufA[i] = make_float2(samples[(2 * pair) * MS_HOP + i] * w, samples[(2 * pair + 1) * MS_HOP + i] * w);
     }
     __syncthreads();
@@ -104,14 +136,26 @@ __global__ void __launch_bounds__(MS_THREADS) melspec_kernel(const float* __rest
       mag[1][k] = sqrtf(br * br + bi * bi);
     }
     __syncthreads();
-    for (int o = warp; o < 2 * n_mels; o += MS_THREADS / 32) {
-      const int which = o / n_mels, m = o - which * n_mels;
-      const int f = fa + which;
-      const int lo = fb_range[2 * m], hi = fb_range[2 * m + 1];
-      float acc = 0.f;
-      for (int k = lo + lane; k < hi; k += 32) acc = fmaf(mag[which][k], __ldg(fb + (size_t)m * MS_BINS + k), acc);
-      acc = warp_sum(acc);
-      if (lane == 0 && f < t_stride) outb[(size_t)f * n_mels + m] = f < T ? logf(fmaxf(acc, log_floor)) : 0.f;
+    if (fb_compact) {   // thread = (frame of the pair, mel): consecutive threads write consecutive mels of one output row
+      for (int o = tid; o < 2 * n_mels; o += MS_THREADS) {
+        const int which = o / n_mels, m = o - which * n_mels;
+        const int f = fa + which;
+        const int off = fb_off[m], n = fb_off[m + 1] - off;
+        const float* mg = mag[which] + fb_lo[m];
+        float acc = 0.f;
+        for (int i = 0; i < n; ++i) acc = fmaf(mg[i], fbc[off + i], acc);
+        if (f < t_stride) outb[(size_t)f * n_mels + m] = f < T ? logf(fmaxf(acc, log_floor)) : 0.f;
+      }
+    } else {            // a filterbank denser than the compact copy holds: one warp per (frame, mel), weights from global memory
+      for (int o = warp; o < 2 * n_mels; o += MS_THREADS / 32) {
+        const int which = o / n_mels, m = o - which * n_mels;
+        const int f = fa + which;
+        const int lo = fb_range[2 * m], hi = fb_range[2 * m + 1];
+        float acc = 0.f;
+        for (int k = lo + lane; k < hi; k += 32) acc = fmaf(mag[which][k], __ldg(fb + (size_t)m * MS_BINS + k), acc);
+        acc = warp_sum(acc);
+        if (lane == 0 && f < t_stride) outb[(size_t)f * n_mels + m] = f < T ? logf(fmaxf(acc, log_floor)) : 0.f;
+      }
     }
     __syncthreads();
   }
@@ -125,7 +169,7 @@ extern "C" int t2_melspec(const float* wav, const long long* wav_len, int B, lon
   T2_REQUIRE(wav && wav_len && window && fb && fb_range && out, T2_ERR_ARG, "t2_melspec: null argument");
   T2_REQUIRE(n_fft == MS_NFFT && hop == MS_HOP, T2_ERR_UNSUPPORTED,
              "t2_melspec: specialised for n_fft=1024, hop=256 (datasets/prosody_dataset.py:39-50), got %d/%d", n_fft, hop);
-  T2_REQUIRE(B > 0 && n_mels > 0 && t_stride > 0 && wav_stride > 0, T2_ERR_ARG, "t2_melspec: bad sizes");
+  T2_REQUIRE(B > 0 && n_mels > 0 && n_mels <= MS_MAXMEL && t_stride > 0 && wav_stride > 0, T2_ERR_ARG, "t2_melspec: bad sizes (n_mels <= %d)", MS_MAXMEL);
   dim3 grid((unsigned)((t_stride + MS_FPC - 1) / MS_FPC), (unsigned)B);
   melspec_kernel<<<grid, MS_THREADS, 0, (cudaStream_t)stream>>>(wav, wav_len, wav_stride, window, fb, fb_range, n_mels, out, t_stride,
                                                                 n_frames, 1e-5f);
