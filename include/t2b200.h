@@ -70,6 +70,16 @@ int t2_decode_ar(t2_ctx* ctx, const float* memory, const float* processed_memory
                  unsigned long long seed, float* mels, float* gates, float* alignments, long long* lengths,
                  int* n_frames, void* ws, long long ws_bytes, void* stream);
 
+/* One chunk (<= 64 utterances) of a larger autoregressive batch.  The reference's stop condition couples the whole batch: the loop
+ * ends when EVERY utterance is done (model/tacotron2.py:321-322), finished utterances keep decoding and `lengths` keeps counting
+ * (:319-320).  A batch of more than 64 utterances is decoded chunk by chunk; a chunk whose own utterances finish early must still
+ * produce as many frames as the slowest chunk, so the stop condition is honoured only once `min_frames` frames have been emitted.
+ * min_frames = 0 is t2_decode_ar. */
+int t2_decode_ar_chunk(t2_ctx* ctx, const float* memory, const float* processed_memory, const unsigned char* mask,
+                       const float* controls, int B, int L, int max_len, int min_frames, const unsigned char* prenet_keep,
+                       unsigned long long seed, float* mels, float* gates, float* alignments, long long* lengths,
+                       int* n_frames, void* ws, long long ws_bytes, void* stream);
+
 /* Teacher-forced frame loop (model/tacotron2.py:255-258,276-317): prenet over the shifted target
  * in bulk, then the same persistent kernel without prenet/stop phases.  mel_target (B,T,M);
  * train != 0 applies the p=0.1 hidden-state dropouts (att_keep/rnn_keep (T,B,H) or RNG). */

@@ -35,6 +35,7 @@ SIGNATURES = {
     "t2_encoder_fwd": (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _P, _LL, _P]),
     "t2_memory_fwd": (_I, [_P, _P, _P, _P, _I, _I, _P, _P, _P, _LL, _P]),
     "t2_decode_ar": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _P, _ULL, _P, _P, _P, _P, _P, _P, _LL, _P]),
+    "t2_decode_ar_chunk": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _ULL, _P, _P, _P, _P, _P, _P, _LL, _P]),
     "t2_decode_tf": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _I, _P, _P, _ULL, _P, _P, _P, _P, _LL, _P]),
     "t2_decoder_step": (_I, [_P] + [_P] * 12 + [_I, _I] + [_P] * 9 + [_P, _LL, _P]),
     "t2_prenet_fwd": (_I, [_P, _P, _P, _P, _ULL, _I, _P, _P, _LL, _P]),

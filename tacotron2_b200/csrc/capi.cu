@@ -663,7 +663,7 @@ static int decode2_impl(t2_ctx* c, bool tf, const float* memory, const float* pm
                         const float* mel_target, int B, int L, int T, const unsigned char* prenet_keep, int train,
                         const unsigned char* att_keep, const unsigned char* rnn_keep, unsigned long long seed, float* mels,
                         float* gates, float* aligns, long long* lengths, int* n_frames, Arena& ar, cudaStream_t st,
-                        const DecTape* tape) {
+                        const DecTape* tape, int min_frames = 0) {
   D2Dims d = dims2(c, B, L);
   State2Plan pl = plan_state2(d, L, ar);
   __nv_bfloat16* tfp = (tf && !tape) ? ar.take<__nv_bfloat16>((size_t)(T + 1) * 2 * D2_BP * d.P) : nullptr;
@@ -696,7 +696,7 @@ static int decode2_impl(t2_ctx* c, bool tf, const float* memory, const float* pm
     T2_CHECK_CUDA(cudaGetLastError());
     io.teacher_forcing = 1; io.stop_enabled = 0;
   } else {
-    io.teacher_forcing = 0; io.stop_enabled = 1;
+    io.teacher_forcing = 0; io.stop_enabled = 1; io.min_frames = min_frames;
     T2_CHECK_CUDA(cudaMemsetAsync(lengths, 0, (size_t)B * sizeof(long long), st));
     s.lengths = lengths;
     s.n_frames = n_frames;
@@ -760,6 +760,20 @@ extern "C" int t2_decode_ar(t2_ctx* c, const float* memory, const float* process
   return decode2_impl(c, false, memory, processed_memory, mask, controls, nullptr, B, L, max_len, prenet_keep,
                                                  0, nullptr, nullptr, seed, mels, gates, alignments, lengths, n_frames, ar,
                                                  (cudaStream_t)stream, nullptr);
+}
+
+extern "C" int t2_decode_ar_chunk(t2_ctx* c, const float* memory, const float* processed_memory, const unsigned char* mask,
+                                  const float* controls, int B, int L, int max_len, int min_frames, const unsigned char* prenet_keep,
+                                  unsigned long long seed, float* mels, float* gates, float* alignments, long long* lengths,
+                                  int* n_frames, void* ws, long long ws_bytes, void* stream) {
+  CHECK_CTX("t2_decode_ar_chunk");
+  T2_REQUIRE(memory && processed_memory && mask && mels && gates && alignments && lengths && n_frames && ws, T2_ERR_ARG,
+             "t2_decode_ar_chunk: null argument");
+  T2_REQUIRE(B > 0 && L > 0 && max_len > 0 && min_frames >= 0 && min_frames <= max_len, T2_ERR_ARG,
+             "t2_decode_ar_chunk: bad sizes B=%d L=%d max_len=%d min_frames=%d", B, L, max_len, min_frames);
+  Arena ar(ws, ws_bytes);
+  return decode2_impl(c, false, memory, processed_memory, mask, controls, nullptr, B, L, max_len, prenet_keep, 0, nullptr, nullptr, seed,
+                      mels, gates, alignments, lengths, n_frames, ar, (cudaStream_t)stream, nullptr, min_frames);
 }
 
 extern "C" int t2_decode_tf(t2_ctx* c, const float* memory, const float* processed_memory, const unsigned char* mask,

@@ -964,7 +964,7 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
         if (!tg::gemm(pipe, &maps.w_att, tile * TG_M, nkb_att, xs, (int)rank, min(npre, nkb_att), D2_CLUSTER, 0u, tg::NoSide{},
                       io.w_policy_att, 1u, -1, gok && (int)rank < npre))
           fail = true;
-        if (io.stop_enabled && __syncthreads_and(mine)) stop = true;
+        if (io.stop_enabled && __syncthreads_and(mine) && t >= io.min_frames) stop = true;   // (t frames have been emitted)
         prof_mark(7);
         if (stop) break;
       }

@@ -74,6 +74,7 @@ struct D2IO {
   float* aligns; // [B][Tmax][L]
   int Tmax, n_steps, t0;
   int teacher_forcing, hidden_dropout, stop_enabled;
+  int min_frames;     // the stop condition is honoured only once this many frames have been emitted (chunks of a larger batch)
   int debug_barrier;  // adds one empty grid barrier per frame and times it (profiling only)
   int precompute;     // set by d2_launch: shared memory allows the location conv + dense to run beside the attention-LSTM GEMM
   int w_policy_att, w_policy_dec;  // set by d2_launch: L2 eviction priority of the LSTM weight tiles (0 default, 1 evict-first, 2 evict-last)

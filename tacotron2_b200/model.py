@@ -354,6 +354,39 @@ class Tacotron2(nn.Module):
                                      _lib.ptr(pmem), _lib.ptr(ws), ws.numel(), self._stream()), "t2_memory_fwd")
         return memory, pmem
 
+    def _decode_ar_chunked(self, lib, memory, pmem, mask, ctrl, B, L, max_len, pk, seed, mels, gates, aligns, lengths, ws, st):
+        """Autoregressive decode of more than 64 utterances.  The reference's loop ends when EVERY utterance of the batch is done
+        (model/tacotron2.py:321-322) and finished utterances keep decoding until then (:319-325), so the chunks (<= 64 utterances
+        per persistent-kernel launch) must all produce the frame count of the slowest one: every chunk is decoded once with its own
+        stop condition; chunks that stopped early are decoded again with the batch's frame count as the minimum (the kernel is
+        deterministic and the dropout draws depend only on (seed, frame, utterance), so the prefix is reproduced bit for bit)."""
+        dev = memory.device
+        chunks = [(b0, min(B, b0 + _MAX_DECODE_BATCH)) for b0 in range(0, B, _MAX_DECODE_BATCH)]
+        nf = torch.zeros(len(chunks), dtype=torch.int32, device=dev)
+
+        def run(i, min_frames):
+            b0, b1 = chunks[i]
+            pkc = None if pk is None else pk[:, :, b0:b1].contiguous()
+            cc = None if ctrl is None else ctrl[b0:b1]
+            _lib.check(lib.t2_decode_ar_chunk(self._ctx, _lib.ptr(memory[b0:b1]), _lib.ptr(pmem[b0:b1]), _lib.ptr(mask[b0:b1]), _lib.ptr(cc),
+                                              b1 - b0, L, max_len, min_frames, _lib.ptr(pkc), seed + b0, _lib.ptr(mels[b0:b1]),
+                                              _lib.ptr(gates[b0:b1]), _lib.ptr(aligns[b0:b1]), _lib.ptr(lengths[b0:b1]), _lib.ptr(nf[i:i + 1]),
+                                              _lib.ptr(ws), ws.numel(), st), "t2_decode_ar_chunk")
+            return pkc   # keep the sliced masks alive until the stream has consumed them
+
+        keep = [run(i, 0) for i in range(len(chunks))]
+        n_c = nf.tolist()   # one host sync for the whole batch
+        if min(n_c) < 0:
+            raise RuntimeError("decoder kernel aborted (grid barrier timeout)")
+        n = max(n_c)
+        keep += [run(i, n) for i in range(len(chunks)) if n_c[i] < n]
+        n_c = nf.tolist()
+        if min(n_c) < 0:
+            raise RuntimeError("decoder kernel aborted (grid barrier timeout)")
+        assert all(x == n for x in n_c), (n_c, n)
+        del keep
+        return n
+
     def _postnet(self, mels_cl, t_stride, keep):
         """mels_cl: (B,T,M) view whose batch stride is t_stride*M."""
         lib = self._ready(mels_cl.device)
@@ -464,10 +497,14 @@ class Tacotron2(nn.Module):
             n = T
             lengths = mel_spectrogram_len.to(device=dev, dtype=torch.int64).contiguous()  # :271
         else:
-            if B > _MAX_DECODE_BATCH:
-                raise RuntimeError(f"autoregressive decode handles at most {_MAX_DECODE_BATCH} utterances per call in this revision "
-                                   "(the stop condition couples the batch, model/tacotron2.py:321); shard larger batches")
             lengths = torch.empty(B, dtype=torch.int64, device=dev)
+            if B > _MAX_DECODE_BATCH:
+                n = self._decode_ar_chunked(lib, memory, pmem, mask, ctrl, B, L, max_len, pk, seed, mels, gates, aligns, lengths, ws, st)
+                post_keep = self._u8(masks.get("postnet"), dev) if train else None
+                post = self._postnet(mels[:, :n], max_len, post_keep)
+                _lib.check(lib.t2_finalize(self._ctx, _lib.ptr(mels), _lib.ptr(post), _lib.ptr(gates), _lib.ptr(lengths), B, n, max_len, st),
+                           "t2_finalize")
+                return mels[:, :n], post, gates[:, :n].unsqueeze(-1), aligns[:, :n]
             nf = torch.zeros(1, dtype=torch.int32, device=dev)
             prof = getattr(self, "_prof", None)  # bench.py: CUDA events around the persistent kernel, same stream
             if prof is not None:

@@ -272,3 +272,32 @@ def test_fallback_attention_path_agrees():
     for k, g in res["default"][1].items():
         g2 = res["fallback"][1][k]
         assert float((g - g2).norm()) <= 1e-4 * float(g.norm()) + 1e-9, k
+
+
+@pytest.mark.parametrize("with_masks", [True, False])
+def test_ar_more_than_64_utterances(with_masks):
+    """Autoregressive decode of a batch larger than one persistent-kernel launch (64): the reference's stop condition couples the
+    whole batch (model/tacotron2.py:319-322), so every chunk has to produce the frame count of the slowest one.  Stop gates are
+    shifted so that the utterances stop at different frames; checked against the CPU oracle run on the whole batch (injected
+    masks), and -- with the in-kernel dropout RNG -- against per-chunk consistency properties."""
+    args, B, L, T = synth.VANILLA, 70, 19, 24
+    sd = synth.synth_state_dict(args, seed=0, gate_shift=-35.35, gate_scale=-1000.0)
+    b = synth.synth_batch(args, B, L, 8, seed=1234)
+    bc = _cuda(b)
+    m = _model(args, sd)
+    if with_masks:
+        masks = synth.synth_masks(args, B, L, T, seed=7)
+        with torch.no_grad():
+            mels, post, gates, al = m(bc["chars_idx"], bc["chars_idx_len"], False, max_len_override=T, dropout_masks=masks)
+        want = O.tacotron2_forward(sd, args, b["chars_idx"], b["chars_idx_len"], False, max_len_override=T, masks=masks)
+        assert mels.shape == want[0].shape, ("frame count (stop decision) differs", mels.shape, want[0].shape)
+        assert torch.equal(gates.cpu() == -1000.0, want[2] == -1000.0), "stop-gate decisions differ"
+        assert _err(al, want[3]) <= ATT_TOL and _err(mels, want[0]) <= MEL_TOL and _err(post, want[1]) <= MEL_TOL
+        n_valid = (want[2] != -1000.0).sum(1).ravel()
+        assert len(set(n_valid.tolist())) > 1, "test is vacuous: every utterance stopped at the same frame"
+    else:
+        torch.manual_seed(3)
+        with torch.no_grad():
+            mels, post, gates, al = m(bc["chars_idx"], bc["chars_idx_len"], False, max_len_override=T)
+        assert mels.shape[0] == B and mels.shape[1] <= T and torch.isfinite(mels).all() and torch.isfinite(post).all()
+        assert float((al.sum(-1) - 1).abs().max()) <= 1e-5

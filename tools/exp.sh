@@ -1,1 +1,2 @@
-for v in nb2 nb3 nb6; do cp tools/ab/$v.so tacotron2_b200/libt2b200.so; echo $v; python tools/melspec_probe.py 2>&1 | tail -1; done
+timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -5
+python tools/phase_probe.py 2>&1 | tail -1
