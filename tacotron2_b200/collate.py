@@ -26,7 +26,7 @@ def _table(ctype, vals):
 class CollatePlan:
     """One prepared ``t2_collate`` launch: the concatenated fields and offset tables are on the device, the outputs are allocated."""
 
-    def __init__(self, fields: dict, device, gate_from: str | None = None):
+    def __init__(self, fields: dict, device, gate_from: str | None = None, gate_len_dev: torch.Tensor | None = None, gate_T: int = 0):
         self.lib = _lib.load()
         device = torch.device(device)
         if device.type != "cuda":
@@ -67,6 +67,13 @@ class CollatePlan:
                 gate_len = (od[1:] - od[:-1]).contiguous()
                 self.keep.append(gate_len)
         self.gate = None
+        if gate_len_dev is not None:   # frame counts already on the device (t2_melspec's n_frames): gate (B, gate_T, 1)
+            assert gate_from is None and gate_len_dev.numel() == B
+            gate_len = gate_len_dev.to(device=device, dtype=torch.int64).contiguous()
+            self.keep.append(gate_len)
+            self.gate = torch.empty((B, gate_T, 1), dtype=torch.float32, device=device)
+            self.outs["gate"] = self.gate
+            self.bytes_written += self.gate.numel() * 4
         if gate_from is not None:
             assert gate_len is not None, f"gate_from={gate_from!r} is not a field"
             self.gate = torch.empty((B, self.outs[gate_from].shape[1], 1), dtype=torch.float32, device=device)
@@ -106,6 +113,38 @@ def collate(data, device="cuda:0"):
     tts_data = pad_fields(dict(cols), device, gate_from="mel_spectrogram" if gen_gate else None)
     tts_data_len = {k: torch.stack(v).squeeze(1).to(device, non_blocking=True) for k, v in lens.items()}
     return tts_data, tts_data_len, dict(extra)
+
+
+def assemble_from_wavs(wavs, chars, device="cuda:0", silence: int = 0, melspectrogram=None):
+    """The GPU form of the per-item work of ``TTSDataset.__getitem__`` + ``_collate`` for a batch of items that are not in the mel
+    cache (datasets/tts_dataset.py:201-214, datasets/tts_dataloader.py:8-35): waveforms (already trimmed; list of 1-D float tensors)
+    are padded with ``silence`` zeros (``F.pad(wav, (0, silence))``, :201), log-mels extracted for the whole batch by one
+    ``t2_melspec`` launch straight into the padded (B, T, n_mels) layout, characters padded and gate targets written by one
+    ``t2_collate`` launch.  Returns ``(tts_data, tts_data_len)`` with ``chars_idx``, ``mel_spectrogram``, ``gate`` and
+    ``chars_idx_len`` (int64), ``mel_spectrogram_len`` / ``gate_len`` (int32, as the reference's IntTensor)."""
+    from .melspec import HOP, TacotronMelSpectrogram
+
+    device = torch.device(device)
+    if device.type != "cuda":
+        raise RuntimeError("tacotron2_b200.collate: CUDA device required (no CPU fallback)")
+    mel_tr = melspectrogram if melspectrogram is not None else TacotronMelSpectrogram()
+    B = len(wavs)
+    assert B == len(chars) and B > 0
+    wl = torch.tensor([int(w.numel()) + silence for w in wavs], dtype=torch.int64)
+    # ragged waveforms -> (B, S_max) zero padded on the device (the zero tail of each row is the silence and the batch padding at once)
+    wav_pad = pad_fields({"wav": [w.reshape(-1, 1).to(torch.float32) for w in wavs]}, device)["wav"].squeeze(-1)
+    s_max = int(wl.max())
+    if wav_pad.shape[1] < s_max:
+        wav_pad = torch.nn.functional.pad(wav_pad, (0, s_max - wav_pad.shape[1]))
+    mel, n_frames = mel_tr.to(device).batch(wav_pad, wl)
+    plan = CollatePlan({"chars_idx": [c.to(torch.int64) for c in chars]}, device, gate_len_dev=n_frames, gate_T=mel.shape[1])
+    out = plan.launch()
+    t_max = int(1 + s_max // HOP)
+    assert mel.shape[1] == t_max
+    data = {"chars_idx": out["chars_idx"], "mel_spectrogram": mel, "gate": out["gate"]}
+    lens = {"chars_idx_len": torch.tensor([int(c.numel()) for c in chars], dtype=torch.int64, device=device),
+            "mel_spectrogram_len": n_frames.to(torch.int32), "gate_len": n_frames.to(torch.int32)}
+    return data, lens
 
 
 def TTSDataLoader(dataset, batch_size=1, num_workers=0, pin_memory=False, pin_memory_device="", shuffle=None, prefetch_factor=None,

@@ -111,3 +111,30 @@ def test_gpu_collate_feeds_the_model():
     with torch.no_grad():
         mels, post, gates, al = m(d["chars_idx"], n["chars_idx_len"], True, d["mel_spectrogram"], n["mel_spectrogram_len"])
     assert mels.shape == d["mel_spectrogram"].shape and gates.shape == d["gate"].shape and torch.isfinite(post).all()
+
+
+@pytest.mark.gpu
+def test_gpu_assemble_from_wavs():
+    """wav -> (silence pad) -> log-mel -> padded batch + gate targets, all on the GPU (datasets/tts_dataset.py:201-214 +
+    datasets/tts_dataloader.py:8-35), against the per-item CPU oracles."""
+    import numpy as np
+    from oracle import melspec_oracle as MO
+    from tacotron2_b200 import synth
+    lens, silence = [9000, 22050, 4100, 256 * 20, 777], 300
+    wavs = [torch.from_numpy(synth.synth_wav(n, seed=50 + i)) for i, n in enumerate(lens)]
+    g = torch.Generator().manual_seed(5)
+    chars = [torch.randint(1, 40, (int(torch.randint(2, 30, (1,), generator=g)),), generator=g, dtype=torch.int64) for _ in lens]
+    data, ln = Cc.assemble_from_wavs(wavs, chars, "cuda:0", silence=silence)
+    torch.cuda.synchronize()
+    items = []
+    for w, c in zip(wavs, chars):
+        mel = torch.from_numpy(MO.log_mel(np.concatenate([w.numpy(), np.zeros(silence, np.float32)])))
+        items.append(({"chars_idx": c, "mel_spectrogram": mel, "gate": O.gate_target(mel.shape[0])},
+                      {"chars_idx_len": torch.tensor([c.numel()]), "mel_spectrogram_len": torch.IntTensor([mel.shape[0]]),
+                       "gate_len": torch.IntTensor([mel.shape[0]])}, {}))
+    want, wl, _ = O.collate(items)
+    assert torch.equal(data["chars_idx"].cpu(), want["chars_idx"]) and torch.equal(data["gate"].cpu(), want["gate"])
+    assert data["mel_spectrogram"].shape == want["mel_spectrogram"].shape
+    assert float((data["mel_spectrogram"].cpu() - want["mel_spectrogram"]).abs().max()) <= 1e-3   # the melspec parity bar
+    for k in wl:
+        assert ln[k].dtype == wl[k].dtype and torch.equal(ln[k].cpu(), wl[k]), k
