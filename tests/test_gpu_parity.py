@@ -301,3 +301,21 @@ def test_ar_more_than_64_utterances(with_masks):
             mels, post, gates, al = m(bc["chars_idx"], bc["chars_idx_len"], False, max_len_override=T)
         assert mels.shape[0] == B and mels.shape[1] <= T and torch.isfinite(mels).all() and torch.isfinite(post).all()
         assert float((al.sum(-1) - 1).abs().max()) <= 1e-5
+
+
+@pytest.mark.parametrize("B,L,T", [(1, 1, 3), (1, 7, 1), (2, 5, 9), (63, 11, 6), (65, 3, 5), (129, 9, 7), (3, 257, 4), (5, 600, 3)])
+def test_ar_edge_shapes(B, L, T):
+    """Edge shapes of the autoregressive path against the oracle: single utterance / character / frame, batch sizes around the
+    64-utterance launch limit (63, 65, 129: chunked decode), encoder lengths beyond one attention tile (257, 600)."""
+    args = synth.VANILLA
+    sd = synth.synth_state_dict(args, seed=0, gate_shift=-35.35, gate_scale=-1000.0)
+    b = synth.synth_batch(args, B, L, 8, seed=1234)
+    masks = synth.synth_masks(args, B, L, T, seed=7)
+    m = _model(args, sd)
+    bc = _cuda(b)
+    with torch.no_grad():
+        mels, post, gates, al = m(bc["chars_idx"], bc["chars_idx_len"], False, max_len_override=T, dropout_masks=masks)
+    want = O.tacotron2_forward(sd, args, b["chars_idx"], b["chars_idx_len"], False, max_len_override=T, masks=masks)
+    assert mels.shape == want[0].shape, ("frame count (stop decision) differs", mels.shape, want[0].shape)
+    assert torch.equal(gates.cpu() == -1000.0, want[2] == -1000.0), "stop-gate decisions differ"
+    assert _err(al, want[3]) <= ATT_TOL and _err(mels, want[0]) <= MEL_TOL and _err(post, want[1]) <= MEL_TOL
