@@ -319,3 +319,20 @@ def test_ar_edge_shapes(B, L, T):
     assert mels.shape == want[0].shape, ("frame count (stop decision) differs", mels.shape, want[0].shape)
     assert torch.equal(gates.cpu() == -1000.0, want[2] == -1000.0), "stop-gate decisions differ"
     assert _err(al, want[3]) <= ATT_TOL and _err(mels, want[0]) <= MEL_TOL and _err(post, want[1]) <= MEL_TOL
+
+
+@pytest.mark.parametrize("B,L,T", [(1, 1, 1), (65, 7, 5), (3, 300, 4)])
+def test_tf_eval_edge_shapes(B, L, T):
+    """Teacher-forced eval forward at edge shapes (one frame; more than 64 utterances = two launches; long encoder) vs the oracle."""
+    args = synth.VANILLA
+    sd = synth.synth_state_dict(args, seed=0)
+    b = synth.synth_batch(args, B, L, T, seed=1234)
+    masks = synth.synth_masks(args, B, L, T, seed=7)
+    m = _model(args, sd)
+    bc = _cuda(b)
+    with torch.no_grad():
+        mels, post, gates, al = m(bc["chars_idx"], bc["chars_idx_len"], True, bc["mel_spectrogram"], bc["mel_spectrogram_len"], dropout_masks=masks)
+    want = O.tacotron2_forward(sd, args, b["chars_idx"], b["chars_idx_len"], True, b["mel_spectrogram"], b["mel_spectrogram_len"], masks=masks)
+    assert mels.shape == want[0].shape
+    assert _err(al, want[3]) <= ATT_TOL and _err(mels, want[0]) <= MEL_TOL and _err(post, want[1]) <= MEL_TOL
+    assert _err(gates, want[2]) <= MEL_TOL
