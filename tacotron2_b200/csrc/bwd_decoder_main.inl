@@ -26,7 +26,8 @@ __device__ __forceinline__ bool dx_tile(tg::Pipe& pipe, const BSmem& sm, const C
     const int k = ktile * TG_M + row;
     *reinterpret_cast<float2*>(dx + (size_t)k * D2_BP + col) = s;
   }
-  tc::cluster_sync();   // peers are done reading this CTA's partial before it is overwritten
+  // (the caller separates two tiles of one cluster with a cluster barrier -- the peers must be done reading this CTA's partial
+  //  before it is overwritten; after the last tile the grid barrier that follows covers it)
   return ok;
 }
 
@@ -179,6 +180,7 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
 #pragma unroll 1
       for (int tile = cl; tile < n_dec + n_att; tile += nclusters) {
         bool ok;
+        if (tile != cl) tc::cluster_sync();   // second tile of this cluster in the same frame: the partial buffer is about to be rewritten
         if (tile < n_dec) ok = dx_tile(pipe, sm, &maps.wt_dec, &maps.dg_dec, tile, npb, rank, wk.dx_dec);
         else ok = dx_tile(pipe, sm, &maps.wt_att, &maps.dg_att, tile - n_dec + att_tile0, npb, rank, wk.dx_att);
         if (!ok) fail = true;
