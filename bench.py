@@ -384,8 +384,8 @@ def train_bench(dev, rank, world, steps, warmup=3):
         alg = 109.6e6 * TRAIN_T
         out["roofline"] = {"kernel": "decoder_bwd_kernel", "bound": "hbm", "achieved": alg / (kernel_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                            "frac": alg / (kernel_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_launch": alg, "kernel_ms": kernel_ms,
-                           "share_of_step": kernel_ms / (total / steps), "traffic": 55.707967e9 + 1.999782e9,
-                           "traffic_source": "profiles/r01_v6_decoder_bwd_full_raw.csv (ncu --set full, same launch shape)"}
+                           "share_of_step": kernel_ms / (total / steps), "traffic": 60.716650e9 + 2.027008e9,
+                           "traffic_source": "profiles/r01_v14_decoder_bwd_full_raw.csv (ncu --set full, same launch shape)"}
     except Exception as e:  # noqa: BLE001
         out["decoder_bwd_phase_us_per_frame"] = str(e)
     if sync is not None:
