@@ -11,11 +11,12 @@ struct DBParams {
 };
 
 // one 128-row tile of an input-gradient GEMM: dx[k0 + r][b] = sum_p WT[k0 + r][p] dg[b][p]
+template <class Side>
 __device__ __forceinline__ bool dx_tile(tg::Pipe& pipe, const BSmem& sm, const CUtensorMap* wmap, const CUtensorMap* dgmap, int ktile,
-                                        int npb, uint32_t rank, float* dx /*[K][BP]*/) {
+                                        int npb, uint32_t rank, float* dx /*[K][BP]*/, Side side) {
   tg::XSrc xs{dgmap, 0, dgmap, 0, npb};
   // transposed weights stream through L2 evict-first (see d2_launch): the per-frame working set of the attention backward stays resident
-  const bool ok = tg::gemm(pipe, wmap, ktile * TG_M, npb, xs, (int)rank, npb, D2_CLUSTER, 0u, 1);
+  const bool ok = tg::gemm(pipe, wmap, ktile * TG_M, npb, xs, (int)rank, npb, D2_CLUSTER, 0u, side, 1);
   tg::accum_to_smem(pipe, 0u, sm.part);
   tc::cluster_sync();
   // CTA `rank` reduces rows [32*rank, 32*rank+32) of the tile over the four partials
@@ -181,8 +182,28 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
       for (int tile = cl; tile < n_dec + n_att; tile += nclusters) {
         bool ok;
         if (tile != cl) tc::cluster_sync();   // second tile of this cluster in the same frame: the partial buffer is about to be rewritten
-        if (tile < n_dec) ok = dx_tile(pipe, sm, &maps.wt_dec, &maps.dg_dec, tile, npb, rank, wk.dx_dec);
-        else ok = dx_tile(pipe, sm, &maps.wt_att, &maps.dg_att, tile - n_dec + att_tile0, npb, rank, wk.dx_att);
+        // Warps 2..7 are idle while the tile streams: they pull the slices of the forward's tape that the attention backward and the
+        // two pointwise phases of this iteration read (written once by the forward, so every first touch is a DRAM miss) into L2.
+        auto tape_prefetch = [&]() {
+          if (tile != cl) return;
+          const int ptid = tid - 64;
+          auto pf = [&](const void* q, size_t bytes) {
+            const char* c = static_cast<const char*>(q);
+            for (size_t o = (size_t)ptid * 128; o < bytes; o += (size_t)192 * 128) tc::prefetch_l2(c + o);
+          };
+          if (att_active) {
+            const int Lc = (d.L + S - 1) / S, nl = max(0, min(d.L, (att_part + 1) * Lc) - att_part * Lc);
+            if (tp.xloc) pf(tp.xloc + ((size_t)t * 128 + blockIdx.x) * Lc * d.A, (size_t)nl * d.A * 4);
+            if (tp.floc) pf(tp.floc + ((size_t)t * 128 + blockIdx.x) * Lc * D2_LOC_F, (size_t)nl * D2_LOC_F * 4);
+          }
+#pragma unroll 1
+          for (int g = 0; g < 5; ++g) {   // post-activation gates and cell state of this CTA's 8 units
+            pf(tp.sav_att + (((size_t)t * 5 + g) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
+            if (t > 0) pf(tp.sav_dec + (((size_t)(t - 1) * 5 + g) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
+          }
+        };
+        if (tile < n_dec) ok = dx_tile(pipe, sm, &maps.wt_dec, &maps.dg_dec, tile, npb, rank, wk.dx_dec, tape_prefetch);
+        else ok = dx_tile(pipe, sm, &maps.wt_att, &maps.dg_att, tile - n_dec + att_tile0, npb, rank, wk.dx_att, tape_prefetch);
         if (!ok) fail = true;
       }
     }
