@@ -201,6 +201,9 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
             pf(tp.sav_att + (((size_t)t * 5 + g) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
             if (t > 0) pf(tp.sav_dec + (((size_t)(t - 1) * 5 + g) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
           }
+          // the previous cell states the two pointwise phases read (c_{t-1} of the attention cell, c_{t-2} of the decoder cell)
+          if (t > 0) pf(tp.sav_att + (((size_t)(t - 1) * 5 + 4) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
+          if (t > 1) pf(tp.sav_dec + (((size_t)(t - 2) * 5 + 4) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
         };
         if (tile < n_dec) ok = dx_tile(pipe, sm, &maps.wt_dec, &maps.dg_dec, tile, npb, rank, wk.dx_dec, tape_prefetch);
         else ok = dx_tile(pipe, sm, &maps.wt_att, &maps.dg_att, tile - n_dec + att_tile0, npb, rank, wk.dx_att, tape_prefetch);
