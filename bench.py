@@ -27,14 +27,21 @@ from tacotron2_b200 import synth  # noqa: E402
 
 B, L, T = 64, 200, 1000
 METRIC, UNIT = "mel_frames_per_sec_ar_decode", "frames/s"
-# dram__bytes_read.sum + dram__bytes_write.sum of decoder_persistent_kernel from the committed ncu --set full capture, per decoded
-# frame (the capture is a 200-frame launch of the same C2 batch; traffic is linear in the frame count)
-NCU_DRAM_BYTES_PER_FRAME = (13.756307e9 + 81.929216e6) / 200
-NCU_DRAM_SOURCE = "profiles/r01_v13_decoder_fwd_full_raw.csv (ncu --set full, 200-frame launch; per frame x frames)"
+# dram__bytes_read.sum + dram__bytes_write.sum of the persistent kernels per frame, from the committed `ncu --set full` captures of the
+# CURRENT kernels: profiles/ncu_traffic.json is rewritten by tools/evidence.sh together with the capture it names (the captures are
+# 200-frame launches of the same batches; traffic is linear in the frame count).  null when no capture of the current kernel exists.
+def ncu_traffic(kernel):
+    try:
+        e = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[kernel]
+        return float(e["dram_bytes_per_frame"]), e["source"]
+    except Exception:  # noqa: BLE001
+        return None, "no ncu capture of the current kernel committed"
+
+
 WORKLOAD = "C2: vanilla-ljspeech-stop AR inference, batch 64 x 200 chars x 1000 frames, fp32, stop gate evaluated (never fires)"
 # kernels launched by one Tacotron2.forward (AR): embed 1, encoder conv 3, BiLSTM input proj 1, BiLSTM 1, memory split 1,
-# att_encoder 1, persistent decoder 1, mel split 1, postnet conv 5, finalize 1  (memsets / memcpys not counted)
-LAUNCHES_PER_STEP = 16
+# att_encoder 1, persistent decoder 1, abort-poison guard 1, mel split 1, postnet conv 5, finalize 1  (memsets / memcpys not counted)
+LAUNCHES_PER_STEP = 17
 
 
 def algorithmic_bytes_per_frame_step(a=synth.VANILLA, b=B, l=L):
@@ -85,84 +92,162 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def oracle_sample(frames, threads):
-    """Times the CPU oracle (port of the reference's torch-CPU path) on the same workload, bounded to
-    `frames` decoder frames (+ encoder + postnet on those frames).  Returns frames/s."""
-    from oracle import tacotron2_oracle as O  # the one place bench.py runs the oracle: the CPU baseline
+def _reference_available():
+    from oracle import ref_model as R   # checker / baseline infrastructure: never on the product path
+    return R.available()
 
+
+def reference_step_cpu(frames, threads):
+    """The reference's own CPU path on the workload: the UNMODIFIED model/tacotron2.py staged under oracle/_ref (by
+    oracle/stage_ref.py, where /root/reference is readable) -- Tacotron2.forward(teacher_forcing=False, max_len_override=frames) in
+    eval mode on all host threads, its own AlwaysDropout draws, its own per-frame stop check.  When oracle/_ref is absent the oracle
+    port (oracle/tacotron2_oracle.py) stands in.  Returns (frames/s, seconds, kind)."""
     torch.set_num_threads(threads)
     sd = synth.synth_state_dict(synth.VANILLA, seed=0, gate_shift=5.0)
     b = synth.synth_batch(synth.VANILLA, B, L, 8, seed=1234)
-    masks = synth.synth_masks(synth.VANILLA, B, L, frames, seed=7)
-    t0 = time.perf_counter()
-    with torch.no_grad():
-        out = O.tacotron2_forward(sd, synth.VANILLA, b["chars_idx"], b["chars_idx_len"], False, max_len_override=frames, masks=masks)
-    dt = time.perf_counter() - t0
-    assert out[0].shape[1] == frames
-    return B * frames / dt, dt
+    if _reference_available():
+        from oracle import ref_model as R
+        m = R.reference_tacotron2(synth.VANILLA, sd).eval()
+        t0 = time.perf_counter()
+        with torch.no_grad():
+            out = m(b["chars_idx"], b["chars_idx_len"], False, max_len_override=frames)
+        dt = time.perf_counter() - t0
+        kind = "reference"
+    else:
+        from oracle import tacotron2_oracle as O
+        masks = synth.synth_masks(synth.VANILLA, B, L, frames, seed=7)
+        t0 = time.perf_counter()
+        with torch.no_grad():
+            out = O.tacotron2_forward(sd, synth.VANILLA, b["chars_idx"], b["chars_idx_len"], False, max_len_override=frames, masks=masks)
+        dt = time.perf_counter() - t0
+        kind = "port"
+    assert out[0].shape[1] == frames, "frames were skipped"
+    return B * frames / dt, dt, kind
 
 
-def torch_eager_cuda_step(dev, frames=100):
-    """The comparator BASELINE.json's north_star names: the reference's own PyTorch-CUDA decoder step at batch 64.  The reference
-    cannot travel to the GPU box, so its per-frame op sequence (model/tacotron2.py:276-325 -> model/decoder.py:53-119 ->
-    model/attention.py:34-69) is restated here with the same stock torch.nn modules it is built from (LSTMCell, Linear, Conv1d,
-    softmax, bmm, F.dropout, the per-frame ``done.all()`` host sync), in eval mode, fp32 with float32_matmul_precision 'high'
-    (run/train.py:170).  A reported baseline only: nothing of this repo's kernels runs here and nothing else uses it."""
-    import torch.nn as nn
-    import torch.nn.functional as F
-    a = synth.VANILLA
-    E, H, A, M, P = a.encoded_dim, a.att_rnn_dim, a.att_dim, a.num_mels, a.prenet_dim
+def reference_cuda_eager(dev):
+    """The comparator BASELINE.json's north_star names: the reference's own PyTorch-CUDA decoder step at batch 64 -- the UNMODIFIED
+    model/tacotron2.py (oracle/_ref) moved to this GPU, eval mode, Tacotron2.forward(teacher_forcing=False) with its per-frame
+    `done.all()` host sync, under the reference's own settings: float32_matmul_precision 'high' (run/train.py:170) in fp32, and
+    under 16-mixed autocast (run/train.py:239).  us per decoder frame = (t[400 frames] - t[100 frames]) / 300, so the encoder and
+    postnet of the call cancel.  A reported baseline: none of this repo's kernels runs here."""
+    if not _reference_available():
+        return {"unavailable": "oracle/_ref not staged (build() stages it where /root/reference is readable)"}
+    from oracle import ref_model as R
     prev = torch.get_float32_matmul_precision()
     torch.set_float32_matmul_precision("high")
-    g = torch.Generator(device="cpu").manual_seed(0)
-    with torch.no_grad():
-        pre1, pre2 = nn.Linear(M, P, bias=False).to(dev), nn.Linear(P, P, bias=False).to(dev)
-        att_rnn, dec_rnn = nn.LSTMCell(P + E, H).to(dev), nn.LSTMCell(H + E, H).to(dev)
-        q_l, v_l = nn.Linear(H, A, bias=False).to(dev), nn.Linear(A, 1, bias=False).to(dev)
-        loc_c, loc_d = nn.Conv1d(2, 32, 31, padding=15, bias=False).to(dev), nn.Linear(32, A, bias=False).to(dev)
-        mel_l, gate_l = nn.Linear(H + E, M).to(dev), nn.Linear(H + E, 1).to(dev)
-        memory = torch.randn(B, L, E, generator=g).to(dev)
-        pmem = torch.randn(B, L, A, generator=g).to(dev)
-        mask = (torch.arange(L)[None, :] >= torch.randint(120, L + 1, (B,), generator=g)[:, None]).to(dev)
+    out = {"what": f"UNMODIFIED reference Tacotron2.forward (oracle/_ref/model/tacotron2.py:276-325) in eval mode on this GPU, B={B} L={L}, "
+                   "teacher_forcing=False, per-frame stop check with host sync; us/frame from the 400- minus the 100-frame call"}
+    try:
+        sd = synth.synth_state_dict(synth.VANILLA, seed=0, gate_shift=5.0)
+        m = R.reference_tacotron2(synth.VANILLA, sd, device=dev).eval()
+        b = synth.synth_batch(synth.VANILLA, B, L, 8, seed=1234)
+        c, n = b["chars_idx"].to(dev), b["chars_idx_len"].to(dev)
 
-        def run(n):
-            z = lambda *sh: torch.zeros(*sh, device=dev)  # noqa: E731
-            ah, ac, ctx, w, wc, rh, rc = z(B, H), z(B, H), z(B, E), z(B, L), z(B, L), z(B, H), z(B, H)
-            x = F.dropout(F.relu(pre2(F.dropout(F.relu(pre1(z(B, M))), 0.5, True))), 0.5, True)
-            done, lengths = torch.zeros(B, dtype=torch.bool, device=dev), torch.zeros(B, dtype=torch.long, device=dev)
-            mels, gates, als = [], [], []
-            for _ in range(n):
-                ah, ac = att_rnn(torch.cat([x, ctx], -1), (ah, ac))
-                wcat = torch.cat([w.unsqueeze(1), wc.unsqueeze(1)], 1)
-                e = v_l(torch.tanh(q_l(ah.unsqueeze(1)) + loc_d(loc_c(wcat).transpose(1, 2)) + pmem)).squeeze(-1)
-                e.masked_fill_(mask, -float("inf"))
-                w = F.softmax(e, dim=1)
-                ctx = torch.bmm(w.unsqueeze(1), memory).squeeze(1)
-                wc = wc + w
-                rh, rc = dec_rnn(torch.cat([ah, ctx], -1), (rh, rc))
-                hc = torch.cat([rh, ctx], -1)
-                mel, gate = mel_l(hc), gate_l(hc)
-                mels.append(mel); gates.append(gate); als.append(w)  # noqa: E702
-                done[gate.squeeze(-1) < 0] = True
-                lengths[gate.squeeze(-1) >= 0] += 1
-                if bool(done.all()):
-                    break
-                x = F.dropout(F.relu(pre2(F.dropout(F.relu(pre1(mel)), 0.5, True))), 0.5, True)
-            return torch.stack(mels, 1), len(mels)
+        def run(frames):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            o = m(c, n, False, max_len_override=frames)
+            e1.record()
+            e1.synchronize()
+            assert o[0].shape[1] == frames
+            return e0.elapsed_time(e1)
 
-        gate_l.bias.fill_(5.0)   # the random-init gate never fires (SURVEY 8c): same as the measured workload
-        run(10)
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        _, n = run(frames)
-        e1.record()
-        e1.synchronize()
-    torch.set_float32_matmul_precision(prev)
-    us = 1e3 * e0.elapsed_time(e1) / n
-    return {"us_per_decoder_step": us, "frames_per_s": B * 1e6 / us, "frames": n,
-            "what": f"stock torch.nn eager restatement of the reference decoder step on this GPU, B={B} L={L}, fp32 matmul precision 'high', "
-                    "eval mode, per-frame stop check with host sync as in model/tacotron2.py:319-322; decoder loop only (no encoder/postnet)"}
+        for key, ctx in (("fp32_high", None), ("amp_16_mixed", torch.autocast("cuda", dtype=torch.float16))):
+            with torch.no_grad():
+                if ctx is not None:
+                    ctx.__enter__()
+                try:
+                    run(20)
+                    t_short, t_long = run(100), run(400)
+                finally:
+                    if ctx is not None:
+                        ctx.__exit__(None, None, None)
+            us = 1e3 * (t_long - t_short) / 300
+            out[key] = {"us_per_decoder_step": us, "frames_per_s": B * 1e6 / us, "ms_400_frames": t_long, "ms_100_frames": t_short}
+        out["us_per_decoder_step"] = out["fp32_high"]["us_per_decoder_step"]
+        del m
+    finally:
+        torch.set_float32_matmul_precision(prev)
+        torch.cuda.empty_cache()
+    return out
+
+
+def reference_cuda_train(dev, steps=2):
+    """Training half of the comparator: the UNMODIFIED reference's training_step arithmetic (Tacotron2.forward in train() mode with
+    teacher forcing, the three losses of model/tts_model.py:197-201, loss.backward()) at C3 on this GPU, eager PyTorch, in fp32 with
+    matmul precision 'high' and under 16-mixed autocast + GradScaler-free backward (run/train.py:170,239).  No optimizer step."""
+    if not _reference_available():
+        return {"unavailable": "oracle/_ref not staged"}
+    from oracle import ref_model as R
+    prev = torch.get_float32_matmul_precision()
+    torch.set_float32_matmul_precision("high")
+    out = {"what": f"UNMODIFIED reference Tacotron2 (oracle/_ref) train() forward + loss + backward on this GPU, C3: B={TRAIN_B} L={TRAIN_L} "
+                   f"T={TRAIN_T}, speaker tokens; eager PyTorch"}
+    try:
+        a = synth.HIFI
+        m = R.reference_tacotron2(a, synth.synth_state_dict(a, seed=0), device=dev).train()
+        b = {k: v.to(dev) for k, v in synth.synth_batch(a, TRAIN_B, TRAIN_L, TRAIN_T, seed=1234, ragged=False).items()}
+
+        def step(amp):
+            m.zero_grad(set_to_none=True)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            with torch.autocast("cuda", dtype=torch.float16, enabled=amp):
+                mels, post, gates, _ = m(b["chars_idx"], b["chars_idx_len"], True, b["mel_spectrogram"], b["mel_spectrogram_len"],
+                                         speaker_id=b["speaker_id"])
+                loss = R.reference_loss(mels.float(), post.float(), gates.float(), b["mel_spectrogram"], b["gate"])
+            (loss * (1024.0 if amp else 1.0)).backward()   # static loss scale stands in for the GradScaler
+            e1.record()
+            e1.synchronize()
+            return e0.elapsed_time(e1)
+
+        for key, amp in (("fp32_high", False), ("amp_16_mixed", True)):
+            step(amp)
+            ms = min(step(amp) for _ in range(steps))
+            out[key] = {"ms_per_step": ms, "frames_per_s": TRAIN_B * TRAIN_T / (ms * 1e-3)}
+        del m
+    finally:
+        torch.set_float32_matmul_precision(prev)
+        torch.cuda.empty_cache()
+    return out
+
+
+def reference_c1_cpu(threads, iters=3):
+    """SURVEY 8d / BASELINE.md section 3: config C1 exactly on the host cores -- vanilla-ljspeech-stop, batch 8 x 150 characters x 600 frames,
+    train() mode, teacher-forced forward + loss + backward, fp32; best and mean of `iters` iterations.  The reference itself
+    (oracle/_ref) when staged, else the oracle port."""
+    torch.set_num_threads(threads)
+    a, Bc, Lc, Tc = synth.VANILLA, 8, 150, 600
+    sd = synth.synth_state_dict(a, seed=0)
+    b = synth.synth_batch(a, Bc, Lc, Tc, seed=1234)
+    times = []
+    if _reference_available():
+        from oracle import ref_model as R
+        m = R.reference_tacotron2(a, sd).train()
+        kind = "reference"
+        for _ in range(iters):
+            m.zero_grad(set_to_none=True)
+            t0 = time.perf_counter()
+            mels, post, gates, _ = m(b["chars_idx"], b["chars_idx_len"], True, b["mel_spectrogram"], b["mel_spectrogram_len"])
+            R.reference_loss(mels, post, gates, b["mel_spectrogram"], b["gate"]).backward()
+            times.append(time.perf_counter() - t0)
+    else:
+        from oracle import tacotron2_oracle as O
+        kind = "port"
+        masks = synth.synth_masks(a, Bc, Lc, Tc, seed=7, train=True)
+        for _ in range(iters):
+            sdg = {k: (v.clone().requires_grad_(True) if v.is_floating_point() and "running_" not in k else v) for k, v in sd.items()}
+            t0 = time.perf_counter()
+            mels, post, gates, _ = O.tacotron2_forward(sdg, a, b["chars_idx"], b["chars_idx_len"], True, b["mel_spectrogram"],
+                                                       b["mel_spectrogram_len"], masks=masks, train=True)
+            O.loss_fn(mels, post, gates, b["mel_spectrogram"], b["gate"]).backward()
+            times.append(time.perf_counter() - t0)
+    frames = int(b["mel_spectrogram_len"].sum())
+    return {"value": frames / min(times), "unit": "frames/s", "cores": threads, "kind": kind,
+            "best_s": min(times), "mean_s": sum(times) / len(times), "iters": iters, "valid_frames": frames,
+            "sample": f"C1 exactly: vanilla B={Bc} L={Lc} T={Tc} (ragged lengths), train() teacher-forced forward + loss + backward, torch CPU fp32, "
+                      f"whole step, best of {iters}"}
 
 
 def bf16_mode_us_per_step(dev, steps=3):
@@ -180,14 +265,17 @@ def bf16_mode_us_per_step(dev, steps=3):
         with torch.no_grad():
             for _ in range(2):
                 m(c, n, False, max_len_override=T)
+            import ctypes
+            from tacotron2_b200 import _lib as L_
+            L_.check(L_.load().t2_debug_set_timing(m._ctx, 1))
             tot = 0.0
             for _ in range(steps):
-                m._prof = []
                 out = m(c, n, False, max_len_override=T)[1]
                 torch.cuda.synchronize()
                 assert out.shape[1] == T
-                tot += sum(x.elapsed_time(y) for x, y in m._prof)
-            m._prof = None
+                ms_ = ctypes.c_float(0.0)
+                L_.check(L_.load().t2_debug_kernel_ms(m._ctx, 0, ctypes.byref(ms_)))
+                tot += ms_.value
         del m
         return 1e3 * tot / steps / T
     finally:
@@ -196,6 +284,11 @@ def bf16_mode_us_per_step(dev, steps=3):
         else:
             os.environ["T2B200_PRECISION"] = old
 
+
+PHASE_NAMES = ["att_lstm_tail", "query_partials_barrier", "attention_ctx_store_barrier", "dec_lstm_tail_barrier", "proj(beside att gemm)",
+               "prenet1(beside att gemm)", "prenet2(beside att gemm)", "x_barrier_and_prenet_kblock_gemm", "att_lstm_gemm_with_output_stage_beside",
+               "dec_lstm_gemm", "attn_query_sum", "attn_energies", "attn_csync", "attn_softmax", "attn_context",
+               "location_precompute(beside dec gemm)"]
 
 TRAIN_B, TRAIN_L, TRAIN_T = 64, 150, 800
 TRAIN_WORKLOAD = ("C3: vanilla-lj-hifi-stop (speaker tokens, 4 speakers) teacher-forced training step, batch 64/GPU x 150 chars x 800 frames, "
@@ -263,6 +356,11 @@ def postnet_bench(dev, steps=10):
             "peak_tflops": peak, "frac_algorithmic": tf / peak, "frac_issued": 3 * tf / peak}
 
 
+def hifigan_bench(dev):
+    from tacotron2_b200 import hifigan
+    return hifigan.bench(dev)
+
+
 def collate_bench(dev, steps=20):
     """Batch assembly of one C3-sized batch: 64 ragged items (<= 800 frames, <= 150 characters), items
     resident in HBM; one t2_collate launch pads characters and mels and writes the gate targets.  HBM-bound byte movement: achieved
@@ -308,6 +406,10 @@ def train_bench(dev, rank, world, steps, warmup=3):
     a = synth.HIFI
     model = Tacotron2(**a.kwargs()).to(dev).train()
     model.load_state_dict(synth.synth_state_dict(a, seed=0))
+    lib = model._ready(dev)
+    from tacotron2_b200 import _lib as L_
+    L_.check(lib.t2_debug_set_timing(model._ctx, 1))   # CUDA events around the two persistent kernels, on the launching stream
+    kern_ms = [0.0, 0.0]
     sync = GradSync(model) if world > 1 else None
     batch = synth.synth_batch(a, TRAIN_B, TRAIN_L, TRAIN_T, seed=1234 + rank, ragged=False)
     host = {k: v.pin_memory() for k, v in batch.items()}
@@ -337,9 +439,14 @@ def train_bench(dev, rank, world, steps, warmup=3):
         loss_h.copy_(loss.detach(), non_blocking=True)  # device -> host read of the step's result
         torch.cuda.current_stream().synchronize()
         if timed:
+            import ctypes
             for i in range(4):
                 phase[i] += ev[i].elapsed_time(ev[i + 1])
             per_step.append([round(ev[i].elapsed_time(ev[i + 1]), 2) for i in range(2)])
+            for which in (0, 1):
+                ms_ = ctypes.c_float(0.0)
+                L_.check(lib.t2_debug_kernel_ms(model._ctx, which, ctypes.byref(ms_)))
+                kern_ms[which] += ms_.value
         return float(loss_h)
 
     for _ in range(warmup):
@@ -380,14 +487,17 @@ def train_bench(dev, rank, world, steps, warmup=3):
             peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0))
         except Exception:  # noqa: BLE001
             peak = 6650.0
-        kernel_ms = sum(cyc[i] for i in range(len(names))) / 1965.0 / 1e3
+        kernel_ms = kern_ms[1] / steps   # decoder_bwd_kernel, CUDA events on the launching stream, mean over the timed steps
+        out["decoder_fwd_kernel_ms"] = kern_ms[0] / steps
+        traffic_pf, traffic_src = ncu_traffic("decoder_bwd_kernel")
         alg = 109.6e6 * TRAIN_T
         out["roofline"] = {"kernel": "decoder_bwd_kernel", "bound": "hbm", "achieved": alg / (kernel_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                            "frac": alg / (kernel_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_launch": alg, "kernel_ms": kernel_ms,
-                           "share_of_step": kernel_ms / (total / steps), "traffic": 60.716650e9 + 2.027008e9,
-                           "traffic_source": "profiles/r01_v14_decoder_bwd_full_raw.csv (ncu --set full, same launch shape)"}
+                           "share_of_step": kernel_ms / (total / steps), "traffic": None if traffic_pf is None else traffic_pf * TRAIN_T,
+                           "traffic_source": traffic_src, "kernel_ms_source": "CUDA events around the launch (t2_debug_kernel_ms)"}
     except Exception as e:  # noqa: BLE001
         out["decoder_bwd_phase_us_per_frame"] = str(e)
+    model.check_status()
     if sync is not None:
         sync.detach()
     del model, opt
@@ -395,43 +505,34 @@ def train_bench(dev, rank, world, steps, warmup=3):
     return out
 
 
-def oracle_train_sample(threads, B=8, L=150, T=24):
-    """CPU baseline of the training half: the oracle's teacher-forced forward + loss + backward (torch CPU autograd), bounded sample."""
-    from oracle import tacotron2_oracle as O
-
-    torch.set_num_threads(threads)
-    a = synth.VANILLA
-    sd = synth.synth_state_dict(a, seed=0)
-    sd = {k: (v.clone().requires_grad_(True) if v.is_floating_point() and "running_" not in k else v) for k, v in sd.items()}
-    b = synth.synth_batch(a, B, L, T, seed=1234, ragged=False)
-    masks = synth.synth_masks(a, B, L, T, seed=7, train=True)
-    t0 = time.perf_counter()
-    mels, post, gates, _ = O.tacotron2_forward(sd, a, b["chars_idx"], b["chars_idx_len"], True, b["mel_spectrogram"], b["mel_spectrogram_len"],
-                                               masks=masks, train=True)
-    O.loss_fn(mels, post, gates, b["mel_spectrogram"], b["gate"]).backward()
-    dt = time.perf_counter() - t0
-    return B * T / dt, dt, f"vanilla B={B} L={L} T={T} teacher-forced fwd + loss + bwd, torch CPU fp32 autograd over the oracle, {dt:.1f} s"
+def bench_config(world):
+    """`config` of the JSON line: identical for both arms (the driver compares them)."""
+    return {"workload": WORKLOAD, "utterances_per_gpu": B, "chars": L, "frames": T, "parallelism": f"replicas x{world}, no collective"}
 
 
 def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU implementation of the path (oracle/_ref: the unmodified model/tacotron2.py) on the
+    host cores, all threads, on the SAME workload as the GPU arm: every step is one whole C2 step -- batch 64 x 200 characters, all
+    1000 frames, encoder + frame loop + postnet (no sampling: a step takes a few seconds).  Rank 0 only."""
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    frames = 24  # bounded sample per step: ~2-4 s of host time
-    for _ in range(args.warmup):
-        oracle_sample(frames, threads)
-    t = []
+    for _ in range(min(args.warmup, 1)):
+        reference_step_cpu(40, threads)   # untimed warm-up (thread pool, allocator): a short call is enough on the CPU
+    t, kind = [], "reference"
     for _ in range(args.steps):
-        v, dt = oracle_sample(frames, threads)
+        v, dt, kind = reference_step_cpu(T, threads)
         t.append(dt)
     ms = 1e3 * sum(t) / len(t)
-    value = B * frames / (ms / 1e3)
-    sample = f"B={B} L={L}, first {frames} of {T} AR frames + encoder + postnet per step, torch CPU fp32"
+    value = B * T / (ms / 1e3)
+    sample = f"whole step: B={B} L={L}, all {T} AR frames + encoder + postnet, torch CPU fp32, {threads} threads"
+    cfg = bench_config(1)
+    cfg["implementation"] = ("oracle/_ref: unmodified reference model/tacotron2.py" if kind == "reference" else "oracle port (oracle/_ref not staged)")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "sample": sample},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "dtype": "f32", "data": "synthetic", "config": cfg,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -485,7 +586,11 @@ def main():
     chars_d, lens_d = chars_h.to(dev), lens_h.to(dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     out_h = torch.empty(B, T, a.num_mels).pin_memory()
-    len_h = torch.empty(B, dtype=torch.int64).pin_memory()
+    gate_h = torch.empty(B, T, 1).pin_memory()   # the masked gates carry the utterance lengths a caller cuts by (run/test.py:167)
+    import ctypes
+    from tacotron2_b200 import _lib as L_
+    lib = model._ready(dev)
+    L_.check(lib.t2_debug_set_timing(model._ctx, 1))   # CUDA events around decoder_persistent_kernel, on the launching stream
 
     def step_resident():
         with torch.no_grad():
@@ -496,6 +601,7 @@ def main():
             c, n = chars_h.to(dev, non_blocking=True), lens_h.to(dev, non_blocking=True)
             mels, post, gates, al = model(c, n, False, max_len_override=T)
             out_h[:, : post.shape[1]].copy_(post, non_blocking=True)
+            gate_h[:, : gates.shape[1]].copy_(gates, non_blocking=True)
             torch.cuda.current_stream().synchronize()
             return post
 
@@ -514,15 +620,15 @@ def main():
         for _ in range(k):
             flush.zero_()  # flush L2 between timed iterations (untimed)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            model._prof = []
             e0.record()
             out = fn()
             e1.record()
             e1.synchronize()
             assert out.shape[1] == T, "frames were skipped"
             total += e0.elapsed_time(e1)
-            dec += sum(x.elapsed_time(y) for x, y in model._prof)
-        model._prof = None
+            ms_ = ctypes.c_float(0.0)
+            L_.check(lib.t2_debug_kernel_ms(model._ctx, 0, ctypes.byref(ms_)))   # the persistent kernel alone
+            dec += ms_.value
         return total, dec
 
     barrier()
@@ -536,6 +642,7 @@ def main():
         tt = torch.tensor([t_res, t_e2e, t_dec], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         t_res, t_e2e, t_dec = (float(x) for x in tt)
+    model.check_status()
     train = None
     if not args.no_train:
         del flush
@@ -558,52 +665,57 @@ def main():
     dec_ms = t_dec / args.steps
     bytes_launch = algorithmic_bytes_per_frame_step() * T
     achieved = bytes_launch / (dec_ms * 1e-3) / 1e9
+    traffic_pf, traffic_src = ncu_traffic("decoder_persistent_kernel")
+    cfg = bench_config(world)
+    cfg.update({"l2": "flushed between timed iterations (256 MiB write)", "us_per_decoder_step": 1e3 * dec_ms / T})
     line = {
         "metric": METRIC, "value": frames / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "l2": "flushed between timed iterations (256 MiB write)", "utterances_per_gpu": B,
-                   "us_per_decoder_step": 1e3 * dec_ms / T, "parallelism": f"replicas x{world}, no collective"},
+        "dtype": "f32", "data": "synthetic", "config": cfg,
         "e2e": {"value": frames / (t_e2e / args.steps * 1e-3), "unit": UNIT,
-                "h2d_bytes_per_step": chars_h.numel() * 8 + lens_h.numel() * 8, "d2h_bytes_per_step": out_h.numel() * 4 + 4},
+                "h2d_bytes_per_step": chars_h.numel() * 8 + lens_h.numel() * 8, "d2h_bytes_per_step": out_h.numel() * 4 + gate_h.numel() * 4 + 4},
         "gpu_launches": LAUNCHES_PER_STEP * args.steps,
         "clocks": clocks,
         "roofline": {"kernel": "decoder_persistent_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": NCU_DRAM_BYTES_PER_FRAME * T, "traffic_source": NCU_DRAM_SOURCE,
+                     "frac": achieved / peak, "traffic": None if traffic_pf is None else traffic_pf * T, "traffic_source": traffic_src,
                      "peak_source": "measured" if peaks else "fallback",
-                     "algorithmic_bytes_per_launch": bytes_launch, "kernel_ms": dec_ms, "share_of_step": dec_ms / ms},
+                     "algorithmic_bytes_per_launch": bytes_launch, "kernel_ms": dec_ms, "share_of_step": dec_ms / ms,
+                     "kernel_ms_source": "CUDA events around the launch (t2_debug_kernel_ms)"},
     }
     try:  # per-phase breakdown of the last decode launch (CTA 0's SM-clock cycles -> us per frame)
-        import ctypes
-        from tacotron2_b200 import _lib
         cyc = (ctypes.c_ulonglong * 16)()
-        _lib.check(_lib.load().t2_debug_phase_cycles(model._ctx, cyc))
+        L_.check(lib.t2_debug_phase_cycles(model._ctx, cyc))
         mhz = clocks.get("sm_mhz") or 1965
-        names = ["att_lstm_tail", "query_partials_barrier", "attention_ctx_store_barrier", "dec_lstm_tail_barrier", "proj(beside att gemm)",
-                 "prenet1(beside att gemm)", "prenet2(beside att gemm)", "x_barrier_and_prenet_kblock_gemm", "att_lstm_gemm_with_output_stage_beside",
-                 "dec_lstm_gemm", "attn_query_sum", "attn_energies", "attn_csync", "attn_softmax", "attn_context",
-                 "location_precompute(beside dec gemm)"]
-        line["config"]["phase_us_per_frame"] = {n: round(cyc[i] / mhz / T, 2) for i, n in enumerate(names)}
+        line["config"]["phase_us_per_frame"] = {n: round(cyc[i] / mhz / T, 2) for i, n in enumerate(PHASE_NAMES)}
     except Exception as e:  # noqa: BLE001
         line["config"]["phase_us_per_frame"] = str(e)
     if train is not None:
         line["train"] = train
-    extras = () if args.no_extras else (("melspec", melspec_bench), ("collate", collate_bench), ("postnet", postnet_bench), ("bf16_mode_us_per_decoder_step", bf16_mode_us_per_step),
-                                        ("torch_cuda_eager", torch_eager_cuda_step))
+        if "error" not in train:
+            # the partitioned path's numbers where the driver keeps them (SCALE_rNN.json retains `config`, not extra keys)
+            line["config"].update({"train_workload": TRAIN_WORKLOAD, "train_frames_per_s": train["value"], "train_ms_per_step": train["ms_per_step"],
+                                   "train_parallelism": train["config"]["parallelism"],
+                                   "allreduce_exposed_ms": train["phase_ms"]["allreduce_exposed"],
+                                   "grad_bytes_allreduced": train["grad_bytes_allreduced_per_step"]})
+    extras = () if args.no_extras else (("melspec", melspec_bench), ("collate", collate_bench), ("postnet", postnet_bench),
+                                        ("hifigan", hifigan_bench), ("bf16_mode_us_per_decoder_step", bf16_mode_us_per_step),
+                                        ("torch_cuda_eager", reference_cuda_eager), ("torch_cuda_eager_train", reference_cuda_train))
     for key, fn in extras:
         try:
             line[key] = fn(dev)
         except Exception as e:  # noqa: BLE001
             line[key] = {"error": f"{type(e).__name__}: {e}"}
-    if not args.no_cpu_baseline:
+    eager = line.get("torch_cuda_eager", {})
+    if isinstance(eager, dict) and "us_per_decoder_step" in eager:
+        line["config"]["reference_cuda_eager_us_per_decoder_step"] = eager["us_per_decoder_step"]
+        line["config"]["speedup_vs_reference_cuda_eager_per_frame"] = eager["us_per_decoder_step"] / (1e3 * dec_ms / T)
+    if not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1
         if train is not None and "error" not in train:
-            oracle_train_sample(threads, T=4)  # warm-up
-            v, dt, sample = oracle_train_sample(threads)
-            train["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample}
-        oracle_sample(4, threads)  # warm-up
-        v, dt = oracle_sample(T, threads)
-        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+            train["cpu_baseline"] = reference_c1_cpu(threads)
+        reference_step_cpu(40, threads)  # warm-up
+        v, dt, kind = reference_step_cpu(T, threads)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": kind,
                                 "sample": f"one whole step of the workload: B={B} L={L}, all {T} AR frames + encoder + postnet, torch CPU fp32, {dt:.1f} s"}
     print(json.dumps(line))
     if world > 1:

@@ -48,7 +48,8 @@ long long t2_workspace_bytes(const t2_ctx* ctx, int B, int L, int T);
 
 /* Encoder.forward (model/encoder.py:54-67).  chars_idx (B,L) int64, lens (B) int64 ->
  * encoded (B,L,E).  keep: NULL (eval) or train-mode dropout keep-masks (3,B,L,E) uint8.
- * train != 0 uses BatchNorm batch statistics (not available in this revision -> T2_ERR_UNSUPPORTED). */
+ * train must be 0 here (eval: BatchNorm running statistics folded into the conv epilogue); the train-mode forward with
+ * batch statistics and a tape for the backward is t2_encoder_train_fwd below. */
 int t2_encoder_fwd(t2_ctx* ctx, const long long* chars_idx, const long long* lens, int B, int L, int train,
                    const unsigned char* keep, float* encoded, void* ws, long long ws_bytes, void* stream);
 
@@ -95,6 +96,14 @@ int t2_decoder_step(t2_ctx* ctx, const float* prev_mel_prenet, const float* att_
                     const float* processed_memory, const unsigned char* mask, const float* controls, int B, int L,
                     float* mel_out, float* gate_out, float* att_h_out, float* att_c_out, float* att_ctx_out, float* w_out,
                     float* w_cum_out, float* rnn_h_out, float* rnn_c_out, void* ws, long long ws_bytes, void* stream);
+
+/* Attention.forward, stand-alone (model/attention.py:34-69): attention_hidden_state (B,H), memory (B,L,EF),
+ * processed_memory (B,L,A), attention_weights_cat (B,2,L) [channel 0 = previous weights, 1 = cumulative, model/decoder.py:78-80],
+ * mask (B,L) uint8 1 = padded -> context (B,EF), weights (B,L).  The same arithmetic runs fused inside the persistent decoder
+ * kernel; this entry exists so the module boundary is callable on its own.  No workspace. */
+int t2_attention_step(t2_ctx* ctx, const float* attention_hidden_state, const float* memory, const float* processed_memory,
+                      const float* attention_weights_cat, const unsigned char* mask, int B, int L, float* context, float* weights,
+                      void* stream);
 
 /* prenet (model/tacotron2.py:85-92) on N rows: x (N,M) -> out (N,P); keep1/keep2 (N,P) uint8 or NULL (RNG). */
 int t2_prenet_fwd(t2_ctx* ctx, const float* x, const unsigned char* keep1, const unsigned char* keep2,
@@ -205,6 +214,16 @@ int t2_melspec(const float* wav, const long long* wav_len, int B, long long wav_
 int t2_collate(int n_fields, const void* const* src, const long long* const* off, const long long* row_bytes,
                const long long* max_rows, void* const* out, int B, const long long* gate_len, float* gate, long long gate_T,
                void* stream);
+
+/* Sticky device status of the context's persistent kernels (decoder forward / backward).  They bound every wait; a timeout makes
+ * all CTAs leave together, NaN-fills the launch's outputs and sets this word.  *status_out = 0 or T2_ERR_DEVICE_ABORT; reading
+ * clears it.  Synchronises the device: call it where the host synchronises anyway (reading a loss, n_frames, a checkpoint). */
+int t2_ctx_status(t2_ctx* ctx, int* status_out);
+
+/* Debug: CUDA events around the persistent decoder kernels on the launching stream.  which: 0 = decoder_persistent_kernel,
+ * 1 = decoder_bwd_kernel of the last timed call; t2_debug_kernel_ms synchronises on the end event. */
+int t2_debug_set_timing(t2_ctx* ctx, int on);
+int t2_debug_kernel_ms(t2_ctx* ctx, int which, float* ms_out);
 
 /* Debug: SM-clock cycles CTA 0 spent in each phase of the last decode call (host pointer, 16 slots;
  * synchronises the device).  Slots: 0 att-LSTM tail, 1 query, 2 attention tail, 3 dec-LSTM tail, 4 projection, 5 prenet1,

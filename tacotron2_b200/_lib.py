@@ -38,6 +38,10 @@ SIGNATURES = {
     "t2_decode_ar_chunk": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _ULL, _P, _P, _P, _P, _P, _P, _LL, _P]),
     "t2_decode_tf": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _I, _P, _P, _ULL, _P, _P, _P, _P, _LL, _P]),
     "t2_decoder_step": (_I, [_P] + [_P] * 12 + [_I, _I] + [_P] * 9 + [_P, _LL, _P]),
+    "t2_attention_step": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P]),
+    "t2_ctx_status": (_I, [_P, C.POINTER(_I)]),
+    "t2_debug_set_timing": (_I, [_P, _I]),
+    "t2_debug_kernel_ms": (_I, [_P, _I, C.POINTER(C.c_float)]),
     "t2_prenet_fwd": (_I, [_P, _P, _P, _P, _ULL, _I, _P, _P, _LL, _P]),
     "t2_postnet_fwd": (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _P, _LL, _P]),
     "t2_debug_phase_cycles": (_I, [_P, _P]),

@@ -51,6 +51,14 @@ def _give_tape(owner, tape):
         pool.append(tape)
 
 
+def _count_bn_batches(module):
+    """nn.BatchNorm1d increments num_batches_tracked on every train-mode forward; the kernels update the running statistics in
+    place, the counter is bumped here so that saved checkpoints match the reference's."""
+    for m in module.modules():
+        if isinstance(m, torch.nn.BatchNorm1d) and m.num_batches_tracked is not None:
+            m.num_batches_tracked += 1
+
+
 def _after_bucket(owner, flat, group, views):
     hook = getattr(owner, "_grad_bucket_hook", None)
     if hook is not None:  # data-parallel: async all-reduce of this bucket (parallel.py)
@@ -71,6 +79,7 @@ class PostnetFn(torch.autograd.Function):
         _lib.check(lib.t2_postnet_train_fwd(owner._ctx, P(x), T, B, T, P(keep), seed, P(out), P(tape), tape.numel(), P(ws), ws.numel(),
                                             _stream()), "t2_postnet_train_fwd")
         owner._bn_dirty = True  # running statistics changed in place: re-fold them before the next eval() forward
+        _count_bn_batches(owner.postnet)
         ctx.owner, ctx.keep, ctx.seed, ctx.tape, ctx.shape = owner, keep, seed, tape, (B, T, M)
         return out
 
@@ -102,6 +111,7 @@ class EncoderFn(torch.autograd.Function):
         _lib.check(lib.t2_encoder_train_fwd(owner._ctx, P(chars), P(lens), B, L, P(keep), seed, P(out), P(tape), tape.numel(), P(ws),
                                             ws.numel(), _stream()), "t2_encoder_train_fwd")
         owner._bn_dirty = True
+        _count_bn_batches(owner.encoder)
         ctx.owner, ctx.args, ctx.tape, ctx.out = owner, (chars, lens, keep, seed, B, L), tape, out
         return out
 
@@ -227,8 +237,10 @@ class LossFn(torch.autograd.Function):
         d_m, d_p, d_g = torch.empty(B, T, M, device=dev), torch.empty(B, T, M, device=dev), torch.empty(B, T, 1, device=dev)
         ws = owner._train_workspace(lib, dev, B, 1, T)
         f = lambda t: t.to(device=dev, dtype=torch.float32).contiguous()  # noqa: E731
-        _lib.check(lib.t2_loss_fwd_bwd(owner._ctx, P(f(mels)), P(f(post)), P(f(gates)), P(f(mel_target)), P(f(gate_target)), B, T, P(loss),
+        ins = [f(mels), f(post), f(gates), f(mel_target), f(gate_target)]   # alive until after the launch (no freed temporaries)
+        _lib.check(lib.t2_loss_fwd_bwd(owner._ctx, *[P(t) for t in ins], B, T, P(loss),
                                        P(d_m), P(d_p), P(d_g), P(ws), ws.numel(), _stream()), "t2_loss_fwd_bwd")
+        del ins
         ctx.save_for_backward(d_m, d_p, d_g)
         return loss
 

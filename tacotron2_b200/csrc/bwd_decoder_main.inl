@@ -261,7 +261,10 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
       }
     }
   }
-  if (blockIdx.x == 0 && tid == 0) wk.barrier[2] = alive ? 0u : 1u;
+  if (blockIdx.x == 0 && tid == 0) {
+    wk.barrier[2] = alive ? 0u : 1u;
+    if (!alive && wk.status) atomicExch(wk.status, 1u);
+  }
   tc::tc_fence_before();
   tc::cluster_sync();
   if ((tid >> 5) == 1) tc::tmem_dealloc<TG_TMEM_COLS>(pipe.tmem);

@@ -21,6 +21,11 @@ extern "C" int t2_abi_version(void) { return 1; }
 
 namespace {
 
+__global__ void poison_on_abort_kernel(const unsigned* status, float* out, long long n) {
+  if (*status == 0u) return;
+  for (long long i = threadIdx.x; i < n; i += blockDim.x) out[i] = __int_as_float(0x7fc00000);
+}
+
 __global__ void add_vec_kernel(const float* a, const float* b, float* o, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) o[i] = a[i] + b[i];
@@ -245,6 +250,13 @@ inline int gsz(long long n) { return (int)std::min<long long>((n + 255) / 256, 1
 
 }  // namespace
 
+int poison_on_abort_launch(const unsigned* status, float* out, long long n, cudaStream_t st) {
+  if (!status || !out || n <= 0) return T2_OK;
+  poison_on_abort_kernel<<<1, 256, 0, st>>>(status, out, std::min<long long>(n, 4096));
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
+
 int make_w_map(CUtensorMap* m, const __nv_bfloat16* w, int Cout, int Cin, int k, int NT, int npass) {
   unsigned long long dims[4] = {(unsigned long long)Cin, (unsigned long long)k, (unsigned long long)Cout, 2ull};
   unsigned long long st[3] = {(unsigned long long)Cin * 2, (unsigned long long)k * Cin * 2, (unsigned long long)Cout * k * Cin * 2};
@@ -268,7 +280,8 @@ extern "C" int t2_ctx_create(const t2_model_config* cfg, t2_ctx** out) {
   T2_CHECK_CUDA(cudaGetDevice(&dev));
   cudaDeviceProp prop;
   T2_CHECK_CUDA(cudaGetDeviceProperties(&prop, dev));
-  T2_REQUIRE(prop.major >= 10, T2_ERR_UNSUPPORTED, "t2_ctx_create: device sm_%d%d; libt2b200 is built for sm_100a only", prop.major,
+  // the binary carries sm_100a SASS only (tcgen05 / TMEM): any other architecture, newer ones included, cannot run it
+  T2_REQUIRE(prop.major == 10, T2_ERR_UNSUPPORTED, "t2_ctx_create: device sm_%d%d; libt2b200 is built for sm_100a only", prop.major,
              prop.minor);
   t2_ctx* c = new t2_ctx();
   c->cfg = *cfg;
@@ -293,6 +306,12 @@ extern "C" int t2_ctx_create(const t2_model_config* cfg, t2_ctx** out) {
   c->slab_bytes = 0;
   c->prof_buf = nullptr;
   T2_CHECK_CUDA(cudaMalloc((void**)&c->prof_buf, 16 * sizeof(unsigned long long)));
+  c->status_dev = nullptr;
+  T2_CHECK_CUDA(cudaMalloc((void**)&c->status_dev, 4 * sizeof(unsigned)));
+  T2_CHECK_CUDA(cudaMemset(c->status_dev, 0, 4 * sizeof(unsigned)));
+  c->timing_on = 0;
+  c->tev_valid[0] = c->tev_valid[1] = false;
+  for (int i = 0; i < 2; ++i) for (int j = 0; j < 2; ++j) T2_CHECK_CUDA(cudaEventCreate(&c->tev[i][j]));
   *out = c;
   return T2_OK;
 }
@@ -301,6 +320,8 @@ extern "C" int t2_ctx_destroy(t2_ctx* c) {
   if (!c) return T2_OK;
   if (c->slab) cudaFree(c->slab);
   if (c->prof_buf) cudaFree(c->prof_buf);
+  if (c->status_dev) cudaFree(c->status_dev);
+  for (int i = 0; i < 2; ++i) for (int j = 0; j < 2; ++j) cudaEventDestroy(c->tev[i][j]);
   delete c;
   return T2_OK;
 }
@@ -673,6 +694,7 @@ static int decode2_impl(t2_ctx* c, bool tf, const float* memory, const float* pm
   T2_CHECK_CUDA(cudaMemsetAsync(pl.zero_begin, 0, pl.zero_bytes, st));
   D2State s = pl.s;
   s.prof = c->prof_buf;
+  s.status = c->status_dev;
   T2_CHECK_CUDA(cudaMemsetAsync(c->prof_buf, 0, 16 * sizeof(unsigned long long), st));
   const int nslots = tape ? T + 1 : 2;
   if (tape) {  // training: every per-frame buffer keeps its whole history
@@ -703,8 +725,11 @@ static int decode2_impl(t2_ctx* c, bool tf, const float* memory, const float* pm
   }
   D2Maps maps;
   RC(make_xmaps(c, d, s, tfp, T + 1, &maps, nslots));
+  timing_begin(c, 0, st);
   RC(d2_launch(d, c->d2w, s, io, maps, st));
+  timing_end(c, 0, st);
   if (tape) RC(decode_proj_bulk(c, tape->xdec, B, T, mels, gates, proj_tmp, st));
+  RC(poison_on_abort_launch(c->status_dev, mels, (long long)B * T * d.M, st));   // an aborted launch must not pass for a result
   return T2_OK;
 }
 
@@ -721,6 +746,7 @@ static int step2_impl(t2_ctx* c, const float* prev, const float* att_h, const fl
   T2_CHECK_CUDA(cudaMemsetAsync(pl.zero_begin, 0, pl.zero_bytes, st));
   T2_CHECK_CUDA(cudaMemsetAsync(tfp, 0, (size_t)2 * D2_BP * d.P * sizeof(__nv_bfloat16), st));
   D2State s = pl.s;
+  s.status = c->status_dev;
   RC(fill_controls2(d, s, controls, B, st));
   const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP, pp = (long long)D2_BP * d.P;
   rm_to_xsplit_kernel<<<gsz(B * d.P), 256, 0, st>>>(prev, d.P, tfp, pp, d.P, 0, d.P, B);
@@ -745,6 +771,7 @@ static int step2_impl(t2_ctx* c, const float* prev, const float* att_h, const fl
   copy2d_kernel<<<gsz(B * d.R), 256, 0, st>>>(s.projin, d.KprojP, rnn_h_out, d.R, B, d.R);
   km_to_rm_kernel<<<gsz(B * d.R), 256, 0, st>>>(s.rnn_c, 0, rnn_c_out, d.R, d.R, B);
   T2_CHECK_CUDA(cudaGetLastError());
+  RC(poison_on_abort_launch(c->status_dev, mel_out, (long long)B * d.M, st));
   return T2_OK;
 }
 
@@ -878,6 +905,31 @@ extern "C" int t2_finalize(t2_ctx* c, float* mels, float* post, float* gates, co
                            void* stream) {
   T2_REQUIRE(c && mels && post && gates && lengths, T2_ERR_ARG, "t2_finalize: null argument");
   return finalize_launch(mels, post, gates, lengths, B, T, t_stride, c->M, (cudaStream_t)stream);
+}
+
+extern "C" int t2_ctx_status(t2_ctx* c, int* status_out) {
+  T2_REQUIRE(c && status_out, T2_ERR_ARG, "t2_ctx_status: null argument");
+  unsigned v = 0;
+  T2_CHECK_CUDA(cudaMemcpy(&v, c->status_dev, sizeof(unsigned), cudaMemcpyDeviceToHost));   // synchronises with the device
+  if (v) T2_CHECK_CUDA(cudaMemset(c->status_dev, 0, sizeof(unsigned)));
+  *status_out = v ? T2_ERR_DEVICE_ABORT : 0;
+  if (v) t2_set_error("a persistent decoder kernel aborted (grid barrier or TMA pipeline timeout); its outputs were NaN-filled");
+  return T2_OK;
+}
+
+extern "C" int t2_debug_set_timing(t2_ctx* c, int on) {
+  T2_REQUIRE(c, T2_ERR_ARG, "t2_debug_set_timing: null context");
+  c->timing_on = on ? 1 : 0;
+  c->tev_valid[0] = c->tev_valid[1] = false;
+  return T2_OK;
+}
+
+extern "C" int t2_debug_kernel_ms(t2_ctx* c, int which, float* ms_out) {
+  T2_REQUIRE(c && ms_out && (which == 0 || which == 1), T2_ERR_ARG, "t2_debug_kernel_ms: bad argument");
+  T2_REQUIRE(c->tev_valid[which], T2_ERR_STATE, "t2_debug_kernel_ms: no timed launch of kernel %d (call t2_debug_set_timing first)", which);
+  T2_CHECK_CUDA(cudaEventSynchronize(c->tev[which][1]));
+  T2_CHECK_CUDA(cudaEventElapsedTime(ms_out, c->tev[which][0], c->tev[which][1]));
+  return T2_OK;
 }
 
 extern "C" int t2_debug_phase_cycles(t2_ctx* c, unsigned long long* host_out16) {

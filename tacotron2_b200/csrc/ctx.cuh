@@ -27,6 +27,10 @@ struct t2_ctx {
   float *post_scale[5], *post_shift[5];
   float *lstm_bias, *lstm_Whh;  // BiLSTM: [1][E][2*4Hh], [2*4Hh], [2][4Hh][Hh]
   unsigned long long* prof_buf;            // [16] device, decoder phase cycles
+  unsigned* status_dev;                    // sticky: set by any persistent kernel that aborted (barrier / pipeline timeout); t2_ctx_status reads + clears
+  int timing_on;                           // t2_debug_set_timing: CUDA events around the persistent decoder kernels
+  cudaEvent_t tev[2][2];                   // [0 = decoder forward, 1 = decoder backward][begin, end]
+  bool tev_valid[2];
   // tensor-core decoder (decoder2)
   __nv_bfloat16 *Watt_b, *Wdec_b;          // [2 hi/lo][4H permuted][KattP] / [2][4R][KdecP]
   float* loc_conv_t;                       // [2][31][32]
@@ -115,3 +119,8 @@ inline DecTape plan_dec_tape(const D2Dims& d, int B, int L, int T, Arena& ar) {
   return t;
 }
 D2Dims dims2(const t2_ctx* c, int B, int L);
+// After a persistent kernel: if the context's sticky status word is set, the first floats of `out` become NaN, so that an abort
+// can never pass for a result (the loss / gradient norm downstream turns NaN) even where no host code looks at the status.
+int poison_on_abort_launch(const unsigned* status, float* out, long long n, cudaStream_t st);
+inline void timing_begin(t2_ctx* c, int which, cudaStream_t st) { if (c->timing_on) { cudaEventRecord(c->tev[which][0], st); } }
+inline void timing_end(t2_ctx* c, int which, cudaStream_t st) { if (c->timing_on) { cudaEventRecord(c->tev[which][1], st); c->tev_valid[which] = true; } }

@@ -1015,7 +1015,10 @@ decoder_persistent_kernel(const __grid_constant__ D2Maps maps, D2Dims d, D2Weigh
     frames = io.n_steps;
     __syncthreads();
   }
-  if (blockIdx.x == 0 && tid == 0) *s.n_frames = alive ? frames : -1;
+  if (blockIdx.x == 0 && tid == 0) {
+    *s.n_frames = alive ? frames : -1;
+    if (!alive && s.status) atomicExch(s.status, 1u);
+  }
   // write the cell states back (single-step API / resumable decoding)
 #pragma unroll 1
   for (int i = tid; i < 8 * D2_BP; i += D2_THREADS) {

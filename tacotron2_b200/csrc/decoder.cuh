@@ -57,6 +57,7 @@ struct D2State {
   int* n_frames;         // [1]
   unsigned* barrier;     // [2]
   unsigned long long* prof;  // [16] or null
+  unsigned* status;          // context's sticky abort word or null
   // history mode (training tape): xatt/xdec/w_prev/w_cum hold T+1 slots and q holds T slots instead of two parities
   float* sav_att;        // [T][5][H][BP] i,f,g,o (post-activation), c of the attention LSTMCell, or null
   float* sav_dec;        // [T][5][R][BP]

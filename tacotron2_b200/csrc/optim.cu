@@ -74,6 +74,9 @@ __global__ void __launch_bounds__(OP_THREADS) adam_kernel(const OpTensor* __rest
   const OpTensor t = tens[c.tensor];
   const long long base = (long long)c.start_div * OP_CHUNK;
   const float clip = scal[1];
+  // a non-finite gradient norm (overflow, or a NaN-poisoned gradient after an aborted kernel) skips the update, as the GradScaler of
+  // the reference's 16-mixed Trainer does (run/train.py:239); the caller sees it in grad_norm_out
+  if (!isfinite(scal[0])) return;
 #pragma unroll
   for (int i = 0; i < OP_CHUNK / OP_THREADS; ++i) {
     const long long e = base + (long long)i * OP_THREADS + threadIdx.x;

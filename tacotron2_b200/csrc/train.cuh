@@ -70,6 +70,7 @@ struct DBWork {
   float* small_partial;     // [grid][A*32 + 2*31*32 + A]  per-CTA partials of location_dense / location_conv / v gradients
   float* dbias;             // [2][4H]   att, dec bias gradients
   unsigned* barrier;        // [4]
+  unsigned* status;         // context's sticky abort word or null
 };
 
 struct DBMaps {

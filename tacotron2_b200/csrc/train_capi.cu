@@ -380,7 +380,7 @@ int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const uns
   DBWork k{};
   k.dprojin = dprojin; k.dg_att = dg_att; k.dg_dec = dg_dec; k.dgT_att = dgT_att; k.dgT_dec = dgT_dec; k.dx_att = dx_att; k.dx_dec = dx_dec;
   k.dpre = dpre; k.dctx_tot = dctx_tot; k.dq = dq; k.dpm = d_pmem; k.dconv = dconv; k.gcum = gcum; k.small_partial = small_partial;
-  k.dbias = dbias; k.barrier = barrier;
+  k.dbias = dbias; k.barrier = barrier; k.status = c->status_dev;
   DBMaps maps;
   maps.wt_att = c->map_wt_att; maps.wt_dec = c->map_wt_dec;
   {
@@ -392,7 +392,9 @@ int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const uns
     RC(tc_make_tmap_bf16(&maps.dg_dec, dg_dec, 3, dims, sb, box));
   }
   T2_CHECK_CUDA(cudaMemsetAsync(c->prof_buf, 0, 16 * sizeof(unsigned long long), st));
+  timing_begin(c, 1, st);
   RC(db_launch(d, T, c->KattT, c->KdecT, w, t, k, maps, c->prof_buf, st));
+  timing_end(c, 1, st);
 
   // ---- small attention weights, biases
   RC(partial_sum_launch(small_partial, 128, nsmall, small_sum, st));
@@ -459,6 +461,9 @@ int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const uns
     Opnd XT{xT, Nn, Np, 1, M, (long long)M * Np};
     RC(bulk_gemm(c, D2T, XT, P, M, 0, GemmNtOut{g_w1, M, 1, 0, 1.f, 0}, partial, st));
   }
+  // an aborted backward kernel must not pass for a result: the gradient norm downstream turns NaN (and the optimizer skips the step)
+  RC(poison_on_abort_launch(c->status_dev, d_memory, (long long)B * L * EF, st));
+  RC(poison_on_abort_launch(c->status_dev, g_dec_hh, (long long)4 * R * R, st));
   return T2_OK;
 }
 

@@ -51,7 +51,17 @@ def _owner_of(mod):
     return o
 
 
-class Attention(nn.Module):
+class _Owned:
+    """Sub-modules reach the owning Tacotron2 (its CUDA context) through a weak reference that is not part of their state:
+    copies / pickles drop it and Tacotron2.__setstate__ re-links."""
+
+    def __getstate__(self):
+        st = dict(self.__dict__)
+        st.pop("_t2_owner", None)
+        return st
+
+
+class Attention(_Owned, nn.Module):
     """model/attention.py:6-69."""
 
     def __init__(self, attention_rnn_dim, embedding_dim, attention_dim, attention_location_n_filters, attention_location_kernel_size):
@@ -64,10 +74,12 @@ class Attention(nn.Module):
         self.location_dense = nn.Linear(attention_location_n_filters, attention_dim, bias=False)
 
     def forward(self, attention_hidden_state, memory, processed_memory, attention_weights_cat, mask):
-        raise RuntimeError("Attention.forward is fused into the decoder-step kernel; call Decoder.forward or Tacotron2.forward")
+        """model/attention.py:34-69 as a stand-alone call (C ABI ``t2_attention_step``).  Inside ``Decoder.forward`` and
+        ``Tacotron2.forward`` the same arithmetic runs fused into the persistent decoder kernel."""
+        return _owner_of(self)._attention_step(attention_hidden_state, memory, processed_memory, attention_weights_cat, mask)
 
 
-class Decoder(nn.Module):
+class Decoder(_Owned, nn.Module):
     """model/decoder.py:10-119."""
 
     def __init__(self, num_mels, embedding_dim, prenet_dim, att_rnn_dim, att_dim, rnn_hidden_dim, dropout,
@@ -90,7 +102,7 @@ class Decoder(nn.Module):
                                              rnn_hidden, encoded, att_encoded, encoded_mask, extra_decoder_in)
 
 
-class Encoder(nn.Module):
+class Encoder(_Owned, nn.Module):
     """model/encoder.py:8-67."""
 
     def __init__(self, num_chars, embedding_dim, encoder_kernel_size, dropout):
@@ -114,7 +126,7 @@ class Encoder(nn.Module):
         return o._encode(char_idx, char_idx_len, None)
 
 
-class Postnet(nn.Module):
+class Postnet(_Owned, nn.Module):
     """model/postnet.py:4-52."""
 
     def __init__(self, num_layers, num_mels, postnet_dim, dropout):
@@ -204,6 +216,34 @@ class Tacotron2(nn.Module):
                 _lib.load().t2_ctx_destroy(self._ctx)
         except Exception:
             pass
+
+    # The CUDA context, its weight signature and the workspace are per-process device state: a copy / pickle of the module carries
+    # the parameters only and rebuilds them lazily on first use (copy.deepcopy(model) / torch.save(model) used to raise).
+    _TRANSIENT = ("_ctx", "_sig", "_ws", "_tape_pool", "_grad_bucket_hook", "_prof")
+
+    def __getstate__(self):
+        st = dict(self.__dict__)
+        for k in self._TRANSIENT:
+            st.pop(k, None)
+        return st
+
+    def __setstate__(self, st):
+        import weakref
+        self.__dict__.update(st)
+        self._ctx = self._sig = self._ws = None
+        ref = weakref.ref(self)
+        for m in (self.encoder, self.decoder, self.decoder.attention, self.postnet):
+            object.__setattr__(m, "_t2_owner", ref)
+
+    def check_status(self):
+        """Raises if a persistent kernel of this model aborted since the last check (C ABI ``t2_ctx_status``; synchronises)."""
+        if self._ctx is None:
+            return
+        st = C.c_int(0)
+        _lib.check(_lib.load().t2_ctx_status(self._ctx, C.byref(st)), "t2_ctx_status")
+        if st.value != 0:
+            raise RuntimeError("tacotron2_b200: a persistent decoder kernel aborted (grid barrier / pipeline timeout); "
+                               "the outputs of that call were NaN-filled")
 
     def _tensors(self):
         out = dict(self.named_parameters())
@@ -350,7 +390,8 @@ class Tacotron2(nn.Module):
         pmem = torch.empty(B, L, self.att_dim, device=dev)
         spk = None if speaker_id is None else speaker_id.to(device=dev, dtype=torch.int64).contiguous()
         desc = None if description is None else description.to(device=dev, dtype=torch.float32).contiguous()
-        _lib.check(lib.t2_memory_fwd(self._ctx, _lib.ptr(encoded.contiguous()), _lib.ptr(spk), _lib.ptr(desc), B, L, _lib.ptr(memory),
+        enc_c = encoded.contiguous()   # bound to a local until after the launch
+        _lib.check(lib.t2_memory_fwd(self._ctx, _lib.ptr(enc_c), _lib.ptr(spk), _lib.ptr(desc), B, L, _lib.ptr(memory),
                                      _lib.ptr(pmem), _lib.ptr(ws), ws.numel(), self._stream()), "t2_memory_fwd")
         return memory, pmem
 
@@ -408,14 +449,31 @@ class Tacotron2(nn.Module):
         H, R, EF, M = self.att_rnn_dim, self.rnn_hidden_dim, self.encoded_full_dim, self.num_mels
         mel, gate, ah, ac, ctx = e(B, M), e(B, 1), e(B, H), e(B, H), e(B, EF)
         w2, wc2, rh, rc = e(B, L), e(B, L), e(B, R), e(B, R)
+        # converted inputs are bound to locals that live until after the call: a temporary freed before the launch could hand its
+        # block to the next conversion
+        ins = [f(prev), f(att_hidden[0]), f(att_hidden[1]), f(att_context), f(w), f(w_cum), f(rnn_hidden[0]), f(rnn_hidden[1]),
+               f(encoded), f(att_encoded), self._u8(mask, dev), None if controls is None else f(controls)]
         _lib.check(lib.t2_decoder_step(
-            self._ctx, _lib.ptr(f(prev)), _lib.ptr(f(att_hidden[0])), _lib.ptr(f(att_hidden[1])), _lib.ptr(f(att_context)),
-            _lib.ptr(f(w)), _lib.ptr(f(w_cum)), _lib.ptr(f(rnn_hidden[0])), _lib.ptr(f(rnn_hidden[1])), _lib.ptr(f(encoded)),
-            _lib.ptr(f(att_encoded)), _lib.ptr(self._u8(mask, dev)), _lib.ptr(None if controls is None else f(controls)), B, L,
+            self._ctx, *[_lib.ptr(t) for t in ins], B, L,
             _lib.ptr(mel), _lib.ptr(gate), _lib.ptr(ah), _lib.ptr(ac), _lib.ptr(ctx), _lib.ptr(w2), _lib.ptr(wc2), _lib.ptr(rh),
             _lib.ptr(rc), _lib.ptr(ws), ws.numel(), self._stream()), "t2_decoder_step")
+        del ins
         w_cum.copy_(wc2)  # the reference updates the caller's tensor in place (model/decoder.py:90)
         return mel, gate, (ah, ac), ctx, w2, w_cum, (rh, rc)
+
+    def _attention_step(self, attention_hidden_state, memory, processed_memory, attention_weights_cat, mask):
+        dev = attention_hidden_state.device
+        lib = self._ready(dev)
+        B, L = processed_memory.shape[0], processed_memory.shape[1]
+        f = lambda t: t.to(device=dev, dtype=torch.float32).contiguous()  # noqa: E731
+        ins = [f(attention_hidden_state), f(memory), f(processed_memory), f(attention_weights_cat), self._u8(mask, dev)]
+        assert tuple(ins[3].shape) == (B, 2, L) and tuple(ins[4].shape) == (B, L), "attention_weights_cat (B,2,L), mask (B,L)"
+        context = torch.empty(B, self.encoded_full_dim, device=dev)
+        weights = torch.empty(B, L, device=dev)
+        _lib.check(lib.t2_attention_step(self._ctx, *[_lib.ptr(t) for t in ins], B, L, _lib.ptr(context), _lib.ptr(weights),
+                                         self._stream()), "t2_attention_step")
+        del ins
+        return context, weights
 
     def init_hidden(self, encoded_len: int, batch_size: int, device: torch.device):
         """model/tacotron2.py:126-153."""
@@ -518,6 +576,7 @@ class Tacotron2(nn.Module):
                 prof.append(ev)
             n = int(nf.item())  # one host sync per utterance batch (the reference syncs every frame, :321)
             if n < 0:
+                self.check_status()
                 raise RuntimeError("decoder kernel aborted (grid barrier timeout)")
         post_keep = self._u8(masks.get("postnet"), dev) if train else None
         post = self._postnet(mels[:, :n], max_len, post_keep)

@@ -40,6 +40,36 @@ class ClipAdam:
     def set_lr(self, lr: float) -> None:
         self.lr = float(lr)
 
+    def state_dict(self) -> dict:
+        """The layout of ``torch.optim.Adam.state_dict()`` (what a Lightning checkpoint stores under ``optimizer_states``), so a
+        run can be handed back to the reference's Trainer: state[i] = {step, exp_avg, exp_avg_sq}, one param group."""
+        n = len(self.params)
+        state = {i: {"step": torch.tensor(float(self.step_count)), "exp_avg": self.exp_avg[i], "exp_avg_sq": self.exp_avg_sq[i]}
+                 for i in range(n)} if self.step_count > 0 else {}
+        group = {"lr": self.lr, "betas": self.betas, "eps": self.eps, "weight_decay": self.weight_decay, "amsgrad": False,
+                 "maximize": False, "foreach": None, "capturable": False, "differentiable": False, "fused": None,
+                 "decoupled_weight_decay": False, "params": list(range(n))}
+        return {"state": state, "param_groups": [group]}
+
+    def load_state_dict(self, sd: dict) -> None:
+        group = sd["param_groups"][0]
+        if len(group["params"]) != len(self.params):
+            raise ValueError(f"ClipAdam.load_state_dict: {len(group['params'])} parameters in the checkpoint, {len(self.params)} here")
+        self.lr, self.betas, self.eps = float(group["lr"]), tuple(float(b) for b in group["betas"]), float(group["eps"])
+        self.weight_decay = float(group["weight_decay"])
+        steps = set()
+        for j, idx in enumerate(group["params"]):
+            st = sd["state"].get(idx)
+            if st is None:
+                self.exp_avg[j].zero_(), self.exp_avg_sq[j].zero_()
+                continue
+            self.exp_avg[j].copy_(st["exp_avg"])
+            self.exp_avg_sq[j].copy_(st["exp_avg_sq"])
+            steps.add(int(float(st["step"])))
+        if len(steps) > 1:
+            raise ValueError("ClipAdam.load_state_dict: per-parameter step counts differ")
+        self.step_count = steps.pop() if steps else 0
+
     def zero_grad(self, set_to_none: bool = True) -> None:
         for p in self.params:
             if set_to_none:

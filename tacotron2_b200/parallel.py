@@ -8,7 +8,8 @@ is enqueued on a side stream the moment the kernels that write it have been laun
 only the 12 MB encoder bucket is exposed).  BatchNorm statistics stay per-GPU (standard DDP semantics).
 
 ``GradSync.finish()`` makes the compute stream wait for the exchange and installs the averaged gradients as ``p.grad``.
-One backward pass per step is assumed (``optimizer.zero_grad(set_to_none=True)``).
+One backward pass per step is assumed (``optimizer.zero_grad(set_to_none=True)``); a parameter group whose bucket arrives
+several times in that pass (decoder chunks of a batch above 64 utterances) is summed over its buckets.
 """
 from __future__ import annotations
 
@@ -42,6 +43,7 @@ class GradSync:
     def finish(self):
         """Wait for every bucket and install the averaged gradients."""
         n = 0
+        seen = set()
         for flat, params, views, work in self.pending:
             if work is not None:
                 work.wait()
@@ -49,7 +51,10 @@ class GradSync:
             elif self.stream is not None and flat.is_cuda:
                 torch.cuda.current_stream(flat.device).wait_stream(self.stream)
             for p, v in zip(params, views):
-                p.grad = v
+                # a parameter group can arrive more than once per backward (a rank with more than 64 utterances runs the decoder
+                # in chunks, each with its own bucket): the contributions add up, as autograd's own accumulation would
+                p.grad = p.grad + v if id(p) in seen else v
+                seen.add(id(p))
             n += flat.numel()
         self.pending.clear()
         return n

@@ -36,11 +36,17 @@ class MultiStepLR:
         self.optimizer.set_lr(self.lr_at(self.last_epoch))
 
     def state_dict(self):
-        return {"last_epoch": self.last_epoch, "base_lr": self.base_lr, "milestones": self.milestones, "gamma": self.gamma}
+        from collections import Counter
+        # torch.optim.lr_scheduler.MultiStepLR.state_dict() keys (milestones as a Counter, base_lrs, _last_lr) + this class's own
+        return {"last_epoch": self.last_epoch, "base_lr": self.base_lr, "milestones": Counter(self.milestones), "gamma": self.gamma,
+                "base_lrs": [self.base_lr], "_last_lr": [self.lr_at(self.last_epoch)], "_step_count": self.last_epoch + 1}
 
     def load_state_dict(self, sd):
-        self.last_epoch, self.base_lr = int(sd["last_epoch"]), float(sd["base_lr"])
-        self.milestones, self.gamma = [int(m) for m in sd["milestones"]], float(sd["gamma"])
+        self.last_epoch = int(sd["last_epoch"])
+        self.base_lr = float(sd["base_lr"] if "base_lr" in sd else sd["base_lrs"][0])
+        ms = sd["milestones"]
+        self.milestones = sorted(int(m) for m in (ms.elements() if hasattr(ms, "elements") else ms))
+        self.gamma = float(sd["gamma"])
         self.optimizer.set_lr(self.lr_at(self.last_epoch))
 
 
@@ -51,6 +57,7 @@ class TTSModel(nn.Module):
                  controls_dim: int = 0, max_len_override: Optional[int] = None, description_embeddings: bool = False,
                  description_embeddings_dim: int = 0, gradient_clip_val: float = 1.0):
         super().__init__()
+        self._hparams = {k: v for k, v in locals().items() if k not in ("self", "__class__", "gradient_clip_val")}   # save_hyperparameters()
         self.lr, self.weight_decay, self.scheduler_milestones = lr, weight_decay, list(scheduler_milestones)
         self.speaker_tokens, self.controls, self.max_len_override = speaker_tokens, controls, max_len_override
         self.description_embeddings = description_embeddings
@@ -96,6 +103,38 @@ class TTSModel(nn.Module):
         if "global_step" in ckpt:
             self.global_step = int(ckpt["global_step"])
         return out
+
+    def save_checkpoint(self, path, optimizer=None, scheduler=None, epoch: int = 0):
+        """What ``trainer.save_checkpoint`` leaves behind (run/train.py:245-255), as far as this model determines it: a dict with
+        ``state_dict`` under the LightningModule's ``tacotron2.`` prefix (the keys ``TTSModel.load_from_checkpoint`` of
+        run/say.py:125-137 reads), ``global_step`` / ``epoch``, ``hyper_parameters`` (the constructor keywords of
+        model/tts_model.py:19-43), and the optimizer / scheduler state in torch's own layouts under Lightning's keys.
+        ``load_reference_checkpoint`` + ``resume`` read it back."""
+        self.tacotron2.check_status()   # never write a checkpoint after an aborted kernel
+        sd = {"tacotron2." + k: v.detach().cpu().clone() for k, v in self.tacotron2.state_dict().items()}
+        ckpt = {"epoch": int(epoch), "global_step": int(self.global_step), "pytorch-lightning_version": "2.0.0", "state_dict": sd,
+                "loops": {}, "callbacks": {}, "hparams_name": "kwargs", "hyper_parameters": dict(self._hparams),
+                "optimizer_states": [], "lr_schedulers": []}
+        if optimizer is not None:
+            osd = optimizer.state_dict()
+            osd["state"] = {i: {k: (v.detach().cpu().clone() if torch.is_tensor(v) else v) for k, v in st.items()}
+                            for i, st in osd["state"].items()}
+            ckpt["optimizer_states"] = [osd]
+        if scheduler is not None:
+            ckpt["lr_schedulers"] = [scheduler.state_dict()]
+        torch.save(ckpt, path)
+        return ckpt
+
+    def resume(self, ckpt, optimizer=None, scheduler=None):
+        """``Trainer.fit(ckpt_path=...)`` (run/train.py:245-249): weights, step counter, optimizer moments, scheduler position."""
+        if not isinstance(ckpt, dict):
+            ckpt = torch.load(ckpt, map_location="cpu", weights_only=False)
+        self.load_reference_checkpoint(ckpt)
+        if optimizer is not None and ckpt.get("optimizer_states"):
+            optimizer.load_state_dict(ckpt["optimizer_states"][0])
+        if scheduler is not None and ckpt.get("lr_schedulers"):
+            scheduler.load_state_dict(ckpt["lr_schedulers"][0])
+        return ckpt
 
     # ------------------------------------------------------------------ reference protocol
     def forward(self, chars_idx: Tensor, chars_idx_len: Tensor, teacher_forcing: bool = True, mel_spectrogram: Optional[Tensor] = None,
@@ -176,6 +215,7 @@ def fit(model: TTSModel, batches, max_steps: int, grad_sync=None, on_step=None):
             model.global_step += 1
             if on_step is not None:
                 on_step(model.global_step, loss, norm)
+                model.tacotron2.check_status()   # on_step reads the loss (a host sync anyway): an aborted kernel raises here
             if model.global_step >= max_steps:
                 break
         if not seen:

@@ -167,3 +167,4 @@ if __name__ == "__main__":
     case_tf("tf_eval_hifi", synth.HIFI, 3, 26, 14, False)
     case_tf("tf_train_vanilla", synth.VANILLA, 3, 29, 17, True)
     case_tf("tf_train_conditioned", synth.CONDITIONED, 2, 18, 9, True)
+    case_tf("tf_train_long", synth.VANILLA, 4, 40, 200, True)

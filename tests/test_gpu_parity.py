@@ -336,3 +336,33 @@ def test_tf_eval_edge_shapes(B, L, T):
     assert mels.shape == want[0].shape
     assert _err(al, want[3]) <= ATT_TOL and _err(mels, want[0]) <= MEL_TOL and _err(post, want[1]) <= MEL_TOL
     assert _err(gates, want[2]) <= MEL_TOL
+
+
+@pytest.mark.parametrize("name,args", [("step_vanilla", synth.VANILLA), ("step_conditioned", synth.CONDITIONED)])
+def test_attention_forward_standalone(name, args):
+    """Attention.forward called on its own (model/attention.py:34-69, C ABI t2_attention_step): against the reference's step golden
+    (the attention inside that Decoder.forward saw query = the new att_h, wcat = (w, w_cum) of the inputs) and against the oracle."""
+    g = dict(np.load(os.path.join(G, name + ".npz")))
+    sd = synth.synth_state_dict(args, seed=0)
+    m = _model(args, sd)
+    t = lambda k: torch.from_numpy(g[k]).to(_dev())  # noqa: E731
+    wcat = torch.stack([t("in/w"), t("in/w_cum")], 1)
+    mask = torch.from_numpy(g["in/mask"]).to(_dev())
+    with torch.no_grad():
+        ctx, w = m.decoder.attention(t("att_h"), t("in/memory"), t("in/pm"), wcat, mask)
+    assert _err(ctx, g["ctx"]) <= 1e-5 and _err(w, g["w"]) <= 1e-6
+    assert float(w.masked_select(mask).abs().max() if bool(mask.any()) else 0.0) == 0.0
+    # a second shape, against the oracle (bool mask, non-contiguous inputs)
+    gen = torch.Generator().manual_seed(4)
+    B, L, EF = 7, 301, args.encoded_full_dim
+    h = torch.randn(B, args.att_rnn_dim, generator=gen) * 0.3
+    mem = torch.randn(B, L, EF, generator=gen) * 0.3
+    pm = torch.randn(B, L, args.att_dim, generator=gen) * 0.5
+    lens = torch.tensor([L, 250, 17, 1, 300, 128, 64])
+    msk = torch.arange(L)[None, :] >= lens[:, None]
+    wp = torch.softmax(torch.randn(B, L, generator=gen).masked_fill(msk, float("-inf")), 1)
+    wc = wp * 3.0
+    want_ctx, want_w = O.attention(sd, h, mem, pm, wp, wc, msk)
+    with torch.no_grad():
+        ctx, w = m.decoder.attention(h.to(_dev()), mem.to(_dev()), pm.to(_dev()), torch.stack([wp, wc], 1).to(_dev()), msk.to(_dev()))
+    assert _err(ctx, want_ctx) <= 1e-5 and _err(w, want_w) <= 1e-6

@@ -227,3 +227,75 @@ def test_full_train_step_vs_reference_golden(name, args):
     for k in g:
         if k.startswith("bn/"):
             assert float(np.abs(st[k[3:]].cpu().numpy() - g[k]).max()) <= 2e-4, k
+
+
+def _full_step_vs_autograd(args, B, L, T, seed_batch, seed_masks, encoder_robust):
+    """Whole training_step (train-mode forward, loss, BPTT backward) through the C ABI against torch CPU autograd over the oracle:
+    every parameter gradient at the GTOL bar of this file (the encoder under its documented whole-module bar when its batch is
+    large, see _check_grads)."""
+    torch.set_num_threads(os.cpu_count() or 1)
+    sd = synth.synth_state_dict(args, seed=0)
+    b = synth.synth_batch(args, B, L, T, seed=seed_batch)
+    masks = synth.synth_masks(args, B, L, T, seed=seed_masks, train=True)
+    m = _model(args, sd)
+    dev = _dev()
+    cu = {k: v.to(dev) for k, v in b.items()}
+    mels, post, gates, al = m(cu["chars_idx"], cu["chars_idx_len"], True, cu["mel_spectrogram"], cu["mel_spectrogram_len"],
+                              speaker_id=cu.get("speaker_id"), controls=cu.get("controls"),
+                              description_embeddings=cu.get("description_embeddings"), dropout_masks=masks)
+    loss = m.loss(mels, post, gates, cu["mel_spectrogram"], cu["gate"])
+    loss.backward()
+    torch.cuda.synchronize()
+    sdg = _sd_grad(sd)
+    om, op, og, oa = O.tacotron2_forward(sdg, args, b["chars_idx"], b["chars_idx_len"], True, b["mel_spectrogram"], b["mel_spectrogram_len"],
+                                         speaker_id=b.get("speaker_id"), controls=b.get("controls"),
+                                         description_embeddings=b.get("description_embeddings"), masks=masks, train=True)
+    oloss = O.loss_fn(om, op, og, b["mel_spectrogram"], b["gate"])
+    oloss.backward()
+    assert float((mels.detach().cpu() - om.detach()).abs().max()) <= 1e-3
+    assert float((post.detach().cpu() - op.detach()).abs().max()) <= 1e-3
+    assert float((al.detach().cpu() - oa.detach()).abs().max()) <= 1e-4
+    assert abs(float(loss.detach()) - float(oloss.detach())) <= 1e-4 * abs(float(oloss.detach()))
+    for prefix in ("decoder.", "prenet.", "postnet.", "att_encoder.", "speaker_embedding.", "description_embeddings_linear."):
+        _check_grads(m, sdg, prefix)
+    _check_grads(m, sdg, "encoder.", robust=encoder_robust)
+
+
+def test_c1_train_step_vs_autograd():
+    """SURVEY 8d's parity config C1 exactly: vanilla-ljspeech-stop, batch 8 x 150 characters x 600 frames, train() mode, teacher
+    forcing, masks injected, BatchNorm batch statistics; 600 reverse steps of BPTT with dgates carried as bf16 (hi,lo)."""
+    _full_step_vs_autograd(synth.VANILLA, 8, 150, 600, 1234, 7, True)
+
+
+def test_c3_shape_long_T_train_step():
+    """The timed training config's length (C3: 800 frames, speaker tokens) at a batch the CPU autograd finishes in a minute."""
+    _full_step_vs_autograd(synth.HIFI, 8, 150, 800, 4321, 11, True)
+
+
+def test_train_step_more_than_64_utterances():
+    """A rank that trains more than 64 utterances (the reference's finetune path doubles batch_size to 128, run/train.py:113) runs
+    the decoder in chunks of 64: the chunks' parameter gradients must add up (the data-parallel hook used to keep only
+    the last chunk's bucket).  Checked with the bucket hook installed (world size 1) against autograd over the oracle."""
+    from tacotron2_b200.parallel import GradSync
+    args, B, L, T = synth.VANILLA, 130, 9, 5
+    sd = synth.synth_state_dict(args, seed=0)
+    b = synth.synth_batch(args, B, L, T, seed=5)
+    masks = synth.synth_masks(args, B, L, T, seed=3, train=True)
+    m = _model(args, sd)
+    sync = GradSync(m)
+    cu = {k: v.to(_dev()) for k, v in b.items()}
+    mels, post, gates, _ = m(cu["chars_idx"], cu["chars_idx_len"], True, cu["mel_spectrogram"], cu["mel_spectrogram_len"], dropout_masks=masks)
+    m.loss(mels, post, gates, cu["mel_spectrogram"], cu["gate"]).backward()
+    sync.finish()
+    sdg = _sd_grad(sd)
+    om, op, og, _ = O.tacotron2_forward(sdg, args, b["chars_idx"], b["chars_idx_len"], True, b["mel_spectrogram"], b["mel_spectrogram_len"],
+                                        masks=masks, train=True)
+    O.loss_fn(om, op, og, b["mel_spectrogram"], b["gate"]).backward()
+    for prefix in ("decoder.", "prenet.", "postnet.", "att_encoder."):
+        _check_grads(m, sdg, prefix)
+    _check_grads(m, sdg, "encoder.", robust=True)
+
+
+def test_full_train_step_long_T_vs_reference_golden():
+    """T = 200 teacher-forced training step against gradients of the UNMODIFIED reference (tests/golden/tf_train_long.npz)."""
+    test_full_train_step_vs_reference_golden("tf_train_long", synth.VANILLA)

@@ -36,11 +36,20 @@ def _worker(rank, world, port, q):
             views.append(flat[off:off + p.numel()].view_as(p))
             off += p.numel()
         m._grad_bucket_hook(flat, params, views)
-        buckets.append((params, sum(sizes)))
+        buckets.append((params, sum(sizes), 1.0))
+    # the first parameter group arrives a second time (a second decoder chunk of a batch above 64 utterances): contributions add
+    params, total, _ = buckets[0]
+    flat2 = torch.arange(total, dtype=torch.float32) * (rank + 1) * 2.0
+    views2, off = [], 0
+    for p in params:
+        views2.append(flat2[off:off + p.numel()].view_as(p))
+        off += p.numel()
+    m._grad_bucket_hook(flat2, params, views2)
+    buckets[0] = (params, total, 3.0)
     n = gs.finish()
-    ok = n == 8 + 7 + 6
-    for params, total in buckets:
-        want = torch.arange(total, dtype=torch.float32) * (sum(range(1, world + 1)) / world)  # mean over ranks
+    ok = n == 8 + 7 + 6 + 8
+    for params, total, mult in buckets:
+        want = torch.arange(total, dtype=torch.float32) * (mult * sum(range(1, world + 1)) / world)  # mean over ranks
         got = torch.cat([p.grad.reshape(-1) for p in params])
         ok = ok and torch.allclose(got, want)
     ok = ok and not gs.pending
