@@ -1,0 +1,926 @@
+// Pipelined autoregressive decoder kernel (eval-mode synthesis: t2_decode_ar / t2_decode_ar_chunk).
+//
+// Same arithmetic, tile ownership and reduction orders as decoder_persistent_kernel (decoder.cu) -- 32 clusters x 4 CTAs, one CTA
+// per SM, CTA `rank` of cluster `tile` owns 8 hidden units of both LSTM cells and every fourth K-block of their gate contractions --
+// but a different SCHEDULE.  The round-1 profile showed a latency chain (DRAM 20 %, tensor pipe 7 %, 77 % of issue slots without an
+// eligible warp): HBM and the tensor pipe idled during the attention phase, the output stage and the four grid barriers of a frame,
+// and the CUDA cores idled while the two weight streams ran.  Here
+//   * two dedicated role warps (TMA producer, MMA issuer) run the weight stream CONTINUOUSLY and in dataflow order: a K-block is
+//     issued as soon as the activations it multiplies exist (its "gate" = the grid barrier that publishes them).  Of the 17 K-blocks a
+//     CTA contracts per frame only 3 sit on the dependent chain (the prenet K-block of the attention LSTM, the two context K-blocks
+//     of the decoder LSTM); the other 14 (att_h / rnn_h / old-context columns) stream behind the attention phase and the output stage;
+//   * eight worker warps run the dependent chain: LSTM tails, attention, output stage, grid barriers;
+//   * the location term of the attention energies (location conv k=31 + location dense, model/attention.py:54-56) is ONE tcgen05
+//     contraction per frame: the two linear layers are folded into a 62-tap filter bank G[a][c][j] at commit, the A operand is the
+//     Toeplitz matrix of (previous, cumulative) weights written straight into TENSOR MEMORY by the threads that own the rows, the
+//     result stays in TMEM next to a resident copy of this CTA's processed-memory slice, and the energy step reads both with
+//     tcgen05.ld.  No shared or global memory holds a location term any more (round 1: 6.5 MB per frame through L2 and 7.3 us of
+//     CUDA-core work beside the decoder GEMM), and the stage ring is never used as scratch, which is what lets the stream run on.
+#include "decoder.cuh"
+#define D2_SYNC() asm volatile("bar.sync 1, 256;" ::: "memory")
+#include "dec_shared.cuh"
+
+#define AR_THREADS 320     // warps 0..7 workers, warp 8 TMA producer, warp 9 MMA issuer
+#define AR_STAGES 3
+#define AR_COL_ATT 0u      // TMEM columns: attention-LSTM accumulator [128 gate rows x 64 utterances]
+#define AR_COL_DEC 64u     // decoder-LSTM accumulator
+#define AR_COL_LOC 128u    // location term [128 positions x 128 attention dims]
+#define AR_COL_PM 256u     // processed memory of this CTA's positions, resident for the whole launch
+#define AR_COL_THI 384u    // Toeplitz operand, hi plane: 128 positions x 64 taps bf16 = 32 columns
+#define AR_COL_TLO 416u    // lo plane
+#define AR_MAX_ENT 40
+
+namespace {
+
+struct KbEnt { unsigned char gemm, kb, gate, flags; };   // flags: 1 first block of its accumulator, 2 last, 4 belongs to frame t+1
+enum { G_X = 0, G_Q = 1, G_C = 2, G_R = 3 };
+
+struct ArSmem {
+  uint8_t* stages;
+  float* part;       // split-K partials | attention scratch | output-stage scratch (phases never overlap, see the hazards note)
+  uint8_t* gfilt;    // [2 hi/lo][128 a][64 taps] bf16, 128-B swizzled K-major: B operand of the location contraction
+  float* c_att;
+  float* c_dec;
+  float* wq;
+  float* h_s;
+  float* v;
+  float* octx;
+  float* wcum;       // [15 | L | 17] cumulative attention weights of this CTA's utterance (full row, zero halo)
+  KbEnt* prog;       // per-frame K-block program of this CTA
+  uint64_t* bars;
+  uint32_t* tmem_slot;
+  volatile unsigned* ctl;   // [0] gate count, [1] quit, [2] role failure, [3] entries in prog
+};
+
+__host__ __device__ inline size_t ar_smem_bytes(const D2Dims& d) {
+  return 1024 + (size_t)AR_STAGES * TG_STAGE_BYTES + TG_M * TG_PART_LD * 4 + 2 * 128 * 64 * 2 + 2 * 8 * D2_BP * 4 + 8 * (size_t)d.A * 4 + 8 * D2_BP * 4 +
+         (size_t)d.A * 4 + 2 * 64 * 4 + (size_t)(d.L + 32) * 4 + AR_MAX_ENT * sizeof(KbEnt) + 24 * 8 + 64;
+}
+
+__device__ __forceinline__ ArSmem ar_carve(uint8_t* base, const D2Dims& d) {
+  ArSmem s;
+  s.stages = base;
+  uint8_t* p = base + (size_t)AR_STAGES * TG_STAGE_BYTES;
+  s.gfilt = p;                             p += 2 * 128 * 64 * 2;    // keeps the 1024-B alignment of the ring
+  s.part = reinterpret_cast<float*>(p);    p += TG_M * TG_PART_LD * 4;
+  s.c_att = reinterpret_cast<float*>(p);   p += 8 * D2_BP * 4;
+  s.c_dec = reinterpret_cast<float*>(p);   p += 8 * D2_BP * 4;
+  s.wq = reinterpret_cast<float*>(p);      p += 8 * d.A * 4;
+  s.h_s = reinterpret_cast<float*>(p);     p += 8 * D2_BP * 4;
+  s.v = reinterpret_cast<float*>(p);       p += d.A * 4;
+  s.octx = reinterpret_cast<float*>(p);    p += 2 * 64 * 4;
+  s.wcum = reinterpret_cast<float*>(p);    p += (size_t)(d.L + 32) * 4;
+  s.prog = reinterpret_cast<KbEnt*>(p);    p += AR_MAX_ENT * sizeof(KbEnt);
+  p = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 7) & ~(uintptr_t)7);
+  s.bars = reinterpret_cast<uint64_t*>(p); p += 24 * 8;
+  s.tmem_slot = reinterpret_cast<uint32_t*>(p); p += 16;
+  s.ctl = reinterpret_cast<volatile unsigned*>(p);
+  return s;
+}
+// barrier slots
+enum { B_FULL = 0, B_EMPTY = AR_STAGES, B_ACC_ATT = 2 * AR_STAGES, B_ACC_DEC, B_LOC, B_RV, B_E, B_MEL, B_P1, B_W1, B_G, B_FIN };
+
+__device__ __forceinline__ void wsync() { D2_SYNC(); }
+
+__device__ __forceinline__ unsigned ld_acquire_cta(const volatile unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(tc::smem_u32(const_cast<const unsigned*>(p))) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_cta(volatile unsigned* p, unsigned v) {
+  asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(tc::smem_u32(const_cast<unsigned*>(p))), "r"(v) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {   // transaction count only, no arrival
+  asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(tc::smem_u32(bar)), "r"(bytes) : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem]^T  (A: lane = row, one 32-bit column = two consecutive bf16 along K)
+__device__ __forceinline__ void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+        "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]),
+        "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// K-block classes by the data the columns hold (decoder.cuh: x_att = [prenet | ctx | att_h], x_dec = [att_h | ctx | controls | rnn_h])
+__host__ __device__ inline int att_class(const D2Dims& d, int kb) {   // 0 prenet_t (gate X), 1 ctx_{t-1} (gate C of t-1), 2 att_h_{t-1} (gate Q of t-1)
+  const int c0 = kb * TG_BK;
+  if (c0 < d.P) return 0;
+  if (c0 < d.P + d.EF) return 1;
+  return 2;
+}
+__host__ __device__ inline int dec_class(const D2Dims& d, int kb) {   // 0 att_h_t (gate Q), 1 ctx_t (gate C), 2 rnn_h_{t-1} / controls / padding (gate R of t-1)
+  const int c0 = kb * TG_BK, c1 = c0 + TG_BK;
+  if (c0 < d.H + d.EF && c1 > d.H) return 1;
+  if (c0 < d.H) return 0;
+  return 2;
+}
+
+// The K-block program of CTA `rank`, in issue order (see the file comment).  Returns the entry count.
+__host__ __device__ inline int build_program(const D2Dims& d, int rank, KbEnt* out) {
+  const int nka = d.KattP / TG_BK, nkd = d.KdecP / TG_BK;
+  int n = 0;
+  auto emit = [&](int gemm, int cls, int gate, int next) {
+    for (int kb = rank; kb < (gemm ? nkd : nka); kb += D2_CLUSTER)
+      if ((gemm ? dec_class(d, kb) : att_class(d, kb)) == cls) {
+        if (n < AR_MAX_ENT) out[n] = KbEnt{(unsigned char)gemm, (unsigned char)kb, (unsigned char)gate, (unsigned char)(next ? 4 : 0)};
+        ++n;
+      }
+  };
+  emit(0, 0, G_X, 0);   // att.P(t)
+  const int last_att = n - 1;
+  emit(1, 0, G_Q, 0);   // dec.A(t)
+  const int first_att = n;
+  emit(0, 2, G_Q, 1);   // att.H(t+1)
+  emit(1, 1, G_C, 0);   // dec.C(t)
+  const int last_dec = n - 1;
+  emit(0, 1, G_C, 1);   // att.C(t+1)
+  const int first_dec = n;
+  emit(1, 2, G_R, 1);   // dec.R(t+1)
+  if (n <= AR_MAX_ENT && last_att >= 0 && first_att < n && last_dec > last_att && first_dec < n) {
+    out[last_att].flags |= 2; out[first_att].flags |= 1; out[last_dec].flags |= 2; out[first_dec].flags |= 1;
+  }
+  return n;
+}
+
+// ------------------------------------------------------------------------------------------ grid barrier (workers only)
+struct ArGridBar {
+  unsigned* ctr;
+  unsigned* abort_flag;
+  unsigned nblocks, epoch;
+  int* ok_s;   // shared word
+  __device__ void arrive(bool fail, volatile unsigned* ctl) {
+    asm volatile("fence.proxy.async.global;" ::: "memory");   // operands written with generic stores are read by TMA after the barrier
+    if (fail) ctl[2] = 1u;
+    wsync();
+    if (threadIdx.x == 0) {
+      ++epoch;
+      if (ctl[2] != 0u) { atomicExch(abort_flag, 1u); atomicOr(ctr, 0x80000000u); }
+      asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+    }
+  }
+  // returns false when the grid aborts; on success thread 0 opens the producer's next gate (ctl[0])
+  __device__ bool wait(volatile unsigned* ctl) {
+    if (threadIdx.x == 0) {
+      const unsigned target = epoch * nblocks;
+      unsigned v;
+      long long spins = 0;
+      while ((((v = ld_acquire_u32(ctr)) & 0x7fffffffu) < target) && !(v & 0x80000000u)) {
+        if (++spins > (1ll << 24)) { atomicExch(abort_flag, 1u); atomicOr(ctr, 0x80000000u); v = 0x80000000u; break; }
+      }
+      const int ok = (v & 0x80000000u) == 0u;
+      *ok_s = ok;
+      if (ok) st_release_cta(ctl, ctl[0] + 1u);
+    }
+    wsync();
+    return *ok_s != 0;
+  }
+  __device__ bool sync(bool fail, volatile unsigned* ctl) { arrive(fail, ctl); return wait(ctl); }
+};
+
+// TMEM accumulator columns [col, col+64) -> part[128][TG_PART_LD]; worker warp w reads lanes 32*(w%4).. and columns 32*(w/4)..
+__device__ __forceinline__ void ar_accum_to_smem(uint32_t tmem, uint32_t col, float* part) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int lane0 = 32 * (warp & 3), col0 = 32 * (warp >> 2);
+  float v[32];
+  tc::tmem_ld32(tmem + ((uint32_t)lane0 << 16) + col + col0, v);
+  tc::tmem_ld_wait();
+  float* dst = part + (size_t)(lane0 + lane) * TG_PART_LD + col0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) *reinterpret_cast<float4*>(dst + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+  tc::tc_fence_before();
+}
+
+// Rendezvous of the worker warps of the four CTAs of a cluster (barrier.cluster would count the role warps too): every CTA's thread 0
+// arrives on all four barriers with release, everybody waits on the local one with acquire.
+__device__ __forceinline__ bool cluster_rendezvous(uint64_t* bar, uint32_t& phase) {
+  wsync();
+  if (threadIdx.x == 0) {
+    const uint32_t a = tc::smem_u32(bar);
+#pragma unroll
+    for (uint32_t r = 0; r < D2_CLUSTER; ++r) tc::mbar_arrive_cluster(tc::mapa(a, r));
+  }
+  const bool ok = tc::mbar_wait_cluster(bar, phase);
+  phase ^= 1u;
+  return ok;
+}
+
+// ------------------------------------------------------------------------------------------ attention
+// Scratch (floats, in `part`): q[A] | qh[8A] | ep[2][128] | red[64] | cred[4*cols] | w row: 15 zeros | L | 17 zeros
+struct ArAtt { float *q_s, *qh, *ep, *red, *cred, *wrow; };
+__device__ __forceinline__ ArAtt ar_att_scratch(float* part, int L, int A, int EF, int S) {
+  ArAtt a;
+  a.q_s = part;
+  a.qh = a.q_s + A;
+  a.ep = a.qh + 8 * A;
+  a.red = a.ep + 256;
+  a.cred = a.red + 64;
+  a.wrow = a.cred + 4 * (size_t)((((EF + S - 1) / S) + 3) & ~3);
+  return a;
+}
+__host__ __device__ inline size_t ar_att_scratch_floats(int L, int A, int EF, int S) {
+  return 9 * (size_t)A + 256 + 64 + 4 * (size_t)((((EF + S - 1) / S) + 3) & ~3) + L + 32;
+}
+
+// Toeplitz rows of this CTA's positions -> tensor memory, then the location contraction (issued by thread 0).
+//   T[p][k]      = w   [l0 + p + k - 15]   k = 0..30
+//   T[p][32 + k] = wcum[l0 + p + k - 15]   k = 0..30        (taps 31 and 63 are zero, and so are those columns of G)
+// Worker warp w owns TMEM lanes 32*(w%4)..+31 (= positions) and writes plane w/4 (0 = hi, 1 = lo).
+__device__ __forceinline__ void build_toeplitz_and_issue(const ArSmem& sm, const float* wrow, uint32_t tmem, int l0, int nl, int npass,
+                                                         uint64_t* loc_bar) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int p = 32 * (warp & 3) + lane, plane = warp >> 2;
+  uint32_t r[32];
+  if (p < nl && (plane == 0 || npass == 3)) {
+    const float* a = wrow + l0 + p;       // wrow[15 + l] holds position l: tap k reads wrow[l0 + p + k]
+    const float* c = sm.wcum + l0 + p;
+#pragma unroll
+    for (int cc = 0; cc < 16; ++cc) {
+      float x0 = a[2 * cc], x1 = (2 * cc + 1 < D2_LOC_K) ? a[2 * cc + 1] : 0.f;
+      float y0 = c[2 * cc], y1 = (2 * cc + 1 < D2_LOC_K) ? c[2 * cc + 1] : 0.f;
+      __nv_bfloat16 h0, l0_, h1, l1, g0, m0, g1, m1;
+      tc::split_bf16(x0, h0, l0_); tc::split_bf16(x1, h1, l1);
+      tc::split_bf16(y0, g0, m0); tc::split_bf16(y1, g1, m1);
+      r[cc] = plane ? pack2_bf16(l0_, l1) : pack2_bf16(h0, h1);
+      r[16 + cc] = plane ? pack2_bf16(m0, m1) : pack2_bf16(g0, g1);
+    }
+  } else {
+#pragma unroll
+    for (int cc = 0; cc < 32; ++cc) r[cc] = 0u;
+  }
+  tmem_st32(tmem + ((uint32_t)(32 * (warp & 3)) << 16) + (plane ? AR_COL_TLO : AR_COL_THI), r);
+  tmem_st_wait();
+  tc::tc_fence_before();
+  wsync();
+  if (threadIdx.x == 0) {
+    tc::tc_fence_after();
+    const uint32_t idesc = tc::idesc_bf16_f32(128, 128);
+    const uint64_t ghi = tc::smem_desc_sw128(tc::smem_u32(sm.gfilt)), glo = tc::smem_desc_sw128(tc::smem_u32(sm.gfilt) + 128 * 64 * 2);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint64_t adv = (uint64_t)(k * 32 >> 4);
+      umma_bf16_ts(tmem + AR_COL_LOC, tmem + AR_COL_THI + 8u * k, ghi + adv, idesc, k ? 1u : 0u);
+      if (npass == 3) {
+        umma_bf16_ts(tmem + AR_COL_LOC, tmem + AR_COL_TLO + 8u * k, ghi + adv, idesc, 1u);
+        umma_bf16_ts(tmem + AR_COL_LOC, tmem + AR_COL_THI + 8u * k, glo + adv, idesc, 1u);
+      }
+    }
+    tc::umma_commit(loc_bar);
+  }
+}
+
+struct ArAttState {
+  int b, part, S, l0, nl, Leff;
+  bool active, masked;     // masked: the position this thread owns in the energy step is padding
+};
+
+// Attention of frame t for this CTA's utterance slice.  Returns false on a wait timeout.  The grid barrier that publishes the context
+// is ARRIVED at inside (after the context stores) and the next frame's Toeplitz operand is built while it completes.
+__device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, const ArSmem& sm, const ArAttState& at, uint32_t tmem,
+                             int cur, int nxt, int t_out, uint32_t fphase, ArGridBar& bar, bool& alive, long long* prof_last) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int L = d.L, A = d.A, EF = d.EF, S = at.S;
+  const ArAtt as = ar_att_scratch(sm.part, L, A, EF, S);
+  bool ok = true;
+  auto mark = [&](int slot) {
+    if (blockIdx.x == 0 && tid == 0 && s.prof) { const long long now = clock64(); s.prof[slot] += (unsigned long long)(now - *prof_last); *prof_last = now; }
+  };
+  if (at.active) {
+    if (tid == 0) tc::mbar_arrive_expect_tx(sm.bars + B_E, (uint32_t)(L * 4));   // the S energy slices of this frame
+    {  // processed query = sum of the 128 per-CTA partials in a fixed order (as decoder.cu)
+      const int a4 = lane * 4;
+      if (a4 < A) {
+        const float* qp = s.qpart + ((size_t)at.b * 128 + warp * 16) * A + a4;
+        float4 v[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = __ldcg(reinterpret_cast<const float4*>(qp + (size_t)i * A));
+        float4 acc = v[0];
+#pragma unroll
+        for (int i = 1; i < 16; ++i) { acc.x += v[i].x; acc.y += v[i].y; acc.z += v[i].z; acc.w += v[i].w; }
+        *reinterpret_cast<float4*>(as.qh + warp * A + a4) = acc;
+      }
+    }
+    if (tid < 32) { as.wrow[tid < 15 ? tid : L + tid] = 0.f; }   // halo: 15 zeros in front, 17 behind
+    wsync();
+    if (tid < A) {
+      float qv = as.qh[tid];
+#pragma unroll
+      for (int g = 1; g < 8; ++g) qv += as.qh[g * A + tid];
+      as.q_s[tid] = qv;
+    }
+    if (!tc::mbar_wait(sm.bars + B_LOC, fphase)) ok = false;   // location term of this frame is in TMEM
+    tc::tc_fence_after();
+    wsync();
+    mark(10);
+    {  // energies: thread = (position = TMEM lane, half of the attention dims); location term + processed memory from tensor memory
+      const int lane0 = 32 * (warp & 3), half = warp >> 2, p = lane0 + lane;
+      float e = 0.f;
+#pragma unroll 1
+      for (int c32 = 0; c32 < 2; ++c32) {
+        const int a0 = 64 * half + 32 * c32;
+        float x[32], pm[32];
+        tc::tmem_ld32(tmem + ((uint32_t)lane0 << 16) + AR_COL_LOC + a0, x);
+        tc::tmem_ld32(tmem + ((uint32_t)lane0 << 16) + AR_COL_PM + a0, pm);
+        tc::tmem_ld_wait();
+        if (a0 < A) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) e = fmaf(sm.v[a0 + i], tanh_fast(as.q_s[a0 + i] + x[i] + pm[i]), e);
+        }
+      }
+      as.ep[half * 128 + p] = e;
+    }
+    tc::tc_fence_before();
+    wsync();
+    if (tid < at.nl) {   // masked_fill (model/attention.py:63) and the exchange: every part of the utterance gets the whole energy row
+      const float e = at.masked ? -INFINITY : (as.ep[tid] + as.ep[128 + tid]);
+      const uint32_t my_rank = tc::cluster_ctarank(), base_rank = my_rank - (uint32_t)at.part;
+      const uint32_t dst = tc::smem_u32(as.wrow + 15 + at.l0 + tid), eb = tc::smem_u32(sm.bars + B_E);
+      for (int r = 0; r < S; ++r) tc::st_async_f32(tc::mapa(dst, base_rank + (uint32_t)r), e, tc::mapa(eb, base_rank + (uint32_t)r));
+    }
+    mark(11);
+    if (!tc::mbar_wait_cluster(sm.bars + B_E, fphase)) ok = false;
+    mark(12);
+    // softmax over the full row (model/attention.py:65); every thread keeps to its own positions through the three passes
+    float* wr = as.wrow + 15;
+    float mx = -INFINITY;
+#pragma unroll 1
+    for (int l = tid; l < L; l += 256) mx = fmaxf(mx, wr[l]);
+    mx = warp_max(mx);
+    if (lane == 0) as.red[warp] = mx;
+    wsync();
+    mx = as.red[0];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) mx = fmaxf(mx, as.red[i]);
+    float sum = 0.f;
+#pragma unroll 1
+    for (int l = tid; l < L; l += 256) {
+      const float pe = expf(wr[l] - mx);
+      wr[l] = pe;
+      sum += pe;
+    }
+    sum = warp_sum(sum);
+    if (lane == 0) as.red[32 + warp] = sum;
+    wsync();
+    sum = as.red[32];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) sum += as.red[32 + i];
+    const float inv = 1.0f / sum;
+    const int l1 = at.l0 + at.nl;
+#pragma unroll 1
+    for (int l = tid; l < L; l += 256) {
+      const float w = wr[l] * inv;
+      wr[l] = w;
+      sm.wcum[15 + l] += w;                                                   // model/decoder.py:90 (every part keeps the whole row)
+      if (l >= at.l0 && l < l1) io.aligns[((size_t)at.b * io.Tmax + t_out) * L + l] = w;
+    }
+    wsync();
+    mark(13);
+    // context columns of this part (model/attention.py:66-67)
+    const int cols_per = ((EF + S - 1) / S + 3) & ~3;
+    const int c0 = at.part * cols_per, c1 = min(EF, c0 + cols_per);
+    const int nq = max(0, (c1 - c0 + 3) >> 2);
+    const float* mem = io.memory + (size_t)at.b * L * EF;
+    const int lg = tid >> 6, cq0 = tid & 63;
+#pragma unroll 1
+    for (int cq = cq0; cq < nq; cq += 64) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4* mp = reinterpret_cast<const float4*>(mem + c0) + cq;
+      const size_t rs = (size_t)EF / 4;
+      int l = lg;
+      for (; l + 28 < at.Leff; l += 32) {
+        float4 m[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) m[u] = __ldg(mp + (size_t)(l + 4 * u) * rs);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const float w = wr[l + 4 * u];
+          acc.x = fmaf(w, m[u].x, acc.x); acc.y = fmaf(w, m[u].y, acc.y);
+          acc.z = fmaf(w, m[u].z, acc.z); acc.w = fmaf(w, m[u].w, acc.w);
+        }
+      }
+      for (; l < at.Leff; l += 4) {
+        const float4 m4 = __ldg(mp + (size_t)l * rs);
+        const float w = wr[l];
+        acc.x = fmaf(w, m4.x, acc.x); acc.y = fmaf(w, m4.y, acc.y);
+        acc.z = fmaf(w, m4.z, acc.z); acc.w = fmaf(w, m4.w, acc.w);
+      }
+      *reinterpret_cast<float4*>(as.cred + (size_t)lg * cols_per + cq * 4) = acc;
+    }
+    wsync();
+    const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
+    __nv_bfloat16* xa = s.xatt + (size_t)nxt * 2 * pa;   // next frame's attention-LSTM input
+    __nv_bfloat16* xd = s.xdec + (size_t)cur * 2 * pd;   // this frame's decoder-LSTM input
+#pragma unroll 1
+    for (int c = tid; c < c1 - c0; c += 256) {
+      const float v = as.cred[c] + as.cred[cols_per + c] + as.cred[2 * cols_per + c] + as.cred[3 * cols_per + c];
+      const int col = c0 + c;
+      store_split(xa, pa, d.KattP, at.b, d.P + col, v);
+      store_split(xd, pd, d.KdecP, at.b, d.H + col, v);
+      s.projin[(size_t)at.b * d.KprojP + d.R + col] = v;
+    }
+  }
+  mark(14);
+  bar.arrive(!ok, sm.ctl);
+  // while the barrier completes: the Toeplitz operand of the NEXT frame's location term (depends on this frame's weights only)
+  if (at.active) build_toeplitz_and_issue(sm, ar_att_scratch(sm.part, L, A, EF, S).wrow, tmem, at.l0, at.nl, d.npass, sm.bars + B_LOC);
+  alive = bar.wait(sm.ctl);
+  return ok;
+}
+
+// ------------------------------------------------------------------------------------------ output stage (all 8 worker warps)
+// As output_side / proj_ctx_side of decoder.cu, on eight warps and on the dependent chain (nothing streams on these warps).
+__device__ void ar_proj_ctx(const D2Dims& d, const D2Weights& w, const D2State& s, const ArSmem& sm, uint32_t rank, int cluster) {
+  const int pw = threadIdx.x >> 5, NW = 8;
+  const int B = d.B, M = d.M, KP = d.KprojP, Kc = KP - d.H;
+  const int b0 = 2 * cluster;
+  if (b0 >= B) return;
+  const float* x0 = s.projin + (size_t)b0 * KP + d.H;
+  const float* x1 = s.projin + (size_t)min(b0 + 1, B - 1) * KP + d.H;
+  const int rows_per = (M + 1 + D2_CLUSTER - 1) / D2_CLUSTER, r0 = (int)rank * rows_per, nr = max(0, min(rows_per, M + 1 - r0));
+  const int rpw = (nr + NW - 1) / NW, rb = r0 + pw * rpw, re = min(r0 + nr, rb + rpw);
+  rows_dot2<true>(w.Wproj + d.H, KP, Kc >> 2, rb, re, x0, x1, sm.octx, r0, 64);
+}
+
+__device__ bool ar_output(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, const ArSmem& sm, uint32_t rank, int cluster,
+                          int tg_, int nxt, uint32_t& cphase, long long* prof_last) {
+  const int tid = threadIdx.x, lane = tid & 31, pw = tid >> 5, NW = 8;
+  const int B = d.B, M = d.M, P = d.P, KP = d.KprojP, MP = (M + 1 + 3) & ~3;
+  const int rq = P / D2_CLUSTER;
+  float* mel_s = sm.part;
+  float* p1_s = mel_s + 2 * MP;
+  float* out_s = p1_s + 2 * P;
+  const int YS = max(64, rq);
+  float* y_s = out_s + 2 * rq;
+  float* w1_s = y_s + 6 * YS;
+  const int w1_off = 2 * MP + 2 * P + 2 * rq + 6 * YS;
+  const bool w1_smem = (M >> 2) <= 32 && (w1_off & 3) == 0 && w1_off + rq * M <= TG_M * TG_PART_LD;
+  uint64_t* mel_bar = sm.bars + B_MEL;
+  uint64_t* p1_bar = sm.bars + B_P1;
+  uint64_t* wbar = sm.bars + B_W1;
+  const int b0 = 2 * cluster;
+  if (b0 >= B) return true;         // uniform over the cluster
+  bool ok = true;
+  const int j = lane & 1, b = b0 + j;
+  auto mark = [&](int slot) {
+    if (blockIdx.x == 0 && tid == 0 && s.prof) { const long long now = clock64(); s.prof[slot] += (unsigned long long)(now - *prof_last); *prof_last = now; }
+  };
+  if (tid == 0) {
+    const uint32_t nu = (uint32_t)min(2, B - b0);
+    tc::mbar_arrive_expect_tx(mel_bar, nu * (uint32_t)M * 4u);
+    tc::mbar_arrive_expect_tx(p1_bar, nu * (uint32_t)P * 4u);
+    if (w1_smem) {
+      tc::mbar_arrive_expect_tx(wbar, (uint32_t)(rq * M * 4));
+      tc::bulk_load_1d(w1_s, w.W1 + (size_t)rank * rq * M, (uint32_t)(rq * M * 4), wbar);
+    }
+  }
+  const int H4 = d.H >> 2;
+  {
+    const int rows_per = (M + 1 + D2_CLUSTER - 1) / D2_CLUSTER, r0 = (int)rank * rows_per, nr = max(0, min(rows_per, M + 1 - r0));
+    const int rpw = (nr + NW - 1) / NW, rb = r0 + pw * rpw, re = min(r0 + nr, rb + rpw);
+    rows_dot2<true>(w.Wproj, KP, H4, rb, re, s.projin + (size_t)b0 * KP, s.projin + (size_t)min(b0 + 1, B - 1) * KP, y_s, r0, YS);
+#pragma unroll 1
+    for (int r = rb + (lane >> 1); r < re && b < B; r += 16) {
+      const float v = y_s[j * YS + r - r0] + sm.octx[j * 64 + r - r0] + __ldg(w.bproj + r);
+      if (r < M) {
+        io.mels[((size_t)b * io.Tmax + tg_) * M + r] = v;
+        st_async_all(mel_s + j * MP + r, v, mel_bar);
+      } else {
+        io.gates[(size_t)b * io.Tmax + tg_] = v;
+        if (io.stop_enabled) {  // model/tacotron2.py:319-320
+          if (v < 0.0f) s.done[b] = 1;
+          if (v >= 0.0f) s.lengths[b] += 1;
+        }
+      }
+    }
+  }
+  mark(4);
+  const float pscale = 1.0f / (1.0f - d.p_prenet);
+  const int pr0 = (int)rank * rq;
+  const int rpw = (rq + NW - 1) / NW, rb = pr0 + pw * rpw, re = min(pr0 + rq, rb + rpw);
+  float* y1 = y_s + 2 * YS;
+  float* y2 = y_s + 4 * YS;
+  if (!tc::mbar_wait_cluster(mel_bar, cphase)) ok = false;
+  if (w1_smem) {
+    if (!tc::mbar_wait(wbar, cphase)) ok = false;
+    rows_short<8, 1, true>(w1_s - (ptrdiff_t)pr0 * M, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
+  } else if ((M >> 2) <= 32) rows_short<8, 1, false>(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
+  else rows_dot2<false>(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
+#pragma unroll 1
+  for (int r = rb + (lane >> 1); r < re && b < B; r += 16) {
+    const size_t kidx = (((size_t)(tg_ + 1) * 2 + 0) * B + b) * P + r;
+    const bool keep = io.prenet_keep ? (io.prenet_keep[kidx] != 0) : rng_keep(io.seed, kidx, d.p_prenet);
+    const float v = y1[j * YS + r - pr0];
+    st_async_all(p1_s + j * P + r, (v > 0.f && keep) ? v * pscale : 0.f, p1_bar);
+  }
+  mark(5);
+  if (!tc::mbar_wait_cluster(p1_bar, cphase)) ok = false;
+  cphase ^= 1u;
+  const long long pa = (long long)D2_BP * d.KattP;
+  __nv_bfloat16* xa = s.xatt + (size_t)nxt * 2 * pa;
+  const bool vec = (rq & 7) == 0 && (d.KattP & 7) == 0;
+  if ((P >> 2) <= 64) rows_short<8, 2, false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
+  else rows_dot2<false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
+#pragma unroll 1
+  for (int r = rb + (lane >> 1); r < re; r += 16) {
+    float v = 0.f;
+    if (b < B) {
+      const size_t kidx = (((size_t)(tg_ + 1) * 2 + 1) * B + b) * P + r;
+      const bool keep = io.prenet_keep ? (io.prenet_keep[kidx] != 0) : rng_keep(io.seed, kidx, d.p_prenet);
+      v = y2[j * YS + r - pr0];
+      v = (v > 0.f && keep) ? v * pscale : 0.f;
+      if (!vec) store_split(xa, pa, d.KattP, b, r, v);
+    }
+    if (vec) out_s[j * rq + r - pr0] = v;
+  }
+  if (vec) {
+    wsync();
+#pragma unroll 1
+    for (int i = tid; i < 4 * (rq >> 3); i += 256) {
+      const int pl = i & 1, jj = (i >> 1) & 1, c8 = i >> 2;
+      if (b0 + jj < B) store_plane8(xa + pl * pa + (size_t)(b0 + jj) * d.KattP + pr0 + 8 * c8, out_s + jj * rq + 8 * c8, pl, true);
+    }
+  }
+  mark(6);
+  return ok;
+}
+
+// ------------------------------------------------------------------------------------------ the kernel
+// Profiling slots (CTA 0, thread 0; SM-clock cycles summed over the launch):
+//   8 wait for the attention-LSTM accumulator (prenet K-block on the chain), 0 its tail, 1 query partials + Q barrier,
+//   10 query sum + location-term wait, 11 energies + exchange issue, 12 exchange wait, 13 softmax, 14 context + stores,
+//   2 C barrier with the Toeplitz build beside it, 15 context half of the projection, 9 wait for the decoder-LSTM accumulator,
+//   3 its tail + R barrier, 4/5/6 projection / prenet 1 / prenet 2, 7 X barrier + stop check
+__global__ void __launch_bounds__(AR_THREADS, 1)
+decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ CUtensorMap gmap, D2Dims d, D2Weights w, D2State s, D2IO io) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* base = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+  const ArSmem sm = ar_carve(base, d);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const bool worker = warp < 8;
+  const uint32_t rank = tc::cluster_ctarank();
+  const int tile = blockIdx.x / D2_CLUSTER;
+  const int unit0 = tile * 32 + (int)rank * 8;
+  const int B = d.B, L = d.L, A = d.A;
+  const int S = (B * 4 <= (int)gridDim.x) ? 4 : ((B * 2 <= (int)gridDim.x) ? 2 : 1);
+  __shared__ int ok_word;
+
+  // ---- one-time setup
+  if (tid == 0) {
+    tc::prefetch_tmap(&maps.w_att); tc::prefetch_tmap(&maps.w_dec); tc::prefetch_tmap(&maps.x_att); tc::prefetch_tmap(&maps.x_dec);
+    tc::prefetch_tmap(&gmap);
+    for (int i = 0; i < AR_STAGES; ++i) { tc::mbar_init(sm.bars + B_FULL + i, 1); tc::mbar_init(sm.bars + B_EMPTY + i, 1); }
+    tc::mbar_init(sm.bars + B_ACC_ATT, 1); tc::mbar_init(sm.bars + B_ACC_DEC, 1); tc::mbar_init(sm.bars + B_LOC, 1);
+    tc::mbar_init(sm.bars + B_RV, D2_CLUSTER); tc::mbar_init(sm.bars + B_E, 1); tc::mbar_init(sm.bars + B_MEL, 1);
+    tc::mbar_init(sm.bars + B_P1, 1); tc::mbar_init(sm.bars + B_W1, 1); tc::mbar_init(sm.bars + B_G, 1); tc::mbar_init(sm.bars + B_FIN, 1);
+    tc::fence_barrier_init();
+    sm.ctl[0] = 1u;   // gate count: the (virtual) barrier that publishes the prenet columns of frame 0 counts as passed
+    sm.ctl[1] = 0u; sm.ctl[2] = 0u;
+    sm.ctl[3] = (unsigned)build_program(d, (int)rank, sm.prog);
+  }
+  if (warp == 9) tc::tmem_alloc<512>(sm.tmem_slot);   // warp 9 owns alloc + dealloc
+  if (worker) {
+#pragma unroll 1
+    for (int i = tid; i < A; i += 256) sm.v[i] = w.v[i];
+#pragma unroll 1
+    for (int i = tid; i < 8 * A; i += 256) sm.wq[i] = w.Wq[(size_t)(i % A) * d.H + unit0 + i / A];
+#pragma unroll 1
+    for (int i = tid; i < 8 * D2_BP; i += 256) {
+      sm.c_att[i] = s.att_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP];
+      sm.c_dec[i] = s.rnn_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP];
+    }
+#pragma unroll 1
+    for (int i = tid; i < L + 32; i += 256) sm.wcum[i] = 0.f;
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = *sm.tmem_slot;
+  if (tid == 0) {   // the folded location filter bank G (hi | lo), 128-B swizzled by TMA
+    tc::mbar_arrive_expect_tx(sm.bars + B_G, 2u * 128u * 64u * 2u);
+    tc::tma_load_3d(sm.gfilt, &gmap, sm.bars + B_G, 0, 0, 0);
+  }
+  tc::cluster_sync();   // barrier inits of the whole cluster are visible before any remote arrive
+
+  const int nprog = (int)sm.ctl[3];
+  const int nkb_att = d.KattP / TG_BK, nkb_dec = d.KdecP / TG_BK;
+  const uint32_t stage_w = (uint32_t)(d.npass == 3 ? 2 * TG_W_TILE : TG_W_TILE), stage_x = (uint32_t)(d.npass == 3 ? 2 * TG_X_TILE : TG_X_TILE);
+
+  if (warp == 8) {
+    // =============================================================== TMA producer
+    if (lane == 0) {
+      const uint64_t wpol = tc::l2_policy_evict_first();
+      long long total = 0;   // K-blocks of the whole launch: prologue (entries of frame -1 that belong to frame 0) + per frame
+      // sequence position -> (frame, entry): frame -1 uses only the next-frame entries
+      int w_f = -1, w_e = 0, x_f = -1, x_e = 0;
+      long long w_n = 0, x_n = 0;
+      auto skip = [&](int f, int e) {   // entry e is not issued in frame f
+        const bool next = (sm.prog[e].flags & 4) != 0;
+        return (f < 0 && !next) || (f == io.n_steps - 1 && next);
+      };
+      auto advance = [&](int& f, int& e) {
+        do { if (++e == nprog) { e = 0; ++f; } } while (f < io.n_steps && skip(f, e));
+      };
+      if (skip(w_f, w_e)) advance(w_f, w_e);
+      if (skip(x_f, x_e)) advance(x_f, x_e);
+      int w_stage = 0, x_stage = 0;
+      uint32_t w_phase = 0;
+      long long idle = 0;
+      bool fenced_for = false;
+      unsigned fenced_gate = 0;
+      (void)total; (void)fenced_for;
+      while (x_f < io.n_steps) {
+        bool progressed = false;
+        if (w_f < io.n_steps && w_n - x_n < AR_STAGES && tc::mbar_try_wait(sm.bars + B_EMPTY + w_stage, w_phase ^ 1)) {
+          const KbEnt en = sm.prog[w_e];
+          uint8_t* st = sm.stages + (size_t)w_stage * TG_STAGE_BYTES;
+          mbar_expect_tx(sm.bars + B_FULL + w_stage, stage_w);
+          const int nkb = en.gemm ? nkb_dec : nkb_att;
+          tc::tma_load_3d_hint(st, en.gemm ? &maps.w_dec : &maps.w_att, sm.bars + B_FULL + w_stage, 0, (tile * nkb + en.kb) * TG_M, 0, wpol);
+          if (++w_stage == AR_STAGES) { w_stage = 0; w_phase ^= 1; }
+          ++w_n;
+          advance(w_f, w_e);
+          progressed = true;
+        }
+        if (x_n < w_n) {
+          const KbEnt en = sm.prog[x_e];
+          const int need = 4 * x_f + (int)en.gate + 1;
+          const unsigned have = ld_acquire_cta(sm.ctl);
+          if ((int)have >= need) {
+            if (have != fenced_gate) { asm volatile("fence.proxy.async;" ::: "memory"); fenced_gate = have; }   // peers' generic stores -> TMA reads
+            const int gf = x_f + ((en.flags & 4) ? 1 : 0);
+            uint8_t* st = sm.stages + (size_t)x_stage * TG_STAGE_BYTES;
+            tc::mbar_arrive_expect_tx(sm.bars + B_FULL + x_stage, stage_x);
+            tc::tma_load_3d(st + 2 * TG_W_TILE, en.gemm ? &maps.x_dec : &maps.x_att, sm.bars + B_FULL + x_stage, en.kb * TG_BK, 0, (gf & 1) * 2);
+            if (++x_stage == AR_STAGES) x_stage = 0;
+            ++x_n;
+            advance(x_f, x_e);
+            progressed = true;
+          }
+        }
+        if (progressed) { idle = 0; continue; }
+        if (sm.ctl[1] != 0u) break;                              // workers stopped (stop gate, abort): no more gates will open
+        if (++idle > (1ll << 26)) { sm.ctl[2] = 1u; break; }     // never hang the GPU
+      }
+      // weight tiles already in flight for K-blocks that will never run (early stop): complete their stages with the (stale) x
+      // tile so that no bulk copy is outstanding when the CTA exits; the MMA issuer drains them
+      while (x_n < w_n) {
+        const KbEnt en = sm.prog[x_e];
+        uint8_t* st = sm.stages + (size_t)x_stage * TG_STAGE_BYTES;
+        tc::mbar_arrive_expect_tx(sm.bars + B_FULL + x_stage, stage_x);
+        tc::tma_load_3d(st + 2 * TG_W_TILE, en.gemm ? &maps.x_dec : &maps.x_att, sm.bars + B_FULL + x_stage, en.kb * TG_BK, 0, 0);
+        if (++x_stage == AR_STAGES) x_stage = 0;
+        ++x_n;
+        advance(x_f, x_e);
+      }
+      st_release_cta(sm.ctl + 4, (unsigned)x_n);   // total K-blocks issued
+      st_release_cta(sm.ctl + 5, 1u);              // producer done
+    }
+    __syncwarp();
+  } else if (warp == 9) {
+    // =============================================================== MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = tc::idesc_bf16_f32(TG_M, TG_N);
+      int f = -1, e = 0;
+      auto skip = [&](int ff, int ee) {
+        const bool next = (sm.prog[ee].flags & 4) != 0;
+        return (ff < 0 && !next) || (ff == io.n_steps - 1 && next);
+      };
+      auto advance = [&]() { do { if (++e == nprog) { e = 0; ++f; } } while (f < io.n_steps && skip(f, e)); };
+      if (skip(f, e)) advance();
+      int stage = 0;
+      uint32_t phase = 0;
+      long long n = 0;
+      bool out = false;
+      while (f < io.n_steps && !out) {
+        long long spins = 0;
+        while (!tc::mbar_try_wait(sm.bars + B_FULL + stage, phase)) {
+          if (ld_acquire_cta(sm.ctl + 5) != 0u && (long long)ld_acquire_cta(sm.ctl + 4) == n) { out = true; break; }   // producer ended: nothing more comes
+          if (++spins > (1ll << 26)) { sm.ctl[2] = 1u; out = true; break; }
+        }
+        if (out) break;
+        tc::tc_fence_after();
+        const KbEnt en = sm.prog[e];
+        const uint32_t sbase = tc::smem_u32(sm.stages + (size_t)stage * TG_STAGE_BYTES);
+        const uint64_t whi = tc::smem_desc_sw128(sbase), wlo = tc::smem_desc_sw128(sbase + TG_W_TILE);
+        const uint64_t xhi = tc::smem_desc_sw128(sbase + 2 * TG_W_TILE), xlo = tc::smem_desc_sw128(sbase + 2 * TG_W_TILE + TG_X_TILE);
+        const uint32_t dcol = tmem + (en.gemm ? AR_COL_DEC : AR_COL_ATT);
+        uint32_t acc = (en.flags & 1) ? 0u : 1u;
+#pragma unroll
+        for (int k = 0; k < TG_BK / 16; ++k) {
+          const uint64_t adv = (uint64_t)(k * 32 >> 4);
+          tc::umma_bf16(dcol, whi + adv, xhi + adv, idesc, acc);
+          if (d.npass == 3) {
+            tc::umma_bf16(dcol, whi + adv, xlo + adv, idesc, 1u);
+            tc::umma_bf16(dcol, wlo + adv, xhi + adv, idesc, 1u);
+          }
+          acc = 1u;
+        }
+        tc::umma_commit(sm.bars + B_EMPTY + stage);
+        if (en.flags & 2) tc::umma_commit(sm.bars + (en.gemm ? B_ACC_DEC : B_ACC_ATT));
+        if (++stage == AR_STAGES) { stage = 0; phase ^= 1; }
+        ++n;
+        advance();
+      }
+      tc::umma_commit(sm.bars + B_FIN);   // every MMA of this thread has retired when this fires
+      tc::mbar_wait(sm.bars + B_FIN, 0);
+    }
+    __syncwarp();
+  } else {
+    // =============================================================== workers
+    ArGridBar bar{s.barrier, s.barrier + 1, gridDim.x, 0u, &ok_word};
+    long long prof_last = clock64();
+    auto prof_mark = [&](int slot) {
+      if (blockIdx.x == 0 && tid == 0 && s.prof) { const long long now = clock64(); s.prof[slot] += (unsigned long long)(now - prof_last); prof_last = now; }
+    };
+    ArAttState at{};
+    at.S = S; at.b = blockIdx.x / S; at.part = blockIdx.x % S; at.active = at.b < B;
+    {
+      const int Lc = (L + S - 1) / S;
+      at.l0 = at.part * Lc;
+      at.nl = max(0, min(L, at.l0 + Lc) - at.l0);
+    }
+    at.masked = false; at.Leff = 0;
+    if (at.active) {
+      const unsigned char* mk = io.mask + (size_t)at.b * L;
+      if (tid < at.nl) at.masked = mk[at.l0 + tid] != 0;
+      int le = 0;
+#pragma unroll 1
+      for (int l = tid; l < L; l += 256) if (mk[l] == 0) le = max(le, l + 1);
+      le = (int)warp_max((float)le);
+      if (lane == 0) sm.part[warp] = (float)le;
+      wsync();
+      for (int i = 0; i < 8; ++i) at.Leff = max(at.Leff, (int)sm.part[i]);
+      wsync();
+      // processed memory of this CTA's positions -> tensor memory (lane = position, column = attention dim), once
+      const int lane0 = 32 * (warp & 3), half = warp >> 2, p = lane0 + lane;
+#pragma unroll 1
+      for (int c32 = 0; c32 < 2; ++c32) {
+        const int a0 = 64 * half + 32 * c32;
+        uint32_t r[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) r[i] = 0u;
+        if (p < at.nl && a0 < A) {
+          const float4* src = reinterpret_cast<const float4*>(io.pmem + ((size_t)at.b * L + at.l0 + p) * A + a0);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 v4 = __ldg(src + i);
+            r[4 * i] = __float_as_uint(v4.x); r[4 * i + 1] = __float_as_uint(v4.y); r[4 * i + 2] = __float_as_uint(v4.z); r[4 * i + 3] = __float_as_uint(v4.w);
+          }
+        }
+        tmem_st32(tmem + ((uint32_t)lane0 << 16) + AR_COL_PM + a0, r);
+      }
+      tmem_st_wait();
+      // frame 0: previous and cumulative weights are zero (model/tacotron2.py:126-153) -> the location term is zero; run the
+      // same path so that the accumulator columns are defined
+      float* wrow = ar_att_scratch(sm.part, L, A, d.EF, S).wrow;
+#pragma unroll 1
+      for (int i = tid; i < L + 32; i += 256) wrow[i] = 0.f;
+      wsync();
+      if (!tc::mbar_wait(sm.bars + B_G, 0)) sm.ctl[2] = 1u;
+      build_toeplitz_and_issue(sm, wrow, tmem, at.l0, at.nl, d.npass, sm.bars + B_LOC);
+    }
+    const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
+    bool alive = true, fail = false, stop = false;
+    uint32_t rv_phase = 0, cphase = 0;
+    int frames = 0;
+#pragma unroll 1
+    for (int t = 0; t < io.n_steps && alive && !stop; ++t) {
+      const int tg_ = io.t0 + t;
+      const int cur = t & 1, nxt = cur ^ 1;
+      // ================= attention LSTMCell (model/decoder.py:70-75): only the prenet K-block of the contraction is still to come
+      if (!tc::mbar_wait(sm.bars + B_ACC_ATT, (uint32_t)(t & 1))) fail = true;
+      tc::tc_fence_after();
+      prof_mark(8);
+      ar_accum_to_smem(tmem, AR_COL_ATT, sm.part);
+      if (!cluster_rendezvous(sm.bars + B_RV, rv_phase)) fail = true;
+      {
+        const HOut ho{s.xatt + (size_t)nxt * 2 * pa, d.KattP, d.P + d.EF, pa, s.xdec + (size_t)cur * 2 * pd, d.KdecP, 0, pd, s.att_h_rm, d.H, 0};
+        lstm_tail(sm.part, rank, unit0, w.batt, d.H, sm.c_att, B, ho, nullptr, false, io.seed, 0ull, nullptr, sm.h_s);
+      }
+      prof_mark(0);
+      query_partial(sm.h_s, sm.wq, A, B, s.qpart + (size_t)blockIdx.x * A, (size_t)128 * A);
+      if (!(alive = bar.sync(fail, sm.ctl))) break;
+      prof_mark(1);
+      // ================= location-sensitive attention (model/attention.py:54-67, model/decoder.py:90) + C barrier
+      if (!ar_attention(d, s, io, sm, at, tmem, cur, nxt, tg_, (uint32_t)(t & 1), bar, alive, &prof_last)) fail = true;
+      if (!alive) break;
+      prof_mark(2);
+      // ================= decoder LSTMCell (model/decoder.py:94-101): the context K-blocks are on their way; meanwhile the context
+      // half of this frame's mel / gate projection
+      ar_proj_ctx(d, w, s, sm, rank, tile);
+      prof_mark(15);
+      if (!tc::mbar_wait(sm.bars + B_ACC_DEC, (uint32_t)(t & 1))) fail = true;
+      tc::tc_fence_after();
+      prof_mark(9);
+      ar_accum_to_smem(tmem, AR_COL_DEC, sm.part);
+      if (!cluster_rendezvous(sm.bars + B_RV, rv_phase)) fail = true;
+      {
+        const HOut ho{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, s.projin, d.KprojP, 0};
+        lstm_tail(sm.part, rank, unit0, w.bdec, d.H, sm.c_dec, B, ho, nullptr, false, io.seed, 0ull, nullptr, sm.h_s);
+      }
+      if (!(alive = bar.sync(fail, sm.ctl))) break;
+      prof_mark(3);
+      // ================= mel / gate projection, stop bookkeeping, prenet on the emitted frame (model/decoder.py:103-109,
+      // model/tacotron2.py:311-325)
+      if (!ar_output(d, w, s, io, sm, rank, tile, tg_, nxt, cphase, &prof_last)) fail = true;
+      frames = t + 1;
+      if (t + 1 < io.n_steps) {
+        if (!(alive = bar.sync(fail, sm.ctl))) break;
+        if (io.stop_enabled) {   // model/tacotron2.py:321-322: leave once every utterance has fired its stop gate
+          int mine = 1;
+#pragma unroll 1
+          for (int b = tid; b < B; b += 256) mine &= (ld_acquire_u32((const unsigned*)s.done + b) != 0u);
+          if (!mine) ok_word = 0;    // (ok_word is 1 after a successful barrier; the next barrier rewrites it)
+          wsync();
+          if (ok_word != 0 && t + 1 >= io.min_frames) stop = true;
+          wsync();
+        }
+        prof_mark(7);
+      }
+    }
+    if (fail) sm.ctl[2] = 1u;
+    wsync();
+    if (tid == 0) {
+      st_release_cta(sm.ctl + 1, 1u);   // role warps: no more gates
+      if (blockIdx.x == 0) {
+        const bool good = alive && sm.ctl[2] == 0u;
+        *s.n_frames = good ? frames : -1;
+        if (!good && s.status) atomicExch(s.status, 1u);
+      }
+    }
+#pragma unroll 1
+    for (int i = tid; i < 8 * D2_BP; i += 256) {
+      s.att_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP] = sm.c_att[i];
+      s.rnn_c[(size_t)(unit0 + i / D2_BP) * D2_BP + i % D2_BP] = sm.c_dec[i];
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::cluster_sync();   // no CTA exits while a peer may still write into its shared memory
+  if (warp == 9) tc::tmem_dealloc<512>(tmem);
+}
+
+}  // namespace
+
+bool d2ar_supported(const D2Dims& d) {
+  if (getenv("T2B200_AR_KERNEL") && !strcmp(getenv("T2B200_AR_KERNEL"), "old")) return false;
+  const int grid = (d.H / 32) * D2_CLUSTER;
+  if (grid != 128 || d.H != d.R || d.B < 1 || d.B > D2_BP) return false;
+  const int S = (d.B * 4 <= grid) ? 4 : ((d.B * 2 <= grid) ? 2 : 1);
+  const int Lc = (d.L + S - 1) / S;
+  if (Lc > 128 || d.A > 128 || d.A % 32 != 0 || d.P % (TG_BK * D2_CLUSTER) != 0 || d.EF % 4 != 0 || d.M % 4 != 0) return false;
+  if (d.H % (TG_BK * D2_CLUSTER) != 0 || d.KattP / TG_BK > 255 || d.KdecP / TG_BK > 255) return false;
+  KbEnt tmp[AR_MAX_ENT];
+  for (int r = 0; r < D2_CLUSTER; ++r) {
+    const int n = build_program(d, r, tmp);
+    if (n > AR_MAX_ENT) return false;
+    int la = 0, fa = 0, ld = 0, fd = 0;
+    for (int i = 0; i < n; ++i) {
+      if (tmp[i].flags & 1) (tmp[i].gemm ? fd : fa)++;
+      if (tmp[i].flags & 2) (tmp[i].gemm ? ld : la)++;
+    }
+    if (la != 1 || fa != 1 || ld != 1 || fd != 1) return false;   // every rank needs a prenet, an att_h, a ctx and an rnn_h K-block
+  }
+  if (ar_att_scratch_floats(d.L, d.A, d.EF, S) * 4 > (size_t)TG_M * TG_PART_LD * 4) return false;
+  if (((size_t)2 * (d.M + 4) + 2 * d.P + 2 * (d.P / D2_CLUSTER) + 6 * 64) * 4 > (size_t)TG_M * TG_PART_LD * 4 || d.P / D2_CLUSTER > 64 ||
+      (d.M + 1 + D2_CLUSTER - 1) / D2_CLUSTER > 64)
+    return false;
+  return ar_smem_bytes(d) <= 227 * 1024;
+}
+
+int d2ar_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, const D2Maps& maps, const CUtensorMap& gmap,
+                cudaStream_t st) {
+  T2_REQUIRE(d2ar_supported(d), T2_ERR_UNSUPPORTED, "decoder (pipelined AR): unsupported shape B=%d L=%d", d.B, d.L);
+  T2_REQUIRE(!io.teacher_forcing && !io.hist && !io.hidden_dropout, T2_ERR_ARG, "decoder (pipelined AR): autoregressive eval mode only");
+  const size_t smem = ar_smem_bytes(d);
+  T2_CHECK_CUDA(cudaFuncSetAttribute(decoder_ar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaLaunchConfig_t cfg{};
+  cudaLaunchAttribute at[1];
+  cfg.gridDim = dim3(128);
+  cfg.blockDim = dim3(AR_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = D2_CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  int nclusters = 0;
+  T2_CHECK_CUDA(cudaOccupancyMaxActiveClusters(&nclusters, decoder_ar_kernel, &cfg));
+  T2_REQUIRE(nclusters * D2_CLUSTER >= 128, T2_ERR_UNSUPPORTED, "decoder (pipelined AR): only %d clusters of %d can be co-resident", nclusters,
+             D2_CLUSTER);
+  T2_CHECK_CUDA(cudaMemsetAsync(s.barrier, 0, 2 * sizeof(unsigned), st));
+  T2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, decoder_ar_kernel, maps, gmap, d, w, s, io));
+  return T2_OK;
+}
