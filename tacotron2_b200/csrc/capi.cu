@@ -218,6 +218,18 @@ __global__ void pack_conv_wT_kernel(const float* W, __nv_bfloat16* dst, int Cout
     dst[n + i] = lo;
   }
 }
+__global__ void pack_loc_filter_kernel(const float* conv /*[32][2][31]*/, const float* dense /*[A][32]*/, int A, __nv_bfloat16* out /*[2][128][64]*/) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 128 * 64) return;
+  const int a = i / 64, k = i % 64, c = k / 32, j = k % 32;
+  float g = 0.f;
+  if (a < A && j < 31)
+    for (int f = 0; f < 32; ++f) g = fmaf(dense[a * 32 + f], conv[(f * 2 + c) * 31 + j], g);
+  __nv_bfloat16 hi, lo;
+  tc::split_bf16(g, hi, lo);
+  out[i] = hi;
+  out[128 * 64 + i] = lo;
+}
 __global__ void conv_t_kernel(const float* w /*[32][2][31]*/, float* out /*[2][31][32]*/) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= 32 * 2 * 31) return;
@@ -363,6 +375,7 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   c->Wdec_b = ar.take<__nv_bfloat16>((size_t)2 * 4 * R * d.KdecP);
   c->loc_conv_t = ar.take<float>(2 * 31 * 32);
   c->loc_dense_t = ar.take<float>((size_t)32 * A);
+  c->locG_b = ar.take<__nv_bfloat16>((size_t)2 * 128 * 64);
   for (int i = 0; i < 3; ++i) c->enc_Wb[i] = ar.take<__nv_bfloat16>((size_t)2 * E * KS * E);
   for (int i = 0; i < 5; ++i) c->post_Wb[i] = ar.take<__nv_bfloat16>((size_t)2 * chans[i + 1] * 5 * chans[i]);
   c->lstm_Wb = ar.take<__nv_bfloat16>((size_t)2 * 8 * Hh * E);
@@ -416,6 +429,14 @@ static int commit_impl(t2_ctx* c, Arena& ar, cudaStream_t st) {
   pack_lstm_bf16_kernel<<<gsz(4ll * H * d.KattP), 256, 0, st>>>(att_ih->ptr, att_hh->ptr, c->Watt_b, H, P + EF, d.KattP);
   pack_lstm_bf16_kernel<<<gsz(4ll * R * d.KdecP), 256, 0, st>>>(dec_ih->ptr, dec_hh->ptr, c->Wdec_b, R, H + EF + C, d.KdecP);
   conv_t_kernel<<<(32 * 2 * 31 + 255) / 256, 256, 0, st>>>(lconv->ptr, c->loc_conv_t);
+  if (A <= 128) {
+    pack_loc_filter_kernel<<<(128 * 64 + 255) / 256, 256, 0, st>>>(lconv->ptr, ldense->ptr, A, c->locG_b);
+    unsigned long long gd[3] = {64ull, 128ull, 2ull};
+    unsigned long long gs[2] = {128ull, 128ull * 128ull};
+    unsigned gb[3] = {64u, 128u, 2u};
+    int rcg;
+    if ((rcg = tc_make_tmap_bf16(&c->map_locG, c->locG_b, 3, gd, gs, gb))) return rcg;
+  }
   T2_CHECK_CUDA(cudaGetLastError());
   { int rc3; if ((rc3 = transpose_launch(ldense->ptr, c->loc_dense_t, A, 32, st))) return rc3; }
   c->d2w = D2Weights{batt, bdec, wq->ptr, wv->ptr, c->loc_conv_t, c->loc_dense_t, Wproj, bproj, w1->ptr, w2->ptr};
@@ -726,7 +747,8 @@ static int decode2_impl(t2_ctx* c, bool tf, const float* memory, const float* pm
   D2Maps maps;
   RC(make_xmaps(c, d, s, tfp, T + 1, &maps, nslots));
   timing_begin(c, 0, st);
-  RC(d2_launch(d, c->d2w, s, io, maps, st));
+  if (!tf && !tape && d2ar_supported(d)) RC(d2ar_launch(d, c->d2w, s, io, maps, c->map_locG, st));   // pipelined autoregressive schedule
+  else RC(d2_launch(d, c->d2w, s, io, maps, st));
   timing_end(c, 0, st);
   if (tape) RC(decode_proj_bulk(c, tape->xdec, B, T, mels, gates, proj_tmp, st));
   RC(poison_on_abort_launch(c->status_dev, mels, (long long)B * T * d.M, st));   // an aborted launch must not pass for a result

@@ -37,6 +37,10 @@ struct t2_ctx {
   float* loc_dense_t;                      // [32][A]
   D2Weights d2w;
   CUtensorMap map_w_att, map_w_dec;
+  // location conv (k = 31, 2 -> 32) and location dense (32 -> A) folded into one 62-tap filter bank per attention dim:
+  // locG_b[2 hi/lo][128 a][64]: column c*32 + j = sum_f dense[a][f] conv[f][c][j], columns 31 / 63 and rows >= A zero
+  __nv_bfloat16* locG_b;
+  CUtensorMap map_locG;
   int npass;
   // tensor-core conv operands (bf16 hi/lo [2][Cout][k][Cin]) and their TMA descriptors
   __nv_bfloat16 *enc_Wb[3], *post_Wb[5], *lstm_Wb, *attenc_Wb;

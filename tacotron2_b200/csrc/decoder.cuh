@@ -91,6 +91,10 @@ struct D2Maps {  // TMA descriptors (bf16, 128-B swizzle, box 64 x rows x {1|2})
   CUtensorMap tf_pre;         // [P][BP][(T+1)*2]
 };
 
+// Pipelined autoregressive schedule (decoder_ar.cu): eval-mode synthesis when the shape fits (else decoder_persistent_kernel)
+bool d2ar_supported(const D2Dims& d);
+int d2ar_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, const D2Maps& maps, const CUtensorMap& gmap,
+                cudaStream_t stream);
 int d2_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, const D2Maps& maps, cudaStream_t stream);
 int d2_max_clusters(int* out);
 size_t d2_smem_bytes(const D2Dims& d);

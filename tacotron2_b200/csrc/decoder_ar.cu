@@ -574,7 +574,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
   const int unit0 = tile * 32 + (int)rank * 8;
   const int B = d.B, L = d.L, A = d.A;
   const int S = (B * 4 <= (int)gridDim.x) ? 4 : ((B * 2 <= (int)gridDim.x) ? 2 : 1);
-  __shared__ int ok_word;
+  __shared__ int ok_word, vote_word;
 
   // ---- one-time setup
   if (tid == 0) {
@@ -586,7 +586,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
     tc::mbar_init(sm.bars + B_P1, 1); tc::mbar_init(sm.bars + B_W1, 1); tc::mbar_init(sm.bars + B_G, 1); tc::mbar_init(sm.bars + B_FIN, 1);
     tc::fence_barrier_init();
     sm.ctl[0] = 1u;   // gate count: the (virtual) barrier that publishes the prenet columns of frame 0 counts as passed
-    sm.ctl[1] = 0u; sm.ctl[2] = 0u;
+    sm.ctl[1] = 0u; sm.ctl[2] = 0u; sm.ctl[4] = 0u; sm.ctl[5] = 0u;
     sm.ctl[3] = (unsigned)build_program(d, (int)rank, sm.prog);
   }
   if (warp == 9) tc::tmem_alloc<512>(sm.tmem_slot);   // warp 9 owns alloc + dealloc
@@ -621,8 +621,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
     // =============================================================== TMA producer
     if (lane == 0) {
       const uint64_t wpol = tc::l2_policy_evict_first();
-      long long total = 0;   // K-blocks of the whole launch: prologue (entries of frame -1 that belong to frame 0) + per frame
-      // sequence position -> (frame, entry): frame -1 uses only the next-frame entries
+      // sequence position -> (frame, entry): frame -1 (prologue) issues only the entries that belong to the following frame
       int w_f = -1, w_e = 0, x_f = -1, x_e = 0;
       long long w_n = 0, x_n = 0;
       auto skip = [&](int f, int e) {   // entry e is not issued in frame f
@@ -637,9 +636,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
       int w_stage = 0, x_stage = 0;
       uint32_t w_phase = 0;
       long long idle = 0;
-      bool fenced_for = false;
       unsigned fenced_gate = 0;
-      (void)total; (void)fenced_for;
       while (x_f < io.n_steps) {
         bool progressed = false;
         if (w_f < io.n_steps && w_n - x_n < AR_STAGES && tc::mbar_try_wait(sm.bars + B_EMPTY + w_stage, w_phase ^ 1)) {
@@ -752,6 +749,8 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
       at.nl = max(0, min(L, at.l0 + Lc) - at.l0);
     }
     at.masked = false; at.Leff = 0;
+    if (tid == 0 && !tc::mbar_wait(sm.bars + B_G, 0)) sm.ctl[2] = 1u;   // the filter bank has landed (every CTA: no copy may be in flight at exit)
+    wsync();
     if (at.active) {
       const unsigned char* mk = io.mask + (size_t)at.b * L;
       if (tid < at.nl) at.masked = mk[at.l0 + tid] != 0;
@@ -788,7 +787,6 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
 #pragma unroll 1
       for (int i = tid; i < L + 32; i += 256) wrow[i] = 0.f;
       wsync();
-      if (!tc::mbar_wait(sm.bars + B_G, 0)) sm.ctl[2] = 1u;
       build_toeplitz_and_issue(sm, wrow, tmem, at.l0, at.nl, d.npass, sm.bars + B_LOC);
     }
     const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
@@ -842,9 +840,11 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
           int mine = 1;
 #pragma unroll 1
           for (int b = tid; b < B; b += 256) mine &= (ld_acquire_u32((const unsigned*)s.done + b) != 0u);
-          if (!mine) ok_word = 0;    // (ok_word is 1 after a successful barrier; the next barrier rewrites it)
+          if (tid == 0) vote_word = 1;
           wsync();
-          if (ok_word != 0 && t + 1 >= io.min_frames) stop = true;
+          if (!mine) vote_word = 0;
+          wsync();
+          if (vote_word != 0 && t + 1 >= io.min_frames) stop = true;
           wsync();
         }
         prof_mark(7);
