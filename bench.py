@@ -40,7 +40,7 @@ def ncu_traffic(kernel):
 
 WORKLOAD = "C2: vanilla-ljspeech-stop AR inference, batch 64 x 200 chars x 1000 frames, fp32, stop gate evaluated (never fires)"
 # kernels launched by one Tacotron2.forward (AR): embed 1, encoder conv 3, BiLSTM input proj 1, BiLSTM 1, memory split 1,
-# att_encoder 1, persistent decoder 1, abort-poison guard 1, mel split 1, postnet conv 5, finalize 1  (memsets / memcpys not counted)
+# att_encoder 1, persistent decoder (decoder_ar_kernel) 1, abort-poison guard 1, mel split 1, postnet conv 5, finalize 1  (memsets / memcpys not counted)
 LAUNCHES_PER_STEP = 17
 
 
@@ -285,10 +285,10 @@ def bf16_mode_us_per_step(dev, steps=3):
             os.environ["T2B200_PRECISION"] = old
 
 
-PHASE_NAMES = ["att_lstm_tail", "query_partials_barrier", "attention_ctx_store_barrier", "dec_lstm_tail_barrier", "proj(beside att gemm)",
-               "prenet1(beside att gemm)", "prenet2(beside att gemm)", "x_barrier_and_prenet_kblock_gemm", "att_lstm_gemm_with_output_stage_beside",
-               "dec_lstm_gemm", "attn_query_sum", "attn_energies", "attn_csync", "attn_softmax", "attn_context",
-               "location_precompute(beside dec gemm)"]
+# profiling slots of decoder_ar_kernel (CTA 0, thread 0; csrc/decoder_ar.cu): the dependent chain of one frame, in slot order
+PHASE_NAMES = ["att_lstm_tail(exchange+pointwise+h stores)", "query_partials+Q_barrier", "C_barrier(+toeplitz build beside it)", "dec_lstm_tail+R_barrier",
+               "projection", "prenet1", "prenet2", "X_barrier+stop_check", "wait_att_accumulator(prenet K-block)", "wait_dec_accumulator(ctx K-blocks)",
+               "attn_query_sum+location_term_wait", "attn_energies(tmem)", "attn_exchange", "attn_softmax", "attn_context+stores", "projection_ctx_half"]
 
 TRAIN_B, TRAIN_L, TRAIN_T = 64, 150, 800
 TRAIN_WORKLOAD = ("C3: vanilla-lj-hifi-stop (speaker tokens, 4 speakers) teacher-forced training step, batch 64/GPU x 150 chars x 800 frames, "
@@ -665,7 +665,7 @@ def main():
     dec_ms = t_dec / args.steps
     bytes_launch = algorithmic_bytes_per_frame_step() * T
     achieved = bytes_launch / (dec_ms * 1e-3) / 1e9
-    traffic_pf, traffic_src = ncu_traffic("decoder_persistent_kernel")
+    traffic_pf, traffic_src = ncu_traffic("decoder_ar_kernel")
     cfg = bench_config(world)
     cfg.update({"l2": "flushed between timed iterations (256 MiB write)", "us_per_decoder_step": 1e3 * dec_ms / T})
     line = {
@@ -676,7 +676,7 @@ def main():
                 "h2d_bytes_per_step": chars_h.numel() * 8 + lens_h.numel() * 8, "d2h_bytes_per_step": out_h.numel() * 4 + gate_h.numel() * 4 + 4},
         "gpu_launches": LAUNCHES_PER_STEP * args.steps,
         "clocks": clocks,
-        "roofline": {"kernel": "decoder_persistent_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "roofline": {"kernel": "decoder_ar_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": None if traffic_pf is None else traffic_pf * T, "traffic_source": traffic_src,
                      "peak_source": "measured" if peaks else "fallback",
                      "algorithmic_bytes_per_launch": bytes_launch, "kernel_ms": dec_ms, "share_of_step": dec_ms / ms,

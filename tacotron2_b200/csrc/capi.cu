@@ -642,6 +642,7 @@ static State2Plan plan_state2(const D2Dims& d, int L, Arena& ar) {
   s.lengths = ar.take<long long>(D2_BP);
   s.n_frames = ar.take<int>(4);
   s.barrier = ar.take<unsigned>(4);
+  s.bar_flags = ar.take<unsigned>(256);   // pipelined AR kernel: one arrival word per CTA
   pl.zero_begin = ar.base ? ar.base + off0 : nullptr;
   pl.zero_bytes = (size_t)(ar.off - off0);
   s.qpart = ar.take<float>((size_t)D2_BP * 128 * d.A);   // fully rewritten every frame: not part of the zeroed region
@@ -730,7 +731,7 @@ static int decode2_impl(t2_ctx* c, bool tf, const float* memory, const float* pm
   io.memory = memory; io.pmem = pmem; io.mask = mask; io.prenet_keep = prenet_keep;
   io.att_keep = att_keep; io.rnn_keep = rnn_keep; io.mels = mels; io.gates = gates; io.aligns = aligns;
   io.Tmax = T; io.n_steps = T; io.t0 = 0; io.seed = seed; io.hidden_dropout = train ? 1 : 0;
-  io.debug_barrier = getenv("T2B200_DEBUG_BARRIER") ? 1 : 0;
+  io.debug_barrier = getenv("T2B200_DEBUG_BARRIER") ? atoi(getenv("T2B200_DEBUG_BARRIER")) : 0;   // experiment switches (bit mask)
   io.hist = tape ? 1 : 0;
   if (tf) {
     if (!tape) T2_CHECK_CUDA(cudaMemsetAsync(tfp, 0, (size_t)(T + 1) * 2 * D2_BP * d.P * sizeof(__nv_bfloat16), st));

@@ -56,6 +56,7 @@ struct D2State {
   long long* lengths;    // [BP]
   int* n_frames;         // [1]
   unsigned* barrier;     // [2]
+  unsigned* bar_flags;   // [256] per-CTA arrival epochs of the pipelined AR kernel's grid barrier
   unsigned long long* prof;  // [16] or null
   unsigned* status;          // context's sticky abort word or null
   // history mode (training tape): xatt/xdec/w_prev/w_cum hold T+1 slots and q holds T slots instead of two parities

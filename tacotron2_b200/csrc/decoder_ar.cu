@@ -46,6 +46,7 @@ struct ArSmem {
   float* v;
   float* octx;
   float* wcum;       // [15 | L | 17] cumulative attention weights of this CTA's utterance (full row, zero halo)
+  float* wrow;       // [15 | L | 17] energies -> attention weights of the current frame (full row, zero halo)
   KbEnt* prog;       // per-frame K-block program of this CTA
   uint64_t* bars;
   uint32_t* tmem_slot;
@@ -54,7 +55,7 @@ struct ArSmem {
 
 __host__ __device__ inline size_t ar_smem_bytes(const D2Dims& d) {
   return 1024 + (size_t)AR_STAGES * TG_STAGE_BYTES + TG_M * TG_PART_LD * 4 + 2 * 128 * 64 * 2 + 2 * 8 * D2_BP * 4 + 8 * (size_t)d.A * 4 + 8 * D2_BP * 4 +
-         (size_t)d.A * 4 + 2 * 64 * 4 + (size_t)(d.L + 32) * 4 + AR_MAX_ENT * sizeof(KbEnt) + 24 * 8 + 64;
+         (size_t)d.A * 4 + 2 * 64 * 4 + 2 * (size_t)(d.L + 32) * 4 + AR_MAX_ENT * sizeof(KbEnt) + 24 * 8 + 80;
 }
 
 __device__ __forceinline__ ArSmem ar_carve(uint8_t* base, const D2Dims& d) {
@@ -70,6 +71,7 @@ __device__ __forceinline__ ArSmem ar_carve(uint8_t* base, const D2Dims& d) {
   s.v = reinterpret_cast<float*>(p);       p += d.A * 4;
   s.octx = reinterpret_cast<float*>(p);    p += 2 * 64 * 4;
   s.wcum = reinterpret_cast<float*>(p);    p += (size_t)(d.L + 32) * 4;
+  s.wrow = reinterpret_cast<float*>(p);    p += (size_t)(d.L + 32) * 4;
   s.prog = reinterpret_cast<KbEnt*>(p);    p += AR_MAX_ENT * sizeof(KbEnt);
   p = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 7) & ~(uintptr_t)7);
   s.bars = reinterpret_cast<uint64_t*>(p); p += 24 * 8;
@@ -78,7 +80,7 @@ __device__ __forceinline__ ArSmem ar_carve(uint8_t* base, const D2Dims& d) {
   return s;
 }
 // barrier slots
-enum { B_FULL = 0, B_EMPTY = AR_STAGES, B_ACC_ATT = 2 * AR_STAGES, B_ACC_DEC, B_LOC, B_RV, B_E, B_MEL, B_P1, B_W1, B_G, B_FIN };
+enum { B_FULL = 0, B_EMPTY = AR_STAGES, B_ACC_ATT = 2 * AR_STAGES, B_ACC_DEC, B_LOC, B_RV, B_E, B_MEL, B_P1, B_W1, B_G, B_FIN, B_RV2 };
 
 __device__ __forceinline__ void wsync() { D2_SYNC(); }
 
@@ -156,33 +158,73 @@ __host__ __device__ inline int build_program(const D2Dims& d, int rank, KbEnt* o
 }
 
 // ------------------------------------------------------------------------------------------ grid barrier (workers only)
+// One arrival word per CTA instead of one counter for the grid: 128 CTAs adding to the same L2 word serialise (~27 cycles per
+// atomic: 1.8 us before the last arrival is even visible); here an arrival is a plain release store of the epoch to the CTA's own
+// word and a waiter's warp 0 reads all 128 words (four 128-byte lines, 16 bytes per lane) until every one has reached the epoch.
 struct ArGridBar {
-  unsigned* ctr;
-  unsigned* abort_flag;
+  unsigned* flags;        // [gridDim.x] arrival epochs (mode 1)
+  unsigned* ctr;          // arrival counter (mode 0)
+  unsigned* abort_flag;   // set by any CTA that failed; polled with the flags
   unsigned nblocks, epoch;
   int* ok_s;   // shared word
+  int mode;    // 0: one counter (release add + acquire poll by thread 0), 1: one word per CTA, polled by warp 0,
+               // 2: as 0 but one add per CLUSTER: the CTAs of a cluster count on a shared-memory word of rank 0, the last one adds
+  unsigned* cl_ctr;   // mode 2: this CTA's cluster counter word (shared memory; rank 0's copy is the one used)
   __device__ void arrive(bool fail, volatile unsigned* ctl) {
     asm volatile("fence.proxy.async.global;" ::: "memory");   // operands written with generic stores are read by TMA after the barrier
     if (fail) ctl[2] = 1u;
     wsync();
+    ++epoch;
     if (threadIdx.x == 0) {
-      ++epoch;
-      if (ctl[2] != 0u) { atomicExch(abort_flag, 1u); atomicOr(ctr, 0x80000000u); }
-      asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+      if (mode == 0) {
+        if (ctl[2] != 0u) { atomicExch(abort_flag, 1u); atomicOr(ctr, 0x80000000u); }
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+      } else if (mode == 2) {
+        if (ctl[2] != 0u) { atomicExch(abort_flag, 1u); atomicOr(ctr, 0x80000000u); }
+        unsigned old;
+        asm volatile("atom.acq_rel.cluster.shared::cluster.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(tc::mapa(tc::smem_u32(cl_ctr), 0u)) : "memory");
+        if ((old & (D2_CLUSTER - 1)) == D2_CLUSTER - 1) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+      } else {
+        if (ctl[2] != 0u) atomicExch(abort_flag, 1u);
+        asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(flags + blockIdx.x), "r"(epoch) : "memory");
+      }
     }
   }
   // returns false when the grid aborts; on success thread 0 opens the producer's next gate (ctl[0])
   __device__ bool wait(volatile unsigned* ctl) {
-    if (threadIdx.x == 0) {
-      const unsigned target = epoch * nblocks;
-      unsigned v;
-      long long spins = 0;
-      while ((((v = ld_acquire_u32(ctr)) & 0x7fffffffu) < target) && !(v & 0x80000000u)) {
-        if (++spins > (1ll << 24)) { atomicExch(abort_flag, 1u); atomicOr(ctr, 0x80000000u); v = 0x80000000u; break; }
+    if (mode == 0 || mode == 2) {
+      if (threadIdx.x == 0) {
+        const unsigned target = mode == 2 ? epoch * (nblocks / D2_CLUSTER) : epoch * nblocks;
+        unsigned v;
+        long long spins = 0;
+        while ((((v = ld_acquire_u32(ctr)) & 0x7fffffffu) < target) && !(v & 0x80000000u)) {
+          if (++spins > (1ll << 24)) { atomicExch(abort_flag, 1u); atomicOr(ctr, 0x80000000u); v = 0x80000000u; break; }
+        }
+        const int ok = (v & 0x80000000u) == 0u;
+        *ok_s = ok;
+        if (ok) st_release_cta(ctl, ctl[0] + 1u);
       }
-      const int ok = (v & 0x80000000u) == 0u;
-      *ok_s = ok;
-      if (ok) st_release_cta(ctl, ctl[0] + 1u);
+    } else if (threadIdx.x < 32) {
+      const unsigned lane = threadIdx.x;
+      const unsigned nq = (nblocks + 3) >> 2;   // 16-byte groups of flags
+      long long spins = 0;
+      int ok = 1;
+      for (;;) {
+        uint4 f = make_uint4(epoch, epoch, epoch, epoch);
+        if (lane < nq) asm volatile("ld.acquire.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(f.x), "=r"(f.y), "=r"(f.z), "=r"(f.w) : "l"(flags + 4 * lane) : "memory");
+        unsigned ab = 0;
+        if (lane == 0) asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(ab) : "l"(abort_flag) : "memory");
+        const bool here = (int)(f.x - epoch) >= 0 && (int)(f.y - epoch) >= 0 && (int)(f.z - epoch) >= 0 && (int)(f.w - epoch) >= 0;
+        const bool all_here = __all_sync(0xffffffffu, here);
+        const bool aborted = __any_sync(0xffffffffu, ab != 0u);
+        if (aborted) { ok = 0; break; }
+        if (all_here) break;
+        if (++spins > (1ll << 22)) { if (lane == 0) atomicExch(abort_flag, 1u); ok = 0; break; }   // a peer died: never hang the GPU
+      }
+      if (lane == 0) {
+        *ok_s = ok;
+        if (ok) st_release_cta(ctl, ctl[0] + 1u);
+      }
     }
     wsync();
     return *ok_s != 0;
@@ -217,21 +259,93 @@ __device__ __forceinline__ bool cluster_rendezvous(uint64_t* bar, uint32_t& phas
   return ok;
 }
 
+// Split-K exchange of an LSTM gate accumulator, push mode.  Rows [32r, 32r+32) of the 128-row tile belong to cluster rank r, and
+// they are exactly the TMEM lanes worker warps r and r+4 can read: every thread sends its 32 partial sums (one row, 32 utterances)
+// straight to the owner's receive buffer recv[source rank][row][utterance] with st.async, whose bytes count on the owner's
+// transaction barrier.  One trip through the SM-to-SM network, no staging store, no rendezvous, no remote loads.
+__device__ __forceinline__ void st_async_v4(uint32_t cluster_addr, float4 v, uint32_t cluster_bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.f32 [%0], {%1, %2, %3, %4}, [%5];"
+               ::"r"(cluster_addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(cluster_bar) : "memory");
+}
+__device__ __forceinline__ void ar_push_partials(uint32_t tmem, uint32_t col, float* recv, uint64_t* bar, uint32_t my_rank) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int owner = warp & 3, col0 = 32 * (warp >> 2);
+  if (threadIdx.x == 0) tc::mbar_arrive_expect_tx(bar, (uint32_t)(D2_CLUSTER * 32 * TG_N * 4));   // four sources x 32 rows x 64 utterances
+  float v[32];
+  tc::tmem_ld32(tmem + ((uint32_t)(32 * owner) << 16) + col + col0, v);
+  tc::tmem_ld_wait();
+  tc::tc_fence_before();
+  const uint32_t dst = tc::mapa(tc::smem_u32(recv + ((size_t)my_rank * 32 + lane) * TG_PART_LD + col0), (uint32_t)owner);
+  const uint32_t rb = tc::mapa(tc::smem_u32(bar), (uint32_t)owner);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) st_async_v4(dst + 16u * i, make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]), rb);
+}
+
+// LSTM pointwise tail on the received partials (same summation order as lstm_tail of dec_shared.cuh: ranks 0..3, then the bias).
+// Thread = (unit ul, utterance pair bp).
+__device__ __forceinline__ void ar_lstm_tail(const float* recv, int unit0, const float* __restrict__ bias, int H, float* cst, int B, const HOut& ho,
+                                             float* h_s) {
+  const int ul = threadIdx.x >> 5, bp = threadIdx.x & 31;
+  const int u = unit0 + ul;
+  float2 pre[4];
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    const float* rp = recv + (size_t)(g * 8 + ul) * TG_PART_LD + 2 * bp;
+    const float2 p0 = *reinterpret_cast<const float2*>(rp), p1 = *reinterpret_cast<const float2*>(rp + 32 * TG_PART_LD);
+    const float2 p2 = *reinterpret_cast<const float2*>(rp + 64 * TG_PART_LD), p3 = *reinterpret_cast<const float2*>(rp + 96 * TG_PART_LD);
+    const float bv = __ldg(bias + g * H + u);
+    pre[g].x = ((p0.x + p1.x) + p2.x) + p3.x + bv;
+    pre[g].y = ((p0.y + p1.y) + p2.y) + p3.y + bv;
+  }
+  float hv[2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int b = 2 * bp + j;
+    const float pi = j ? pre[0].y : pre[0].x, pf = j ? pre[1].y : pre[1].x;
+    const float pg = j ? pre[2].y : pre[2].x, po = j ? pre[3].y : pre[3].x;
+    const float si = sigmoid_fast(pi), sf = sigmoid_fast(pf), tg = tanh_fast(pg), so = sigmoid_fast(po);
+    const float c = sf * cst[ul * D2_BP + b] + si * tg;
+    const float h = so * tanh_fast(c);
+    if (b < B) cst[ul * D2_BP + b] = c;
+    hv[j] = b < B ? h : 0.f;
+  }
+  *reinterpret_cast<float2*>(h_s + ul * D2_BP + 2 * bp) = make_float2(hv[0], hv[1]);
+  wsync();
+  const int b = threadIdx.x & 63, w = threadIdx.x >> 6;
+  if (b < B) {
+    float h8[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) h8[i] = h_s[i * D2_BP + b];
+    __nv_bfloat16* x = w < 2 ? ho.x0 : ho.x1;
+    if (x) {
+      const long long plane = w < 2 ? ho.plane0 : ho.plane1;
+      const int ld = w < 2 ? ho.ld0 : ho.ld1, col = (w < 2 ? ho.col0 : ho.col1) + unit0;
+      store_plane8(x + (w & 1) * plane + (size_t)b * ld + col, h8, w & 1, ((ld | col) & 7) == 0);
+    }
+    if (ho.rm && (ho.x1 ? w < 2 : w >= 2)) {
+      float* dst = ho.rm + (size_t)b * ho.rm_ld + ho.rm_col + unit0 + (w & 1) * 4;
+      const float* src = h8 + (w & 1) * 4;
+      if (((ho.rm_ld | (ho.rm_col + unit0)) & 3) == 0) *reinterpret_cast<float4*>(dst) = make_float4(src[0], src[1], src[2], src[3]);
+      else { dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2]; dst[3] = src[3]; }
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------ attention
-// Scratch (floats, in `part`): q[A] | qh[8A] | ep[2][128] | red[64] | cred[4*cols] | w row: 15 zeros | L | 17 zeros
+// Scratch (floats, in `part`): q[A] | qh[8A] | ep[2][128] | red[64] | cred[4*cols]; the weight row has its own buffer (sm.wrow)
 struct ArAtt { float *q_s, *qh, *ep, *red, *cred, *wrow; };
-__device__ __forceinline__ ArAtt ar_att_scratch(float* part, int L, int A, int EF, int S) {
+__device__ __forceinline__ ArAtt ar_att_scratch(const ArSmem& sm, int A) {
   ArAtt a;
-  a.q_s = part;
+  a.q_s = sm.part;
   a.qh = a.q_s + A;
   a.ep = a.qh + 8 * A;
   a.red = a.ep + 256;
   a.cred = a.red + 64;
-  a.wrow = a.cred + 4 * (size_t)((((EF + S - 1) / S) + 3) & ~3);
+  a.wrow = sm.wrow;
   return a;
 }
 __host__ __device__ inline size_t ar_att_scratch_floats(int L, int A, int EF, int S) {
-  return 9 * (size_t)A + 256 + 64 + 4 * (size_t)((((EF + S - 1) / S) + 3) & ~3) + L + 32;
+  return 9 * (size_t)A + 256 + 64 + 4 * (size_t)((((EF + S - 1) / S) + 3) & ~3);
 }
 
 // Toeplitz rows of this CTA's positions -> tensor memory, then the location contraction (issued by thread 0).
@@ -292,7 +406,7 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
                              int cur, int nxt, int t_out, uint32_t fphase, ArGridBar& bar, bool& alive, long long* prof_last) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int L = d.L, A = d.A, EF = d.EF, S = at.S;
-  const ArAtt as = ar_att_scratch(sm.part, L, A, EF, S);
+  const ArAtt as = ar_att_scratch(sm, A);
   bool ok = true;
   auto mark = [&](int slot) {
     if (blockIdx.x == 0 && tid == 0 && s.prof) { const long long now = clock64(); s.prof[slot] += (unsigned long long)(now - *prof_last); *prof_last = now; }
@@ -434,7 +548,7 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
   mark(14);
   bar.arrive(!ok, sm.ctl);
   // while the barrier completes: the Toeplitz operand of the NEXT frame's location term (depends on this frame's weights only)
-  if (at.active) build_toeplitz_and_issue(sm, ar_att_scratch(sm.part, L, A, EF, S).wrow, tmem, at.l0, at.nl, d.npass, sm.bars + B_LOC);
+  if (at.active) build_toeplitz_and_issue(sm, sm.wrow, tmem, at.l0, at.nl, d.npass, sm.bars + B_LOC);
   alive = bar.wait(sm.ctl);
   return ok;
 }
@@ -574,7 +688,8 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
   const int unit0 = tile * 32 + (int)rank * 8;
   const int B = d.B, L = d.L, A = d.A;
   const int S = (B * 4 <= (int)gridDim.x) ? 4 : ((B * 2 <= (int)gridDim.x) ? 2 : 1);
-  __shared__ int ok_word, vote_word;
+  int& ok_word = *reinterpret_cast<int*>(const_cast<unsigned*>(sm.ctl + 6));     // (dynamic shared memory: the kernel has no static allocation)
+  int& vote_word = *reinterpret_cast<int*>(const_cast<unsigned*>(sm.ctl + 7));
 
   // ---- one-time setup
   if (tid == 0) {
@@ -582,11 +697,11 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
     tc::prefetch_tmap(&gmap);
     for (int i = 0; i < AR_STAGES; ++i) { tc::mbar_init(sm.bars + B_FULL + i, 1); tc::mbar_init(sm.bars + B_EMPTY + i, 1); }
     tc::mbar_init(sm.bars + B_ACC_ATT, 1); tc::mbar_init(sm.bars + B_ACC_DEC, 1); tc::mbar_init(sm.bars + B_LOC, 1);
-    tc::mbar_init(sm.bars + B_RV, D2_CLUSTER); tc::mbar_init(sm.bars + B_E, 1); tc::mbar_init(sm.bars + B_MEL, 1);
+    tc::mbar_init(sm.bars + B_RV, 1); tc::mbar_init(sm.bars + B_RV2, D2_CLUSTER); tc::mbar_init(sm.bars + B_E, 1); tc::mbar_init(sm.bars + B_MEL, 1);
     tc::mbar_init(sm.bars + B_P1, 1); tc::mbar_init(sm.bars + B_W1, 1); tc::mbar_init(sm.bars + B_G, 1); tc::mbar_init(sm.bars + B_FIN, 1);
     tc::fence_barrier_init();
     sm.ctl[0] = 1u;   // gate count: the (virtual) barrier that publishes the prenet columns of frame 0 counts as passed
-    sm.ctl[1] = 0u; sm.ctl[2] = 0u; sm.ctl[4] = 0u; sm.ctl[5] = 0u;
+    sm.ctl[1] = 0u; sm.ctl[2] = 0u; sm.ctl[4] = 0u; sm.ctl[5] = 0u; sm.ctl[8] = 0u;
     sm.ctl[3] = (unsigned)build_program(d, (int)rank, sm.prog);
   }
   if (warp == 9) tc::tmem_alloc<512>(sm.tmem_slot);   // warp 9 owns alloc + dealloc
@@ -736,7 +851,9 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
     __syncwarp();
   } else {
     // =============================================================== workers
-    ArGridBar bar{s.barrier, s.barrier + 1, gridDim.x, 0u, &ok_word};
+    ArGridBar bar{s.bar_flags, s.barrier, s.barrier + 1, gridDim.x, 0u, &ok_word, (io.debug_barrier & 4) ? 2 : ((io.debug_barrier & 1) ? 1 : 0),   // experiment bits: 1 per-CTA flags, 4 per-cluster add
+                  const_cast<unsigned*>(sm.ctl + 8)};
+    const bool pull_tails = (io.debug_barrier & 2) != 0;
     long long prof_last = clock64();
     auto prof_mark = [&](int slot) {
       if (blockIdx.x == 0 && tid == 0 && s.prof) { const long long now = clock64(); s.prof[slot] += (unsigned long long)(now - prof_last); prof_last = now; }
@@ -758,9 +875,9 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
 #pragma unroll 1
       for (int l = tid; l < L; l += 256) if (mk[l] == 0) le = max(le, l + 1);
       le = (int)warp_max((float)le);
-      if (lane == 0) sm.part[warp] = (float)le;
+      if (lane == 0) sm.octx[warp] = (float)le;   // (not `part`: a peer's first partial sums may already be arriving there)
       wsync();
-      for (int i = 0; i < 8; ++i) at.Leff = max(at.Leff, (int)sm.part[i]);
+      for (int i = 0; i < 8; ++i) at.Leff = max(at.Leff, (int)sm.octx[i]);
       wsync();
       // processed memory of this CTA's positions -> tensor memory (lane = position, column = attention dim), once
       const int lane0 = 32 * (warp & 3), half = warp >> 2, p = lane0 + lane;
@@ -783,7 +900,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
       tmem_st_wait();
       // frame 0: previous and cumulative weights are zero (model/tacotron2.py:126-153) -> the location term is zero; run the
       // same path so that the accumulator columns are defined
-      float* wrow = ar_att_scratch(sm.part, L, A, d.EF, S).wrow;
+      float* wrow = sm.wrow;
 #pragma unroll 1
       for (int i = tid; i < L + 32; i += 256) wrow[i] = 0.f;
       wsync();
@@ -791,7 +908,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
     }
     const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
     bool alive = true, fail = false, stop = false;
-    uint32_t rv_phase = 0, cphase = 0;
+    uint32_t rv_phase = 0, rv2_phase = 0, cphase = 0;
     int frames = 0;
 #pragma unroll 1
     for (int t = 0; t < io.n_steps && alive && !stop; ++t) {
@@ -801,14 +918,23 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
       if (!tc::mbar_wait(sm.bars + B_ACC_ATT, (uint32_t)(t & 1))) fail = true;
       tc::tc_fence_after();
       prof_mark(8);
-      ar_accum_to_smem(tmem, AR_COL_ATT, sm.part);
-      if (!cluster_rendezvous(sm.bars + B_RV, rv_phase)) fail = true;
       {
         const HOut ho{s.xatt + (size_t)nxt * 2 * pa, d.KattP, d.P + d.EF, pa, s.xdec + (size_t)cur * 2 * pd, d.KdecP, 0, pd, s.att_h_rm, d.H, 0};
-        lstm_tail(sm.part, rank, unit0, w.batt, d.H, sm.c_att, B, ho, nullptr, false, io.seed, 0ull, nullptr, sm.h_s);
+        if (pull_tails) {
+          ar_accum_to_smem(tmem, AR_COL_ATT, sm.part);
+          if (!cluster_rendezvous(sm.bars + B_RV2, rv2_phase)) fail = true;
+          lstm_tail(sm.part, rank, unit0, w.batt, d.H, sm.c_att, B, ho, nullptr, false, io.seed, 0ull, nullptr, sm.h_s);
+        } else {
+          ar_push_partials(tmem, AR_COL_ATT, sm.part, sm.bars + B_RV, rank);
+          if (!tc::mbar_wait_cluster(sm.bars + B_RV, rv_phase)) fail = true;
+          rv_phase ^= 1u;
+          if (io.debug_barrier & 8) prof_mark(8);   // (experiment: the exchange is charged to slot 8)
+          ar_lstm_tail(sm.part, unit0, w.batt, d.H, sm.c_att, B, ho, sm.h_s);
+        }
       }
       prof_mark(0);
       query_partial(sm.h_s, sm.wq, A, B, s.qpart + (size_t)blockIdx.x * A, (size_t)128 * A);
+      if (io.debug_barrier & 8) prof_mark(0);   // (experiment: the query partials are charged to slot 0, slot 1 is the bare barrier)
       if (!(alive = bar.sync(fail, sm.ctl))) break;
       prof_mark(1);
       // ================= location-sensitive attention (model/attention.py:54-67, model/decoder.py:90) + C barrier
@@ -822,11 +948,18 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
       if (!tc::mbar_wait(sm.bars + B_ACC_DEC, (uint32_t)(t & 1))) fail = true;
       tc::tc_fence_after();
       prof_mark(9);
-      ar_accum_to_smem(tmem, AR_COL_DEC, sm.part);
-      if (!cluster_rendezvous(sm.bars + B_RV, rv_phase)) fail = true;
       {
         const HOut ho{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, s.projin, d.KprojP, 0};
-        lstm_tail(sm.part, rank, unit0, w.bdec, d.H, sm.c_dec, B, ho, nullptr, false, io.seed, 0ull, nullptr, sm.h_s);
+        if (pull_tails) {
+          ar_accum_to_smem(tmem, AR_COL_DEC, sm.part);
+          if (!cluster_rendezvous(sm.bars + B_RV2, rv2_phase)) fail = true;
+          lstm_tail(sm.part, rank, unit0, w.bdec, d.H, sm.c_dec, B, ho, nullptr, false, io.seed, 0ull, nullptr, sm.h_s);
+        } else {
+          ar_push_partials(tmem, AR_COL_DEC, sm.part, sm.bars + B_RV, rank);
+          if (!tc::mbar_wait_cluster(sm.bars + B_RV, rv_phase)) fail = true;
+          rv_phase ^= 1u;
+          ar_lstm_tail(sm.part, unit0, w.bdec, d.H, sm.c_dec, B, ho, sm.h_s);
+        }
       }
       if (!(alive = bar.sync(fail, sm.ctl))) break;
       prof_mark(3);
@@ -897,7 +1030,7 @@ bool d2ar_supported(const D2Dims& d) {
   if (((size_t)2 * (d.M + 4) + 2 * d.P + 2 * (d.P / D2_CLUSTER) + 6 * 64) * 4 > (size_t)TG_M * TG_PART_LD * 4 || d.P / D2_CLUSTER > 64 ||
       (d.M + 1 + D2_CLUSTER - 1) / D2_CLUSTER > 64)
     return false;
-  return ar_smem_bytes(d) <= 227 * 1024;
+  return ar_smem_bytes(d) <= 227 * 1024 - 1024;   // (the 1024-aligned extern array costs up to 1 KB of the 227 KB opt-in limit)
 }
 
 int d2ar_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, const D2Maps& maps, const CUtensorMap& gmap,
