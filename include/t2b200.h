@@ -215,6 +215,37 @@ int t2_collate(int n_fields, const void* const* src, const long long* const* off
                const long long* max_rows, void* const* out, int B, const long long* gate_len, float* gate, long long gate_T,
                void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------------
+ * HiFi-GAN generator: model/hifi_gan.py:154-216 Generator.forward with ResBlock1 / ResBlock2
+ * (:20-151), the vocoder run/say.py:153-157 and run/test.py:170 call on the acoustic model's output.  mel (B, num_mels, T) fp32
+ * (the layout the reference passes: mel_spectrogram_post.swapaxes(1, 2)) -> wav (B, T * prod(upsample_rates)) fp32 = the
+ * reference's (B, 1, T') output without the singleton channel.  Parameters are registered under the reference's state-dict keys
+ * AFTER Generator.remove_weight_norm() (run/say.py:88): "conv_pre.weight" (C0, num_mels, 7), "conv_pre.bias", "ups.i.weight"
+ * (Cin, Cout, k) [ConvTranspose1d layout], "ups.i.bias", "resblocks.n.convs1.m.{weight,bias}", "resblocks.n.convs2.m.*"
+ * (ResBlock2: "resblocks.n.convs.m.*"), "conv_post.weight" (1, C, 7), "conv_post.bias".  Same conventions as above: device
+ * pointers, zero-copy parameters, caller-owned workspace, asynchronous on `stream`.
+ * ------------------------------------------------------------------------------------------------------------------ */
+typedef struct t2_hifigan t2_hifigan;
+typedef struct {
+  int num_mels;                     /* 80 (conv_pre input channels, model/hifi_gan.py:161) */
+  int upsample_initial_channel;     /* h.upsample_initial_channel */
+  int num_upsamples;                /* len(h.upsample_rates) <= 8 */
+  int upsample_rates[8];
+  int upsample_kernel_sizes[8];
+  int resblock;                     /* 1 = ResBlock1 (h.resblock == "1"), 2 = ResBlock2 */
+  int num_kernels;                  /* len(h.resblock_kernel_sizes) <= 8 */
+  int resblock_kernel_sizes[8];
+  int resblock_dilation_sizes[8][3];
+  int precision;                    /* 0 = fp32-parity (three bf16 hi/lo passes), 1 = bf16 */
+} t2_hifigan_config;
+int t2_hifigan_create(const t2_hifigan_config* cfg, t2_hifigan** out);
+int t2_hifigan_destroy(t2_hifigan* g);
+int t2_hifigan_set_param(t2_hifigan* g, const char* key, const float* ptr, long long numel);
+int t2_hifigan_commit(t2_hifigan* g, void* stream);
+long long t2_hifigan_workspace_bytes(const t2_hifigan* g, int B, int T);
+long long t2_hifigan_out_len(const t2_hifigan* g, int T);
+int t2_hifigan_fwd(t2_hifigan* g, const float* mel, int B, int T, float* wav, void* ws, long long ws_bytes, void* stream);
+
 /* Sticky device status of the context's persistent kernels (decoder forward / backward).  They bound every wait; a timeout makes
  * all CTAs leave together, NaN-fills the launch's outputs and sets this word.  *status_out = 0 or T2_ERR_DEVICE_ABORT; reading
  * clears it.  Synchronises the device: call it where the host synchronises anyway (reading a loss, n_frames, a checkpoint). */

@@ -21,6 +21,14 @@ class T2ModelConfig(C.Structure):
     ]
 
 
+class T2HifiganConfig(C.Structure):
+    _fields_ = [
+        ("num_mels", C.c_int), ("upsample_initial_channel", C.c_int), ("num_upsamples", C.c_int), ("upsample_rates", C.c_int * 8),
+        ("upsample_kernel_sizes", C.c_int * 8), ("resblock", C.c_int), ("num_kernels", C.c_int), ("resblock_kernel_sizes", C.c_int * 8),
+        ("resblock_dilation_sizes", (C.c_int * 3) * 8), ("precision", C.c_int),
+    ]
+
+
 _P, _I, _LL, _ULL = C.c_void_p, C.c_int, C.c_longlong, C.c_ulonglong
 
 # name -> (restype, argtypes); kept in sync with include/t2b200.h (tests/test_abi.py checks the symbol list)
@@ -42,6 +50,13 @@ SIGNATURES = {
     "t2_ctx_status": (_I, [_P, C.POINTER(_I)]),
     "t2_debug_set_timing": (_I, [_P, _I]),
     "t2_debug_kernel_ms": (_I, [_P, _I, C.POINTER(C.c_float)]),
+    "t2_hifigan_create": (_I, [C.POINTER(T2HifiganConfig), C.POINTER(_P)]),
+    "t2_hifigan_destroy": (_I, [_P]),
+    "t2_hifigan_set_param": (_I, [_P, C.c_char_p, _P, _LL]),
+    "t2_hifigan_commit": (_I, [_P, _P]),
+    "t2_hifigan_workspace_bytes": (_LL, [_P, _I, _I]),
+    "t2_hifigan_out_len": (_LL, [_P, _I]),
+    "t2_hifigan_fwd": (_I, [_P, _P, _I, _I, _P, _P, _LL, _P]),
     "t2_prenet_fwd": (_I, [_P, _P, _P, _P, _ULL, _I, _P, _P, _LL, _P]),
     "t2_postnet_fwd": (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _P, _LL, _P]),
     "t2_debug_phase_cycles": (_I, [_P, _P]),

@@ -21,7 +21,8 @@ __global__ void __launch_bounds__(256, 1) conv_tc_kernel(const __grid_constant__
   const int tiles_t = (a.T + 127) >> 7;
   const int b = blockIdx.x / tiles_t, t0 = (blockIdx.x % tiles_t) * 128;
   const int n0 = blockIdx.y * a.NT;
-  const int cblocks = (a.Cin + 63) >> 6, nkb = a.k * cblocks, pad = (a.k - 1) >> 1;
+  const int dil = a.dil > 1 ? a.dil : 1;
+  const int cblocks = (a.Cin + 63) >> 6, nkb = a.k * cblocks, pad = ((a.k - 1) >> 1) * dil;
   const uint32_t b_tile = (uint32_t)a.NT * 128u;  // bytes of one bf16 weight tile (NT rows x 128 B)
 
   if (tid == 0) {
@@ -47,7 +48,7 @@ __global__ void __launch_bounds__(256, 1) conv_tc_kernel(const __grid_constant__
       if (!tc::mbar_wait(empty + st, ph ^ 1)) { ok = false; break; }
       uint8_t* sp = base + (size_t)st * CT_STAGE_BYTES;
       tc::mbar_arrive_expect_tx(full + st, tx);
-      tc::tma_load_4d(sp, &a.in_map, full + st, c0, t0 + j - pad, b, 0);          // zero fill outside [0,T) = conv padding
+      tc::tma_load_4d(sp, &a.in_map, full + st, c0, t0 + j * dil - pad, b, 0);    // zero fill outside [0,T) = conv padding
       tc::tma_load_4d(sp + 2 * CT_A_TILE, &a.w_map, full + st, c0, j, n0, 0);
       if (++st == CT_STAGES) { st = 0; ph ^= 1; }
     }
@@ -98,14 +99,18 @@ __global__ void __launch_bounds__(256, 1) conv_tc_kernel(const __grid_constant__
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
         float x = v[i];
-        if (a.scale) x = fmaf(x, __ldg(a.scale + n + i), __ldg(a.shift + n + i));
-        else if (a.shift) x += __ldg(a.shift + n + i);
+        const int ci = a.chan_mod > 0 ? (n + i) % a.chan_mod : n + i;
+        if (a.scale) x = fmaf(x, __ldg(a.scale + ci), __ldg(a.shift + ci));
+        else if (a.shift) x += __ldg(a.shift + ci);
         if (a.act == ACT_RELU) x = fmaxf(x, 0.f);
         else if (a.act == ACT_TANH) x = tanhf(x);
         if (a.keep) x = a.keep[pos * a.keep_ld + n + i] ? x * a.drop_scale : 0.f;
         if (a.residual) x += a.residual[(size_t)b * a.res_bstride + (size_t)t * a.Cout + n + i];
+        if (a.out_scale != 0.f) x *= a.out_scale;
+        if (a.accum) x += a.accum[pos * a.Cout + n + i];
         v[i] = x;
       }
+      if (a.out_c0 && n == 0) a.out_c0[pos] = v[0];
       if (a.out_f32) {
         float4* dst = reinterpret_cast<float4*>(a.out_f32 + pos * a.Cout + n);
 #pragma unroll
@@ -114,7 +119,7 @@ __global__ void __launch_bounds__(256, 1) conv_tc_kernel(const __grid_constant__
       if (a.out_b16) {
         __align__(16) __nv_bfloat16 hi[16], lo[16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) tc::split_bf16(v[i], hi[i], lo[i]);
+        for (int i = 0; i < 16; ++i) tc::split_bf16((a.b16_slope != 0.f && v[i] < 0.f) ? v[i] * a.b16_slope : v[i], hi[i], lo[i]);
         uint4* dh = reinterpret_cast<uint4*>(a.out_b16 + pos * a.Cout + n);
         uint4* dl = reinterpret_cast<uint4*>(a.out_b16 + plane + pos * a.Cout + n);
         dh[0] = reinterpret_cast<const uint4*>(hi)[0]; dh[1] = reinterpret_cast<const uint4*>(hi)[1];

@@ -22,6 +22,13 @@ struct ConvTcArgs {
   __nv_bfloat16* out_b16;     // [2][B][T][Cout] (hi plane, lo plane) or null
   const float* residual;      // optional [B][res_tstride][Cout] added before the store (postnet residual), or null
   long long res_bstride;
+  // --- extensions used by the HiFi-GAN generator (hifigan.cu); zero-initialised = the plain conv above
+  int dil;                    // dilation (0 or 1 = none): tap j reads position t + (j - (k-1)/2) * dil
+  int chan_mod;               // > 0: scale / shift are indexed by (channel % chan_mod) (transposed conv as u phase groups of Cout)
+  float out_scale;            // 0 = 1: value is multiplied by this after the residual add ...
+  const float* accum;         // ... and this [B][T][Cout] tensor is added (may alias out_f32): multi-receptive-field sum
+  float b16_slope;            // != 0: the bf16 (hi,lo) copy holds leaky_relu(value, slope) -- the next conv's input -- out_f32 the value
+  float* out_c0;              // optional [B][T]: channel 0 only (conv_post: one real output channel in a 16-wide tile)
 };
 
 int convtc_launch(const ConvTcArgs& a, cudaStream_t st);

@@ -450,7 +450,13 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
         tc::tmem_ld_wait();
         if (a0 < A) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) e = fmaf(sm.v[a0 + i], tanh_fast(as.q_s[a0 + i] + x[i] + pm[i]), e);
+          for (int i = 0; i < 8; ++i) {   // q and v as 16-byte broadcast loads
+            const float4 q4 = *reinterpret_cast<const float4*>(as.q_s + a0 + 4 * i), v4 = *reinterpret_cast<const float4*>(sm.v + a0 + 4 * i);
+            e = fmaf(v4.x, tanh_fast(q4.x + x[4 * i] + pm[4 * i]), e);
+            e = fmaf(v4.y, tanh_fast(q4.y + x[4 * i + 1] + pm[4 * i + 1]), e);
+            e = fmaf(v4.z, tanh_fast(q4.z + x[4 * i + 2] + pm[4 * i + 2]), e);
+            e = fmaf(v4.w, tanh_fast(q4.w + x[4 * i + 3] + pm[4 * i + 3]), e);
+          }
         }
       }
       as.ep[half * 128 + p] = e;
