@@ -204,6 +204,14 @@ int t2_clip_adam_step(int n_tensors, float* const* params, float* const* grads, 
 int t2_melspec(const float* wav, const long long* wav_len, int B, long long wav_stride, const float* window, const float* fb,
                const int* fb_range, int n_fft, int hop, int n_mels, float* out, int t_stride, long long* n_frames, void* stream);
 
+/* Silence trim bounds of a waveform batch: librosa.effects.trim(wav, top_db, frame_length) as datasets/tts_dataset.py:194-200 calls it
+ * (hop_length 512 is librosa's default): start / end (B) int64 sample bounds of the kept interval of every utterance (end = start = 0
+ * when no frame is above the threshold).  wav (B, wav_stride) fp32, wav_len (B) int64 on the device, max_len >= every length.
+ * librosa is external to the reference: parity is pinned to oracle/trim_oracle.py.  ws: t2_trim_workspace_bytes. */
+long long t2_trim_workspace_bytes(int B, long long max_len, int hop_length);
+int t2_trim(const float* wav, const long long* wav_len, int B, long long wav_stride, long long max_len, float top_db, int frame_length,
+            int hop_length, long long* start, long long* end, void* ws, long long ws_bytes, void* stream);
+
 /* Batch assembly: `_collate` of datasets/tts_dataloader.py:8-35 -- nn.utils.rnn.pad_sequence(batch_first=True) over every data
  * key of the batch (chars_idx (L,) int64, mel_spectrogram (T, n_mels) fp32, gate (T, 1) fp32, ...) -- plus the gate targets of
  * datasets/tts_dataset.py:211-214 (ones, last valid frame 0), in one launch.  Field f: src[f] = the B items' rows concatenated

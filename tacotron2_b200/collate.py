@@ -115,10 +115,83 @@ def collate(data, device="cuda:0"):
     return tts_data, tts_data_len, dict(extra)
 
 
-def assemble_from_wavs(wavs, chars, device="cuda:0", silence: int = 0, melspectrogram=None):
+def trim_bounds(wav_pad, wav_len, top_db: float = 60.0, frame_length: int = 2048, hop_length: int = 512):
+    """``librosa.effects.trim(wav, top_db=top_db, frame_length=frame_length)`` (datasets/tts_dataset.py:194-200) for a padded batch on
+    the device: returns (start, end) int64 device tensors of the kept sample interval of every utterance (C ABI ``t2_trim``)."""
+    lib = _lib.load()
+    dev = wav_pad.device
+    if dev.type != "cuda":
+        raise RuntimeError("tacotron2_b200.collate: CUDA device required (no CPU fallback)")
+    wav_pad = wav_pad.to(torch.float32).contiguous()
+    wl = wav_len.to(device=dev, dtype=torch.int64).contiguous()
+    B, stride = wav_pad.shape
+    ws = torch.empty(lib.t2_trim_workspace_bytes(B, stride, hop_length), dtype=torch.uint8, device=dev)
+    start, end = torch.empty(B, dtype=torch.int64, device=dev), torch.empty(B, dtype=torch.int64, device=dev)
+    _lib.check(lib.t2_trim(_lib.ptr(wav_pad), _lib.ptr(wl), B, stride, stride, float(top_db), int(frame_length), int(hop_length), _lib.ptr(start),
+                           _lib.ptr(end), _lib.ptr(ws), ws.numel(), torch.cuda.current_stream(dev).cuda_stream), "t2_trim")
+    return start, end
+
+
+class MelCache:
+    """The reference's per-item mel cache (datasets/tts_dataset.py:184-188,206-207): ``cache_dir/<filename with '/' -> '_'>.pt`` holding
+    the (T, n_mels) log-mel tensor written with ``torch.save``.  Files written here are read by the reference and vice versa."""
+
+    def __init__(self, cache_dir: str):
+        import os
+        self.cache_dir = cache_dir
+        os.makedirs(cache_dir, exist_ok=True)
+
+    def path(self, filename: str) -> str:
+        import os
+        return os.path.join(self.cache_dir, f"{filename.replace('/', '_')}.pt")
+
+    def has(self, filename: str) -> bool:
+        import os
+        return os.path.exists(self.path(filename))
+
+    def load(self, filename: str, device=None):
+        mel = torch.load(self.path(filename), map_location="cpu")
+        return mel if device is None else mel.to(device, non_blocking=True)
+
+    def save(self, filename: str, mel) -> None:
+        torch.save(mel.detach().to("cpu", torch.float32).contiguous().clone(), self.path(filename))
+
+
+def assemble_items(filenames, load_wav, chars, device="cuda:0", cache: "MelCache | None" = None, trim: bool = False, trim_top_db: float = 60.0,
+                   trim_frame_length: int = 2048, silence: int = 0, melspectrogram=None):
+    """``TTSDataset.__getitem__`` + ``_collate`` for a batch of files (datasets/tts_dataset.py:173-214, datasets/tts_dataloader.py:8-35)
+    with the arithmetic on the GPU: items found in the mel cache are read from it, the others are loaded with ``load_wav(filename)``
+    (1-D float tensor), trimmed / padded / turned into log-mels in one batch on the device and written back to the cache in the
+    reference's format.  Returns ``(tts_data, tts_data_len)`` like ``assemble_from_wavs``."""
+    device = torch.device(device)
+    B = len(filenames)
+    assert B == len(chars) and B > 0
+    mels = [None] * B
+    miss = [i for i, f in enumerate(filenames) if cache is None or not cache.has(f)]
+    for i in range(B):
+        if i not in miss:
+            mels[i] = cache.load(filenames[i], device)
+    if miss:
+        data, lens = assemble_from_wavs([load_wav(filenames[i]) for i in miss], [chars[i] for i in miss], device, silence, melspectrogram, trim,
+                                        trim_top_db, trim_frame_length)
+        n = lens["mel_spectrogram_len"].tolist()
+        for j, i in enumerate(miss):
+            mels[i] = data["mel_spectrogram"][j, : n[j]]
+            if cache is not None:
+                cache.save(filenames[i], mels[i])
+    out = pad_fields({"chars_idx": [c.to(torch.int64) for c in chars], "mel_spectrogram": [m.to(torch.float32) for m in mels]}, device,
+                     gate_from="mel_spectrogram")
+    nf = torch.tensor([int(m.shape[0]) for m in mels], dtype=torch.int32, device=device)
+    return out, {"chars_idx_len": torch.tensor([int(c.numel()) for c in chars], dtype=torch.int64, device=device), "mel_spectrogram_len": nf,
+                 "gate_len": nf.clone()}
+
+
+def assemble_from_wavs(wavs, chars, device="cuda:0", silence: int = 0, melspectrogram=None, trim: bool = False, trim_top_db: float = 60.0,
+                       trim_frame_length: int = 2048):
     """The GPU form of the per-item work of ``TTSDataset.__getitem__`` + ``_collate`` for a batch of items that are not in the mel
-    cache (datasets/tts_dataset.py:201-214, datasets/tts_dataloader.py:8-35): waveforms (already trimmed; list of 1-D float tensors)
-    are padded with ``silence`` zeros (``F.pad(wav, (0, silence))``, :201), log-mels extracted for the whole batch by one
+    cache (datasets/tts_dataset.py:194-214, datasets/tts_dataloader.py:8-35): waveforms (list of 1-D float tensors)
+    are optionally trimmed (``trim=True``: ``librosa.effects.trim`` as :194-200, C ABI ``t2_trim``), padded with ``silence`` zeros
+    (``F.pad(wav, (0, silence))``, :201), log-mels extracted for the whole batch by one
     ``t2_melspec`` launch straight into the padded (B, T, n_mels) layout, characters padded and gate targets written by one
     ``t2_collate`` launch.  Returns ``(tts_data, tts_data_len)`` with ``chars_idx``, ``mel_spectrogram``, ``gate`` and
     ``chars_idx_len`` (int64), ``mel_spectrogram_len`` / ``gate_len`` (int32, as the reference's IntTensor)."""
@@ -130,6 +203,11 @@ def assemble_from_wavs(wavs, chars, device="cuda:0", silence: int = 0, melspectr
     mel_tr = melspectrogram if melspectrogram is not None else TacotronMelSpectrogram()
     B = len(wavs)
     assert B == len(chars) and B > 0
+    if trim:   # librosa.effects.trim on the device (datasets/tts_dataset.py:194-200): bounds for the whole batch, one host read
+        raw = pad_fields({"wav": [w.reshape(-1, 1).to(torch.float32) for w in wavs]}, device)["wav"].squeeze(-1)
+        s_dev, e_dev = trim_bounds(raw, torch.tensor([int(w.numel()) for w in wavs], dtype=torch.int64), trim_top_db, trim_frame_length)
+        se = torch.stack([s_dev, e_dev]).tolist()
+        wavs = [raw[b, se[0][b]: se[1][b]] for b in range(B)]
     wl = torch.tensor([int(w.numel()) + silence for w in wavs], dtype=torch.int64)
     # ragged waveforms -> (B, S_max) zero padded on the device (the zero tail of each row is the silence and the batch padding at once)
     wav_pad = pad_fields({"wav": [w.reshape(-1, 1).to(torch.float32) for w in wavs]}, device)["wav"].squeeze(-1)

@@ -138,3 +138,68 @@ def test_gpu_assemble_from_wavs():
     assert float((data["mel_spectrogram"].cpu() - want["mel_spectrogram"]).abs().max()) <= 1e-3   # the melspec parity bar
     for k in wl:
         assert ln[k].dtype == wl[k].dtype and torch.equal(ln[k].cpu(), wl[k]), k
+
+
+def test_trim_oracle_properties_cpu():
+    """The CPU restatement of librosa.effects.trim (parity unpinned vs librosa, absent here): silence around a burst is removed on
+    512-sample frame boundaries, an all-quiet signal trims to nothing, a loud signal is kept whole."""
+    import numpy as np
+    from oracle import trim_oracle as T
+    y = np.zeros(22050, np.float32)
+    y[5000:9000] = 0.5 * np.sin(np.arange(4000) * 0.1).astype(np.float32)
+    out, (s, e) = T.trim(y, top_db=40.0, frame_length=2048, hop_length=512)
+    assert s % 512 == 0 and s <= 5000 < s + 2048 and 9000 <= e <= 9000 + 2048 and out.shape[0] == e - s
+    assert T.trim(np.zeros(4000, np.float32))[1] == (0, 4000)          # every frame is at the amin floor = the max: nothing is below -top_db
+    assert T.trim(np.ones(3000, np.float32) * 0.3)[1] == (0, 3000)
+
+
+@pytest.mark.gpu
+def test_gpu_trim_matches_oracle():
+    import numpy as np
+    from oracle import trim_oracle as T
+    from tacotron2_b200 import synth
+    from tacotron2_b200.collate import trim_bounds
+    dev = torch.device("cuda:0")
+    wavs = []
+    for i, (n, lead, tail) in enumerate(((22050, 3000, 4000), (9000, 0, 2500), (5120, 700, 0), (2048, 100, 100), (40000, 12345, 777))):
+        w = synth.synth_wav(n, seed=i)
+        w = np.concatenate([np.zeros(lead, np.float32) + 1e-6 * np.sin(np.arange(lead)), w, np.zeros(tail, np.float32)]).astype(np.float32)
+        wavs.append(w)
+    L = max(len(w) for w in wavs)
+    pad = torch.zeros(len(wavs), L)
+    for i, w in enumerate(wavs):
+        pad[i, : len(w)] = torch.from_numpy(w)
+    lens = torch.tensor([len(w) for w in wavs])
+    for top_db, fl in ((60.0, 2048), (30.0, 1024), (80.0, 512)):
+        s, e = trim_bounds(pad.to(dev), lens, top_db, fl)
+        want = [T.trim(w, top_db=top_db, frame_length=fl)[1] for w in wavs]
+        assert list(zip(s.tolist(), e.tolist())) == want, (top_db, fl, s.tolist(), e.tolist(), want)
+
+
+@pytest.mark.gpu
+def test_assemble_items_with_trim_and_mel_cache(tmp_path):
+    """Trim + mel on the device + the reference's .pt cache format: the first pass computes and writes the cache, the second pass reads
+    it (and a file written the way the reference writes it is read back the same way)."""
+    import numpy as np
+    from oracle import melspec_oracle as MO
+    from oracle import trim_oracle as T
+    from tacotron2_b200 import synth
+    from tacotron2_b200.collate import MelCache, assemble_items
+    dev = torch.device("cuda:0")
+    names = ["spk/a.wav", "spk/b.wav", "c.wav"]
+    wav = {n: torch.from_numpy(np.concatenate([np.zeros(1500, np.float32), synth.synth_wav(6000 + 1700 * i, seed=i)])) for i, n in enumerate(names)}
+    chars = [torch.arange(1, 5 + i) for i in range(3)]
+    cache = MelCache(str(tmp_path / "mel"))
+    torch.save(torch.full((7, 80), -3.0), cache.path("c.wav"))     # an item the reference cached earlier
+    d1, l1 = assemble_items(names, lambda f: wav[f], chars, dev, cache, trim=True, trim_top_db=40.0, trim_frame_length=1024, silence=256)
+    assert cache.has("spk/a.wav") and cache.path("spk/a.wav").endswith("spk_a.wav.pt")
+    assert l1["mel_spectrogram_len"].tolist()[2] == 7 and float(d1["mel_spectrogram"][2, :7].mean()) == -3.0
+    for i, n in enumerate(names[:2]):
+        y, _ = T.trim(wav[n].numpy(), top_db=40.0, frame_length=1024)
+        want = MO.log_mel(np.concatenate([y, np.zeros(256, np.float32)]))
+        got = d1["mel_spectrogram"][i, : l1["mel_spectrogram_len"][i]].cpu().numpy()
+        assert got.shape == want.shape and float(np.abs(got - want).max()) <= 1e-3
+        assert torch.equal(torch.load(cache.path(n)), d1["mel_spectrogram"][i, : l1["mel_spectrogram_len"][i]].cpu())
+        assert float(d1["gate"][i, l1["gate_len"][i] - 1]) == 0.0 and float(d1["gate"][i, 0]) == 1.0
+    d2, l2 = assemble_items(names, lambda f: (_ for _ in ()).throw(AssertionError("cache miss")), chars, dev, cache)
+    assert torch.equal(d1["mel_spectrogram"], d2["mel_spectrogram"]) and torch.equal(l1["mel_spectrogram_len"], l2["mel_spectrogram_len"])
