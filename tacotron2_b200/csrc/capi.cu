@@ -748,7 +748,11 @@ static int decode2_impl(t2_ctx* c, bool tf, const float* memory, const float* pm
   D2Maps maps;
   RC(make_xmaps(c, d, s, tfp, T + 1, &maps, nslots));
   timing_begin(c, 0, st);
-  if (!tf && !tape && d2ar_supported(d)) RC(d2ar_launch(d, c->d2w, s, io, maps, c->map_locG, st));   // pipelined autoregressive schedule
+  // pipelined schedule: autoregressive synthesis and the teacher-forced training forward (history mode)
+  if (((!tf && !tape) || (tf && tape)) && d2ar_supported(d)) {
+    if (tape) s.floc = nullptr;   // the pipelined kernel tapes the location term (xloc) but not the conv features: the backward recomputes them
+    RC(d2ar_launch(d, c->d2w, s, io, maps, c->map_locG, st));
+  }
   else RC(d2_launch(d, c->d2w, s, io, maps, st));
   timing_end(c, 0, st);
   if (tape) RC(decode_proj_bulk(c, tape->xdec, B, T, mels, gates, proj_tmp, st));

@@ -284,7 +284,8 @@ __device__ __forceinline__ void ar_push_partials(uint32_t tmem, uint32_t col, fl
 // LSTM pointwise tail on the received partials (same summation order as lstm_tail of dec_shared.cuh: ranks 0..3, then the bias).
 // Thread = (unit ul, utterance pair bp).
 __device__ __forceinline__ void ar_lstm_tail(const float* recv, int unit0, const float* __restrict__ bias, int H, float* cst, int B, const HOut& ho,
-                                             float* h_s) {
+                                             float* h_s, const unsigned char* keep = nullptr, bool hidden_dropout = false,
+                                             unsigned long long seed = 0ull, unsigned long long rng_base = 0ull, float* sav = nullptr) {
   const int ul = threadIdx.x >> 5, bp = threadIdx.x & 31;
   const int u = unit0 + ul;
   float2 pre[4];
@@ -297,7 +298,7 @@ __device__ __forceinline__ void ar_lstm_tail(const float* recv, int unit0, const
     pre[g].x = ((p0.x + p1.x) + p2.x) + p3.x + bv;
     pre[g].y = ((p0.y + p1.y) + p2.y) + p3.y + bv;
   }
-  float hv[2];
+  float hv[2], sv[5][2];
 #pragma unroll
   for (int j = 0; j < 2; ++j) {
     const int b = 2 * bp + j;
@@ -305,9 +306,24 @@ __device__ __forceinline__ void ar_lstm_tail(const float* recv, int unit0, const
     const float pg = j ? pre[2].y : pre[2].x, po = j ? pre[3].y : pre[3].x;
     const float si = sigmoid_fast(pi), sf = sigmoid_fast(pf), tg = tanh_fast(pg), so = sigmoid_fast(po);
     const float c = sf * cst[ul * D2_BP + b] + si * tg;
-    const float h = so * tanh_fast(c);
+    float h = so * tanh_fast(c);
     if (b < B) cst[ul * D2_BP + b] = c;
+    sv[0][j] = si; sv[1][j] = sf; sv[2][j] = tg; sv[3][j] = so; sv[4][j] = c;
+    if (hidden_dropout && b < B) {  // nn.Dropout(0.1), train only (model/decoder.py:75,101)
+      const bool k = keep ? (keep[(size_t)b * H + u] != 0) : rng_keep(seed, rng_base + (unsigned long long)b * H + u, 0.1f);
+      h = k ? h * (1.0f / 0.9f) : 0.f;
+    }
     hv[j] = b < B ? h : 0.f;
+  }
+  if (sav) {  // training tape: [5][H][BP] (i, f, g, o post-activation, c), write-once
+    const size_t o = (size_t)u * D2_BP + 2 * bp, gs = (size_t)H * D2_BP;
+    if (2 * bp + 1 < B) {
+#pragma unroll
+      for (int g = 0; g < 5; ++g) __stcs(reinterpret_cast<float2*>(sav + g * gs + o), make_float2(sv[g][0], sv[g][1]));
+    } else if (2 * bp < B) {
+#pragma unroll
+      for (int g = 0; g < 5; ++g) sav[g * gs + o] = sv[g][0];
+    }
   }
   *reinterpret_cast<float2*>(h_s + ul * D2_BP + 2 * bp) = make_float2(hv[0], hv[1]);
   wsync();
@@ -433,6 +449,7 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
 #pragma unroll
       for (int g = 1; g < 8; ++g) qv += as.qh[g * A + tid];
       as.q_s[tid] = qv;
+      if (io.hist && at.part == 0) s.q[((size_t)t_out * D2_BP + at.b) * A + tid] = qv;   // training tape
     }
     if (!tc::mbar_wait(sm.bars + B_LOC, fphase)) ok = false;   // location term of this frame is in TMEM
     tc::tc_fence_after();
@@ -448,6 +465,11 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
         tc::tmem_ld32(tmem + ((uint32_t)lane0 << 16) + AR_COL_LOC + a0, x);
         tc::tmem_ld32(tmem + ((uint32_t)lane0 << 16) + AR_COL_PM + a0, pm);
         tc::tmem_ld_wait();
+        if (io.hist && s.accpm && a0 < A && p < at.nl) {   // training tape: location term + processed memory of this frame (the
+          float4* dst = reinterpret_cast<float4*>(s.accpm + (((size_t)t_out * 128 + blockIdx.x) * ((L + S - 1) / S) + p) * A + a0);   // backward's pre-tanh argument - q)
+#pragma unroll
+          for (int i = 0; i < 8; ++i) __stcs(dst + i, make_float4(x[4 * i] + pm[4 * i], x[4 * i + 1] + pm[4 * i + 1], x[4 * i + 2] + pm[4 * i + 2], x[4 * i + 3] + pm[4 * i + 3]));
+        }
         if (a0 < A) {
 #pragma unroll
           for (int i = 0; i < 8; ++i) {   // q and v as 16-byte broadcast loads
@@ -503,7 +525,13 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
       const float w = wr[l] * inv;
       wr[l] = w;
       sm.wcum[15 + l] += w;                                                   // model/decoder.py:90 (every part keeps the whole row)
-      if (l >= at.l0 && l < l1) io.aligns[((size_t)at.b * io.Tmax + t_out) * L + l] = w;
+      if (l >= at.l0 && l < l1) {
+        io.aligns[((size_t)at.b * io.Tmax + t_out) * L + l] = w;
+        if (io.hist) {   // training tape: weights / cumulative weights after this frame (slot t+1)
+          s.w_prev[((size_t)nxt * D2_BP + at.b) * L + l] = w;
+          s.w_cum[((size_t)nxt * D2_BP + at.b) * L + l] = sm.wcum[15 + l];
+        }
+      }
     }
     wsync();
     mark(13);
@@ -548,7 +576,7 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
       const int col = c0 + c;
       store_split(xa, pa, d.KattP, at.b, d.P + col, v);
       store_split(xd, pd, d.KdecP, at.b, d.H + col, v);
-      s.projin[(size_t)at.b * d.KprojP + d.R + col] = v;
+      if (!io.hist) s.projin[(size_t)at.b * d.KprojP + d.R + col] = v;
     }
   }
   mark(14);
@@ -706,7 +734,8 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
     tc::mbar_init(sm.bars + B_RV, 1); tc::mbar_init(sm.bars + B_RV2, D2_CLUSTER); tc::mbar_init(sm.bars + B_E, 1); tc::mbar_init(sm.bars + B_MEL, 1);
     tc::mbar_init(sm.bars + B_P1, 1); tc::mbar_init(sm.bars + B_W1, 1); tc::mbar_init(sm.bars + B_G, 1); tc::mbar_init(sm.bars + B_FIN, 1);
     tc::fence_barrier_init();
-    sm.ctl[0] = 1u;   // gate count: the (virtual) barrier that publishes the prenet columns of frame 0 counts as passed
+    sm.ctl[0] = io.teacher_forcing ? 0u : 1u;   // gate count; autoregressive: the (virtual) barrier that publishes the prenet columns of
+                                                // frame 0 counts as passed.  Teacher forcing has three barriers per frame (no X)
     sm.ctl[1] = 0u; sm.ctl[2] = 0u; sm.ctl[4] = 0u; sm.ctl[5] = 0u; sm.ctl[8] = 0u;
     sm.ctl[3] = (unsigned)build_program(d, (int)rank, sm.prog);
   }
@@ -773,14 +802,18 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
         }
         if (x_n < w_n) {
           const KbEnt en = sm.prog[x_e];
-          const int need = 4 * x_f + (int)en.gate + 1;
+          // teacher forcing: the prenet columns of every frame exist before the launch (bulk prenet), three barriers per frame (Q, C, R)
+          const int need = io.teacher_forcing ? (en.gate == G_X ? -1 : 3 * x_f + (int)en.gate) : 4 * x_f + (int)en.gate + 1;
           const unsigned have = ld_acquire_cta(sm.ctl);
           if ((int)have >= need) {
             if (have != fenced_gate) { asm volatile("fence.proxy.async;" ::: "memory"); fenced_gate = have; }   // peers' generic stores -> TMA reads
             const int gf = x_f + ((en.flags & 4) ? 1 : 0);
             uint8_t* st = sm.stages + (size_t)x_stage * TG_STAGE_BYTES;
             tc::mbar_arrive_expect_tx(sm.bars + B_FULL + x_stage, stage_x);
-            tc::tma_load_3d(st + 2 * TG_W_TILE, en.gemm ? &maps.x_dec : &maps.x_att, sm.bars + B_FULL + x_stage, en.kb * TG_BK, 0, (gf & 1) * 2);
+            const int slot = io.hist ? gf : (gf & 1);   // history mode (training tape): one slot per frame instead of two parities
+            const bool pre = io.teacher_forcing && !en.gemm && en.gate == G_X;   // prenet K-block: from the bulk prenet output
+            tc::tma_load_3d(st + 2 * TG_W_TILE, pre ? &maps.tf_pre : (en.gemm ? &maps.x_dec : &maps.x_att), sm.bars + B_FULL + x_stage, en.kb * TG_BK, 0,
+                            (pre ? gf : slot) * 2);
             if (++x_stage == AR_STAGES) x_stage = 0;
             ++x_n;
             advance(x_f, x_e);
@@ -914,12 +947,19 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
     }
     const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
     bool alive = true, fail = false, stop = false;
+    const bool has_out = !io.teacher_forcing;
     uint32_t rv_phase = 0, rv2_phase = 0, cphase = 0;
     int frames = 0;
 #pragma unroll 1
     for (int t = 0; t < io.n_steps && alive && !stop; ++t) {
       const int tg_ = io.t0 + t;
-      const int cur = t & 1, nxt = cur ^ 1;
+      const int cur = io.hist ? tg_ : (t & 1), nxt = io.hist ? tg_ + 1 : (cur ^ 1);   // history mode: one slot per frame (training tape)
+      const unsigned char* att_keep = io.att_keep ? io.att_keep + (size_t)tg_ * B * d.H : nullptr;
+      const unsigned char* rnn_keep = io.rnn_keep ? io.rnn_keep + (size_t)tg_ * B * d.H : nullptr;
+      const unsigned long long rb_att = (1ull << 40) + (unsigned long long)tg_ * B * d.H, rb_dec = (2ull << 40) + (unsigned long long)tg_ * B * d.H;
+      float* sav_att = s.sav_att ? s.sav_att + (size_t)tg_ * 5 * d.H * D2_BP : nullptr;
+      float* sav_dec = s.sav_dec ? s.sav_dec + (size_t)tg_ * 5 * d.H * D2_BP : nullptr;
+      const bool hdrop = io.hidden_dropout != 0;
       // ================= attention LSTMCell (model/decoder.py:70-75): only the prenet K-block of the contraction is still to come
       if (!tc::mbar_wait(sm.bars + B_ACC_ATT, (uint32_t)(t & 1))) fail = true;
       tc::tc_fence_after();
@@ -929,13 +969,13 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
         if (pull_tails) {
           ar_accum_to_smem(tmem, AR_COL_ATT, sm.part);
           if (!cluster_rendezvous(sm.bars + B_RV2, rv2_phase)) fail = true;
-          lstm_tail(sm.part, rank, unit0, w.batt, d.H, sm.c_att, B, ho, nullptr, false, io.seed, 0ull, nullptr, sm.h_s);
+          lstm_tail(sm.part, rank, unit0, w.batt, d.H, sm.c_att, B, ho, att_keep, hdrop, io.seed, rb_att, sav_att, sm.h_s);
         } else {
           ar_push_partials(tmem, AR_COL_ATT, sm.part, sm.bars + B_RV, rank);
           if (!tc::mbar_wait_cluster(sm.bars + B_RV, rv_phase)) fail = true;
           rv_phase ^= 1u;
           if (io.debug_barrier & 8) prof_mark(8);   // (experiment: the exchange is charged to slot 8)
-          ar_lstm_tail(sm.part, unit0, w.batt, d.H, sm.c_att, B, ho, sm.h_s);
+          ar_lstm_tail(sm.part, unit0, w.batt, d.H, sm.c_att, B, ho, sm.h_s, att_keep, hdrop, io.seed, rb_att, sav_att);
         }
       }
       prof_mark(0);
@@ -949,30 +989,31 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
       prof_mark(2);
       // ================= decoder LSTMCell (model/decoder.py:94-101): the context K-blocks are on their way; meanwhile the context
       // half of this frame's mel / gate projection
-      ar_proj_ctx(d, w, s, sm, rank, tile);
+      if (has_out) ar_proj_ctx(d, w, s, sm, rank, tile);
       prof_mark(15);
       if (!tc::mbar_wait(sm.bars + B_ACC_DEC, (uint32_t)(t & 1))) fail = true;
       tc::tc_fence_after();
       prof_mark(9);
       {
-        const HOut ho{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, s.projin, d.KprojP, 0};
+        const HOut ho{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, io.hist ? nullptr : s.projin, d.KprojP, 0};
         if (pull_tails) {
           ar_accum_to_smem(tmem, AR_COL_DEC, sm.part);
           if (!cluster_rendezvous(sm.bars + B_RV2, rv2_phase)) fail = true;
-          lstm_tail(sm.part, rank, unit0, w.bdec, d.H, sm.c_dec, B, ho, nullptr, false, io.seed, 0ull, nullptr, sm.h_s);
+          lstm_tail(sm.part, rank, unit0, w.bdec, d.H, sm.c_dec, B, ho, rnn_keep, hdrop, io.seed, rb_dec, sav_dec, sm.h_s);
         } else {
           ar_push_partials(tmem, AR_COL_DEC, sm.part, sm.bars + B_RV, rank);
           if (!tc::mbar_wait_cluster(sm.bars + B_RV, rv_phase)) fail = true;
           rv_phase ^= 1u;
-          ar_lstm_tail(sm.part, unit0, w.bdec, d.H, sm.c_dec, B, ho, sm.h_s);
+          ar_lstm_tail(sm.part, unit0, w.bdec, d.H, sm.c_dec, B, ho, sm.h_s, rnn_keep, hdrop, io.seed, rb_dec, sav_dec);
         }
       }
       if (!(alive = bar.sync(fail, sm.ctl))) break;
       prof_mark(3);
       // ================= mel / gate projection, stop bookkeeping, prenet on the emitted frame (model/decoder.py:103-109,
       // model/tacotron2.py:311-325)
-      if (!ar_output(d, w, s, io, sm, rank, tile, tg_, nxt, cphase, &prof_last)) fail = true;
       frames = t + 1;
+      if (!has_out) continue;   // teacher-forced training: the projection is one bulk GEMM after the kernel, the prenet ran before it
+      if (!ar_output(d, w, s, io, sm, rank, tile, tg_, nxt, cphase, &prof_last)) fail = true;
       if (t + 1 < io.n_steps) {
         if (!(alive = bar.sync(fail, sm.ctl))) break;
         if (io.stop_enabled) {   // model/tacotron2.py:321-322: leave once every utterance has fired its stop gate
@@ -1042,7 +1083,8 @@ bool d2ar_supported(const D2Dims& d) {
 int d2ar_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, const D2Maps& maps, const CUtensorMap& gmap,
                 cudaStream_t st) {
   T2_REQUIRE(d2ar_supported(d), T2_ERR_UNSUPPORTED, "decoder (pipelined AR): unsupported shape B=%d L=%d", d.B, d.L);
-  T2_REQUIRE(!io.teacher_forcing && !io.hist && !io.hidden_dropout, T2_ERR_ARG, "decoder (pipelined AR): autoregressive eval mode only");
+  T2_REQUIRE((!io.teacher_forcing && !io.hist && !io.hidden_dropout) || (io.teacher_forcing && io.hist), T2_ERR_ARG,
+             "decoder (pipelined): autoregressive eval mode or the teacher-forced training forward (history mode) only");
   const size_t smem = ar_smem_bytes(d);
   T2_CHECK_CUDA(cudaFuncSetAttribute(decoder_ar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg{};

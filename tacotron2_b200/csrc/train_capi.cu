@@ -375,7 +375,9 @@ int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const uns
   DBWeights w{wq->ptr, wv->ptr, c->loc_conv_t, c->loc_dense_t};
   DBTape t{};
   t.sav_att = tp.sav_att; t.sav_dec = tp.sav_dec; t.q = tp.q; t.w_hist = tp.w_hist; t.wcum_hist = tp.wcum_hist;
-  if (d2_precompute_fits(d)) { t.xloc = tp.xloc; t.floc = tp.floc; }   // same decision as the forward that wrote the tape
+  // same decision as the forward that wrote the tape: the pipelined forward (decoder_ar.cu) tapes the location term only
+  if (d2ar_supported(d)) { t.xloc = tp.xloc; t.floc = nullptr; }
+  else if (d2_precompute_fits(d)) { t.xloc = tp.xloc; t.floc = tp.floc; }
   t.memory = memory; t.pmem = pmem; t.mask = mask; t.att_keep = att_keep; t.rnn_keep = rnn_keep; t.seed = seed; t.hidden_dropout = 1;
   DBWork k{};
   k.dprojin = dprojin; k.dg_att = dg_att; k.dg_dec = dg_dec; k.dgT_att = dgT_att; k.dgT_dec = dgT_dec; k.dx_att = dx_att; k.dx_dec = dx_dec;

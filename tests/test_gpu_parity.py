@@ -244,9 +244,11 @@ def test_c5_long_form():
             os.environ["T2B200_PRECISION"] = old
 
 
-def test_fallback_attention_path_agrees():
-    """The decoder launch chooses the precomputed-location-term path when shared memory allows it; the in-phase path (very long
-    utterances, T2B200_NO_PRECOMPUTE=1) must give the same results up to summation order, forward and backward."""
+def test_decoder_schedules_agree():
+    """Three implementations of the frame loop must give the same results up to summation order, forward and backward: the pipelined
+    kernel (decoder_ar.cu: autoregressive synthesis and the training forward; default), decoder_persistent_kernel with the location
+    term precomputed beside the GEMMs (T2B200_AR_KERNEL=old), and its in-phase path for very long utterances (+ T2B200_NO_PRECOMPUTE=1).
+    The backward consumes three different tapes accordingly (location term taped without / with conv features / not at all)."""
     args, B, L, T = synth.VANILLA, 6, 41, 10
     sd = synth.synth_state_dict(args, seed=0, gate_shift=5.0)
     bc = _cuda(synth.synth_batch(args, B, L, T, seed=5))
@@ -254,24 +256,30 @@ def test_fallback_attention_path_agrees():
     masks_tr = synth.synth_masks(args, B, L, T, seed=7, train=True)
     res = {}
     try:
-        for mode in ("default", "fallback"):
-            if mode == "fallback":
-                os.environ["T2B200_NO_PRECOMPUTE"] = "1"
+        for mode, env in (("pipelined", {}), ("persistent", {"T2B200_AR_KERNEL": "old"}),
+                          ("persistent-inphase", {"T2B200_AR_KERNEL": "old", "T2B200_NO_PRECOMPUTE": "1"})):
+            os.environ.update(env)
             m = _model(args, sd)
             with torch.no_grad():
                 ar = m(bc["chars_idx"], bc["chars_idx_len"], False, max_len_override=T, dropout_masks=masks_ar)
             m.train()
-            mels, post, gates, _ = m(bc["chars_idx"], bc["chars_idx_len"], True, bc["mel_spectrogram"], bc["mel_spectrogram_len"],
-                                     dropout_masks=masks_tr)
+            mels, post, gates, al = m(bc["chars_idx"], bc["chars_idx_len"], True, bc["mel_spectrogram"], bc["mel_spectrogram_len"],
+                                      dropout_masks=masks_tr)
             m.loss(mels, post, gates, bc["mel_spectrogram"], bc["gate"]).backward()
-            res[mode] = (ar, {k: p.grad.detach().clone() for k, p in m.named_parameters() if k.startswith("decoder.attention")})
+            res[mode] = (ar, (mels.detach(), al.detach()),
+                         {k: p.grad.detach().clone() for k, p in m.named_parameters() if k.startswith(("decoder.", "prenet."))})
+            m.check_status()
     finally:
         os.environ.pop("T2B200_NO_PRECOMPUTE", None)
-    for a, b_ in zip(res["default"][0], res["fallback"][0]):
-        assert _err(a, b_) <= 2e-5
-    for k, g in res["default"][1].items():
-        g2 = res["fallback"][1][k]
-        assert float((g - g2).norm()) <= 1e-4 * float(g.norm()) + 1e-9, k
+        os.environ.pop("T2B200_AR_KERNEL", None)
+    for mode in ("persistent", "persistent-inphase"):
+        for a, b_ in zip(res["pipelined"][0], res[mode][0]):
+            assert _err(a, b_) <= 2e-5, mode
+        for a, b_ in zip(res["pipelined"][1], res[mode][1]):
+            assert _err(a, b_) <= 2e-5, mode
+        for k, g in res["pipelined"][2].items():
+            g2 = res[mode][2][k]
+            assert float((g - g2).norm()) <= 2e-4 * float(g.norm()) + 1e-9, (mode, k, float((g - g2).norm()), float(g.norm()))
 
 
 @pytest.mark.parametrize("with_masks", [True, False])
