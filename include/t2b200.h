@@ -254,6 +254,28 @@ long long t2_hifigan_workspace_bytes(const t2_hifigan* g, int B, int T);
 long long t2_hifigan_out_len(const t2_hifigan* g, int T);
 int t2_hifigan_fwd(t2_hifigan* g, const float* mel, int B, int T, float* wav, void* ws, long long ws_bytes, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------------
+ * Description-embedding front end: BertModel(input_ids, token_type_ids, attention_mask).pooler_output
+ * as run/say.py:93-106 computes it (google-bert/bert-base-uncased), batched: input_ids / token_type_ids (B, S) int64 (token_type_ids
+ * may be NULL = zeros), attention_mask (B, S) fp32 1 = token / 0 = padding (NULL = all ones) -> pooler_output (B, hidden) and
+ * optionally last_hidden_state (B, S, hidden).  Parameters under the Hugging Face BertModel state-dict keys
+ * ("embeddings.word_embeddings.weight", "encoder.layer.0.attention.self.query.weight", ..., "pooler.dense.bias").  The WordPiece
+ * tokenizer is host string processing outside this library.
+ * ------------------------------------------------------------------------------------------------------------------ */
+typedef struct t2_bert t2_bert;
+typedef struct {
+  int vocab_size, hidden_size, num_layers, num_heads, intermediate_size, max_position, type_vocab_size;
+  float layer_norm_eps;
+  int precision;   /* 0 = fp32-parity (three bf16 hi/lo passes), 1 = bf16 */
+} t2_bert_config;
+int t2_bert_create(const t2_bert_config* cfg, t2_bert** out);
+int t2_bert_destroy(t2_bert* g);
+int t2_bert_set_param(t2_bert* g, const char* key, const float* ptr, long long numel);
+int t2_bert_commit(t2_bert* g, void* stream);
+long long t2_bert_workspace_bytes(const t2_bert* g, int B, int S);
+int t2_bert_pooler_fwd(t2_bert* g, const long long* input_ids, const long long* token_type_ids, const float* attention_mask, int B, int S,
+                       float* pooler_output, float* last_hidden_state, void* ws, long long ws_bytes, void* stream);
+
 /* Sticky device status of the context's persistent kernels (decoder forward / backward).  They bound every wait; a timeout makes
  * all CTAs leave together, NaN-fills the launch's outputs and sets this word.  *status_out = 0 or T2_ERR_DEVICE_ABORT; reading
  * clears it.  Synchronises the device: call it where the host synchronises anyway (reading a loss, n_frames, a checkpoint). */

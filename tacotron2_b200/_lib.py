@@ -29,6 +29,11 @@ class T2HifiganConfig(C.Structure):
     ]
 
 
+class T2BertConfig(C.Structure):
+    _fields_ = [("vocab_size", C.c_int), ("hidden_size", C.c_int), ("num_layers", C.c_int), ("num_heads", C.c_int), ("intermediate_size", C.c_int),
+                ("max_position", C.c_int), ("type_vocab_size", C.c_int), ("layer_norm_eps", C.c_float), ("precision", C.c_int)]
+
+
 _P, _I, _LL, _ULL = C.c_void_p, C.c_int, C.c_longlong, C.c_ulonglong
 
 # name -> (restype, argtypes); kept in sync with include/t2b200.h (tests/test_abi.py checks the symbol list)
@@ -57,6 +62,12 @@ SIGNATURES = {
     "t2_hifigan_workspace_bytes": (_LL, [_P, _I, _I]),
     "t2_hifigan_out_len": (_LL, [_P, _I]),
     "t2_hifigan_fwd": (_I, [_P, _P, _I, _I, _P, _P, _LL, _P]),
+    "t2_bert_create": (_I, [C.POINTER(T2BertConfig), C.POINTER(_P)]),
+    "t2_bert_destroy": (_I, [_P]),
+    "t2_bert_set_param": (_I, [_P, C.c_char_p, _P, _LL]),
+    "t2_bert_commit": (_I, [_P, _P]),
+    "t2_bert_workspace_bytes": (_LL, [_P, _I, _I]),
+    "t2_bert_pooler_fwd": (_I, [_P, _P, _P, _P, _I, _I, _P, _P, _P, _LL, _P]),
     "t2_prenet_fwd": (_I, [_P, _P, _P, _P, _ULL, _I, _P, _P, _LL, _P]),
     "t2_postnet_fwd": (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _P, _LL, _P]),
     "t2_debug_phase_cycles": (_I, [_P, _P]),

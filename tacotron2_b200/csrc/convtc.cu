@@ -104,6 +104,7 @@ __global__ void __launch_bounds__(256, 1) conv_tc_kernel(const __grid_constant__
         else if (a.shift) x += __ldg(a.shift + ci);
         if (a.act == ACT_RELU) x = fmaxf(x, 0.f);
         else if (a.act == ACT_TANH) x = tanhf(x);
+        else if (a.act == ACT_GELU) x = 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
         if (a.keep) x = a.keep[pos * a.keep_ld + n + i] ? x * a.drop_scale : 0.f;
         if (a.residual) x += a.residual[(size_t)b * a.res_bstride + (size_t)t * a.Cout + n + i];
         if (a.out_scale != 0.f) x *= a.out_scale;

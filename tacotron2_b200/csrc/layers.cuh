@@ -2,7 +2,7 @@
 #pragma once
 #include "common.cuh"
 
-enum { ACT_NONE = 0, ACT_RELU = 1, ACT_TANH = 2 };
+enum { ACT_NONE = 0, ACT_RELU = 1, ACT_TANH = 2, ACT_GELU = 3 };   // GELU: exact erf form (BERT "gelu")
 
 int bilstm_launch(const float* xproj /*[B][L][2][4Hh]*/, const float* Whh /*[2][4Hh][Hh] (reference layout)*/, const long long* lens,
                   float* out /*[B][L][2Hh]*/, int B, int L, int Hh, cudaStream_t st,
