@@ -212,6 +212,18 @@ long long t2_trim_workspace_bytes(int B, long long max_len, int hop_length);
 int t2_trim(const float* wav, const long long* wav_len, int B, long long wav_stride, long long max_len, float top_db, int frame_length,
             int hop_length, long long* start, long long* end, void* ws, long long ws_bytes, void* stream);
 
+/* t2_trim without a workspace argument and without any allocation, for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  This entry point has no counterpart in the reference.
+ * Same inputs, outputs and results as t2_trim; the frame-RMS scratch is a file-scope device array
+ * of T2_TRIM_STATIC_MAX_FRAMES floats (1 MiB, resident on every GPU that loads the library until the process exits).  Requests with
+ * B * (1 + max_len / hop_length) > T2_TRIM_STATIC_MAX_FRAMES return T2_ERR_WORKSPACE (-4) with a message in t2_last_error() and
+ * launch nothing.  All calls on a device share the array (it keeps the previous call's contents; nothing in it needs clearing):
+ * calls that overlap on the GPU race -- serialise them on one stream, or use t2_trim with a workspace per stream.  The first call
+ * on each device looks the array's device address up (cudaGetSymbolAddress, no allocation). */
+#define T2_TRIM_STATIC_MAX_FRAMES 262144
+int t2_trim_static(const float* wav, const long long* wav_len, int B, long long wav_stride, long long max_len, float top_db,
+                   int frame_length, int hop_length, long long* start, long long* end, void* stream);
+
 /* Batch assembly: `_collate` of datasets/tts_dataloader.py:8-35 -- nn.utils.rnn.pad_sequence(batch_first=True) over every data
  * key of the batch (chars_idx (L,) int64, mel_spectrogram (T, n_mels) fp32, gate (T, 1) fp32, ...) -- plus the gate targets of
  * datasets/tts_dataset.py:211-214 (ones, last valid frame 0), in one launch.  Field f: src[f] = the B items' rows concatenated

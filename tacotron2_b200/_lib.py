@@ -90,6 +90,7 @@ SIGNATURES = {
     "t2_melspec": (_I, [_P, _P, _I, _LL, _P, _P, _P, _I, _I, _I, _P, _I, _P, _P]),
     "t2_trim_workspace_bytes": (_LL, [_I, _LL, _I]),
     "t2_trim": (_I, [_P, _P, _I, _LL, _LL, C.c_float, _I, _I, _P, _P, _P, _LL, _P]),
+    "t2_trim_static": (_I, [_P, _P, _I, _LL, _LL, C.c_float, _I, _I, _P, _P, _P]),
     "t2_collate": (_I, [_I, _P, _P, _P, _P, _P, _I, _P, _P, _LL, _P]),
     "t2_clip_adam_chunks": (_LL, [_I, _P]),
     "t2_clip_adam_workspace_bytes": (_LL, [_I, _LL]),

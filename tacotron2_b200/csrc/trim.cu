@@ -90,3 +90,62 @@ extern "C" int t2_trim(const float* wav, const long long* wav_len, int B, long l
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------------------
+// t2_trim_static: t2_trim for callers that may not allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).
+// No counterpart in the reference.  The frame-RMS scratch that t2_trim takes as a
+// caller workspace lives in the file-scope device array below instead: T2_TRIM_STATIC_MAX_FRAMES floats = 1 MiB, held by every GPU
+// that loads the library until the process exits.  Limits and sharing:
+//   * B * (1 + max_len / hop_length) <= T2_TRIM_STATIC_MAX_FRAMES (262144: e.g. 64 utterances of 2.09 M samples = 95 s at 22.05 kHz
+//     with librosa's hop of 512); larger requests are rejected with T2_ERR_WORKSPACE before any launch;
+//   * every call on a device shares the one array, which keeps the previous call's contents.  Nothing in it has to start at zero:
+//     trim_rms_kernel writes frames [0, 1 + len/hop) of every utterance and trim_bounds_kernel reads exactly those, so there is no
+//     clearing pass;
+//   * calls that overlap on the GPU (two streams, or two host threads on one device) race on the array: serialise them, or use
+//     t2_trim with one workspace per stream.
+// In host code `g_trim_static_rms` is only a host-side stand-in for the symbol, not a device address: the address handed to the
+// kernels comes from cudaGetSymbolAddress, looked up once per device with that device current (first call on the device) and cached.
+// The call allocates nothing: no cudaMalloc / cudaFree, no allocating library routine.
+static_assert(T2_TRIM_STATIC_MAX_FRAMES == 262144, "the limit is stated in include/t2b200.h, DESIGN.md and INTEGRATION.md");
+static __device__ __align__(256) float g_trim_static_rms[T2_TRIM_STATIC_MAX_FRAMES];
+
+namespace {
+constexpr int TRIM_STATIC_MAX_DEVICES = 64;
+float* g_trim_static_ptr[TRIM_STATIC_MAX_DEVICES];   // per-device address of g_trim_static_rms (null = not looked up yet)
+
+// address of the scratch array on the CURRENT device (set-up on the first call per device; racing first calls store the same value)
+int trim_static_scratch(float** out) {
+  int dev = -1;
+  T2_CHECK_CUDA(cudaGetDevice(&dev));
+  T2_REQUIRE(dev >= 0 && dev < TRIM_STATIC_MAX_DEVICES, T2_ERR_UNSUPPORTED, "t2_trim_static: device ordinal %d beyond %d", dev,
+             TRIM_STATIC_MAX_DEVICES);
+  float* p = __atomic_load_n(&g_trim_static_ptr[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    T2_CHECK_CUDA(cudaGetSymbolAddress((void**)&p, g_trim_static_rms));
+    T2_REQUIRE(p != nullptr, T2_ERR_CUDA, "t2_trim_static: cudaGetSymbolAddress returned a null address on device %d", dev);
+    __atomic_store_n(&g_trim_static_ptr[dev], p, __ATOMIC_RELEASE);
+  }
+  *out = p;
+  return T2_OK;
+}
+}  // namespace
+
+extern "C" int t2_trim_static(const float* wav, const long long* wav_len, int B, long long wav_stride, long long max_len, float top_db,
+                              int frame_length, int hop_length, long long* start, long long* end, void* stream) {
+  T2_REQUIRE(wav && wav_len && start && end && B > 0 && frame_length > 0 && hop_length > 0 && max_len >= 0 && max_len <= wav_stride,
+             T2_ERR_ARG, "t2_trim_static: bad argument");
+  const long long max_frames = 1 + max_len / hop_length;
+  T2_REQUIRE(max_frames <= T2_TRIM_STATIC_MAX_FRAMES && (long long)B * max_frames <= T2_TRIM_STATIC_MAX_FRAMES, T2_ERR_WORKSPACE,
+             "t2_trim_static: B=%d x %lld frames (max_len %lld, hop %d) = %lld frames exceeds the built-in scratch of %lld frames; "
+             "use t2_trim with a caller workspace",
+             B, max_frames, max_len, hop_length, (long long)B * max_frames, (long long)T2_TRIM_STATIC_MAX_FRAMES);
+  float* rms = nullptr;
+  const int rc = trim_static_scratch(&rms);
+  if (rc != T2_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const unsigned gx = (unsigned)std::min<long long>((max_frames + 7) / 8, 148 * 4);
+  trim_rms_kernel<<<dim3(gx, (unsigned)B), 256, 0, st>>>(wav, wav_len, wav_stride, frame_length, hop_length, rms, max_frames);
+  trim_bounds_kernel<<<B, 256, 0, st>>>(rms, wav_len, hop_length, top_db, max_frames, start, end);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
