@@ -21,8 +21,11 @@ struct BSmem {
   float* dense;       // [32][A]   (f-major, as the forward)
   float* dense_af;    // [A][36]   (a-major copy for d f = ds * Wd: 16-byte rows over f)
   float* v;           // [A]
-  uint64_t* bars;
-  uint32_t* tmem_slot;
+  uint8_t* gfT;       // tensor-core attention path (bwd_decoder_att_tc.inl), in place of conv_t / dense / dense_af:
+                      // folded filter bank G[(c,j)][a] as bf16 (hi,lo) K-major sw128 tiles [2 hl][2 kt][64 rows][128 B]
+  uint8_t* ident;     // 16 x 16 identity as one K-major sw128 tile (2 KB)
+  uint64_t* bars;     // ring full[3] empty[3], accumulator, spare, attention H done, attention all done
+  uint32_t* tmem_slot;   // [0] GEMM accumulators (256 columns), [1] d pm + Y accumulators of the tensor-core attention path (256 columns)
 };
 
 __device__ __forceinline__ BSmem carve(uint8_t* base, const D2Dims& d) {
@@ -32,18 +35,19 @@ __device__ __forceinline__ BSmem carve(uint8_t* base, const D2Dims& d) {
   s.part = reinterpret_cast<float*>(p);    p += TG_M * TG_PART_LD * 4;
   s.dc_att = reinterpret_cast<float*>(p);  p += 8 * D2_BP * 4;
   s.dc_dec = reinterpret_cast<float*>(p);  p += 8 * D2_BP * 4;
+  s.gfT = p; s.ident = p + 32768;          // (offset 182 KB from the 1024-aligned base: tile aligned)
   s.conv_t = reinterpret_cast<float*>(p);  p += 2 * D2_LOC_K * D2_LOC_F * 4;
   s.dense = reinterpret_cast<float*>(p);   p += d.A * D2_LOC_F * 4;
   s.dense_af = reinterpret_cast<float*>(p); p += d.A * 36 * 4;
   s.v = reinterpret_cast<float*>(p);       p += d.A * 4;
-  s.bars = reinterpret_cast<uint64_t*>(p); p += (2 * D2_STAGES + 2) * 8;
+  s.bars = reinterpret_cast<uint64_t*>(p); p += (2 * D2_STAGES + 4) * 8;
   s.tmem_slot = reinterpret_cast<uint32_t*>(p);
   return s;
 }
 
 size_t bsmem_bytes(const D2Dims& d) {
   return 1024 + (size_t)D2_STAGES * TG_STAGE_BYTES + TG_M * TG_PART_LD * 4 + 2 * 8 * D2_BP * 4 + 2 * D2_LOC_K * D2_LOC_F * 4 +
-         (size_t)d.A * D2_LOC_F * 4 + (size_t)d.A * 36 * 4 + d.A * 4 + (2 * D2_STAGES + 2) * 8 + 64;
+         (size_t)d.A * D2_LOC_F * 4 + (size_t)d.A * 36 * 4 + d.A * 4 + (2 * D2_STAGES + 4) * 8 + 64;
 }
 
 __device__ __forceinline__ float block_reduce_sum(float v, float* red) {
@@ -156,4 +160,5 @@ __device__ __forceinline__ void lstm_pointwise_bwd(const PwArgs& a, int H, int B
 }  // namespace
 
 #include "bwd_decoder_att.inl"
+#include "bwd_decoder_att_tc.inl"
 #include "bwd_decoder_main.inl"

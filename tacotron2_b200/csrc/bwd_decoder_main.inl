@@ -4,6 +4,7 @@ namespace {
 struct DBParams {
   D2Dims d;
   int T, KattT, KdecT, S;
+  int tc_att;                 // 1: attention backward contractions on tcgen05 (bwd_decoder_att_tc.inl), 0: CUDA cores (bwd_decoder_att.inl)
   DBWeights w;
   DBTape tp;
   DBWork wk;
@@ -51,21 +52,55 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
   if (tid == 0) {
     tc::prefetch_tmap(&maps.wt_att); tc::prefetch_tmap(&maps.wt_dec); tc::prefetch_tmap(&maps.dg_att); tc::prefetch_tmap(&maps.dg_dec);
   }
+  if (p.tc_att) {
+    // folded filter bank G[(c,j)][a] = sum_f Wd[a][f] Wc[c][j][f] (row c*32 + j; rows 31 and 63 zero) as bf16 (hi,lo) operand tiles, and
+    // the 16 x 16 identity block of the d pm accumulation
 #pragma unroll 1
-  for (int i = tid; i < 2 * D2_LOC_K * D2_LOC_F; i += D2_THREADS) sm.conv_t[i] = p.w.loc_conv_t[i];
+    for (int i = tid; i < 64 * d.A; i += D2_THREADS) {
+      const int cj = i / d.A, a_ = i - cj * d.A, c = cj >> 5, j = cj & 31;
+      float g = 0.f;
+      if (j < D2_LOC_K)
+#pragma unroll 8
+        for (int f = 0; f < D2_LOC_F; ++f) g = fmaf(__ldg(p.w.loc_dense + f * d.A + a_), __ldg(p.w.loc_conv_t + (c * D2_LOC_K + j) * D2_LOC_F + f), g);
+      __nv_bfloat16 hi, lo;
+      tc::split_bf16(g, hi, lo);
+      const uint32_t off = (uint32_t)((a_ >> 6) * 8192) + tc::sw128_off(cj, a_ & 63);
+      *reinterpret_cast<__nv_bfloat16*>(sm.gfT + off) = hi;
+      *reinterpret_cast<__nv_bfloat16*>(sm.gfT + 16384 + off) = lo;
+    }
 #pragma unroll 1
-  for (int i = tid; i < d.A * D2_LOC_F; i += D2_THREADS) {
-    const float v = p.w.loc_dense[i];           // [f][a]
-    sm.dense[i] = v;
-    sm.dense_af[(i % d.A) * 36 + i / d.A] = v;  // [a][f]
+    for (int i = tid; i < 16 * 64; i += D2_THREADS) {
+      const int r = i >> 6, k = i & 63;
+      *reinterpret_cast<__nv_bfloat16*>(sm.ident + tc::sw128_off(r, k)) = __float2bfloat16_rn(r == k ? 1.f : 0.f);
+    }
+    tc::fence_proxy_async();
+  } else {
+#pragma unroll 1
+    for (int i = tid; i < 2 * D2_LOC_K * D2_LOC_F; i += D2_THREADS) sm.conv_t[i] = p.w.loc_conv_t[i];
+#pragma unroll 1
+    for (int i = tid; i < d.A * D2_LOC_F; i += D2_THREADS) {
+      const float v = p.w.loc_dense[i];           // [f][a]
+      sm.dense[i] = v;
+      sm.dense_af[(i % d.A) * 36 + i / d.A] = v;  // [a][f]
+    }
   }
 #pragma unroll 1
   for (int i = tid; i < d.A; i += D2_THREADS) sm.v[i] = p.w.v[i];
 #pragma unroll 1
   for (int i = tid; i < 8 * D2_BP; i += D2_THREADS) { sm.dc_att[i] = 0.f; sm.dc_dec[i] = 0.f; }
   tg::Pipe pipe;
-  tg::pipe_init(pipe, sm.bars, sm.stages, D2_STAGES, d.npass, sm.tmem_slot);
+  // 512 tensor-memory columns: [0,256) GEMM accumulators (H of the attention phase aliases them), [256,384) d pm, [384,448) Y
+  tg::pipe_init<512>(pipe, sm.bars, sm.stages, D2_STAGES, d.npass, sm.tmem_slot);
+  if (tid == 0) {
+    tc::mbar_init(sm.bars + 2 * D2_STAGES + 1, 1);
+    tc::mbar_init(sm.bars + 2 * D2_STAGES + 2, 1);
+    tc::fence_barrier_init();
+  }
+  tc::tc_fence_before();
   tc::cluster_sync();
+  tc::tc_fence_after();
+  const uint32_t tmem_p = pipe.tmem + 256u;   // d pm [0,128) and Y [128,192) of the tensor-core attention path: live for the whole kernel
+  AttTcState stt{0u, false};
 
   GridBar bar{wk.barrier, wk.barrier + 1, gridDim.x, 0u};
   long long prof_last = clock64();
@@ -213,7 +248,11 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
     if (!(alive = bar.sync(fail, false))) break;
     prof_mark(0);
     // ---- A: attention backward of frame t
-    attention_bwd_phase(d, tp, wk, sm, scratch, att_active, att_b, att_part, S, t, T, have_att_next, p.KattT, p.KdecT, acc, p.prof, &prof_last);
+    if (p.tc_att)
+      attention_bwd_phase_tc(d, tp, wk, sm, base, att_active, att_b, att_part, S, t, T, have_att_next, pipe.tmem, tmem_p, acc.dv, stt, fail,
+                             p.prof, &prof_last);
+    else
+      attention_bwd_phase(d, tp, wk, sm, scratch, att_active, att_b, att_part, S, t, T, have_att_next, p.KattT, p.KdecT, acc, p.prof, &prof_last);
     if (!(alive = bar.sync(fail, false))) break;
     prof_mark(1);
     // ---- P: attention cell of frame t, decoder cell of frame t-1
@@ -225,26 +264,58 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
 
   // ---- per-CTA partials of the small attention weight gradients, bias gradients
   {
-    float* sp = wk.small_partial + (size_t)blockIdx.x * (d.A * 32 + 2 * D2_LOC_K * D2_LOC_F + d.A);
+    float* sp = wk.small_partial + (size_t)blockIdx.x * (p.tc_att ? d.A * 64 + d.A : d.A * 32 + 2 * D2_LOC_K * D2_LOC_F + d.A);
     const int a4 = lane * 4, f4 = warp * 4;
-    if (a4 < d.A)
-#pragma unroll
-      for (int i = 0; i < 16; ++i) sp[(a4 + (i >> 2)) * 32 + f4 + (i & 3)] = acc.wd[i];            // [a][f] = location_dense.weight layout
     float* spc = sp + d.A * 32;
-    const int ff = (tid & 7) * 4, cj0 = tid >> 3;
+    if (p.tc_att) {
+      // Y[a][(c,j)] (lanes = attention dims) -> this CTA's partial; d pm (lanes = positions) -> its rows of the gradient
+      const bool has = att_active && stt.issued;
+      const int lane0 = 32 * (warp & 3), half = warp >> 2, row = lane0 + lane;
+      float v[32];
+      tc::tc_fence_after();
+      if (has) { tc::tmem_ld32(tmem_p + ((uint32_t)lane0 << 16) + 128u + 32u * half, v); tc::tmem_ld_wait(); }
+      else {
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const int cj = cj0 + 32 * h;
-      if (cj >= 2 * D2_LOC_K) continue;
-      const int c = cj / D2_LOC_K, j = cj - c * D2_LOC_K;
+        for (int i = 0; i < 32; ++i) v[i] = 0.f;
+      }
+      if (row < d.A) {
 #pragma unroll
-      for (int i = 0; i < 4; ++i) spc[((ff + i) * 2 + c) * D2_LOC_K + j] = acc.wc[4 * h + i];       // [f][c][j] = location_conv.weight layout
+        for (int i = 0; i < 8; ++i)
+          *reinterpret_cast<float4*>(sp + (size_t)row * 64 + 32 * half + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+      }
+      if (has) {
+        const int Lc = (d.L + S - 1) / S, l0 = min(d.L, att_part * Lc), nl = min(d.L, l0 + Lc) - l0;
+#pragma unroll 1
+        for (int cc = 0; cc < 2; ++cc) {
+          tc::tmem_ld32(tmem_p + ((uint32_t)lane0 << 16) + 64u * half + 32u * cc, v);
+          tc::tmem_ld_wait();
+          if (row < nl) {
+            float4* dst = reinterpret_cast<float4*>(wk.dpm + ((size_t)att_b * d.L + l0 + row) * d.A + 64 * half + 32 * cc);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          }
+        }
+      }
+      tc::tc_fence_before();
+    } else {
+      if (a4 < d.A)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) sp[(a4 + (i >> 2)) * 32 + f4 + (i & 3)] = acc.wd[i];            // [a][f] = location_dense.weight layout
+      const int ff = (tid & 7) * 4, cj0 = tid >> 3;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int cj = cj0 + 32 * h;
+        if (cj >= 2 * D2_LOC_K) continue;
+        const int c = cj / D2_LOC_K, j = cj - c * D2_LOC_K;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) spc[((ff + i) * 2 + c) * D2_LOC_K + j] = acc.wc[4 * h + i];       // [f][c][j] = location_conv.weight layout
+      }
     }
     __syncthreads();
     float* red = scratch;   // [8][A]
     if (a4 < d.A) *reinterpret_cast<float4*>(red + warp * d.A + a4) = make_float4(acc.dv[0], acc.dv[1], acc.dv[2], acc.dv[3]);
     __syncthreads();
-    float* spv = spc + 2 * D2_LOC_K * D2_LOC_F;
+    float* spv = p.tc_att ? sp + d.A * 64 : spc + 2 * D2_LOC_K * D2_LOC_F;
 #pragma unroll 1
     for (int a_ = tid; a_ < d.A; a_ += D2_THREADS) {
       float s = 0.f;
@@ -267,7 +338,9 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
   }
   tc::tc_fence_before();
   tc::cluster_sync();
-  if ((tid >> 5) == 1) tc::tmem_dealloc<TG_TMEM_COLS>(pipe.tmem);
+  if ((tid >> 5) == 1) {
+    tc::tmem_dealloc<512>(pipe.tmem);
+  }
 }
 
 }  // namespace
@@ -276,11 +349,27 @@ int db_parts(const D2Dims& d) {
   const int grid = (d.H / 32) * D2_CLUSTER;
   return (d.B * 4 <= grid) ? 4 : ((d.B * 2 <= grid) ? 2 : 1);
 }
-size_t db_small_floats(const D2Dims& d) { return (size_t)d.A * 32 + 2 * D2_LOC_K * D2_LOC_F + d.A; }
+// The tensor-core attention backward needs the taped pre-tanh argument, att_dim == 128 (the M of the Y contraction) and slices of at
+// most 128 positions (TMEM lanes).  T2B200_BWD_ATT=cuda forces the CUDA-core version (A/B runs, tests of both).
+bool db_tc_att(const D2Dims& d, bool have_xloc) {
+  const char* e = getenv("T2B200_BWD_ATT");
+  if (e && e[0] == 'c') return false;
+  const int S = db_parts(d), Lc = (d.L + S - 1) / S;
+  return have_xloc && d.A == 128 && Lc <= 128 && d.EF % 4 == 0;
+}
+// per-CTA partial of the small attention gradients: tensor-core path Y[A][64] | dv[A]; CUDA-core path dWd[A][32] | dWc[32][2][31] | dv[A]
+size_t db_small_floats(const D2Dims& d, bool tc_att) {
+  return tc_att ? (size_t)d.A * 64 + d.A : (size_t)d.A * 32 + 2 * D2_LOC_K * D2_LOC_F + d.A;
+}
 
 static size_t att_bwd_scratch_floats_host(int L, int S, int A, int EF) {
   const int Lc = (L + S - 1) / S, Lh4 = (Lc + 30 + 3) & ~3, Lc4 = (Lc + 3) & ~3;
   return (size_t)A + 2 * Lh4 + (size_t)Lc * 36 + EF + 3 * Lc4 + 64 + 8 + 8 * (size_t)A + (size_t)Lc * (A + 4) + (size_t)(Lc + 30) * 36 + (size_t)(Lc + 30) * 64;
+}
+
+static size_t att_tc_scratch_bytes_host(int L, int S, int A, int EF) {
+  const int Lc = (L + S - 1) / S, Lh4 = (Lc + 30 + 3) & ~3, Lc4 = (Lc + 3) & ~3;
+  return 65536 + 32768 + 4 * ((size_t)A + 2 * Lh4 + EF + 3 * Lc4 + 64 + 8 + 8 * (size_t)A + 2 * Lh4);
 }
 
 int db_launch(const D2Dims& d, int T, int KattT, int KdecT, const DBWeights& w, const DBTape& tp, const DBWork& wk, const DBMaps& maps,
@@ -292,8 +381,10 @@ int db_launch(const D2Dims& d, int T, int KattT, int KdecT, const DBWeights& w, 
   T2_REQUIRE(grid == 128, T2_ERR_UNSUPPORTED, "decoder backward: laid out for 128 CTAs (att_rnn_dim = 1024), got %d", grid);
   const int S = db_parts(d);
   const size_t ring = (size_t)D2_STAGES * TG_STAGE_BYTES;
-  T2_REQUIRE(att_bwd_scratch_floats_host(d.L, S, d.A, d.EF) * 4 <= ring, T2_ERR_UNSUPPORTED,
-             "decoder backward: L=%d too long for the attention scratch", d.L);
+  const bool tc_att = db_tc_att(d, tp.xloc != nullptr);
+  T2_REQUIRE((tc_att ? att_tc_scratch_bytes_host(d.L, S, d.A, d.EF) : att_bwd_scratch_floats_host(d.L, S, d.A, d.EF) * 4) <= ring,
+             T2_ERR_UNSUPPORTED, "decoder backward: L=%d too long for the attention scratch", d.L);
+  T2_REQUIRE(!tc_att || 2 * D2_LOC_K * 128 * 4 <= TG_M * TG_PART_LD * 4, T2_ERR_UNSUPPORTED, "decoder backward: H staging");
   T2_REQUIRE((size_t)(64 * 33 + 16 + d.A * D2_BP + d.A * 8) * 4 <= ring, T2_ERR_UNSUPPORTED, "decoder backward: pointwise staging");
   const size_t smem = bsmem_bytes(d);
   T2_REQUIRE(smem <= 227 * 1024, T2_ERR_UNSUPPORTED, "decoder backward: %zu B shared memory", smem);
@@ -313,7 +404,7 @@ int db_launch(const D2Dims& d, int T, int KattT, int KdecT, const DBWeights& w, 
   T2_REQUIRE(nclusters * D2_CLUSTER >= grid, T2_ERR_UNSUPPORTED, "decoder backward: only %d clusters co-resident, %d needed", nclusters,
              grid / D2_CLUSTER);
   T2_CHECK_CUDA(cudaMemsetAsync(wk.barrier, 0, 4 * sizeof(unsigned), st));
-  DBParams p{d, T, KattT, KdecT, S, w, tp, wk, prof};
+  DBParams p{d, T, KattT, KdecT, S, tc_att ? 1 : 0, w, tp, wk, prof};
   T2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, decoder_bwd_kernel, maps, p));
   return T2_OK;
 }

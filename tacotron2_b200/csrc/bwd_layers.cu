@@ -219,6 +219,30 @@ int partial_sum_launch(const float* partial, int nparts, int n, float* out, cuda
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }
+// Small attention weight gradients from the utterance-summed Y[a][(c,j)] (column c*32 + j) of the tensor-core attention backward:
+//   d location_dense[a][f]   = sum_{c,j} Y[a][(c,j)] Wc[c][j][f]        d location_conv[f][c][j] = sum_a Wd[a][f] Y[a][(c,j)]
+// conv_t = location_conv as [c][j][f], dense_t = location_dense as [f][a]
+__global__ void att_small_finish_kernel(const float* __restrict__ Y, const float* __restrict__ conv_t, const float* __restrict__ dense_t, int A,
+                                        float* __restrict__ g_dense, float* __restrict__ g_conv) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < A * 32) {
+    const int a = i / 32, f = i % 32;
+    float acc = 0.f;
+    for (int c = 0; c < 2; ++c)
+      for (int j = 0; j < 31; ++j) acc = fmaf(Y[(size_t)a * 64 + c * 32 + j], conv_t[(c * 31 + j) * 32 + f], acc);
+    g_dense[i] = acc;
+  } else if (i < A * 32 + 32 * 2 * 31) {
+    const int k = i - A * 32, f = k / 62, c = (k / 31) % 2, j = k % 31;
+    float acc = 0.f;
+    for (int a = 0; a < A; ++a) acc = fmaf(dense_t[(size_t)f * A + a], Y[(size_t)a * 64 + c * 32 + j], acc);
+    g_conv[k] = acc;
+  }
+}
+int att_small_finish_launch(const float* Y, const float* conv_t, const float* dense_t, int A, float* g_dense, float* g_conv, cudaStream_t st) {
+  att_small_finish_kernel<<<(A * 32 + 32 * 2 * 31 + 127) / 128, 128, 0, st>>>(Y, conv_t, dense_t, A, g_dense, g_conv);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
+}
 int copy2_launch(const float* src, float* a, float* b, int n, cudaStream_t st) {
   copy2_kernel<<<(n + 255) / 256, 256, 0, st>>>(src, a, b, n);
   T2_CHECK_CUDA(cudaGetLastError());

@@ -144,6 +144,27 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
 __host__ __device__ constexpr uint32_t idesc_bf16_f32(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
+// The same with an MN-major A operand (bit 15, UMMA::InstrDescriptor::a_major_): A is read from a tile whose M index is the
+// contiguous one -- the transposed view of a K-major tile that lies in shared memory.
+__host__ __device__ constexpr uint32_t idesc_bf16_f32_amn(int M, int N) { return idesc_bf16_f32(M, N) | (1u << 15); }
+// MN-major operand, 128-byte swizzle (canonical layout ((8,8,m),(8,k)):((1,8,LBO),(64,SBO)) in bf16 elements, cute make_umma_desc<Major::MN>):
+// 64 consecutive M (or N) indices are the 128 contiguous bytes of one row, 8 consecutive K indices are 8 rows (one 1024-byte swizzle
+// atom); the next 64 M indices start lbo_bytes further, the next 8 K indices sbo_bytes further.  Byte for byte this is the memory image
+// of K-major sw128 tiles [K rows][64 M] laid side by side (the swizzle is a function of the address only), so a tile written once can
+// be contracted over either of its two indices.
+__device__ __forceinline__ uint64_t smem_desc_sw128_mn(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// byte offset of element (row r, k) of a K-major sw128 bf16 tile with 128-byte rows (k < 64): what TMA SWIZZLE_128B would have written
+__device__ __forceinline__ uint32_t sw128_off(int r, int k) {
+  return (uint32_t)(((r >> 3) << 10) + ((r & 7) << 7) + ((((k >> 3) & 7) ^ (r & 7)) << 4) + ((k & 7) << 1));
+}
 // D[tmem] (+)= A[smem] * B[smem]^T; single thread issues on behalf of the CTA.
 __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
   asm volatile(

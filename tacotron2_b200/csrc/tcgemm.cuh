@@ -37,6 +37,7 @@ struct XSrc {  // where the x (activation) K-blocks come from: blocks [0,split) 
   int split;
 };
 
+template <int COLS = TG_TMEM_COLS>   // tensor-memory columns to allocate (a CTA allocates once: the permit is relinquished right after)
 __device__ __forceinline__ void pipe_init(Pipe& p, uint64_t* bars, uint8_t* stages, int nstages, int npass, uint32_t* tmem_slot) {
   p.full = bars; p.empty = bars + nstages; p.accum = bars + 2 * nstages;
   p.stages = stages; p.nstages = nstages; p.npass = npass;
@@ -46,7 +47,7 @@ __device__ __forceinline__ void pipe_init(Pipe& p, uint64_t* bars, uint8_t* stag
     tc::mbar_init(p.accum, 1);
     tc::fence_barrier_init();
   }
-  if ((threadIdx.x >> 5) == 1) tc::tmem_alloc<TG_TMEM_COLS>(tmem_slot);  // warp 1 owns alloc + dealloc
+  if ((threadIdx.x >> 5) == 1) tc::tmem_alloc<COLS>(tmem_slot);  // warp 1 owns alloc + dealloc
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();

@@ -85,7 +85,8 @@ int db_launch(const D2Dims& d, int T, int KattT, int KdecT, const DBWeights& w, 
 struct t2_ctx;
 int decode_proj_bulk(t2_ctx* c, const __nv_bfloat16* xdec_tape, int B, int T, float* mels, float* gates, float* tmp, cudaStream_t st);
 int db_parts(const D2Dims& d);        // S: CTAs per utterance in the attention backward
-size_t db_small_floats(const D2Dims& d);
+bool db_tc_att(const D2Dims& d, bool have_xloc);   // attention backward contractions on tcgen05 (else CUDA cores)
+size_t db_small_floats(const D2Dims& d, bool tc_att);
 
 // ---- BiLSTM backward (bwd_layers.cu) ------------------------------------------------------------------------------
 // sav [B][L][2][5][Hh] (i,f,g,o,c) from the train-mode forward; d_out [B][L][2Hh]; dgates out [B][L][2][4Hh] (zeros at t >= len)
@@ -103,6 +104,7 @@ int build_dproj_launch(const float* d_mels, const float* d_gates, int B, int T, 
 int dq_sumT_launch(const float* dq, int T, int S, int A, int B, __nv_bfloat16* out, cudaStream_t st);
 int partial_sum_launch(const float* partial, int nparts, int n, float* out, cudaStream_t st);
 int copy2_launch(const float* src, float* a, float* b, int n, cudaStream_t st);
+int att_small_finish_launch(const float* Y, const float* conv_t, const float* dense_t, int A, float* g_dense, float* g_conv, cudaStream_t st);
 int prenet_d2_launch(const float* dpre, const __nv_bfloat16* tfp, int B, int T, int P, float scale, float* d2, cudaStream_t st);
 int prenet_d1_launch(const float* dp1, const float* p1, long long n, float scale, float* d1, cudaStream_t st);
 int prenet_xT_launch(const float* mel_target, int B, int T, int M, int Np, __nv_bfloat16* xT, cudaStream_t st);

@@ -298,7 +298,7 @@ int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const uns
   const long long TB = (long long)T * D2_BP, TB1 = (long long)(T + 1) * D2_BP;
   const int Tp = round8(T);
   const int Nn = T * B, Np = round8(Nn);
-  const int nsmall = (int)db_small_floats(d);
+  const int nsmall = (int)std::max(db_small_floats(d, true), db_small_floats(d, false));
   // ---- workspace
   void* scratch = wa.take<char>(bn_scratch_bytes(std::max(M, 128)));
   __nv_bfloat16* dP = wa.take<__nv_bfloat16>((size_t)2 * TB * PROJ_LD);
@@ -399,10 +399,18 @@ int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const uns
   timing_end(c, 1, st);
 
   // ---- small attention weights, biases
-  RC(partial_sum_launch(small_partial, 128, nsmall, small_sum, st));
-  RC(copy2_launch(small_sum, g_ldense, nullptr, A * 32, st));
-  RC(copy2_launch(small_sum + A * 32, g_lconv, nullptr, 2 * 31 * 32, st));
-  RC(copy2_launch(small_sum + A * 32 + 2 * 31 * 32, g_v, nullptr, A, st));
+  if (db_tc_att(d, t.xloc != nullptr)) {
+    const int ns = (int)db_small_floats(d, true);
+    RC(partial_sum_launch(small_partial, 128, ns, small_sum, st));
+    RC(att_small_finish_launch(small_sum, c->loc_conv_t, c->loc_dense_t, A, g_ldense, g_lconv, st));
+    RC(copy2_launch(small_sum + A * 64, g_v, nullptr, A, st));
+  } else {
+    const int ns = (int)db_small_floats(d, false);
+    RC(partial_sum_launch(small_partial, 128, ns, small_sum, st));
+    RC(copy2_launch(small_sum, g_ldense, nullptr, A * 32, st));
+    RC(copy2_launch(small_sum + A * 32, g_lconv, nullptr, 2 * 31 * 32, st));
+    RC(copy2_launch(small_sum + A * 32 + 2 * 31 * 32, g_v, nullptr, A, st));
+  }
   RC(copy2_launch(dbias, g_att_bi, g_att_bh, 4 * H, st));
   RC(copy2_launch(dbias + 4 * H, g_dec_bi, g_dec_bh, 4 * R, st));
 
