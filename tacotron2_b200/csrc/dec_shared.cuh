@@ -8,6 +8,9 @@
 #ifndef D2_SYNC
 #define D2_SYNC() __syncthreads()
 #endif
+#ifndef D2_LDW
+#define D2_LDW(p) __ldg(p)   // weight-row load of the dense layers (decoder_ar.cu: without L1 allocation)
+#endif
 
 namespace {
 
@@ -34,7 +37,7 @@ __device__ __noinline__ void rows_dot2(const float* __restrict__ W, int ldw, int
     for (int k = lane; k < K4; k += 32) {
       const float4 xa = XG ? __ldcg(reinterpret_cast<const float4*>(x0) + k) : *reinterpret_cast<const float4*>(x0 + 4 * k);
       const float4 xb = XG ? __ldcg(reinterpret_cast<const float4*>(x1) + k) : *reinterpret_cast<const float4*>(x1 + 4 * k);
-      const float4 wv[4] = {__ldg(w0 + k), __ldg(w1 + k), __ldg(w2 + k), __ldg(w3 + k)};
+      const float4 wv[4] = {D2_LDW(w0 + k), D2_LDW(w1 + k), D2_LDW(w2 + k), D2_LDW(w3 + k)};
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         a0[i] = fmaf(wv[i].x, xa.x, a0[i]); a0[i] = fmaf(wv[i].y, xa.y, a0[i]); a0[i] = fmaf(wv[i].z, xa.z, a0[i]); a0[i] = fmaf(wv[i].w, xa.w, a0[i]);
@@ -72,7 +75,7 @@ __device__ __noinline__ void rows_short(const float* __restrict__ W, int ldw, in
       for (int k = 0; k < NK; ++k) {
         const int kk = lane + 32 * k;
         const float4* wp = reinterpret_cast<const float4*>(W + (ptrdiff_t)min(r + i, re - 1) * ldw) + kk;
-        wv[i][k] = kk < K4 ? (WS ? *wp : __ldg(wp)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        wv[i][k] = kk < K4 ? (WS ? *wp : D2_LDW(wp)) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
 #pragma unroll
     for (int i = 0; i < NR; ++i) {

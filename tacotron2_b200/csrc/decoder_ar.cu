@@ -17,6 +17,15 @@
 //     tcgen05.ld.  No shared or global memory holds a location term any more (round 1: 6.5 MB per frame through L2 and 7.3 us of
 //     CUDA-core work beside the decoder GEMM), and the stage ring is never used as scratch, which is what lets the stream run on.
 #include "decoder.cuh"
+#ifndef AR_NOALLOC
+#define AR_NOALLOC 0      // streamed weight / memory rows are loaded without allocating in the 28 KB L1
+#endif
+#if AR_NOALLOC
+#define AR_LDW(p) ldg_stream4(p)
+#else
+#define AR_LDW(p) __ldg(p)
+#endif
+#define D2_LDW(p) AR_LDW(p)
 #define D2_SYNC() asm volatile("bar.sync 1, 256;" ::: "memory")
 #include "dec_shared.cuh"
 
@@ -29,11 +38,23 @@
 #define AR_COL_THI 384u    // Toeplitz operand, hi plane: 128 positions x 64 taps bf16 = 32 columns
 #define AR_COL_TLO 416u    // lo plane
 #define AR_MAX_ENT 40
+#ifndef AR_TANH4
+#define AR_TANH4 1        // energy step: four tanh share one reciprocal
+#endif
+#ifndef AR_CTXPF
+#define AR_CTXPF 1        // context: first memory rows requested before the softmax, 16 loads in flight per thread
+#endif
+#ifndef AR_LEAN
+#define AR_LEAN 1         // ex2 / rcp .approx.ftz directly (no range fix-up code), Toeplitz planes split per warp, idle producer sleeps
+#endif
+#ifndef AR_XRED
+#define AR_XRED 1         // dense-layer warp reductions by value halving (16 shuffles for 16 sums instead of 80)
+#endif
 
 namespace {
 
 struct KbEnt { unsigned char gemm, kb, gate, flags; };   // flags: 1 first block of its accumulator, 2 last, 4 belongs to frame t+1
-enum { G_X = 0, G_Q = 1, G_C = 2, G_R = 3 };
+enum { G_X = 0, G_Q = 1, G_C = 2, G_R = 3, G_RP = 4 };   // G_RP: the R barrier of the previous frame
 
 struct ArSmem {
   uint8_t* stages;
@@ -80,7 +101,7 @@ __device__ __forceinline__ ArSmem ar_carve(uint8_t* base, const D2Dims& d) {
   return s;
 }
 // barrier slots
-enum { B_FULL = 0, B_EMPTY = AR_STAGES, B_ACC_ATT = 2 * AR_STAGES, B_ACC_DEC, B_LOC, B_RV, B_E, B_MEL, B_P1, B_W1, B_G, B_FIN, B_RV2 };
+enum { B_FULL = 0, B_EMPTY = AR_STAGES, B_ACC_ATT = 2 * AR_STAGES, B_ACC_DEC, B_LOC, B_RV, B_E, B_MEL, B_P1, B_W1, B_G, B_FIN };
 
 __device__ __forceinline__ void wsync() { D2_SYNC(); }
 
@@ -116,6 +137,21 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* r) {
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
+// ------------------------------------------------------------------------------------------ lean math
+// __expf / __fdividef carry range fix-up code (FSETP + two FMUL per call); the arguments here never need it.
+__device__ __forceinline__ float ex2_ftz(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rcp_ftz(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+#if AR_LEAN
+__device__ __forceinline__ float ar_sigmoid(float x) { return rcp_ftz(1.0f + ex2_ftz(-1.4426950408889634f * x)); }
+__device__ __forceinline__ float ar_tanh(float x) {
+  const float t = ex2_ftz(-2.8853900817779268f * fabsf(x));
+  return copysignf((1.0f - t) * rcp_ftz(1.0f + t), x);
+}
+#else
+__device__ __forceinline__ float ar_sigmoid(float x) { return sigmoid_fast(x); }
+__device__ __forceinline__ float ar_tanh(float x) { return tanh_fast(x); }
+#endif
+
 // K-block classes by the data the columns hold (decoder.cuh: x_att = [prenet | ctx | att_h], x_dec = [att_h | ctx | controls | rnn_h])
 __host__ __device__ inline int att_class(const D2Dims& d, int kb) {   // 0 prenet_t (gate X), 1 ctx_{t-1} (gate C of t-1), 2 att_h_{t-1} (gate Q of t-1)
   const int c0 = kb * TG_BK;
@@ -131,7 +167,7 @@ __host__ __device__ inline int dec_class(const D2Dims& d, int kb) {   // 0 att_h
 }
 
 // The K-block program of CTA `rank`, in issue order (see the file comment).  Returns the entry count.
-__host__ __device__ inline int build_program(const D2Dims& d, int rank, KbEnt* out) {
+__host__ __device__ inline int build_program(const D2Dims& d, int rank, KbEnt* out, bool legacy_order = false) {
   const int nka = d.KattP / TG_BK, nkd = d.KdecP / TG_BK;
   int n = 0;
   auto emit = [&](int gemm, int cls, int gate, int next) {
@@ -141,123 +177,90 @@ __host__ __device__ inline int build_program(const D2Dims& d, int rank, KbEnt* o
         ++n;
       }
   };
-  emit(0, 0, G_X, 0);   // att.P(t)
+  if (legacy_order) {
+    emit(0, 0, G_X, 0);   // att.P(t)
+    const int last_att = n - 1;
+    emit(1, 0, G_Q, 0);   // dec.A(t)
+    const int first_att = n;
+    emit(0, 2, G_Q, 1);   // att.H(t+1)
+    emit(1, 1, G_C, 0);   // dec.C(t)
+    const int last_dec = n - 1;
+    emit(0, 1, G_C, 1);   // att.C(t+1)
+    const int first_dec = n;
+    emit(1, 2, G_R, 1);   // dec.R(t+1)
+    if (n <= AR_MAX_ENT && last_att >= 0 && first_att < n && last_dec > last_att && first_dec < n) {
+      out[last_att].flags |= 2; out[first_att].flags |= 1; out[last_dec].flags |= 2; out[first_dec].flags |= 1;
+    }
+    return n;
+  }
+  // The background K-blocks are placed in the two windows in which the workers read little from L2 (attention-LSTM tail after X,
+  // decoder-LSTM tail after C); the windows of the context sum (after Q) and of the output stage (after R) stay as quiet as the
+  // dependencies allow, because the SM's L2 ingress is what the CUDA-core loads of those phases and the weight stream share:
+  //   after X(t-1): att.P(t) [on the chain], dec.R(t) (rnn_h of frame t-1, published at R(t-1))
+  //   after Q(t):   dec.A(t)                                   (must be in the accumulator before the context blocks close it)
+  //   after C(t):   dec.C(t) [on the chain], att.H(t+1) (att_h of frame t), att.C(t+1)
+  //   after R(t):   nothing -- the next entry, att.P(t+1), waits for X(t) with its weights already in shared memory
+  emit(0, 0, G_X, 0);    // att.P(t)
   const int last_att = n - 1;
-  emit(1, 0, G_Q, 0);   // dec.A(t)
-  const int first_att = n;
-  emit(0, 2, G_Q, 1);   // att.H(t+1)
-  emit(1, 1, G_C, 0);   // dec.C(t)
-  const int last_dec = n - 1;
-  emit(0, 1, G_C, 1);   // att.C(t+1)
   const int first_dec = n;
-  emit(1, 2, G_R, 1);   // dec.R(t+1)
-  if (n <= AR_MAX_ENT && last_att >= 0 && first_att < n && last_dec > last_att && first_dec < n) {
+  emit(1, 2, G_RP, 0);   // dec.R(t)
+  emit(1, 0, G_Q, 0);    // dec.A(t)
+  emit(1, 1, G_C, 0);    // dec.C(t)
+  const int last_dec = n - 1;
+  const int first_att = n;
+  emit(0, 2, G_Q, 1);    // att.H(t+1)
+  emit(0, 1, G_C, 1);    // att.C(t+1)
+  if (n <= AR_MAX_ENT && last_att >= 0 && first_att < n && last_dec > first_dec && first_dec < n) {
     out[last_att].flags |= 2; out[first_att].flags |= 1; out[last_dec].flags |= 2; out[first_dec].flags |= 1;
   }
   return n;
 }
 
 // ------------------------------------------------------------------------------------------ grid barrier (workers only)
-// One arrival word per CTA instead of one counter for the grid: 128 CTAs adding to the same L2 word serialise (~27 cycles per
-// atomic: 1.8 us before the last arrival is even visible); here an arrival is a plain release store of the epoch to the CTA's own
-// word and a waiter's warp 0 reads all 128 words (four 128-byte lines, 16 bytes per lane) until every one has reached the epoch.
+// One 64-bit word: the low half counts arrivals (release add by thread 0 of every CTA, acquire poll; bit 31 = abort), the high half
+// counts the utterances whose stop gate has fired -- it is added with the arrival at the X barrier and read with the poll, so the
+// stop check (model/tacotron2.py:321-322) costs no L2 round trip of its own.  Measured alternatives (profiles/r02_v2_ar_barrier*.log):
+// one arrival word per CTA polled by a warp +1.5 us per barrier, one add per cluster after a shared-memory count +0.3 us.
 struct ArGridBar {
-  unsigned* flags;        // [gridDim.x] arrival epochs (mode 1)
-  unsigned* ctr;          // arrival counter (mode 0)
-  unsigned* abort_flag;   // set by any CTA that failed; polled with the flags
+  unsigned* ctr;          // the 64-bit word (8-byte aligned)
+  unsigned* abort_flag;   // host-visible copy of the abort state
   unsigned nblocks, epoch;
-  int* ok_s;   // shared word
-  int mode;    // 0: one counter (release add + acquire poll by thread 0), 1: one word per CTA, polled by warp 0,
-               // 2: as 0 but one add per CLUSTER: the CTAs of a cluster count on a shared-memory word of rank 0, the last one adds
-  unsigned* cl_ctr;   // mode 2: this CTA's cluster counter word (shared memory; rank 0's copy is the one used)
+  int* ok_s;              // shared word
   __device__ void arrive(bool fail, volatile unsigned* ctl) {
     asm volatile("fence.proxy.async.global;" ::: "memory");   // operands written with generic stores are read by TMA after the barrier
     if (fail) ctl[2] = 1u;
     wsync();
     ++epoch;
     if (threadIdx.x == 0) {
-      if (mode == 0) {
-        if (ctl[2] != 0u) { atomicExch(abort_flag, 1u); atomicOr(ctr, 0x80000000u); }
-        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
-      } else if (mode == 2) {
-        if (ctl[2] != 0u) { atomicExch(abort_flag, 1u); atomicOr(ctr, 0x80000000u); }
-        unsigned old;
-        asm volatile("atom.acq_rel.cluster.shared::cluster.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(tc::mapa(tc::smem_u32(cl_ctr), 0u)) : "memory");
-        if ((old & (D2_CLUSTER - 1)) == D2_CLUSTER - 1) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
-      } else {
-        if (ctl[2] != 0u) atomicExch(abort_flag, 1u);
-        asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(flags + blockIdx.x), "r"(epoch) : "memory");
-      }
+      if (ctl[2] != 0u) { atomicExch(abort_flag, 1u); atomicOr(ctr, 0x80000000u); }
+      const unsigned fired = ctl[9];   // stop gates that fired in this CTA since its last arrival (output stage)
+      ctl[9] = 0u;
+      asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(ctr), "l"(1ull | ((unsigned long long)fired << 32)) : "memory");
     }
   }
-  // returns false when the grid aborts; on success thread 0 opens the producer's next gate (ctl[0])
+  // returns false when the grid aborts; on success thread 0 opens the producer's next gate (ctl[0]) and leaves the done count in ctl[10]
   __device__ bool wait(volatile unsigned* ctl) {
-    if (mode == 0 || mode == 2) {
-      if (threadIdx.x == 0) {
-        const unsigned target = mode == 2 ? epoch * (nblocks / D2_CLUSTER) : epoch * nblocks;
-        unsigned v;
-        long long spins = 0;
-        while ((((v = ld_acquire_u32(ctr)) & 0x7fffffffu) < target) && !(v & 0x80000000u)) {
-          if (++spins > (1ll << 24)) { atomicExch(abort_flag, 1u); atomicOr(ctr, 0x80000000u); v = 0x80000000u; break; }
-        }
-        const int ok = (v & 0x80000000u) == 0u;
-        *ok_s = ok;
-        if (ok) st_release_cta(ctl, ctl[0] + 1u);
-      }
-    } else if (threadIdx.x < 32) {
-      const unsigned lane = threadIdx.x;
-      const unsigned nq = (nblocks + 3) >> 2;   // 16-byte groups of flags
+    if (threadIdx.x == 0) {
+      const unsigned target = epoch * nblocks;
+      unsigned long long vv;
+      unsigned v;
       long long spins = 0;
-      int ok = 1;
       for (;;) {
-        uint4 f = make_uint4(epoch, epoch, epoch, epoch);
-        if (lane < nq) asm volatile("ld.acquire.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(f.x), "=r"(f.y), "=r"(f.z), "=r"(f.w) : "l"(flags + 4 * lane) : "memory");
-        unsigned ab = 0;
-        if (lane == 0) asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(ab) : "l"(abort_flag) : "memory");
-        const bool here = (int)(f.x - epoch) >= 0 && (int)(f.y - epoch) >= 0 && (int)(f.z - epoch) >= 0 && (int)(f.w - epoch) >= 0;
-        const bool all_here = __all_sync(0xffffffffu, here);
-        const bool aborted = __any_sync(0xffffffffu, ab != 0u);
-        if (aborted) { ok = 0; break; }
-        if (all_here) break;
-        if (++spins > (1ll << 22)) { if (lane == 0) atomicExch(abort_flag, 1u); ok = 0; break; }   // a peer died: never hang the GPU
+        asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(vv) : "l"(ctr) : "memory");
+        v = (unsigned)vv;
+        if ((v & 0x7fffffffu) >= target || (v & 0x80000000u)) break;
+        if (++spins > (1ll << 24)) { atomicExch(abort_flag, 1u); atomicOr(ctr, 0x80000000u); v = 0x80000000u; break; }   // a peer died: never hang the GPU
       }
-      if (lane == 0) {
-        *ok_s = ok;
-        if (ok) st_release_cta(ctl, ctl[0] + 1u);
-      }
+      const int ok = (v & 0x80000000u) == 0u;
+      *ok_s = ok;
+      ctl[10] = (unsigned)(vv >> 32);   // utterances done, as every CTA sees it at this barrier
+      if (ok) st_release_cta(ctl, ctl[0] + 1u);
     }
     wsync();
     return *ok_s != 0;
   }
   __device__ bool sync(bool fail, volatile unsigned* ctl) { arrive(fail, ctl); return wait(ctl); }
 };
-
-// TMEM accumulator columns [col, col+64) -> part[128][TG_PART_LD]; worker warp w reads lanes 32*(w%4).. and columns 32*(w/4)..
-__device__ __forceinline__ void ar_accum_to_smem(uint32_t tmem, uint32_t col, float* part) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int lane0 = 32 * (warp & 3), col0 = 32 * (warp >> 2);
-  float v[32];
-  tc::tmem_ld32(tmem + ((uint32_t)lane0 << 16) + col + col0, v);
-  tc::tmem_ld_wait();
-  float* dst = part + (size_t)(lane0 + lane) * TG_PART_LD + col0;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) *reinterpret_cast<float4*>(dst + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-  tc::tc_fence_before();
-}
-
-// Rendezvous of the worker warps of the four CTAs of a cluster (barrier.cluster would count the role warps too): every CTA's thread 0
-// arrives on all four barriers with release, everybody waits on the local one with acquire.
-__device__ __forceinline__ bool cluster_rendezvous(uint64_t* bar, uint32_t& phase) {
-  wsync();
-  if (threadIdx.x == 0) {
-    const uint32_t a = tc::smem_u32(bar);
-#pragma unroll
-    for (uint32_t r = 0; r < D2_CLUSTER; ++r) tc::mbar_arrive_cluster(tc::mapa(a, r));
-  }
-  const bool ok = tc::mbar_wait_cluster(bar, phase);
-  phase ^= 1u;
-  return ok;
-}
 
 // Split-K exchange of an LSTM gate accumulator, push mode.  Rows [32r, 32r+32) of the 128-row tile belong to cluster rank r, and
 // they are exactly the TMEM lanes worker warps r and r+4 can read: every thread sends its 32 partial sums (one row, 32 utterances)
@@ -304,9 +307,9 @@ __device__ __forceinline__ void ar_lstm_tail(const float* recv, int unit0, const
     const int b = 2 * bp + j;
     const float pi = j ? pre[0].y : pre[0].x, pf = j ? pre[1].y : pre[1].x;
     const float pg = j ? pre[2].y : pre[2].x, po = j ? pre[3].y : pre[3].x;
-    const float si = sigmoid_fast(pi), sf = sigmoid_fast(pf), tg = tanh_fast(pg), so = sigmoid_fast(po);
+    const float si = ar_sigmoid(pi), sf = ar_sigmoid(pf), tg = ar_tanh(pg), so = ar_sigmoid(po);
     const float c = sf * cst[ul * D2_BP + b] + si * tg;
-    float h = so * tanh_fast(c);
+    float h = so * ar_tanh(c);
     if (b < B) cst[ul * D2_BP + b] = c;
     sv[0][j] = si; sv[1][j] = sf; sv[2][j] = tg; sv[3][j] = so; sv[4][j] = c;
     if (hidden_dropout && b < B) {  // nn.Dropout(0.1), train only (model/decoder.py:75,101)
@@ -347,6 +350,70 @@ __device__ __forceinline__ void ar_lstm_tail(const float* recv, int unit0, const
   }
 }
 
+// Sums over the 32 lanes of C values per lane by value halving: at each step a lane keeps one half of its values and receives the
+// partner's partial sums of that half (C - 1 shuffles in total instead of 5 C).  Afterwards lane l holds the total of v[l * C / 32 ...]
+// -- for C = 32: value l in v[0]; for C = 16: value (l >> 1) in v[0] (lane pairs hold the same total).  Fixed order: deterministic.
+template <int C>
+__device__ __forceinline__ void xreduce(float* v) {
+  const int lane = threadIdx.x & 31;
+  int m = 16;
+#pragma unroll
+  for (int c = C; c > 1; c >>= 1, m >>= 1) {
+    const bool upper = (lane & m) != 0;
+#pragma unroll
+    for (int i = 0; i < c / 2; ++i) {
+      const float send = upper ? v[i] : v[i + c / 2], keep = upper ? v[i + c / 2] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, m);
+    }
+  }
+#pragma unroll
+  for (; m > 0; m >>= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], m);
+}
+
+// Short dense layer for the two utterances of a cluster, 8 rows per warp and pass (as rows_short<8, NK, WS> of dec_shared.cuh), with
+// the sixteen sums of a pass reduced by value halving.
+template <int NK, bool WS>
+__device__ __noinline__ void ar_rows8(const float* __restrict__ W, int ldw, int K4, int rb, int re, const float* x0, const float* x1, float* y,
+                                      int ybase, int ys) {
+  const int lane = threadIdx.x & 31;
+  float4 xa[NK], xb[NK];
+#pragma unroll
+  for (int k = 0; k < NK; ++k) {
+    const int kk = lane + 32 * k;
+    xa[k] = kk < K4 ? *reinterpret_cast<const float4*>(x0 + 4 * kk) : make_float4(0.f, 0.f, 0.f, 0.f);
+    xb[k] = kk < K4 ? *reinterpret_cast<const float4*>(x1 + 4 * kk) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+#pragma unroll 1
+  for (int r = rb; r < re; r += 8) {
+    float4 wv[8][NK];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int k = 0; k < NK; ++k) {
+        const int kk = lane + 32 * k;
+        const float4* wp = reinterpret_cast<const float4*>(W + (ptrdiff_t)min(r + i, re - 1) * ldw) + kk;
+        wv[i][k] = kk < K4 ? (WS ? *wp : AR_LDW(wp)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    __syncwarp();   // scheduling fence: every load of the pass is issued before the first dependent FMA (ptxas otherwise interleaves
+                    // them to save registers, which turns one L2 round trip into several)
+    float v[16];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+      for (int k = 0; k < NK; ++k) {
+        a0 = fmaf(wv[i][k].x, xa[k].x, a0); a0 = fmaf(wv[i][k].y, xa[k].y, a0); a0 = fmaf(wv[i][k].z, xa[k].z, a0); a0 = fmaf(wv[i][k].w, xa[k].w, a0);
+        a1 = fmaf(wv[i][k].x, xb[k].x, a1); a1 = fmaf(wv[i][k].y, xb[k].y, a1); a1 = fmaf(wv[i][k].z, xb[k].z, a1); a1 = fmaf(wv[i][k].w, xb[k].w, a1);
+      }
+      v[i] = a0; v[8 + i] = a1;
+    }
+    xreduce<16>(v);
+    const int q = lane >> 1, i = q & 7, j = q >> 3;   // lane pair q holds sum q: row r + (q & 7) of utterance q >> 3
+    if ((lane & 1) == 0 && r + i < re) y[j * ys + r + i - ybase] = v[0];
+  }
+  __syncwarp();
+}
+
 // ------------------------------------------------------------------------------------------ attention
 // Scratch (floats, in `part`): q[A] | qh[8A] | ep[2][128] | red[64] | cred[4*cols]; the weight row has its own buffer (sm.wrow)
 struct ArAtt { float *q_s, *qh, *ep, *red, *cred, *wrow; };
@@ -368,29 +435,61 @@ __host__ __device__ inline size_t ar_att_scratch_floats(int L, int A, int EF, in
 //   T[p][k]      = w   [l0 + p + k - 15]   k = 0..30
 //   T[p][32 + k] = wcum[l0 + p + k - 15]   k = 0..30        (taps 31 and 63 are zero, and so are those columns of G)
 // Worker warp w owns TMEM lanes 32*(w%4)..+31 (= positions) and writes plane w/4 (0 = hi, 1 = lo).
-__device__ __forceinline__ void build_toeplitz_and_issue(const ArSmem& sm, const float* wrow, uint32_t tmem, int l0, int nl, int npass,
-                                                         uint64_t* loc_bar) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int p = 32 * (warp & 3) + lane, plane = warp >> 2;
-  uint32_t r[32];
-  if (p < nl && (plane == 0 || npass == 3)) {
-    const float* a = wrow + l0 + p;       // wrow[15 + l] holds position l: tap k reads wrow[l0 + p + k]
-    const float* c = sm.wcum + l0 + p;
+// The work is cut in two so that each half hides behind a grid barrier of its own (between arrive and wait): `which` 0 = the taps of
+// the previous weights (columns 0..15 of a plane, K steps 0-1 of the contraction), 1 = the taps of the cumulative weights (columns
+// 16..31, K steps 2-3, then the commit that publishes the location term); 2 = both (prologue).
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+        "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void toeplitz_half(const float* src, bool on, int plane, uint32_t taddr) {
+  uint32_t r[16];
+#if AR_LEAN
+  if (on && plane == 0) {   // hi plane: one packed conversion per pair of taps (the plane is uniform over the warp)
 #pragma unroll
     for (int cc = 0; cc < 16; ++cc) {
-      float x0 = a[2 * cc], x1 = (2 * cc + 1 < D2_LOC_K) ? a[2 * cc + 1] : 0.f;
-      float y0 = c[2 * cc], y1 = (2 * cc + 1 < D2_LOC_K) ? c[2 * cc + 1] : 0.f;
-      __nv_bfloat16 h0, l0_, h1, l1, g0, m0, g1, m1;
-      tc::split_bf16(x0, h0, l0_); tc::split_bf16(x1, h1, l1);
-      tc::split_bf16(y0, g0, m0); tc::split_bf16(y1, g1, m1);
-      r[cc] = plane ? pack2_bf16(l0_, l1) : pack2_bf16(h0, h1);
-      r[16 + cc] = plane ? pack2_bf16(m0, m1) : pack2_bf16(g0, g1);
+      const float x0 = src[2 * cc], x1 = (2 * cc + 1 < D2_LOC_K) ? src[2 * cc + 1] : 0.f;
+      const __nv_bfloat162 h = __floats2bfloat162_rn(x0, x1);
+      r[cc] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+  } else if (on) {          // lo plane: x - bf16(x), rounded again
+#pragma unroll
+    for (int cc = 0; cc < 16; ++cc) {
+      const float x0 = src[2 * cc], x1 = (2 * cc + 1 < D2_LOC_K) ? src[2 * cc + 1] : 0.f;
+      const __nv_bfloat162 h = __floats2bfloat162_rn(x0, x1);
+      const uint32_t hb = *reinterpret_cast<const uint32_t*>(&h);
+      const __nv_bfloat162 l = __floats2bfloat162_rn(x0 - __uint_as_float(hb << 16), x1 - __uint_as_float(hb & 0xffff0000u));
+      r[cc] = *reinterpret_cast<const uint32_t*>(&l);
     }
   } else {
+#else
+  if (on) {
 #pragma unroll
-    for (int cc = 0; cc < 32; ++cc) r[cc] = 0u;
+    for (int cc = 0; cc < 16; ++cc) {
+      const float x0 = src[2 * cc], x1 = (2 * cc + 1 < D2_LOC_K) ? src[2 * cc + 1] : 0.f;
+      __nv_bfloat16 h0, l0, h1, l1;
+      tc::split_bf16(x0, h0, l0); tc::split_bf16(x1, h1, l1);
+      r[cc] = plane ? pack2_bf16(l0, l1) : pack2_bf16(h0, h1);
+    }
+  } else {
+#endif
+#pragma unroll
+    for (int cc = 0; cc < 16; ++cc) r[cc] = 0u;
   }
-  tmem_st32(tmem + ((uint32_t)(32 * (warp & 3)) << 16) + (plane ? AR_COL_TLO : AR_COL_THI), r);
+  tmem_st16(taddr, r);
+}
+__device__ __forceinline__ void build_toeplitz_and_issue(const ArSmem& sm, const float* wrow, uint32_t tmem, int l0, int nl, int npass,
+                                                         uint64_t* loc_bar, int which) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int p = 32 * (warp & 3) + lane, plane = warp >> 2;
+  const bool on = p < nl && (plane == 0 || npass == 3);
+  const uint32_t taddr = tmem + ((uint32_t)(32 * (warp & 3)) << 16) + (plane ? AR_COL_TLO : AR_COL_THI);
+  // wrow[15 + l] holds position l: tap k reads wrow[l0 + p + k]
+  if (which != 1) toeplitz_half(wrow + l0 + p, on, plane, taddr);
+  if (which != 0) toeplitz_half(sm.wcum + l0 + p, on, plane, taddr + 16u);
   tmem_st_wait();
   tc::tc_fence_before();
   wsync();
@@ -398,8 +497,9 @@ __device__ __forceinline__ void build_toeplitz_and_issue(const ArSmem& sm, const
     tc::tc_fence_after();
     const uint32_t idesc = tc::idesc_bf16_f32(128, 128);
     const uint64_t ghi = tc::smem_desc_sw128(tc::smem_u32(sm.gfilt)), glo = tc::smem_desc_sw128(tc::smem_u32(sm.gfilt) + 128 * 64 * 2);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    const int k0 = which == 1 ? 2 : 0, k1 = which == 0 ? 2 : 4;
+#pragma unroll 1
+    for (int k = k0; k < k1; ++k) {
       const uint64_t adv = (uint64_t)(k * 32 >> 4);
       umma_bf16_ts(tmem + AR_COL_LOC, tmem + AR_COL_THI + 8u * k, ghi + adv, idesc, k ? 1u : 0u);
       if (npass == 3) {
@@ -407,8 +507,32 @@ __device__ __forceinline__ void build_toeplitz_and_issue(const ArSmem& sm, const
         umma_bf16_ts(tmem + AR_COL_LOC, tmem + AR_COL_THI + 8u * k, glo + adv, idesc, 1u);
       }
     }
-    tc::umma_commit(loc_bar);
+    if (which != 0) tc::umma_commit(loc_bar);
   }
+}
+
+// e + v . tanh(z) for four arguments: tanh(z) = sign(z) (1 - t) / (1 + t), t = exp(-2|z|) in (0, 1]; the four denominators (each in
+// (1, 2]) share ONE reciprocal of their product -- 5 MUFU operations instead of 8 (the energy step is MUFU-bound)
+__device__ __forceinline__ float tanh4_dot(float4 v, float z0, float z1, float z2, float z3, float e) {
+#if AR_LEAN
+  const float k = -2.8853900817779268f;   // -2 log2(e)
+  const float t0 = ex2_ftz(k * fabsf(z0)), t1 = ex2_ftz(k * fabsf(z1)), t2 = ex2_ftz(k * fabsf(z2)), t3 = ex2_ftz(k * fabsf(z3));
+#else
+  const float t0 = __expf(-2.0f * fabsf(z0)), t1 = __expf(-2.0f * fabsf(z1)), t2 = __expf(-2.0f * fabsf(z2)), t3 = __expf(-2.0f * fabsf(z3));
+#endif
+  const float a0 = 1.0f + t0, a1 = 1.0f + t1, a2 = 1.0f + t2, a3 = 1.0f + t3;
+  const float p01 = a0 * a1, p23 = a2 * a3;
+#if AR_LEAN
+  const float r = rcp_ftz(p01 * p23);
+#else
+  const float r = __fdividef(1.0f, p01 * p23);
+#endif
+  const float r01 = r * p23, r23 = r * p01;   // 1 / (a0 a1), 1 / (a2 a3)
+  e = fmaf(v.x, copysignf((1.0f - t0) * (r01 * a1), z0), e);
+  e = fmaf(v.y, copysignf((1.0f - t1) * (r01 * a0), z1), e);
+  e = fmaf(v.z, copysignf((1.0f - t2) * (r23 * a3), z2), e);
+  e = fmaf(v.w, copysignf((1.0f - t3) * (r23 * a2), z3), e);
+  return e;
 }
 
 struct ArAttState {
@@ -418,8 +542,9 @@ struct ArAttState {
 
 // Attention of frame t for this CTA's utterance slice.  Returns false on a wait timeout.  The grid barrier that publishes the context
 // is ARRIVED at inside (after the context stores) and the next frame's Toeplitz operand is built while it completes.
+template <bool TF>
 __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, const ArSmem& sm, const ArAttState& at, uint32_t tmem,
-                             int cur, int nxt, int t_out, uint32_t fphase, ArGridBar& bar, bool& alive, long long* prof_last) {
+                             int cur, int nxt, int t_out, uint32_t fphase, ArGridBar& bar, bool& alive, long long* prof_last, bool split_toeplitz) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int L = d.L, A = d.A, EF = d.EF, S = at.S;
   const ArAtt as = ar_att_scratch(sm, A);
@@ -449,7 +574,7 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
 #pragma unroll
       for (int g = 1; g < 8; ++g) qv += as.qh[g * A + tid];
       as.q_s[tid] = qv;
-      if (io.hist && at.part == 0) s.q[((size_t)t_out * D2_BP + at.b) * A + tid] = qv;   // training tape
+      if (TF && at.part == 0) s.q[((size_t)t_out * D2_BP + at.b) * A + tid] = qv;   // training tape
     }
     if (!tc::mbar_wait(sm.bars + B_LOC, fphase)) ok = false;   // location term of this frame is in TMEM
     tc::tc_fence_after();
@@ -465,7 +590,7 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
         tc::tmem_ld32(tmem + ((uint32_t)lane0 << 16) + AR_COL_LOC + a0, x);
         tc::tmem_ld32(tmem + ((uint32_t)lane0 << 16) + AR_COL_PM + a0, pm);
         tc::tmem_ld_wait();
-        if (io.hist && s.accpm && a0 < A && p < at.nl) {   // training tape: location term + processed memory of this frame (the
+        if (TF && s.accpm && a0 < A && p < at.nl) {   // training tape: location term + processed memory of this frame (the
           float4* dst = reinterpret_cast<float4*>(s.accpm + (((size_t)t_out * 128 + blockIdx.x) * ((L + S - 1) / S) + p) * A + a0);   // backward's pre-tanh argument - q)
 #pragma unroll
           for (int i = 0; i < 8; ++i) __stcs(dst + i, make_float4(x[4 * i] + pm[4 * i], x[4 * i + 1] + pm[4 * i + 1], x[4 * i + 2] + pm[4 * i + 2], x[4 * i + 3] + pm[4 * i + 3]));
@@ -474,10 +599,15 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
 #pragma unroll
           for (int i = 0; i < 8; ++i) {   // q and v as 16-byte broadcast loads
             const float4 q4 = *reinterpret_cast<const float4*>(as.q_s + a0 + 4 * i), v4 = *reinterpret_cast<const float4*>(sm.v + a0 + 4 * i);
-            e = fmaf(v4.x, tanh_fast(q4.x + x[4 * i] + pm[4 * i]), e);
-            e = fmaf(v4.y, tanh_fast(q4.y + x[4 * i + 1] + pm[4 * i + 1]), e);
-            e = fmaf(v4.z, tanh_fast(q4.z + x[4 * i + 2] + pm[4 * i + 2]), e);
-            e = fmaf(v4.w, tanh_fast(q4.w + x[4 * i + 3] + pm[4 * i + 3]), e);
+#if AR_TANH4
+            e = tanh4_dot(v4, q4.x + x[4 * i] + pm[4 * i], q4.y + x[4 * i + 1] + pm[4 * i + 1], q4.z + x[4 * i + 2] + pm[4 * i + 2],
+                          q4.w + x[4 * i + 3] + pm[4 * i + 3], e);
+#else
+            e = fmaf(v4.x, ar_tanh(q4.x + x[4 * i] + pm[4 * i]), e);
+            e = fmaf(v4.y, ar_tanh(q4.y + x[4 * i + 1] + pm[4 * i + 1]), e);
+            e = fmaf(v4.z, ar_tanh(q4.z + x[4 * i + 2] + pm[4 * i + 2]), e);
+            e = fmaf(v4.w, ar_tanh(q4.w + x[4 * i + 3] + pm[4 * i + 3]), e);
+#endif
           }
         }
       }
@@ -492,6 +622,23 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
       for (int r = 0; r < S; ++r) tc::st_async_f32(tc::mapa(dst, base_rank + (uint32_t)r), e, tc::mapa(eb, base_rank + (uint32_t)r));
     }
     mark(11);
+    // context operand (model/attention.py:66-67): the memory rows do not depend on the weights -- the first 8 rows of this thread's
+    // column quad are requested now and land during the exchange and the softmax
+    const int cols_per = ((EF + S - 1) / S + 3) & ~3;
+    const int c0 = at.part * cols_per, c1 = min(EF, c0 + cols_per);
+    const int nq = max(0, (c1 - c0 + 3) >> 2);
+    const int lg = tid >> 6, cq0 = tid & 63;
+    const size_t rs = (size_t)EF / 4;
+    const float4* mp0 = reinterpret_cast<const float4*>(io.memory + (size_t)at.b * L * EF + c0);
+    const int lclamp = max(at.Leff - 1, 0);
+#if AR_CTXPF
+    const bool ctx_new = AR_CTXPF == 1 || (io.debug_barrier & 64) == 0;
+    float4 pf[8];
+    if (cq0 < nq && ctx_new) {
+#pragma unroll
+      for (int u = 0; u < 8; ++u) pf[u] = AR_LDW(mp0 + cq0 + (size_t)min(lg + 4 * u, lclamp) * rs);
+    }
+#endif
     if (!tc::mbar_wait_cluster(sm.bars + B_E, fphase)) ok = false;
     mark(12);
     // softmax over the full row (model/attention.py:65); every thread keeps to its own positions through the three passes
@@ -527,7 +674,7 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
       sm.wcum[15 + l] += w;                                                   // model/decoder.py:90 (every part keeps the whole row)
       if (l >= at.l0 && l < l1) {
         io.aligns[((size_t)at.b * io.Tmax + t_out) * L + l] = w;
-        if (io.hist) {   // training tape: weights / cumulative weights after this frame (slot t+1)
+        if (TF) {   // training tape: weights / cumulative weights after this frame (slot t+1)
           s.w_prev[((size_t)nxt * D2_BP + at.b) * L + l] = w;
           s.w_cum[((size_t)nxt * D2_BP + at.b) * L + l] = sm.wcum[15 + l];
         }
@@ -535,22 +682,49 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
     }
     wsync();
     mark(13);
-    // context columns of this part (model/attention.py:66-67)
-    const int cols_per = ((EF + S - 1) / S + 3) & ~3;
-    const int c0 = at.part * cols_per, c1 = min(EF, c0 + cols_per);
-    const int nq = max(0, (c1 - c0 + 3) >> 2);
-    const float* mem = io.memory + (size_t)at.b * L * EF;
-    const int lg = tid >> 6, cq0 = tid & 63;
+    // context columns of this part: thread = (row group lg of 4, column quad); rows lg, lg + 4, ...: the 8 requested above, then batches of 16 loads; rows
+    // beyond the last unmasked position carry weight 0 exactly and are skipped (clamped address, zero weight inside a batch)
 #pragma unroll 1
     for (int cq = cq0; cq < nq; cq += 64) {
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      const float4* mp = reinterpret_cast<const float4*>(mem + c0) + cq;
-      const size_t rs = (size_t)EF / 4;
+      const float4* mp = mp0 + cq;
+#if AR_CTXPF
+      if (ctx_new) {
+      if (cq != cq0) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) pf[u] = AR_LDW(mp + (size_t)min(lg + 4 * u, lclamp) * rs);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const float w = (lg + 4 * u < at.Leff) ? wr[lg + 4 * u] : 0.f;
+        acc.x = fmaf(w, pf[u].x, acc.x); acc.y = fmaf(w, pf[u].y, acc.y);
+        acc.z = fmaf(w, pf[u].z, acc.z); acc.w = fmaf(w, pf[u].w, acc.w);
+      }
+#pragma unroll 1
+      for (int l = lg + 32; l < at.Leff; l += 64) {
+        float4 m[16];
+#pragma unroll
+        for (int u = 0; u < 16; ++u) m[u] = AR_LDW(mp + (size_t)min(l + 4 * u, lclamp) * rs);
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+          const float w = (l + 4 * u < at.Leff) ? wr[l + 4 * u] : 0.f;
+          acc.x = fmaf(w, m[u].x, acc.x); acc.y = fmaf(w, m[u].y, acc.y);
+          acc.z = fmaf(w, m[u].z, acc.z); acc.w = fmaf(w, m[u].w, acc.w);
+        }
+      }
+      }
+#endif
+#if AR_CTXPF != 1
+#if AR_CTXPF == 2
+      if (!ctx_new) {
+#else
+      {
+#endif
       int l = lg;
       for (; l + 28 < at.Leff; l += 32) {
         float4 m[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) m[u] = __ldg(mp + (size_t)(l + 4 * u) * rs);
+        for (int u = 0; u < 8; ++u) m[u] = AR_LDW(mp + (size_t)(l + 4 * u) * rs);
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
           const float w = wr[l + 4 * u];
@@ -559,11 +733,13 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
         }
       }
       for (; l < at.Leff; l += 4) {
-        const float4 m4 = __ldg(mp + (size_t)l * rs);
+        const float4 m4 = AR_LDW(mp + (size_t)l * rs);
         const float w = wr[l];
         acc.x = fmaf(w, m4.x, acc.x); acc.y = fmaf(w, m4.y, acc.y);
         acc.z = fmaf(w, m4.z, acc.z); acc.w = fmaf(w, m4.w, acc.w);
       }
+      }
+#endif
       *reinterpret_cast<float4*>(as.cred + (size_t)lg * cols_per + cq * 4) = acc;
     }
     wsync();
@@ -576,13 +752,13 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
       const int col = c0 + c;
       store_split(xa, pa, d.KattP, at.b, d.P + col, v);
       store_split(xd, pd, d.KdecP, at.b, d.H + col, v);
-      if (!io.hist) s.projin[(size_t)at.b * d.KprojP + d.R + col] = v;
+      if (!TF) s.projin[(size_t)at.b * d.KprojP + d.R + col] = v;
     }
   }
   mark(14);
   bar.arrive(!ok, sm.ctl);
   // while the barrier completes: the Toeplitz operand of the NEXT frame's location term (depends on this frame's weights only)
-  if (at.active) build_toeplitz_and_issue(sm, sm.wrow, tmem, at.l0, at.nl, d.npass, sm.bars + B_LOC);
+  if (at.active) build_toeplitz_and_issue(sm, sm.wrow, tmem, at.l0, at.nl, d.npass, sm.bars + B_LOC, split_toeplitz ? 0 : 2);
   alive = bar.wait(sm.ctl);
   return ok;
 }
@@ -599,6 +775,7 @@ __device__ void ar_proj_ctx(const D2Dims& d, const D2Weights& w, const D2State& 
   const int rows_per = (M + 1 + D2_CLUSTER - 1) / D2_CLUSTER, r0 = (int)rank * rows_per, nr = max(0, min(rows_per, M + 1 - r0));
   const int rpw = (nr + NW - 1) / NW, rb = r0 + pw * rpw, re = min(r0 + nr, rb + rpw);
   rows_dot2<true>(w.Wproj + d.H, KP, Kc >> 2, rb, re, x0, x1, sm.octx, r0, 64);
+
 }
 
 __device__ bool ar_output(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, const ArSmem& sm, uint32_t rank, int cluster,
@@ -646,9 +823,17 @@ __device__ bool ar_output(const D2Dims& d, const D2Weights& w, const D2State& s,
         st_async_all(mel_s + j * MP + r, v, mel_bar);
       } else {
         io.gates[(size_t)b * io.Tmax + tg_] = v;
-        if (io.stop_enabled) {  // model/tacotron2.py:319-320
-          if (v < 0.0f) s.done[b] = 1;
-          if (v >= 0.0f) s.lengths[b] += 1;
+        if (io.stop_enabled) {  // model/tacotron2.py:319-320; the running values live in shared memory (this thread is their only writer)
+          if (v < 0.0f && sm.ctl[11 + j] == 0u) {
+            sm.ctl[11 + j] = 1u;
+            s.done[b] = 1;
+            atomicAdd(const_cast<unsigned*>(sm.ctl + 9), 1u);   // travels with this CTA's arrival at the X barrier
+          }
+          if (v >= 0.0f) {
+            const unsigned n = sm.ctl[13 + j] + 1u;
+            sm.ctl[13 + j] = n;
+            s.lengths[b] = (long long)n;
+          }
         }
       }
     }
@@ -662,8 +847,13 @@ __device__ bool ar_output(const D2Dims& d, const D2Weights& w, const D2State& s,
   if (!tc::mbar_wait_cluster(mel_bar, cphase)) ok = false;
   if (w1_smem) {
     if (!tc::mbar_wait(wbar, cphase)) ok = false;
+#if AR_XRED
+    ar_rows8<1, true>(w1_s - (ptrdiff_t)pr0 * M, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
+  } else if ((M >> 2) <= 32) ar_rows8<1, false>(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
+#else
     rows_short<8, 1, true>(w1_s - (ptrdiff_t)pr0 * M, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
   } else if ((M >> 2) <= 32) rows_short<8, 1, false>(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
+#endif
   else rows_dot2<false>(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
 #pragma unroll 1
   for (int r = rb + (lane >> 1); r < re && b < B; r += 16) {
@@ -678,7 +868,11 @@ __device__ bool ar_output(const D2Dims& d, const D2Weights& w, const D2State& s,
   const long long pa = (long long)D2_BP * d.KattP;
   __nv_bfloat16* xa = s.xatt + (size_t)nxt * 2 * pa;
   const bool vec = (rq & 7) == 0 && (d.KattP & 7) == 0;
+#if AR_XRED
+  if ((P >> 2) <= 64) ar_rows8<2, false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
+#else
   if ((P >> 2) <= 64) rows_short<8, 2, false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
+#endif
   else rows_dot2<false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
 #pragma unroll 1
   for (int r = rb + (lane >> 1); r < re; r += 16) {
@@ -710,6 +904,7 @@ __device__ bool ar_output(const D2Dims& d, const D2Weights& w, const D2State& s,
 //   10 query sum + location-term wait, 11 energies + exchange issue, 12 exchange wait, 13 softmax, 14 context + stores,
 //   2 C barrier with the Toeplitz build beside it, 15 context half of the projection, 9 wait for the decoder-LSTM accumulator,
 //   3 its tail + R barrier, 4/5/6 projection / prenet 1 / prenet 2, 7 X barrier + stop check
+template <bool TF>   // TF: teacher-forced training forward (history mode: per-frame tape slots), else autoregressive eval
 __global__ void __launch_bounds__(AR_THREADS, 1)
 decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ CUtensorMap gmap, D2Dims d, D2Weights w, D2State s, D2IO io) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -723,7 +918,6 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
   const int B = d.B, L = d.L, A = d.A;
   const int S = (B * 4 <= (int)gridDim.x) ? 4 : ((B * 2 <= (int)gridDim.x) ? 2 : 1);
   int& ok_word = *reinterpret_cast<int*>(const_cast<unsigned*>(sm.ctl + 6));     // (dynamic shared memory: the kernel has no static allocation)
-  int& vote_word = *reinterpret_cast<int*>(const_cast<unsigned*>(sm.ctl + 7));
 
   // ---- one-time setup
   if (tid == 0) {
@@ -731,13 +925,14 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
     tc::prefetch_tmap(&gmap);
     for (int i = 0; i < AR_STAGES; ++i) { tc::mbar_init(sm.bars + B_FULL + i, 1); tc::mbar_init(sm.bars + B_EMPTY + i, 1); }
     tc::mbar_init(sm.bars + B_ACC_ATT, 1); tc::mbar_init(sm.bars + B_ACC_DEC, 1); tc::mbar_init(sm.bars + B_LOC, 1);
-    tc::mbar_init(sm.bars + B_RV, 1); tc::mbar_init(sm.bars + B_RV2, D2_CLUSTER); tc::mbar_init(sm.bars + B_E, 1); tc::mbar_init(sm.bars + B_MEL, 1);
+    tc::mbar_init(sm.bars + B_RV, 1); tc::mbar_init(sm.bars + B_E, 1); tc::mbar_init(sm.bars + B_MEL, 1);
     tc::mbar_init(sm.bars + B_P1, 1); tc::mbar_init(sm.bars + B_W1, 1); tc::mbar_init(sm.bars + B_G, 1); tc::mbar_init(sm.bars + B_FIN, 1);
     tc::fence_barrier_init();
-    sm.ctl[0] = io.teacher_forcing ? 0u : 1u;   // gate count; autoregressive: the (virtual) barrier that publishes the prenet columns of
+    sm.ctl[0] = TF ? 0u : 1u;   // gate count; autoregressive: the (virtual) barrier that publishes the prenet columns of
                                                 // frame 0 counts as passed.  Teacher forcing has three barriers per frame (no X)
-    sm.ctl[1] = 0u; sm.ctl[2] = 0u; sm.ctl[4] = 0u; sm.ctl[5] = 0u; sm.ctl[8] = 0u;
-    sm.ctl[3] = (unsigned)build_program(d, (int)rank, sm.prog);
+    sm.ctl[1] = 0u; sm.ctl[2] = 0u; sm.ctl[4] = 0u; sm.ctl[5] = 0u;
+    for (int i = 8; i < 15; ++i) sm.ctl[i] = 0u;   // 8 cluster counter (barrier mode 2), 9 fired stop gates, 10 done count, 11-12 fired flags, 13-14 lengths
+    sm.ctl[3] = (unsigned)build_program(d, (int)rank, sm.prog, (io.debug_barrier & 256) != 0);   // (experiment bit 256: round-2 order)
   }
   if (warp == 9) tc::tmem_alloc<512>(sm.tmem_slot);   // warp 9 owns alloc + dealloc
   if (worker) {
@@ -764,6 +959,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
   tc::cluster_sync();   // barrier inits of the whole cluster are visible before any remote arrive
 
   const int nprog = (int)sm.ctl[3];
+  const int nst = (io.debug_barrier & 16) ? 2 : AR_STAGES;   // (experiment bit 16: two ring stages in use, to measure what the third buys)
   const int nkb_att = d.KattP / TG_BK, nkb_dec = d.KdecP / TG_BK;
   const uint32_t stage_w = (uint32_t)(d.npass == 3 ? 2 * TG_W_TILE : TG_W_TILE), stage_x = (uint32_t)(d.npass == 3 ? 2 * TG_X_TILE : TG_X_TILE);
 
@@ -789,13 +985,13 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
       unsigned fenced_gate = 0;
       while (x_f < io.n_steps) {
         bool progressed = false;
-        if (w_f < io.n_steps && w_n - x_n < AR_STAGES && tc::mbar_try_wait(sm.bars + B_EMPTY + w_stage, w_phase ^ 1)) {
+        if (w_f < io.n_steps && w_n - x_n < nst && tc::mbar_try_wait(sm.bars + B_EMPTY + w_stage, w_phase ^ 1)) {
           const KbEnt en = sm.prog[w_e];
           uint8_t* st = sm.stages + (size_t)w_stage * TG_STAGE_BYTES;
           mbar_expect_tx(sm.bars + B_FULL + w_stage, stage_w);
           const int nkb = en.gemm ? nkb_dec : nkb_att;
           tc::tma_load_3d_hint(st, en.gemm ? &maps.w_dec : &maps.w_att, sm.bars + B_FULL + w_stage, 0, (tile * nkb + en.kb) * TG_M, 0, wpol);
-          if (++w_stage == AR_STAGES) { w_stage = 0; w_phase ^= 1; }
+          if (++w_stage == nst) { w_stage = 0; w_phase ^= 1; }
           ++w_n;
           advance(w_f, w_e);
           progressed = true;
@@ -803,26 +999,30 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
         if (x_n < w_n) {
           const KbEnt en = sm.prog[x_e];
           // teacher forcing: the prenet columns of every frame exist before the launch (bulk prenet), three barriers per frame (Q, C, R)
-          const int need = io.teacher_forcing ? (en.gate == G_X ? -1 : 3 * x_f + (int)en.gate) : 4 * x_f + (int)en.gate + 1;
+          const int need = en.gate == G_RP ? (TF ? 3 : 4) * x_f
+                                           : (TF ? (en.gate == G_X ? -1 : 3 * x_f + (int)en.gate) : 4 * x_f + (int)en.gate + 1);
           const unsigned have = ld_acquire_cta(sm.ctl);
           if ((int)have >= need) {
             if (have != fenced_gate) { asm volatile("fence.proxy.async;" ::: "memory"); fenced_gate = have; }   // peers' generic stores -> TMA reads
             const int gf = x_f + ((en.flags & 4) ? 1 : 0);
             uint8_t* st = sm.stages + (size_t)x_stage * TG_STAGE_BYTES;
             tc::mbar_arrive_expect_tx(sm.bars + B_FULL + x_stage, stage_x);
-            const int slot = io.hist ? gf : (gf & 1);   // history mode (training tape): one slot per frame instead of two parities
-            const bool pre = io.teacher_forcing && !en.gemm && en.gate == G_X;   // prenet K-block: from the bulk prenet output
+            const int slot = TF ? gf : (gf & 1);   // history mode (training tape): one slot per frame instead of two parities
+            const bool pre = TF && !en.gemm && en.gate == G_X;   // prenet K-block: from the bulk prenet output
             tc::tma_load_3d(st + 2 * TG_W_TILE, pre ? &maps.tf_pre : (en.gemm ? &maps.x_dec : &maps.x_att), sm.bars + B_FULL + x_stage, en.kb * TG_BK, 0,
                             (pre ? gf : slot) * 2);
-            if (++x_stage == AR_STAGES) x_stage = 0;
+            if (++x_stage == nst) x_stage = 0;
             ++x_n;
             advance(x_f, x_e);
             progressed = true;
           }
         }
         if (progressed) { idle = 0; continue; }
+#if AR_LEAN
+        __nanosleep((io.debug_barrier & 128) ? 400 : 32);   // nothing to issue: leave the issue slots of this scheduler to the worker warps
+#endif
         if (sm.ctl[1] != 0u) break;                              // workers stopped (stop gate, abort): no more gates will open
-        if (++idle > (1ll << 26)) { sm.ctl[2] = 1u; break; }     // never hang the GPU
+        if (++idle > (1ll << 24)) { sm.ctl[2] = 1u; break; }     // never hang the GPU
       }
       // weight tiles already in flight for K-blocks that will never run (early stop): complete their stages with the (stale) x
       // tile so that no bulk copy is outstanding when the CTA exits; the MMA issuer drains them
@@ -831,7 +1031,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
         uint8_t* st = sm.stages + (size_t)x_stage * TG_STAGE_BYTES;
         tc::mbar_arrive_expect_tx(sm.bars + B_FULL + x_stage, stage_x);
         tc::tma_load_3d(st + 2 * TG_W_TILE, en.gemm ? &maps.x_dec : &maps.x_att, sm.bars + B_FULL + x_stage, en.kb * TG_BK, 0, 0);
-        if (++x_stage == AR_STAGES) x_stage = 0;
+        if (++x_stage == nst) x_stage = 0;
         ++x_n;
         advance(x_f, x_e);
       }
@@ -880,7 +1080,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
         }
         tc::umma_commit(sm.bars + B_EMPTY + stage);
         if (en.flags & 2) tc::umma_commit(sm.bars + (en.gemm ? B_ACC_DEC : B_ACC_ATT));
-        if (++stage == AR_STAGES) { stage = 0; phase ^= 1; }
+        if (++stage == nst) { stage = 0; phase ^= 1; }
         ++n;
         advance();
       }
@@ -890,9 +1090,8 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
     __syncwarp();
   } else {
     // =============================================================== workers
-    ArGridBar bar{s.bar_flags, s.barrier, s.barrier + 1, gridDim.x, 0u, &ok_word, (io.debug_barrier & 4) ? 2 : ((io.debug_barrier & 1) ? 1 : 0),   // experiment bits: 1 per-CTA flags, 4 per-cluster add
-                  const_cast<unsigned*>(sm.ctl + 8)};
-    const bool pull_tails = (io.debug_barrier & 2) != 0;
+    ArGridBar bar{s.barrier, s.barrier + 2, gridDim.x, 0u, &ok_word};
+    const bool split_toeplitz = (io.debug_barrier & 32) == 0;   // (experiment bit 32: whole Toeplitz build behind the C barrier, as before)
     long long prof_last = clock64();
     auto prof_mark = [&](int slot) {
       if (blockIdx.x == 0 && tid == 0 && s.prof) { const long long now = clock64(); s.prof[slot] += (unsigned long long)(now - prof_last); prof_last = now; }
@@ -943,48 +1142,40 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
 #pragma unroll 1
       for (int i = tid; i < L + 32; i += 256) wrow[i] = 0.f;
       wsync();
-      build_toeplitz_and_issue(sm, wrow, tmem, at.l0, at.nl, d.npass, sm.bars + B_LOC);
+      build_toeplitz_and_issue(sm, wrow, tmem, at.l0, at.nl, d.npass, sm.bars + B_LOC, 2);
     }
     const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
     bool alive = true, fail = false, stop = false;
-    const bool has_out = !io.teacher_forcing;
-    uint32_t rv_phase = 0, rv2_phase = 0, cphase = 0;
+    constexpr bool has_out = !TF;
+    uint32_t rv_phase = 0, cphase = 0;
     int frames = 0;
 #pragma unroll 1
     for (int t = 0; t < io.n_steps && alive && !stop; ++t) {
       const int tg_ = io.t0 + t;
-      const int cur = io.hist ? tg_ : (t & 1), nxt = io.hist ? tg_ + 1 : (cur ^ 1);   // history mode: one slot per frame (training tape)
-      const unsigned char* att_keep = io.att_keep ? io.att_keep + (size_t)tg_ * B * d.H : nullptr;
-      const unsigned char* rnn_keep = io.rnn_keep ? io.rnn_keep + (size_t)tg_ * B * d.H : nullptr;
+      const int cur = TF ? tg_ : (t & 1), nxt = TF ? tg_ + 1 : (cur ^ 1);   // history mode: one slot per frame (training tape)
+      const unsigned char* att_keep = (TF && io.att_keep) ? io.att_keep + (size_t)tg_ * B * d.H : nullptr;
+      const unsigned char* rnn_keep = (TF && io.rnn_keep) ? io.rnn_keep + (size_t)tg_ * B * d.H : nullptr;
       const unsigned long long rb_att = (1ull << 40) + (unsigned long long)tg_ * B * d.H, rb_dec = (2ull << 40) + (unsigned long long)tg_ * B * d.H;
-      float* sav_att = s.sav_att ? s.sav_att + (size_t)tg_ * 5 * d.H * D2_BP : nullptr;
-      float* sav_dec = s.sav_dec ? s.sav_dec + (size_t)tg_ * 5 * d.H * D2_BP : nullptr;
-      const bool hdrop = io.hidden_dropout != 0;
+      float* sav_att = (TF && s.sav_att) ? s.sav_att + (size_t)tg_ * 5 * d.H * D2_BP : nullptr;
+      float* sav_dec = (TF && s.sav_dec) ? s.sav_dec + (size_t)tg_ * 5 * d.H * D2_BP : nullptr;
+      const bool hdrop = TF && io.hidden_dropout != 0;
       // ================= attention LSTMCell (model/decoder.py:70-75): only the prenet K-block of the contraction is still to come
       if (!tc::mbar_wait(sm.bars + B_ACC_ATT, (uint32_t)(t & 1))) fail = true;
       tc::tc_fence_after();
       prof_mark(8);
       {
         const HOut ho{s.xatt + (size_t)nxt * 2 * pa, d.KattP, d.P + d.EF, pa, s.xdec + (size_t)cur * 2 * pd, d.KdecP, 0, pd, s.att_h_rm, d.H, 0};
-        if (pull_tails) {
-          ar_accum_to_smem(tmem, AR_COL_ATT, sm.part);
-          if (!cluster_rendezvous(sm.bars + B_RV2, rv2_phase)) fail = true;
-          lstm_tail(sm.part, rank, unit0, w.batt, d.H, sm.c_att, B, ho, att_keep, hdrop, io.seed, rb_att, sav_att, sm.h_s);
-        } else {
-          ar_push_partials(tmem, AR_COL_ATT, sm.part, sm.bars + B_RV, rank);
-          if (!tc::mbar_wait_cluster(sm.bars + B_RV, rv_phase)) fail = true;
-          rv_phase ^= 1u;
-          if (io.debug_barrier & 8) prof_mark(8);   // (experiment: the exchange is charged to slot 8)
-          ar_lstm_tail(sm.part, unit0, w.batt, d.H, sm.c_att, B, ho, sm.h_s, att_keep, hdrop, io.seed, rb_att, sav_att);
-        }
+        ar_push_partials(tmem, AR_COL_ATT, sm.part, sm.bars + B_RV, rank);
+        if (!tc::mbar_wait_cluster(sm.bars + B_RV, rv_phase)) fail = true;
+        rv_phase ^= 1u;
+        ar_lstm_tail(sm.part, unit0, w.batt, d.H, sm.c_att, B, ho, sm.h_s, att_keep, hdrop, io.seed, rb_att, sav_att);
       }
       prof_mark(0);
       query_partial(sm.h_s, sm.wq, A, B, s.qpart + (size_t)blockIdx.x * A, (size_t)128 * A);
-      if (io.debug_barrier & 8) prof_mark(0);   // (experiment: the query partials are charged to slot 0, slot 1 is the bare barrier)
       if (!(alive = bar.sync(fail, sm.ctl))) break;
       prof_mark(1);
       // ================= location-sensitive attention (model/attention.py:54-67, model/decoder.py:90) + C barrier
-      if (!ar_attention(d, s, io, sm, at, tmem, cur, nxt, tg_, (uint32_t)(t & 1), bar, alive, &prof_last)) fail = true;
+      if (!ar_attention<TF>(d, s, io, sm, at, tmem, cur, nxt, tg_, (uint32_t)(t & 1), bar, alive, &prof_last, split_toeplitz)) fail = true;
       if (!alive) break;
       prof_mark(2);
       // ================= decoder LSTMCell (model/decoder.py:94-101): the context K-blocks are on their way; meanwhile the context
@@ -995,19 +1186,16 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
       tc::tc_fence_after();
       prof_mark(9);
       {
-        const HOut ho{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, io.hist ? nullptr : s.projin, d.KprojP, 0};
-        if (pull_tails) {
-          ar_accum_to_smem(tmem, AR_COL_DEC, sm.part);
-          if (!cluster_rendezvous(sm.bars + B_RV2, rv2_phase)) fail = true;
-          lstm_tail(sm.part, rank, unit0, w.bdec, d.H, sm.c_dec, B, ho, rnn_keep, hdrop, io.seed, rb_dec, sav_dec, sm.h_s);
-        } else {
-          ar_push_partials(tmem, AR_COL_DEC, sm.part, sm.bars + B_RV, rank);
-          if (!tc::mbar_wait_cluster(sm.bars + B_RV, rv_phase)) fail = true;
-          rv_phase ^= 1u;
-          ar_lstm_tail(sm.part, unit0, w.bdec, d.H, sm.c_dec, B, ho, sm.h_s, rnn_keep, hdrop, io.seed, rb_dec, sav_dec);
-        }
+        const HOut ho{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, TF ? nullptr : s.projin, d.KprojP, 0};
+        ar_push_partials(tmem, AR_COL_DEC, sm.part, sm.bars + B_RV, rank);
+        if (!tc::mbar_wait_cluster(sm.bars + B_RV, rv_phase)) fail = true;
+        rv_phase ^= 1u;
+        ar_lstm_tail(sm.part, unit0, w.bdec, d.H, sm.c_dec, B, ho, sm.h_s, rnn_keep, hdrop, io.seed, rb_dec, sav_dec);
       }
-      if (!(alive = bar.sync(fail, sm.ctl))) break;
+      bar.arrive(fail, sm.ctl);
+      // behind the R barrier: the second half of the next frame's Toeplitz operand (cumulative weights) and the commit
+      if (split_toeplitz && at.active) build_toeplitz_and_issue(sm, sm.wrow, tmem, at.l0, at.nl, d.npass, sm.bars + B_LOC, 1);
+      if (!(alive = bar.wait(sm.ctl))) break;
       prof_mark(3);
       // ================= mel / gate projection, stop bookkeeping, prenet on the emitted frame (model/decoder.py:103-109,
       // model/tacotron2.py:311-325)
@@ -1016,17 +1204,8 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
       if (!ar_output(d, w, s, io, sm, rank, tile, tg_, nxt, cphase, &prof_last)) fail = true;
       if (t + 1 < io.n_steps) {
         if (!(alive = bar.sync(fail, sm.ctl))) break;
-        if (io.stop_enabled) {   // model/tacotron2.py:321-322: leave once every utterance has fired its stop gate
-          int mine = 1;
-#pragma unroll 1
-          for (int b = tid; b < B; b += 256) mine &= (ld_acquire_u32((const unsigned*)s.done + b) != 0u);
-          if (tid == 0) vote_word = 1;
-          wsync();
-          if (!mine) vote_word = 0;
-          wsync();
-          if (vote_word != 0 && t + 1 >= io.min_frames) stop = true;
-          wsync();
-        }
+        // model/tacotron2.py:321-322: leave once every utterance has fired its stop gate (the count arrived with the barrier word)
+        if (io.stop_enabled && (int)sm.ctl[10] >= B && t + 1 >= io.min_frames) stop = true;
         prof_mark(7);
       }
     }
@@ -1086,7 +1265,8 @@ int d2ar_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2I
   T2_REQUIRE((!io.teacher_forcing && !io.hist && !io.hidden_dropout) || (io.teacher_forcing && io.hist), T2_ERR_ARG,
              "decoder (pipelined): autoregressive eval mode or the teacher-forced training forward (history mode) only");
   const size_t smem = ar_smem_bytes(d);
-  T2_CHECK_CUDA(cudaFuncSetAttribute(decoder_ar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  auto kern = io.teacher_forcing ? decoder_ar_kernel<true> : decoder_ar_kernel<false>;
+  T2_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg{};
   cudaLaunchAttribute at[1];
   cfg.gridDim = dim3(128);
@@ -1098,10 +1278,10 @@ int d2ar_launch(const D2Dims& d, const D2Weights& w, const D2State& s, const D2I
   cfg.attrs = at;
   cfg.numAttrs = 1;
   int nclusters = 0;
-  T2_CHECK_CUDA(cudaOccupancyMaxActiveClusters(&nclusters, decoder_ar_kernel, &cfg));
+  T2_CHECK_CUDA(cudaOccupancyMaxActiveClusters(&nclusters, kern, &cfg));
   T2_REQUIRE(nclusters * D2_CLUSTER >= 128, T2_ERR_UNSUPPORTED, "decoder (pipelined AR): only %d clusters of %d can be co-resident", nclusters,
              D2_CLUSTER);
-  T2_CHECK_CUDA(cudaMemsetAsync(s.barrier, 0, 2 * sizeof(unsigned), st));
-  T2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, decoder_ar_kernel, maps, gmap, d, w, s, io));
+  T2_CHECK_CUDA(cudaMemsetAsync(s.barrier, 0, 4 * sizeof(unsigned), st));   // [0..1] 64-bit barrier word, [2] abort flag
+  T2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, maps, gmap, d, w, s, io));
   return T2_OK;
 }
