@@ -30,13 +30,16 @@
 #include "dec_shared.cuh"
 
 #define AR_THREADS 320     // warps 0..7 workers, warp 8 TMA producer, warp 9 MMA issuer
-#define AR_STAGES 3
+#define AR_STAGES 2        // two 48 KB ring stages: a third bought nothing (measured), its shared memory holds projection rows instead
 #define AR_COL_ATT 0u      // TMEM columns: attention-LSTM accumulator [128 gate rows x 64 utterances]
 #define AR_COL_DEC 64u     // decoder-LSTM accumulator
 #define AR_COL_LOC 128u    // location term [128 positions x 128 attention dims]
 #define AR_COL_PM 256u     // processed memory of this CTA's positions, resident for the whole launch
 #define AR_COL_THI 384u    // Toeplitz operand, hi plane: 128 positions x 64 taps bf16 = 32 columns
 #define AR_COL_TLO 416u    // lo plane
+#define AR_COL_WP 448u     // 8 rows of the mel / gate projection weights (rnn_h half): lane = K / 4 index mod 128, 2 x 32 columns
+#define AR_WRES_ROWS 12    // rows of the same weights resident in shared memory (48 KB)
+#define AR_WTM_ROWS 8      // rows resident in tensor memory
 #define AR_MAX_ENT 40
 #ifndef AR_TANH4
 #define AR_TANH4 1        // energy step: four tanh share one reciprocal
@@ -60,6 +63,7 @@ struct ArSmem {
   uint8_t* stages;
   float* part;       // split-K partials | attention scratch | output-stage scratch (phases never overlap, see the hazards note)
   uint8_t* gfilt;    // [2 hi/lo][128 a][64 taps] bf16, 128-B swizzled K-major: B operand of the location contraction
+  float* wres;       // [AR_WRES_ROWS][H] first rows of this CTA's slice of the projection weights (rnn_h half), resident
   float* c_att;
   float* c_dec;
   float* wq;
@@ -75,7 +79,7 @@ struct ArSmem {
 };
 
 __host__ __device__ inline size_t ar_smem_bytes(const D2Dims& d) {
-  return 1024 + (size_t)AR_STAGES * TG_STAGE_BYTES + TG_M * TG_PART_LD * 4 + 2 * 128 * 64 * 2 + 2 * 8 * D2_BP * 4 + 8 * (size_t)d.A * 4 + 8 * D2_BP * 4 +
+  return 1024 + (size_t)AR_STAGES * TG_STAGE_BYTES + (size_t)AR_WRES_ROWS * d.H * 4 + TG_M * TG_PART_LD * 4 + 2 * 128 * 64 * 2 + 2 * 8 * D2_BP * 4 + 8 * (size_t)d.A * 4 + 8 * D2_BP * 4 +
          (size_t)d.A * 4 + 2 * 64 * 4 + 2 * (size_t)(d.L + 32) * 4 + AR_MAX_ENT * sizeof(KbEnt) + 24 * 8 + 80;
 }
 
@@ -84,6 +88,7 @@ __device__ __forceinline__ ArSmem ar_carve(uint8_t* base, const D2Dims& d) {
   s.stages = base;
   uint8_t* p = base + (size_t)AR_STAGES * TG_STAGE_BYTES;
   s.gfilt = p;                             p += 2 * 128 * 64 * 2;    // keeps the 1024-B alignment of the ring
+  s.wres = reinterpret_cast<float*>(p);    p += (size_t)AR_WRES_ROWS * d.H * 4;
   s.part = reinterpret_cast<float*>(p);    p += TG_M * TG_PART_LD * 4;
   s.c_att = reinterpret_cast<float*>(p);   p += 8 * D2_BP * 4;
   s.c_dec = reinterpret_cast<float*>(p);   p += 8 * D2_BP * 4;
@@ -763,6 +768,15 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
   return ok;
 }
 
+// The rnn_h half of the mel / gate projection reads its weights from chip memory when the CTA's rows fit: AR_WRES_ROWS rows in shared
+// memory, AR_WTM_ROWS in tensor memory, at most one more from L2 (vanilla: 21 rows per CTA; lane = one float4 of K, K = 1024).
+__host__ __device__ inline bool ar_proj_fast(const D2Dims& d) {
+  const int rows_per = (d.M + 1 + D2_CLUSTER - 1) / D2_CLUSTER, rq = d.P / D2_CLUSTER;
+  const int w1_off = 2 * ((d.M + 4) & ~3) + 2 * d.P + 2 * rq + 6 * (rq > 64 ? rq : 64);
+  const bool w1_smem = (d.M >> 2) <= 32 && (w1_off & 3) == 0 && w1_off + rq * d.M <= TG_M * TG_PART_LD;
+  return d.H == 1024 && rows_per <= AR_WRES_ROWS + AR_WTM_ROWS + 1 && w1_off + (w1_smem ? rq * d.M : 0) + 8 * 2 * 24 <= TG_M * TG_PART_LD;
+}
+
 // ------------------------------------------------------------------------------------------ output stage (all 8 worker warps)
 // As output_side / proj_ctx_side of decoder.cu, on eight warps and on the dependent chain (nothing streams on these warps).
 __device__ void ar_proj_ctx(const D2Dims& d, const D2Weights& w, const D2State& s, const ArSmem& sm, uint32_t rank, int cluster) {
@@ -779,7 +793,7 @@ __device__ void ar_proj_ctx(const D2Dims& d, const D2Weights& w, const D2State& 
 }
 
 __device__ bool ar_output(const D2Dims& d, const D2Weights& w, const D2State& s, const D2IO& io, const ArSmem& sm, uint32_t rank, int cluster,
-                          int tg_, int nxt, uint32_t& cphase, long long* prof_last) {
+                          int tg_, int nxt, uint32_t& cphase, long long* prof_last, uint32_t tmem, bool proj_fast) {
   const int tid = threadIdx.x, lane = tid & 31, pw = tid >> 5, NW = 8;
   const int B = d.B, M = d.M, P = d.P, KP = d.KprojP, MP = (M + 1 + 3) & ~3;
   const int rq = P / D2_CLUSTER;
@@ -814,10 +828,53 @@ __device__ bool ar_output(const D2Dims& d, const D2Weights& w, const D2State& s,
   {
     const int rows_per = (M + 1 + D2_CLUSTER - 1) / D2_CLUSTER, r0 = (int)rank * rows_per, nr = max(0, min(rows_per, M + 1 - r0));
     const int rpw = (nr + NW - 1) / NW, rb = r0 + pw * rpw, re = min(r0 + nr, rb + rpw);
-    rows_dot2<true>(w.Wproj, KP, H4, rb, re, s.projin + (size_t)b0 * KP, s.projin + (size_t)min(b0 + 1, B - 1) * KP, y_s, r0, YS);
+    float* pr = mel_s + w1_off + (w1_smem ? rq * M : 0);   // [8 warps][2][24] partial sums of the fast path
+    if (proj_fast) {
+      // K split over the threads (this thread: float4 index k of every row), weights from shared memory (rows 0..11), tensor memory
+      // (12..19) and L2 (row 20): the only L2 round trip on the chain is the two input rows (8 KB per CTA) and that last row
+      const int k = tid;
+      float tw[4 * AR_WTM_ROWS];
+      tc::tmem_ld32(tmem + ((uint32_t)(32 * (pw & 3)) << 16) + AR_COL_WP + 32u * (uint32_t)(pw >> 2), tw);
+      const float4 xa = __ldcg(reinterpret_cast<const float4*>(s.projin + (size_t)b0 * KP) + k);
+      const float4 xb = __ldcg(reinterpret_cast<const float4*>(s.projin + (size_t)min(b0 + 1, B - 1) * KP) + k);
+      float4 wl = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (nr > AR_WRES_ROWS + AR_WTM_ROWS) wl = AR_LDW(reinterpret_cast<const float4*>(w.Wproj + (size_t)(r0 + AR_WRES_ROWS + AR_WTM_ROWS) * KP) + k);
+      tc::tmem_ld_wait();
+      const float4* ws = reinterpret_cast<const float4*>(sm.wres) + k;
+#pragma unroll
+      for (int c = 0; c < 24; c += 8) {
+        float v[16];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int ri = c + i;
+          float4 wv;
+          if (ri < AR_WRES_ROWS) wv = ws[ri * (1024 / 4)];
+          else if (ri < AR_WRES_ROWS + AR_WTM_ROWS) wv = make_float4(tw[4 * (ri - AR_WRES_ROWS)], tw[4 * (ri - AR_WRES_ROWS) + 1], tw[4 * (ri - AR_WRES_ROWS) + 2], tw[4 * (ri - AR_WRES_ROWS) + 3]);
+          else if (ri == AR_WRES_ROWS + AR_WTM_ROWS) wv = wl;
+          else wv = make_float4(0.f, 0.f, 0.f, 0.f);
+          v[i] = fmaf(wv.w, xa.w, fmaf(wv.z, xa.z, fmaf(wv.y, xa.y, wv.x * xa.x)));
+          v[8 + i] = fmaf(wv.w, xb.w, fmaf(wv.z, xb.z, fmaf(wv.y, xb.y, wv.x * xb.x)));
+        }
+        xreduce<16>(v);
+        const int q = lane >> 1, i = c + (q & 7);
+        if ((lane & 1) == 0 && i < nr) pr[(pw * 2 + (q >> 3)) * 24 + i] = v[0];
+      }
+      tc::tc_fence_before();
+      wsync();
+    } else {
+      rows_dot2<true>(w.Wproj, KP, H4, rb, re, s.projin + (size_t)b0 * KP, s.projin + (size_t)min(b0 + 1, B - 1) * KP, y_s, r0, YS);
+    }
 #pragma unroll 1
-    for (int r = rb + (lane >> 1); r < re && b < B; r += 16) {
-      const float v = y_s[j * YS + r - r0] + sm.octx[j * 64 + r - r0] + __ldg(w.bproj + r);
+    for (int r = proj_fast ? r0 + (tid >> 1) : rb + (lane >> 1); r < (proj_fast ? min(r0 + nr, r0 + (tid >> 1) + 1) : re) && b < B; r += 16) {
+      float v;
+      if (proj_fast) {
+        v = pr[j * 24 + r - r0];
+#pragma unroll
+        for (int wi = 1; wi < 8; ++wi) v += pr[(wi * 2 + j) * 24 + r - r0];
+      } else {
+        v = y_s[j * YS + r - r0];
+      }
+      v += sm.octx[j * 64 + r - r0] + __ldg(w.bproj + r);
       if (r < M) {
         io.mels[((size_t)b * io.Tmax + tg_) * M + r] = v;
         st_async_all(mel_s + j * MP + r, v, mel_bar);
@@ -959,7 +1016,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
   tc::cluster_sync();   // barrier inits of the whole cluster are visible before any remote arrive
 
   const int nprog = (int)sm.ctl[3];
-  const int nst = (io.debug_barrier & 16) ? 2 : AR_STAGES;   // (experiment bit 16: two ring stages in use, to measure what the third buys)
+  constexpr int nst = AR_STAGES;
   const int nkb_att = d.KattP / TG_BK, nkb_dec = d.KdecP / TG_BK;
   const uint32_t stage_w = (uint32_t)(d.npass == 3 ? 2 * TG_W_TILE : TG_W_TILE), stage_x = (uint32_t)(d.npass == 3 ? 2 * TG_X_TILE : TG_X_TILE);
 
@@ -1147,6 +1204,26 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
     const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
     bool alive = true, fail = false, stop = false;
     constexpr bool has_out = !TF;
+    const bool proj_fast = has_out && ar_proj_fast(d) && 2 * tile < B && (io.debug_barrier & 1024) == 0;
+    if (proj_fast) {   // this CTA's rows of the projection weights (rnn_h half) -> shared memory and tensor memory, once per launch
+      const int rows_per = (d.M + 1 + D2_CLUSTER - 1) / D2_CLUSTER, r0 = (int)rank * rows_per, nr = max(0, min(rows_per, d.M + 1 - r0));
+      const float4* wp = reinterpret_cast<const float4*>(w.Wproj);
+      const size_t ld4 = (size_t)(d.KprojP >> 2);
+#pragma unroll 1
+      for (int i = tid; i < min(AR_WRES_ROWS, nr) * 256; i += 256)
+        reinterpret_cast<float4*>(sm.wres)[i] = __ldg(wp + (size_t)(r0 + (i >> 8)) * ld4 + (i & 255));
+      uint32_t r[32];
+#pragma unroll
+      for (int i = 0; i < AR_WTM_ROWS; ++i) {
+        const int row = AR_WRES_ROWS + i;
+        const float4 v4 = row < nr ? __ldg(wp + (size_t)(r0 + row) * ld4 + tid) : make_float4(0.f, 0.f, 0.f, 0.f);
+        r[4 * i] = __float_as_uint(v4.x); r[4 * i + 1] = __float_as_uint(v4.y); r[4 * i + 2] = __float_as_uint(v4.z); r[4 * i + 3] = __float_as_uint(v4.w);
+      }
+      tmem_st32(tmem + ((uint32_t)(32 * (warp & 3)) << 16) + AR_COL_WP + 32u * (uint32_t)(warp >> 2), r);
+      tmem_st_wait();
+      tc::tc_fence_before();
+      wsync();
+    }
     uint32_t rv_phase = 0, cphase = 0;
     int frames = 0;
 #pragma unroll 1
@@ -1193,17 +1270,20 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
         ar_lstm_tail(sm.part, unit0, w.bdec, d.H, sm.c_dec, B, ho, sm.h_s, rnn_keep, hdrop, io.seed, rb_dec, sav_dec);
       }
       bar.arrive(fail, sm.ctl);
-      // behind the R barrier: the second half of the next frame's Toeplitz operand (cumulative weights) and the commit
-      if (split_toeplitz && at.active) build_toeplitz_and_issue(sm, sm.wrow, tmem, at.l0, at.nl, d.npass, sm.bars + B_LOC, 1);
+      // behind the R barrier (training forward) or the X barrier (autoregressive: the output stage reads tensor memory right after R):
+      // the second half of the next frame's Toeplitz operand (cumulative weights) and the commit
+      if (TF && split_toeplitz && at.active) build_toeplitz_and_issue(sm, sm.wrow, tmem, at.l0, at.nl, d.npass, sm.bars + B_LOC, 1);
       if (!(alive = bar.wait(sm.ctl))) break;
       prof_mark(3);
       // ================= mel / gate projection, stop bookkeeping, prenet on the emitted frame (model/decoder.py:103-109,
       // model/tacotron2.py:311-325)
       frames = t + 1;
       if (!has_out) continue;   // teacher-forced training: the projection is one bulk GEMM after the kernel, the prenet ran before it
-      if (!ar_output(d, w, s, io, sm, rank, tile, tg_, nxt, cphase, &prof_last)) fail = true;
+      if (!ar_output(d, w, s, io, sm, rank, tile, tg_, nxt, cphase, &prof_last, tmem, proj_fast)) fail = true;
       if (t + 1 < io.n_steps) {
-        if (!(alive = bar.sync(fail, sm.ctl))) break;
+        bar.arrive(fail, sm.ctl);
+        if (split_toeplitz && at.active) build_toeplitz_and_issue(sm, sm.wrow, tmem, at.l0, at.nl, d.npass, sm.bars + B_LOC, 1);
+        if (!(alive = bar.wait(sm.ctl))) break;
         // model/tacotron2.py:321-322: leave once every utterance has fired its stop gate (the count arrived with the barrier word)
         if (io.stop_enabled && (int)sm.ctl[10] >= B && t + 1 >= io.min_frames) stop = true;
         prof_mark(7);
