@@ -38,7 +38,15 @@
 #define AR_COL_THI 384u    // Toeplitz operand, hi plane: 128 positions x 64 taps bf16 = 32 columns
 #define AR_COL_TLO 416u    // lo plane
 #define AR_COL_WP 448u     // 8 rows of the mel / gate projection weights (rnn_h half): lane = K / 4 index mod 128, 2 x 32 columns
+#ifndef AR_BULKX
+#define AR_BULKX 1         // split-K exchange: partial rows staged in shared memory and sent as three bulk copies (else st.async per thread)
+#endif
+#if AR_BULKX
+#define AR_WRES_ROWS 5     // rows of the same weights resident in shared memory (20 KB; the staging buffers of the exchange take 25.5 KB)
+#else
 #define AR_WRES_ROWS 12    // rows of the same weights resident in shared memory (48 KB)
+#endif
+#define AR_PROJ_ROWS 21    // most projection rows per CTA on the fast path: the rest (beyond shared and tensor memory) comes from L2
 #define AR_WTM_ROWS 8      // rows resident in tensor memory
 #define AR_MAX_ENT 40
 #ifndef AR_TANH4
@@ -57,13 +65,14 @@
 namespace {
 
 struct KbEnt { unsigned char gemm, kb, gate, flags; };   // flags: 1 first block of its accumulator, 2 last, 4 belongs to frame t+1
-enum { G_X = 0, G_Q = 1, G_C = 2, G_R = 3, G_RP = 4 };   // G_RP: the R barrier of the previous frame
+enum { G_X = 0, G_Q = 1, G_C = 2, G_R = 3 };
 
 struct ArSmem {
   uint8_t* stages;
   float* part;       // split-K partials | attention scratch | output-stage scratch (phases never overlap, see the hazards note)
   uint8_t* gfilt;    // [2 hi/lo][128 a][64 taps] bf16, 128-B swizzled K-major: B operand of the location contraction
   float* wres;       // [AR_WRES_ROWS][H] first rows of this CTA's slice of the projection weights (rnn_h half), resident
+  float* stg;        // [3][32][TG_PART_LD] outgoing partial rows of the split-K exchange, one block per peer (AR_BULKX)
   float* c_att;
   float* c_dec;
   float* wq;
@@ -79,7 +88,7 @@ struct ArSmem {
 };
 
 __host__ __device__ inline size_t ar_smem_bytes(const D2Dims& d) {
-  return 1024 + (size_t)AR_STAGES * TG_STAGE_BYTES + (size_t)AR_WRES_ROWS * d.H * 4 + TG_M * TG_PART_LD * 4 + 2 * 128 * 64 * 2 + 2 * 8 * D2_BP * 4 + 8 * (size_t)d.A * 4 + 8 * D2_BP * 4 +
+  return 1024 + (size_t)AR_STAGES * TG_STAGE_BYTES + (size_t)AR_WRES_ROWS * d.H * 4 + (AR_BULKX ? 3 * 32 * TG_PART_LD * 4 : 0) + TG_M * TG_PART_LD * 4 + 2 * 128 * 64 * 2 + 2 * 8 * D2_BP * 4 + 8 * (size_t)d.A * 4 + 8 * D2_BP * 4 +
          (size_t)d.A * 4 + 2 * 64 * 4 + 2 * (size_t)(d.L + 32) * 4 + AR_MAX_ENT * sizeof(KbEnt) + 24 * 8 + 80;
 }
 
@@ -89,6 +98,7 @@ __device__ __forceinline__ ArSmem ar_carve(uint8_t* base, const D2Dims& d) {
   uint8_t* p = base + (size_t)AR_STAGES * TG_STAGE_BYTES;
   s.gfilt = p;                             p += 2 * 128 * 64 * 2;    // keeps the 1024-B alignment of the ring
   s.wres = reinterpret_cast<float*>(p);    p += (size_t)AR_WRES_ROWS * d.H * 4;
+  s.stg = reinterpret_cast<float*>(p);     p += AR_BULKX ? 3 * 32 * TG_PART_LD * 4 : 0;
   s.part = reinterpret_cast<float*>(p);    p += TG_M * TG_PART_LD * 4;
   s.c_att = reinterpret_cast<float*>(p);   p += 8 * D2_BP * 4;
   s.c_dec = reinterpret_cast<float*>(p);   p += 8 * D2_BP * 4;
@@ -172,7 +182,7 @@ __host__ __device__ inline int dec_class(const D2Dims& d, int kb) {   // 0 att_h
 }
 
 // The K-block program of CTA `rank`, in issue order (see the file comment).  Returns the entry count.
-__host__ __device__ inline int build_program(const D2Dims& d, int rank, KbEnt* out, bool legacy_order = false) {
+__host__ __device__ inline int build_program(const D2Dims& d, int rank, KbEnt* out) {
   const int nka = d.KattP / TG_BK, nkd = d.KdecP / TG_BK;
   int n = 0;
   auto emit = [&](int gemm, int cls, int gate, int next) {
@@ -182,40 +192,23 @@ __host__ __device__ inline int build_program(const D2Dims& d, int rank, KbEnt* o
         ++n;
       }
   };
-  if (legacy_order) {
-    emit(0, 0, G_X, 0);   // att.P(t)
-    const int last_att = n - 1;
-    emit(1, 0, G_Q, 0);   // dec.A(t)
-    const int first_att = n;
-    emit(0, 2, G_Q, 1);   // att.H(t+1)
-    emit(1, 1, G_C, 0);   // dec.C(t)
-    const int last_dec = n - 1;
-    emit(0, 1, G_C, 1);   // att.C(t+1)
-    const int first_dec = n;
-    emit(1, 2, G_R, 1);   // dec.R(t+1)
-    if (n <= AR_MAX_ENT && last_att >= 0 && first_att < n && last_dec > last_att && first_dec < n) {
-      out[last_att].flags |= 2; out[first_att].flags |= 1; out[last_dec].flags |= 2; out[first_dec].flags |= 1;
-    }
-    return n;
-  }
-  // The background K-blocks are placed in the two windows in which the workers read little from L2 (attention-LSTM tail after X,
-  // decoder-LSTM tail after C); the windows of the context sum (after Q) and of the output stage (after R) stay as quiet as the
-  // dependencies allow, because the SM's L2 ingress is what the CUDA-core loads of those phases and the weight stream share:
-  //   after X(t-1): att.P(t) [on the chain], dec.R(t) (rnn_h of frame t-1, published at R(t-1))
-  //   after Q(t):   dec.A(t)                                   (must be in the accumulator before the context blocks close it)
-  //   after C(t):   dec.C(t) [on the chain], att.H(t+1) (att_h of frame t), att.C(t+1)
-  //   after R(t):   nothing -- the next entry, att.P(t+1), waits for X(t) with its weights already in shared memory
-  emit(0, 0, G_X, 0);    // att.P(t)
+  // Order = which barrier window a background block streams in.  The windows after Q (query sum, context sum: 270 KB of CUDA-core
+  // loads per CTA) and after X share the SM's L2 ingress with whatever streams there, so only the blocks the decoder cell needs before
+  // the context blocks close its accumulator (dec.A) follow Q; att.H / att.C of the next frame follow the on-chain context blocks
+  // (decoder-LSTM tail window), dec.R of the next frame follows R (the output stage reads its projection weights from chip memory).
+  // Measured at C2 (profiles/r02_v14_ar_ab.log): this order 32.7 us per frame, round 2's first order (att.H right after dec.A) 32.8,
+  // dec.R behind the next att.P instead (after X) 33.4.
+  emit(0, 0, G_X, 0);   // att.P(t)      [on the chain]
   const int last_att = n - 1;
-  const int first_dec = n;
-  emit(1, 2, G_RP, 0);   // dec.R(t)
-  emit(1, 0, G_Q, 0);    // dec.A(t)
-  emit(1, 1, G_C, 0);    // dec.C(t)
+  emit(1, 0, G_Q, 0);   // dec.A(t)
+  emit(1, 1, G_C, 0);   // dec.C(t)      [on the chain]
   const int last_dec = n - 1;
   const int first_att = n;
-  emit(0, 2, G_Q, 1);    // att.H(t+1)
-  emit(0, 1, G_C, 1);    // att.C(t+1)
-  if (n <= AR_MAX_ENT && last_att >= 0 && first_att < n && last_dec > first_dec && first_dec < n) {
+  emit(0, 2, G_Q, 1);   // att.H(t+1)
+  emit(0, 1, G_C, 1);   // att.C(t+1)
+  const int first_dec = n;
+  emit(1, 2, G_R, 1);   // dec.R(t+1)
+  if (n <= AR_MAX_ENT && last_att >= 0 && first_att < n && last_dec > last_att && first_dec < n) {
     out[last_att].flags |= 2; out[first_att].flags |= 1; out[last_dec].flags |= 2; out[first_dec].flags |= 1;
   }
   return n;
@@ -275,11 +268,34 @@ __device__ __forceinline__ void st_async_v4(uint32_t cluster_addr, float4 v, uin
   asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.f32 [%0], {%1, %2, %3, %4}, [%5];"
                ::"r"(cluster_addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(cluster_bar) : "memory");
 }
-__device__ __forceinline__ void ar_push_partials(uint32_t tmem, uint32_t col, float* recv, uint64_t* bar, uint32_t my_rank) {
+__device__ __forceinline__ void ar_push_partials(uint32_t tmem, uint32_t col, float* recv, float* stg, uint64_t* bar, uint32_t my_rank) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int owner = warp & 3, col0 = 32 * (warp >> 2);
-  if (threadIdx.x == 0) tc::mbar_arrive_expect_tx(bar, (uint32_t)(D2_CLUSTER * 32 * TG_N * 4));   // four sources x 32 rows x 64 utterances
   float v[32];
+#if AR_BULKX
+  // Staged form: the 32 rows for peer r leave as ONE bulk copy shared::cta -> shared::cluster (about 20 B/clk; the per-thread st.async
+  // form moved 6 B/clk), the CTA's own rows go straight into its receive block.  Block layout [32 rows][TG_PART_LD] on both sides.
+  constexpr uint32_t BLK = 32 * TG_PART_LD * 4;
+  if (threadIdx.x == 0) tc::mbar_arrive_expect_tx(bar, 3u * BLK);
+  tc::tmem_ld32(tmem + ((uint32_t)(32 * owner) << 16) + col + col0, v);
+  tc::tmem_ld_wait();
+  tc::tc_fence_before();
+  float* blk = (uint32_t)owner == my_rank ? recv + (size_t)my_rank * 32 * TG_PART_LD : stg + (size_t)(((uint32_t)owner - my_rank - 1u) & 3u) * 32 * TG_PART_LD;
+  float* dst = blk + (size_t)lane * TG_PART_LD + col0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) *reinterpret_cast<float4*>(dst + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the bulk copy reads the block through the async proxy
+  wsync();
+  if (threadIdx.x < 3) {
+    const uint32_t peer = (my_rank + 1u + threadIdx.x) & 3u;
+    const uint32_t src = tc::smem_u32(stg + (size_t)threadIdx.x * 32 * TG_PART_LD);
+    const uint32_t dstc = tc::mapa(tc::smem_u32(recv + (size_t)my_rank * 32 * TG_PART_LD), peer), rb = tc::mapa(tc::smem_u32(bar), peer);
+    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dstc), "r"(src), "r"(BLK), "r"(rb) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the block may be overwritten by the next exchange
+  }
+#else
+  if (threadIdx.x == 0) tc::mbar_arrive_expect_tx(bar, (uint32_t)(D2_CLUSTER * 32 * TG_N * 4));   // four sources x 32 rows x 64 utterances
   tc::tmem_ld32(tmem + ((uint32_t)(32 * owner) << 16) + col + col0, v);
   tc::tmem_ld_wait();
   tc::tc_fence_before();
@@ -287,6 +303,8 @@ __device__ __forceinline__ void ar_push_partials(uint32_t tmem, uint32_t col, fl
   const uint32_t rb = tc::mapa(tc::smem_u32(bar), (uint32_t)owner);
 #pragma unroll
   for (int i = 0; i < 8; ++i) st_async_v4(dst + 16u * i, make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]), rb);
+  (void)stg;
+#endif
 }
 
 // LSTM pointwise tail on the received partials (same summation order as lstm_tail of dec_shared.cuh: ranks 0..3, then the bias).
@@ -774,7 +792,7 @@ __host__ __device__ inline bool ar_proj_fast(const D2Dims& d) {
   const int rows_per = (d.M + 1 + D2_CLUSTER - 1) / D2_CLUSTER, rq = d.P / D2_CLUSTER;
   const int w1_off = 2 * ((d.M + 4) & ~3) + 2 * d.P + 2 * rq + 6 * (rq > 64 ? rq : 64);
   const bool w1_smem = (d.M >> 2) <= 32 && (w1_off & 3) == 0 && w1_off + rq * d.M <= TG_M * TG_PART_LD;
-  return d.H == 1024 && rows_per <= AR_WRES_ROWS + AR_WTM_ROWS + 1 && w1_off + (w1_smem ? rq * d.M : 0) + 8 * 2 * 24 <= TG_M * TG_PART_LD;
+  return d.H == 1024 && rows_per <= AR_PROJ_ROWS && w1_off + (w1_smem ? rq * d.M : 0) + 8 * 2 * 24 <= TG_M * TG_PART_LD;
 }
 
 // ------------------------------------------------------------------------------------------ output stage (all 8 worker warps)
@@ -830,15 +848,18 @@ __device__ bool ar_output(const D2Dims& d, const D2Weights& w, const D2State& s,
     const int rpw = (nr + NW - 1) / NW, rb = r0 + pw * rpw, re = min(r0 + nr, rb + rpw);
     float* pr = mel_s + w1_off + (w1_smem ? rq * M : 0);   // [8 warps][2][24] partial sums of the fast path
     if (proj_fast) {
-      // K split over the threads (this thread: float4 index k of every row), weights from shared memory (rows 0..11), tensor memory
-      // (12..19) and L2 (row 20): the only L2 round trip on the chain is the two input rows (8 KB per CTA) and that last row
+      // K split over the threads (this thread: float4 index k of every row), weights from shared memory (first AR_WRES_ROWS rows), tensor memory (next 8)
+      // and L2 (the rest), all requested at once: one L2 round trip on the chain
       const int k = tid;
       float tw[4 * AR_WTM_ROWS];
       tc::tmem_ld32(tmem + ((uint32_t)(32 * (pw & 3)) << 16) + AR_COL_WP + 32u * (uint32_t)(pw >> 2), tw);
       const float4 xa = __ldcg(reinterpret_cast<const float4*>(s.projin + (size_t)b0 * KP) + k);
       const float4 xb = __ldcg(reinterpret_cast<const float4*>(s.projin + (size_t)min(b0 + 1, B - 1) * KP) + k);
-      float4 wl = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (nr > AR_WRES_ROWS + AR_WTM_ROWS) wl = AR_LDW(reinterpret_cast<const float4*>(w.Wproj + (size_t)(r0 + AR_WRES_ROWS + AR_WTM_ROWS) * KP) + k);
+      constexpr int NL2 = AR_PROJ_ROWS - AR_WRES_ROWS - AR_WTM_ROWS;
+      float4 wl[NL2];
+#pragma unroll
+      for (int i = 0; i < NL2; ++i)
+        wl[i] = AR_LDW(reinterpret_cast<const float4*>(w.Wproj + (size_t)(r0 + min(AR_WRES_ROWS + AR_WTM_ROWS + i, nr - 1)) * KP) + k);
       tc::tmem_ld_wait();
       const float4* ws = reinterpret_cast<const float4*>(sm.wres) + k;
 #pragma unroll
@@ -850,7 +871,7 @@ __device__ bool ar_output(const D2Dims& d, const D2Weights& w, const D2State& s,
           float4 wv;
           if (ri < AR_WRES_ROWS) wv = ws[ri * (1024 / 4)];
           else if (ri < AR_WRES_ROWS + AR_WTM_ROWS) wv = make_float4(tw[4 * (ri - AR_WRES_ROWS)], tw[4 * (ri - AR_WRES_ROWS) + 1], tw[4 * (ri - AR_WRES_ROWS) + 2], tw[4 * (ri - AR_WRES_ROWS) + 3]);
-          else if (ri == AR_WRES_ROWS + AR_WTM_ROWS) wv = wl;
+          else if (ri < AR_PROJ_ROWS) wv = wl[ri - AR_WRES_ROWS - AR_WTM_ROWS < 0 ? 0 : ri - AR_WRES_ROWS - AR_WTM_ROWS];
           else wv = make_float4(0.f, 0.f, 0.f, 0.f);
           v[i] = fmaf(wv.w, xa.w, fmaf(wv.z, xa.z, fmaf(wv.y, xa.y, wv.x * xa.x)));
           v[8 + i] = fmaf(wv.w, xb.w, fmaf(wv.z, xb.z, fmaf(wv.y, xb.y, wv.x * xb.x)));
@@ -989,7 +1010,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
                                                 // frame 0 counts as passed.  Teacher forcing has three barriers per frame (no X)
     sm.ctl[1] = 0u; sm.ctl[2] = 0u; sm.ctl[4] = 0u; sm.ctl[5] = 0u;
     for (int i = 8; i < 15; ++i) sm.ctl[i] = 0u;   // 8 cluster counter (barrier mode 2), 9 fired stop gates, 10 done count, 11-12 fired flags, 13-14 lengths
-    sm.ctl[3] = (unsigned)build_program(d, (int)rank, sm.prog, (io.debug_barrier & 256) != 0);   // (experiment bit 256: round-2 order)
+    sm.ctl[3] = (unsigned)build_program(d, (int)rank, sm.prog);
   }
   if (warp == 9) tc::tmem_alloc<512>(sm.tmem_slot);   // warp 9 owns alloc + dealloc
   if (worker) {
@@ -1056,8 +1077,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
         if (x_n < w_n) {
           const KbEnt en = sm.prog[x_e];
           // teacher forcing: the prenet columns of every frame exist before the launch (bulk prenet), three barriers per frame (Q, C, R)
-          const int need = en.gate == G_RP ? (TF ? 3 : 4) * x_f
-                                           : (TF ? (en.gate == G_X ? -1 : 3 * x_f + (int)en.gate) : 4 * x_f + (int)en.gate + 1);
+          const int need = TF ? (en.gate == G_X ? -1 : 3 * x_f + (int)en.gate) : 4 * x_f + (int)en.gate + 1;
           const unsigned have = ld_acquire_cta(sm.ctl);
           if ((int)have >= need) {
             if (have != fenced_gate) { asm volatile("fence.proxy.async;" ::: "memory"); fenced_gate = have; }   // peers' generic stores -> TMA reads
@@ -1242,7 +1262,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
       prof_mark(8);
       {
         const HOut ho{s.xatt + (size_t)nxt * 2 * pa, d.KattP, d.P + d.EF, pa, s.xdec + (size_t)cur * 2 * pd, d.KdecP, 0, pd, s.att_h_rm, d.H, 0};
-        ar_push_partials(tmem, AR_COL_ATT, sm.part, sm.bars + B_RV, rank);
+        ar_push_partials(tmem, AR_COL_ATT, sm.part, sm.stg, sm.bars + B_RV, rank);
         if (!tc::mbar_wait_cluster(sm.bars + B_RV, rv_phase)) fail = true;
         rv_phase ^= 1u;
         ar_lstm_tail(sm.part, unit0, w.batt, d.H, sm.c_att, B, ho, sm.h_s, att_keep, hdrop, io.seed, rb_att, sav_att);
@@ -1264,7 +1284,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
       prof_mark(9);
       {
         const HOut ho{s.xdec + (size_t)nxt * 2 * pd, d.KdecP, d.H + d.EF + d.C, pd, nullptr, 0, 0, 0, TF ? nullptr : s.projin, d.KprojP, 0};
-        ar_push_partials(tmem, AR_COL_DEC, sm.part, sm.bars + B_RV, rank);
+        ar_push_partials(tmem, AR_COL_DEC, sm.part, sm.stg, sm.bars + B_RV, rank);
         if (!tc::mbar_wait_cluster(sm.bars + B_RV, rv_phase)) fail = true;
         rv_phase ^= 1u;
         ar_lstm_tail(sm.part, unit0, w.bdec, d.H, sm.c_dec, B, ho, sm.h_s, rnn_keep, hdrop, io.seed, rb_dec, sav_dec);
