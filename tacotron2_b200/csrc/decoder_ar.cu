@@ -396,8 +396,8 @@ __device__ __forceinline__ void xreduce(float* v) {
 // Short dense layer for the two utterances of a cluster, 8 rows per warp and pass (as rows_short<8, NK, WS> of dec_shared.cuh), with
 // the sixteen sums of a pass reduced by value halving.
 template <int NK, bool WS>
-__device__ __noinline__ void ar_rows8(const float* __restrict__ W, int ldw, int K4, int rb, int re, const float* x0, const float* x1, float* y,
-                                      int ybase, int ys) {
+__device__ __forceinline__ void ar_rows8_body(const float* __restrict__ W, int ldw, int K4, int rb, int re, const float* x0, const float* x1, float* y,
+                                              int ybase, int ys) {
   const int lane = threadIdx.x & 31;
   float4 xa[NK], xb[NK];
 #pragma unroll
@@ -435,6 +435,11 @@ __device__ __noinline__ void ar_rows8(const float* __restrict__ W, int ldw, int 
     if ((lane & 1) == 0 && r + i < re) y[j * ys + r + i - ybase] = v[0];
   }
   __syncwarp();
+}
+template <int NK, bool WS>
+__device__ __noinline__ void ar_rows8(const float* __restrict__ W, int ldw, int K4, int rb, int re, const float* x0, const float* x1, float* y,
+                                      int ybase, int ys) {
+  ar_rows8_body<NK, WS>(W, ldw, K4, rb, re, x0, x1, y, ybase, ys);
 }
 
 // ------------------------------------------------------------------------------------------ attention
@@ -922,8 +927,14 @@ __device__ bool ar_output(const D2Dims& d, const D2Weights& w, const D2State& s,
   const int rpw = (rq + NW - 1) / NW, rb = pr0 + pw * rpw, re = min(pr0 + rq, rb + rpw);
   float* y1 = y_s + 2 * YS;
   float* y2 = y_s + 4 * YS;
+  // prenet layer 2 reads 64 KB of weights per CTA from L2; they depend on nothing, so when the shape is the usual one (8 rows per warp,
+  // 256 columns) this lane's sixteen float4 are requested before the wait for the all-gather of layer 1's output
+  const bool w2_pre = AR_XRED && w1_smem && rq == 64 && P == 256;
   if (!tc::mbar_wait_cluster(mel_bar, cphase)) ok = false;
-  if (w1_smem) {
+  if (w2_pre) {
+    if (!tc::mbar_wait(wbar, cphase)) ok = false;
+    ar_rows8_body<1, true>(w1_s - (ptrdiff_t)pr0 * M, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
+  } else if (w1_smem) {
     if (!tc::mbar_wait(wbar, cphase)) ok = false;
 #if AR_XRED
     ar_rows8<1, true>(w1_s - (ptrdiff_t)pr0 * M, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
@@ -941,17 +952,51 @@ __device__ bool ar_output(const D2Dims& d, const D2Weights& w, const D2State& s,
     st_async_all(p1_s + j * P + r, (v > 0.f && keep) ? v * pscale : 0.f, p1_bar);
   }
   mark(5);
-  if (!tc::mbar_wait_cluster(p1_bar, cphase)) ok = false;
+  const uint32_t p1_phase = cphase;
   cphase ^= 1u;
   const long long pa = (long long)D2_BP * d.KattP;
   __nv_bfloat16* xa = s.xatt + (size_t)nxt * 2 * pa;
   const bool vec = (rq & 7) == 0 && (d.KattP & 7) == 0;
 #if AR_XRED
-  if ((P >> 2) <= 64) ar_rows8<2, false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
+  if (w2_pre) {
+    float4 w2v[8][2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float4* wp = reinterpret_cast<const float4*>(w.W2 + (size_t)(rb + i) * P) + lane;
+      w2v[i][0] = AR_LDW(wp); w2v[i][1] = AR_LDW(wp + 32);
+    }
+    if (!tc::mbar_wait_cluster(p1_bar, p1_phase)) ok = false;
+    float4 p1a[2], p1b[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      p1a[k] = *reinterpret_cast<const float4*>(p1_s + 4 * (lane + 32 * k));
+      p1b[k] = *reinterpret_cast<const float4*>(p1_s + P + 4 * (lane + 32 * k));
+    }
+    float v[16];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        a0 = fmaf(w2v[i][k].x, p1a[k].x, a0); a0 = fmaf(w2v[i][k].y, p1a[k].y, a0); a0 = fmaf(w2v[i][k].z, p1a[k].z, a0); a0 = fmaf(w2v[i][k].w, p1a[k].w, a0);
+        a1 = fmaf(w2v[i][k].x, p1b[k].x, a1); a1 = fmaf(w2v[i][k].y, p1b[k].y, a1); a1 = fmaf(w2v[i][k].z, p1b[k].z, a1); a1 = fmaf(w2v[i][k].w, p1b[k].w, a1);
+      }
+      v[i] = a0; v[8 + i] = a1;
+    }
+    xreduce<16>(v);
+    const int q = lane >> 1;
+    if ((lane & 1) == 0) y2[(q >> 3) * YS + rb + (q & 7) - pr0] = v[0];
+    __syncwarp();
+  } else {
+    if (!tc::mbar_wait_cluster(p1_bar, p1_phase)) ok = false;
+    if ((P >> 2) <= 64) ar_rows8<2, false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
+    else rows_dot2<false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
+  }
 #else
+  if (!tc::mbar_wait_cluster(p1_bar, p1_phase)) ok = false;
   if ((P >> 2) <= 64) rows_short<8, 2, false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
-#endif
   else rows_dot2<false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
+#endif
 #pragma unroll 1
   for (int r = rb + (lane >> 1); r < re; r += 16) {
     float v = 0.f;
