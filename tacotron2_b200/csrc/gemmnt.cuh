@@ -25,6 +25,10 @@ struct GemmNtArgs {
   CUtensorMap a_map2, b_map2;
   int Kin2;
   int b_row_step;               // B-operand row coordinate of N-tile nt is nt*b_row_step (0: nt*NT) -- rows interleaved with other data
+  // mn = 1: both operands are read MN-major from channels-last tensors [2][Kout][Kin][rows] (maps from gemmnt_make_map_cl: dims
+  // {rows, Kin, Kout, 2}, box {64, 64, 1, planes}): the contraction index kin is then an OUTER TMA coordinate, so the per-z shift may be
+  // any integer (conv taps need no shifted copies) and neither operand needs a K-major transpose.  No second segment, no z row offsets.
+  int mn;
 };
 
 struct GemmNtOut {
@@ -41,6 +45,9 @@ int gemmnt_launch(const GemmNtArgs& a, const GemmNtOut& o, cudaStream_t st);
 // Operand maps for a K-major bf16 (hi,lo) matrix stored as [2][rows][Kout][kin_ld] (kin contiguous, kin_ld % 8 == 0).
 int gemmnt_make_map(CUtensorMap* m, const __nv_bfloat16* base, int Kin, int kin_ld, int Kout, int rows, long long plane_elems,
                     int box_rows, int npass);
+
+// Operand map for a channels-last bf16 (hi,lo) tensor [2][Kout][Kin][rows] (rows contiguous, rows % 8 == 0), read MN-major (a.mn = 1).
+int gemmnt_make_map_cl(CUtensorMap* m, const __nv_bfloat16* base, int Kin, int Kout, int rows, long long plane_elems, int npass);
 
 // Batched transposes into K-major operands.  Batch bb reads src + bb*src_bstride ([R][C], row stride ld) and writes
 // dst[plane][c][bb*dst_boff + r] for r < R_ld (zeros for r >= R); dst row stride dst_ld, plane stride dst_plane elements.
