@@ -410,15 +410,31 @@ __global__ void condition_bwd_kernel(const float* __restrict__ dmem, const float
   }
 }
 // d speaker_embedding[s][c] = sum over utterances with speaker s, all positions, of d_enc  (one block per (s), thread per c)
-__global__ void speaker_grad_kernel(const float* __restrict__ d_enc, const long long* __restrict__ spk, int B, int L, int E, float* __restrict__ out) {
-  const int s = blockIdx.x;
-  for (int c = threadIdx.x; c < E; c += blockDim.x) {
-    float acc = 0.f;
-    for (int b = 0; b < B; ++b) {
+// grid (speakers, ceil(E / 32)): warp w sums the utterances b = w, w + 8, ... of speaker s over all positions for 32 columns (128-byte
+// coalesced rows), the eight warp sums are added in a fixed order (deterministic).  The one-CTA-per-speaker form took 0.8 ms at C3.
+__global__ void __launch_bounds__(256) speaker_grad_kernel(const float* __restrict__ d_enc, const long long* __restrict__ spk, int B, int L, int E,
+                                                           float* __restrict__ out) {
+  __shared__ float red[8][33];
+  const int s = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, c = blockIdx.y * 32 + lane;
+  float acc = 0.f;
+  if (c < E) {
+    for (int b = warp; b < B; b += 8) {
       if (spk[b] != s) continue;
-      for (int l = 0; l < L; ++l) acc += d_enc[((size_t)b * L + l) * E + c];
+      const float* p = d_enc + (size_t)b * L * E + c;
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+      int l = 0;
+      for (; l + 3 < L; l += 4) { a0 += p[(size_t)l * E]; a1 += p[(size_t)(l + 1) * E]; a2 += p[(size_t)(l + 2) * E]; a3 += p[(size_t)(l + 3) * E]; }
+      for (; l < L; ++l) a0 += p[(size_t)l * E];
+      acc += (a0 + a1) + (a2 + a3);
     }
-    out[(size_t)s * E + c] = acc;
+  }
+  red[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0 && c < E) {
+    float t = red[0][lane];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) t += red[w][lane];
+    out[(size_t)s * E + c] = t;
   }
 }
 // description path: dpre[b][j] = (sum_l dmem[b][l][E+j]) * (1 - dvec^2), dvec = memory[b][0][E+j]
@@ -470,7 +486,7 @@ int condition_bwd_launch(const float* dmem, const float* mem, int speaker, float
   return T2_OK;
 }
 int speaker_grad_launch(const float* d_enc, const long long* spk, int B, int L, int E, int nspk, float* out, cudaStream_t st) {
-  speaker_grad_kernel<<<nspk, 256, 0, st>>>(d_enc, spk, B, L, E, out);
+  speaker_grad_kernel<<<dim3((unsigned)nspk, (unsigned)((E + 31) / 32)), 256, 0, st>>>(d_enc, spk, B, L, E, out);
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }

@@ -76,65 +76,101 @@ struct PrenetArgs {
   __nv_bfloat16* out_b;  // mode 2: bf16 (hi,lo) [T+1][2][D2_BP][P] for the tensor-core decoder
   float* p1_out;         // optional [N][P]: layer-1 output after dropout (training tape)
 };
-#define PN_ROWS 8
+// 32 rows per CTA, both layers as shared-memory tiled products: thread (ty = warp, tx = lane) accumulates rows 4 ty .. 4 ty + 3 for the
+// outputs tx + 32 j; the inputs sit transposed in shared memory (one broadcast LDS.128 per k for the four rows), the weights pass
+// through a [32 k][P] tile (filled with coalesced 128-byte row pieces, read conflict-free).  Products are added in ascending k as before.
+#define PN_ROWS 32
+#define PN_KC 32
+__host__ __device__ inline size_t prenet_smem_bytes(int M, int P) { return ((size_t)M * PN_ROWS + (size_t)P * PN_ROWS + (size_t)PN_KC * (P + 1)) * sizeof(float); }
 __global__ void __launch_bounds__(256) prenet_rows_kernel(PrenetArgs a) {
-  extern __shared__ float sh[];  // xs[PN_ROWS][M] | hs[PN_ROWS][P]
-  float* xs = sh;
-  float* hs = sh + PN_ROWS * a.M;
-  const float scale = 1.0f / (1.0f - a.p);
+  extern __shared__ float sh[];
   const int M = a.M, P = a.P;
+  float* xT = sh;                       // [M][PN_ROWS]
+  float* hT = xT + (size_t)M * PN_ROWS; // [P][PN_ROWS]   layer-1 output, transposed
+  float* Ws = hT + (size_t)P * PN_ROWS; // [PN_KC][P + 1]
+  const float scale = 1.0f / (1.0f - a.p);
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int NJ = P / 32;                // outputs per thread (P % 32 == 0, P <= 256: checked by the callers' shapes)
   for (int n0 = blockIdx.x * PN_ROWS; n0 < a.N; n0 += gridDim.x * PN_ROWS) {
+    __syncthreads();
     for (int i = threadIdx.x; i < PN_ROWS * M; i += blockDim.x) {
-      const int n = n0 + i / M, c = i % M;
+      const int r = i / M, cidx = i - r * M, n = n0 + r;
       float v = 0.f;
       if (n < a.N) {
-        if (a.mode == 0) v = a.x[(size_t)n * M + c];
-        else { const int t = n / a.B, b = n % a.B; if (t > 0) v = a.x[((size_t)b * a.T + (t - 1)) * M + c]; }
+        if (a.mode == 0) v = a.x[(size_t)n * M + cidx];
+        else { const int t = n / a.B, bb = n % a.B; if (t > 0) v = a.x[((size_t)bb * a.T + (t - 1)) * M + cidx]; }
       }
-      xs[i] = v;
+      xT[cidx * PN_ROWS + r] = v;
     }
-    __syncthreads();
     for (int layer = 0; layer < 2; ++layer) {
       const float* W = layer ? a.W2 : a.W1;
       const int K = layer ? P : M;
-      const float* in = layer ? hs : xs;
-      for (int o = threadIdx.x; o < P; o += blockDim.x) {
-        float acc[PN_ROWS];
+      const float* inT = layer ? hT : xT;
+      float acc[8][4];
 #pragma unroll
-        for (int r = 0; r < PN_ROWS; ++r) acc[r] = 0.f;
-        for (int k = 0; k < K; ++k) {
-          const float w = __ldg(W + (size_t)o * K + k);
+      for (int j = 0; j < 8; ++j) { acc[j][0] = 0.f; acc[j][1] = 0.f; acc[j][2] = 0.f; acc[j][3] = 0.f; }
+      for (int k0 = 0; k0 < K; k0 += PN_KC) {
+        __syncthreads();   // the previous tile (and, first time, the inputs) are done with / in place
+        for (int o = ty; o < P; o += 8) Ws[tx * (P + 1) + o] = (k0 + tx < K) ? __ldg(W + (size_t)o * K + k0 + tx) : 0.f;
+        __syncthreads();
+        const int kn = min(PN_KC, K - k0);
+#pragma unroll 4
+        for (int kk = 0; kk < kn; ++kk) {
+          const float4 x4 = *reinterpret_cast<const float4*>(inT + (size_t)(k0 + kk) * PN_ROWS + 4 * ty);
 #pragma unroll
-          for (int r = 0; r < PN_ROWS; ++r) acc[r] = fmaf(w, in[r * K + k], acc[r]);
-        }
-#pragma unroll
-        for (int r = 0; r < PN_ROWS; ++r) {
-          const int n = n0 + r;
-          if (n >= a.N) continue;
-          size_t kidx; unsigned long long ridx;
-          if (a.mode == 0) { kidx = (size_t)n * P + o; ridx = ((unsigned long long)n * 2 + layer) * P + o; }
-          else {
-            const int t = n / a.B, b = n % a.B;
-            kidx = (((size_t)t * 2 + layer) * a.B + b) * P + o;
-            ridx = kidx;
-          }
-          const unsigned char* km = layer ? a.k2 : a.k1;
-          const bool keep = km ? (km[kidx] != 0) : rng_keep(a.seed, ridx, a.p);
-          const float v = (acc[r] > 0.f && keep) ? acc[r] * scale : 0.f;
-          if (layer == 0) { hs[r * P + o] = v; if (a.p1_out) a.p1_out[(size_t)n * P + o] = v; }  // each thread writes only its own o
-          else if (a.mode == 0) a.out[(size_t)n * P + o] = v;
-          else {
-            const int t = n / a.B, b = n % a.B;
-            __nv_bfloat16 hi, lo;
-            tc::split_bf16(v, hi, lo);
-            a.out_b[(((size_t)t * 2 + 0) * D2_BP + b) * P + o] = hi;
-            a.out_b[(((size_t)t * 2 + 1) * D2_BP + b) * P + o] = lo;
+          for (int j = 0; j < 8; ++j) {
+            if (j < NJ) {
+              const float w = Ws[kk * (P + 1) + tx + 32 * j];
+              acc[j][0] = fmaf(w, x4.x, acc[j][0]); acc[j][1] = fmaf(w, x4.y, acc[j][1]);
+              acc[j][2] = fmaf(w, x4.z, acc[j][2]); acc[j][3] = fmaf(w, x4.w, acc[j][3]);
+            }
           }
         }
       }
-      __syncthreads();
+      const unsigned char* km = layer ? a.k2 : a.k1;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (j >= NJ) continue;
+        const int o = tx + 32 * j;
+        float v4[4];
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr) {
+          const int n = n0 + 4 * ty + rr;
+          float v = 0.f;
+          if (n < a.N) {
+            size_t kidx; unsigned long long ridx;
+            if (a.mode == 0) { kidx = (size_t)n * P + o; ridx = ((unsigned long long)n * 2 + layer) * P + o; }
+            else {
+              const int t = n / a.B, bb = n % a.B;
+              kidx = (((size_t)t * 2 + layer) * a.B + bb) * P + o;
+              ridx = kidx;
+            }
+            const bool keep = km ? (km[kidx] != 0) : rng_keep(a.seed, ridx, a.p);
+            v = (acc[j][rr] > 0.f && keep) ? acc[j][rr] * scale : 0.f;
+            if (layer == 0) { if (a.p1_out) a.p1_out[(size_t)n * P + o] = v; }
+            else if (a.mode == 0) a.out[(size_t)n * P + o] = v;
+            else {
+              const int t = n / a.B, bb = n % a.B;
+              __nv_bfloat16 hi, lo;
+              tc::split_bf16(v, hi, lo);
+              a.out_b[(((size_t)t * 2 + 0) * D2_BP + bb) * P + o] = hi;
+              a.out_b[(((size_t)t * 2 + 1) * D2_BP + bb) * P + o] = lo;
+            }
+          }
+          v4[rr] = v;
+        }
+        if (layer == 0) *reinterpret_cast<float4*>(hT + (size_t)o * PN_ROWS + 4 * ty) = make_float4(v4[0], v4[1], v4[2], v4[3]);
+      }
     }
   }
+}
+static int prenet_rows_launch(const PrenetArgs& pa, cudaStream_t st) {
+  T2_REQUIRE(pa.P % 32 == 0 && pa.P <= 256, T2_ERR_UNSUPPORTED, "prenet: prenet_dim %d (multiple of 32, at most 256)", pa.P);
+  const size_t smem = prenet_smem_bytes(pa.M, pa.P);
+  T2_CHECK_CUDA(cudaFuncSetAttribute(prenet_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  prenet_rows_kernel<<<std::min((pa.N + PN_ROWS - 1) / PN_ROWS, 148 * 16), 256, smem, st>>>(pa);
+  T2_CHECK_CUDA(cudaGetLastError());
+  return T2_OK;
 }
 
 // bf16 (hi,lo) planes of [W_ih | W_hh] with rows permuted so that each 128-row tile holds 32 hidden units and
@@ -736,8 +772,7 @@ static int decode2_impl(t2_ctx* c, bool tf, const float* memory, const float* pm
   if (tf) {
     if (!tape) T2_CHECK_CUDA(cudaMemsetAsync(tfp, 0, (size_t)(T + 1) * 2 * D2_BP * d.P * sizeof(__nv_bfloat16), st));
     PrenetArgs pa{mel_target, c->d2w.W1, c->d2w.W2, prenet_keep, prenet_keep, seed, d.p_prenet, (T + 1) * B, d.M, d.P, 2, B, T, nullptr, tfp, tape ? tape->p1 : nullptr};
-    prenet_rows_kernel<<<std::min(((T + 1) * B + PN_ROWS - 1) / PN_ROWS, 148 * 4), 256, PN_ROWS * (d.M + d.P) * sizeof(float), st>>>(pa);
-    T2_CHECK_CUDA(cudaGetLastError());
+    RC(prenet_rows_launch(pa, st));
     io.teacher_forcing = 1; io.stop_enabled = 0;
   } else {
     io.teacher_forcing = 0; io.stop_enabled = 1; io.min_frames = min_frames;
@@ -892,10 +927,7 @@ extern "C" int t2_prenet_fwd(t2_ctx* c, const float* x, const unsigned char* kee
   T2_REQUIRE(x && out && N > 0, T2_ERR_ARG, "t2_prenet_fwd: bad argument");
   (void)ws; (void)ws_bytes;
   PrenetArgs pa{x, c->d2w.W1, c->d2w.W2, keep1, keep2, seed, c->cfg.dropout, N, c->M, c->P, 0, 0, 0, out, nullptr, nullptr};
-  prenet_rows_kernel<<<std::min((N + PN_ROWS - 1) / PN_ROWS, 148 * 4), 256, PN_ROWS * (c->M + c->P) * sizeof(float),
-                       (cudaStream_t)stream>>>(pa);
-  T2_CHECK_CUDA(cudaGetLastError());
-  return T2_OK;
+  return prenet_rows_launch(pa, (cudaStream_t)stream);
 }
 
 static int postnet_impl(t2_ctx* c, const float* mels, int t_stride, int B, int T, int train, const unsigned char* keep, float* out,
