@@ -121,34 +121,43 @@ __device__ void attention_bwd_phase_tc(const D2Dims& d, const DBTape& tp, const 
       *reinterpret_cast<uint4*>(toep + 16384 + off) = *reinterpret_cast<const uint4*>(lo);
     }
     ABW_MARK(3);
-    // ---- g_w[l] += d ctx . memory[l]: warp per position, two positions in flight per warp (8 independent 16-byte loads per lane)
+    // ---- g_w[l] += d ctx . memory[l]: warp per position, four positions in flight per warp (16 independent 16-byte loads per lane: the
+    // phase is a chain of L2 round trips, one per group of positions -- two per group took 6-7 trips, 3.0 us)
     {
       const float* mem = tp.memory + (size_t)b * L * EF;
       const int nq = EF / 4;
 #pragma unroll 1
-      for (int li = 2 * warp; li < nl; li += 2 * (D2_THREADS / 32)) {
-        const int li1 = min(li + 1, nl - 1);
-        const float4* mp0 = reinterpret_cast<const float4*>(mem + (size_t)(l0 + li) * EF);
-        const float4* mp1 = reinterpret_cast<const float4*>(mem + (size_t)(l0 + li1) * EF);
-        float s0 = 0.f, s1 = 0.f;
+      for (int li = 4 * warp; li < nl; li += 4 * (D2_THREADS / 32)) {
+        const float4* mp[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) mp[r] = reinterpret_cast<const float4*>(mem + (size_t)(l0 + min(li + r, nl - 1)) * EF);
+        float sacc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 1
         for (int c4 = lane; c4 < nq; c4 += 128) {
-          float4 m0[4], m1[4];
+          float4 m[4][4];
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             const int cc = min(c4 + 32 * u, nq - 1);
-            m0[u] = __ldg(mp0 + cc); m1[u] = __ldg(mp1 + cc);
+#pragma unroll
+            for (int r = 0; r < 4; ++r) m[r][u] = __ldg(mp[r] + cc);
           }
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             if (c4 + 32 * u >= nq) continue;
             const float4 d4 = *reinterpret_cast<const float4*>(dctx + (c4 + 32 * u) * 4);
-            s0 = fmaf(m0[u].x, d4.x, s0); s0 = fmaf(m0[u].y, d4.y, s0); s0 = fmaf(m0[u].z, d4.z, s0); s0 = fmaf(m0[u].w, d4.w, s0);
-            s1 = fmaf(m1[u].x, d4.x, s1); s1 = fmaf(m1[u].y, d4.y, s1); s1 = fmaf(m1[u].z, d4.z, s1); s1 = fmaf(m1[u].w, d4.w, s1);
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+              sacc[r] = fmaf(m[r][u].x, d4.x, sacc[r]); sacc[r] = fmaf(m[r][u].y, d4.y, sacc[r]);
+              sacc[r] = fmaf(m[r][u].z, d4.z, sacc[r]); sacc[r] = fmaf(m[r][u].w, d4.w, sacc[r]);
+            }
           }
         }
-        s0 = warp_sum(s0); s1 = warp_sum(s1);
-        if (lane == 0) { gw[li] += s0; if (li + 1 < nl) gw[li + 1] += s1; }
+#pragma unroll
+        for (int r = 0; r < 4; ++r) sacc[r] = warp_sum(sacc[r]);
+        if (lane == 0) {
+#pragma unroll
+          for (int r = 0; r < 4; ++r) if (li + r < nl) gw[li + r] += sacc[r];
+        }
       }
     }
     __syncthreads();
