@@ -375,11 +375,211 @@ __global__ void __launch_bounds__(256, 1) bilstm_bwd_cluster_kernel(const float*
 }
 }  // namespace
 
+// ------------------------------------------------------------------------------------------ the same on tcgen05 (Hh = 256)
+// One cluster of 8 CTAs per (direction, 16 utterances).  CTA `rank` owns the 128 gate rows of its 32 units: it forms their gate
+// gradients dg (pointwise, from the tape) and contracts THEM -- local data, no all-gather -- with the matching 128 rows of W_hh:
+// part[unit m of all 256][utterance] = sum_{own rows} W_hh[row][m] dg[row][utterance]  (A = W_hh rows transposed, bf16 (hi,lo) sw128,
+// 128 KB resident; B = dg, 8 KB; two 128-row accumulators in tensor memory).  The recurrent d h of a CTA's own units is the sum of the
+// eight CTAs' partial rows for them: warp w holds exactly the block for rank w (TMEM lane quarter w % 4 of accumulator w / 4), stages
+// it, and one 2 KB bulk copy per peer delivers it, counted on the receiver's transaction barrier.  No cluster barrier per character;
+// the tape values of the next step are requested one step ahead.  The CUDA-core form above takes 20 us per character.
+namespace {
+#define BBT_NB 16
+__host__ __device__ inline size_t bilstm_bwd_tc_smem() { return 1024 + 131072 + 8192 + 16384 + 32768 + 256; }
+__global__ void __launch_bounds__(256, 1) bilstm_bwd_tc_kernel(const float* __restrict__ sav, const float* __restrict__ Whh,
+                                                               const long long* __restrict__ lens, const float* __restrict__ d_out,
+                                                               float* __restrict__ dgates, int B, int L) {
+  constexpr int Hh = 256, UPC = 32, G4 = 4 * Hh;
+  extern __shared__ __align__(1024) uint8_t raw[];
+  uint8_t* base = raw + ((1024u - (tc::smem_u32(raw) & 1023u)) & 1023u);
+  uint8_t* At = base;                                        // [2 M tiles][2 K blocks][hi, lo][128 units x 128 B]
+  uint8_t* Bt = At + 131072;                                 // [2 K blocks][hi, lo][16 utterances x 128 B]
+  float* stg = reinterpret_cast<float*>(Bt + 8192);          // [8 dest ranks][32 units][16]
+  float* recv = stg + 8 * 32 * 16;                           // [2][8 source ranks][32 units][16]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(recv + 2 * 8 * 32 * 16);   // rbar[2], mma
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+  int* len_s = reinterpret_cast<int*>(tmem_slot + 2);
+  const uint32_t rank = tc::cluster_ctarank();
+  const int cid = blockIdx.x / BB_CL, dir = cid & 1, grp = cid >> 1;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  {  // A[m = unit][k = local gate row lr = gate * 32 + ul] = W_hh[gate * Hh + 32 rank + ul][m]
+    const float* W = Whh + (size_t)dir * G4 * Hh;
+#pragma unroll 1
+    for (int i = tid; i < 128 * Hh; i += 256) {
+      const int lr = i >> 8, m = i & 255, g = lr >> 5, ul = lr & 31;
+      __nv_bfloat16 hi, lo;
+      tc::split_bf16(__ldg(W + (size_t)(g * Hh + (int)rank * UPC + ul) * Hh + m), hi, lo);
+      uint8_t* t = At + (size_t)(m >> 7) * 65536 + (size_t)(lr >> 6) * 32768 + tc::sw128_off(m & 127, lr & 63);
+      *reinterpret_cast<__nv_bfloat16*>(t) = hi;
+      *reinterpret_cast<__nv_bfloat16*>(t + 16384) = lo;
+    }
+  }
+  if (tid < BBT_NB) {
+    const int b = grp * BBT_NB + tid;
+    len_s[tid] = b < B ? (int)min((long long)L, max(0ll, lens[b])) : 0;
+  }
+  if (tid == 0) {
+    tc::mbar_init(bars + 0, 1); tc::mbar_init(bars + 1, 1); tc::mbar_init(bars + 2, 1);
+    tc::fence_barrier_init();
+  }
+  if (warp == 0) tc::tmem_alloc<32>(tmem_slot);
+  tc::fence_proxy_async();
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  int maxlen = 0;
+  for (int i = 0; i < BBT_NB; ++i) maxlen = max(maxlen, len_s[i]);
+  tc::cluster_sync();
+
+  const int pu = lane, pb = warp;           // pointwise role: unit pu, utterances pb and pb + 8
+  const int u = (int)rank * UPC + pu;
+  struct Tape { float si, sf, tg, so, c, cp, dout; };
+  auto load_tape = [&](int s, Tape (&tp)[2]) {
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int bl = pb + 8 * j, n = len_s[bl];
+      tp[j] = Tape{0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (s >= 0 && s < n) {
+        const int b = grp * BBT_NB + bl, t = dir ? (n - 1 - s) : s;
+        const float* sv = sav + (((size_t)b * L + t) * 2 + dir) * 5 * Hh + u;
+        tp[j].si = __ldg(sv); tp[j].sf = __ldg(sv + Hh); tp[j].tg = __ldg(sv + 2 * Hh); tp[j].so = __ldg(sv + 3 * Hh); tp[j].c = __ldg(sv + 4 * Hh);
+        if (s > 0) {
+          const int tq = dir ? t + 1 : t - 1;
+          tp[j].cp = __ldg(sav + (((size_t)b * L + tq) * 2 + dir) * 5 * Hh + 4 * Hh + u);
+        }
+        tp[j].dout = __ldg(d_out + ((size_t)b * L + t) * 2 * Hh + dir * Hh + u);
+      }
+    }
+  };
+  Tape cur_t[2];
+  load_tape(maxlen - 1, cur_t);
+  float dc[2] = {0.f, 0.f}, dhr[2] = {0.f, 0.f};
+  uint32_t rph[2] = {0u, 0u}, mph = 0u;
+#pragma unroll 1
+  for (int s = maxlen - 1; s >= 0; --s) {
+    const int buf = s & 1;
+    Tape nxt_t[2];
+    load_tape(s - 1, nxt_t);
+    // ---- pointwise: gate gradients of the own units at forward step s -> global, and (bf16 hi,lo) -> the B tile
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int bl = pb + 8 * j, n = len_s[bl];
+      float dg4[4] = {0.f, 0.f, 0.f, 0.f};
+      if (s < n) {
+        const Tape& tp = cur_t[j];
+        const float dh = tp.dout + dhr[j];
+        const float tc_ = tanhf(tp.c);
+        dg4[3] = dh * tc_ * tp.so * (1.f - tp.so);
+        const float dct = dh * tp.so * (1.f - tc_ * tc_) + dc[j];
+        dg4[0] = dct * tp.tg * tp.si * (1.f - tp.si);
+        dg4[1] = dct * tp.cp * tp.sf * (1.f - tp.sf);
+        dg4[2] = dct * tp.si * (1.f - tp.tg * tp.tg);
+        dc[j] = dct * tp.sf;
+        const int b = grp * BBT_NB + bl, t = dir ? (n - 1 - s) : s;
+        float* o = dgates + (((size_t)b * L + t) * 2 + dir) * G4 + u;
+        o[0] = dg4[0]; o[Hh] = dg4[1]; o[2 * Hh] = dg4[2]; o[3 * Hh] = dg4[3];
+      }
+      if (s > 0) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          __nv_bfloat16 hi, lo;
+          tc::split_bf16(dg4[g], hi, lo);
+          const int lr = g * UPC + pu;
+          uint8_t* t = Bt + (size_t)(lr >> 6) * 4096 + tc::sw128_off(bl, lr & 63);
+          *reinterpret_cast<__nv_bfloat16*>(t) = hi;
+          *reinterpret_cast<__nv_bfloat16*>(t + 2048) = lo;
+        }
+      }
+    }
+    if (s == 0) break;
+    tc::fence_proxy_async();
+    __syncthreads();
+    if (tid == 0) {
+      tc::mbar_arrive_expect_tx(bars + buf, 8u * 2048u);   // the eight partial blocks for the own units of this step
+      tc::tc_fence_after();
+      const uint32_t idesc = tc::idesc_bf16_f32(128, BBT_NB);
+      const uint32_t ab = tc::smem_u32(At), bb = tc::smem_u32(Bt);
+#pragma unroll 1
+      for (int mt = 0; mt < 2; ++mt) {
+        uint32_t acc = 0u;
+#pragma unroll 1
+        for (int kb = 0; kb < 2; ++kb) {
+          const uint64_t ahi = tc::smem_desc_sw128(ab + (uint32_t)mt * 65536u + (uint32_t)kb * 32768u), alo = tc::smem_desc_sw128(ab + (uint32_t)mt * 65536u + (uint32_t)kb * 32768u + 16384u);
+          const uint64_t bhi = tc::smem_desc_sw128(bb + (uint32_t)kb * 4096u), blo = tc::smem_desc_sw128(bb + (uint32_t)kb * 4096u + 2048u);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t adv = (uint64_t)(k * 2);
+            tc::umma_bf16(tmem + 16u * mt, alo + adv, bhi + adv, idesc, acc);
+            tc::umma_bf16(tmem + 16u * mt, ahi + adv, blo + adv, idesc, 1u);
+            tc::umma_bf16(tmem + 16u * mt, ahi + adv, bhi + adv, idesc, 1u);
+            acc = 1u;
+          }
+        }
+      }
+      tc::umma_commit(bars + 2);
+    }
+    if (!tc::mbar_wait(bars + 2, mph)) { /* timeout: results undefined; the caller's parity / status checks catch it */ }
+    mph ^= 1u;
+    tc::tc_fence_after();
+    {  // warp w: units 32 w .. 32 w + 31 of the partial = the block for cluster rank w
+      float v[16];
+      tc::tmem_ld16(tmem + ((uint32_t)(32 * (warp & 3)) << 16) + 16u * (uint32_t)(warp >> 2), v);
+      tc::tmem_ld_wait();
+      float4* dst = reinterpret_cast<float4*>(stg + ((size_t)warp * 32 + lane) * 16);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+    }
+    tc::tc_fence_before();
+    tc::fence_proxy_async();
+    __syncthreads();
+    if (tid < 8) {
+      const uint32_t dst = tc::mapa(tc::smem_u32(recv + ((size_t)buf * 8 + rank) * 32 * 16), (uint32_t)tid);
+      const uint32_t rb = tc::mapa(tc::smem_u32(bars + buf), (uint32_t)tid);
+      asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(dst), "r"(tc::smem_u32(stg + (size_t)tid * 32 * 16)), "r"(2048u), "r"(rb) : "memory");
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the staging block is rewritten next step
+    }
+    tc::mbar_wait_cluster(bars + buf, rph[buf]);
+    rph[buf] ^= 1u;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {   // recurrent d h of (unit pu, utterance pb + 8 j) at step s - 1: the eight partials in rank order
+      const float* r = recv + (size_t)buf * 8 * 32 * 16 + pu * 16 + pb + 8 * j;
+      float a = r[0];
+#pragma unroll
+      for (int src = 1; src < 8; ++src) a += r[src * 32 * 16];
+      dhr[j] = a;
+      cur_t[j] = nxt_t[j];
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::cluster_sync();   // no CTA exits while a peer may still copy into its shared memory
+  if (warp == 0) tc::tmem_dealloc<32>(tmem);
+}
+}  // namespace
+
 int bilstm_bwd_launch(const float* sav, const float* Whh, const long long* lens, const float* d_out, float* dgates, int B, int L, int Hh,
                       cudaStream_t st) {
   const int UPC = Hh / BB_CL;
   T2_REQUIRE(Hh % BB_CL == 0 && UPC == 32, T2_ERR_UNSUPPORTED, "bilstm backward: hidden size %d unsupported (needs Hh == 256)", Hh);
   T2_CHECK_CUDA(cudaMemsetAsync(dgates, 0, (size_t)B * L * 8 * Hh * sizeof(float), st));
+  if (Hh == 256 && !(getenv("T2B200_BILSTM") && !strcmp(getenv("T2B200_BILSTM"), "cuda"))) {   // tensor-core form
+    const size_t smem = bilstm_bwd_tc_smem();
+    T2_CHECK_CUDA(cudaFuncSetAttribute(bilstm_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)(2 * ((B + BBT_NB - 1) / BBT_NB) * BB_CL));
+    cfg.blockDim = dim3(256);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = BB_CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    T2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, bilstm_bwd_tc_kernel, sav, Whh, lens, d_out, dgates, B, L));
+    return T2_OK;
+  }
   const size_t smem = ((size_t)4 * Hh * UPC + (size_t)2 * 4 * Hh * BB_NB + (size_t)UPC * BB_NB + (size_t)8 * BB_NB * UPC) * sizeof(float);
   T2_CHECK_CUDA(cudaFuncSetAttribute(bilstm_bwd_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg{};
