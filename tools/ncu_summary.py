@@ -22,6 +22,8 @@ for r in rows:
         seq.append((name, v / 1e6 if u.startswith("n") else (v / 1e3 if u.startswith("u") else v)))
 idx = [i for i, (n, _) in enumerate(seq) if n.startswith(marker)]
 step = seq[idx[-1]:] if idx else seq
+if len(idx) >= 2 and len(step) < 50:   # the capture window ended a few launches into a new step: take the last complete one
+    step = seq[idx[-2]:idx[-1]]
 agg = collections.defaultdict(lambda: [0, 0.0])
 for n, ms in step:
     agg[n][0] += 1
