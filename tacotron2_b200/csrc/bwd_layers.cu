@@ -663,15 +663,35 @@ __global__ void desc_wgrad_kernel(const float* __restrict__ dpre, const float* _
   }
 }
 // d embedding[row][c] = sum over positions with chars == row (row 0 = padding_idx gets no gradient, model/encoder.py:25)
-__global__ void embedding_grad_kernel(const float* __restrict__ dx, const long long* __restrict__ chars, long long npos, int E, int nrows,
-                                      float* __restrict__ out) {
-  const int row = blockIdx.x;
+// One CTA per table row: warp w scans the positions p = w, w + 8, ... (the index load is a broadcast), lanes own columns lane + 32 j;
+// the eight warp sums are added in warp order (deterministic).  The one-thread-scans-everything form took 0.7 ms at C3.
+#define EG_MAXJ 32   // E <= 1024
+__global__ void __launch_bounds__(256) embedding_grad_kernel(const float* __restrict__ dx, const long long* __restrict__ chars, long long npos,
+                                                             int E, int nrows, float* __restrict__ out) {
+  extern __shared__ float eg_red[];   // [8][E]
+  const int row = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nj = (E + 31) / 32;
+  float acc[EG_MAXJ];
+#pragma unroll
+  for (int j = 0; j < EG_MAXJ; ++j) acc[j] = 0.f;
+  if (row > 0) {
+    for (long long p = warp; p < npos; p += 8) {
+      if (chars[p] != row) continue;
+      const float* src = dx + p * E + lane;
+#pragma unroll
+      for (int j = 0; j < EG_MAXJ; ++j)
+        if (j < nj && lane + 32 * j < E) acc[j] += src[32 * j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < EG_MAXJ; ++j)
+    if (j < nj && lane + 32 * j < E) eg_red[warp * E + lane + 32 * j] = acc[j];
+  __syncthreads();
   for (int c = threadIdx.x; c < E; c += blockDim.x) {
-    float acc = 0.f;
-    if (row > 0)
-      for (long long p = 0; p < npos; ++p)
-        if (chars[p] == row) acc += dx[p * E + c];
-    out[(size_t)row * E + c] = acc;
+    float t = eg_red[c];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) t += eg_red[w * E + c];
+    out[(size_t)row * E + c] = t;
   }
 }
 __global__ void zero_kernel(float* p, long long n) {
@@ -698,7 +718,8 @@ int desc_bwd_launch(const float* dmem, const float* mem, const float* desc, int 
   return T2_OK;
 }
 int embedding_grad_launch(const float* dx, const long long* chars, long long npos, int E, int nrows, float* out, cudaStream_t st) {
-  embedding_grad_kernel<<<nrows, 256, 0, st>>>(dx, chars, npos, E, nrows, out);
+  T2_REQUIRE(E <= 32 * EG_MAXJ, T2_ERR_UNSUPPORTED, "embedding gradient: encoded_dim %d > %d", E, 32 * EG_MAXJ);
+  embedding_grad_kernel<<<nrows, 256, (size_t)8 * E * sizeof(float), st>>>(dx, chars, npos, E, nrows, out);
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }

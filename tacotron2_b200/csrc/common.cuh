@@ -55,15 +55,6 @@ struct Arena {
 __device__ __forceinline__ float ld_cg(const float* p) { return __ldcg(p); }
 __device__ __forceinline__ float4 ld_cg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
 
-// Read-only 16-byte load that does not allocate a line in L1: for weight / memory rows that are streamed once per frame.  The L1 of
-// the persistent decoder kernels is what the 228 KB shared-memory carve-out leaves (28 KB), and every load in flight that allocates
-// holds a line of it -- as do the kernel's stack lines.
-__device__ __forceinline__ float4 ldg_stream4(const float4* p) {
-  float4 v;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
-  return v;
-}
-
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
   unsigned v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");

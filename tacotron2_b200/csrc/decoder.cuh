@@ -77,7 +77,7 @@ struct D2IO {
   int Tmax, n_steps, t0;
   int teacher_forcing, hidden_dropout, stop_enabled;
   int min_frames;     // the stop condition is honoured only once this many frames have been emitted (chunks of a larger batch)
-  int debug_barrier;  // adds one empty grid barrier per frame and times it (profiling only)
+  int debug_barrier;  // experiment bit mask (env T2B200_DEBUG_BARRIER): read by profiling builds of the decoder kernels only
   int precompute;     // set by d2_launch: shared memory allows the location conv + dense to run beside the attention-LSTM GEMM
   int w_policy_att, w_policy_dec;  // set by d2_launch: L2 eviction priority of the LSTM weight tiles (0 default, 1 evict-first, 2 evict-last)
   int hist;           // 1: state buffers are indexed by frame (slot t / t+1) instead of parity -- the training tape

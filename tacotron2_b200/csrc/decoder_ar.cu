@@ -17,14 +17,7 @@
 //     tcgen05.ld.  No shared or global memory holds a location term any more (round 1: 6.5 MB per frame through L2 and 7.3 us of
 //     CUDA-core work beside the decoder GEMM), and the stage ring is never used as scratch, which is what lets the stream run on.
 #include "decoder.cuh"
-#ifndef AR_NOALLOC
-#define AR_NOALLOC 0      // streamed weight / memory rows are loaded without allocating in the 28 KB L1
-#endif
-#if AR_NOALLOC
-#define AR_LDW(p) ldg_stream4(p)
-#else
-#define AR_LDW(p) __ldg(p)
-#endif
+#define AR_LDW(p) __ldg(p)   // (ld.global.nc.L1::no_allocate made the context sum 2x slower: the 28 KB L1 does serve these loads)
 #define D2_LDW(p) AR_LDW(p)
 #define D2_SYNC() asm volatile("bar.sync 1, 256;" ::: "memory")
 #include "dec_shared.cuh"
@@ -38,29 +31,10 @@
 #define AR_COL_THI 384u    // Toeplitz operand, hi plane: 128 positions x 64 taps bf16 = 32 columns
 #define AR_COL_TLO 416u    // lo plane
 #define AR_COL_WP 448u     // 8 rows of the mel / gate projection weights (rnn_h half): lane = K / 4 index mod 128, 2 x 32 columns
-#ifndef AR_BULKX
-#define AR_BULKX 1         // split-K exchange: partial rows staged in shared memory and sent as three bulk copies (else st.async per thread)
-#endif
-#if AR_BULKX
 #define AR_WRES_ROWS 5     // rows of the same weights resident in shared memory (20 KB; the staging buffers of the exchange take 25.5 KB)
-#else
-#define AR_WRES_ROWS 12    // rows of the same weights resident in shared memory (48 KB)
-#endif
 #define AR_PROJ_ROWS 21    // most projection rows per CTA on the fast path: the rest (beyond shared and tensor memory) comes from L2
 #define AR_WTM_ROWS 8      // rows resident in tensor memory
 #define AR_MAX_ENT 40
-#ifndef AR_TANH4
-#define AR_TANH4 1        // energy step: four tanh share one reciprocal
-#endif
-#ifndef AR_CTXPF
-#define AR_CTXPF 1        // context: first memory rows requested before the softmax, 16 loads in flight per thread
-#endif
-#ifndef AR_LEAN
-#define AR_LEAN 1         // ex2 / rcp .approx.ftz directly (no range fix-up code), Toeplitz planes split per warp, idle producer sleeps
-#endif
-#ifndef AR_XRED
-#define AR_XRED 1         // dense-layer warp reductions by value halving (16 shuffles for 16 sums instead of 80)
-#endif
 
 namespace {
 
@@ -72,7 +46,7 @@ struct ArSmem {
   float* part;       // split-K partials | attention scratch | output-stage scratch (phases never overlap, see the hazards note)
   uint8_t* gfilt;    // [2 hi/lo][128 a][64 taps] bf16, 128-B swizzled K-major: B operand of the location contraction
   float* wres;       // [AR_WRES_ROWS][H] first rows of this CTA's slice of the projection weights (rnn_h half), resident
-  float* stg;        // [3][32][TG_PART_LD] outgoing partial rows of the split-K exchange, one block per peer (AR_BULKX)
+  float* stg;        // [3][32][TG_PART_LD] outgoing partial rows of the split-K exchange, one block per peer
   float* c_att;
   float* c_dec;
   float* wq;
@@ -88,7 +62,7 @@ struct ArSmem {
 };
 
 __host__ __device__ inline size_t ar_smem_bytes(const D2Dims& d) {
-  return 1024 + (size_t)AR_STAGES * TG_STAGE_BYTES + (size_t)AR_WRES_ROWS * d.H * 4 + (AR_BULKX ? 3 * 32 * TG_PART_LD * 4 : 0) + TG_M * TG_PART_LD * 4 + 2 * 128 * 64 * 2 + 2 * 8 * D2_BP * 4 + 8 * (size_t)d.A * 4 + 8 * D2_BP * 4 +
+  return 1024 + (size_t)AR_STAGES * TG_STAGE_BYTES + (size_t)AR_WRES_ROWS * d.H * 4 + 3 * 32 * TG_PART_LD * 4 + TG_M * TG_PART_LD * 4 + 2 * 128 * 64 * 2 + 2 * 8 * D2_BP * 4 + 8 * (size_t)d.A * 4 + 8 * D2_BP * 4 +
          (size_t)d.A * 4 + 2 * 64 * 4 + 2 * (size_t)(d.L + 32) * 4 + AR_MAX_ENT * sizeof(KbEnt) + 24 * 8 + 80;
 }
 
@@ -98,7 +72,7 @@ __device__ __forceinline__ ArSmem ar_carve(uint8_t* base, const D2Dims& d) {
   uint8_t* p = base + (size_t)AR_STAGES * TG_STAGE_BYTES;
   s.gfilt = p;                             p += 2 * 128 * 64 * 2;    // keeps the 1024-B alignment of the ring
   s.wres = reinterpret_cast<float*>(p);    p += (size_t)AR_WRES_ROWS * d.H * 4;
-  s.stg = reinterpret_cast<float*>(p);     p += AR_BULKX ? 3 * 32 * TG_PART_LD * 4 : 0;
+  s.stg = reinterpret_cast<float*>(p);     p += 3 * 32 * TG_PART_LD * 4;
   s.part = reinterpret_cast<float*>(p);    p += TG_M * TG_PART_LD * 4;
   s.c_att = reinterpret_cast<float*>(p);   p += 8 * D2_BP * 4;
   s.c_dec = reinterpret_cast<float*>(p);   p += 8 * D2_BP * 4;
@@ -156,16 +130,11 @@ __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.
 // __expf / __fdividef carry range fix-up code (FSETP + two FMUL per call); the arguments here never need it.
 __device__ __forceinline__ float ex2_ftz(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float rcp_ftz(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
-#if AR_LEAN
 __device__ __forceinline__ float ar_sigmoid(float x) { return rcp_ftz(1.0f + ex2_ftz(-1.4426950408889634f * x)); }
 __device__ __forceinline__ float ar_tanh(float x) {
   const float t = ex2_ftz(-2.8853900817779268f * fabsf(x));
   return copysignf((1.0f - t) * rcp_ftz(1.0f + t), x);
 }
-#else
-__device__ __forceinline__ float ar_sigmoid(float x) { return sigmoid_fast(x); }
-__device__ __forceinline__ float ar_tanh(float x) { return tanh_fast(x); }
-#endif
 
 // K-block classes by the data the columns hold (decoder.cuh: x_att = [prenet | ctx | att_h], x_dec = [att_h | ctx | controls | rnn_h])
 __host__ __device__ inline int att_class(const D2Dims& d, int kb) {   // 0 prenet_t (gate X), 1 ctx_{t-1} (gate C of t-1), 2 att_h_{t-1} (gate Q of t-1)
@@ -274,7 +243,6 @@ __device__ __forceinline__ void ar_push_partials(uint32_t tmem, uint32_t col, fl
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int owner = warp & 3, col0 = 32 * (warp >> 2);
   float v[32];
-#if AR_BULKX
   // Staged form: the 32 rows for peer r leave as ONE bulk copy shared::cta -> shared::cluster (about 20 B/clk; the per-thread st.async
   // form moved 6 B/clk), the CTA's own rows go straight into its receive block.  Block layout [32 rows][TG_PART_LD] on both sides.
   constexpr uint32_t BLK = 32 * TG_PART_LD * 4;
@@ -296,17 +264,6 @@ __device__ __forceinline__ void ar_push_partials(uint32_t tmem, uint32_t col, fl
     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
     asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the block may be overwritten by the next exchange
   }
-#else
-  if (threadIdx.x == 0) tc::mbar_arrive_expect_tx(bar, (uint32_t)(D2_CLUSTER * 32 * TG_N * 4));   // four sources x 32 rows x 64 utterances
-  tc::tmem_ld32(tmem + ((uint32_t)(32 * owner) << 16) + col + col0, v);
-  tc::tmem_ld_wait();
-  tc::tc_fence_before();
-  const uint32_t dst = tc::mapa(tc::smem_u32(recv + ((size_t)my_rank * 32 + lane) * TG_PART_LD + col0), (uint32_t)owner);
-  const uint32_t rb = tc::mapa(tc::smem_u32(bar), (uint32_t)owner);
-#pragma unroll
-  for (int i = 0; i < 8; ++i) st_async_v4(dst + 16u * i, make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]), rb);
-  (void)stg;
-#endif
 }
 
 // LSTM pointwise tail on the received partials (same summation order as lstm_tail of dec_shared.cuh: ranks 0..3, then the bias).
@@ -477,7 +434,6 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
 }
 __device__ __forceinline__ void toeplitz_half(const float* src, bool on, int plane, uint32_t taddr) {
   uint32_t r[16];
-#if AR_LEAN
   if (on && plane == 0) {   // hi plane: one packed conversion per pair of taps (the plane is uniform over the warp)
 #pragma unroll
     for (int cc = 0; cc < 16; ++cc) {
@@ -495,17 +451,6 @@ __device__ __forceinline__ void toeplitz_half(const float* src, bool on, int pla
       r[cc] = *reinterpret_cast<const uint32_t*>(&l);
     }
   } else {
-#else
-  if (on) {
-#pragma unroll
-    for (int cc = 0; cc < 16; ++cc) {
-      const float x0 = src[2 * cc], x1 = (2 * cc + 1 < D2_LOC_K) ? src[2 * cc + 1] : 0.f;
-      __nv_bfloat16 h0, l0, h1, l1;
-      tc::split_bf16(x0, h0, l0); tc::split_bf16(x1, h1, l1);
-      r[cc] = plane ? pack2_bf16(l0, l1) : pack2_bf16(h0, h1);
-    }
-  } else {
-#endif
 #pragma unroll
     for (int cc = 0; cc < 16; ++cc) r[cc] = 0u;
   }
@@ -544,19 +489,11 @@ __device__ __forceinline__ void build_toeplitz_and_issue(const ArSmem& sm, const
 // e + v . tanh(z) for four arguments: tanh(z) = sign(z) (1 - t) / (1 + t), t = exp(-2|z|) in (0, 1]; the four denominators (each in
 // (1, 2]) share ONE reciprocal of their product -- 5 MUFU operations instead of 8 (the energy step is MUFU-bound)
 __device__ __forceinline__ float tanh4_dot(float4 v, float z0, float z1, float z2, float z3, float e) {
-#if AR_LEAN
   const float k = -2.8853900817779268f;   // -2 log2(e)
   const float t0 = ex2_ftz(k * fabsf(z0)), t1 = ex2_ftz(k * fabsf(z1)), t2 = ex2_ftz(k * fabsf(z2)), t3 = ex2_ftz(k * fabsf(z3));
-#else
-  const float t0 = __expf(-2.0f * fabsf(z0)), t1 = __expf(-2.0f * fabsf(z1)), t2 = __expf(-2.0f * fabsf(z2)), t3 = __expf(-2.0f * fabsf(z3));
-#endif
   const float a0 = 1.0f + t0, a1 = 1.0f + t1, a2 = 1.0f + t2, a3 = 1.0f + t3;
   const float p01 = a0 * a1, p23 = a2 * a3;
-#if AR_LEAN
   const float r = rcp_ftz(p01 * p23);
-#else
-  const float r = __fdividef(1.0f, p01 * p23);
-#endif
   const float r01 = r * p23, r23 = r * p01;   // 1 / (a0 a1), 1 / (a2 a3)
   e = fmaf(v.x, copysignf((1.0f - t0) * (r01 * a1), z0), e);
   e = fmaf(v.y, copysignf((1.0f - t1) * (r01 * a0), z1), e);
@@ -629,15 +566,8 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
 #pragma unroll
           for (int i = 0; i < 8; ++i) {   // q and v as 16-byte broadcast loads
             const float4 q4 = *reinterpret_cast<const float4*>(as.q_s + a0 + 4 * i), v4 = *reinterpret_cast<const float4*>(sm.v + a0 + 4 * i);
-#if AR_TANH4
             e = tanh4_dot(v4, q4.x + x[4 * i] + pm[4 * i], q4.y + x[4 * i + 1] + pm[4 * i + 1], q4.z + x[4 * i + 2] + pm[4 * i + 2],
                           q4.w + x[4 * i + 3] + pm[4 * i + 3], e);
-#else
-            e = fmaf(v4.x, ar_tanh(q4.x + x[4 * i] + pm[4 * i]), e);
-            e = fmaf(v4.y, ar_tanh(q4.y + x[4 * i + 1] + pm[4 * i + 1]), e);
-            e = fmaf(v4.z, ar_tanh(q4.z + x[4 * i + 2] + pm[4 * i + 2]), e);
-            e = fmaf(v4.w, ar_tanh(q4.w + x[4 * i + 3] + pm[4 * i + 3]), e);
-#endif
           }
         }
       }
@@ -661,14 +591,11 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
     const size_t rs = (size_t)EF / 4;
     const float4* mp0 = reinterpret_cast<const float4*>(io.memory + (size_t)at.b * L * EF + c0);
     const int lclamp = max(at.Leff - 1, 0);
-#if AR_CTXPF
-    const bool ctx_new = AR_CTXPF == 1 || (io.debug_barrier & 64) == 0;
     float4 pf[8];
-    if (cq0 < nq && ctx_new) {
+    if (cq0 < nq) {
 #pragma unroll
       for (int u = 0; u < 8; ++u) pf[u] = AR_LDW(mp0 + cq0 + (size_t)min(lg + 4 * u, lclamp) * rs);
     }
-#endif
     if (!tc::mbar_wait_cluster(sm.bars + B_E, fphase)) ok = false;
     mark(12);
     // softmax over the full row (model/attention.py:65); every thread keeps to its own positions through the three passes
@@ -718,8 +645,6 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
     for (int cq = cq0; cq < nq; cq += 64) {
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
       const float4* mp = mp0 + cq;
-#if AR_CTXPF
-      if (ctx_new) {
       if (cq != cq0) {
 #pragma unroll
         for (int u = 0; u < 8; ++u) pf[u] = AR_LDW(mp + (size_t)min(lg + 4 * u, lclamp) * rs);
@@ -742,34 +667,6 @@ __device__ bool ar_attention(const D2Dims& d, const D2State& s, const D2IO& io, 
           acc.z = fmaf(w, m[u].z, acc.z); acc.w = fmaf(w, m[u].w, acc.w);
         }
       }
-      }
-#endif
-#if AR_CTXPF != 1
-#if AR_CTXPF == 2
-      if (!ctx_new) {
-#else
-      {
-#endif
-      int l = lg;
-      for (; l + 28 < at.Leff; l += 32) {
-        float4 m[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) m[u] = AR_LDW(mp + (size_t)(l + 4 * u) * rs);
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const float w = wr[l + 4 * u];
-          acc.x = fmaf(w, m[u].x, acc.x); acc.y = fmaf(w, m[u].y, acc.y);
-          acc.z = fmaf(w, m[u].z, acc.z); acc.w = fmaf(w, m[u].w, acc.w);
-        }
-      }
-      for (; l < at.Leff; l += 4) {
-        const float4 m4 = AR_LDW(mp + (size_t)l * rs);
-        const float w = wr[l];
-        acc.x = fmaf(w, m4.x, acc.x); acc.y = fmaf(w, m4.y, acc.y);
-        acc.z = fmaf(w, m4.z, acc.z); acc.w = fmaf(w, m4.w, acc.w);
-      }
-      }
-#endif
       *reinterpret_cast<float4*>(as.cred + (size_t)lg * cols_per + cq * 4) = acc;
     }
     wsync();
@@ -931,20 +828,15 @@ __device__ bool ar_output(const D2Dims& d, const D2Weights& w, const D2State& s,
   float* y2 = y_s + 4 * YS;
   // prenet layer 2 reads 64 KB of weights per CTA from L2; they depend on nothing, so when the shape is the usual one (8 rows per warp,
   // 256 columns) this lane's sixteen float4 are requested before the wait for the all-gather of layer 1's output
-  const bool w2_pre = AR_XRED && w1_smem && rq == 64 && P == 256;
+  const bool w2_pre = w1_smem && rq == 64 && P == 256;
   if (!tc::mbar_wait_cluster(mel_bar, cphase)) ok = false;
   if (w2_pre) {
     if (!tc::mbar_wait(wbar, cphase)) ok = false;
     ar_rows8_body<1, true>(w1_s - (ptrdiff_t)pr0 * M, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
   } else if (w1_smem) {
     if (!tc::mbar_wait(wbar, cphase)) ok = false;
-#if AR_XRED
     ar_rows8<1, true>(w1_s - (ptrdiff_t)pr0 * M, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
   } else if ((M >> 2) <= 32) ar_rows8<1, false>(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
-#else
-    rows_short<8, 1, true>(w1_s - (ptrdiff_t)pr0 * M, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
-  } else if ((M >> 2) <= 32) rows_short<8, 1, false>(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
-#endif
   else rows_dot2<false>(w.W1, M, M >> 2, rb, re, mel_s, mel_s + MP, y1, pr0, YS);
 #pragma unroll 1
   for (int r = rb + (lane >> 1); r < re && b < B; r += 16) {
@@ -959,7 +851,6 @@ __device__ bool ar_output(const D2Dims& d, const D2Weights& w, const D2State& s,
   const long long pa = (long long)D2_BP * d.KattP;
   __nv_bfloat16* xa = s.xatt + (size_t)nxt * 2 * pa;
   const bool vec = (rq & 7) == 0 && (d.KattP & 7) == 0;
-#if AR_XRED
   if (w2_pre) {
     float4 w2v[8][2];
 #pragma unroll
@@ -994,11 +885,6 @@ __device__ bool ar_output(const D2Dims& d, const D2Weights& w, const D2State& s,
     if ((P >> 2) <= 64) ar_rows8<2, false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
     else rows_dot2<false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
   }
-#else
-  if (!tc::mbar_wait_cluster(p1_bar, p1_phase)) ok = false;
-  if ((P >> 2) <= 64) rows_short<8, 2, false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
-  else rows_dot2<false>(w.W2, P, P >> 2, rb, re, p1_s, p1_s + P, y2, pr0, YS);
-#endif
 #pragma unroll 1
   for (int r = rb + (lane >> 1); r < re; r += 16) {
     float v = 0.f;
@@ -1142,9 +1028,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
           }
         }
         if (progressed) { idle = 0; continue; }
-#if AR_LEAN
-        __nanosleep((io.debug_barrier & 128) ? 400 : 32);   // nothing to issue: leave the issue slots of this scheduler to the worker warps
-#endif
+        __nanosleep(32);   // nothing to issue: leave the issue slots of this scheduler to the worker warps
         if (sm.ctl[1] != 0u) break;                              // workers stopped (stop gate, abort): no more gates will open
         if (++idle > (1ll << 24)) { sm.ctl[2] = 1u; break; }     // never hang the GPU
       }
@@ -1215,7 +1099,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
   } else {
     // =============================================================== workers
     ArGridBar bar{s.barrier, s.barrier + 2, gridDim.x, 0u, &ok_word, 50u};   // measured at C2: no pause 30.6 us per frame, 50 ns 30.3, 150 ns 30.5, 300 ns 31.0
-    const bool split_toeplitz = (io.debug_barrier & 32) == 0;   // (experiment bit 32: whole Toeplitz build behind the C barrier, as before)
+    constexpr bool split_toeplitz = true;   // (whole build behind the C barrier: C barrier 3.0 instead of 2.3 us)
     long long prof_last = clock64();
     auto prof_mark = [&](int slot) {
       if (blockIdx.x == 0 && tid == 0 && s.prof) { const long long now = clock64(); s.prof[slot] += (unsigned long long)(now - prof_last); prof_last = now; }
@@ -1271,7 +1155,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
     const long long pa = (long long)D2_BP * d.KattP, pd = (long long)D2_BP * d.KdecP;
     bool alive = true, fail = false, stop = false;
     constexpr bool has_out = !TF;
-    const bool proj_fast = has_out && ar_proj_fast(d) && 2 * tile < B && (io.debug_barrier & 1024) == 0;
+    const bool proj_fast = has_out && ar_proj_fast(d) && 2 * tile < B;
     if (proj_fast) {   // this CTA's rows of the projection weights (rnn_h half) -> shared memory and tensor memory, once per launch
       const int rows_per = (d.M + 1 + D2_CLUSTER - 1) / D2_CLUSTER, r0 = (int)rank * rows_per, nr = max(0, min(rows_per, d.M + 1 - r0));
       const float4* wp = reinterpret_cast<const float4*>(w.Wproj);
