@@ -151,14 +151,21 @@ __host__ __device__ inline int dec_class(const D2Dims& d, int kb) {   // 0 att_h
 }
 
 // The K-block program of CTA `rank`, in issue order (see the file comment).  Returns the entry count.
-__host__ __device__ inline int build_program(const D2Dims& d, int rank, KbEnt* out) {
+__host__ __device__ inline int build_program(const D2Dims& d, int rank, KbEnt* out, bool tf) {
+  // att.H blocks streamed behind dec.A in the attention window instead of the decoder-LSTM tail window.  Measured at C3 / C2: teacher
+  // forcing 0 -> 19.9 ms per 800-frame forward, 1 -> 19.4, 2 -> 19.3, 3 / 4 -> 19.5; autoregressive 0 -> 30.3 us per frame, 1 -> 30.4, 2 -> 31.0
+  const int early_h = 2, early_ar = 0;
   const int nka = d.KattP / TG_BK, nkd = d.KdecP / TG_BK;
   int n = 0;
-  auto emit = [&](int gemm, int cls, int gate, int next) {
+  auto emit = [&](int gemm, int cls, int gate, int next, int skip = 0, int take = 1 << 20) {   // blocks [skip, skip + take) of the class
+    int i = 0;
     for (int kb = rank; kb < (gemm ? nkd : nka); kb += D2_CLUSTER)
       if ((gemm ? dec_class(d, kb) : att_class(d, kb)) == cls) {
-        if (n < AR_MAX_ENT) out[n] = KbEnt{(unsigned char)gemm, (unsigned char)kb, (unsigned char)gate, (unsigned char)(next ? 4 : 0)};
-        ++n;
+        if (i >= skip && i < skip + take) {
+          if (n < AR_MAX_ENT) out[n] = KbEnt{(unsigned char)gemm, (unsigned char)kb, (unsigned char)gate, (unsigned char)(next ? 4 : 0)};
+          ++n;
+        }
+        ++i;
       }
   };
   // Order = which barrier window a background block streams in.  The windows after Q (query sum, context sum: 270 KB of CUDA-core
@@ -167,13 +174,39 @@ __host__ __device__ inline int build_program(const D2Dims& d, int rank, KbEnt* o
   // (decoder-LSTM tail window), dec.R of the next frame follows R (the output stage reads its projection weights from chip memory).
   // Measured at C2 (profiles/r02_v14_ar_ab.log): this order 32.7 us per frame, round 2's first order (att.H right after dec.A) 32.8,
   // dec.R behind the next att.P instead (after X) 33.4.
+  if (tf) {
+    // Teacher forcing: the prenet block has no gate (bulk prenet before the launch) and there is no output stage after R for the rnn_h
+    // blocks to hide behind -- in the order below they sat in front of the next frame's prenet block and the workers waited 5 us per
+    // frame for the attention cell's accumulator.  Here the prenet block of frame t+1 closes that accumulator in the decoder-LSTM
+    // tail window of frame t, and the rnn_h blocks stream behind the attention-LSTM tail of frame t+1.
+    emit(1, 0, G_Q, 0);   // dec.A(t)
+    int first_att = n;
+    emit(0, 2, G_Q, 1, 0, early_h);        // att.H(t+1), first blocks: behind dec.A in the attention window
+    const bool none_early = n == first_att;
+    emit(1, 1, G_C, 0);   // dec.C(t)      [on the chain]
+    const int last_dec = n - 1;
+    if (none_early) first_att = n;
+    emit(0, 2, G_Q, 1, early_h);           // att.H(t+1), the rest: with att.C and att.P in the decoder-LSTM tail window
+    emit(0, 1, G_C, 1);   // att.C(t+1)
+    emit(0, 0, G_X, 1);   // att.P(t+1)
+    const int last_att = n - 1;
+    const int first_dec = n;
+    emit(1, 2, G_R, 1);   // dec.R(t+1)
+    if (n <= AR_MAX_ENT && last_dec >= 0 && first_att < n && last_att > first_att && first_dec < n) {
+      out[last_att].flags |= 2; out[first_att].flags |= 1; out[last_dec].flags |= 2; out[first_dec].flags |= 1;
+    }
+    return n;
+  }
   emit(0, 0, G_X, 0);   // att.P(t)      [on the chain]
   const int last_att = n - 1;
   emit(1, 0, G_Q, 0);   // dec.A(t)
+  int first_att = n;
+  emit(0, 2, G_Q, 1, 0, early_ar);   // att.H(t+1), first blocks
+  const bool none_early = n == first_att;
   emit(1, 1, G_C, 0);   // dec.C(t)      [on the chain]
   const int last_dec = n - 1;
-  const int first_att = n;
-  emit(0, 2, G_Q, 1);   // att.H(t+1)
+  if (none_early) first_att = n;
+  emit(0, 2, G_Q, 1, early_ar);      // att.H(t+1), the rest
   emit(0, 1, G_C, 1);   // att.C(t+1)
   const int first_dec = n;
   emit(1, 2, G_R, 1);   // dec.R(t+1)
@@ -943,7 +976,7 @@ decoder_ar_kernel(const __grid_constant__ D2Maps maps, const __grid_constant__ C
                                                 // frame 0 counts as passed.  Teacher forcing has three barriers per frame (no X)
     sm.ctl[1] = 0u; sm.ctl[2] = 0u; sm.ctl[4] = 0u; sm.ctl[5] = 0u;
     for (int i = 8; i < 15; ++i) sm.ctl[i] = 0u;   // 8 cluster counter (barrier mode 2), 9 fired stop gates, 10 done count, 11-12 fired flags, 13-14 lengths
-    sm.ctl[3] = (unsigned)build_program(d, (int)rank, sm.prog);
+    sm.ctl[3] = (unsigned)build_program(d, (int)rank, sm.prog, TF);
   }
   if (warp == 9) tc::tmem_alloc<512>(sm.tmem_slot);   // warp 9 owns alloc + dealloc
   if (worker) {
@@ -1273,8 +1306,8 @@ bool d2ar_supported(const D2Dims& d) {
   if (Lc > 128 || d.A > 128 || d.A % 32 != 0 || d.P % (TG_BK * D2_CLUSTER) != 0 || d.EF % 4 != 0 || d.M % 4 != 0) return false;
   if (d.H % (TG_BK * D2_CLUSTER) != 0 || d.KattP / TG_BK > 255 || d.KdecP / TG_BK > 255) return false;
   KbEnt tmp[AR_MAX_ENT];
-  for (int r = 0; r < D2_CLUSTER; ++r) {
-    const int n = build_program(d, r, tmp);
+  for (int r = 0; r < 2 * D2_CLUSTER; ++r) {   // both orders (autoregressive, teacher forcing)
+    const int n = build_program(d, r % D2_CLUSTER, tmp, r >= D2_CLUSTER);
     if (n > AR_MAX_ENT) return false;
     int la = 0, fa = 0, ld = 0, fd = 0;
     for (int i = 0; i < n; ++i) {
