@@ -4,6 +4,7 @@ namespace {
 struct DBParams {
   D2Dims d;
   int T, KattT, KdecT, S;
+  int wpol_att, wpol_dec;     // L2 eviction priority of the transposed-weight tiles of the two cells (1 evict-first, 0 default, 2 evict-last)
   int tc_att;                 // 1: attention backward contractions on tcgen05 (bwd_decoder_att_tc.inl), 0: CUDA cores (bwd_decoder_att.inl)
   DBWeights w;
   DBTape tp;
@@ -14,10 +15,10 @@ struct DBParams {
 // one 128-row tile of an input-gradient GEMM: dx[k0 + r][b] = sum_p WT[k0 + r][p] dg[b][p]
 template <class Side>
 __device__ __forceinline__ bool dx_tile(tg::Pipe& pipe, const BSmem& sm, const CUtensorMap* wmap, const CUtensorMap* dgmap, int ktile,
-                                        int npb, uint32_t rank, float* dx /*[K][BP]*/, Side side) {
+                                        int npb, uint32_t rank, float* dx /*[K][BP]*/, Side side, int wpol) {
   tg::XSrc xs{dgmap, 0, dgmap, 0, npb};
-  // transposed weights stream through L2 evict-first (see d2_launch): the per-frame working set of the attention backward stays resident
-  const bool ok = tg::gemm(pipe, wmap, ktile * TG_M, npb, xs, (int)rank, npb, D2_CLUSTER, 0u, side, 1);
+  // the transposed weights of the decoder cell stream through L2 evict-first: the per-frame working set of the attention backward stays resident
+  const bool ok = tg::gemm(pipe, wmap, ktile * TG_M, npb, xs, (int)rank, npb, D2_CLUSTER, 0u, side, wpol);
   tg::accum_to_smem(pipe, 0u, sm.part);
   tc::cluster_sync();
   // CTA `rank` reduces rows [32*rank, 32*rank+32) of the tile over the four partials
@@ -240,8 +241,8 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
           if (t > 0) pf(tp.sav_att + (((size_t)(t - 1) * 5 + 4) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
           if (t > 1) pf(tp.sav_dec + (((size_t)(t - 2) * 5 + 4) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
         };
-        if (tile < n_dec) ok = dx_tile(pipe, sm, &maps.wt_dec, &maps.dg_dec, tile, npb, rank, wk.dx_dec, tape_prefetch);
-        else ok = dx_tile(pipe, sm, &maps.wt_att, &maps.dg_att, tile - n_dec + att_tile0, npb, rank, wk.dx_att, tape_prefetch);
+        if (tile < n_dec) ok = dx_tile(pipe, sm, &maps.wt_dec, &maps.dg_dec, tile, npb, rank, wk.dx_dec, tape_prefetch, p.wpol_dec);
+        else ok = dx_tile(pipe, sm, &maps.wt_att, &maps.dg_att, tile - n_dec + att_tile0, npb, rank, wk.dx_att, tape_prefetch, p.wpol_att);
         if (!ok) fail = true;
       }
     }
@@ -404,7 +405,11 @@ int db_launch(const D2Dims& d, int T, int KattT, int KdecT, const DBWeights& w, 
   T2_REQUIRE(nclusters * D2_CLUSTER >= grid, T2_ERR_UNSUPPORTED, "decoder backward: only %d clusters co-resident, %d needed", nclusters,
              grid / D2_CLUSTER);
   T2_CHECK_CUDA(cudaMemsetAsync(wk.barrier, 0, 4 * sizeof(unsigned), st));
-  DBParams p{d, T, KattT, KdecT, S, tc_att ? 1 : 0, w, tp, wk, prof};
+  // the attention cell's transposed weights (25 MB) with default L2 priority, the decoder cell's (46 MB) evict-first: measured at C3
+  // (att, dec) = (first, first) 43.2 ms per backward, (default, first) 42.8, (last, first) 42.8, (first, default) 43.0, (default, default) 45.5
+  const int wpol_att = getenv("T2B200_BWD_WPOL_ATT") ? atoi(getenv("T2B200_BWD_WPOL_ATT")) : 0;
+  const int wpol_dec = getenv("T2B200_BWD_WPOL_DEC") ? atoi(getenv("T2B200_BWD_WPOL_DEC")) : 1;
+  DBParams p{d, T, KattT, KdecT, S, wpol_att, wpol_dec, tc_att ? 1 : 0, w, tp, wk, prof};
   T2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, decoder_bwd_kernel, maps, p));
   return T2_OK;
 }
