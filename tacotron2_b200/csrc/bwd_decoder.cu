@@ -24,6 +24,7 @@ struct BSmem {
   uint8_t* gfT;       // tensor-core attention path (bwd_decoder_att_tc.inl), in place of conv_t / dense / dense_af:
                       // folded filter bank G[(c,j)][a] as bf16 (hi,lo) K-major sw128 tiles [2 hl][2 kt][64 rows][128 B]
   uint8_t* ident;     // 16 x 16 identity as one K-major sw128 tile (2 KB)
+  float* wq;          // [A][8] query-weight columns of this CTA's 8 units, resident (tensor-core attention path: behind `ident`)
   uint64_t* bars;     // ring full[3] empty[3], accumulator, spare, attention H done, attention all done
   uint32_t* tmem_slot;   // [0] GEMM accumulators (256 columns), [1] d pm + Y accumulators of the tensor-core attention path (256 columns)
 };
@@ -36,6 +37,7 @@ __device__ __forceinline__ BSmem carve(uint8_t* base, const D2Dims& d) {
   s.dc_att = reinterpret_cast<float*>(p);  p += 8 * D2_BP * 4;
   s.dc_dec = reinterpret_cast<float*>(p);  p += 8 * D2_BP * 4;
   s.gfT = p; s.ident = p + 32768;          // (offset 182 KB from the 1024-aligned base: tile aligned)
+  s.wq = reinterpret_cast<float*>(p + 32768 + 2048);
   s.conv_t = reinterpret_cast<float*>(p);  p += 2 * D2_LOC_K * D2_LOC_F * 4;
   s.dense = reinterpret_cast<float*>(p);   p += d.A * D2_LOC_F * 4;
   s.dense_af = reinterpret_cast<float*>(p); p += d.A * 36 * 4;
@@ -82,24 +84,47 @@ struct PwArgs {
   long long ldT; long long tcol;
 };
 
-__device__ __forceinline__ void lstm_pointwise_bwd(const PwArgs& a, int H, int B, int unit0, int pbase, float* dcs, float* stg,
-                                                   const float* dh_extra2, float* bias_acc /*[4]*/) {
+// The inputs of one thread (tape and gradient rows of both its utterances), loaded ahead of use: the pointwise phase issues the loads of
+// both cells and of the query gradient together, so the phase pays one L2 round trip instead of one per step.
+struct PwIn {
+  float2 si2, sf2, tg2, so2, c2, cp2, d02, d12;
+  float rm[2];
+  bool keep[2];
+};
+
+__device__ __forceinline__ PwIn lstm_pointwise_load(const PwArgs& a, int H, int B, int unit0) {
   const int ul = threadIdx.x >> 5, bp = threadIdx.x & 31;
   const int u = unit0 + ul;
   const size_t gs = (size_t)H * D2_BP;
-  float dgv[4][2];
-  // tape and gradient rows of both utterances of this thread: 8-byte loads; the tape is read once -> streaming (evict-first)
+  // 8-byte loads; the tape is read once -> streaming (evict-first)
   const size_t o2 = (size_t)u * D2_BP + 2 * bp;
   const float2 zero2 = make_float2(0.f, 0.f);
   const bool any = 2 * bp < B;
-  const float2 si2 = any ? __ldcs(reinterpret_cast<const float2*>(a.sav + o2)) : zero2;
-  const float2 sf2 = any ? __ldcs(reinterpret_cast<const float2*>(a.sav + gs + o2)) : zero2;
-  const float2 tg2 = any ? __ldcs(reinterpret_cast<const float2*>(a.sav + 2 * gs + o2)) : zero2;
-  const float2 so2 = any ? __ldcs(reinterpret_cast<const float2*>(a.sav + 3 * gs + o2)) : zero2;
-  const float2 c2 = any ? __ldcs(reinterpret_cast<const float2*>(a.sav + 4 * gs + o2)) : zero2;
-  const float2 cp2 = (any && a.cprev) ? __ldcg(reinterpret_cast<const float2*>(a.cprev + o2)) : zero2;   // read again as c of the next iteration
-  const float2 d02 = (any && a.dh0) ? __ldcg(reinterpret_cast<const float2*>(a.dh0 + (size_t)(a.row0 + u) * D2_BP + 2 * bp)) : zero2;
-  const float2 d12 = (any && a.dh1) ? __ldcg(reinterpret_cast<const float2*>(a.dh1 + (size_t)(a.row1 + u) * D2_BP + 2 * bp)) : zero2;
+  PwIn in;
+  in.si2 = any ? __ldcs(reinterpret_cast<const float2*>(a.sav + o2)) : zero2;
+  in.sf2 = any ? __ldcs(reinterpret_cast<const float2*>(a.sav + gs + o2)) : zero2;
+  in.tg2 = any ? __ldcs(reinterpret_cast<const float2*>(a.sav + 2 * gs + o2)) : zero2;
+  in.so2 = any ? __ldcs(reinterpret_cast<const float2*>(a.sav + 3 * gs + o2)) : zero2;
+  in.c2 = any ? __ldcs(reinterpret_cast<const float2*>(a.sav + 4 * gs + o2)) : zero2;
+  in.cp2 = (any && a.cprev) ? __ldcg(reinterpret_cast<const float2*>(a.cprev + o2)) : zero2;   // read again as c of the next iteration
+  in.d02 = (any && a.dh0) ? __ldcg(reinterpret_cast<const float2*>(a.dh0 + (size_t)(a.row0 + u) * D2_BP + 2 * bp)) : zero2;
+  in.d12 = (any && a.dh1) ? __ldcg(reinterpret_cast<const float2*>(a.dh1 + (size_t)(a.row1 + u) * D2_BP + 2 * bp)) : zero2;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int b = 2 * bp + j;
+    in.rm[j] = (b < B && a.dh_rm) ? ld_cg(a.dh_rm + (size_t)b * a.ld_rm + a.col_rm + u) : 0.f;
+    in.keep[j] = (b < B && a.hidden_dropout && a.keep) ? (a.keep[(size_t)b * H + u] != 0) : true;
+  }
+  return in;
+}
+
+// compute half: d gates of this thread's (unit, utterance pair) -> weight-gradient operand (global) and the staging tile `stg` [64][33]
+__device__ __forceinline__ void lstm_pointwise_compute(const PwArgs& a, const PwIn& in, int H, int B, int unit0, float* dcs, float* stg,
+                                                       const float* dh_extra2, float* bias_acc /*[4]*/) {
+  const int ul = threadIdx.x >> 5, bp = threadIdx.x & 31;
+  const int u = unit0 + ul;
+  float dgv[4][2];
+  const float2 si2 = in.si2, sf2 = in.sf2, tg2 = in.tg2, so2 = in.so2, c2 = in.c2, cp2 = in.cp2, d02 = in.d02, d12 = in.d12;
 #pragma unroll
   for (int j = 0; j < 2; ++j) {
     const int b = 2 * bp + j;
@@ -110,9 +135,9 @@ __device__ __forceinline__ void lstm_pointwise_bwd(const PwArgs& a, int H, int B
       float dh = dh_extra2 ? dh_extra2[j] : 0.f;
       dh += j ? d02.y : d02.x;
       dh += j ? d12.y : d12.x;
-      if (a.dh_rm) dh += ld_cg(a.dh_rm + (size_t)b * a.ld_rm + a.col_rm + u);
+      dh += in.rm[j];
       if (a.hidden_dropout) {  // nn.Dropout(0.1) on h (model/decoder.py:75,101): same draw as the forward
-        const bool k = a.keep ? (a.keep[(size_t)b * H + u] != 0) : rng_keep(a.seed, a.rng_base + (unsigned long long)b * H + u, 0.1f);
+        const bool k = a.keep ? in.keep[j] : rng_keep(a.seed, a.rng_base + (unsigned long long)b * H + u, 0.1f);
         dh = k ? dh * (1.0f / 0.9f) : 0.f;
       }
       const float tc_ = tanh_fast(c);
@@ -140,8 +165,11 @@ __device__ __forceinline__ void lstm_pointwise_bwd(const PwArgs& a, int H, int B
     stg[(2 * bp) * 33 + g * 8 + ul] = dgv[g][0];
     stg[(2 * bp + 1) * 33 + g * 8 + ul] = dgv[g][1];
   }
-  __syncthreads();
-  // packed operand: rows [pbase, pbase+32) of every utterance, both planes: 64 x 2 x 4 chunks of 8 bf16
+}
+
+// pack half (after a block barrier): the staged d gates as the packed GEMM operand, rows [pbase, pbase+32) of every utterance, both
+// planes: 64 x 2 x 4 chunks of 8 bf16
+__device__ __forceinline__ void lstm_pointwise_pack(const PwArgs& a, int H, int pbase, const float* stg) {
 #pragma unroll 1
   for (int i = threadIdx.x; i < D2_BP * 2 * 4; i += D2_THREADS) {
     const int ch = i & 3, hl = (i >> 2) & 1, b = i >> 3;
@@ -154,6 +182,13 @@ __device__ __forceinline__ void lstm_pointwise_bwd(const PwArgs& a, int H, int B
     }
     *reinterpret_cast<uint4*>(a.dg + ((size_t)hl * D2_BP + b) * 4 * H + pbase + ch * 8) = *reinterpret_cast<const uint4*>(v8);
   }
+}
+
+__device__ __forceinline__ void lstm_pointwise_bwd(const PwArgs& a, const PwIn& in, int H, int B, int unit0, int pbase, float* dcs, float* stg,
+                                                   const float* dh_extra2, float* bias_acc /*[4]*/) {
+  lstm_pointwise_compute(a, in, H, B, unit0, dcs, stg, dh_extra2, bias_acc);
+  __syncthreads();
+  lstm_pointwise_pack(a, H, pbase, stg);
   __syncthreads();
 }
 

@@ -270,13 +270,14 @@ __device__ void attention_bwd_phase_tc(const D2Dims& d, const DBTape& tp, const 
       tc::umma_commit(bar_all);
     }
     if (has) stt.issued = true;
-    // d query of this slice (summed over the parts by the pointwise phase)
+    // d query of this slice: the eight warps' sums, left in row 0 (each thread reads and writes its own column); part 0 adds the parts
+    // after the cluster barrier below
 #pragma unroll 1
     for (int a = tid; a < A; a += D2_THREADS) {
       float s = 0.f;
 #pragma unroll
       for (int w8 = 0; w8 < D2_THREADS / 32; ++w8) s += dqw[w8 * A + a];
-      wk.dq[(((size_t)t * S + part) * A + a) * D2_BP + b] = s;   // [t][part][a][b]: utterance-minor, the layout phase P stages
+      dqw[a] = s;
     }
     // ---- H -> shared memory, [c][j][position] (lanes = consecutive positions: conflict-free)
     if (has) {
@@ -322,6 +323,20 @@ __device__ void attention_bwd_phase_tc(const D2Dims& d, const DBTape& tp, const 
         o += v;
       }
       wk.dconv[((size_t)c * D2_BP + b) * L + l] = o;
+    }
+    // d query of the utterance = sum over the parts, [t][a][b] utterance-minor (the layout phase P reads); the upper threads, beside
+    // the d wcat rows above
+    if (part == 0) {
+#pragma unroll 1
+      for (int a = D2_THREADS - 1 - tid; a < A; a += D2_THREADS) {
+        float s = dqw[a];
+        for (int pr = 1; pr < S; ++pr) {
+          float v;
+          asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(tc::mapa(tc::smem_u32(dqw + a), base_rank + (uint32_t)pr)) : "memory");
+          s += v;
+        }
+        wk.dq[((size_t)t * S * A + a) * D2_BP + b] = s;
+      }
     }
     if (has) {   // all MMAs of this frame have retired: the operand tiles may be overwritten (the next phase streams through them)
       if (!tc::mbar_wait(bar_all, stt.phase)) fail = true;

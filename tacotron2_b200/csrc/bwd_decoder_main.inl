@@ -74,6 +74,8 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
       const int r = i >> 6, k = i & 63;
       *reinterpret_cast<__nv_bfloat16*>(sm.ident + tc::sw128_off(r, k)) = __float2bfloat16_rn(r == k ? 1.f : 0.f);
     }
+#pragma unroll 1
+    for (int i = tid; i < d.A * 8; i += D2_THREADS) sm.wq[i] = __ldg(p.w.Wq + (size_t)(i >> 3) * d.H + unit0 + (i & 7));
     tc::fence_proxy_async();
   } else {
 #pragma unroll 1
@@ -125,12 +127,13 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) acc.dv[i] = 0.f;
   float bias_att[4] = {0.f, 0.f, 0.f, 0.f}, bias_dec[4] = {0.f, 0.f, 0.f, 0.f};
-  float* stg = scratch;                       // [64][33] staging of the pointwise phase
-  float* dq_s = scratch + 64 * 33 + 16;       // [A][64] summed d query, utterance-minor
-  float* wq_s = dq_s + d.A * D2_BP;           // [A][8]  query weight columns of this CTA's 8 units (reloaded per frame: L2 hit)
+  float* stg = scratch;                       // [64][33] staging of the pointwise phase: attention cell
+  float* stg2 = scratch + 64 * 33 + 16;       // decoder cell
+  float* qred = stg2 + 64 * 33 + 16;          // [8 warps][8 units][64] partial d att_h of the query layer
+  float* wq_s = qred + 64 * D2_BP;            // [A][8] query weight columns when they are not resident (CUDA-core attention path)
   bool alive = true, fail = false;
 
-  auto pw_dec = [&](int t, bool have_next) {   // decoder LSTMCell of frame t
+  auto args_dec = [&](int t, bool have_next) {   // decoder LSTMCell of frame t
     PwArgs a{};
     a.sav = tp.sav_dec + (size_t)t * 5 * H * D2_BP;
     a.cprev = t > 0 ? tp.sav_dec + ((size_t)(t - 1) * 5 + 4) * H * D2_BP : nullptr;
@@ -139,58 +142,9 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
     a.keep = tp.rnn_keep ? tp.rnn_keep + (size_t)t * B * H : nullptr;
     a.hidden_dropout = tp.hidden_dropout != 0; a.seed = tp.seed; a.rng_base = (2ull << 40) + (unsigned long long)t * B * H;
     a.dg = wk.dg_dec; a.dgT = wk.dgT_dec; a.ldT = (long long)T * D2_BP; a.tcol = (long long)t * D2_BP;
-    lstm_pointwise_bwd(a, H, B, unit0, pbase, sm.dc_dec, stg, nullptr, bias_dec);
+    return a;
   };
-  auto pw_att = [&](int t, bool have_next) {   // attention LSTMCell of frame t (its h also feeds the query and the decoder cell)
-    // d query [a][b] summed over the attention parts (the parts write it utterance-minor, so it is staged as it lies: 16-byte
-    // loads and stores, no transposition).  The query-weight columns are requested first so both latencies overlap, and all
-    // loads of a chunk are issued before any use (a one-load-per-iteration loop pays the full L2 latency every time).
-#pragma unroll 1
-    for (int i = tid; i < d.A * 8; i += D2_THREADS) wq_s[i] = __ldg(p.w.Wq + (size_t)(i >> 3) * H + unit0 + (i & 7));
-    {
-      const int n4 = d.A * D2_BP / 4;              // float4 elements of one part's (A, 64) block; columns b >= B are stale, never used
-      const size_t pstride = (size_t)D2_BP * d.A;  // floats between parts
-      const float* src = wk.dq + (size_t)t * S * pstride;
-#pragma unroll 1
-      for (int i0 = 0; i0 < n4; i0 += 4 * D2_THREADS) {
-        float4 v[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const int i = i0 + k * D2_THREADS + tid;
-          v[k] = i < n4 ? ld_cg4(src + (size_t)i * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-        for (int pr = 1; pr < S; ++pr) {
-          float4 w4[4];
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const int i = i0 + k * D2_THREADS + tid;
-            w4[k] = i < n4 ? ld_cg4(src + pr * pstride + (size_t)i * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
-#pragma unroll
-          for (int k = 0; k < 4; ++k) { v[k].x += w4[k].x; v[k].y += w4[k].y; v[k].z += w4[k].z; v[k].w += w4[k].w; }
-        }
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const int i = i0 + k * D2_THREADS + tid;
-          if (i < n4) *reinterpret_cast<float4*>(dq_s + (size_t)i * 4) = v[k];
-        }
-      }
-    }
-    __syncthreads();
-    prof_mark(8);
-    float ex[2] = {0.f, 0.f};
-    {
-      const int ul = warp, bp = lane;
-#pragma unroll 4
-      for (int a_ = 0; a_ < d.A; ++a_) {
-        const float wv = wq_s[a_ * 8 + ul];
-        const float2 q2 = *reinterpret_cast<const float2*>(dq_s + a_ * D2_BP + 2 * bp);
-        ex[0] = fmaf(wv, q2.x, ex[0]); ex[1] = fmaf(wv, q2.y, ex[1]);
-      }
-      if (2 * bp >= B) ex[0] = 0.f;        // utterance slots >= B hold stale scratch
-      if (2 * bp + 1 >= B) ex[1] = 0.f;
-    }
-    prof_mark(9);
+  auto args_att = [&](int t, bool have_next) {   // attention LSTMCell of frame t (its h also feeds the query and the decoder cell)
     PwArgs a{};
     a.sav = tp.sav_att + (size_t)t * 5 * H * D2_BP;
     a.cprev = t > 0 ? tp.sav_att + ((size_t)(t - 1) * 5 + 4) * H * D2_BP : nullptr;
@@ -199,8 +153,84 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
     a.keep = tp.att_keep ? tp.att_keep + (size_t)t * B * H : nullptr;
     a.hidden_dropout = tp.hidden_dropout != 0; a.seed = tp.seed; a.rng_base = (1ull << 40) + (unsigned long long)t * B * H;
     a.dg = wk.dg_att; a.dgT = wk.dgT_att; a.ldT = (long long)T * D2_BP; a.tcol = (long long)t * D2_BP;
-    lstm_pointwise_bwd(a, H, B, unit0, pbase, sm.dc_att, stg, ex, bias_att);
+    return a;
+  };
+  auto pw_dec = [&](int t, bool have_next) {
+    const PwArgs a = args_dec(t, have_next);
+    const PwIn in = lstm_pointwise_load(a, H, B, unit0);
+    lstm_pointwise_bwd(a, in, H, B, unit0, pbase, sm.dc_dec, stg, nullptr, bias_dec);
+  };
+  // Phase P: attention cell of frame t and decoder cell of frame t-1.  Everything the phase reads is final when it starts (dx of phase
+  // G, d query of phase A, the tape), so ALL loads -- both cells' tape / gradient rows and the d query -- are issued before the first
+  // use: one L2 round trip for the phase instead of one per step.  d att_h through the query layer is split over the attention dims:
+  // warp w multiplies dims [16w, 16w+16) for all 8 units of the CTA straight from registers (every d query element is read once per CTA,
+  // not once per warp), the eight partials meet in shared memory.  Both cells share the two block barriers.
+  auto pw_phase = [&](int t, bool have_next) {
+    const PwArgs aa = args_att(t, have_next);
+    const PwIn ia = lstm_pointwise_load(aa, H, B, unit0);
+    PwArgs ad{};
+    PwIn id{};
+    if (t > 0) { ad = args_dec(t - 1, true); id = lstm_pointwise_load(ad, H, B, unit0); }
+    const float* wq = sm.wq;
+    if (!p.tc_att) {   // CUDA-core attention path: the resident slot holds its filter banks, the columns are restaged per frame
+#pragma unroll 1
+      for (int i = tid; i < d.A * 8; i += D2_THREADS) wq_s[i] = __ldg(p.w.Wq + (size_t)(i >> 3) * H + unit0 + (i & 7));
+      __syncthreads();
+      wq = wq_s;
+    }
+    {
+      const int SP = p.tc_att ? 1 : S;             // the tensor-core attention path sums the parts itself (DSMEM), the other leaves S blocks
+      const size_t pstride = (size_t)D2_BP * d.A;  // floats between parts; columns b >= B are stale, never used
+      const float* src = wk.dq + (size_t)t * S * pstride + 2 * lane;
+      float acc0[8], acc1[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) { acc0[u] = 0.f; acc1[u] = 0.f; }
+#pragma unroll 1
+      for (int ab = 16 * warp; ab < d.A; ab += 16 * (D2_THREADS / 32)) {
+        float2 q[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) q[k] = __ldcg(reinterpret_cast<const float2*>(src + (size_t)(ab + k) * D2_BP));
+        for (int pr = 1; pr < SP; ++pr) {
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
+            const float2 w2 = __ldcg(reinterpret_cast<const float2*>(src + pr * pstride + (size_t)(ab + k) * D2_BP));
+            q[k].x += w2.x; q[k].y += w2.y;
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          const float4 wa = *reinterpret_cast<const float4*>(wq + (ab + k) * 8), wb = *reinterpret_cast<const float4*>(wq + (ab + k) * 8 + 4);
+          acc0[0] = fmaf(wa.x, q[k].x, acc0[0]); acc1[0] = fmaf(wa.x, q[k].y, acc1[0]);
+          acc0[1] = fmaf(wa.y, q[k].x, acc0[1]); acc1[1] = fmaf(wa.y, q[k].y, acc1[1]);
+          acc0[2] = fmaf(wa.z, q[k].x, acc0[2]); acc1[2] = fmaf(wa.z, q[k].y, acc1[2]);
+          acc0[3] = fmaf(wa.w, q[k].x, acc0[3]); acc1[3] = fmaf(wa.w, q[k].y, acc1[3]);
+          acc0[4] = fmaf(wb.x, q[k].x, acc0[4]); acc1[4] = fmaf(wb.x, q[k].y, acc1[4]);
+          acc0[5] = fmaf(wb.y, q[k].x, acc0[5]); acc1[5] = fmaf(wb.y, q[k].y, acc1[5]);
+          acc0[6] = fmaf(wb.z, q[k].x, acc0[6]); acc1[6] = fmaf(wb.z, q[k].y, acc1[6]);
+          acc0[7] = fmaf(wb.w, q[k].x, acc0[7]); acc1[7] = fmaf(wb.w, q[k].y, acc1[7]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) *reinterpret_cast<float2*>(qred + (warp * 8 + u) * D2_BP + 2 * lane) = make_float2(acc0[u], acc1[u]);
+    }
+    __syncthreads();
+    prof_mark(8);
+    float ex[2] = {0.f, 0.f};
+#pragma unroll
+    for (int w8 = 0; w8 < D2_THREADS / 32; ++w8) {
+      const float2 r = *reinterpret_cast<const float2*>(qred + (w8 * 8 + warp) * D2_BP + 2 * lane);
+      ex[0] += r.x; ex[1] += r.y;
+    }
+    if (2 * lane >= B) ex[0] = 0.f;        // utterance slots >= B hold stale scratch
+    if (2 * lane + 1 >= B) ex[1] = 0.f;
+    prof_mark(9);
+    lstm_pointwise_compute(aa, ia, H, B, unit0, sm.dc_att, stg, ex, bias_att);
+    if (t > 0) lstm_pointwise_compute(ad, id, H, B, unit0, sm.dc_dec, stg2, nullptr, bias_dec);
+    __syncthreads();
+    lstm_pointwise_pack(aa, H, pbase, stg);
+    if (t > 0) lstm_pointwise_pack(ad, H, pbase, stg2);
     prof_mark(10);
+    // (no block barrier here: the grid barrier that follows synchronises the block before the ring -- where the staging lies -- is refilled)
   };
 
   // prologue: decoder cell of the last frame
@@ -257,8 +287,7 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
     if (!(alive = bar.sync(fail, false))) break;
     prof_mark(1);
     // ---- P: attention cell of frame t, decoder cell of frame t-1
-    pw_att(t, have_att_next);
-    if (t > 0) pw_dec(t - 1, true);
+    pw_phase(t, have_att_next);
     if (!(alive = bar.sync(fail, true))) break;
     prof_mark(2);
   }
@@ -386,7 +415,7 @@ int db_launch(const D2Dims& d, int T, int KattT, int KdecT, const DBWeights& w, 
   T2_REQUIRE((tc_att ? att_tc_scratch_bytes_host(d.L, S, d.A, d.EF) : att_bwd_scratch_floats_host(d.L, S, d.A, d.EF) * 4) <= ring,
              T2_ERR_UNSUPPORTED, "decoder backward: L=%d too long for the attention scratch", d.L);
   T2_REQUIRE(!tc_att || 2 * D2_LOC_K * 128 * 4 <= TG_M * TG_PART_LD * 4, T2_ERR_UNSUPPORTED, "decoder backward: H staging");
-  T2_REQUIRE((size_t)(64 * 33 + 16 + d.A * D2_BP + d.A * 8) * 4 <= ring, T2_ERR_UNSUPPORTED, "decoder backward: pointwise staging");
+  T2_REQUIRE((size_t)(2 * (64 * 33 + 16) + 64 * D2_BP + d.A * 8) * 4 <= ring, T2_ERR_UNSUPPORTED, "decoder backward: pointwise staging");
   const size_t smem = bsmem_bytes(d);
   T2_REQUIRE(smem <= 227 * 1024, T2_ERR_UNSUPPORTED, "decoder backward: %zu B shared memory", smem);
   T2_CHECK_CUDA(cudaFuncSetAttribute(decoder_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

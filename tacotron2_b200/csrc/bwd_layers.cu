@@ -139,8 +139,9 @@ __global__ void build_dproj_kernel(const float* __restrict__ d_mels, const float
   }
 }
 
-// dq [T][S][BP][A] -> sum over S, transposed bf16 (hi,lo) [2][A][T*BP]
-__global__ void dq_sumT_kernel(const float* __restrict__ dq, int T, int S, int A, int B, __nv_bfloat16* __restrict__ out) {
+// dq [T][S][A][BP] -> sum over the first SP of the S part blocks (the tensor-core attention backward sums the parts itself and fills
+// block 0 only: SP = 1), transposed bf16 (hi,lo) [2][A][T*BP]
+__global__ void dq_sumT_kernel(const float* __restrict__ dq, int T, int S, int SP, int A, int B, __nv_bfloat16* __restrict__ out) {
   const long long cols = (long long)T * D2_BP, n = cols * A;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const long long tb = i % cols;
@@ -148,7 +149,7 @@ __global__ void dq_sumT_kernel(const float* __restrict__ dq, int T, int S, int A
     const int b = (int)(tb % D2_BP), t = (int)(tb / D2_BP);
     float s = 0.f;
     if (b < B)
-      for (int p = 0; p < S; ++p) s += dq[(((size_t)t * S + p) * A + a) * D2_BP + b];
+      for (int p = 0; p < SP; ++p) s += dq[(((size_t)t * S + p) * A + a) * D2_BP + b];
     __nv_bfloat16 hi, lo;
     tc::split_bf16(s, hi, lo);
     out[i] = hi; out[n + i] = lo;
@@ -209,8 +210,8 @@ int build_dproj_launch(const float* d_mels, const float* d_gates, int B, int T, 
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }
-int dq_sumT_launch(const float* dq, int T, int S, int A, int B, __nv_bfloat16* out, cudaStream_t st) {
-  dq_sumT_kernel<<<gs((long long)T * D2_BP * A), 256, 0, st>>>(dq, T, S, A, B, out);
+int dq_sumT_launch(const float* dq, int T, int S, int SP, int A, int B, __nv_bfloat16* out, cudaStream_t st) {
+  dq_sumT_kernel<<<gs((long long)T * D2_BP * A), 256, 0, st>>>(dq, T, S, SP, A, B, out);
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }

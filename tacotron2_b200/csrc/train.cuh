@@ -101,7 +101,7 @@ int finalize_bwd_launch(const float* d_mels, const float* d_post, const float* d
                         float* d_mels_raw, float* d_postout, float* d_gates_raw, cudaStream_t st);
 int build_dproj_launch(const float* d_mels, const float* d_gates, int B, int T, int M, int ld, __nv_bfloat16* dP, __nv_bfloat16* dPT,
                        cudaStream_t st);
-int dq_sumT_launch(const float* dq, int T, int S, int A, int B, __nv_bfloat16* out, cudaStream_t st);
+int dq_sumT_launch(const float* dq, int T, int S, int SP, int A, int B, __nv_bfloat16* out, cudaStream_t st);
 int partial_sum_launch(const float* partial, int nparts, int n, float* out, cudaStream_t st);
 int copy2_launch(const float* src, float* a, float* b, int n, cudaStream_t st);
 int att_small_finish_launch(const float* Y, const float* conv_t, const float* dense_t, int A, float* g_dense, float* g_conv, cudaStream_t st);

@@ -423,7 +423,7 @@ int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const uns
     RC(bulk_gemm(c, Gd, xrows(xT_dec, d.KdecP, H + EF + C, R), 4 * R, R, 0, GemmNtOut{g_dec_hh, R, 1, 0, 1.f, 0}, partial, st));
   }
   {  // query layer: dWq[a][h] = sum dq[t,b][a] att_h_t[b][h]   (att_h_t = first block of the decoder-cell input of frame t)
-    RC(dq_sumT_launch(dq, T, S, A, B, dqT, st));
+    RC(dq_sumT_launch(dq, T, S, db_tc_att(d, t.xloc != nullptr) ? 1 : S, A, B, dqT, st));
     Opnd Q{dqT, (int)TB, (int)TB, 1, A, (long long)A * TB};
     RC(bulk_gemm(c, Q, xrows(xT_dec, d.KdecP, 0, H), A, H, 0, GemmNtOut{g_wq, H, 1, 0, 1.f, 0}, partial, st));
   }
