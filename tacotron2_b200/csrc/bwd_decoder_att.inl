@@ -60,8 +60,8 @@ __device__ void attention_bwd_phase(const D2Dims& d, const DBTape& tp, const DBW
     }
 #pragma unroll 1
     for (int c = tid; c < EF; c += D2_THREADS) {
-      float v = ld_cg(wk.dprojin + ((size_t)t * D2_BP + b) * d.KprojP + d.R + c) + ld_cg(wk.dx_dec + (size_t)(d.H + c) * D2_BP + b);
-      if (have_att_next) v += ld_cg(wk.dx_att + (size_t)(d.P + c) * D2_BP + b);
+      float v = ld_cg(wk.dprojin + ((size_t)t * D2_BP + b) * d.KprojP + d.R + c) + ld_cg(wk.dctxT_dec + (size_t)b * EF + c);
+      if (have_att_next) v += ld_cg(wk.dctxT_att + (size_t)b * EF + c);
       dctx[c] = v;
       if (part == 0) wk.dctx_tot[((size_t)t * D2_BP + b) * EF + c] = v;
     }

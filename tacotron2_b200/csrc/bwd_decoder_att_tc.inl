@@ -59,52 +59,70 @@ __device__ void attention_bwd_phase_tc(const D2Dims& d, const DBTape& tp, const 
   uint64_t* bar_h = sm.bars + 2 * D2_STAGES + 1;
   uint64_t* bar_all = sm.bars + 2 * D2_STAGES + 2;
 
-  float4 pre[3][4];   // taped pre-tanh arguments of this thread's first three position quads: requested now, used after the context step
-  if (has) {
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-      const int lt = (warp + 8 * i) * 4;
-#pragma unroll
-      for (int l = 0; l < 4; ++l)
-        pre[i][l] = (warp + 8 * i < ntile) ? __ldcs(reinterpret_cast<const float4*>(xloc + (size_t)min(lt + l, nl - 1) * A + a4))
-                                            : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-  }
+  float4 pre[3][4];   // taped pre-tanh arguments of this thread's first three position quads: requested behind the staging loads, used after the context step
   if (active) {
     // ---- stage: q_t, wcat of this frame (w_{t-1}, cum_{t-1}) with halo, total d ctx_t, w_t slice
     const float* wprev = tp.w_hist + ((size_t)t * D2_BP + b) * L;
     const float* wcum = tp.wcum_hist + ((size_t)t * D2_BP + b) * L;
     const float* wcur = tp.w_hist + ((size_t)(t + 1) * D2_BP + b) * L;
-#pragma unroll 1
-    for (int i = tid; i < A; i += D2_THREADS) q_s[i] = tp.q[((size_t)t * D2_BP + b) * A + i];
-#pragma unroll 1
-    for (int i = tid; i < Lh4; i += D2_THREADS) {
-      const int l = l0 + i - 15;
-      const bool in = (i < nl + 30 && l >= 0 && l < L);
-      wp[i] = in ? wprev[l] : 0.f;
-      wc[i] = in ? wcum[l] : 0.f;
+    // Every load of the staging step is issued before the first store (the loops it replaces paid one L2 round trip each: A == 128,
+    // Lh4 <= 160 and nl <= 128 give one element per thread, d ctx two; wider encoder outputs take the trailing loop): the step costs one round
+    // trip (~1.5 us under this load; storing the weight rows first and building the Toeplitz operand under the other loads was no faster).
+    const float qv = tid < A ? tp.q[((size_t)t * D2_BP + b) * A + tid] : 0.f;
+    const int lw = l0 + tid - 15;
+    const bool inw = tid < nl + 30 && lw >= 0 && lw < L;
+    const float wpv = inw ? wprev[lw] : 0.f, wcv = inw ? wcum[lw] : 0.f;
+    float dcv[2] = {0.f, 0.f};
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int c = tid + h * D2_THREADS;
+      if (c < EF) {
+        dcv[h] = ld_cg(wk.dprojin + ((size_t)t * D2_BP + b) * d.KprojP + d.R + c) + ld_cg(wk.dctxT_dec + (size_t)b * EF + c);
+        if (have_att_next) dcv[h] += ld_cg(wk.dctxT_att + (size_t)b * EF + c);
+      }
+    }
+    float* gc = wk.gcum + (size_t)b * L;
+    float wsv = 0.f, g = 0.f, s0 = 0.f;
+    if (tid < nl) {
+      const int l = l0 + tid;
+      wsv = wcur[l];
+      g = gc[l];
+      if (t + 1 < T) { g += wk.dconv[((size_t)1 * D2_BP + b) * L + l]; s0 = wk.dconv[((size_t)0 * D2_BP + b) * L + l]; }
+    }
+    if (has) {
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        const int lt = (warp + 8 * i) * 4;
+#pragma unroll
+        for (int l = 0; l < 4; ++l)
+          pre[i][l] = (warp + 8 * i < ntile) ? __ldcs(reinterpret_cast<const float4*>(xloc + (size_t)min(lt + l, nl - 1) * A + a4))
+                                              : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+    if (tid < Lh4) { wp[tid] = wpv; wc[tid] = wcv; }
+    if (tid < A) q_s[tid] = qv;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int c = tid + h * D2_THREADS;
+      if (c < EF) {
+        dctx[c] = dcv[h];
+        if (part == 0) wk.dctx_tot[((size_t)t * D2_BP + b) * EF + c] = dcv[h];
+      }
+    }
+    if (tid < nl) {
+      w_s[tid] = wsv;
+      gc[l0 + tid] = g;        // d/d cum_t (cum_t feeds cum_{t+1} and conv channel 1 of frame t+1)
+      gw[tid] = s0 + g;        // w_t also enters cum_t; the context term is added below
     }
 #pragma unroll 1
-    for (int c = tid; c < EF; c += D2_THREADS) {
-      float v = ld_cg(wk.dprojin + ((size_t)t * D2_BP + b) * d.KprojP + d.R + c) + ld_cg(wk.dx_dec + (size_t)(d.H + c) * D2_BP + b);
-      if (have_att_next) v += ld_cg(wk.dx_att + (size_t)(d.P + c) * D2_BP + b);
+    for (int c = tid + 2 * D2_THREADS; c < EF; c += D2_THREADS) {
+      float v = ld_cg(wk.dprojin + ((size_t)t * D2_BP + b) * d.KprojP + d.R + c) + ld_cg(wk.dctxT_dec + (size_t)b * EF + c);
+      if (have_att_next) v += ld_cg(wk.dctxT_att + (size_t)b * EF + c);
       dctx[c] = v;
       if (part == 0) wk.dctx_tot[((size_t)t * D2_BP + b) * EF + c] = v;
     }
-#pragma unroll 1
-    for (int i = tid; i < nl; i += D2_THREADS) w_s[i] = wcur[l0 + i];
-    {
-      float* gc = wk.gcum + (size_t)b * L;
-#pragma unroll 1
-      for (int i = tid; i < nl; i += D2_THREADS) {
-        const int l = l0 + i;
-        float g = gc[l], s0 = 0.f;
-        if (t + 1 < T) { g += wk.dconv[((size_t)1 * D2_BP + b) * L + l]; s0 = wk.dconv[((size_t)0 * D2_BP + b) * L + l]; }
-        gc[l] = g;             // d/d cum_t (cum_t feeds cum_{t+1} and conv channel 1 of frame t+1)
-        gw[i] = s0 + g;        // w_t also enters cum_t; the context term is added below
-      }
-    }
     __syncthreads();
+    ABW_MARK(12);
     // ---- Toeplitz operand of Y: row (c,j) = c*32 + j holds wcat[c][l0 + li + j - 15] over li (K-major in li); rows 31 / 63 and li >= nl are zero
 #pragma unroll 1
     for (int task = tid; task < 64 * (Kl >> 3); task += D2_THREADS) {
@@ -169,7 +187,28 @@ __device__ void attention_bwd_phase_tc(const D2Dims& d, const DBTape& tp, const 
     pd = block_reduce_sum(pd, red);
     if (tid == 0) xch[0] = pd;
   }
-  tc::cluster_sync();
+  // between the arrival and the wait of the cluster barrier (the peers' dot products): everything of the next step that does not need
+  // the total -- tanh of the taped arguments in place, the zero rows of the ds tiles
+  tc::cluster_arrive();
+  if (has) {
+    const float4 q4 = *reinterpret_cast<const float4*>(q_s + a4);
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int l = 0; l < 4; ++l) {
+        pre[i][l].x = tanh_fast(q4.x + pre[i][l].x); pre[i][l].y = tanh_fast(q4.y + pre[i][l].y);
+        pre[i][l].z = tanh_fast(q4.z + pre[i][l].z); pre[i][l].w = tanh_fast(q4.w + pre[i][l].w);
+      }
+  }
+  if (active) {
+    // rows [nl, Kl) of the ds tiles are part of the Y contraction: zero (the region is the TMA ring of the GEMM phase)
+#pragma unroll 1
+    for (int i = tid; i < (Kl - nl) * 4 * 8; i += D2_THREADS) {
+      const int r = nl + (i >> 5), tile = (i >> 3) & 3, ch = i & 7;
+      *reinterpret_cast<uint4*>(ds_t + tile * 16384 + ((r >> 3) << 10) + ((r & 7) << 7) + (ch << 4)) = make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+  tc::cluster_wait();
   if (active) {
     float tot = 0.f;
     {
@@ -182,12 +221,6 @@ __device__ void attention_bwd_phase_tc(const D2Dims& d, const DBTape& tp, const 
     }
 #pragma unroll 1
     for (int i = tid; i < nl; i += D2_THREADS) de[i] = w_s[i] * (gw[i] - tot);   // masked positions have w = 0 -> de = 0
-    // rows [nl, Kl) of the ds tiles are part of the Y contraction: zero (the region is the TMA ring of the GEMM phase)
-#pragma unroll 1
-    for (int i = tid; i < (Kl - nl) * 4 * 8; i += D2_THREADS) {
-      const int r = nl + (i >> 5), tile = (i >> 3) & 3, ch = i & 7;
-      *reinterpret_cast<uint4*>(ds_t + tile * 16384 + ((r >> 3) << 10) + ((r & 7) << 7) + (ch << 4)) = make_uint4(0u, 0u, 0u, 0u);
-    }
     __syncthreads();
 
     // ---- s = tanh(q + taped argument); ds = de * v * (1 - s^2) -> bf16 (hi,lo) operand tiles; dv, dq   (warp = 4 positions, lane = 4 dims)
@@ -205,11 +238,15 @@ __device__ void attention_bwd_phase_tc(const D2Dims& d, const DBTape& tp, const 
 #pragma unroll
         for (int l = 0; l < 4; ++l) {
           if (lt + l >= nl) continue;
-          float4 pm;
-          if (i < 3) pm = pre[i < 3 ? i : 0][l];
-          else pm = __ldcs(reinterpret_cast<const float4*>(xloc + (size_t)(lt + l) * A + a4));
+          float s0, s1, s2, s3;
+          if (i < 3) {
+            const float4 sv = pre[i < 3 ? i : 0][l];   // tanh applied above
+            s0 = sv.x; s1 = sv.y; s2 = sv.z; s3 = sv.w;
+          } else {
+            const float4 pm = __ldcs(reinterpret_cast<const float4*>(xloc + (size_t)(lt + l) * A + a4));
+            s0 = tanh_fast(q4.x + pm.x); s1 = tanh_fast(q4.y + pm.y); s2 = tanh_fast(q4.z + pm.z); s3 = tanh_fast(q4.w + pm.w);
+          }
           const float del = de[lt + l];
-          const float s0 = tanh_fast(q4.x + pm.x), s1 = tanh_fast(q4.y + pm.y), s2 = tanh_fast(q4.z + pm.z), s3 = tanh_fast(q4.w + pm.w);
           dvl[0] = fmaf(del, s0, dvl[0]); dvl[1] = fmaf(del, s1, dvl[1]); dvl[2] = fmaf(del, s2, dvl[2]); dvl[3] = fmaf(del, s3, dvl[3]);
           const float d0 = del * v4.x * (1.f - s0 * s0), d1 = del * v4.y * (1.f - s1 * s1), d2 = del * v4.z * (1.f - s2 * s2),
                       d3 = del * v4.w * (1.f - s3 * s3);

@@ -13,21 +13,45 @@ struct DBParams {
 };
 
 // one 128-row tile of an input-gradient GEMM: dx[k0 + r][b] = sum_p WT[k0 + r][p] dg[b][p]
+// Rows [c0, c1) of the product are the context block of the cell input: the attention backward reads them per utterance, so a tile that
+// holds any of them is reduced with lanes over rows and those rows go to dxT [BP][c1 - c0] (utterance-major, 128-byte stores) instead of
+// the k-major dx (whose column read costs one 32-byte sector per element: 1.2 us of the attention phase).
 template <class Side>
 __device__ __forceinline__ bool dx_tile(tg::Pipe& pipe, const BSmem& sm, const CUtensorMap* wmap, const CUtensorMap* dgmap, int ktile,
-                                        int npb, uint32_t rank, float* dx /*[K][BP]*/, Side side, int wpol) {
+                                        int npb, uint32_t rank, float* dx /*[K][BP]*/, float* dxT, int c0, int c1, Side side, int wpol) {
   tg::XSrc xs{dgmap, 0, dgmap, 0, npb};
   // the transposed weights of the decoder cell stream through L2 evict-first: the per-frame working set of the attention backward stays resident
   const bool ok = tg::gemm(pipe, wmap, ktile * TG_M, npb, xs, (int)rank, npb, D2_CLUSTER, 0u, side, wpol);
   tg::accum_to_smem(pipe, 0u, sm.part);
   tc::cluster_sync();
   // CTA `rank` reduces rows [32*rank, 32*rank+32) of the tile over the four partials
+  if (ktile * TG_M < c1 && (ktile + 1) * TG_M > c0) {
+    // the sums of the context rows go back into this CTA's own rows of its partial (only this CTA reads them, each element by the thread
+    // that rewrites it), then leave transposed from local shared memory.  (Reading the peers' partials with lanes over rows instead
+    // cost 4.6 us per frame: four times the DSMEM packets.)
 #pragma unroll 1
-  for (int i = threadIdx.x; i < 32 * (TG_N / 2); i += D2_THREADS) {
-    const int row = 32 * (int)rank + i / (TG_N / 2), col = 2 * (i % (TG_N / 2));
-    const float2 s = tg::reduce4(sm.part, row, col);
-    const int k = ktile * TG_M + row;
-    *reinterpret_cast<float2*>(dx + (size_t)k * D2_BP + col) = s;
+    for (int i = threadIdx.x; i < 32 * (TG_N / 2); i += D2_THREADS) {
+      const int row = 32 * (int)rank + i / (TG_N / 2), col = 2 * (i % (TG_N / 2));
+      const float2 s = tg::reduce4(sm.part, row, col);
+      const int k = ktile * TG_M + row;
+      if (k >= c0 && k < c1) *reinterpret_cast<float2*>(sm.part + row * TG_PART_LD + col) = s;
+      else *reinterpret_cast<float2*>(dx + (size_t)k * D2_BP + col) = s;
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (int i = threadIdx.x; i < 32 * TG_N; i += D2_THREADS) {
+      const int row = 32 * (int)rank + (i & 31), col = i >> 5;
+      const int k = ktile * TG_M + row;
+      if (k >= c0 && k < c1) dxT[(size_t)col * (c1 - c0) + (k - c0)] = sm.part[row * TG_PART_LD + col];
+    }
+  } else {
+#pragma unroll 1
+    for (int i = threadIdx.x; i < 32 * (TG_N / 2); i += D2_THREADS) {
+      const int row = 32 * (int)rank + i / (TG_N / 2), col = 2 * (i % (TG_N / 2));
+      const float2 s = tg::reduce4(sm.part, row, col);
+      const int k = ktile * TG_M + row;
+      *reinterpret_cast<float2*>(dx + (size_t)k * D2_BP + col) = s;
+    }
   }
   // (the caller separates two tiles of one cluster with a cluster barrier -- the peers must be done reading this CTA's partial
   //  before it is overwritten; after the last tile the grid barrier that follows covers it)
@@ -133,6 +157,40 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
   float* wq_s = qred + 64 * D2_BP;            // [A][8] query weight columns when they are not resident (CUDA-core attention path)
   bool alive = true, fail = false;
 
+  // Every first touch of the forward's tape is a DRAM miss (written once by the forward kernel).  The slices an iteration reads are pulled
+  // into L2 ahead of use -- NOT beside the input-gradient GEMMs, whose weight stream owns the HBM bandwidth of that phase (prefetching
+  // there moved 11 MB per frame into the one bandwidth-bound phase), but from the latency-bound phase before: the pointwise phase of
+  // frame t+1 requests what the attention phase of frame t reads, the attention phase what the pointwise phase after it reads.
+  auto pf = [&](const void* q, size_t bytes) {
+    const uintptr_t a0 = reinterpret_cast<uintptr_t>(q);
+    const char* c = reinterpret_cast<const char*>(a0 & ~(uintptr_t)127);
+    bytes += (size_t)(a0 & 127);
+    for (size_t o = (size_t)tid * 128; o < bytes; o += (size_t)D2_THREADS * 128) tc::prefetch_l2(c + o);
+  };
+  auto prefetch_for_attention = [&](int t) {   // location term, conv features, query, weight rows with halo, the projection's share of d ctx
+    if (t < 0 || !att_active) return;
+    const int Lc = (d.L + S - 1) / S, l0 = min(d.L, att_part * Lc), nl = max(0, min(d.L, l0 + Lc) - l0);
+    if (tp.xloc) pf(tp.xloc + ((size_t)t * 128 + blockIdx.x) * Lc * d.A, (size_t)nl * d.A * 4);
+    if (tp.floc) pf(tp.floc + ((size_t)t * 128 + blockIdx.x) * Lc * D2_LOC_F, (size_t)nl * D2_LOC_F * 4);
+    const int lo = max(0, l0 - 15), hi = min(d.L, l0 + nl + 15);
+    if (hi > lo) {
+      pf(tp.w_hist + ((size_t)t * D2_BP + att_b) * d.L + lo, (size_t)(hi - lo) * 4);
+      pf(tp.wcum_hist + ((size_t)t * D2_BP + att_b) * d.L + lo, (size_t)(hi - lo) * 4);
+      pf(tp.w_hist + ((size_t)(t + 1) * D2_BP + att_b) * d.L + lo, (size_t)(hi - lo) * 4);
+    }
+    pf(tp.q + ((size_t)t * D2_BP + att_b) * d.A, (size_t)d.A * 4);
+    pf(wk.dprojin + ((size_t)t * D2_BP + att_b) * d.KprojP + d.R, (size_t)d.EF * 4);
+  };
+  auto prefetch_for_pointwise = [&](int t) {   // gates and cell states of this CTA's 8 units (attention cell t, decoder cell t-1), d rnn_h columns
+#pragma unroll 1
+    for (int g = 0; g < 5; ++g) {
+      pf(tp.sav_att + (((size_t)t * 5 + g) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
+      if (t > 0) pf(tp.sav_dec + (((size_t)(t - 1) * 5 + g) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
+    }
+    if (t > 0) pf(tp.sav_att + (((size_t)(t - 1) * 5 + 4) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
+    if (t > 1) pf(tp.sav_dec + (((size_t)(t - 2) * 5 + 4) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
+    if (t > 0 && tid < D2_BP) tc::prefetch_l2(wk.dprojin + ((size_t)(t - 1) * D2_BP + tid) * d.KprojP + unit0);
+  };
   auto args_dec = [&](int t, bool have_next) {   // decoder LSTMCell of frame t
     PwArgs a{};
     a.sav = tp.sav_dec + (size_t)t * 5 * H * D2_BP;
@@ -171,6 +229,7 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
     PwArgs ad{};
     PwIn id{};
     if (t > 0) { ad = args_dec(t - 1, true); id = lstm_pointwise_load(ad, H, B, unit0); }
+    prefetch_for_attention(t - 1);   // behind this phase's own loads
     const float* wq = sm.wq;
     if (!p.tc_att) {   // CUDA-core attention path: the resident slot holds its filter banks, the columns are restaged per frame
 #pragma unroll 1
@@ -235,6 +294,7 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
 
   // prologue: decoder cell of the last frame
   pw_dec(T - 1, false);
+  prefetch_for_attention(T - 1);
   alive = bar.sync(fail, true);
   prof_mark(2);
 
@@ -248,37 +308,16 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
       for (int tile = cl; tile < n_dec + n_att; tile += nclusters) {
         bool ok;
         if (tile != cl) tc::cluster_sync();   // second tile of this cluster in the same frame: the partial buffer is about to be rewritten
-        // Warps 2..7 are idle while the tile streams: they pull the slices of the forward's tape that the attention backward and the
-        // two pointwise phases of this iteration read (written once by the forward, so every first touch is a DRAM miss) into L2.
-        auto tape_prefetch = [&]() {
-          if (tile != cl) return;
-          const int ptid = tid - 64;
-          auto pf = [&](const void* q, size_t bytes) {
-            const char* c = static_cast<const char*>(q);
-            for (size_t o = (size_t)ptid * 128; o < bytes; o += (size_t)192 * 128) tc::prefetch_l2(c + o);
-          };
-          if (att_active) {
-            const int Lc = (d.L + S - 1) / S, nl = max(0, min(d.L, (att_part + 1) * Lc) - att_part * Lc);
-            if (tp.xloc) pf(tp.xloc + ((size_t)t * 128 + blockIdx.x) * Lc * d.A, (size_t)nl * d.A * 4);
-            if (tp.floc) pf(tp.floc + ((size_t)t * 128 + blockIdx.x) * Lc * D2_LOC_F, (size_t)nl * D2_LOC_F * 4);
-          }
-#pragma unroll 1
-          for (int g = 0; g < 5; ++g) {   // post-activation gates and cell state of this CTA's 8 units
-            pf(tp.sav_att + (((size_t)t * 5 + g) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
-            if (t > 0) pf(tp.sav_dec + (((size_t)(t - 1) * 5 + g) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
-          }
-          // the previous cell states the two pointwise phases read (c_{t-1} of the attention cell, c_{t-2} of the decoder cell)
-          if (t > 0) pf(tp.sav_att + (((size_t)(t - 1) * 5 + 4) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
-          if (t > 1) pf(tp.sav_dec + (((size_t)(t - 2) * 5 + 4) * H + unit0) * D2_BP, (size_t)8 * D2_BP * 4);
-        };
-        if (tile < n_dec) ok = dx_tile(pipe, sm, &maps.wt_dec, &maps.dg_dec, tile, npb, rank, wk.dx_dec, tape_prefetch, p.wpol_dec);
-        else ok = dx_tile(pipe, sm, &maps.wt_att, &maps.dg_att, tile - n_dec + att_tile0, npb, rank, wk.dx_att, tape_prefetch, p.wpol_att);
+        auto no_side = []() {};
+        if (tile < n_dec) ok = dx_tile(pipe, sm, &maps.wt_dec, &maps.dg_dec, tile, npb, rank, wk.dx_dec, wk.dctxT_dec, d.H, d.H + d.EF, no_side, p.wpol_dec);
+        else ok = dx_tile(pipe, sm, &maps.wt_att, &maps.dg_att, tile - n_dec + att_tile0, npb, rank, wk.dx_att, wk.dctxT_att, d.P, d.P + d.EF, no_side, p.wpol_att);
         if (!ok) fail = true;
       }
     }
     if (!(alive = bar.sync(fail, false))) break;
     prof_mark(0);
     // ---- A: attention backward of frame t
+    prefetch_for_pointwise(t);
     if (p.tc_att)
       attention_bwd_phase_tc(d, tp, wk, sm, base, att_active, att_b, att_part, S, t, T, have_att_next, pipe.tmem, tmem_p, acc.dv, stt, fail,
                              p.prof, &prof_last);

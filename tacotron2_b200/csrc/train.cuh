@@ -61,6 +61,8 @@ struct DBWork {
   __nv_bfloat16* dgT_dec;   // [2][4R][T*BP]
   float* dx_att;            // [2 parity][KattT][BP]  output of the att input-gradient GEMM (k-major)
   float* dx_dec;            // [2 parity][KdecT][BP]
+  float* dctxT_dec;         // [BP][EF] the context rows of dx_dec / dx_att utterance-major: the attention backward reads one utterance's
+  float* dctxT_att;         //          row (the k-major layout costs one 32-byte sector per element there)
   float* dpre;              // [T][BP][P]     d/d prenet output
   float* dctx_tot;          // [T][BP][EF]    total d/d ctx_t (for the bulk memory gradient)
   float* dq;                // [T][S][A][BP]  per-part partial d/d query (utterance-minor)

@@ -302,6 +302,8 @@ int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const uns
   const int64_t zoff0 = wa.off;
   float* dx_att = wa.take<float>((size_t)c->KattT * D2_BP);
   float* dx_dec = wa.take<float>((size_t)c->KdecT * D2_BP);
+  float* dctxT_dec = wa.take<float>((size_t)D2_BP * EF);
+  float* dctxT_att = wa.take<float>((size_t)D2_BP * EF);
   float* dconv = wa.take<float>((size_t)2 * D2_BP * L);
   float* gcum = wa.take<float>((size_t)D2_BP * L);
   unsigned* barrier = wa.take<unsigned>(4);
@@ -371,7 +373,7 @@ int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const uns
   else if (d2_precompute_fits(d)) { t.xloc = tp.xloc; t.floc = tp.floc; }
   t.memory = memory; t.pmem = pmem; t.mask = mask; t.att_keep = att_keep; t.rnn_keep = rnn_keep; t.seed = seed; t.hidden_dropout = 1;
   DBWork k{};
-  k.dprojin = dprojin; k.dg_att = dg_att; k.dg_dec = dg_dec; k.dgT_att = dgT_att; k.dgT_dec = dgT_dec; k.dx_att = dx_att; k.dx_dec = dx_dec;
+  k.dprojin = dprojin; k.dg_att = dg_att; k.dg_dec = dg_dec; k.dgT_att = dgT_att; k.dgT_dec = dgT_dec; k.dx_att = dx_att; k.dx_dec = dx_dec; k.dctxT_dec = dctxT_dec; k.dctxT_att = dctxT_att;
   k.dpre = dpre; k.dctx_tot = dctx_tot; k.dq = dq; k.dpm = d_pmem; k.dconv = dconv; k.gcum = gcum; k.small_partial = small_partial;
   k.dbias = dbias; k.barrier = barrier; k.status = c->status_dev;
   DBMaps maps;
