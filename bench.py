@@ -480,8 +480,8 @@ def train_bench(dev, rank, world, steps, warmup=3):
         from tacotron2_b200 import _lib
         cyc = (ctypes.c_ulonglong * 16)()
         _lib.check(_lib.load().t2_debug_phase_cycles(model._ctx, cyc))
-        names = ["input_grad_gemms", "attention_bwd_tail", "pointwise_barrier", "att_toeplitz_build", "att_ctx_dot", "att_softmax_dense_ds",
-                 "att_df_dWd", "att_dwcat", "pointwise_loads_query_partials", "pointwise_query_reduce", "pointwise_cells", "att_csync_df", "att_stage_loads", "att_dWc"]
+        names = ["input_grad_epilogue_barrier", "attention_bwd_tail", "pointwise_barrier", "att_toeplitz_build", "att_ctx_dot", "att_softmax_dense_ds",
+                 "att_df_dWd", "att_dwcat", "pointwise_loads_query_partials", "pointwise_query_reduce", "pointwise_cells", "att_csync_df", "att_stage_loads", "input_grad_gemm_stream"]
         out["decoder_bwd_phase_us_per_frame"] = {n: round(cyc[i] / 1965.0 / TRAIN_T, 2) for i, n in enumerate(names)}
         # roofline of the step's dominant kernel (decoder_bwd_kernel): algorithmic bytes per frame for 64 utterances at C3 =
         # transposed LSTM weights 71.3 MB + memory / processed memory 24.6 MB + gate tapes 5.2 MB + operand rows 2.4 MB +

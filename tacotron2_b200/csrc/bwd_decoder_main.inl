@@ -9,19 +9,21 @@ struct DBParams {
   DBWeights w;
   DBTape tp;
   DBWork wk;
-  unsigned long long* prof;   // [16] or null: cycles of CTA 0 (0 G, 1 A tail, 2 P decoder cell + barrier, 3..7 inside A, 8..10 inside P)
+  unsigned long long* prof;   // [16] or null: cycles of CTA 0 (13 G until the accumulator is complete, 0 G epilogue + barrier, 12 / 3..7 / 11 inside A,
+                              // 1 A tail + barrier, 8..10 inside P, 2 P barrier)
 };
 
 // one 128-row tile of an input-gradient GEMM: dx[k0 + r][b] = sum_p WT[k0 + r][p] dg[b][p]
 // Rows [c0, c1) of the product are the context block of the cell input: the attention backward reads them per utterance, so a tile that
 // holds any of them is reduced with lanes over rows and those rows go to dxT [BP][c1 - c0] (utterance-major, 128-byte stores) instead of
 // the k-major dx (whose column read costs one 32-byte sector per element: 1.2 us of the attention phase).
-template <class Side>
+template <class Side, class Mark>
 __device__ __forceinline__ bool dx_tile(tg::Pipe& pipe, const BSmem& sm, const CUtensorMap* wmap, const CUtensorMap* dgmap, int ktile,
-                                        int npb, uint32_t rank, float* dx /*[K][BP]*/, float* dxT, int c0, int c1, Side side, int wpol) {
+                                        int npb, uint32_t rank, float* dx /*[K][BP]*/, float* dxT, int c0, int c1, Side side, int wpol, Mark mark) {
   tg::XSrc xs{dgmap, 0, dgmap, 0, npb};
   // the transposed weights of the decoder cell stream through L2 evict-first: the per-frame working set of the attention backward stays resident
   const bool ok = tg::gemm(pipe, wmap, ktile * TG_M, npb, xs, (int)rank, npb, D2_CLUSTER, 0u, side, wpol);
+  mark();
   tg::accum_to_smem(pipe, 0u, sm.part);
   tc::cluster_sync();
   // CTA `rank` reduces rows [32*rank, 32*rank+32) of the tile over the four partials
@@ -309,8 +311,8 @@ decoder_bwd_kernel(const __grid_constant__ DBMaps maps, const DBParams p) {
         bool ok;
         if (tile != cl) tc::cluster_sync();   // second tile of this cluster in the same frame: the partial buffer is about to be rewritten
         auto no_side = []() {};
-        if (tile < n_dec) ok = dx_tile(pipe, sm, &maps.wt_dec, &maps.dg_dec, tile, npb, rank, wk.dx_dec, wk.dctxT_dec, d.H, d.H + d.EF, no_side, p.wpol_dec);
-        else ok = dx_tile(pipe, sm, &maps.wt_att, &maps.dg_att, tile - n_dec + att_tile0, npb, rank, wk.dx_att, wk.dctxT_att, d.P, d.P + d.EF, no_side, p.wpol_att);
+        if (tile < n_dec) ok = dx_tile(pipe, sm, &maps.wt_dec, &maps.dg_dec, tile, npb, rank, wk.dx_dec, wk.dctxT_dec, d.H, d.H + d.EF, no_side, p.wpol_dec, [&]() { prof_mark(13); });
+        else ok = dx_tile(pipe, sm, &maps.wt_att, &maps.dg_att, tile - n_dec + att_tile0, npb, rank, wk.dx_att, wk.dctxT_att, d.P, d.P + d.EF, no_side, p.wpol_att, [&]() { prof_mark(13); });
         if (!ok) fail = true;
       }
     }
