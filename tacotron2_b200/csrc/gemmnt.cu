@@ -46,17 +46,29 @@ __global__ void __launch_bounds__(256, 1) gemm_nt_kernel(const __grid_constant__
   if (warp == 0 && lane == 0) {
     asm volatile("fence.proxy.async;" ::: "memory");
     int st = 0; uint32_t ph = 0;
-    const uint32_t tx = (uint32_t)(a.npass == 3 ? 2 : 1) * (GN_A_TILE + (a.mn ? (uint32_t)((a.NT + 63) / 64) * 8192u : b_tile));
+    const bool amn = (a.mn & 1) != 0, bmn = (a.mn & 2) != 0;
+    const int kinb_blocks = ((a.KinB ? a.KinB : a.Kin) + 63) >> 6;   // the B operand's own two-level split of the contraction index
+    const uint32_t tx = (uint32_t)(a.npass == 3 ? 2 : 1) * (GN_A_TILE + (bmn ? (uint32_t)((a.NT + 63) / 64) * 8192u : b_tile));
     for (int kb = kb0; kb < kb1; ++kb) {
       if (!tc::mbar_wait(empty + st, ph ^ 1)) { ok = false; break; }
       uint8_t* sp_ = base + (size_t)st * GN_STAGE_BYTES;
       tc::mbar_arrive_expect_tx(full + st, tx);
-      if (a.mn) {   // channels-last operands: [64 kin rows][64 channels] tiles, hi then lo plane per 64-channel block
+      if (a.mn) {   // an MN-major operand arrives as [64 kin rows][64 channels] tiles, hi then lo plane per 64-channel block
         const int ko = kb / kin_blocks, ki = (kb - ko * kin_blocks) * 64;
+        const int kob = kb / kinb_blocks, kib = (kb - kob * kinb_blocks) * 64;
         const uint32_t blk = (a.npass == 3 ? 2u : 1u) * 8192u;
-        tc::tma_load_4d(sp_, &a.a_map, full + st, m0, ki, ko, 0);
-        tc::tma_load_4d(sp_ + blk, &a.a_map, full + st, m0 + 64, ki, ko, 0);
-        for (int nb = 0; nb * 64 < a.NT; ++nb) tc::tma_load_4d(sp_ + 2 * GN_A_TILE + nb * blk, &a.b_map, full + st, n0 + nb * 64, ki + shift, ko, 0);
+        if (amn) {
+          tc::tma_load_4d(sp_, &a.a_map, full + st, m0, ki, ko, 0);
+          tc::tma_load_4d(sp_ + blk, &a.a_map, full + st, m0 + 64, ki, ko, 0);
+        } else {
+          tc::tma_load_4d(sp_, &a.a_map, full + st, ki, ko, m0 + z * a.a_zrow, 0);
+        }
+        if (bmn) {
+          for (int nb = 0; nb * 64 < a.NT; ++nb)
+            tc::tma_load_4d(sp_ + 2 * GN_A_TILE + nb * blk, &a.b_map, full + st, n0 + nb * 64, kib + shift, kob, 0);
+        } else {
+          tc::tma_load_4d(sp_ + 2 * GN_A_TILE, &a.b_map, full + st, kib + shift, kob, brow0 + z * a.b_zrow, 0);
+        }
       } else if (kb < nkb_seg1) {
         const int ko = kb / kin_blocks, ki = (kb - ko * kin_blocks) * 64;
         tc::tma_load_4d(sp_, &a.a_map, full + st, ki, ko, m0 + z * a.a_zrow, 0);
@@ -70,29 +82,29 @@ __global__ void __launch_bounds__(256, 1) gemm_nt_kernel(const __grid_constant__
     }
   } else if (warp == 1 && lane == 0) {
     int st = 0; uint32_t ph = 0, acc = 0;
-    const uint32_t idesc = tc::idesc_bf16_f32(128, a.NT) | (a.mn ? (1u << 15) | (1u << 16) : 0u);   // bits 15 / 16: A / B MN-major
+    const bool amn = (a.mn & 1) != 0, bmn = (a.mn & 2) != 0;
+    const uint32_t idesc = tc::idesc_bf16_f32(128, a.NT) | (amn ? (1u << 15) : 0u) | (bmn ? (1u << 16) : 0u);   // bits 15 / 16: A / B MN-major
     for (int kb = kb0; kb < kb1; ++kb) {
       if (!tc::mbar_wait(full + st, ph)) { ok = false; break; }
       tc::tc_fence_after();
       const uint32_t sb = tc::smem_u32(base + (size_t)st * GN_STAGE_BYTES);
       uint64_t ahi, alo, bhi, blo;
-      if (a.mn) {   // 64-channel blocks lie blk bytes apart (hi | lo per block), 8 kin rows = one 1024-byte swizzle atom
-        const uint32_t blk = (a.npass == 3 ? 2u : 1u) * 8192u;
-        ahi = tc::smem_desc_sw128_mn(sb, blk, 1024); alo = tc::smem_desc_sw128_mn(sb + 8192, blk, 1024);
-        bhi = tc::smem_desc_sw128_mn(sb + 2 * GN_A_TILE, blk, 1024); blo = tc::smem_desc_sw128_mn(sb + 2 * GN_A_TILE + 8192, blk, 1024);
-      } else {
-        ahi = tc::smem_desc_sw128(sb); alo = tc::smem_desc_sw128(sb + GN_A_TILE);
-        bhi = tc::smem_desc_sw128(sb + 2 * GN_A_TILE); blo = tc::smem_desc_sw128(sb + 2 * GN_A_TILE + b_tile);
-      }
+      // MN-major: 64-channel blocks lie blk bytes apart (hi | lo per block), 8 kin rows = one 1024-byte swizzle atom
+      const uint32_t blk = (a.npass == 3 ? 2u : 1u) * 8192u;
+      if (amn) { ahi = tc::smem_desc_sw128_mn(sb, blk, 1024); alo = tc::smem_desc_sw128_mn(sb + 8192, blk, 1024); }
+      else { ahi = tc::smem_desc_sw128(sb); alo = tc::smem_desc_sw128(sb + GN_A_TILE); }
+      if (bmn) { bhi = tc::smem_desc_sw128_mn(sb + 2 * GN_A_TILE, blk, 1024); blo = tc::smem_desc_sw128_mn(sb + 2 * GN_A_TILE + 8192, blk, 1024); }
+      else { bhi = tc::smem_desc_sw128(sb + 2 * GN_A_TILE); blo = tc::smem_desc_sw128(sb + 2 * GN_A_TILE + b_tile); }
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        const uint64_t adv = a.mn ? (uint64_t)(k * 128) : (uint64_t)(k * 2);   // 16 kin: two atoms (2048 B) MN-major, 32 B K-major
+        // 16 kin: two atoms (2048 B) MN-major, 32 B K-major
+        const uint64_t adva = amn ? (uint64_t)(k * 128) : (uint64_t)(k * 2), advb = bmn ? (uint64_t)(k * 128) : (uint64_t)(k * 2);
         if (a.npass == 3) {
-          tc::umma_bf16(tmem, alo + adv, bhi + adv, idesc, acc);
-          tc::umma_bf16(tmem, ahi + adv, blo + adv, idesc, 1u);
-          tc::umma_bf16(tmem, ahi + adv, bhi + adv, idesc, 1u);
+          tc::umma_bf16(tmem, alo + adva, bhi + advb, idesc, acc);
+          tc::umma_bf16(tmem, ahi + adva, blo + advb, idesc, 1u);
+          tc::umma_bf16(tmem, ahi + adva, bhi + advb, idesc, 1u);
         } else {
-          tc::umma_bf16(tmem, ahi + adv, bhi + adv, idesc, acc);
+          tc::umma_bf16(tmem, ahi + adva, bhi + advb, idesc, acc);
         }
         acc = 1u;
       }
@@ -251,7 +263,9 @@ int gemmnt_launch(const GemmNtArgs& a, const GemmNtOut& o, cudaStream_t st) {
   T2_REQUIRE(a.NT % 16 == 0 && a.NT >= 16 && a.NT <= 128 && a.splitk >= 1 && a.nz >= 1 && (a.partial || a.direct_out), T2_ERR_ARG,
              "gemmnt: bad arguments NT=%d splitk=%d nz=%d", a.NT, a.splitk, a.nz);
   T2_REQUIRE(!a.direct_out || (a.splitk == 1 && a.nz == 1), T2_ERR_ARG, "gemmnt: direct output needs splitk == 1 and nz == 1");
-  T2_REQUIRE(!a.mn || (a.Kin2 == 0 && a.a_zrow == 0 && a.b_zrow == 0 && a.b_row_step == 0), T2_ERR_ARG, "gemmnt: MN-major mode takes one segment and no row offsets");
+  T2_REQUIRE(!a.mn || (a.Kin2 == 0 && a.b_row_step == 0 && (!(a.mn & 1) || a.a_zrow == 0) && (!(a.mn & 2) || a.b_zrow == 0)), T2_ERR_ARG,
+             "gemmnt: an MN-major operand takes one segment and no row offsets");
+  T2_REQUIRE(a.mn >= 0 && a.mn <= 3 && (a.KinB == 0 || a.mn), T2_ERR_ARG, "gemmnt: mn = %d / KinB = %d", a.mn, a.KinB);
   if (a.M <= 0 || a.N <= 0) return T2_OK;
   const int Nt = (a.N + a.NT - 1) / a.NT, Mt = (a.M + 127) / 128;
   const size_t smem = 1024 + (size_t)GN_STAGES * GN_STAGE_BYTES + 128;
@@ -277,6 +291,16 @@ int gemmnt_make_map(CUtensorMap* m, const __nv_bfloat16* base, int Kin, int kin_
   unsigned long long dims[4] = {(unsigned long long)Kin, (unsigned long long)Kout, (unsigned long long)rows, 2ull};
   unsigned long long st[3] = {(unsigned long long)kin_ld * 2, (unsigned long long)Kout * kin_ld * 2, (unsigned long long)plane_elems * 2};
   unsigned box[4] = {64u, 1u, (unsigned)box_rows, npass == 3 ? 2u : 1u};
+  return tc_make_tmap_bf16(m, base, 4, dims, st, box);
+}
+
+int gemmnt_make_map_cl_strided(CUtensorMap* m, const __nv_bfloat16* base, int Kin, int Kout, int rows, long long kin_elems, long long kout_elems,
+                               long long plane_elems, int npass) {
+  T2_REQUIRE(kin_elems % 8 == 0 && kout_elems % 8 == 0 && plane_elems % 8 == 0 && ((uintptr_t)base & 15) == 0, T2_ERR_ARG,
+             "gemmnt: MN-major operand strides %lld / %lld / %lld or base not 16-byte aligned", kin_elems, kout_elems, plane_elems);
+  unsigned long long dims[4] = {(unsigned long long)rows, (unsigned long long)Kin, (unsigned long long)Kout, 2ull};
+  unsigned long long st[3] = {(unsigned long long)kin_elems * 2, (unsigned long long)kout_elems * 2, (unsigned long long)plane_elems * 2};
+  unsigned box[4] = {64u, 64u, 1u, npass == 3 ? 2u : 1u};
   return tc_make_tmap_bf16(m, base, 4, dims, st, box);
 }
 

@@ -28,7 +28,12 @@ struct GemmNtArgs {
   // mn = 1: both operands are read MN-major from channels-last tensors [2][Kout][Kin][rows] (maps from gemmnt_make_map_cl: dims
   // {rows, Kin, Kout, 2}, box {64, 64, 1, planes}): the contraction index kin is then an OUTER TMA coordinate, so the per-z shift may be
   // any integer (conv taps need no shifted copies) and neither operand needs a K-major transpose.  No second segment, no z row offsets.
+  // mn is a bit mask: 1 = A MN-major, 2 = B MN-major, 3 = both (the conv weight gradients).  With one MN-major operand the other keeps the
+  // K-major form above and the two operands may split the contraction index differently: KinB (0 = Kin) is the B operand's inner extent,
+  // K-block kb reads B at (kin, kout) = ((kb mod KinB/64)*64 + shift, kb div KinB/64).  E.g. the LSTM weight gradients: A = d gates
+  // K-major over (frame, utterance) as one run of T*64, B = the operand rows [frame][plane][utterance][k] as they lie: KinB = 64, kout = frame.
   int mn;
+  int KinB;
 };
 
 struct GemmNtOut {
@@ -48,6 +53,9 @@ int gemmnt_make_map(CUtensorMap* m, const __nv_bfloat16* base, int Kin, int kin_
 
 // Operand map for a channels-last bf16 (hi,lo) tensor [2][Kout][Kin][rows] (rows contiguous, rows % 8 == 0), read MN-major (a.mn = 1).
 int gemmnt_make_map_cl(CUtensorMap* m, const __nv_bfloat16* base, int Kin, int Kout, int rows, long long plane_elems, int npass);
+// The same with explicit element strides of the kin / kout / plane coordinates (operand rows that are interleaved with other data).
+int gemmnt_make_map_cl_strided(CUtensorMap* m, const __nv_bfloat16* base, int Kin, int Kout, int rows, long long kin_elems, long long kout_elems,
+                               long long plane_elems, int npass);
 
 // Batched transposes into K-major operands.  Batch bb reads src + bb*src_bstride ([R][C], row stride ld) and writes
 // dst[plane][c][bb*dst_boff + r] for r < R_ld (zeros for r >= R); dst row stride dst_ld, plane stride dst_plane elements.

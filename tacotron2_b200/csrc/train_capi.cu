@@ -42,7 +42,7 @@ int conv_wgrad(t2_ctx* c, const __nv_bfloat16* dz, const __nv_bfloat16* x, int B
   GemmNtArgs a{};
   a.M = Cout; a.N = Cin; a.NT = Cin % 128 == 0 ? 128 : ((Cin + 15) & ~15);
   T2_REQUIRE(a.NT <= 128, T2_ERR_UNSUPPORTED, "conv_wgrad: Cin=%d", Cin);
-  a.Kin = T; a.Kout = B; a.nz = k; a.shift0 = -((k - 1) / 2); a.shift_step = 1; a.a_zrow = 0; a.b_zrow = 0; a.mn = 1;
+  a.Kin = T; a.Kout = B; a.nz = k; a.shift0 = -((k - 1) / 2); a.shift_step = 1; a.a_zrow = 0; a.b_zrow = 0; a.mn = 3;
   a.splitk = 0; a.npass = c->npass;
   const long long need = gemmnt_partial_floats(a, c->num_sms);
   T2_REQUIRE(need <= partial_floats, T2_ERR_WORKSPACE, "conv_wgrad: partial buffer too small");
@@ -237,6 +237,26 @@ int bulk_gemm(t2_ctx* c, const Opnd& A, const Opnd& Bo, int M, int N, int shiftB
   return gemmnt_launch(a, o, st);
 }
 
+// The same product with the B operand read MN-major from the decoder's operand rows as the forward kernel left them,
+// x [slot][plane][64 utterances][KP]: C[m][n] = sum_{t < T, b} A[m][t*64 + b] x[slot0 + t][b][col0 + n].  No K-major copy of x is made
+// (the three transposes of the LSTM inputs were 0.65 ms of the training step).  col0 and KP must be multiples of 8 elements.
+struct XRows { const __nv_bfloat16* x; int KP, col0, slot0; };
+int bulk_gemm_xrows(t2_ctx* c, const Opnd& A, const XRows& X, int T, int M, int N, const GemmNtOut& o, float* partial, cudaStream_t st) {
+  GemmNtArgs a{};
+  a.M = M; a.N = N; a.NT = (N >= 128 || N % 16) ? (N >= 128 ? 128 : ((N + 15) & ~15)) : N;
+  a.Kin = A.Kin; a.Kout = A.Kout; a.nz = 1; a.npass = c->npass; a.mn = 2; a.KinB = D2_BP;
+  T2_REQUIRE(A.Kout == 1 && A.Kin == T * D2_BP && X.col0 % 8 == 0 && X.KP % 8 == 0, T2_ERR_ARG, "bulk_gemm_xrows: operand shapes");
+  a.splitk = 0;
+  const long long need = gemmnt_partial_floats(a, c->num_sms);
+  T2_REQUIRE(need <= BULK_PARTIAL_FLOATS, T2_ERR_WORKSPACE, "bulk_gemm_xrows: split-K slab of %lld floats exceeds the reserved %lld", need,
+             (long long)BULK_PARTIAL_FLOATS);
+  a.partial = partial;
+  RC(gemmnt_make_map(&a.a_map, A.base, A.Kin, A.kin_ld, A.Kout, A.rows, A.plane, 128, c->npass));
+  const long long slot = 2ll * D2_BP * X.KP;
+  RC(gemmnt_make_map_cl_strided(&a.b_map, X.x + (size_t)X.slot0 * slot + X.col0, D2_BP, T, N, X.KP, slot, (long long)D2_BP * X.KP, c->npass));
+  return gemmnt_launch(a, o, st);
+}
+
 // tmp[m][t*64 + b] (+ bias) -> mels[b][t][m], gates[b][t]; one CTA per frame, transposed through shared memory
 __global__ void proj_finish_kernel(const float* __restrict__ tmp, const float* __restrict__ bias, int B, int T, int M, float* __restrict__ mels,
                                    float* __restrict__ gates) {
@@ -407,36 +427,50 @@ int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const uns
   RC(copy2_launch(dbias, g_att_bi, g_att_bh, 4 * H, st));
   RC(copy2_launch(dbias + 4 * H, g_dec_bi, g_dec_bh, 4 * R, st));
 
-  // ---- K-major copies of the per-frame LSTM inputs: xT[k][slot*64 + b]
-  RC(transpose_bf16_launch(tp.xatt, d.KattP, (long long)2 * D2_BP * d.KattP, (long long)D2_BP * d.KattP, xT_att, D2_BP, d.KattP, D2_BP, TB1,
-                           D2_BP, T + 1, 0, (long long)d.KattP * TB1, st));
-  RC(transpose_bf16_launch(tp.tfp, P, (long long)2 * D2_BP * P, (long long)D2_BP * P, xT_att, D2_BP, P, D2_BP, TB1, D2_BP, T + 1, 0,
-                           (long long)d.KattP * TB1, st));   // teacher forcing: the prenet block of the input lives in tfp
-  RC(transpose_bf16_launch(tp.xdec, d.KdecP, (long long)2 * D2_BP * d.KdecP, (long long)D2_BP * d.KdecP, xT_dec, D2_BP, d.KdecP, D2_BP, TB1,
-                           D2_BP, T + 1, 0, (long long)d.KdecP * TB1, st));
-  auto xrows = [&](const __nv_bfloat16* xTb, int KP, int row0, int rows, bool all_slots = false) {
-    return Opnd{xTb + (size_t)row0 * TB1, (int)(all_slots ? TB1 : TB), (int)TB1, 1, rows, (long long)KP * TB1};
-  };
-  {  // LSTMCell weight gradients  dW[r][k] = sum_{t,b} dgates[t,b][r] x[t,b][k]
-    Opnd Ga{dgT_att, (int)TB, (int)TB, 1, 4 * H, 4ll * H * TB}, Gd{dgT_dec, (int)TB, (int)TB, 1, 4 * R, 4ll * R * TB};
+  // The weight gradients that contract d gates / d query / d projection with the per-frame operand rows read those rows MN-major as the
+  // forward left them ([slot][plane][utterance][k]) when every column window starts on a 16-byte boundary; otherwise (controls of odd
+  // width) they go through K-major copies xT[k][slot*64 + b].
+  const bool x_mn = P % 8 == 0 && (P + EF) % 8 == 0 && H % 8 == 0 && (H + EF + C) % 8 == 0 && d.KattP % 8 == 0 && d.KdecP % 8 == 0 &&
+                    !getenv("T2B200_WGRAD_KMAJOR");
+  const Opnd Ga{dgT_att, (int)TB, (int)TB, 1, 4 * H, 4ll * H * TB}, Gd{dgT_dec, (int)TB, (int)TB, 1, 4 * R, 4ll * R * TB};
+  const Opnd Q{dqT, (int)TB, (int)TB, 1, A, (long long)A * TB}, Pm{dPT, (int)TB, (int)TB, 1, M + 1, (long long)PROJ_LD * TB};
+  RC(dq_sumT_launch(dq, T, S, db_tc_att(d, t.xloc != nullptr) ? 1 : S, A, B, dqT, st));
+  if (x_mn) {
+    const XRows Xpre{tp.tfp, P, 0, 0};   // teacher forcing: the prenet block of the attention-cell input lives in tfp
+    auto xa = [&](int col0) { return XRows{tp.xatt, d.KattP, col0, 0}; };
+    auto xd = [&](int col0, int slot0 = 0) { return XRows{tp.xdec, d.KdecP, col0, slot0}; };
+    // LSTMCell weight gradients  dW[r][k] = sum_{t,b} dgates[t,b][r] x[t,b][k]
+    RC(bulk_gemm_xrows(c, Ga, Xpre, T, 4 * H, P, GemmNtOut{g_att_ih, P + EF, 1, 0, 1.f, 0}, partial, st));
+    RC(bulk_gemm_xrows(c, Ga, xa(P), T, 4 * H, EF, GemmNtOut{g_att_ih + P, P + EF, 1, 0, 1.f, 0}, partial, st));
+    RC(bulk_gemm_xrows(c, Ga, xa(P + EF), T, 4 * H, H, GemmNtOut{g_att_hh, H, 1, 0, 1.f, 0}, partial, st));
+    RC(bulk_gemm_xrows(c, Gd, xd(0), T, 4 * R, H + EF + C, GemmNtOut{g_dec_ih, H + EF + C, 1, 0, 1.f, 0}, partial, st));
+    RC(bulk_gemm_xrows(c, Gd, xd(H + EF + C), T, 4 * R, R, GemmNtOut{g_dec_hh, R, 1, 0, 1.f, 0}, partial, st));
+    // query layer: dWq[a][h] = sum dq[t,b][a] att_h_t[b][h]   (att_h_t = first block of the decoder-cell input of frame t)
+    RC(bulk_gemm_xrows(c, Q, xd(0), T, A, H, GemmNtOut{g_wq, H, 1, 0, 1.f, 0}, partial, st));
+    // mel / gate projection weights: input [rnn_h_t | ctx_t | controls]; rnn_h_t sits in slot t+1 of the decoder-cell input
+    RC(bulk_gemm_xrows(c, Pm, xd(H + EF + C, 1), T, M + 1, R, GemmNtOut{wtmp, d.KprojP, 1, 0, 1.f, 0}, partial, st));
+    RC(bulk_gemm_xrows(c, Pm, xd(H), T, M + 1, EF + C, GemmNtOut{wtmp + R, d.KprojP, 1, 0, 1.f, 0}, partial, st));
+  } else {
+    RC(transpose_bf16_launch(tp.xatt, d.KattP, (long long)2 * D2_BP * d.KattP, (long long)D2_BP * d.KattP, xT_att, D2_BP, d.KattP, D2_BP, TB1,
+                             D2_BP, T + 1, 0, (long long)d.KattP * TB1, st));
+    RC(transpose_bf16_launch(tp.tfp, P, (long long)2 * D2_BP * P, (long long)D2_BP * P, xT_att, D2_BP, P, D2_BP, TB1, D2_BP, T + 1, 0,
+                             (long long)d.KattP * TB1, st));   // teacher forcing: the prenet block of the input lives in tfp
+    RC(transpose_bf16_launch(tp.xdec, d.KdecP, (long long)2 * D2_BP * d.KdecP, (long long)D2_BP * d.KdecP, xT_dec, D2_BP, d.KdecP, D2_BP, TB1,
+                             D2_BP, T + 1, 0, (long long)d.KdecP * TB1, st));
+    auto xrows = [&](const __nv_bfloat16* xTb, int KP, int row0, int rows, bool all_slots = false) {
+      return Opnd{xTb + (size_t)row0 * TB1, (int)(all_slots ? TB1 : TB), (int)TB1, 1, rows, (long long)KP * TB1};
+    };
     RC(bulk_gemm(c, Ga, xrows(xT_att, d.KattP, 0, P + EF), 4 * H, P + EF, 0, GemmNtOut{g_att_ih, P + EF, 1, 0, 1.f, 0}, partial, st));
     RC(bulk_gemm(c, Ga, xrows(xT_att, d.KattP, P + EF, H), 4 * H, H, 0, GemmNtOut{g_att_hh, H, 1, 0, 1.f, 0}, partial, st));
     RC(bulk_gemm(c, Gd, xrows(xT_dec, d.KdecP, 0, H + EF + C), 4 * R, H + EF + C, 0, GemmNtOut{g_dec_ih, H + EF + C, 1, 0, 1.f, 0}, partial, st));
     RC(bulk_gemm(c, Gd, xrows(xT_dec, d.KdecP, H + EF + C, R), 4 * R, R, 0, GemmNtOut{g_dec_hh, R, 1, 0, 1.f, 0}, partial, st));
-  }
-  {  // query layer: dWq[a][h] = sum dq[t,b][a] att_h_t[b][h]   (att_h_t = first block of the decoder-cell input of frame t)
-    RC(dq_sumT_launch(dq, T, S, db_tc_att(d, t.xloc != nullptr) ? 1 : S, A, B, dqT, st));
-    Opnd Q{dqT, (int)TB, (int)TB, 1, A, (long long)A * TB};
     RC(bulk_gemm(c, Q, xrows(xT_dec, d.KdecP, 0, H), A, H, 0, GemmNtOut{g_wq, H, 1, 0, 1.f, 0}, partial, st));
-  }
-  {  // mel / gate projection weights: input [rnn_h_t | ctx_t | controls]; rnn_h_t sits in slot t+1 of the decoder-cell input
-    Opnd Pm{dPT, (int)TB, (int)TB, 1, M + 1, (long long)PROJ_LD * TB};
     RC(bulk_gemm(c, Pm, xrows(xT_dec, d.KdecP, H + EF + C, R, true), M + 1, R, D2_BP, GemmNtOut{wtmp, d.KprojP, 1, 0, 1.f, 0}, partial, st));
     RC(bulk_gemm(c, Pm, xrows(xT_dec, d.KdecP, H, EF + C), M + 1, EF + C, 0, GemmNtOut{wtmp + R, d.KprojP, 1, 0, 1.f, 0}, partial, st));
-    T2_CHECK_CUDA(cudaMemcpy2DAsync(g_wmel, (size_t)(R + EF + C) * 4, wtmp, (size_t)d.KprojP * 4, (size_t)(R + EF + C) * 4, M,
-                                    cudaMemcpyDeviceToDevice, st));
-    T2_CHECK_CUDA(cudaMemcpyAsync(g_wgate, wtmp + (size_t)M * d.KprojP, (size_t)(R + EF) * 4, cudaMemcpyDeviceToDevice, st));
   }
+  T2_CHECK_CUDA(cudaMemcpy2DAsync(g_wmel, (size_t)(R + EF + C) * 4, wtmp, (size_t)d.KprojP * 4, (size_t)(R + EF + C) * 4, M,
+                                  cudaMemcpyDeviceToDevice, st));
+  T2_CHECK_CUDA(cudaMemcpyAsync(g_wgate, wtmp + (size_t)M * d.KprojP, (size_t)(R + EF) * 4, cudaMemcpyDeviceToDevice, st));
   {  // attention memory: d memory[b][l][c] = sum_t w_t[b][l] dctx_t[b][c]   (one GEMM per utterance, batched over z = b)
     RC(transpose_split_launch(aligns, L, (long long)T * L, alT, T, L, Tp, Tp, (long long)L * Tp, B, (long long)B * L * Tp, st));
     RC(transpose_split_launch(dctx_tot, (long long)D2_BP * EF, EF, dcT, T, EF, Tp, Tp, (long long)EF * Tp, B, (long long)B * EF * Tp, st));
@@ -444,9 +478,19 @@ int decode_bwd_impl(t2_ctx* c, const float* memory, const float* pmem, const uns
     RC(bulk_gemm(c, Aw, Dc, L, EF, 0, GemmNtOut{d_memory, EF, 1, (long long)L * EF, 1.f, 0}, partial, st, B, L, EF));
   }
   {  // d prenet output [t][b][k] = sum_r dgates_att[t,b][r] W_ih[r][k], k < P: off the recurrent chain, one bulk GEMM
-    RC(transpose_bf16_launch(dgT_att, TB, 0, 4ll * H * TB, dgH, 4 * H, (int)TB, 4 * H, 4 * H, 0, 1, 0, TB * 4 * H, st));
-    Opnd Gh{dgH, 4 * H, 4 * H, 1, (int)TB, TB * 4 * H}, Wp{c->WpreT_b, 4 * H, 4 * H, 1, P, (long long)P * 4 * H};
-    RC(bulk_gemm(c, Gh, Wp, (int)TB, P, 0, GemmNtOut{dpre, P, 1, 0, 1.f, 0}, nullptr, st, 1, 0, 0, true));
+    // A = the d gates history dgT_att [4H][T*64] read MN-major (rows of the product = its contiguous index): no [T*64][4H] copy
+    if (!getenv("T2B200_WGRAD_KMAJOR")) {
+      GemmNtArgs a{};
+      a.M = (int)TB; a.N = P; a.NT = P >= 128 ? 128 : ((P + 15) & ~15);
+      a.Kin = 4 * H; a.Kout = 1; a.nz = 1; a.npass = c->npass; a.mn = 1; a.splitk = 1; a.direct_out = dpre; a.direct_ldm = P;
+      RC(gemmnt_make_map_cl(&a.a_map, dgT_att, 4 * H, 1, (int)TB, 4ll * H * TB, c->npass));
+      RC(gemmnt_make_map(&a.b_map, c->WpreT_b, 4 * H, 4 * H, 1, P, (long long)P * 4 * H, a.NT, c->npass));
+      RC(gemmnt_launch(a, GemmNtOut{dpre, P, 1, 0, 1.f, 0}, st));
+    } else {
+      RC(transpose_bf16_launch(dgT_att, TB, 0, 4ll * H * TB, dgH, 4 * H, (int)TB, 4 * H, 4 * H, 0, 1, 0, TB * 4 * H, st));
+      Opnd Gh{dgH, 4 * H, 4 * H, 1, (int)TB, TB * 4 * H}, Wp{c->WpreT_b, 4 * H, 4 * H, 1, P, (long long)P * 4 * H};
+      RC(bulk_gemm(c, Gh, Wp, (int)TB, P, 0, GemmNtOut{dpre, P, 1, 0, 1.f, 0}, nullptr, st, 1, 0, 0, true));
+    }
   }
   {  // prenet backward (model/tacotron2.py:85-92), rows n = t*B + b, t < T (the T+1-th prenet frame is never used, :317)
     const float scale = 1.0f / (1.0f - c->cfg.dropout);
