@@ -99,9 +99,42 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       }
     }
   } else {
-    // ---- epilogue warps 2..9: thread = output position (TMEM lane quarter = warp % 4), 16-channel chunks alternate between the two groups
+    // ---- epilogue warps 2..9: thread = output position (TMEM lane quarter = warp % 4), 16-channel chunks alternate between the two groups.
+    // What a chunk adds from global memory (residual, running sum, dropout mask: first-touch DRAM reads in the narrow HiFi-GAN stages)
+    // is requested one chunk AHEAD -- the next chunk of this tile or the first of the next tile -- so its latency runs under the
+    // accumulator wait, the tensor-memory read and the stores of the current chunk (it used to sit between them: 5.8 us per tile).
     const int q = warp & 3, grp = (warp - 2) >> 2, row = 32 * q + lane;
     const long long plane = (long long)a.B * a.T * a.Cout;
+    const int nch = a.NT / 16;
+    struct Pre { float4 r[4], ac[4]; uint4 kp; };
+    const bool keep16 = (a.keep_ld & 15) == 0 && (reinterpret_cast<uintptr_t>(a.keep) & 15) == 0;
+    auto load_pre = [&](int tile, int c, Pre& p) {
+      const int bt = tile / ntn, n = (tile - bt * ntn) * a.NT + c * 16;
+      const int b = bt / tiles_t, t = (bt - b * tiles_t) * 128 + row;
+      if (t >= a.T) return;
+      const size_t pos = (size_t)b * a.T + t;
+      if (a.residual) {
+        const float4* src = reinterpret_cast<const float4*>(a.residual + (size_t)b * a.res_bstride + (size_t)t * a.Cout + n);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) p.r[i] = src[i];
+      }
+      if (a.accum) {
+        const float4* src = reinterpret_cast<const float4*>(a.accum + pos * a.Cout + n);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) p.ac[i] = src[i];   // (may alias out_f32: each element is read, then written, by this thread only)
+      }
+      if (a.keep) {
+        const unsigned char* kp = a.keep + pos * a.keep_ld + n;
+        if (keep16) p.kp = __ldg(reinterpret_cast<const uint4*>(kp));
+        else {
+          unsigned char* dstb = reinterpret_cast<unsigned char*>(&p.kp);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) dstb[i] = __ldg(kp + i);
+        }
+      }
+    };
+    Pre cur, nxt;
+    if ((int)blockIdx.x < ntiles && grp < nch) load_pre(blockIdx.x, grp, cur);
     int it = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       const int buf = it & 1;
@@ -114,42 +147,52 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       const bool valid = got && t < a.T && !*fail_s;
       const size_t pos = (size_t)b * a.T + min(t, a.T - 1);
 #pragma unroll 1
-      for (int c = grp; c < a.NT / 16; c += 2) {
+      for (int c = grp; c < nch; c += 2) {
+        {
+          int ntile = tile, nc = c + 2;
+          if (nc >= nch) { ntile = tile + gridDim.x; nc = grp; }
+          if (ntile < ntiles) load_pre(ntile, nc, nxt);
+        }
         float v[16];
         tc::tmem_ld16(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * 128 + c * 16), v);
         tc::tmem_ld_wait();
-        if (!valid) continue;
-        const int n = n0 + c * 16;
+        if (valid) {
+          const int n = n0 + c * 16;
+          const float* rr = reinterpret_cast<const float*>(cur.r);
+          const float* aa = reinterpret_cast<const float*>(cur.ac);
+          const unsigned char* kk = reinterpret_cast<const unsigned char*>(&cur.kp);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          float x = v[i];
-          const int ci = a.chan_mod > 0 ? (n + i) % a.chan_mod : n + i;
-          if (a.scale) x = fmaf(x, __ldg(a.scale + ci), __ldg(a.shift + ci));
-          else if (a.shift) x += __ldg(a.shift + ci);
-          if (a.act == ACT_RELU) x = fmaxf(x, 0.f);
-          else if (a.act == ACT_TANH) x = tanhf(x);
-          else if (a.act == ACT_GELU) x = 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
-          if (a.keep) x = a.keep[pos * a.keep_ld + n + i] ? x * a.drop_scale : 0.f;
-          if (a.residual) x += a.residual[(size_t)b * a.res_bstride + (size_t)t * a.Cout + n + i];
-          if (a.out_scale != 0.f) x *= a.out_scale;
-          if (a.accum) x += a.accum[pos * a.Cout + n + i];
-          v[i] = x;
-        }
-        if (a.out_c0 && n == 0) a.out_c0[pos] = v[0];
-        if (a.out_f32) {
-          float4* dst = reinterpret_cast<float4*>(a.out_f32 + pos * a.Cout + n);
+          for (int i = 0; i < 16; ++i) {
+            float x = v[i];
+            const int ci = a.chan_mod > 0 ? (n + i) % a.chan_mod : n + i;
+            if (a.scale) x = fmaf(x, __ldg(a.scale + ci), __ldg(a.shift + ci));
+            else if (a.shift) x += __ldg(a.shift + ci);
+            if (a.act == ACT_RELU) x = fmaxf(x, 0.f);
+            else if (a.act == ACT_TANH) x = tanhf(x);
+            else if (a.act == ACT_GELU) x = 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
+            if (a.keep) x = kk[i] ? x * a.drop_scale : 0.f;
+            if (a.residual) x += rr[i];
+            if (a.out_scale != 0.f) x *= a.out_scale;
+            if (a.accum) x += aa[i];
+            v[i] = x;
+          }
+          if (a.out_c0 && n == 0) a.out_c0[pos] = v[0];
+          if (a.out_f32) {
+            float4* dst = reinterpret_cast<float4*>(a.out_f32 + pos * a.Cout + n);
 #pragma unroll
-          for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-        }
-        if (a.out_b16) {
-          __align__(16) __nv_bfloat16 hi[16], lo[16];
+            for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          }
+          if (a.out_b16) {
+            __align__(16) __nv_bfloat16 hi[16], lo[16];
 #pragma unroll
-          for (int i = 0; i < 16; ++i) tc::split_bf16((a.b16_slope != 0.f && v[i] < 0.f) ? v[i] * a.b16_slope : v[i], hi[i], lo[i]);
-          uint4* dh = reinterpret_cast<uint4*>(a.out_b16 + pos * a.Cout + n);
-          uint4* dl = reinterpret_cast<uint4*>(a.out_b16 + plane + pos * a.Cout + n);
-          dh[0] = reinterpret_cast<const uint4*>(hi)[0]; dh[1] = reinterpret_cast<const uint4*>(hi)[1];
-          dl[0] = reinterpret_cast<const uint4*>(lo)[0]; dl[1] = reinterpret_cast<const uint4*>(lo)[1];
+            for (int i = 0; i < 16; ++i) tc::split_bf16((a.b16_slope != 0.f && v[i] < 0.f) ? v[i] * a.b16_slope : v[i], hi[i], lo[i]);
+            uint4* dh = reinterpret_cast<uint4*>(a.out_b16 + pos * a.Cout + n);
+            uint4* dl = reinterpret_cast<uint4*>(a.out_b16 + plane + pos * a.Cout + n);
+            dh[0] = reinterpret_cast<const uint4*>(hi)[0]; dh[1] = reinterpret_cast<const uint4*>(hi)[1];
+            dl[0] = reinterpret_cast<const uint4*>(lo)[0]; dl[1] = reinterpret_cast<const uint4*>(lo)[1];
+          }
         }
+        cur = nxt;
       }
       tc::tc_fence_before();
       __syncwarp();
