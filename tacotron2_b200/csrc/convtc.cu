@@ -13,6 +13,96 @@
 
 namespace {
 
+// What one 16-channel chunk of the epilogue adds from global memory, requested ahead of its use.
+struct CtPre { float4 r[4], ac[4]; uint4 kp; };
+
+__device__ __forceinline__ void ct_load_pre(const ConvTcArgs& a, int b, int t, int n, bool keep16, CtPre& p) {
+  if (t >= a.T) return;
+  const size_t pos = (size_t)b * a.T + t;
+  if (a.residual) {
+    const float4* src = reinterpret_cast<const float4*>(a.residual + (size_t)b * a.res_bstride + (size_t)t * a.Cout + n);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) p.r[i] = __ldcs(src + i);   // read once: keep it from evicting the per-channel tables and the weights
+  }
+  if (a.accum) {
+    const float4* src = reinterpret_cast<const float4*>(a.accum + pos * a.Cout + n);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) p.ac[i] = __ldcs(src + i);   // (may alias out_f32: each element is read, then written, by this thread only)
+  }
+  if (a.keep) {
+    const unsigned char* kp = a.keep + pos * a.keep_ld + n;
+    if (keep16) p.kp = __ldg(reinterpret_cast<const uint4*>(kp));
+    else {
+      unsigned char* dstb = reinterpret_cast<unsigned char*>(&p.kp);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) dstb[i] = __ldg(kp + i);
+    }
+  }
+}
+
+// bias / folded BatchNorm, activation, dropout, residual, receptive-field sum, then the fp32 and bf16 (hi,lo) stores of one chunk
+// tab: the per-channel shift (and scale) of all Cout columns in shared memory ([Cout] shift, then [Cout] scale), or null: from global
+// memory.  (ncu on the narrow HiFi-GAN layers: 27 % of all stall samples sat on the sixteen bias loads of a chunk -- the activations
+// streaming through L1 kept evicting the 128-byte bias vector, one L2 round trip per chunk.)
+#define CT_TAB_MAX 2048
+__device__ __forceinline__ void ct_fill_tab(const ConvTcArgs& a, float* tab) {
+  for (int n = threadIdx.x; n < a.Cout; n += blockDim.x) {
+    const int ci = a.chan_mod > 0 ? n % a.chan_mod : n;
+    tab[n] = a.shift ? __ldg(a.shift + ci) : 0.f;
+    tab[a.Cout + n] = a.scale ? __ldg(a.scale + ci) : 1.f;
+  }
+}
+
+__device__ __forceinline__ void ct_finish_chunk(const ConvTcArgs& a, float (&v)[16], const CtPre& cur, size_t pos, int n, long long plane,
+                                                const float* tab) {
+  const float* rr = reinterpret_cast<const float*>(cur.r);
+  const float* aa = reinterpret_cast<const float*>(cur.ac);
+  const unsigned char* kk = reinterpret_cast<const unsigned char*>(&cur.kp);
+  float sh[16], sc[16];
+  if (tab) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      *reinterpret_cast<float4*>(sh + 4 * i) = *reinterpret_cast<const float4*>(tab + n + 4 * i);
+      if (a.scale) *reinterpret_cast<float4*>(sc + 4 * i) = *reinterpret_cast<const float4*>(tab + a.Cout + n + 4 * i);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    float x = v[i];
+    if (tab) {
+      if (a.scale) x = fmaf(x, sc[i], sh[i]);
+      else if (a.shift) x += sh[i];
+    } else {
+      const int ci = a.chan_mod > 0 ? (n + i) % a.chan_mod : n + i;
+      if (a.scale) x = fmaf(x, __ldg(a.scale + ci), __ldg(a.shift + ci));
+      else if (a.shift) x += __ldg(a.shift + ci);
+    }
+    if (a.act == ACT_RELU) x = fmaxf(x, 0.f);
+    else if (a.act == ACT_TANH) x = tanhf(x);
+    else if (a.act == ACT_GELU) x = 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
+    if (a.keep) x = kk[i] ? x * a.drop_scale : 0.f;
+    if (a.residual) x += rr[i];
+    if (a.out_scale != 0.f) x *= a.out_scale;
+    if (a.accum) x += aa[i];
+    v[i] = x;
+  }
+  if (a.out_c0 && n == 0) a.out_c0[pos] = v[0];
+  if (a.out_f32) {
+    float4* dst = reinterpret_cast<float4*>(a.out_f32 + pos * a.Cout + n);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+  }
+  if (a.out_b16) {
+    __align__(16) __nv_bfloat16 hi[16], lo[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) tc::split_bf16((a.b16_slope != 0.f && v[i] < 0.f) ? v[i] * a.b16_slope : v[i], hi[i], lo[i]);
+    uint4* dh = reinterpret_cast<uint4*>(a.out_b16 + pos * a.Cout + n);
+    uint4* dl = reinterpret_cast<uint4*>(a.out_b16 + plane + pos * a.Cout + n);
+    dh[0] = reinterpret_cast<const uint4*>(hi)[0]; dh[1] = reinterpret_cast<const uint4*>(hi)[1];
+    dl[0] = reinterpret_cast<const uint4*>(lo)[0]; dl[1] = reinterpret_cast<const uint4*>(lo)[1];
+  }
+}
+
 __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_constant__ ConvTcArgs a, int ntiles) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* base = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -22,8 +112,10 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   uint64_t* acc_empty = acc_full + 2;        // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
   volatile int* fail_s = reinterpret_cast<volatile int*>(tmem_slot + 1);
+  float* tab = a.Cout <= CT_TAB_MAX ? reinterpret_cast<float*>(base + CT_STAGES * CT_STAGE_BYTES + 128) : nullptr;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int tiles_t = (a.T + 127) >> 7, tiles_bt = a.B * tiles_t;
+  if (tab) ct_fill_tab(a, tab);
   const int dil = a.dil > 1 ? a.dil : 1;
   const int cblocks = (a.Cin + 63) >> 6, nkb = a.k * cblocks, pad = ((a.k - 1) >> 1) * dil;
   const uint32_t b_tile = (uint32_t)a.NT * 128u;  // bytes of one bf16 weight tile (NT rows x 128 B)
@@ -106,34 +198,13 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
     const int q = warp & 3, grp = (warp - 2) >> 2, row = 32 * q + lane;
     const long long plane = (long long)a.B * a.T * a.Cout;
     const int nch = a.NT / 16;
-    struct Pre { float4 r[4], ac[4]; uint4 kp; };
     const bool keep16 = (a.keep_ld & 15) == 0 && (reinterpret_cast<uintptr_t>(a.keep) & 15) == 0;
-    auto load_pre = [&](int tile, int c, Pre& p) {
+    auto load_pre = [&](int tile, int c, CtPre& p) {
       const int bt = tile / ntn, n = (tile - bt * ntn) * a.NT + c * 16;
       const int b = bt / tiles_t, t = (bt - b * tiles_t) * 128 + row;
-      if (t >= a.T) return;
-      const size_t pos = (size_t)b * a.T + t;
-      if (a.residual) {
-        const float4* src = reinterpret_cast<const float4*>(a.residual + (size_t)b * a.res_bstride + (size_t)t * a.Cout + n);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) p.r[i] = src[i];
-      }
-      if (a.accum) {
-        const float4* src = reinterpret_cast<const float4*>(a.accum + pos * a.Cout + n);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) p.ac[i] = src[i];   // (may alias out_f32: each element is read, then written, by this thread only)
-      }
-      if (a.keep) {
-        const unsigned char* kp = a.keep + pos * a.keep_ld + n;
-        if (keep16) p.kp = __ldg(reinterpret_cast<const uint4*>(kp));
-        else {
-          unsigned char* dstb = reinterpret_cast<unsigned char*>(&p.kp);
-#pragma unroll
-          for (int i = 0; i < 16; ++i) dstb[i] = __ldg(kp + i);
-        }
-      }
+      ct_load_pre(a, b, t, n, keep16, p);
     };
-    Pre cur, nxt;
+    CtPre cur, nxt;
     if ((int)blockIdx.x < ntiles && grp < nch) load_pre(blockIdx.x, grp, cur);
     int it = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
@@ -156,43 +227,180 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         float v[16];
         tc::tmem_ld16(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * 128 + c * 16), v);
         tc::tmem_ld_wait();
-        if (valid) {
-          const int n = n0 + c * 16;
-          const float* rr = reinterpret_cast<const float*>(cur.r);
-          const float* aa = reinterpret_cast<const float*>(cur.ac);
-          const unsigned char* kk = reinterpret_cast<const unsigned char*>(&cur.kp);
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            float x = v[i];
-            const int ci = a.chan_mod > 0 ? (n + i) % a.chan_mod : n + i;
-            if (a.scale) x = fmaf(x, __ldg(a.scale + ci), __ldg(a.shift + ci));
-            else if (a.shift) x += __ldg(a.shift + ci);
-            if (a.act == ACT_RELU) x = fmaxf(x, 0.f);
-            else if (a.act == ACT_TANH) x = tanhf(x);
-            else if (a.act == ACT_GELU) x = 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
-            if (a.keep) x = kk[i] ? x * a.drop_scale : 0.f;
-            if (a.residual) x += rr[i];
-            if (a.out_scale != 0.f) x *= a.out_scale;
-            if (a.accum) x += aa[i];
-            v[i] = x;
-          }
-          if (a.out_c0 && n == 0) a.out_c0[pos] = v[0];
-          if (a.out_f32) {
-            float4* dst = reinterpret_cast<float4*>(a.out_f32 + pos * a.Cout + n);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-          }
-          if (a.out_b16) {
-            __align__(16) __nv_bfloat16 hi[16], lo[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) tc::split_bf16((a.b16_slope != 0.f && v[i] < 0.f) ? v[i] * a.b16_slope : v[i], hi[i], lo[i]);
-            uint4* dh = reinterpret_cast<uint4*>(a.out_b16 + pos * a.Cout + n);
-            uint4* dl = reinterpret_cast<uint4*>(a.out_b16 + plane + pos * a.Cout + n);
-            dh[0] = reinterpret_cast<const uint4*>(hi)[0]; dh[1] = reinterpret_cast<const uint4*>(hi)[1];
-            dl[0] = reinterpret_cast<const uint4*>(lo)[0]; dl[1] = reinterpret_cast<const uint4*>(lo)[1];
-          }
-        }
+        if (valid) ct_finish_chunk(a, v, cur, pos, n0 + c * 16, plane, tab);
         cur = nxt;
+      }
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(acc_empty + buf);   // this warp has read its lanes of the accumulator
+      if (!got) break;
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tc::tmem_dealloc<CT_TMEM_COLS>(tmem);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------------------
+// Narrow layers (HiFi-GAN stages of 64 / 32 channels, conv_post).  conv_tc_kernel fetches the [128 positions x 64 channels] activation
+// tile once per TAP: k = 11 reads every position eleven times from L2, and at 32-64 channels that stream -- not the tensor pipe, not HBM
+// -- is what the layer costs (0.37 us per K-block on every SM).  Here a CTA loads 256 positions plus the halo ((k-1)*dil <= 64 rows) ONCE
+// into a K-major SWIZZLE_128B buffer of 320 rows and tap j multiplies the view that starts j*dil rows further down: the shared-memory
+// descriptor's start address moves by whole 128-byte rows, the swizzle is a function of the address bits, so the shifted view is
+// read exactly as TMA wrote it.  Weights (one [NT x 64] tile per tap) stream through a small ring and serve both 128-position halves.
+#define CH_ROWS 320
+#define CH_PLANE (CH_ROWS * 128)          // one plane (hi or lo) of the haloed tile
+#define CH_ABUF (2 * CH_PLANE)
+#define CH_WSTAGE 16384                   // one tap's weights: hi | lo, NT <= 64 rows of 128 B
+#define CH_WSTAGES 3
+#define CH_G 2                            // 128-position sub-tiles per tile
+
+__global__ void __launch_bounds__(CT_THREADS, 1) conv_halo_kernel(const __grid_constant__ ConvTcArgs a, int ntiles) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* base = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* wring = base + 2 * CH_ABUF;
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(wring + CH_WSTAGES * CH_WSTAGE);   // [2]
+  uint64_t* a_empty = a_full + 2;            // [2]
+  uint64_t* w_full = a_empty + 2;            // [CH_WSTAGES]
+  uint64_t* w_empty = w_full + CH_WSTAGES;
+  uint64_t* acc_full = w_empty + CH_WSTAGES; // [2]
+  uint64_t* acc_empty = acc_full + 2;        // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  volatile int* fail_s = reinterpret_cast<volatile int*>(tmem_slot + 1);
+  float* tab = reinterpret_cast<float*>(wring + CH_WSTAGES * CH_WSTAGE + 256);   // [2][Cout <= 64]
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tiles_t = (a.T + 128 * CH_G - 1) / (128 * CH_G);
+  ct_fill_tab(a, tab);
+  const int dil = a.dil > 1 ? a.dil : 1, pad = ((a.k - 1) >> 1) * dil;
+  const int planes = a.npass == 3 ? 2 : 1;
+  const uint32_t b_tile = (uint32_t)a.NT * 128u;
+
+  if (tid == 0) {
+    tc::prefetch_tmap(&a.in_map_h);
+    tc::prefetch_tmap(&a.in_map_t);
+    tc::prefetch_tmap(&a.w_map);
+    for (int i = 0; i < 2; ++i) { tc::mbar_init(a_full + i, 1); tc::mbar_init(a_empty + i, 1); tc::mbar_init(acc_full + i, 1); tc::mbar_init(acc_empty + i, 8); }
+    for (int i = 0; i < CH_WSTAGES; ++i) { tc::mbar_init(w_full + i, 1); tc::mbar_init(w_empty + i, 1); }
+    *fail_s = 0;
+    tc::fence_barrier_init();
+  }
+  if (warp == 1) tc::tmem_alloc<CT_TMEM_COLS>(tmem_slot);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      asm volatile("fence.proxy.async;" ::: "memory");
+      int ws = 0; uint32_t wph = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < ntiles && !*fail_s; tile += gridDim.x, ++it) {
+        const int b = tile / tiles_t, t0 = (tile - b * tiles_t) * 128 * CH_G;
+        const int ab = it & 1;
+        if (!tc::mbar_wait(a_empty + ab, (uint32_t)((it >> 1) & 1) ^ 1u)) { *fail_s = 1; break; }
+        uint8_t* ap = base + (size_t)ab * CH_ABUF;
+        tc::mbar_arrive_expect_tx(a_full + ab, (uint32_t)planes * (uint32_t)CH_PLANE);
+        for (int pl = 0; pl < planes; ++pl) {   // rows t0 - pad ... of the input; outside [0, T) TMA fills zeros = the conv padding
+          tc::tma_load_4d(ap + pl * CH_PLANE, &a.in_map_h, a_full + ab, 0, t0 - pad, b, pl);
+          tc::tma_load_4d(ap + pl * CH_PLANE + 16384, &a.in_map_h, a_full + ab, 0, t0 - pad + 128, b, pl);
+          tc::tma_load_4d(ap + pl * CH_PLANE + 32768, &a.in_map_t, a_full + ab, 0, t0 - pad + 256, b, pl);
+        }
+        for (int j = 0; j < a.k; ++j) {
+          if (!tc::mbar_wait(w_empty + ws, wph ^ 1)) { *fail_s = 1; break; }
+          tc::mbar_arrive_expect_tx(w_full + ws, (uint32_t)planes * b_tile);
+          tc::tma_load_4d(wring + (size_t)ws * CH_WSTAGE, &a.w_map, w_full + ws, 0, j, 0, 0);
+          if (++ws == CH_WSTAGES) { ws = 0; wph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int ws = 0; uint32_t wph = 0;
+      const uint32_t idesc = tc::idesc_bf16_f32(128, a.NT);
+      const int ksteps = (a.Cin + 15) >> 4;   // channels beyond Cin are zero fill: no MMA for them
+      int it = 0;
+      for (int tile = blockIdx.x; tile < ntiles && !*fail_s; tile += gridDim.x, ++it) {
+        const int buf = it & 1;
+        const uint32_t par = (uint32_t)((it >> 1) & 1);
+        if (!tc::mbar_wait(acc_empty + buf, par ^ 1u)) { *fail_s = 1; break; }   // the epilogue has drained this accumulator
+        if (!tc::mbar_wait(a_full + buf, par)) { *fail_s = 1; break; }
+        tc::tc_fence_after();
+        const uint32_t ab = tc::smem_u32(base + (size_t)buf * CH_ABUF);
+        for (int j = 0; j < a.k; ++j) {
+          if (!tc::mbar_wait(w_full + ws, wph)) { *fail_s = 1; break; }
+          tc::tc_fence_after();
+          const uint32_t wb = tc::smem_u32(wring + (size_t)ws * CH_WSTAGE);
+          const uint64_t bhi = tc::smem_desc_sw128(wb), blo = tc::smem_desc_sw128(wb + b_tile);
+#pragma unroll 1
+          for (int g = 0; g < CH_G; ++g) {
+            const uint32_t arow = ab + (uint32_t)(g * 128 + j * dil) * 128u;
+            const uint64_t ahi = tc::smem_desc_sw128(arow), alo = tc::smem_desc_sw128(arow + CH_PLANE);
+            const uint32_t dcol = tmem + (uint32_t)(buf * 128 + g * a.NT);
+            for (int k = 0; k < ksteps; ++k) {
+              const uint64_t adv = (uint64_t)(k * 2);
+              const uint32_t acc = (j || k) ? 1u : 0u;
+              if (a.npass == 3) {
+                tc::umma_bf16(dcol, alo + adv, bhi + adv, idesc, acc);
+                tc::umma_bf16(dcol, ahi + adv, blo + adv, idesc, 1u);
+                tc::umma_bf16(dcol, ahi + adv, bhi + adv, idesc, 1u);
+              } else {
+                tc::umma_bf16(dcol, ahi + adv, bhi + adv, idesc, acc);
+              }
+            }
+          }
+          tc::umma_commit(w_empty + ws);
+          if (++ws == CH_WSTAGES) { ws = 0; wph ^= 1; }
+        }
+        tc::umma_commit(acc_full + buf);
+        tc::umma_commit(a_empty + buf);
+      }
+    }
+  } else {
+    // ---- epilogue warps 2..9 (as in conv_tc_kernel): thread = output position of a 128-position sub-tile, items = (sub-tile, 16-channel
+    // chunk), the global reads of the next item requested before the current one is finished
+    const int q = warp & 3, grp = (warp - 2) >> 2, row = 32 * q + lane;
+    const long long plane = (long long)a.B * a.T * a.Cout;
+    const int nch = a.NT / 16;
+    const bool keep16 = (a.keep_ld & 15) == 0 && (reinterpret_cast<uintptr_t>(a.keep) & 15) == 0;
+    auto load_pre = [&](int tile, int g, int c, CtPre& p) {
+      const int b = tile / tiles_t, t = (tile - b * tiles_t) * 128 * CH_G + g * 128 + row;
+      ct_load_pre(a, b, t, c * 16, keep16, p);
+    };
+    // items of this warp in order: (tile, g, c), c = grp, grp + 2, ...; the reads of the next item are requested before the current one
+    // is finished (two ahead was no faster)
+    auto advance = [&](int& tile, int& g, int& c) {
+      c += 2;
+      if (c >= nch) { c = grp; if (++g == CH_G) { g = 0; tile += gridDim.x; } }
+    };
+    CtPre cur, nx1;
+    int ptile = blockIdx.x, pg = 0, pc = grp;   // the item whose reads are requested next
+    if (grp < nch) {
+      if (ptile < ntiles) load_pre(ptile, pg, pc, cur);
+      advance(ptile, pg, pc);
+    }
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const int buf = it & 1;
+      const int b = tile / tiles_t, t0 = (tile - b * tiles_t) * 128 * CH_G;
+      const bool got = tc::mbar_wait(acc_full + buf, (uint32_t)((it >> 1) & 1));
+      if (!got) *fail_s = 1;
+      tc::tc_fence_after();
+      const bool live = got && !*fail_s;
+#pragma unroll 1
+      for (int g = 0; g < CH_G; ++g) {
+        const int t = t0 + g * 128 + row;
+        const size_t pos = (size_t)b * a.T + min(t, a.T - 1);
+#pragma unroll 1
+        for (int c = grp; c < nch; c += 2) {
+          if (ptile < ntiles) load_pre(ptile, pg, pc, nx1);
+          advance(ptile, pg, pc);
+          float v[16];
+          tc::tmem_ld16(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * 128 + g * a.NT + c * 16), v);
+          tc::tmem_ld_wait();
+          if (live && t < a.T) ct_finish_chunk(a, v, cur, pos, c * 16, plane, tab);
+          cur = nx1;
+        }
       }
       tc::tc_fence_before();
       __syncwarp();
@@ -251,7 +459,7 @@ int convtc_launch(const ConvTcArgs& a, cudaStream_t st) {
   T2_REQUIRE(a.NT % 16 == 0 && a.NT >= 16 && a.NT <= 128 && a.Cout % a.NT == 0 && (a.k & 1) && a.Cin % 8 == 0 && a.Cout % 8 == 0,
              T2_ERR_UNSUPPORTED, "convtc: unsupported shape Cin=%d Cout=%d k=%d NT=%d", a.Cin, a.Cout, a.k, a.NT);
   if (a.B * a.T == 0) return T2_OK;
-  const size_t smem = 1024 + (size_t)CT_STAGES * CT_STAGE_BYTES + 128;
+  const size_t smem = 1024 + (size_t)CT_STAGES * CT_STAGE_BYTES + 128 + 2 * CT_TAB_MAX * sizeof(float);
   static bool attr_set = false;
   static int num_sms = 0;
   if (!attr_set) {
@@ -261,10 +469,39 @@ int convtc_launch(const ConvTcArgs& a, cudaStream_t st) {
     T2_CHECK_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
     attr_set = true;
   }
+  if (a.halo) {
+    T2_REQUIRE(convtc_halo_ok(a.Cin, a.Cout, a.NT, a.k, a.dil), T2_ERR_ARG, "convtc: layer does not qualify for the halo kernel");
+    const size_t hsmem = 1024 + 2 * (size_t)CH_ABUF + (size_t)CH_WSTAGES * CH_WSTAGE + 256 + 2 * 64 * sizeof(float);
+    static bool hattr_set = false;
+    if (!hattr_set) {
+      T2_CHECK_CUDA(cudaFuncSetAttribute(conv_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsmem));
+      hattr_set = true;
+    }
+    const int htiles = a.B * ((a.T + 128 * CH_G - 1) / (128 * CH_G));
+    conv_halo_kernel<<<std::min(htiles, num_sms), CT_THREADS, hsmem, st>>>(a, htiles);
+    T2_CHECK_CUDA(cudaGetLastError());
+    return T2_OK;
+  }
   const int ntiles = a.B * ((a.T + 127) / 128) * (a.Cout / a.NT);
   conv_tc_kernel<<<std::min(ntiles, num_sms), CT_THREADS, smem, st>>>(a, ntiles);
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
+}
+
+bool convtc_halo_ok(int Cin, int Cout, int NT, int k, int dil) {
+  const char* e = getenv("T2B200_CONV_HALO");
+  if (e && e[0] == '0') return false;
+  const int d = dil > 1 ? dil : 1;
+  return Cin <= 64 && Cin % 8 == 0 && Cout == NT && NT <= 64 && NT % 16 == 0 && (k & 1) && k >= 3 && (k - 1) * d <= CH_ROWS - 128 * CH_G;
+}
+
+int convtc_make_halo_maps(ConvTcArgs& a, const __nv_bfloat16* x, int B, int T, int Cin) {
+  unsigned long long dims[4] = {(unsigned long long)Cin, (unsigned long long)T, (unsigned long long)B, 2ull};
+  unsigned long long st[3] = {(unsigned long long)Cin * 2, (unsigned long long)T * Cin * 2, (unsigned long long)B * T * Cin * 2};
+  unsigned boxh[4] = {64u, 128u, 1u, 1u}, boxt[4] = {64u, 64u, 1u, 1u};
+  const int rc = tc_make_tmap_bf16(&a.in_map_h, x, 4, dims, st, boxh);
+  if (rc != T2_OK) return rc;
+  return tc_make_tmap_bf16(&a.in_map_t, x, 4, dims, st, boxt);
 }
 
 int split_cl_launch(const float* src, long long src_bstride, __nv_bfloat16* dst, int B, int T, int C, cudaStream_t st) {

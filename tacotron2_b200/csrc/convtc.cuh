@@ -29,7 +29,16 @@ struct ConvTcArgs {
   const float* accum;         // ... and this [B][T][Cout] tensor is added (may alias out_f32): multi-receptive-field sum
   float b16_slope;            // != 0: the bf16 (hi,lo) copy holds leaky_relu(value, slope) -- the next conv's input -- out_f32 the value
   float* out_c0;              // optional [B][T]: channel 0 only (conv_post: one real output channel in a 16-wide tile)
+  // --- narrow layers (Cin <= 64, Cout == NT <= 64, k >= 3): conv_halo_kernel loads each 256-position activation tile ONCE with its halo
+  // and gives every tap a shifted view of it, instead of reloading the tile per tap.  halo = 1 asks for it; the two extra maps are
+  // single-plane views of the input (convtc_make_halo_maps): box {64, 128, 1, 1} and {64, 64, 1, 1}.
+  int halo;
+  CUtensorMap in_map_h, in_map_t;
 };
+
+// Whether the layer qualifies for conv_halo_kernel (T2B200_CONV_HALO=0 disables it), and the two maps it needs.
+bool convtc_halo_ok(int Cin, int Cout, int NT, int k, int dil);
+int convtc_make_halo_maps(ConvTcArgs& a, const __nv_bfloat16* x, int B, int T, int Cin);
 
 int convtc_launch(const ConvTcArgs& a, cudaStream_t st);
 // fp32 [B][T(stride)][C] -> bf16 (hi,lo) [2][B][T][C]

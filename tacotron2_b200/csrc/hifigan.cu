@@ -254,6 +254,10 @@ static int hconv(const t2_hifigan* g, const HConv& h, const __nv_bfloat16* in, i
   a.scale = nullptr; a.shift = h.bias; a.keep = nullptr; a.keep_ld = 0; a.drop_scale = 1.f;
   a.out_f32 = out_f32; a.out_b16 = out_b16; a.residual = residual; a.res_bstride = (long long)T * h.Cout;
   a.dil = h.dil; a.chan_mod = h.chan_mod; a.out_scale = out_scale; a.accum = accum; a.b16_slope = b16_slope; a.out_c0 = out_c0;
+  if (convtc_halo_ok(h.Cin, h.Cout, h.NT, h.k, h.dil)) {
+    a.halo = 1;
+    RC(convtc_make_halo_maps(a, in, B, T, h.Cin));
+  }
   return convtc_launch(a, st);
 }
 
