@@ -66,25 +66,48 @@ __device__ __forceinline__ void ct_finish_chunk(const ConvTcArgs& a, float (&v)[
       if (a.scale) *reinterpret_cast<float4*>(sc + 4 * i) = *reinterpret_cast<const float4*>(tab + a.Cout + n + 4 * i);
     }
   }
+  // every option is tested once per chunk, not once per element: the executed path is short straight-line code (with the tests inside
+  // the element loop the narrow layers spent a third of their stall samples on instruction fetch and branch resolution)
+  if (tab) {
+    if (a.scale) {
 #pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    float x = v[i];
-    if (tab) {
-      if (a.scale) x = fmaf(x, sc[i], sh[i]);
-      else if (a.shift) x += sh[i];
-    } else {
-      const int ci = a.chan_mod > 0 ? (n + i) % a.chan_mod : n + i;
-      if (a.scale) x = fmaf(x, __ldg(a.scale + ci), __ldg(a.shift + ci));
-      else if (a.shift) x += __ldg(a.shift + ci);
+      for (int i = 0; i < 16; ++i) v[i] = fmaf(v[i], sc[i], sh[i]);
+    } else if (a.shift) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] += sh[i];
     }
-    if (a.act == ACT_RELU) x = fmaxf(x, 0.f);
-    else if (a.act == ACT_TANH) x = tanhf(x);
-    else if (a.act == ACT_GELU) x = 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
-    if (a.keep) x = kk[i] ? x * a.drop_scale : 0.f;
-    if (a.residual) x += rr[i];
-    if (a.out_scale != 0.f) x *= a.out_scale;
-    if (a.accum) x += aa[i];
-    v[i] = x;
+  } else if (a.shift) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int ci = a.chan_mod > 0 ? (n + i) % a.chan_mod : n + i;
+      v[i] = a.scale ? fmaf(v[i], __ldg(a.scale + ci), __ldg(a.shift + ci)) : v[i] + __ldg(a.shift + ci);
+    }
+  }
+  if (a.act == ACT_RELU) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);
+  } else if (a.act == ACT_TANH) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = tanhf(v[i]);
+  } else if (a.act == ACT_GELU) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = 0.5f * v[i] * (1.0f + erff(v[i] * 0.70710678118654752f));
+  }
+  if (a.keep) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = kk[i] ? v[i] * a.drop_scale : 0.f;
+  }
+  if (a.residual) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] += rr[i];
+  }
+  if (a.out_scale != 0.f) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] *= a.out_scale;
+  }
+  if (a.accum) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] += aa[i];
   }
   if (a.out_c0 && n == 0) a.out_c0[pos] = v[0];
   if (a.out_f32) {
