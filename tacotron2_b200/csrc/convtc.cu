@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   volatile int* fail_s = reinterpret_cast<volatile int*>(tmem_slot + 1);
   float* tab = a.Cout <= CT_TAB_MAX ? reinterpret_cast<float*>(base + CT_STAGES * CT_STAGE_BYTES + 128) : nullptr;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int tiles_t = (a.T + 127) >> 7, tiles_bt = a.B * tiles_t;
+  const int tiles_t = (a.T + 127) >> 7;
   if (tab) ct_fill_tab(a, tab);
   const int dil = a.dil > 1 ? a.dil : 1;
   const int cblocks = (a.Cin + 63) >> 6, nkb = a.k * cblocks, pad = ((a.k - 1) >> 1) * dil;
@@ -277,8 +277,13 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
 #define CH_WSTAGE 16384                   // one tap's weights: hi | lo, NT <= 64 rows of 128 B
 #define CH_WSTAGES 3
 #define CH_G 2                            // 128-position sub-tiles per tile
+#ifndef CH_NG
+#define CH_NG 2                           // epilogue warp groups (4 warps each: one per tensor-memory lane quarter); 3 and 4 measured slower
+                                          // (20.3 / 21.7 ms against 19.2 for the HiFi-GAN generator: 128 / 96 registers per thread spill)
+#endif
+#define CH_THREADS (64 + CH_NG * 128)
 
-__global__ void __launch_bounds__(CT_THREADS, 1) conv_halo_kernel(const __grid_constant__ ConvTcArgs a, int ntiles) {
+__global__ void __launch_bounds__(CH_THREADS, 1) conv_halo_kernel(const __grid_constant__ ConvTcArgs a, int ntiles) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* base = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* wring = base + 2 * CH_ABUF;
@@ -302,7 +307,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_halo_kernel(const __grid_c
     tc::prefetch_tmap(&a.in_map_h);
     tc::prefetch_tmap(&a.in_map_t);
     tc::prefetch_tmap(&a.w_map);
-    for (int i = 0; i < 2; ++i) { tc::mbar_init(a_full + i, 1); tc::mbar_init(a_empty + i, 1); tc::mbar_init(acc_full + i, 1); tc::mbar_init(acc_empty + i, 8); }
+    for (int i = 0; i < 2; ++i) { tc::mbar_init(a_full + i, 1); tc::mbar_init(a_empty + i, 1); tc::mbar_init(acc_full + i, 1); tc::mbar_init(acc_empty + i, 4 * CH_NG); }
     for (int i = 0; i < CH_WSTAGES; ++i) { tc::mbar_init(w_full + i, 1); tc::mbar_init(w_empty + i, 1); }
     *fail_s = 0;
     tc::fence_barrier_init();
@@ -380,27 +385,28 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_halo_kernel(const __grid_c
       }
     }
   } else {
-    // ---- epilogue warps 2..9 (as in conv_tc_kernel): thread = output position of a 128-position sub-tile, items = (sub-tile, 16-channel
-    // chunk), the global reads of the next item requested before the current one is finished
+    // ---- epilogue warps 2.. : CH_NG groups of four warps (thread = output position of a 128-position sub-tile, tensor-memory lane quarter
+    // = warp % 4).  The items of a tile -- (sub-tile g, 16-channel chunk c), e = g * nch + c -- go round-robin to the groups; the global
+    // reads of a warp's next item are requested before its current one is finished.  The epilogue, not the tensor pipe, bounds these
+    // layers (8 bytes of output and ~20 instructions per element).
     const int q = warp & 3, grp = (warp - 2) >> 2, row = 32 * q + lane;
     const long long plane = (long long)a.B * a.T * a.Cout;
-    const int nch = a.NT / 16;
+    const int nch = a.NT / 16, nitem = CH_G * nch;
     const bool keep16 = (a.keep_ld & 15) == 0 && (reinterpret_cast<uintptr_t>(a.keep) & 15) == 0;
-    auto load_pre = [&](int tile, int g, int c, CtPre& p) {
+    auto load_pre = [&](int tile, int e, CtPre& p) {
+      const int g = e / nch, c = e - g * nch;
       const int b = tile / tiles_t, t = (tile - b * tiles_t) * 128 * CH_G + g * 128 + row;
       ct_load_pre(a, b, t, c * 16, keep16, p);
     };
-    // items of this warp in order: (tile, g, c), c = grp, grp + 2, ...; the reads of the next item are requested before the current one
-    // is finished (two ahead was no faster)
-    auto advance = [&](int& tile, int& g, int& c) {
-      c += 2;
-      if (c >= nch) { c = grp; if (++g == CH_G) { g = 0; tile += gridDim.x; } }
-    };
     CtPre cur, nx1;
-    int ptile = blockIdx.x, pg = 0, pc = grp;   // the item whose reads are requested next
-    if (grp < nch) {
-      if (ptile < ntiles) load_pre(ptile, pg, pc, cur);
-      advance(ptile, pg, pc);
+    int ptile = blockIdx.x, pe = grp;   // the item whose reads are requested next
+    auto advance = [&]() {
+      pe += CH_NG;
+      if (pe >= nitem) { pe = grp; ptile += gridDim.x; }
+    };
+    if (grp < nitem) {
+      if (ptile < ntiles) load_pre(ptile, pe, cur);
+      advance();
     }
     int it = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
@@ -411,23 +417,21 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_halo_kernel(const __grid_c
       tc::tc_fence_after();
       const bool live = got && !*fail_s;
 #pragma unroll 1
-      for (int g = 0; g < CH_G; ++g) {
+      for (int e = grp; e < nitem; e += CH_NG) {
+        const int g = e / nch, c = e - g * nch;
         const int t = t0 + g * 128 + row;
         const size_t pos = (size_t)b * a.T + min(t, a.T - 1);
-#pragma unroll 1
-        for (int c = grp; c < nch; c += 2) {
-          if (ptile < ntiles) load_pre(ptile, pg, pc, nx1);
-          advance(ptile, pg, pc);
-          float v[16];
-          tc::tmem_ld16(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * 128 + g * a.NT + c * 16), v);
-          tc::tmem_ld_wait();
-          if (live && t < a.T) ct_finish_chunk(a, v, cur, pos, c * 16, plane, tab);
-          cur = nx1;
-        }
+        if (ptile < ntiles) load_pre(ptile, pe, nx1);
+        advance();
+        float v[16];
+        tc::tmem_ld16(tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * 128 + g * a.NT + c * 16), v);
+        tc::tmem_ld_wait();
+        if (live && t < a.T) ct_finish_chunk(a, v, cur, pos, c * 16, plane, tab);
+        cur = nx1;
       }
       tc::tc_fence_before();
       __syncwarp();
-      if (lane == 0) tc::mbar_arrive(acc_empty + buf);   // this warp has read its lanes of the accumulator
+      if (lane == 0) tc::mbar_arrive(acc_empty + buf);   // this warp has read its lanes of the accumulators
       if (!got) break;
     }
   }
@@ -501,7 +505,7 @@ int convtc_launch(const ConvTcArgs& a, cudaStream_t st) {
       hattr_set = true;
     }
     const int htiles = a.B * ((a.T + 128 * CH_G - 1) / (128 * CH_G));
-    conv_halo_kernel<<<std::min(htiles, num_sms), CT_THREADS, hsmem, st>>>(a, htiles);
+    conv_halo_kernel<<<std::min(htiles, num_sms), CH_THREADS, hsmem, st>>>(a, htiles);
     T2_CHECK_CUDA(cudaGetLastError());
     return T2_OK;
   }
