@@ -140,6 +140,126 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(BnLayer L, const floa
   }
 }
 
+// ---- four channels per thread (C % 4 == 0, 16-byte aligned tensors): 16-byte loads and stores, one row / channel split per four
+// elements instead of a 64-bit division per element.  Same arithmetic and the same summation order as the scalar kernels above.
+struct Bn4 { float4 mean, rstd, gamma, beta; };
+__device__ __forceinline__ Bn4 bn4_params(const BnLayer& L, int c) {
+  Bn4 p;
+  p.mean = __ldg(reinterpret_cast<const float4*>(L.mean + c)); p.rstd = __ldg(reinterpret_cast<const float4*>(L.rstd + c));
+  p.gamma = __ldg(reinterpret_cast<const float4*>(L.gamma + c)); p.beta = __ldg(reinterpret_cast<const float4*>(L.beta + c));
+  return p;
+}
+__device__ __forceinline__ void bn4_keep(const BnLayer& L, long long r, int c, bool (&k)[4]) {
+  if (L.keep) {
+    const uchar4 m = *reinterpret_cast<const uchar4*>(L.keep + r * L.keep_ld + c);
+    k[0] = m.x != 0; k[1] = m.y != 0; k[2] = m.z != 0; k[3] = m.w != 0;
+  } else {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) k[e] = rng_keep(L.seed, L.rng_base + (unsigned long long)(r * L.keep_ld + c + e), L.p);
+  }
+}
+__device__ __forceinline__ void st_split4(__nv_bfloat16* hi_p, __nv_bfloat16* lo_p, const float (&v)[4]) {
+  __align__(8) __nv_bfloat16 hi[4], lo[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) tc::split_bf16(v[e], hi[e], lo[e]);
+  *reinterpret_cast<uint2*>(hi_p) = *reinterpret_cast<const uint2*>(hi);
+  *reinterpret_cast<uint2*>(lo_p) = *reinterpret_cast<const uint2*>(lo);
+}
+
+__global__ void __launch_bounds__(256) bn_apply4_kernel(BnLayer L, long long rows, float* __restrict__ out_f32, __nv_bfloat16* __restrict__ out_b16) {
+  const int C4 = L.C >> 2;
+  const long long n4 = rows * C4, n = rows * L.C;
+  const float dscale = 1.0f / (1.0f - L.p);
+  for (long long i4 = blockIdx.x * (long long)blockDim.x + threadIdx.x; i4 < n4; i4 += (long long)gridDim.x * blockDim.x) {
+    const long long r = i4 / C4;
+    const int c = (int)(i4 - r * C4) * 4;
+    const Bn4 p = bn4_params(L, c);
+    const float4 z = *reinterpret_cast<const float4*>(L.z + i4 * 4);
+    float y[4] = {act_fwd((z.x - p.mean.x) * p.rstd.x * p.gamma.x + p.beta.x, L.act), act_fwd((z.y - p.mean.y) * p.rstd.y * p.gamma.y + p.beta.y, L.act),
+                  act_fwd((z.z - p.mean.z) * p.rstd.z * p.gamma.z + p.beta.z, L.act), act_fwd((z.w - p.mean.w) * p.rstd.w * p.gamma.w + p.beta.w, L.act)};
+    if (L.dropout) {
+      bool k[4];
+      bn4_keep(L, r, c, k);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) y[e] = k[e] ? y[e] * dscale : 0.f;
+    }
+    if (out_f32) *reinterpret_cast<float4*>(out_f32 + i4 * 4) = make_float4(y[0], y[1], y[2], y[3]);
+    if (out_b16) st_split4(out_b16 + i4 * 4, out_b16 + n + i4 * 4, y);
+  }
+}
+
+// d_a of four channels of one row (bn_da), zhat alongside
+__device__ __forceinline__ void bn_da4(const BnLayer& L, const float* __restrict__ dy, long long r, int c, float (&d)[4], float (&zh)[4]) {
+  const Bn4 p = bn4_params(L, c);
+  const long long i = r * L.C + c;
+  const float4 z = *reinterpret_cast<const float4*>(L.z + i), g = *reinterpret_cast<const float4*>(dy + i);
+  zh[0] = (z.x - p.mean.x) * p.rstd.x; zh[1] = (z.y - p.mean.y) * p.rstd.y; zh[2] = (z.z - p.mean.z) * p.rstd.z; zh[3] = (z.w - p.mean.w) * p.rstd.w;
+  const float a[4] = {zh[0] * p.gamma.x + p.beta.x, zh[1] * p.gamma.y + p.beta.y, zh[2] * p.gamma.z + p.beta.z, zh[3] * p.gamma.w + p.beta.w};
+  d[0] = g.x; d[1] = g.y; d[2] = g.z; d[3] = g.w;
+  if (L.dropout) {
+    bool k[4];
+    bn4_keep(L, r, c, k);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) d[e] = k[e] ? d[e] * (1.0f / (1.0f - L.p)) : 0.f;
+  }
+  if (L.act == ACT_RELU) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) d[e] = a[e] > 0.f ? d[e] : 0.f;
+  } else if (L.act == ACT_TANH) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) { const float t = tanhf(a[e]); d[e] *= 1.f - t * t; }
+  }
+}
+
+__global__ void __launch_bounds__(256) bn_bwd_partial4_kernel(BnLayer L, const float* __restrict__ dy, long long rows, double2* __restrict__ partial) {
+  __shared__ double2 red[8][4][33];
+  const int C = L.C;
+  const int c = blockIdx.x * 128 + threadIdx.x * 4;
+  double s[4] = {0.0, 0.0, 0.0, 0.0}, q[4] = {0.0, 0.0, 0.0, 0.0};
+  if (c < C)
+    for (long long r = blockIdx.y * 8 + threadIdx.y; r < rows; r += (long long)gridDim.y * 8) {
+      float d[4], zh[4];
+      bn_da4(L, dy, r, c, d, zh);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { s[e] += (double)d[e]; q[e] += (double)d[e] * (double)zh[e]; }
+    }
+#pragma unroll
+  for (int e = 0; e < 4; ++e) red[threadIdx.y][e][threadIdx.x] = make_double2(s[e], q[e]);
+  __syncthreads();
+  if (threadIdx.y == 0 && c < C) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      for (int i = 1; i < 8; ++i) { s[e] += red[i][e][threadIdx.x].x; q[e] += red[i][e][threadIdx.x].y; }
+      partial[(size_t)blockIdx.y * C + c + e] = make_double2(s[e], q[e]);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) bn_bwd_apply4_kernel(BnLayer L, const float* __restrict__ dy, long long rows, const float* __restrict__ s1n,
+                                                            const float* __restrict__ s2n, __nv_bfloat16* __restrict__ dz_b16,
+                                                            float* __restrict__ dz_f32) {
+  const int C4 = L.C >> 2;
+  const long long n4 = rows * C4, n = rows * L.C;
+  for (long long i4 = blockIdx.x * (long long)blockDim.x + threadIdx.x; i4 < n4; i4 += (long long)gridDim.x * blockDim.x) {
+    const long long r = i4 / C4;
+    const int c = (int)(i4 - r * C4) * 4;
+    float d[4], zh[4];
+    bn_da4(L, dy, r, c, d, zh);
+    const float4 ga = __ldg(reinterpret_cast<const float4*>(L.gamma + c)), rs = __ldg(reinterpret_cast<const float4*>(L.rstd + c));
+    const float4 m1 = __ldg(reinterpret_cast<const float4*>(s1n + c)), m2 = __ldg(reinterpret_cast<const float4*>(s2n + c));
+    const float dz[4] = {ga.x * rs.x * (d[0] - m1.x - zh[0] * m2.x), ga.y * rs.y * (d[1] - m1.y - zh[1] * m2.y),
+                         ga.z * rs.z * (d[2] - m1.z - zh[2] * m2.z), ga.w * rs.w * (d[3] - m1.w - zh[3] * m2.w)};
+    if (dz_f32) *reinterpret_cast<float4*>(dz_f32 + i4 * 4) = make_float4(dz[0], dz[1], dz[2], dz[3]);
+    if (dz_b16) st_split4(dz_b16 + i4 * 4, dz_b16 + n + i4 * 4, dz);
+  }
+}
+
+__host__ inline bool bn_vec4(const BnLayer& L, const void* a, const void* b, const void* c2) {
+  auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  return L.C % 4 == 0 && al(L.z) && al(L.mean) && al(L.rstd) && al(L.gamma) && al(L.beta) && al(a) && al(b) && al(c2) &&
+         (!L.keep || ((L.keep_ld & 3) == 0 && (reinterpret_cast<uintptr_t>(L.keep) & 3) == 0)) && (L.keep_ld & 3) == 0 && !getenv("T2B200_BN_SCALAR");
+}
+
 inline int gs(long long n) { long long g = (n + 255) / 256; return (int)(g < 1 ? 1 : (g > 148 * 16 ? 148 * 16 : g)); }
 
 }  // namespace
@@ -157,7 +277,8 @@ int bn_stats_launch(const float* z, long long rows, int C, float* mean, float* r
 }
 
 int bn_apply_launch(const BnLayer& L, long long rows, float* out_f32, __nv_bfloat16* out_b16, cudaStream_t st) {
-  bn_apply_kernel<<<gs(rows * L.C), 256, 0, st>>>(L, rows, out_f32, out_b16);
+  if (bn_vec4(L, out_f32, out_b16, nullptr)) bn_apply4_kernel<<<gs(rows * L.C / 4), 256, 0, st>>>(L, rows, out_f32, out_b16);
+  else bn_apply_kernel<<<gs(rows * L.C), 256, 0, st>>>(L, rows, out_f32, out_b16);
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }
@@ -168,9 +289,12 @@ int bn_bwd_launch(const BnLayer& L, const float* dy, long long rows, float* dgam
   float* s1n = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + (size_t)BN_NS * L.C * sizeof(double2));
   float* s2n = s1n + L.C;
   dim3 grid((L.C + 31) / 32, BN_NS), block(32, 8);
-  bn_bwd_partial_kernel<<<grid, block, 0, st>>>(L, dy, rows, partial);
+  const bool v4 = bn_vec4(L, dy, dz_b16, dz_f32);
+  if (v4) bn_bwd_partial4_kernel<<<dim3((L.C + 127) / 128, BN_NS), block, 0, st>>>(L, dy, rows, partial);
+  else bn_bwd_partial_kernel<<<grid, block, 0, st>>>(L, dy, rows, partial);
   bn_bwd_final_kernel<<<(L.C + 127) / 128, 128, 0, st>>>(partial, BN_NS, rows, L.C, s1n, s2n, dgamma, dbeta);
-  bn_bwd_apply_kernel<<<gs(rows * L.C), 256, 0, st>>>(L, dy, rows, s1n, s2n, dz_b16, dz_f32);
+  if (v4) bn_bwd_apply4_kernel<<<gs(rows * L.C / 4), 256, 0, st>>>(L, dy, rows, s1n, s2n, dz_b16, dz_f32);
+  else bn_bwd_apply_kernel<<<gs(rows * L.C), 256, 0, st>>>(L, dy, rows, s1n, s2n, dz_b16, dz_f32);
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }
