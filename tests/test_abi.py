@@ -83,3 +83,18 @@ def test_reference_asserts():
         v(x, n, False, controls=torch.zeros(1, 5), max_len_override=2)
     with pytest.raises(Exception, match="max_len_override is required"):
         v(x, n, False)
+
+
+def test_environment_switches_are_documented():
+    """Every T2B200_* variable the library or the host side reads is listed in INTEGRATION.md (each one selects between two CUDA
+    implementations: none of them may appear undocumented, and none may route to a CPU path)."""
+    names = set()
+    for d in (os.path.join(ROOT, "tacotron2_b200", "csrc"), os.path.join(ROOT, "tacotron2_b200")):
+        for f in os.listdir(d):
+            if f.endswith((".cu", ".cuh", ".inl", ".py")):
+                names |= set(re.findall(r"getenv\(\"(T2B200_[A-Z0-9_]+)\"\)|environ(?:\.get)?[\(\[]\"(T2B200_[A-Z0-9_]+)\"", open(os.path.join(d, f)).read()))
+    names = {a or b for a, b in names}
+    assert names, "no switches found: the scan is broken"
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    missing = sorted(n for n in names if n not in doc)
+    assert not missing, missing
