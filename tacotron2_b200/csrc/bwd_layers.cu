@@ -638,6 +638,44 @@ __global__ void __launch_bounds__(256) speaker_grad_kernel(const float* __restri
     out[(size_t)s * E + c] = t;
   }
 }
+// The same in two steps when a scratch of B * E floats is at hand (E % 4 == 0): per-utterance column sums on B x ceil(E / 128) CTAs
+// (warp w adds the rows l = w, w + 8, ..., lanes hold four columns: 512-byte coalesced rows, eight rows in flight per warp), then one thread
+// per (speaker, column) adds its utterances in index order.  64 CTAs of the form above read 19.7 MB in 0.22 ms at C3.
+__global__ void __launch_bounds__(256) utt_colsum_kernel(const float* __restrict__ d_enc, int L, int E, float* __restrict__ usum) {
+  __shared__ float4 red[8][32];
+  const int b = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, c = blockIdx.y * 128 + lane * 4;
+  float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+  if (c < E) {
+    const float* p = d_enc + (size_t)b * L * E + c;
+    int l = warp;
+    for (; l + 8 < L; l += 16) {
+      const float4 v0 = *reinterpret_cast<const float4*>(p + (size_t)l * E), v1 = *reinterpret_cast<const float4*>(p + (size_t)(l + 8) * E);
+      a0.x += v0.x; a0.y += v0.y; a0.z += v0.z; a0.w += v0.w;
+      a1.x += v1.x; a1.y += v1.y; a1.z += v1.z; a1.w += v1.w;
+    }
+    if (l < L) {
+      const float4 v0 = *reinterpret_cast<const float4*>(p + (size_t)l * E);
+      a0.x += v0.x; a0.y += v0.y; a0.z += v0.z; a0.w += v0.w;
+    }
+  }
+  red[warp][lane] = make_float4(a0.x + a1.x, a0.y + a1.y, a0.z + a1.z, a0.w + a1.w);
+  __syncthreads();
+  if (warp == 0 && c < E) {
+    float4 t = red[0][lane];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) { const float4 v = red[w][lane]; t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w; }
+    *reinterpret_cast<float4*>(usum + (size_t)b * E + c) = t;
+  }
+}
+__global__ void speaker_sum_kernel(const float* __restrict__ usum, const long long* __restrict__ spk, int B, int E, int nspk, float* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nspk * E) return;
+  const int s = i / E, c = i - s * E;
+  float t = 0.f;
+  for (int b = 0; b < B; ++b)
+    if (spk[b] == s) t += usum[(size_t)b * E + c];
+  out[i] = t;
+}
 // description path: dpre[b][j] = (sum_l dmem[b][l][E+j]) * (1 - dvec^2), dvec = memory[b][0][E+j]
 __global__ void desc_dpre_kernel(const float* __restrict__ dmem, const float* __restrict__ mem, int B, int L, int E, int D, float* __restrict__ dpre) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -664,35 +702,40 @@ __global__ void desc_wgrad_kernel(const float* __restrict__ dpre, const float* _
   }
 }
 // d embedding[row][c] = sum over positions with chars == row (row 0 = padding_idx gets no gradient, model/encoder.py:25)
-// One CTA per table row: warp w scans the positions p = w, w + 8, ... (the index load is a broadcast), lanes own columns lane + 32 j;
-// the eight warp sums are added in warp order (deterministic).  The one-thread-scans-everything form took 0.7 ms at C3.
-#define EG_MAXJ 32   // E <= 1024
+// grid (table rows, ceil(E / 128)): warp w looks at 32 positions at a time (one coalesced index load, a ballot of the matches) and adds the
+// matching rows' 128-column slice, lanes own columns lane + 32 j; the eight warp sums are added in warp order (deterministic).  The form
+// that tested one position per iteration paid the index load's latency 1200 times per warp (0.34 ms at C3), one CTA per table row.
+#define EG_COLS 128
 __global__ void __launch_bounds__(256) embedding_grad_kernel(const float* __restrict__ dx, const long long* __restrict__ chars, long long npos,
                                                              int E, int nrows, float* __restrict__ out) {
-  extern __shared__ float eg_red[];   // [8][E]
-  const int row = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int nj = (E + 31) / 32;
-  float acc[EG_MAXJ];
+  __shared__ float eg_red[8][EG_COLS];
+  const int row = blockIdx.x, c0 = blockIdx.y * EG_COLS, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float acc[EG_COLS / 32];
 #pragma unroll
-  for (int j = 0; j < EG_MAXJ; ++j) acc[j] = 0.f;
+  for (int j = 0; j < EG_COLS / 32; ++j) acc[j] = 0.f;
   if (row > 0) {
-    for (long long p = warp; p < npos; p += 8) {
-      if (chars[p] != row) continue;
-      const float* src = dx + p * E + lane;
+    for (long long base = (long long)warp * 32; base < npos; base += 8 * 32) {
+      const long long p = base + lane;
+      const bool hit = p < npos && chars[p] == row;
+      unsigned m = __ballot_sync(0xffffffffu, hit);
+      while (m) {
+        const int bit = __ffs(m) - 1;
+        m &= m - 1;
+        const float* src = dx + (base + bit) * E + c0 + lane;
 #pragma unroll
-      for (int j = 0; j < EG_MAXJ; ++j)
-        if (j < nj && lane + 32 * j < E) acc[j] += src[32 * j];
+        for (int j = 0; j < EG_COLS / 32; ++j)
+          if (c0 + lane + 32 * j < E) acc[j] += src[32 * j];
+      }
     }
   }
 #pragma unroll
-  for (int j = 0; j < EG_MAXJ; ++j)
-    if (j < nj && lane + 32 * j < E) eg_red[warp * E + lane + 32 * j] = acc[j];
+  for (int j = 0; j < EG_COLS / 32; ++j) eg_red[warp][lane + 32 * j] = acc[j];
   __syncthreads();
-  for (int c = threadIdx.x; c < E; c += blockDim.x) {
-    float t = eg_red[c];
+  for (int c = threadIdx.x; c < EG_COLS && c0 + c < E; c += blockDim.x) {
+    float t = eg_red[0][c];
 #pragma unroll
-    for (int w = 1; w < 8; ++w) t += eg_red[w * E + c];
-    out[(size_t)row * E + c] = t;
+    for (int w = 1; w < 8; ++w) t += eg_red[w][c];
+    out[(size_t)row * E + c0 + c] = t;
   }
 }
 __global__ void zero_kernel(float* p, long long n) {
@@ -706,8 +749,13 @@ int condition_bwd_launch(const float* dmem, const float* mem, int speaker, float
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }
-int speaker_grad_launch(const float* d_enc, const long long* spk, int B, int L, int E, int nspk, float* out, cudaStream_t st) {
-  speaker_grad_kernel<<<dim3((unsigned)nspk, (unsigned)((E + 31) / 32)), 256, 0, st>>>(d_enc, spk, B, L, E, out);
+int speaker_grad_launch(const float* d_enc, const long long* spk, int B, int L, int E, int nspk, float* out, float* scratch, cudaStream_t st) {
+  if (scratch && E % 4 == 0 && (reinterpret_cast<uintptr_t>(d_enc) & 15) == 0 && (reinterpret_cast<uintptr_t>(scratch) & 15) == 0) {
+    utt_colsum_kernel<<<dim3((unsigned)B, (unsigned)((E + 127) / 128)), 256, 0, st>>>(d_enc, L, E, scratch);
+    speaker_sum_kernel<<<(nspk * E + 255) / 256, 256, 0, st>>>(scratch, spk, B, E, nspk, out);
+  } else {
+    speaker_grad_kernel<<<dim3((unsigned)nspk, (unsigned)((E + 31) / 32)), 256, 0, st>>>(d_enc, spk, B, L, E, out);
+  }
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }
@@ -719,8 +767,7 @@ int desc_bwd_launch(const float* dmem, const float* mem, const float* desc, int 
   return T2_OK;
 }
 int embedding_grad_launch(const float* dx, const long long* chars, long long npos, int E, int nrows, float* out, cudaStream_t st) {
-  T2_REQUIRE(E <= 32 * EG_MAXJ, T2_ERR_UNSUPPORTED, "embedding gradient: encoded_dim %d > %d", E, 32 * EG_MAXJ);
-  embedding_grad_kernel<<<nrows, 256, (size_t)8 * E * sizeof(float), st>>>(dx, chars, npos, E, nrows, out);
+  embedding_grad_kernel<<<dim3((unsigned)nrows, (unsigned)((E + EG_COLS - 1) / EG_COLS)), 256, 0, st>>>(dx, chars, npos, E, nrows, out);
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }

@@ -111,7 +111,8 @@ int prenet_d2_launch(const float* dpre, const __nv_bfloat16* tfp, int B, int T, 
 int prenet_d1_launch(const float* dp1, const float* p1, long long n, float scale, float* d1, cudaStream_t st);
 int prenet_xT_launch(const float* mel_target, int B, int T, int M, int Np, __nv_bfloat16* xT, cudaStream_t st);
 int condition_bwd_launch(const float* dmem, const float* mem, int speaker, float* d_enc, long long rows, int E, int EF, cudaStream_t st);
-int speaker_grad_launch(const float* d_enc, const long long* spk, int B, int L, int E, int nspk, float* out, cudaStream_t st);
+int speaker_grad_launch(const float* d_enc, const long long* spk, int B, int L, int E, int nspk, float* out, float* scratch /*[B][E] or null*/,
+                        cudaStream_t st);
 int desc_bwd_launch(const float* dmem, const float* mem, const float* desc, int B, int L, int E, int D, int Din, float* dpre, float* dW,
                     float* db, cudaStream_t st);
 int embedding_grad_launch(const float* dx, const long long* chars, long long npos, int E, int nrows, float* out, cudaStream_t st);

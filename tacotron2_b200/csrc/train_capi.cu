@@ -727,7 +727,7 @@ static int memory_bwd_impl(t2_ctx* c, const float* memory, const long long* spk,
   if (speaker) {
     T2_REQUIRE(spk, T2_ERR_ARG, "speaker_id tensor required when speaker tokens are active!");
     NEED_GRAD(g_spk, "speaker_embedding.weight", (size_t)c->cfg.num_speakers * E);
-    RC(speaker_grad_launch(d_encoded, spk, B, L, E, c->cfg.num_speakers, g_spk, st));
+    RC(speaker_grad_launch(d_encoded, spk, B, L, E, c->cfg.num_speakers, g_spk, partial /* free again: the GEMM above has reduced it */, st));
   }
   if (D > 0) {
     T2_REQUIRE(desc, T2_ERR_ARG, "description tensor required when description tokens are active!");
