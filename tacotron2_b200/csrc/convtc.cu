@@ -478,6 +478,22 @@ __global__ void embed_split_kernel(const long long* idx, const float* table, __n
   }
 }
 
+// four channels per thread (C % 4 == 0, 16-byte aligned): 16-byte loads, 8-byte stores, one division per four elements
+__global__ void split_cl4_kernel(const float* src, long long src_bstride, __nv_bfloat16* dst, int B, int T, int C) {
+  const int C4 = C >> 2;
+  const long long n4 = (long long)B * T * C4, n = n4 * 4;
+  for (long long i4 = blockIdx.x * (long long)blockDim.x + threadIdx.x; i4 < n4; i4 += (long long)gridDim.x * blockDim.x) {
+    const long long p = i4 / C4;
+    const int c = (int)(i4 - p * C4) * 4;
+    const int b = (int)(p / T), t = (int)(p - (long long)b * T);
+    const float4 v = *reinterpret_cast<const float4*>(src + (size_t)b * src_bstride + (size_t)t * C + c);
+    __align__(8) __nv_bfloat16 hi[4], lo[4];
+    tc::split_bf16(v.x, hi[0], lo[0]); tc::split_bf16(v.y, hi[1], lo[1]); tc::split_bf16(v.z, hi[2], lo[2]); tc::split_bf16(v.w, hi[3], lo[3]);
+    *reinterpret_cast<uint2*>(dst + i4 * 4) = *reinterpret_cast<const uint2*>(hi);
+    *reinterpret_cast<uint2*>(dst + n + i4 * 4) = *reinterpret_cast<const uint2*>(lo);
+  }
+}
+
 inline int gs(long long n) { long long g = (n + 255) / 256; return (int)(g < 1 ? 1 : (g > 148 * 16 ? 148 * 16 : g)); }
 
 }  // namespace
@@ -533,7 +549,11 @@ int convtc_make_halo_maps(ConvTcArgs& a, const __nv_bfloat16* x, int B, int T, i
 
 int split_cl_launch(const float* src, long long src_bstride, __nv_bfloat16* dst, int B, int T, int C, cudaStream_t st) {
   if (B * T == 0) return T2_OK;
-  split_cl_kernel<<<gs((long long)B * T * C), 256, 0, st>>>(src, src_bstride, dst, B, T, C);
+  if (C % 4 == 0 && src_bstride % 4 == 0 && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0 &&
+      ((long long)B * T * C) % 8 == 0)
+    split_cl4_kernel<<<gs((long long)B * T * C / 4), 256, 0, st>>>(src, src_bstride, dst, B, T, C);
+  else
+    split_cl_kernel<<<gs((long long)B * T * C), 256, 0, st>>>(src, src_bstride, dst, B, T, C);
   T2_CHECK_CUDA(cudaGetLastError());
   return T2_OK;
 }

@@ -219,6 +219,25 @@ __global__ void transpose_bf16_kernel(const __nv_bfloat16* __restrict__ src, lon
   }
 }
 
+// the same, four columns per thread (unit column stride, N / strides multiples of 4, 16-byte aligned destination)
+__global__ void gemm_nt_reduce4_kernel(const float* __restrict__ partial, int splitk, int nz, int Mp, int Np, int M, int N, GemmNtOut o) {
+  const int N4 = N >> 2;
+  const long long total = (long long)nz * M * N4;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long mz = i / N4;
+    const int n = (int)(i - mz * N4) * 4;
+    const int m = (int)(mz % M), z = (int)(mz / M);
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int sp = 0; sp < splitk; ++sp) {
+      const float4 v = *reinterpret_cast<const float4*>(partial + (((size_t)sp * nz + z) * Mp + m) * Np + n);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    float4* d = reinterpret_cast<float4*>(o.out + (size_t)m * o.ldm + n + (size_t)z * o.ldz);
+    if (o.accumulate) { const float4 p = *d; *d = make_float4(p.x + o.alpha * s.x, p.y + o.alpha * s.y, p.z + o.alpha * s.z, p.w + o.alpha * s.w); }
+    else *d = make_float4(o.alpha * s.x, o.alpha * s.y, o.alpha * s.z, o.alpha * s.w);
+  }
+}
+
 // 64x64 tiles, 4-byte (bf16x2) global accesses on both sides: 128 B per warp row instead of 64 B.  Needs even C, src_ld, dst_ld,
 // dst_boff, R_ld and 4-byte aligned bases (the launch falls back to the 32x32 kernel otherwise).
 __global__ void __launch_bounds__(256) transpose_bf16x2_kernel(const __nv_bfloat16* __restrict__ src, long long src_ld, long long src_bstride,
@@ -289,6 +308,12 @@ int gemmnt_launch(const GemmNtArgs& a, const GemmNtOut& o, cudaStream_t st) {
   T2_CHECK_CUDA(cudaGetLastError());
   if (a.direct_out) return T2_OK;
   const long long total = (long long)a.nz * a.M * a.N;
+  if (o.ldn == 1 && a.N % 4 == 0 && o.ldm % 4 == 0 && o.ldz % 4 == 0 && (reinterpret_cast<uintptr_t>(o.out) & 15) == 0) {
+    const int g4 = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 8);
+    gemm_nt_reduce4_kernel<<<g4, 256, 0, st>>>(a.partial, a.splitk, a.nz, Mt * 128, Nt * a.NT, a.M, a.N, o);
+    T2_CHECK_CUDA(cudaGetLastError());
+    return T2_OK;
+  }
   const int g = (int)std::min<long long>((total + 255) / 256, 148 * 8);
   gemm_nt_reduce_kernel<<<g, 256, 0, st>>>(a.partial, a.splitk, a.nz, Mt * 128, Nt * a.NT, a.M, a.N, o);
   T2_CHECK_CUDA(cudaGetLastError());
