@@ -10,6 +10,7 @@ kernel -> postnet -> residual/masking.  N > 1: one process per GPU, each with it
 (weak scaling, no data-path collective); timing = max over ranks of device time.
 """
 import argparse
+import gc
 import json
 import os
 import subprocess
@@ -458,10 +459,15 @@ def train_bench(dev, rank, world, steps, warmup=3):
         dist.barrier()
     torch.cuda.synchronize()
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # no Python garbage-collection pass inside the timed region (a full pass over a process that has built two models takes
+    # milliseconds of host time in front of a step's first launch; one r02_v11 run showed a 42.6 ms forward among 23.8 ms ones)
+    gc.collect()
+    gc.disable()
     t0.record()
     losses = [step(True) for _ in range(steps)]
     t1.record()
     t1.synchronize()
+    gc.enable()
     total = t0.elapsed_time(t1)
     if world > 1:
         tt = torch.tensor([total], device=dev, dtype=torch.float64)
@@ -636,9 +642,12 @@ def main():
 
     barrier()
     sampler.mark()
+    gc.collect()
+    gc.disable()   # (see train_bench)
     t_res, t_dec = timed(step_resident, args.steps)
     barrier()
     t_e2e, _ = timed(step_e2e, args.steps)
+    gc.enable()
     barrier()
     clocks = sampler.stop()
     if world > 1:
